@@ -1,0 +1,99 @@
+"""ctypes binding of ``include/lifter_b200.h`` (the C ABI of the sm_100a kernels).
+
+There is no CPU fallback and no PyTorch fallback: if the library cannot be loaded, or a call is made
+without a B200, this module raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import build as _build
+
+_LIB = None
+
+FMT_F16, FMT_BF16 = 0, 1
+OUT_16, OUT_32_SLABS, OUT_32_DIRECT = 0, 1, 2
+ERR_INVALID, ERR_CUDA, ERR_BATCH1, ERR_NODEVICE = -1, -2, -3, -4
+
+
+class LifterConfig(C.Structure):
+    """``lifter_config_t``: the constructor arguments of LinearModel (baselineModel.py:51-56)."""
+    _fields_ = [("i_dim", C.c_int32), ("o_dim", C.c_int32), ("linear_size", C.c_int32), ("num_stage", C.c_int32),
+                ("use_bn", C.c_int32), ("p_dropout", C.c_float), ("bn_eps", C.c_float), ("bn_momentum", C.c_float)]
+
+
+class GemmDesc(C.Structure):
+    """``lifter_gemm_desc_t``"""
+    _fields_ = [("A", C.c_void_p), ("lda", C.c_int64), ("B", C.c_void_p), ("ldb", C.c_int64),
+                ("M", C.c_int32), ("N", C.c_int32), ("K", C.c_int32), ("a_mn_major", C.c_int32),
+                ("b_mn_major", C.c_int32), ("fmt", C.c_int32), ("out_mode", C.c_int32),
+                ("D", C.c_void_p), ("ldd", C.c_int64), ("n_valid", C.c_int32), ("splits", C.c_int32),
+                ("relu", C.c_int32), ("scale", C.c_void_p), ("shift", C.c_void_p), ("residual", C.c_void_p),
+                ("ldr", C.c_int64), ("stat_sum", C.c_void_p), ("stat_sq", C.c_void_p)]
+
+
+_P, _I64, _I32, _F = C.c_void_p, C.c_int64, C.c_int32, C.c_float
+_CFG = C.POINTER(LifterConfig)
+
+# name -> (restype, argtypes); must list every symbol include/lifter_b200.h declares (tests check this)
+SIGNATURES = {
+    "lifter_version": (_I32, []),
+    "lifter_last_error": (C.c_char_p, []),
+    "lifter_device_check": (_I32, []),
+    "lifter_num_param_tensors": (_I32, [_CFG]),
+    "lifter_param_offset": (_I64, [_CFG, _I32]),
+    "lifter_param_numel": (_I64, [_CFG, _I32]),
+    "lifter_param_total": (_I64, [_CFG]),
+    "lifter_operand_bytes": (_I64, [_CFG]),
+    "lifter_eval_workspace_bytes": (_I64, [_CFG, _I64]),
+    "lifter_pack_weights": (_I32, [_CFG, _P, _P, _I32, _P]),
+    "lifter_fold_bn": (_I32, [_CFG, _P, _P, _P, _P, _P]),
+    "lifter_forward_eval": (_I32, [_CFG, _P, _P, _P, _P, _P, _I64, _P, _P, _P, _P, _P, _I64, _I32, _I64, _P]),
+    "lifter_gemm": (_I32, [C.POINTER(GemmDesc), _P]),
+    "lifter_gemm_slab_rows": (_I32, [_I32]),
+    "lifter_gemm_stat_rows": (_I32, [_I32]),
+    "lifter_gemm_effective_splits": (_I32, [_I32, _I32]),
+}
+
+
+def lib():
+    """The loaded C-ABI library; builds it in-tree with nvcc if the prebuilt .so is missing or stale."""
+    global _LIB
+    if _LIB is None:
+        path = _build.lib_path()
+        if not os.path.exists(path) or (_build.is_stale() and os.environ.get("LIFTER_NO_REBUILD") != "1"):
+            path = _build.build()
+        handle = C.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)        # AttributeError if the library does not export it
+            fn.restype, fn.argtypes = res, args
+        _LIB = handle
+    return _LIB
+
+
+def last_error():
+    msg = lib().lifter_last_error()
+    return msg.decode() if msg else ""
+
+
+def check(code, what=""):
+    """Map a negative return code to the exception the reference's PyTorch path would raise."""
+    if code is None or code >= 0:
+        return code
+    msg = last_error() or what
+    if code == ERR_BATCH1:
+        raise ValueError(msg)
+    if code == ERR_INVALID:
+        raise ValueError(msg)
+    raise RuntimeError(msg)
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (or None)."""
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,260 @@
+"""Implementation behind ``baselineModel.py`` (the drop-in import name).
+
+Mirror of the reference's ``phase1_lifting/baselineModel.py`` lifter: ``LinearModel``,
+its residual block ``Linear`` and ``weight_init`` -- same import names, constructor arguments,
+``forward`` signature, ``state_dict`` keys and ``.apply(weight_init)`` behaviour (SURVEY.md §8b,
+reference ``baselineModel.py:10-102``), with all arithmetic in hand-written sm_100a CUDA behind the
+C ABI of ``include/lifter_b200.h``.
+
+Call sites this drops into unchanged: ``train_1.py:17,34,39,44,71,86,114,186``,
+``backup_june8.py:19,70-72,83,118,137-138,174``, ``main.py:395-396``.
+
+There is no CPU path: ``forward`` on a non-CUDA tensor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+
+from . import _autograd, _cabi
+
+__all__ = ["weight_init", "Linear", "LinearModel"]
+
+
+def weight_init(m):
+    """``baselineModel.py:10-12``: kaiming-normal on every ``torch.nn.Linear`` weight (``model.apply``)."""
+    if isinstance(m, torch.nn.Linear):
+        torch.nn.init.kaiming_normal_(m.weight)
+
+
+class Linear(torch.nn.Module):
+    """Residual block of ``baselineModel.py:14-47``: w1, batch_norm1, w2, batch_norm2 (+ relu/dropout).
+
+    It owns the block's parameters under the reference's names; the arithmetic of a block is fused
+    into ``LinearModel.forward`` (two tcgen05 GEMMs with BN/ReLU/dropout/residual around them).
+    """
+
+    def __init__(self, linear_size, p_dropout=0.5, BN=True):
+        super().__init__()
+        self.l_size = linear_size
+        self.relu = torch.nn.ReLU(inplace=True)
+        self.relu2 = torch.nn.ReLU(inplace=True)
+        self.dropout = torch.nn.Dropout(p_dropout)
+        self.dropout2 = torch.nn.Dropout(p_dropout)
+        self.w1 = torch.nn.Linear(self.l_size, self.l_size)
+        self.batch_norm1 = torch.nn.BatchNorm1d(self.l_size)
+        self.w2 = torch.nn.Linear(self.l_size, self.l_size)
+        self.batch_norm2 = torch.nn.BatchNorm1d(self.l_size)
+        self.BN = BN
+
+    def forward(self, x):
+        raise RuntimeError("the residual block runs fused inside LinearModel.forward (sm_100a kernels); "
+                           "it has no standalone or CPU path")
+
+
+class LinearModel(torch.nn.Module):
+    """``baselineModel.py:50-102``.  ``LinearModel(i_dim, o_dim, linear_size=1024, num_stage=2,
+    p_dropout=0.5, BN=True)``; ``forward(x)`` takes ``(B, 17, 2)`` or ``(B, i_dim)`` fp32 CUDA and
+    returns ``(B, o_dim)`` fp32, contiguous and autograd-connected.
+
+    Extras that the reference does not have (all optional, defaults keep reference behaviour):
+      * ``eval_format`` / ``train_format``: 16-bit tensor-core operand format ("fp16" for inference --
+        10-bit mantissa keeps the 0.5 mm / 1e-2 tolerance --, "bf16" for training range);
+      * ``dropout_seed`` / ``dropout_step``: the Philox stream of the dropout masks (reproducible,
+        re-addressable in backward, identical across data-parallel shards of one global batch);
+      * ``row_offset`` / ``global_batch`` / ``process_group``: data-parallel BatchNorm synchronisation.
+    """
+
+    def __init__(self, i_dim, o_dim, linear_size=1024, num_stage=2, p_dropout=0.5, BN=True):
+        super().__init__()
+        self.linear_size = linear_size
+        self.p_dropout = p_dropout
+        self.num_stage = num_stage
+        self.input_size = i_dim
+        self.output_size = o_dim
+
+        # same construction order as the reference => same torch RNG consumption => same default init
+        self.w1 = torch.nn.Linear(self.input_size, self.linear_size)
+        self.batch_norm1 = torch.nn.BatchNorm1d(self.linear_size)
+        self.linear_stages = torch.nn.ModuleList(
+            [Linear(self.linear_size, self.p_dropout, BN) for _ in range(num_stage)])
+        self.w2 = torch.nn.Linear(self.linear_size, self.output_size)
+        self.relu = torch.nn.ReLU(inplace=True)
+        self.dropout = torch.nn.Dropout(self.p_dropout)
+        self.flat = torch.nn.Flatten()
+        self.BN = BN
+
+        self.eval_format = "fp16"
+        self.train_format = "bf16"
+        self.dropout_seed = 0
+        self.dropout_step = 0
+        self.row_offset = 0
+        self.process_group = None            # set by the data-parallel trainer: SyncBN over this group
+        self._cfg = _cabi.LifterConfig(int(i_dim), int(o_dim), int(linear_size), int(num_stage), int(bool(BN)),
+                                       float(p_dropout), 1e-5, 0.1)
+        _cabi.check(_cabi.lib().lifter_param_total(C.byref(self._cfg)))      # validates the shape (ValueError)
+        self._cache = {}
+        self._flatten()
+
+    # ------------------------------------------------------------------ layout
+    def _hidden_layers(self):
+        """(Linear, BatchNorm1d) of every hidden layer in forward order."""
+        yield self.w1, self.batch_norm1
+        for blk in self.linear_stages:
+            yield blk.w1, blk.batch_norm1
+            yield blk.w2, blk.batch_norm2
+
+    def _ordered_params(self):
+        out = []
+        for lin, bn in self._hidden_layers():
+            out += [lin.weight, lin.bias, bn.weight, bn.bias]
+        return out + [self.w2.weight, self.w2.bias]
+
+    def _flatten(self):
+        """Re-home every parameter / BN buffer as a view into one flat buffer (C-ABI layout)."""
+        lib, cfg = _cabi.lib(), C.byref(self._cfg)
+        params = self._ordered_params()
+        dev = params[0].device
+        total = lib.lifter_param_total(cfg)
+        flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        self._offsets = []
+        with torch.no_grad():
+            for t, p in enumerate(params):
+                off, n = lib.lifter_param_offset(cfg, t), lib.lifter_param_numel(cfg, t)
+                assert n == p.numel()
+                flat[off:off + n].copy_(p.detach().reshape(-1).float())
+                p.data = flat[off:off + n].view(p.shape)
+                self._offsets.append((off, n))
+        L, H = 2 * self.num_stage + 1, self.linear_size
+        rm = torch.zeros(L, H, dtype=torch.float32, device=dev)
+        rv = torch.ones(L, H, dtype=torch.float32, device=dev)
+        nbt = torch.zeros(L, dtype=torch.int64, device=dev)
+        with torch.no_grad():
+            for l, (_, bn) in enumerate(self._hidden_layers()):
+                rm[l].copy_(bn.running_mean)
+                rv[l].copy_(bn.running_var)
+                nbt[l].copy_(bn.num_batches_tracked)
+                bn.running_mean, bn.running_var, bn.num_batches_tracked = rm[l], rv[l], nbt[l]
+        self._flat, self._rm, self._rv, self._nbt = flat, rm, rv, nbt
+        self._cache = {}
+
+    def _apply(self, fn, *args, **kwargs):
+        super()._apply(fn, *args, **kwargs)
+        self._flatten()                       # .to(device) / .cuda() / .float(): rebuild the flat views
+        return self
+
+    def _flat_is_intact(self):
+        base = self._flat.data_ptr()
+        for p, (off, _) in zip(self._ordered_params(), self._offsets):
+            if p.data_ptr() != base + 4 * off:
+                return False
+        return self.batch_norm1.running_mean.data_ptr() == self._rm.data_ptr()
+
+    def _versions(self):
+        return tuple(p._version for p in self._ordered_params())
+
+    # ------------------------------------------------------------------ cached device-side derivatives
+    @staticmethod
+    def _fmt_code(name):
+        try:
+            return {"fp16": _cabi.FMT_F16, "float16": _cabi.FMT_F16, "bf16": _cabi.FMT_BF16,
+                    "bfloat16": _cabi.FMT_BF16}[name]
+        except KeyError:
+            raise ValueError(f"unknown operand format {name!r}: use 'fp16' or 'bf16'") from None
+
+    def _operands(self, fmt):
+        """16-bit zero-padded copies of the Linear weights, refreshed when a parameter changed."""
+        if not self._flat_is_intact():
+            self._flatten()
+        key = ("op", fmt)
+        ver = (self._versions(), self._flat.data_ptr())
+        hit = self._cache.get(key)
+        if hit is None or hit[0] != ver:
+            lib, cfg = _cabi.lib(), C.byref(self._cfg)
+            buf = hit[1] if hit is not None and hit[1].device == self._flat.device else torch.empty(
+                lib.lifter_operand_bytes(cfg), dtype=torch.uint8, device=self._flat.device)
+            _cabi.check(lib.lifter_pack_weights(cfg, _cabi.ptr(self._flat), _cabi.ptr(buf), fmt, _cabi.stream_ptr()))
+            self._cache[key] = (ver, buf)
+        return self._cache[key][1]
+
+    def _folded_bn(self):
+        """Eval-mode BatchNorm + bias folded to per-column scale/shift [L][2][H]."""
+        ver = (self._versions(), self._rm._version, self._rv._version,
+               tuple(bn.running_mean._version for _, bn in self._hidden_layers()),
+               tuple(bn.running_var._version for _, bn in self._hidden_layers()), self._flat.data_ptr())
+        hit = self._cache.get("fold")
+        if hit is None or hit[0] != ver:
+            lib, cfg = _cabi.lib(), C.byref(self._cfg)
+            L, H = 2 * self.num_stage + 1, self.linear_size
+            ss = torch.empty(L, 2, H, dtype=torch.float32, device=self._flat.device)
+            _cabi.check(lib.lifter_fold_bn(cfg, _cabi.ptr(self._flat), _cabi.ptr(self._rm), _cabi.ptr(self._rv),
+                                           _cabi.ptr(ss), _cabi.stream_ptr()))
+            self._cache["fold"] = (ver, ss)
+        return self._cache["fold"][1]
+
+    # ------------------------------------------------------------------ forward
+    def _check_input(self, x):
+        if not torch.is_tensor(x):
+            raise TypeError("LinearModel.forward expects a tensor")
+        if not x.is_cuda:
+            raise RuntimeError("LinearModel (sm_100a build) has no CPU path: move the input and the model to a "
+                               "B200 with .to('cuda')")
+        if not self._flat.is_cuda or self._flat.device != x.device:
+            raise RuntimeError(f"input is on {x.device} but the model parameters are on {self._flat.device}")
+        y = x.reshape(x.shape[0], -1)                     # torch.nn.Flatten, baselineModel.py:89
+        if y.shape[1] != self.input_size:
+            raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({y.shape[0]}x{y.shape[1]} and "
+                               f"{self.input_size}x{self.linear_size})")
+        if y.dtype != torch.float32:
+            raise RuntimeError(f"expected a float32 input (the reference calls .float(), train_1.py:80), got {y.dtype}")
+        return y.contiguous()
+
+    def infer(self, x, in_stats=None, out_stats=None, out=None, chunk_rows=0):
+        """Inference without autograd: ``model.eval()`` + ``torch.no_grad()`` forward (train_1.py:112-118).
+
+        ``in_stats=(mean, std)`` / ``out_stats=(mean, std)`` fuse the keypoint standardisation
+        ``(x - mean) / std`` (main.py:334) and the de-standardisation ``y * std + mean`` (main.py:473-479).
+        """
+        y = self._check_input(x)
+        lib, cfg = _cabi.lib(), C.byref(self._cfg)
+        fmt = self._fmt_code(self.eval_format)
+        ops, ss = self._operands(fmt), self._folded_bn()
+        B = y.shape[0]
+        if out is None:
+            out = torch.empty(B, self.output_size, dtype=torch.float32, device=y.device)
+        if B == 0:
+            return out
+        ws_bytes = lib.lifter_eval_workspace_bytes(cfg, B) if chunk_rows == 0 else None
+        if ws_bytes is None:
+            H, Ip = self.linear_size, (self.input_size + 63) // 64 * 64
+            rows = min(B, chunk_rows)
+            ws_bytes = ((rows * Ip * 2 + 1023) // 1024 + 3 * ((rows * H * 2 + 1023) // 1024) + 1) * 1024
+        ws = self._cache.get("eval_ws")
+        if ws is None or ws.numel() < ws_bytes or ws.device != y.device:
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=y.device)
+            self._cache["eval_ws"] = ws
+
+        def _stat(t, n):
+            if t is None:
+                return None
+            t = torch.as_tensor(t, dtype=torch.float32, device=y.device).reshape(-1).contiguous()
+            if t.numel() != n:
+                raise ValueError(f"statistics vector has {t.numel()} entries, expected {n}")
+            return t
+        im, isd = (_stat(in_stats[0], self.input_size), _stat(in_stats[1], self.input_size)) if in_stats else (None, None)
+        om, osd = (_stat(out_stats[0], self.output_size), _stat(out_stats[1], self.output_size)) if out_stats else (None, None)
+        off_b2 = self._offsets[-1][0]
+        _cabi.check(lib.lifter_forward_eval(cfg, _cabi.ptr(ops), _cabi.ptr(ss), C.c_void_p(self._flat.data_ptr() + 4 * off_b2),
+                                            _cabi.ptr(y), _cabi.ptr(out), B, _cabi.ptr(im), _cabi.ptr(isd),
+                                            _cabi.ptr(om), _cabi.ptr(osd), _cabi.ptr(ws), ws.numel(), fmt,
+                                            int(chunk_rows), _cabi.stream_ptr()))
+        return out
+
+    def forward(self, x):
+        y = self._check_input(x)
+        needs_grad = torch.is_grad_enabled() and (y.requires_grad or any(p.requires_grad for p in self.parameters()))
+        if not self.training and not needs_grad:
+            return self.infer(y)
+        return _autograd.lifter_apply(self, y, needs_grad)

@@ -1,0 +1,99 @@
+/* lifter_b200.h -- C ABI of the B200-native phase1_lifting LinearModel hot path.
+ *
+ * The reference (RHnejad/3D_PoseEstimation) has no FFI/plugin layer: its boundary is the Python
+ * nn.Module contract of phase1_lifting/baselineModel.py:50-102.  This header is
+ * what the Python mirror (3d_poseestimation_b200/baselineModel.py, losses.py, trainer.py) binds with
+ * ctypes; every entry point names the reference code it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller (PyTorch's caching allocator) unless it is
+ *     a struct passed by address; the library allocates nothing and never synchronises the host;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*);
+ *   - return value: 0 = OK, negative = error (LIFTER_ERR_*); text via lifter_last_error();
+ *   - "fmt" is the 16-bit operand format of the tensor-core GEMMs: 0 = fp16, 1 = bf16 (fp32 accumulate);
+ *   - flat parameter layout = reference model.parameters() order (baselineModel.py:68-85, 24-28), each
+ *     tensor starting at a multiple of 32 floats: use lifter_param_offset().
+ */
+#ifndef LIFTER_B200_H
+#define LIFTER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LIFTER_OK 0
+#define LIFTER_ERR_INVALID (-1)
+#define LIFTER_ERR_CUDA (-2)
+#define LIFTER_ERR_BATCH1 (-3)   /* train-mode BatchNorm with one row: the reference raises ValueError */
+#define LIFTER_ERR_NODEVICE (-4)
+
+#define LIFTER_FMT_F16 0
+#define LIFTER_FMT_BF16 1
+
+/* constructor arguments of LinearModel (baselineModel.py:51-56) */
+typedef struct lifter_config {
+    int32_t i_dim;        /* input features  (17*2 = 34)            */
+    int32_t o_dim;        /* output features (17*3 = 51), <= 64     */
+    int32_t linear_size;  /* hidden width H: 64..2048, power of two */
+    int32_t num_stage;    /* residual blocks                         */
+    int32_t use_bn;       /* BN flag (baselineModel.py:85)           */
+    float p_dropout;      /* baselineModel.py:81                     */
+    float bn_eps;         /* 1e-5  (torch.nn.BatchNorm1d default)    */
+    float bn_momentum;    /* 0.1                                      */
+} lifter_config_t;
+
+/* ---- library ------------------------------------------------------------------------------- */
+int lifter_version(void);
+const char* lifter_last_error(void);
+int lifter_device_check(void);                       /* 0 if the current device is sm_100 */
+
+/* ---- layout queries (host only) -------------------------------------------------------------- */
+/* Flat fp32 parameter buffer.  tensor index t: per hidden layer l (0 .. 2*num_stage):
+ *   4l+0 Linear.weight [H][in], 4l+1 Linear.bias [H], 4l+2 BatchNorm.weight [H], 4l+3 BatchNorm.bias [H];
+ *   then w2.weight [o_dim][H], w2.bias [o_dim].                                                      */
+int lifter_num_param_tensors(const lifter_config_t* cfg);
+int64_t lifter_param_offset(const lifter_config_t* cfg, int tensor);      /* in floats            */
+int64_t lifter_param_numel(const lifter_config_t* cfg, int tensor);
+int64_t lifter_param_total(const lifter_config_t* cfg);                   /* padded flat length   */
+/* BatchNorm buffers: running_mean | running_var, each [num_layers][H] fp32; num_batches_tracked int64[num_layers] */
+int64_t lifter_operand_bytes(const lifter_config_t* cfg);                 /* 16-bit padded GEMM operand copy of the weights */
+int64_t lifter_eval_workspace_bytes(const lifter_config_t* cfg, int64_t batch);
+
+/* ---- weights -------------------------------------------------------------------------------- */
+/* fp32 flat params -> zero-padded 16-bit operand copies (private to the kernels; refreshed after every update) */
+int lifter_pack_weights(const lifter_config_t* cfg, const float* params, void* operands, int fmt, void* stream);
+/* eval-mode BatchNorm (+ Linear bias) folded to per-column scale/shift [num_layers][2][H]
+ * (torch BatchNorm1d eval: (z - running_mean) / sqrt(running_var + eps) * weight + bias)          */
+int lifter_fold_bn(const lifter_config_t* cfg, const float* params, const float* running_mean,
+                   const float* running_var, float* scale_shift, void* stream);
+
+/* ---- inference: LinearModel.forward under model.eval() + torch.no_grad() (baselineModel.py:87-102) --- */
+/* x [batch][i_dim] fp32 -> out [batch][o_dim] fp32.  in_mean/in_std (nullable, [i_dim]) fuse the input
+ * normalisation (x - mean) / std of main.py:334; out_mean/out_std (nullable, [o_dim]) fuse the
+ * de-standardisation y * std + mean of main.py:473-479.  chunk_rows = 0 picks an L2-resident chunk.   */
+int lifter_forward_eval(const lifter_config_t* cfg, const void* operands, const float* scale_shift,
+                        const float* w2_bias, const float* x, float* out, int64_t batch,
+                        const float* in_mean, const float* in_std, const float* out_mean, const float* out_std,
+                        void* workspace, int64_t workspace_bytes, int fmt, int64_t chunk_rows, void* stream);
+
+/* ---- test hook: one tcgen05 GEMM  D[M][N] = sum_k A(m,k) B(n,k) ------------------------------------ */
+typedef struct lifter_gemm_desc {
+    const void* A; int64_t lda; const void* B; int64_t ldb;
+    int32_t M, N, K, a_mn_major, b_mn_major, fmt;
+    int32_t out_mode;            /* 0: 16-bit [M][ldd], 1: fp32 split-K slabs, 2: fp32 [M][n_valid] */
+    void* D; int64_t ldd; int32_t n_valid; int32_t splits; int32_t relu;
+    const float* scale; const float* shift; const void* residual; int64_t ldr;
+    float* stat_sum; float* stat_sq;
+} lifter_gemm_desc_t;
+int lifter_gemm(const lifter_gemm_desc_t* desc, void* stream);
+int lifter_gemm_slab_rows(int M);
+int lifter_gemm_stat_rows(int M);
+int lifter_gemm_effective_splits(int K, int splits);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LIFTER_B200_H */
