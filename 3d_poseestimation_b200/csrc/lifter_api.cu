@@ -126,7 +126,7 @@ int lifter_forward_eval(const lifter_config_t* cfg, const void* operands, const 
     const int64_t chunk = chunk_rows > 0 ? (chunk_rows < batch ? chunk_rows : batch) : default_eval_chunk(lay, batch);
     LIFTER_REQUIRE(workspace_bytes >= eval_ws_bytes(lay, chunk), "forward_eval: workspace too small (%lld < %lld bytes)",
                    static_cast<long long>(workspace_bytes), static_cast<long long>(eval_ws_bytes(lay, chunk)));
-    LIFTER_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 1023) == 0, "forward_eval: workspace must be 1024-byte aligned");
+    LIFTER_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "forward_eval: workspace must be 256-byte aligned");
 
     uint8_t* ws = static_cast<uint8_t*>(workspace);
     float* out_scale = reinterpret_cast<float*>(ws);

@@ -63,10 +63,10 @@ def test_kmajor_16bit_output(cabi, M, N, K, fmt):
 
 
 @pytest.mark.parametrize("a_mn,b_mn", [(0, 1), (1, 0), (1, 1)])
-@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 256, 128), (1024, 1024, 512), (200, 320, 100)])
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 256, 128), (1024, 1024, 512), (200, 320, 100), (200, 320, 104)])
 def test_mn_major_operands(cabi, M, N, K, a_mn, b_mn):
     fmt = 1
-    if (a_mn and M % 8) or (b_mn and N % 8):
+    if (a_mn and M % 8) or (b_mn and N % 8) or ((not a_mn or not b_mn) and K % 8):
         pytest.skip("row stride must be a multiple of 16 bytes")
     A, B, ref = _operands(M, N, K, a_mn, b_mn, fmt, 2)
     D = torch.full((M, N), float("nan"), device="cuda").to(_dt(fmt))
