@@ -33,8 +33,22 @@ class GemmDesc(C.Structure):
                 ("ldr", C.c_int64), ("stat_sum", C.c_void_p), ("stat_sq", C.c_void_p)]
 
 
+class TrainCtx(C.Structure):
+    """``lifter_train_ctx_t``: one forward/backward pair of the training path."""
+    _fields_ = [("params", C.c_void_p), ("operands", C.c_void_p), ("running_mean", C.c_void_p),
+                ("running_var", C.c_void_p), ("num_batches_tracked", C.c_void_p), ("x", C.c_void_p),
+                ("out", C.c_void_p), ("saved", C.c_void_p), ("saved_bytes", C.c_int64), ("batch", C.c_int64),
+                ("global_batch", C.c_int64), ("row_offset", C.c_int64), ("fmt", C.c_int32), ("bn_mode", C.c_int32),
+                ("apply_dropout", C.c_int32), ("step", C.c_uint32), ("seed", C.c_uint64), ("grad_out", C.c_void_p),
+                ("grad_params", C.c_void_p), ("grad_x", C.c_void_p), ("scratch", C.c_void_p),
+                ("scratch_bytes", C.c_int64)]
+
+
+LOSS_MSE, LOSS_L1, LOSS_MPJPE = 0, 1, 2
+
 _P, _I64, _I32, _F = C.c_void_p, C.c_int64, C.c_int32, C.c_float
 _CFG = C.POINTER(LifterConfig)
+_CTX = C.POINTER(TrainCtx)
 
 # name -> (restype, argtypes); must list every symbol include/lifter_b200.h declares (tests check this)
 SIGNATURES = {
@@ -50,6 +64,23 @@ SIGNATURES = {
     "lifter_pack_weights": (_I32, [_CFG, _P, _P, _I32, _P]),
     "lifter_fold_bn": (_I32, [_CFG, _P, _P, _P, _P, _P]),
     "lifter_forward_eval": (_I32, [_CFG, _P, _P, _P, _P, _P, _I64, _P, _P, _P, _P, _P, _I64, _I32, _I64, _P]),
+    "lifter_train_saved_bytes": (_I64, [_CFG, _I64]),
+    "lifter_train_scratch_bytes": (_I64, [_CFG, _I64]),
+    "lifter_train_fwd_sums_offset": (_I64, [_CFG, _I64, _I32]),
+    "lifter_train_bwd_sums_offset": (_I64, [_CFG, _I64, _I32]),
+    "lifter_train_fwd_layer_gemm": (_I32, [_CFG, _CTX, _I32, _P]),
+    "lifter_train_fwd_layer_finish": (_I32, [_CFG, _CTX, _I32, _P]),
+    "lifter_train_fwd_output": (_I32, [_CFG, _CTX, _P]),
+    "lifter_train_forward": (_I32, [_CFG, _CTX, _P]),
+    "lifter_train_bwd_begin": (_I32, [_CFG, _CTX, _P]),
+    "lifter_train_bwd_layer_stats": (_I32, [_CFG, _CTX, _I32, _P]),
+    "lifter_train_bwd_layer_finish": (_I32, [_CFG, _CTX, _I32, _P]),
+    "lifter_train_backward": (_I32, [_CFG, _CTX, _P]),
+    "lifter_loss_scratch_bytes": (_I64, [_I64, _I32]),
+    "lifter_loss": (_I32, [_P, _P, _I64, _I32, _I32, _I64, _P, _P, _P, _P, _I32, _P]),
+    "lifter_l1_sum": (_I32, [_P, _P, _I64, _I32, _I32, _F, _P, _P, _P]),
+    "lifter_l1_grad": (_I32, [_P, _P, _I64, _I32, _I32, _P, _F, _P, _P, _P]),
+    "lifter_adam_step": (_I32, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _I32, _F, _P]),
     "lifter_gemm": (_I32, [C.POINTER(GemmDesc), _P]),
     "lifter_gemm_slab_rows": (_I32, [_I32]),
     "lifter_gemm_stat_rows": (_I32, [_I32]),

@@ -1,0 +1,436 @@
+// Training path of the lifter behind the C ABI: forward with saved activations, backward, fused loss, Adam.
+//
+// Reference being replaced: the autograd graph torch builds for LinearModel.forward in train mode
+// (baselineModel.py:87-102 with the blocks of :32-47) and loss.backward() / optimizer.step() at
+// train_1.py:94-96.  Per hidden layer l (0 = input stage, 2i+1 / 2i+2 = the two layers of block i):
+//
+//   forward   z_l = a_{l-1} W_l^T                      tcgen05 GEMM, epilogue stores z (16-bit) + column sums
+//             mu, var over the (global) batch           reduce + finalize (SyncBN: all-reduce of the sums between)
+//             a_l = drop(relu(gamma (z-mu) rstd + beta)) [+ block input]     bn_apply_fwd, also stores the active bits
+//   backward  dy = g * active / (1-p);  dgamma = sum dy zhat;  dbeta = sum dy          bwd_stats (+ reduce)
+//             dz = gamma rstd (dy - mean dy - zhat mean(dy zhat))                     bwd_dz
+//             dW_l = dz^T a_{l-1}   (split-K, MN-major operands)                      GEMM + wgrad_reduce
+//             g_{l-1} = dz W_l [+ gradient of the residual stream]                    GEMM (residual in the epilogue)
+#include "../../include/lifter_b200.h"
+#include "elementwise.cuh"
+#include "gemm_sm100.cuh"
+#include "layout.cuh"
+#include "loss_adam.cuh"
+#include "train_kernels.cuh"
+
+using namespace lifter;
+
+namespace {
+
+struct Carver {
+    uint8_t* base; size_t off;
+    explicit Carver(void* b) : base(static_cast<uint8_t*>(b)), off(0) {}
+    template <typename T> T* take(size_t bytes) {
+        T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+        off += align_up(bytes, 256);
+        return p;
+    }
+};
+
+struct SavedWs {                        // forward workspace kept for backward
+    uint16_t* a0;
+    std::vector<uint16_t*> z, a;
+    std::vector<uint8_t*> bits;
+    std::vector<float*> mean_z, rstd, scale, shift;
+    std::vector<double*> sums;
+    std::vector<size_t> sums_off;
+    float *psum, *psq, *out_scale, *out_shift;
+    size_t bytes;
+};
+
+void carve_saved(const Layout& lay, int64_t B, void* base, SavedWs* w) {
+    Carver c(base);
+    const size_t act = static_cast<size_t>(B) * lay.H * 2;
+    w->a0 = c.take<uint16_t>(static_cast<size_t>(B) * lay.Ip * 2);
+    w->z.resize(lay.L); w->a.resize(lay.L); w->bits.resize(lay.L);
+    w->mean_z.resize(lay.L); w->rstd.resize(lay.L); w->scale.resize(lay.L); w->shift.resize(lay.L);
+    w->sums.resize(lay.L); w->sums_off.resize(lay.L);
+    for (int l = 0; l < lay.L; ++l) {
+        w->z[l] = c.take<uint16_t>(act);
+        w->a[l] = c.take<uint16_t>(act);
+        w->bits[l] = c.take<uint8_t>(static_cast<size_t>(B) * lay.H / 8);
+        w->mean_z[l] = c.take<float>(lay.H * 4);
+        w->rstd[l] = c.take<float>(lay.H * 4);
+        w->scale[l] = c.take<float>(lay.H * 4);
+        w->shift[l] = c.take<float>(lay.H * 4);
+        w->sums_off[l] = c.off;
+        w->sums[l] = c.take<double>(2 * lay.H * 8);
+    }
+    const size_t P = gemm_stat_rows(static_cast<int>(B));
+    w->psum = c.take<float>(P * lay.H * 4);
+    w->psq = c.take<float>(P * lay.H * 4);
+    w->out_scale = c.take<float>(64 * 4);
+    w->out_shift = c.take<float>(64 * 4);
+    w->bytes = c.off;
+}
+
+int wgrad_splits(int M, int N, int K) {
+    const int bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+    const int tiles = ceil_div(M, 128) * ceil_div(N, bn);
+    int s = num_sms() / tiles;
+    if (s < 1) s = 1;
+    if (s > 16) s = 16;
+    return gemm_effective_splits(K, s);
+}
+
+struct ScratchWs {                      // backward workspace
+    uint16_t *dO, *G[2], *Gh, *dz;
+    float *pA, *pB, *coef, *slabs;
+    std::vector<double*> bsums;
+    std::vector<size_t> bsums_off;
+    size_t bytes;
+};
+
+void carve_scratch(const Layout& lay, int64_t B, void* base, ScratchWs* w) {
+    Carver c(base);
+    const size_t act = static_cast<size_t>(B) * lay.H * 2;
+    w->dO = c.take<uint16_t>(static_cast<size_t>(B) * lay.Op * 2);
+    w->G[0] = c.take<uint16_t>(act);
+    w->G[1] = c.take<uint16_t>(act);
+    w->Gh = c.take<uint16_t>(act);
+    w->dz = c.take<uint16_t>(act);
+    size_t R = ew_partial_rows(B, lay.H);
+    const size_t R64 = ew_partial_rows(B, 64);
+    size_t pbytes = R * lay.H * 4;
+    if (R64 * 64 * 4 > pbytes) pbytes = R64 * 64 * 4;
+    w->pA = c.take<float>(pbytes);
+    w->pB = c.take<float>(pbytes);
+    w->coef = c.take<float>(3 * lay.H * 4);
+    w->bsums.resize(lay.L); w->bsums_off.resize(lay.L);
+    for (int l = 0; l < lay.L; ++l) {
+        w->bsums_off[l] = c.off;
+        w->bsums[l] = c.take<double>(2 * lay.H * 8);
+    }
+    // split-K slabs: the largest of the wgrad GEMMs
+    const int Bk = static_cast<int>(B);
+    size_t slab = static_cast<size_t>(wgrad_splits(lay.H, lay.Ip, Bk)) * gemm_slab_rows(lay.H) * lay.Ip * 4;
+    const size_t hh = static_cast<size_t>(wgrad_splits(lay.H, lay.H, Bk)) * gemm_slab_rows(lay.H) * lay.H * 4;
+    const size_t oh = static_cast<size_t>(wgrad_splits(lay.Op, lay.H, Bk)) * gemm_slab_rows(lay.Op) * lay.H * 4;
+    if (lay.S > 0 && hh > slab) slab = hh;
+    if (oh > slab) slab = oh;
+    w->slabs = c.take<float>(slab);
+    w->bytes = c.off;
+}
+
+int check_ctx(const lifter_config_t* cfg, const lifter_train_ctx_t* t, Layout* lay, bool backward) {
+    LIFTER_PROPAGATE(make_layout(cfg, lay));
+    LIFTER_REQUIRE(t != nullptr, "train: null context");
+    LIFTER_REQUIRE(t->batch >= 1 && t->batch < (1ll << 31), "train: batch %lld out of range", static_cast<long long>(t->batch));
+    LIFTER_REQUIRE(t->global_batch >= t->batch, "train: global_batch < batch");
+    LIFTER_REQUIRE(t->fmt == FMT_F16 || t->fmt == FMT_BF16, "train: unknown operand format %d", t->fmt);
+    LIFTER_REQUIRE(t->params && t->operands && t->saved, "train: null pointer");
+    LIFTER_REQUIRE((reinterpret_cast<uintptr_t>(t->saved) & 255) == 0, "train: workspace must be 256-byte aligned");
+    SavedWs s;
+    carve_saved(*lay, t->batch, nullptr, &s);
+    LIFTER_REQUIRE(t->saved_bytes >= static_cast<int64_t>(s.bytes), "train: saved workspace too small (%lld < %lld)",
+                   static_cast<long long>(t->saved_bytes), static_cast<long long>(s.bytes));
+    if (backward) {
+        LIFTER_REQUIRE(t->grad_out && t->grad_params && t->scratch, "backward: null pointer");
+        LIFTER_REQUIRE((reinterpret_cast<uintptr_t>(t->scratch) & 255) == 0, "backward: scratch must be 256-byte aligned");
+        ScratchWs b;
+        carve_scratch(*lay, t->batch, nullptr, &b);
+        LIFTER_REQUIRE(t->scratch_bytes >= static_cast<int64_t>(b.bytes), "backward: scratch too small (%lld < %lld)",
+                       static_cast<long long>(t->scratch_bytes), static_cast<long long>(b.bytes));
+    } else {
+        LIFTER_REQUIRE(t->x && t->out, "forward: null pointer");
+        if (cfg->use_bn && t->bn_mode == 0 && t->global_batch == 1) {
+            set_error("Expected more than 1 value per channel when training, got input size torch.Size([1, %d])", lay->H);
+            return LIFTER_ERR_BATCH1;
+        }
+        LIFTER_REQUIRE(!(cfg->use_bn && t->bn_mode == 1) || (t->running_mean && t->running_var),
+                       "forward: running statistics required in eval mode");
+    }
+    return LIFTER_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int64_t lifter_train_saved_bytes(const lifter_config_t* cfg, int64_t batch) {
+    Layout lay;
+    if (make_layout(cfg, &lay) != 0) return LIFTER_ERR_INVALID;
+    if (batch < 1) { set_error("batch must be >= 1"); return LIFTER_ERR_INVALID; }
+    SavedWs s;
+    carve_saved(lay, batch, nullptr, &s);
+    return static_cast<int64_t>(s.bytes);
+}
+int64_t lifter_train_scratch_bytes(const lifter_config_t* cfg, int64_t batch) {
+    Layout lay;
+    if (make_layout(cfg, &lay) != 0) return LIFTER_ERR_INVALID;
+    if (batch < 1) { set_error("batch must be >= 1"); return LIFTER_ERR_INVALID; }
+    ScratchWs s;
+    carve_scratch(lay, batch, nullptr, &s);
+    return static_cast<int64_t>(s.bytes);
+}
+int64_t lifter_train_fwd_sums_offset(const lifter_config_t* cfg, int64_t batch, int layer) {
+    Layout lay;
+    if (make_layout(cfg, &lay) != 0) return LIFTER_ERR_INVALID;
+    if (layer < 0 || layer >= lay.L || batch < 1) { set_error("layer/batch out of range"); return LIFTER_ERR_INVALID; }
+    SavedWs s;
+    carve_saved(lay, batch, nullptr, &s);
+    return static_cast<int64_t>(s.sums_off[layer]);
+}
+int64_t lifter_train_bwd_sums_offset(const lifter_config_t* cfg, int64_t batch, int layer) {
+    Layout lay;
+    if (make_layout(cfg, &lay) != 0) return LIFTER_ERR_INVALID;
+    if (layer < 0 || layer >= lay.L || batch < 1) { set_error("layer/batch out of range"); return LIFTER_ERR_INVALID; }
+    ScratchWs s;
+    carve_scratch(lay, batch, nullptr, &s);
+    return static_cast<int64_t>(s.bsums_off[layer]);
+}
+
+// ---------------------------------------------------------------------------------------------- forward
+int lifter_train_fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, false));
+    LIFTER_REQUIRE(l >= 0 && l < lay.L, "forward: layer %d out of range", l);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SavedWs w;
+    carve_saved(lay, t->batch, t->saved, &w);
+    const int B = static_cast<int>(t->batch), H = lay.H;
+    const uint16_t* ops = static_cast<const uint16_t*>(t->operands);
+    if (l == 0) LIFTER_PROPAGATE(prep_input(t->x, B, lay.I, lay.Ip, nullptr, nullptr, w.a0, t->fmt, st));
+    const bool stats = cfg->use_bn && t->bn_mode == 0;
+    GemmArgs g;
+    g.A = l == 0 ? w.a0 : w.a[l - 1]; g.lda = lay.in_pad(l);
+    g.B = ops + lay.w_off[l]; g.ldb = lay.in_pad(l);
+    g.M = B; g.N = H; g.K = lay.in_pad(l); g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.D = w.z[l]; g.ldd = H;
+    if (stats) { g.stat_sum = w.psum; g.stat_sq = w.psq; }
+    LIFTER_PROPAGATE(gemm_launch(g, st));
+    if (stats) LIFTER_PROPAGATE(reduce_rows_f64(w.psum, w.psq, gemm_stat_rows(B), H, w.sums[l], w.sums[l] + H, st));
+    return LIFTER_OK;
+}
+
+int lifter_train_fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, false));
+    LIFTER_REQUIRE(l >= 0 && l < lay.L, "forward: layer %d out of range", l);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SavedWs w;
+    carve_saved(lay, t->batch, t->saved, &w);
+    const int H = lay.H;
+    BnFwdFinalize f;
+    f.sums = w.sums[l]; f.count = static_cast<double>(t->global_batch);
+    f.bias = t->params + lay.p_off[lay.t_bias(l)];
+    f.gamma = t->params + lay.p_off[lay.t_gamma(l)];
+    f.beta = t->params + lay.p_off[lay.t_beta(l)];
+    f.running_mean = t->running_mean ? t->running_mean + static_cast<int64_t>(l) * H : nullptr;
+    f.running_var = t->running_var ? t->running_var + static_cast<int64_t>(l) * H : nullptr;
+    f.num_batches_tracked = t->num_batches_tracked ? reinterpret_cast<long long*>(t->num_batches_tracked) + l : nullptr;
+    f.momentum = cfg->bn_momentum; f.eps = cfg->bn_eps; f.H = H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode;
+    f.mean_z = w.mean_z[l]; f.rstd = w.rstd[l]; f.scale = w.scale[l]; f.shift = w.shift[l];
+    LIFTER_PROPAGATE(bn_finalize_fwd(f, st));
+    BnApplyFwd a;
+    a.z = w.z[l]; a.scale = w.scale[l]; a.shift = w.shift[l];
+    a.resid = (l >= 2 && l % 2 == 0) ? w.a[l - 2] : nullptr;                // out = x + y, baselineModel.py:45
+    a.rows = t->batch; a.H = H; a.fmt = t->fmt;
+    a.apply_dropout = t->apply_dropout && cfg->p_dropout > 0.0f; a.p = cfg->p_dropout;
+    a.seed = t->seed; a.step = t->step; a.site = static_cast<unsigned>(l); a.row_offset = t->row_offset;
+    a.a = w.a[l]; a.bits = w.bits[l];
+    LIFTER_PROPAGATE(bn_apply_fwd(a, st));
+    return LIFTER_OK;
+}
+
+int lifter_train_fwd_output(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, false));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SavedWs w;
+    carve_saved(lay, t->batch, t->saved, &w);
+    LIFTER_PROPAGATE(make_out_affine(t->params + lay.p_off[lay.t_b2()], nullptr, nullptr, lay.O, lay.Op, w.out_scale,
+                                     w.out_shift, st));
+    GemmArgs g;
+    g.A = w.a[lay.L - 1]; g.lda = lay.H;
+    g.B = static_cast<const uint16_t*>(t->operands) + lay.w_off[lay.L]; g.ldb = lay.H;
+    g.M = static_cast<int>(t->batch); g.N = lay.Op; g.K = lay.H; g.fmt = t->fmt; g.out_mode = OUT_32_DIRECT;
+    g.D = t->out; g.n_valid = lay.O; g.scale = w.out_scale; g.shift = w.out_shift;
+    return gemm_launch(g, st);
+}
+
+int lifter_train_forward(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, false));
+    for (int l = 0; l < lay.L; ++l) {
+        LIFTER_PROPAGATE(lifter_train_fwd_layer_gemm(cfg, t, l, stream));
+        LIFTER_PROPAGATE(lifter_train_fwd_layer_finish(cfg, t, l, stream));
+    }
+    return lifter_train_fwd_output(cfg, t, stream);
+}
+
+// ---------------------------------------------------------------------------------------------- backward
+static int wgrad(const Layout& lay, const lifter_train_ctx_t* t, const ScratchWs& b, const uint16_t* dz, int M, long ldz,
+                 const uint16_t* a_in, int N, long lda_in, int rows_valid, int cols_valid, float* grad, cudaStream_t st) {
+    const int B = static_cast<int>(t->batch);
+    GemmArgs g;                                                   // dW[M][N] = dz^T [M][B] * a_in [B][N]
+    g.A = dz; g.lda = ldz; g.a_mn_major = 1;
+    g.B = a_in; g.ldb = lda_in; g.b_mn_major = 1;
+    g.M = M; g.N = N; g.K = B; g.fmt = t->fmt; g.out_mode = OUT_32_TMA; g.D = b.slabs; g.ldd = N;
+    g.splits = wgrad_splits(M, N, B);
+    LIFTER_PROPAGATE(gemm_launch(g, st));
+    return wgrad_reduce(b.slabs, gemm_effective_splits(B, g.splits), gemm_slab_rows(M), N, rows_valid, cols_valid, grad, st);
+}
+
+int lifter_train_bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SavedWs w; ScratchWs b;
+    carve_saved(lay, t->batch, t->saved, &w);
+    carve_scratch(lay, t->batch, t->scratch, &b);
+    const int B = static_cast<int>(t->batch), H = lay.H;
+    const uint16_t* ops = static_cast<const uint16_t*>(t->operands);
+    // grad_out -> 16-bit padded, bias gradient of the output layer
+    LIFTER_PROPAGATE(prep_grad_out(t->grad_out, B, lay.O, lay.Op, t->fmt, b.dO, b.pA, st));
+    LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(B, lay.Op), lay.O, t->grad_params + lay.p_off[lay.t_b2()], st));
+    // dW2 = dOut^T a_{L-1}
+    LIFTER_PROPAGATE(wgrad(lay, t, b, b.dO, lay.Op, lay.Op, w.a[lay.L - 1], H, H, lay.O, H,
+                           t->grad_params + lay.p_off[lay.t_w2()], st));
+    // gradient of the residual stream at the top: g = dOut W2
+    GemmArgs g;
+    g.A = b.dO; g.lda = lay.Op; g.B = ops + lay.w_off[lay.L]; g.ldb = H; g.b_mn_major = 1;
+    g.M = B; g.N = H; g.K = lay.Op; g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.D = b.G[0]; g.ldd = H;
+    return gemm_launch(g, st);
+}
+
+// which buffer holds the incoming gradient g_l of hidden layer l, given that the stream gradient after
+// bwd_begin sits in G[0] and flips at every block boundary
+static const uint16_t* g_in(const Layout& lay, const ScratchWs& b, int l) {
+    if (l % 2 == 1) return b.Gh;                                  // first layer of a block: dh from the second
+    const int block_from_top = (lay.L - 1 - l) / 2;               // l even: stream gradient dX
+    return b.G[block_from_top & 1];
+}
+
+int lifter_train_bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
+    LIFTER_REQUIRE(l >= 0 && l < lay.L, "backward: layer %d out of range", l);
+    if (!cfg->use_bn) return LIFTER_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SavedWs w; ScratchWs b;
+    carve_saved(lay, t->batch, t->saved, &w);
+    carve_scratch(lay, t->batch, t->scratch, &b);
+    const int H = lay.H;
+    BwdCommon c;
+    c.g = g_in(lay, b, l); c.z = w.z[l]; c.bits = w.bits[l]; c.mean_z = w.mean_z[l]; c.rstd = w.rstd[l];
+    c.rows = t->batch; c.H = H; c.fmt = t->fmt;
+    const bool drop = t->apply_dropout && cfg->p_dropout > 0.0f;
+    c.inv_keep = drop ? (cfg->p_dropout < 1.0f ? 1.0f / (1.0f - cfg->p_dropout) : 0.0f) : 1.0f;
+    LIFTER_PROPAGATE(bwd_stats(c, b.pA, b.pB, st));
+    LIFTER_PROPAGATE(reduce_rows_f64(b.pA, b.pB, ew_partial_rows(t->batch, H), H, b.bsums[l], b.bsums[l] + H, st));
+    // parameter gradients from the LOCAL sums (the data-parallel gradient all-reduce adds the shards)
+    return bn_param_grads(b.bsums[l], H, t->grad_params + lay.p_off[lay.t_gamma(l)],
+                          t->grad_params + lay.p_off[lay.t_beta(l)], st);
+}
+
+int lifter_train_bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
+    LIFTER_REQUIRE(l >= 0 && l < lay.L, "backward: layer %d out of range", l);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SavedWs w; ScratchWs b;
+    carve_saved(lay, t->batch, t->saved, &w);
+    carve_scratch(lay, t->batch, t->scratch, &b);
+    const int B = static_cast<int>(t->batch), H = lay.H;
+    const uint16_t* ops = static_cast<const uint16_t*>(t->operands);
+
+    BnBwdFinalize f;
+    f.sums = b.bsums[l]; f.count = static_cast<double>(t->global_batch);
+    f.gamma = t->params + lay.p_off[lay.t_gamma(l)]; f.rstd = w.rstd[l];
+    f.H = H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode; f.coef = b.coef;
+    LIFTER_PROPAGATE(bn_finalize_bwd(f, st));
+    if (!cfg->use_bn) {                                            // the BN affine exists but is unused: zero gradient
+        LIFTER_CHECK_CUDA(cudaMemsetAsync(t->grad_params + lay.p_off[lay.t_gamma(l)], 0, H * 4, st));
+        LIFTER_CHECK_CUDA(cudaMemsetAsync(t->grad_params + lay.p_off[lay.t_beta(l)], 0, H * 4, st));
+    }
+
+    BwdCommon c;
+    c.g = g_in(lay, b, l); c.z = w.z[l]; c.bits = w.bits[l]; c.mean_z = w.mean_z[l]; c.rstd = w.rstd[l];
+    c.rows = t->batch; c.H = H; c.fmt = t->fmt;
+    const bool drop = t->apply_dropout && cfg->p_dropout > 0.0f;
+    c.inv_keep = drop ? (cfg->p_dropout < 1.0f ? 1.0f / (1.0f - cfg->p_dropout) : 0.0f) : 1.0f;
+    LIFTER_PROPAGATE(bwd_dz(c, b.coef, b.dz, b.pA, st));
+    LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(t->batch, H), H, t->grad_params + lay.p_off[lay.t_bias(l)], st));
+
+    // dW_l = dz^T a_{l-1}
+    const uint16_t* a_in = l == 0 ? w.a0 : w.a[l - 1];
+    LIFTER_PROPAGATE(wgrad(lay, t, b, b.dz, H, H, a_in, lay.in_pad(l), lay.in_pad(l), H, lay.in_dim(l),
+                           t->grad_params + lay.p_off[lay.t_weight(l)], st));
+
+    if (l == 0) {
+        if (t->grad_x == nullptr) return LIFTER_OK;
+        GemmArgs g;                                                // dx = dz_0 W1   (input gradient, phase-5 call site)
+        g.A = b.dz; g.lda = H; g.B = ops + lay.w_off[0]; g.ldb = lay.Ip; g.b_mn_major = 1;
+        g.M = B; g.N = lay.Ip; g.K = H; g.fmt = t->fmt;
+        if (lay.Ip <= 64) {
+            g.out_mode = OUT_32_DIRECT; g.D = t->grad_x; g.n_valid = lay.I;
+        } else {
+            LIFTER_REQUIRE(lay.I % 4 == 0, "input gradient needs i_dim %% 4 == 0 when i_dim > 64 (got %d)", lay.I);
+            g.N = lay.I; g.out_mode = OUT_32_TMA; g.D = t->grad_x; g.ldd = lay.I;
+        }
+        return gemm_launch(g, st);
+    }
+    GemmArgs g;                                                    // g_{l-1} = dz_l W_l (+ stream gradient)
+    g.A = b.dz; g.lda = H; g.B = ops + lay.w_off[l]; g.ldb = H; g.b_mn_major = 1;
+    g.M = B; g.N = H; g.K = H; g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.ldd = H;
+    if (l % 2 == 0) {
+        g.D = b.Gh;                                                // second layer of a block -> dh
+    } else {
+        const int block_from_top = (lay.L - 1 - (l + 1)) / 2;     // the block whose output gradient we consumed
+        g.residual = b.G[block_from_top & 1]; g.ldr = H;           // dX_i = dX_{i+1} + dz W
+        g.D = b.G[(block_from_top + 1) & 1];
+    }
+    return gemm_launch(g, st);
+}
+
+int lifter_train_backward(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
+    LIFTER_PROPAGATE(lifter_train_bwd_begin(cfg, t, stream));
+    for (int l = lay.L - 1; l >= 0; --l) {
+        LIFTER_PROPAGATE(lifter_train_bwd_layer_stats(cfg, t, l, stream));
+        LIFTER_PROPAGATE(lifter_train_bwd_layer_finish(cfg, t, l, stream));
+    }
+    return LIFTER_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- loss / optimiser
+int64_t lifter_loss_scratch_bytes(int64_t rows, int joints) {
+    if (rows < 1 || joints < 1) return LIFTER_ERR_INVALID;
+    return static_cast<int64_t>(loss_partial_rows(rows)) * (1 + joints) * 4;
+}
+
+int lifter_loss(const float* pred, const float* target, int64_t rows, int joints, int kind, int64_t global_rows,
+                const float* stdv, float* dpred, float* scratch, float* out, int accumulate_metric, void* stream) {
+    LIFTER_REQUIRE(pred && target && scratch && out, "loss: null pointer");
+    return fused_loss(pred, target, rows, joints, kind, static_cast<double>(global_rows), stdv, dpred, scratch, out,
+                      accumulate_metric, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, float scale, float* scratch,
+                  float* out, void* stream) {
+    LIFTER_REQUIRE(a && b && scratch && out, "l1_sum: null pointer");
+    return l1_sum(a, b, n, row_len, centre, scale, scratch, out, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, const float* gscale,
+                   float scale, float* da, float* db, void* stream) {
+    LIFTER_REQUIRE(a && b && da, "l1_grad: null pointer");
+    return l1_grad(a, b, n, row_len, centre, gscale, scale, da, db, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                     float eps, float weight_decay, int decoupled, int step, float grad_scale, void* stream) {
+    LIFTER_REQUIRE(p && g && m && v, "adam: null pointer");
+    AdamArgs a;
+    a.p = p; a.g = g; a.m = m; a.v = v; a.n = n; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
+    a.weight_decay = weight_decay; a.decoupled = decoupled; a.step = step; a.grad_scale = grad_scale;
+    return adam_step(a, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,236 @@
+#include "loss_adam.cuh"
+
+#include <math.h>
+
+namespace lifter {
+
+namespace {
+
+constexpr int LOSS_THREADS = 256;
+constexpr int LOSS_ROWS_PER_BLOCK = 64;
+constexpr int MAX_J = 21;                       // 64 output columns / 3
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+    return v;
+}
+
+// one thread per (row, joint): coalesced enough for 204-byte rows (consecutive threads = consecutive joints)
+__global__ void __launch_bounds__(LOSS_THREADS) fused_loss_kernel(const float* __restrict__ pred,
+                                                                  const float* __restrict__ target, long rows, int J,
+                                                                  int kind, float inv_count,
+                                                                  const float* __restrict__ stdv,
+                                                                  float* __restrict__ dpred,
+                                                                  float* __restrict__ partials) {
+    __shared__ float sh_loss[LOSS_THREADS / 32];
+    __shared__ float sh_metric[MAX_J];
+    if (threadIdx.x < MAX_J) sh_metric[threadIdx.x] = 0.0f;
+    __syncthreads();
+    const long row0 = static_cast<long>(blockIdx.x) * LOSS_ROWS_PER_BLOCK;
+    const int items = LOSS_ROWS_PER_BLOCK * J;
+    float loss = 0.0f;
+    const int O = 3 * J;
+    const float g_mse = 2.0f * inv_count / O, g_l1 = inv_count / O, g_mp = inv_count / J;
+    for (int it = threadIdx.x; it < items; it += LOSS_THREADS) {
+        const int r = it / J, j = it - r * J;
+        const long row = row0 + r;
+        if (row >= rows) break;
+        const long o = row * O + 3 * j;
+        const float dx = pred[o] - target[o], dy = pred[o + 1] - target[o + 1], dz = pred[o + 2] - target[o + 2];
+        float gx, gy, gz;
+        if (kind == LOSS_MSE) {
+            loss += dx * dx + dy * dy + dz * dz;
+            gx = g_mse * dx; gy = g_mse * dy; gz = g_mse * dz;
+        } else if (kind == LOSS_L1) {
+            loss += fabsf(dx) + fabsf(dy) + fabsf(dz);
+            gx = dx > 0 ? g_l1 : (dx < 0 ? -g_l1 : 0.0f);
+            gy = dy > 0 ? g_l1 : (dy < 0 ? -g_l1 : 0.0f);
+            gz = dz > 0 ? g_l1 : (dz < 0 ? -g_l1 : 0.0f);
+        } else {
+            const float nrm = sqrtf(dx * dx + dy * dy + dz * dz);
+            loss += nrm;
+            const float s = nrm > 0.0f ? g_mp / nrm : 0.0f;            // torch.norm backward is 0 at 0
+            gx = s * dx; gy = s * dy; gz = s * dz;
+        }
+        if (dpred != nullptr) { dpred[o] = gx; dpred[o + 1] = gy; dpred[o + 2] = gz; }
+        float mx = dx, my = dy, mz = dz;
+        if (stdv != nullptr) { mx *= stdv[3 * j]; my *= stdv[3 * j + 1]; mz *= stdv[3 * j + 2]; }
+        atomicAdd(&sh_metric[j], sqrtf(mx * mx + my * my + mz * mz));   // shared-memory atomics, <= 64 rows deep
+    }
+    loss = warp_sum(loss);
+    if ((threadIdx.x & 31) == 0) sh_loss[threadIdx.x >> 5] = loss;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f;
+        for (int w = 0; w < LOSS_THREADS / 32; ++w) t += sh_loss[w];
+        partials[static_cast<long>(blockIdx.x) * (1 + J)] = t;
+    }
+    if (threadIdx.x < J) partials[static_cast<long>(blockIdx.x) * (1 + J) + 1 + threadIdx.x] = sh_metric[threadIdx.x];
+}
+
+// single block: fixed-order reduction of the per-block partials
+__global__ void loss_finalize_kernel(const float* __restrict__ partials, int nblk, int J, float loss_scale,
+                                     float* __restrict__ out, int accumulate_metric) {
+    __shared__ double sh[32][MAX_J + 1];
+    const int c = threadIdx.x % 32, lane_r = threadIdx.x / 32;          // 32 columns x 32 row lanes
+    double s = 0.0;
+    if (c < 1 + J)
+        for (int b = lane_r; b < nblk; b += 32) s += static_cast<double>(partials[static_cast<long>(b) * (1 + J) + c]);
+    if (c < 1 + J) sh[lane_r][c] = s;
+    __syncthreads();
+    if (lane_r == 0 && c < 1 + J) {
+        double t = 0.0;
+        for (int r = 0; r < 32; ++r) t += sh[r][c];
+        if (c == 0) out[0] = static_cast<float>(t * loss_scale);
+        else if (accumulate_metric) out[c] += static_cast<float>(t);
+        else out[c] = static_cast<float>(t);
+    }
+}
+
+constexpr int L1_THREADS = 256;
+constexpr int L1_PER_THREAD = 8;
+
+__global__ void __launch_bounds__(L1_THREADS) l1_sum_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                            long n, int row_len, int centre,
+                                                            float* __restrict__ partials) {
+    __shared__ float sh[L1_THREADS / 32];
+    const long base = (static_cast<long>(blockIdx.x) * L1_THREADS + threadIdx.x) * L1_PER_THREAD;
+    float s = 0.0f;
+#pragma unroll
+    for (int e = 0; e < L1_PER_THREAD; ++e) {
+        const long i = base + e;
+        if (i < n) {
+            float d = a[i] - b[i];
+            if (centre && i >= row_len) { const long c = i % row_len; d -= a[c] - b[c]; }
+            s += fabsf(d);
+        }
+    }
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f;
+        for (int w = 0; w < L1_THREADS / 32; ++w) t += sh[w];
+        partials[blockIdx.x] = t;
+    }
+}
+
+__global__ void l1_finalize_kernel(const float* __restrict__ partials, int nblk, float scale, float* __restrict__ out) {
+    __shared__ double sh[256];
+    double s = 0.0;
+    for (int b = threadIdx.x; b < nblk; b += 256) s += static_cast<double>(partials[b]);
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int i = 0; i < 256; ++i) t += sh[i];
+        out[0] = static_cast<float>(t * scale);
+    }
+}
+
+__global__ void l1_grad_kernel(const float* __restrict__ a, const float* __restrict__ b, long n, int row_len,
+                               int centre, const float* __restrict__ gscale, float scale, float* __restrict__ da,
+                               float* __restrict__ db) {
+    const long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float gs = (gscale != nullptr ? gscale[0] : 1.0f) * scale;
+    float g;
+    if (!centre || i >= row_len) {
+        float d = a[i] - b[i];
+        if (centre) { const long c = i % row_len; d -= a[c] - b[c]; }
+        g = d > 0 ? gs : (d < 0 ? -gs : 0.0f);
+    } else {                                   // element of row 0: own term minus every other row's gradient
+        const float d0 = a[i] - b[i];
+        g = d0 > 0 ? gs : (d0 < 0 ? -gs : 0.0f);
+        const long rows = n / row_len;
+        for (long r = 1; r < rows; ++r) {
+            const float d = (a[r * row_len + i] - b[r * row_len + i]) - d0;
+            g -= d > 0 ? gs : (d < 0 ? -gs : 0.0f);
+        }
+    }
+    da[i] = g;
+    if (db != nullptr) db[i] = -g;
+}
+
+__global__ void __launch_bounds__(256) adam_kernel(AdamArgs a, float step_size, float inv_sqrt_bc2, float decay) {
+    const long n4 = a.n >> 2;
+    const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+    for (long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        float4 p = reinterpret_cast<float4*>(a.p)[i];
+        const float4 g4 = reinterpret_cast<const float4*>(a.g)[i];
+        float4 m = reinterpret_cast<float4*>(a.m)[i];
+        float4 v = reinterpret_cast<float4*>(a.v)[i];
+        float* pp = &p.x; const float* gp = &g4.x; float* mp = &m.x; float* vp = &v.x;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            float g = gp[e] * a.grad_scale;
+            if (a.decoupled) pp[e] *= decay;                            // AdamW: p *= 1 - lr * wd
+            else if (a.weight_decay != 0.0f) g = fmaf(a.weight_decay, pp[e], g);
+            mp[e] = a.beta1 * mp[e] + (1.0f - a.beta1) * g;
+            vp[e] = a.beta2 * vp[e] + (1.0f - a.beta2) * g * g;
+            const float denom = sqrtf(vp[e]) * inv_sqrt_bc2 + a.eps;
+            pp[e] -= step_size * (mp[e] / denom);
+        }
+        reinterpret_cast<float4*>(a.p)[i] = p;
+        reinterpret_cast<float4*>(a.m)[i] = m;
+        reinterpret_cast<float4*>(a.v)[i] = v;
+    }
+}
+
+}  // namespace
+
+int loss_partial_rows(int64_t rows) { return static_cast<int>((rows + LOSS_ROWS_PER_BLOCK - 1) / LOSS_ROWS_PER_BLOCK); }
+
+int fused_loss(const float* pred, const float* target, int64_t rows, int J, int kind, double count, const float* stdv,
+               float* dpred, float* partials, float* out, int accumulate_metric, cudaStream_t st) {
+    LIFTER_REQUIRE(J >= 1 && J <= MAX_J, "fused_loss: %d joints unsupported (1..%d)", J, MAX_J);
+    LIFTER_REQUIRE(kind >= LOSS_MSE && kind <= LOSS_MPJPE, "fused_loss: unknown loss kind %d", kind);
+    LIFTER_REQUIRE(rows >= 1 && count >= 1.0, "fused_loss: empty batch");
+    const int nblk = loss_partial_rows(rows);
+    const float inv_count = static_cast<float>(1.0 / count);
+    fused_loss_kernel<<<nblk, LOSS_THREADS, 0, st>>>(pred, target, rows, J, kind, inv_count, stdv, dpred, partials);
+    LIFTER_CHECK_CUDA(cudaGetLastError());
+    const double denom = kind == LOSS_MPJPE ? count * J : count * 3.0 * J;
+    loss_finalize_kernel<<<1, 1024, 0, st>>>(partials, nblk, J, static_cast<float>(1.0 / denom), out, accumulate_metric);
+    LIFTER_CHECK_CUDA(cudaGetLastError());
+    return LIFTER_OK;
+}
+
+int l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, float scale, float* partials, float* out,
+           cudaStream_t st) {
+    LIFTER_REQUIRE(n >= 1 && row_len >= 1 && n % row_len == 0, "l1_sum: bad shape");
+    const int nblk = static_cast<int>((n + L1_THREADS * L1_PER_THREAD - 1) / (L1_THREADS * L1_PER_THREAD));
+    l1_sum_kernel<<<nblk, L1_THREADS, 0, st>>>(a, b, n, row_len, centre, partials);
+    LIFTER_CHECK_CUDA(cudaGetLastError());
+    l1_finalize_kernel<<<1, 256, 0, st>>>(partials, nblk, scale, out);
+    LIFTER_CHECK_CUDA(cudaGetLastError());
+    return LIFTER_OK;
+}
+
+int l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, const float* gscale, float scale,
+            float* da, float* db, cudaStream_t st) {
+    LIFTER_REQUIRE(n >= 1 && row_len >= 1 && n % row_len == 0, "l1_grad: bad shape");
+    l1_grad_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a, b, n, row_len, centre, gscale, scale, da, db);
+    LIFTER_CHECK_CUDA(cudaGetLastError());
+    return LIFTER_OK;
+}
+
+int adam_step(const AdamArgs& a, cudaStream_t st) {
+    LIFTER_REQUIRE(a.n % 4 == 0, "adam: flat buffer length must be a multiple of 4");
+    LIFTER_REQUIRE(a.step >= 1, "adam: step is 1-based");
+    const double bc1 = 1.0 - pow(static_cast<double>(a.beta1), a.step);
+    const double bc2 = 1.0 - pow(static_cast<double>(a.beta2), a.step);
+    const float step_size = static_cast<float>(a.lr / bc1);
+    const float inv_sqrt_bc2 = static_cast<float>(1.0 / sqrt(bc2));
+    const float decay = 1.0f - a.lr * a.weight_decay;
+    const long n4 = a.n / 4;
+    long blocks = (n4 + 255) / 256;
+    const long cap = static_cast<long>(num_sms()) * 8;             // grid = multiple of the SM count, grid-stride
+    if (blocks > cap) blocks = cap;
+    adam_kernel<<<static_cast<unsigned>(blocks), 256, 0, st>>>(a, step_size, inv_sqrt_bc2, decay);
+    LIFTER_CHECK_CUDA(cudaGetLastError());
+    return LIFTER_OK;
+}
+
+}  // namespace lifter

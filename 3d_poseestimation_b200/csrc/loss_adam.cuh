@@ -1,0 +1,36 @@
+// Fused loss / metric kernel (b) and fused flat-buffer Adam (c) of BASELINE.json's north_star.
+#pragma once
+#include "common.cuh"
+
+namespace lifter {
+
+enum : int { LOSS_MSE = 0, LOSS_L1 = 1, LOSS_MPJPE = 2 };
+
+// pred/target [rows][J*3] fp32.  One pass computes
+//   loss   = mean over the GLOBAL batch (count rows) of  (d^2 | |d| | ||d_joint||)          -> out[0]
+//   dpred  = d loss / d pred  (nullable)                                                      [rows][J*3]
+//   metric = per-joint sum over the local rows of ||(pred - target) * std|| (loss_MPJPE)      -> out[1 .. J]
+// `stdv` (nullable, [J*3]) de-standardises the error for the metric (y*std+mean on both sides cancels the mean).
+// partials: [loss_partial_rows(rows)][1 + J] floats of scratch.  accumulate_metric: out[1..J] += (epoch accumulation).
+int loss_partial_rows(int64_t rows);
+int fused_loss(const float* pred, const float* target, int64_t rows, int J, int kind, double count,
+               const float* stdv, float* dpred, float* partials, float* out, int accumulate_metric, cudaStream_t st);
+
+// sum |a - b| over n elements -> out[0] = sum * scale (L1Loss building block of TriangleLoss, losses.py:21-53);
+// centre: subtract row 0 (row_len elements) from rows 1.. of both tensors first (the reference's batch-dim quirk).
+int l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, float scale, float* partials,
+           float* out, cudaStream_t st);
+// da = sign(a' - b') * gscale[0] * scale (and db = -da when db != nullptr); with centre, row 0 collects the
+// negated sum of the other rows' gradients.
+int l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, const float* gscale, float scale,
+            float* da, float* db, cudaStream_t st);
+
+struct AdamArgs {
+    float* p; const float* g; float* m; float* v; int64_t n;
+    float lr, beta1, beta2, eps, weight_decay; int decoupled;     // AdamW: decoupled = 1
+    int step;                                                     // 1-based
+    float grad_scale;                                             // multiplies g first (1/world for DP means)
+};
+int adam_step(const AdamArgs& a, cudaStream_t st);
+
+}  // namespace lifter

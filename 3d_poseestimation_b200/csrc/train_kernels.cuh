@@ -1,0 +1,68 @@
+// Elementwise + column-reduction kernels of the training path (BatchNorm statistics, BN/ReLU/dropout apply,
+// their backward, gradient reductions).  All are L2/HBM-bound: 16-byte vector accesses, deterministic
+// two-stage column reductions (per-block partial rows, then a fixed-order reduce) -- no float atomics.
+#pragma once
+#include "common.cuh"
+
+namespace lifter {
+
+constexpr int EW_THREADS = 256;
+constexpr int EW_ITERS = 8;                 // row-iterations per block in the column-reducing kernels
+
+// rows handled by one block of the column-reducing elementwise kernels, and the partial-row count for `rows`
+int ew_rows_per_block(int H);
+int ew_partial_rows(int64_t rows, int H);
+
+// out_a[n] = sum_p a[p][n] (fp64 accumulate), same for b (nullable)
+int reduce_rows_f64(const float* a, const float* b, int P, int n, double* out_a, double* out_b, cudaStream_t st);
+// out[n] = sum_p a[p][n] written as fp32 (bias gradients)
+int reduce_rows_f32(const float* a, int P, int n, float* out, cudaStream_t st);
+
+struct BnFwdFinalize {
+    const double* sums;        // [2][H] (sum z, sum z^2) over the GLOBAL batch; unused when bn_mode != 0
+    double count;              // global batch rows
+    const float* bias; const float* gamma; const float* beta;
+    float* running_mean; float* running_var; long long* num_batches_tracked;   // nullable: no update
+    float momentum, eps;
+    int H, use_bn, bn_mode;    // bn_mode 0: batch statistics (train), 1: running statistics (eval with autograd)
+    float* mean_z; float* rstd; float* scale; float* shift;                     // [H] each
+};
+int bn_finalize_fwd(const BnFwdFinalize& a, cudaStream_t st);
+
+struct BnApplyFwd {
+    const void* z; const float* scale; const float* shift; const void* resid;   // resid nullable
+    int64_t rows; int H; int fmt;
+    int apply_dropout; float p; unsigned long long seed; unsigned step, site; long long row_offset;
+    void* a; uint8_t* bits;     // a [rows][H] 16-bit, bits [rows][H/8]: relu-active AND kept
+};
+int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st);
+
+struct BwdCommon {
+    const void* g; const void* z; const uint8_t* bits; const float* mean_z; const float* rstd;
+    int64_t rows; int H; int fmt; float inv_keep;
+};
+// partial column sums of dy and dy * zhat: psum_dy / psum_dyz are [ew_partial_rows][H]
+int bwd_stats(const BwdCommon& c, float* psum_dy, float* psum_dyz, cudaStream_t st);
+
+struct BnBwdFinalize {
+    const double* sums;        // [2][H] (sum dy, sum dy*zhat) over the GLOBAL batch
+    double count;
+    const float* gamma; const float* rstd;
+    int H, use_bn, bn_mode;
+    float* coef;               // [3][H]: k = gamma*rstd, c1 = sum dy / count, c2 = sum dy*zhat / count
+};
+int bn_finalize_bwd(const BnBwdFinalize& a, cudaStream_t st);
+// dgamma = sum dy*zhat, dbeta = sum dy from the LOCAL sums (the gradient all-reduce adds the shards)
+int bn_param_grads(const double* local_sums, int H, float* dgamma, float* dbeta, cudaStream_t st);
+
+// dz = k * (dy - c1 - zhat * c2) as 16-bit, plus partial column sums of dz (bias gradient)
+int bwd_dz(const BwdCommon& c, const float* coef, void* dz, float* psum_dz, cudaStream_t st);
+
+// sum of split-K slabs -> dense fp32 gradient [rows][cols]
+int wgrad_reduce(const float* slabs, int splits, int slab_rows, int ld, int rows, int cols, float* grad,
+                 cudaStream_t st);
+
+// grad_out fp32 [rows][O] -> 16-bit [rows][Op] zero padded, plus partial column sums (output-layer bias gradient)
+int prep_grad_out(const float* dout, int64_t rows, int O, int Op, int fmt, void* d16, float* psum, cudaStream_t st);
+
+}  // namespace lifter

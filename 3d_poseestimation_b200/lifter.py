@@ -96,6 +96,8 @@ class LinearModel(torch.nn.Module):
                                        float(p_dropout), 1e-5, 0.1)
         _cabi.check(_cabi.lib().lifter_param_total(C.byref(self._cfg)))      # validates the shape (ValueError)
         self._cache = {}
+        self._stats_epoch = 0                # bumped when a kernel rewrites the running statistics
+        self._param_epoch = 0                # bumped when a kernel (fused Adam) rewrites the flat parameters
         self._flatten()
 
     # ------------------------------------------------------------------ layout
@@ -153,7 +155,7 @@ class LinearModel(torch.nn.Module):
         return self.batch_norm1.running_mean.data_ptr() == self._rm.data_ptr()
 
     def _versions(self):
-        return tuple(p._version for p in self._ordered_params())
+        return (self._param_epoch,) + tuple(p._version for p in self._ordered_params())
 
     # ------------------------------------------------------------------ cached device-side derivatives
     @staticmethod
@@ -181,7 +183,7 @@ class LinearModel(torch.nn.Module):
 
     def _folded_bn(self):
         """Eval-mode BatchNorm + bias folded to per-column scale/shift [L][2][H]."""
-        ver = (self._versions(), self._rm._version, self._rv._version,
+        ver = (self._versions(), self._stats_epoch, self._rm._version, self._rv._version,
                tuple(bn.running_mean._version for _, bn in self._hidden_layers()),
                tuple(bn.running_var._version for _, bn in self._hidden_layers()), self._flat.data_ptr())
         hit = self._cache.get("fold")

@@ -1,0 +1,148 @@
+"""Fused training step of the lifter: the loop body of ``phase1_lifting/train_1.py:73-100``
+(``zero_grad -> forward -> loss -> backward -> optimizer.step -> metric``) as one sequence of sm_100a
+kernels with no host synchronisation: forward with saved activations, fused loss + gradient + MPJPE
+metric, backward, (data parallel: NCCL all-reduce of the flat gradient and of the BatchNorm column sums),
+fused flat-buffer Adam/AdamW, refresh of the 16-bit operand copies.
+
+The reference reads ``loss.cpu().item()`` every step (train_1.py:98); here the loss stays on the device and
+``loss_value()`` reads it when the caller wants it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _autograd, _cabi
+
+_LOSS = {"mse": _cabi.LOSS_MSE, "l1": _cabi.LOSS_L1, "mpjpe": _cabi.LOSS_MPJPE}
+
+
+class LifterTrainer:
+    """``LifterTrainer(model, lr=1e-4, loss="mse", optimizer="adamw")``.
+
+    optimizer: "adam" (torch.optim.Adam: weight_decay is L2) or "adamw" (decoupled, default 0.01 as at
+    train_1.py:39).  ``process_group`` enables data parallelism: every rank calls ``step`` with its shard of
+    the global batch; gradients are summed over ranks (the loss is a mean over the GLOBAL batch) and
+    BatchNorm uses global batch statistics.
+    """
+
+    def __init__(self, model, lr=1e-4, loss="mse", optimizer="adamw", betas=(0.9, 0.999), eps=1e-8,
+                 weight_decay=None, seed=0, process_group=None, world_size=None, rank=None, metric_std=None):
+        if loss not in _LOSS:
+            raise ValueError(f"unknown loss {loss!r}: use 'mse', 'l1' or 'mpjpe'")
+        if optimizer not in ("adam", "adamw"):
+            raise ValueError(f"unknown optimizer {optimizer!r}: use 'adam' or 'adamw'")
+        if model.output_size % 3 != 0:
+            raise ValueError("the fused loss works on (J, 3) joint outputs: o_dim must be a multiple of 3")
+        if not model._flat.is_cuda:
+            raise RuntimeError("LifterTrainer needs the model on a B200 (no CPU path)")
+        self.model = model
+        self.lr, self.betas, self.eps = float(lr), betas, float(eps)
+        self.decoupled = optimizer == "adamw"
+        self.weight_decay = float(weight_decay if weight_decay is not None else (0.01 if self.decoupled else 0.0))
+        self.loss_kind = _LOSS[loss]
+        self.joints = model.output_size // 3
+        self.step_count = 0
+        model.dropout_seed = int(seed)
+        self.pg = process_group
+        if process_group is None and world_size is not None and world_size > 1:
+            import torch.distributed as dist
+            self.pg = dist.group.WORLD
+        model.process_group = self.pg
+        if self.pg is not None:
+            import torch.distributed as dist
+            self.world, self.rank = dist.get_world_size(self.pg), dist.get_rank(self.pg)
+        else:
+            self.world, self.rank = 1, 0
+        dev = model._flat.device
+        self.m = torch.zeros_like(model._flat)
+        self.v = torch.zeros_like(model._flat)
+        self.grad = torch.zeros_like(model._flat)
+        self.loss_out = torch.zeros(1 + self.joints, dtype=torch.float32, device=dev)     # [loss, metric per joint]
+        self.metric_std = None if metric_std is None else torch.as_tensor(
+            metric_std, dtype=torch.float32, device=dev).reshape(-1).contiguous()
+        self._bufs = {}
+
+    # ------------------------------------------------------------------ buffers sized by the batch
+    def _buffers(self, B, dev):
+        b = self._bufs.get(B)
+        if b is None:
+            lib, cfg = _cabi.lib(), C.byref(self.model._cfg)
+            b = dict(
+                saved=torch.empty(_cabi.check(lib.lifter_train_saved_bytes(cfg, B)), dtype=torch.uint8, device=dev),
+                scratch=torch.empty(_cabi.check(lib.lifter_train_scratch_bytes(cfg, B)), dtype=torch.uint8, device=dev),
+                out=torch.empty(B, self.model.output_size, dtype=torch.float32, device=dev),
+                dpred=torch.empty(B, self.model.output_size, dtype=torch.float32, device=dev),
+                lscratch=torch.empty(_cabi.check(lib.lifter_loss_scratch_bytes(B, self.joints)), dtype=torch.uint8,
+                                     device=dev))
+            self._bufs = {B: b}                       # keep one batch size resident
+        return b
+
+    def launches_per_step(self, B):
+        L = 2 * self.model.num_stage + 1
+        use_bn = 1 if self.model.BN else 0
+        fwd = 1 + L * (1 + use_bn + 2) + 2
+        loss = 2
+        bwd = 2 + 2 + 1 + L * (2 * use_bn + use_bn + 1 + 1 + 1 + 2 + 1) - 1
+        return fwd + loss + bwd + 1 + (L + 1)
+
+    # ------------------------------------------------------------------ one optimiser step
+    def step(self, x, y, accumulate_metric=False):
+        """x: (B, 17, 2) or (B, i_dim) fp32 CUDA, y: (B, 17, 3) or (B, o_dim).  Returns the device loss scalar."""
+        model = self.model
+        lib, cfg = _cabi.lib(), C.byref(model._cfg)
+        x = model._check_input(x)
+        y = y.reshape(y.shape[0], -1)
+        if y.shape != (x.shape[0], model.output_size) or y.dtype != torch.float32 or not y.is_cuda:
+            raise RuntimeError(f"target must be a float32 CUDA tensor of {x.shape[0]} x {model.output_size} values")
+        y = y.contiguous()
+        B = x.shape[0]
+        b = self._buffers(B, x.device)
+        model.train()
+        st = _cabi.stream_ptr()
+        # forward (saved activations), dropout stream addressed by the optimiser step
+        out, _, t = _autograd.run_forward(model, x, True, saved=b["saved"], out=b["out"], step=self.step_count)
+        # fused loss + dL/dpred + per-joint MPJPE sums; the mean is over the GLOBAL batch
+        _cabi.check(lib.lifter_loss(_cabi.ptr(out), _cabi.ptr(y), B, self.joints, self.loss_kind, B * self.world,
+                                    _cabi.ptr(self.metric_std), _cabi.ptr(b["dpred"]), _cabi.ptr(b["lscratch"]),
+                                    _cabi.ptr(self.loss_out), int(accumulate_metric), st))
+        _autograd.run_backward(model, t, b["dpred"], self.grad, None, scratch=b["scratch"])
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(self.grad, group=self.pg)             # sum of shard gradients = global-batch gradient
+        self.step_count += 1
+        _cabi.check(lib.lifter_adam_step(_cabi.ptr(model._flat), _cabi.ptr(self.grad), _cabi.ptr(self.m),
+                                         _cabi.ptr(self.v), model._flat.numel(), self.lr, self.betas[0], self.betas[1],
+                                         self.eps, self.weight_decay, int(self.decoupled), self.step_count, 1.0, st))
+        model._param_epoch += 1                                   # the flat parameters changed under torch's feet
+        model._operands(model._fmt_code(model.train_format))      # refresh the 16-bit operand copies now
+        return self.loss_out[0]
+
+    def loss_value(self):
+        """Host read of the last step's loss (synchronises); with data parallelism, the sum over ranks."""
+        if self.world > 1:
+            import torch.distributed as dist
+            t = self.loss_out[:1].clone()
+            dist.all_reduce(t, group=self.pg)
+            return float(t.item())
+        return float(self.loss_out[0].item())
+
+    def metric_sums(self):
+        """Per-joint sums of L2 errors (``loss_MPJPE``, losses.py:3-7) accumulated since the last reset."""
+        return self.loss_out[1:]
+
+    def reset_metric(self):
+        self.loss_out[1:].zero_()
+
+    def set_lr(self, lr):
+        """The per-step host scalar ReduceLROnPlateau drives (train_1.py:41,106)."""
+        self.lr = float(lr)
+
+    def state_dict(self):
+        return {"step": self.step_count, "m": self.m, "v": self.v, "lr": self.lr}
+
+    def load_state_dict(self, sd):
+        self.step_count, self.lr = int(sd["step"]), float(sd["lr"])
+        self.m.copy_(sd["m"])
+        self.v.copy_(sd["v"])

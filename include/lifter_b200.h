@@ -79,6 +79,70 @@ int lifter_forward_eval(const lifter_config_t* cfg, const void* operands, const 
                         const float* in_mean, const float* in_std, const float* out_mean, const float* out_std,
                         void* workspace, int64_t workspace_bytes, int fmt, int64_t chunk_rows, void* stream);
 
+/* ---- training: forward with saved activations, backward, loss, optimiser ----------------------------
+ * Replaces the autograd graph of LinearModel.forward in train mode (baselineModel.py:87-102, 32-47),
+ * loss.backward() and optimizer.step() (train_1.py:94-96).  One context describes one forward/backward
+ * pair; `saved` is written by forward and read by backward.                                            */
+typedef struct lifter_train_ctx {
+    const float* params;            /* flat fp32 parameters                                              */
+    const void* operands;           /* 16-bit operand copies in `fmt` (lifter_pack_weights)              */
+    float* running_mean;            /* [layers][H]  nullable: no running-stat update                      */
+    float* running_var;             /* [layers][H]                                                        */
+    int64_t* num_batches_tracked;   /* [layers]     nullable                                              */
+    const float* x;                 /* [batch][i_dim] fp32                                                */
+    float* out;                     /* [batch][o_dim] fp32                                                */
+    void* saved; int64_t saved_bytes;          /* lifter_train_saved_bytes()                              */
+    int64_t batch;                  /* local rows                                                         */
+    int64_t global_batch;           /* rows of the whole data-parallel step (BatchNorm statistics count)  */
+    int64_t row_offset;             /* global index of local row 0 (dropout stream)                       */
+    int32_t fmt;
+    int32_t bn_mode;                /* 0: batch statistics (model.train()), 1: running statistics (eval) */
+    int32_t apply_dropout;          /* 1 in train mode                                                    */
+    uint32_t step;                  /* dropout stream: optimiser step                                     */
+    uint64_t seed;                  /* dropout stream: seed                                               */
+    const float* grad_out;          /* backward: [batch][o_dim] fp32                                      */
+    float* grad_params;             /* backward: flat fp32, parameter layout; every tensor is overwritten */
+    float* grad_x;                  /* backward: [batch][i_dim] fp32, nullable                            */
+    void* scratch; int64_t scratch_bytes;      /* backward: lifter_train_scratch_bytes()                  */
+} lifter_train_ctx_t;
+
+int64_t lifter_train_saved_bytes(const lifter_config_t* cfg, int64_t batch);
+int64_t lifter_train_scratch_bytes(const lifter_config_t* cfg, int64_t batch);
+/* byte offset inside `saved` / `scratch` of layer l's double[2][H] column sums: the quantity a data-parallel
+ * run all-reduces between ..._gemm/_stats and ..._finish (synchronised BatchNorm)                          */
+int64_t lifter_train_fwd_sums_offset(const lifter_config_t* cfg, int64_t batch, int layer);
+int64_t lifter_train_bwd_sums_offset(const lifter_config_t* cfg, int64_t batch, int layer);
+
+int lifter_train_fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, int layer, void* stream);
+int lifter_train_fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, int layer, void* stream);
+int lifter_train_fwd_output(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, void* stream);
+int lifter_train_forward(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, void* stream);   /* all layers, one GPU */
+
+int lifter_train_bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, void* stream);
+int lifter_train_bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, int layer, void* stream);
+int lifter_train_bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, int layer, void* stream);
+int lifter_train_backward(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, void* stream);  /* all layers, one GPU */
+
+/* Fused loss + gradient + MPJPE metric (losses.py:3-7, train_1.py:37,94,100; two2three.py:387-390).
+ * kind 0: MSELoss(mean), 1: L1Loss(mean), 2: mean MPJPE.  out[0] = loss over `global_rows`, out[1..joints] =
+ * per-joint sum over the local rows of ||(pred - target) * std|| (std nullable).  dpred nullable.        */
+#define LIFTER_LOSS_MSE 0
+#define LIFTER_LOSS_L1 1
+#define LIFTER_LOSS_MPJPE 2
+int64_t lifter_loss_scratch_bytes(int64_t rows, int joints);
+int lifter_loss(const float* pred, const float* target, int64_t rows, int joints, int kind, int64_t global_rows,
+                const float* stdv, float* dpred, float* scratch, float* out, int accumulate_metric, void* stream);
+/* L1 building blocks of TriangleLoss / TriangleLoss_sep (losses.py:10-119); centre = the reference's
+ * "t[1:] -= t[0]" on both tensors.  scratch: ceil(n / 2048) floats.                                      */
+int lifter_l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, float scale, float* scratch,
+                  float* out, void* stream);
+int lifter_l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, const float* gscale,
+                   float scale, float* da, float* db, void* stream);
+
+/* torch.optim.Adam / AdamW (train_1.py:39) over the flat buffer; step is 1-based; n %% 4 == 0.           */
+int lifter_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                     float eps, float weight_decay, int decoupled, int step, float grad_scale, void* stream);
+
 /* ---- test hook: one tcgen05 GEMM  D[M][N] = sum_k A(m,k) B(n,k) ------------------------------------ */
 typedef struct lifter_gemm_desc {
     const void* A; int64_t lda; const void* B; int64_t ldb;

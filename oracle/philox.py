@@ -11,7 +11,7 @@ Stream definition (one call yields eight 16-bit lanes = eight consecutive column
     counter = (row, col // 8, site, step)      key = (seed_lo, seed_hi)
     r0..r3  = Philox4x32-10(counter, key)
     u16[e]  = (r[e // 2] >> (16 * (e % 2))) & 0xFFFF           e = col % 8
-    keep    = u16 >= round(p * 65536)
+    keep    = u16 >= floor(float32(p) * 65536 + 0.5)
 """
 import numpy as np
 
@@ -40,7 +40,9 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
 
 
 def dropout_threshold(p):
-    return int(min(max(round(float(p) * 65536.0), 0), 65536))
+    """round-half-up of float32(p) * 65536, clipped to [0, 65536] (same expression as csrc/philox.cuh)."""
+    t = float(np.float32(p)) * 65536.0
+    return int(min(max(int(np.floor(t + 0.5)), 0), 65536))
 
 
 def dropout_keep_mask(rows, cols, site, step, seed, p, row_offset=0):

@@ -1,0 +1,211 @@
+"""GPU parity of the training path (forward with batch statistics + Philox dropout, backward, fused loss,
+fused Adam) against the CPU oracle and the reference-generated golden vectors.  The kernels use bf16
+tensor-core operands with fp32 accumulation, so agreement is to bf16 rounding, not bit-exact: outputs and
+gradients are compared by relative L2 error and cosine; the loss curve within 1 % (north_star)."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import adam_oracle, lifter_oracle as lo, losses_oracle as L
+from oracle.philox import dropout_keep_mask
+
+pytestmark = pytest.mark.gpu
+T = torch.from_numpy
+
+
+def rel_l2(a, b):
+    a, b = torch.as_tensor(a).double().reshape(-1), torch.as_tensor(b).double().reshape(-1)
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def _case(golden_dir, tag):
+    g = dict(np.load(os.path.join(golden_dir, f"lifter_{tag}.npz")))
+    i_dim, o_dim, H, S, B, BN, seed = [int(v) for v in g["cfg"]]
+    params, buffers = lo.numpy_init(i_dim, o_dim, H, S, seed)
+    return g, (i_dim, o_dim, H, S, B, bool(BN), seed, float(g["p"])), params, buffers
+
+
+def _model(pkg, params, buffers, i_dim, o_dim, H, S, p, BN):
+    m = pkg.LinearModel(i_dim, o_dim, linear_size=H, num_stage=S, p_dropout=p, BN=BN)
+    m.load_state_dict({**params, **buffers})
+    return m.cuda()
+
+
+@pytest.mark.parametrize("tag", ["small", "small_nobn", "h1024", "wide"])
+def test_train_step_matches_reference_golden(pkg, golden_dir, tag):
+    g, (i_dim, o_dim, H, S, B, BN, seed, p), params, buffers = _case(golden_dir, tag)
+    m = _model(pkg, params, buffers, i_dim, o_dim, H, S, p, BN).train()
+    m.dropout_seed, m.dropout_step = seed + 7, 0                 # the mask stream the golden run used
+    x = T(g["x"]).cuda().requires_grad_(True)
+    y = T(g["y"]).cuda()
+    out = m(x)
+    loss = torch.nn.MSELoss(reduction="mean")(out, y)            # train_1.py:37,94
+    loss.backward()
+    assert rel_l2(out.detach().cpu(), g["train_out"]) < 2e-2
+    assert abs(loss.item() - float(g["train_loss"])) < 1e-2 * float(g["train_loss"])
+    assert rel_l2(x.grad.cpu(), g["train_dx"]) < 4e-2
+    sd = m.state_dict()
+    for k in buffers:
+        np.testing.assert_allclose(sd[k].cpu().numpy(), g["buf_after/" + k], rtol=2e-2, atol=2e-3, err_msg=k)
+    # gradients: against the oracle (which the CPU suite pins to these same golden vectors)
+    masks = [dropout_keep_mask(B, H, s, 0, seed + 7, p) for s in range(2 * S + 1)]
+    ref = lo.lifter_forward_backward(params, buffers, T(g["x"]), lambda o: ((o - T(g["y"])) ** 2).mean(),
+                                     num_stage=S, training=True, use_bn=BN, p_dropout=p, masks=masks)
+    for name, prm in m.named_parameters():
+        gr = ref["grads"][name]
+        if BN and name.endswith(".bias") and "batch_norm" not in name and name != "w2.bias":
+            assert prm.grad.abs().max().item() < 1e-3 * max(1.0, ref["grads"]["w2.bias"].abs().max().item()) + 1e-4
+            continue                                            # analytically zero under train-mode BN
+        if not BN and "batch_norm" in name:
+            assert prm.grad is None or float(prm.grad.abs().max()) == 0.0
+            continue
+        assert rel_l2(prm.grad.cpu(), gr) < 5e-2, f"{name}: rel l2 {rel_l2(prm.grad.cpu(), gr)}"
+
+
+@pytest.mark.parametrize("tag", ["small", "h1024"])
+def test_eval_mode_backward_to_input(pkg, golden_dir, tag):
+    """Phase-5 call site: frozen lifter in eval mode, gradients flow through it to its input."""
+    g, (i_dim, o_dim, H, S, B, BN, seed, p), params, buffers = _case(golden_dir, tag)
+    m = _model(pkg, params, buffers, i_dim, o_dim, H, S, p, BN).eval()
+    x = T(g["x"]).cuda().requires_grad_(True)
+    out = m(x)
+    torch.nn.functional.mse_loss(out, T(g["y"]).cuda()).backward()
+    assert rel_l2(out.detach().cpu(), g["eval_out"]) < 2e-2
+    assert rel_l2(x.grad.cpu(), g["eval_dx"]) < 4e-2
+    sd = m.state_dict()
+    for k in buffers:                                            # eval mode leaves the running statistics alone
+        assert torch.equal(sd[k].cpu(), buffers[k]), k
+
+
+def test_train_mode_batch_of_one_raises(pkg):
+    m = pkg.LinearModel(34, 51, linear_size=64, num_stage=1).cuda().train()
+    with pytest.raises(ValueError, match="Expected more than 1 value per channel"):
+        m(torch.zeros(1, 34, device="cuda"))
+
+
+def test_dropout_stream_and_no_grad_train_forward(pkg):
+    params, buffers = lo.numpy_init(34, 51, 256, 1, seed=3)
+    m = _model(pkg, params, buffers, 34, 51, 256, 1, 0.5, True).train()
+    x = torch.randn(64, 34, device="cuda")
+    m.dropout_seed, m.dropout_step = 5, 0
+    with torch.no_grad():
+        a = m(x)
+        b = m(x)                                 # step advanced: fresh masks
+        m.dropout_step = 0
+        c = m(x)
+    assert not torch.allclose(a, b) and torch.allclose(a, c)
+    assert int(m.batch_norm1.num_batches_tracked) == 3
+
+
+@pytest.mark.parametrize("kind", ["mse", "l1", "mpjpe"])
+def test_fused_loss_matches_oracle(pkg, golden_dir, kind):
+    cabi = importlib.import_module("3d_poseestimation_b200._cabi")
+    st = dict(np.load(os.path.join(golden_dir, "h36m_stats.npz")))
+    std3 = T(st["std_train_3d"]).float()
+    B, J = 1000, 17
+    g = torch.Generator().manual_seed(4)
+    pred, tgt = torch.randn(B, J, 3, generator=g), torch.randn(B, J, 3, generator=g)
+    fn = {"mse": L.mse_mean, "l1": L.l1_mean, "mpjpe": L.mpjpe_mean}[kind]
+    p = pred.clone().requires_grad_(True)
+    ref = fn(p, tgt)
+    ref.backward()
+    lib = cabi.lib()
+    out = torch.zeros(1 + J, device="cuda")
+    dpred = torch.empty(B, J * 3, device="cuda")
+    scratch = torch.empty(lib.lifter_loss_scratch_bytes(B, J), dtype=torch.uint8, device="cuda")
+    pc, tc, sc = pred.reshape(B, -1).cuda(), tgt.reshape(B, -1).cuda(), std3.reshape(-1).cuda()
+    code = {"mse": 0, "l1": 1, "mpjpe": 2}[kind]
+    cabi.check(lib.lifter_loss(cabi.ptr(pc), cabi.ptr(tc), B, J, code, B, cabi.ptr(sc), cabi.ptr(dpred),
+                               cabi.ptr(scratch), cabi.ptr(out), 0, cabi.stream_ptr()))
+    np.testing.assert_allclose(out[0].item(), float(ref), rtol=1e-5)
+    np.testing.assert_allclose(dpred.cpu().numpy(), p.grad.reshape(B, -1).numpy(), rtol=1e-4, atol=1e-9)
+    metric = L.mpjpe_per_joint_sum(pred * std3, tgt * std3)      # de-standardised MPJPE sums, losses.py:3-7
+    np.testing.assert_allclose(out[1:].cpu().numpy(), metric.numpy(), rtol=1e-4)
+    cabi.check(lib.lifter_loss(cabi.ptr(pc), cabi.ptr(tc), B, J, code, B, None, None, cabi.ptr(scratch),
+                               cabi.ptr(out), 1, cabi.stream_ptr()))          # accumulate, no std, no gradient
+    plain = L.mpjpe_per_joint_sum(pred, tgt)
+    np.testing.assert_allclose(out[1:].cpu().numpy(), (metric + plain).numpy(), rtol=1e-4)
+
+
+def test_fused_adam_matches_torch_optim_golden(pkg, golden_dir):
+    cabi = importlib.import_module("3d_poseestimation_b200._cabi")
+    g = dict(np.load(os.path.join(golden_dir, "adam.npz")))
+    n = g["p0"].shape[0]
+    npad = (n + 3) // 4 * 4
+    for tag, wd, dec in (("adam", 0.0, 0), ("adam_l2", 1e-2, 0), ("adamw", 1e-2, 1)):
+        p = torch.zeros(npad, device="cuda")
+        p[:n] = T(g["p0"]).cuda()
+        m, v = torch.zeros_like(p), torch.zeros_like(p)
+        for s in range(g["grads"].shape[0]):
+            gr = torch.zeros(npad, device="cuda")
+            gr[:n] = T(g["grads"][s]).cuda()
+            cabi.check(cabi.lib().lifter_adam_step(cabi.ptr(p), cabi.ptr(gr), cabi.ptr(m), cabi.ptr(v), npad, 1e-3, 0.9,
+                                                   0.999, 1e-8, wd, dec, s + 1, 1.0, cabi.stream_ptr()))
+            np.testing.assert_allclose(p[:n].cpu().numpy(), g[tag][s], rtol=2e-6, atol=2e-7, err_msg=f"{tag} step {s}")
+
+
+def test_external_torch_optimizer_drives_the_module(pkg, golden_dir):
+    """train_1.py:39,75,94-96 unchanged: torch.optim over model.parameters(); loss curve of the golden run."""
+    g = dict(np.load(os.path.join(golden_dir, "train_curve.npz")))
+    i_dim, o_dim, H, S, B, seed, steps = [int(v) for v in g["cfg"]]
+    params, buffers = lo.numpy_init(i_dim, o_dim, H, S, seed, randomize_bn=False)
+    m = _model(pkg, params, buffers, i_dim, o_dim, H, S, float(g["p"]), True).train()
+    opt = torch.optim.Adam(m.parameters(), lr=1e-3)
+    rs = np.random.RandomState(seed + 1)
+    xs = rs.normal(0, 1, (steps, B, i_dim)).astype(np.float32)
+    ys = np.tanh(xs @ g["wtrue"]).astype(np.float32)
+    m.dropout_seed = seed + 7
+    losses = []
+    for s in range(steps):
+        m.dropout_step = s
+        opt.zero_grad()
+        loss = torch.nn.MSELoss(reduction="mean")(m(T(xs[s]).cuda()), T(ys[s]).cuda())
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    np.testing.assert_allclose(losses, g["losses"], rtol=2e-2)
+    assert abs(np.mean(losses[-10:]) - np.mean(g["losses"][-10:])) < 1e-2 * np.mean(g["losses"][-10:])
+
+
+@pytest.mark.parametrize("optimizer", ["adam", "adamw"])
+def test_fused_trainer_follows_the_oracle_curve(pkg, optimizer):
+    """Loop body train_1.py:73-100 as the fused step (forward, MSE, backward, Adam) vs the oracle, same masks."""
+    trainer_mod = importlib.import_module("3d_poseestimation_b200.trainer")
+    i_dim, o_dim, H, S, B, seed, steps = 34, 51, 256, 2, 64, 31, 60
+    params, buffers = lo.numpy_init(i_dim, o_dim, H, S, seed, randomize_bn=False)
+    m = _model(pkg, params, buffers, i_dim, o_dim, H, S, 0.5, True)
+    tr = trainer_mod.LifterTrainer(m, lr=1e-3, loss="mse", optimizer=optimizer, seed=seed + 7)
+    rs = np.random.RandomState(seed + 1)
+    xs = rs.normal(0, 1, (steps, B, i_dim)).astype(np.float32)
+    wtrue = rs.normal(0, 0.3, (i_dim, o_dim)).astype(np.float32)
+    ys = np.tanh(xs @ wtrue).astype(np.float32)
+    mo = {k: torch.zeros_like(v) for k, v in params.items()}
+    vo = {k: torch.zeros_like(v) for k, v in params.items()}
+    kw = dict(weight_decay=0.01, decoupled=True) if optimizer == "adamw" else {}
+    got, exp = [], []
+    for s in range(steps):
+        got.append(float(tr.step(T(xs[s]).cuda(), T(ys[s]).cuda()).item()))
+        masks = [dropout_keep_mask(B, H, site, s, seed + 7, 0.5) for site in range(2 * S + 1)]
+        y = T(ys[s])
+        r = lo.lifter_forward_backward(params, buffers, T(xs[s]), lambda o: ((o - y) ** 2).mean(), num_stage=S,
+                                       training=True, p_dropout=0.5, masks=masks)
+        buffers = r["buffers"]
+        for k in params:
+            params[k], mo[k], vo[k] = adam_oracle.adam_step(params[k], r["grads"][k], mo[k], vo[k], s + 1, 1e-3, **kw)
+        exp.append(float(r["loss"]))
+    np.testing.assert_allclose(got, exp, rtol=2e-2)
+    assert abs(np.mean(got[-10:]) - np.mean(exp[-10:])) < 1e-2 * np.mean(exp[-10:])
+    sd = m.state_dict()
+    assert rel_l2(sd["w2.weight"].cpu(), params["w2.weight"]) < 2e-2
+    assert rel_l2(sd["batch_norm1.running_var"].cpu(), buffers["batch_norm1.running_var"]) < 2e-2
+    assert int(sd["batch_norm1.num_batches_tracked"]) == steps
+    # the eval path sees the trained weights and running statistics
+    m.eval()
+    xe = T(xs[0])
+    ref, _ = lo.lifter_forward(params, buffers, xe, num_stage=S, training=False)
+    with torch.no_grad():
+        out = m(xe.cuda()).cpu()
+    assert rel_l2(out, ref) < 3e-2
