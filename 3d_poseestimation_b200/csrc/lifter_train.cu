@@ -203,7 +203,7 @@ int lifter_train_fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_c
     g.M = B; g.N = H; g.K = lay.in_pad(l); g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.D = w.z[l]; g.ldd = H;
     if (stats) { g.stat_sum = w.psum; g.stat_sq = w.psq; }
     LIFTER_PROPAGATE(gemm_launch(g, st));
-    if (stats) LIFTER_PROPAGATE(reduce_rows_f64(w.psum, w.psq, gemm_stat_rows(B), H, w.sums[l], w.sums[l] + H, st));
+    if (stats) LIFTER_PROPAGATE(reduce_rows_f64(w.psum, w.psq, gemm_stat_rows(B), H, H, w.sums[l], w.sums[l] + H, st));
     return LIFTER_OK;
 }
 
@@ -287,7 +287,7 @@ int lifter_train_bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t*
     const uint16_t* ops = static_cast<const uint16_t*>(t->operands);
     // grad_out -> 16-bit padded, bias gradient of the output layer
     LIFTER_PROPAGATE(prep_grad_out(t->grad_out, B, lay.O, lay.Op, t->fmt, b.dO, b.pA, st));
-    LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(B, lay.Op), lay.O, t->grad_params + lay.p_off[lay.t_b2()], st));
+    LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(B, lay.Op), lay.O, lay.Op, t->grad_params + lay.p_off[lay.t_b2()], st));
     // dW2 = dOut^T a_{L-1}
     LIFTER_PROPAGATE(wgrad(lay, t, b, b.dO, lay.Op, lay.Op, w.a[lay.L - 1], H, H, lay.O, H,
                            t->grad_params + lay.p_off[lay.t_w2()], st));
@@ -322,7 +322,7 @@ int lifter_train_bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_
     const bool drop = t->apply_dropout && cfg->p_dropout > 0.0f;
     c.inv_keep = drop ? (cfg->p_dropout < 1.0f ? 1.0f / (1.0f - cfg->p_dropout) : 0.0f) : 1.0f;
     LIFTER_PROPAGATE(bwd_stats(c, b.pA, b.pB, st));
-    LIFTER_PROPAGATE(reduce_rows_f64(b.pA, b.pB, ew_partial_rows(t->batch, H), H, b.bsums[l], b.bsums[l] + H, st));
+    LIFTER_PROPAGATE(reduce_rows_f64(b.pA, b.pB, ew_partial_rows(t->batch, H), H, H, b.bsums[l], b.bsums[l] + H, st));
     // parameter gradients from the LOCAL sums (the data-parallel gradient all-reduce adds the shards)
     return bn_param_grads(b.bsums[l], H, t->grad_params + lay.p_off[lay.t_gamma(l)],
                           t->grad_params + lay.p_off[lay.t_beta(l)], st);
@@ -355,7 +355,7 @@ int lifter_train_bwd_layer_finish(const lifter_config_t* cfg, const lifter_train
     const bool drop = t->apply_dropout && cfg->p_dropout > 0.0f;
     c.inv_keep = drop ? (cfg->p_dropout < 1.0f ? 1.0f / (1.0f - cfg->p_dropout) : 0.0f) : 1.0f;
     LIFTER_PROPAGATE(bwd_dz(c, b.coef, b.dz, b.pA, st));
-    LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(t->batch, H), H, t->grad_params + lay.p_off[lay.t_bias(l)], st));
+    LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(t->batch, H), H, H, t->grad_params + lay.p_off[lay.t_bias(l)], st));
 
     // dW_l = dz^T a_{l-1}
     const uint16_t* a_in = l == 0 ? w.a0 : w.a[l - 1];

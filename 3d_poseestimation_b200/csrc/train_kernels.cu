@@ -27,7 +27,7 @@ __device__ __forceinline__ void load8f(const float* p, float (&v)[8]) {
 // ---------------------------------------------------------------------------------- row reductions
 // block = 32 columns x 32 row-lanes; every thread sums its rows in order, then a fixed-order tree over lanes
 template <typename OutT>
-__global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int P, int n,
+__global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int P, int n, int ld,
                                    OutT* __restrict__ out_a, OutT* __restrict__ out_b) {
     __shared__ double sh[2][32][33];
     const int col = blockIdx.x * 32 + threadIdx.x;
@@ -35,8 +35,8 @@ __global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __r
     double sa = 0.0, sb = 0.0;
     if (col < n) {
         for (int p = lane_r; p < P; p += 32) {
-            sa += static_cast<double>(a[static_cast<long>(p) * n + col]);
-            if (b != nullptr) sb += static_cast<double>(b[static_cast<long>(p) * n + col]);
+            sa += static_cast<double>(a[static_cast<long>(p) * ld + col]);
+            if (b != nullptr) sb += static_cast<double>(b[static_cast<long>(p) * ld + col]);
         }
     }
     sh[0][lane_r][threadIdx.x] = sa;
@@ -283,13 +283,13 @@ int ew_partial_rows(int64_t rows, int H) {
     return static_cast<int>((rows + rpb - 1) / rpb);
 }
 
-int reduce_rows_f64(const float* a, const float* b, int P, int n, double* out_a, double* out_b, cudaStream_t st) {
-    reduce_rows_kernel<double><<<ceil_div(n, 32), dim3(32, 32), 0, st>>>(a, b, P, n, out_a, out_b);
+int reduce_rows_f64(const float* a, const float* b, int P, int n, int ld, double* out_a, double* out_b, cudaStream_t st) {
+    reduce_rows_kernel<double><<<ceil_div(n, 32), dim3(32, 32), 0, st>>>(a, b, P, n, ld, out_a, out_b);
     LIFTER_CHECK_CUDA(cudaGetLastError());
     return LIFTER_OK;
 }
-int reduce_rows_f32(const float* a, int P, int n, float* out, cudaStream_t st) {
-    reduce_rows_kernel<float><<<ceil_div(n, 32), dim3(32, 32), 0, st>>>(a, nullptr, P, n, out, nullptr);
+int reduce_rows_f32(const float* a, int P, int n, int ld, float* out, cudaStream_t st) {
+    reduce_rows_kernel<float><<<ceil_div(n, 32), dim3(32, 32), 0, st>>>(a, nullptr, P, n, ld, out, nullptr);
     LIFTER_CHECK_CUDA(cudaGetLastError());
     return LIFTER_OK;
 }

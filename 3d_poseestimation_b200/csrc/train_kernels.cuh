@@ -13,10 +13,10 @@ constexpr int EW_ITERS = 8;                 // row-iterations per block in the c
 int ew_rows_per_block(int H);
 int ew_partial_rows(int64_t rows, int H);
 
-// out_a[n] = sum_p a[p][n] (fp64 accumulate), same for b (nullable)
-int reduce_rows_f64(const float* a, const float* b, int P, int n, double* out_a, double* out_b, cudaStream_t st);
-// out[n] = sum_p a[p][n] written as fp32 (bias gradients)
-int reduce_rows_f32(const float* a, int P, int n, float* out, cudaStream_t st);
+// out_a[j] = sum_p a[p * ld + j] for j < n (fp64 accumulate), same for b (nullable)
+int reduce_rows_f64(const float* a, const float* b, int P, int n, int ld, double* out_a, double* out_b, cudaStream_t st);
+// out[j] = sum_p a[p * ld + j] written as fp32 (bias gradients)
+int reduce_rows_f32(const float* a, int P, int n, int ld, float* out, cudaStream_t st);
 
 struct BnFwdFinalize {
     const double* sums;        // [2][H] (sum z, sum z^2) over the GLOBAL batch; unused when bn_mode != 0
