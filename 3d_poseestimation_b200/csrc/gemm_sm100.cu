@@ -433,8 +433,9 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     if (a.out_mode == OUT_16_TMA) {
         LIFTER_PROPAGATE(encode_2d(&p.tmD, dt16, 2, a.D, a.M, a.N, a.ldd, 64, 32));
     } else if (a.out_mode == OUT_32_TMA) {
+        // rows of the last slab are clipped to M, so a single-slab output may be exactly [M][ldd]
         LIFTER_PROPAGATE(encode_2d(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, a.D,
-                                   static_cast<long>(p.splits) * p.slab_rows, a.N, a.ldd, 32, 32));
+                                   static_cast<long>(p.splits - 1) * p.slab_rows + a.M, a.N, a.ldd, 32, 32));
     }
     p.num_n_blocks = ceil_div(a.N, BLOCK_N);
     p.num_tiles = p.num_m_blocks * p.num_n_blocks * p.splits;
