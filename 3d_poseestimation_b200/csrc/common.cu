@@ -1,5 +1,6 @@
 #include "common.cuh"
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace lifter {
@@ -25,6 +26,15 @@ int num_sms() {
         cached[dev] = n;
     }
     return cached[dev];
+}
+
+bool pdl_enabled() {
+    static int cached = -1;
+    if (cached < 0) {
+        const char* e = getenv("LIFTER_NO_PDL");
+        cached = (e != nullptr && e[0] == '1') ? 0 : 1;
+    }
+    return cached == 1;
 }
 
 }  // namespace lifter

@@ -47,7 +47,7 @@ struct Cfg {
 struct alignas(64) GemmParams {
     CUtensorMap tmA, tmB, tmD;
     int M, N, K;
-    int num_m_blocks, num_n_blocks, splits, k_blocks_total, k_blocks_per_split, num_tiles;
+    int num_m_blocks, num_n_blocks, splits, k_blocks_total, k_blocks_per_split, num_tiles;   // num_tiles counts M-groups of CL blocks
     int a_mn_major, b_mn_major, fmt, out_mode, relu, has_affine;
     const float* scale;
     const float* shift;
@@ -96,9 +96,14 @@ __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], uint32_t lan
     return v[0];
 }
 
-template <int BLOCK_N>
+// CL = CTAs per cluster.  With CL = 2 the two CTAs of a cluster work on vertically adjacent M-blocks of the same
+// N-block and K-range: each loads its own A tile and HALF of the shared B tile, multicast into both CTAs' smem, so
+// the L2->SM operand traffic per stage drops from 16 KB + B to 16 KB + B/2 per SM.  The MMAs stay per-CTA
+// (cta_group::1); only the smem-slot release is cluster-wide (each CTA's commit arrives on both empty barriers).
+template <int BLOCK_N, int CL>
 __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
     using C = Cfg<BLOCK_N>;
+    static_assert(CL == 1 || (CL == 2 && BLOCK_N >= 128), "cluster multicast splits the B tile in two");
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t smem_base = smem_u32(smem);
     const uint32_t warp = threadIdx.x >> 5;
@@ -119,7 +124,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
     } else if (warp == 1 && lane == 0) {
         for (int i = 0; i < C::STAGES; ++i) {
             mbar_init(bar_full + i * 8, 1);
-            mbar_init(bar_empty + i * 8, 1);
+            mbar_init(bar_empty + i * 8, CL);          // one MMA-commit arrival per CTA of the cluster
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar_tfull + i * 8, 1);
@@ -129,20 +134,25 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
     } else if (warp == 2) {
         tmem_alloc<C::TMEM_COLS>(smem_u32(tmem_ptr_smem));
     }
+    griddep_launch();                                         // let the next kernel's prologue overlap our tail
     tcgen05_fence_before();
-    __syncthreads();
+    if (CL > 1) cluster_sync_all(); else __syncthreads();     // peers' barriers are initialised before any remote arrive
     tcgen05_fence_after();
+    griddep_wait();                                           // everything above touched no global data
     const uint32_t tmem_base = *tmem_ptr_smem;
 
     const int tiles_per_m = p.num_n_blocks * p.splits;
+    const uint32_t crank = CL > 1 ? cluster_ctarank() : 0;
+    const int first_tile = blockIdx.x / CL, tile_step = gridDim.x / CL;
 
     if (warp == 0) {
-        if (lane == 0) {
+        if (elect_one_sync()) {
             // ===================== TMA producer =====================
             uint32_t stage = 0, phase = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-                const int m_blk = tile / tiles_per_m;
-                const int rem = tile - m_blk * tiles_per_m;
+            for (int tile = first_tile; tile < p.num_tiles; tile += tile_step) {
+                const int m_grp = tile / tiles_per_m;
+                const int m_blk = m_grp * CL + crank;
+                const int rem = tile - m_grp * tiles_per_m;
                 const int split = rem / p.num_n_blocks;
                 const int n_blk = rem - split * p.num_n_blocks;
                 const int kb0 = split * p.k_blocks_per_split;
@@ -160,49 +170,71 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
                         for (int j = 0; j < BLOCK_M / 64; ++j)
                             tma_load_2d(&p.tmA, sa + j * 8192, full, m_blk * BLOCK_M + j * 64, kb * BLOCK_K);
                     }
-                    if (!p.b_mn_major) {
-                        tma_load_2d(&p.tmB, sb, full, kb * BLOCK_K, n_blk * BLOCK_N);
-                    } else {
+                    if (CL == 1) {
+                        if (!p.b_mn_major) {
+                            tma_load_2d(&p.tmB, sb, full, kb * BLOCK_K, n_blk * BLOCK_N);
+                        } else {
 #pragma unroll
-                        for (int j = 0; j < BLOCK_N / 64; ++j)
-                            tma_load_2d(&p.tmB, sb + j * 8192, full, n_blk * BLOCK_N + j * 64, kb * BLOCK_K);
+                            for (int j = 0; j < BLOCK_N / 64; ++j)
+                                tma_load_2d(&p.tmB, sb + j * 8192, full, n_blk * BLOCK_N + j * 64, kb * BLOCK_K);
+                        }
+                    } else {                                       // my half of B, delivered to both CTAs
+                        constexpr int HALF = BLOCK_N / 2;
+                        if (!p.b_mn_major) {
+                            tma_load_2d_multicast(&p.tmB, sb + crank * (HALF * 128), full, kb * BLOCK_K,
+                                                  n_blk * BLOCK_N + crank * HALF, 0x3);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < HALF / 64; ++j) {
+                                const int atom = crank * (HALF / 64) + j;
+                                tma_load_2d_multicast(&p.tmB, sb + atom * 8192, full, n_blk * BLOCK_N + atom * 64,
+                                                      kb * BLOCK_K, 0x3);
+                            }
+                        }
                     }
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===================== UMMA issuer =====================
-            const uint32_t idesc = make_idesc(p.fmt, p.a_mn_major, p.b_mn_major, BLOCK_N);
-            const uint32_t a_lbo = p.a_mn_major ? 8192u : 0u, b_lbo = p.b_mn_major ? 8192u : 0u;
-            const uint32_t a_kstep = p.a_mn_major ? 2048u : 32u, b_kstep = p.b_mn_major ? 2048u : 32u;
-            uint32_t stage = 0, phase = 0;
-            int it = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-                const int rem = tile % tiles_per_m;
-                const int split = rem / p.num_n_blocks;
-                const int kb0 = split * p.k_blocks_per_split;
-                const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
-                const uint32_t as = it & 1, aph = (it >> 1) & 1;
-                mbar_wait(bar_tempty + as * 8, aph ^ 1);           // epilogue drained this accumulator
+        // ===================== UMMA issuer =====================
+        // The whole warp walks the pipeline (waits are warp-wide); one elected lane issues the MMAs and commits.
+        const uint32_t idesc = make_idesc(p.fmt, p.a_mn_major, p.b_mn_major, BLOCK_N);
+        const uint32_t a_kstep = (p.a_mn_major ? 2048u : 32u) >> 4, b_kstep = (p.b_mn_major ? 2048u : 32u) >> 4;
+        const uint64_t da0 = make_smem_desc(smem_base + C::OFF_A, p.a_mn_major ? 8192u : 0u);
+        const uint64_t db0 = make_smem_desc(smem_base + C::OFF_B, p.b_mn_major ? 8192u : 0u);
+        const uint32_t a_hi = static_cast<uint32_t>(da0 >> 32), b_hi = static_cast<uint32_t>(db0 >> 32);
+        const uint32_t a_lo0 = static_cast<uint32_t>(da0), b_lo0 = static_cast<uint32_t>(db0);
+        uint32_t stage = 0, phase = 0;
+        int it = 0;
+        for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+            const int rem = tile % tiles_per_m;
+            const int split = rem / p.num_n_blocks;
+            const int kb0 = split * p.k_blocks_per_split;
+            const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
+            const uint32_t as = it & 1, aph = (it >> 1) & 1;
+            mbar_wait(bar_tempty + as * 8, aph ^ 1);               // epilogue drained this accumulator
+            tcgen05_fence_after();
+            const uint32_t tmem_d = tmem_base + as * BLOCK_N;
+            for (int kb = kb0; kb < kb1; ++kb) {
+                mbar_wait(bar_full + stage * 8, phase);            // TMA bytes landed
                 tcgen05_fence_after();
-                const uint32_t tmem_d = tmem_base + as * BLOCK_N;
-                for (int kb = kb0; kb < kb1; ++kb) {
-                    mbar_wait(bar_full + stage * 8, phase);        // TMA bytes landed
-                    tcgen05_fence_after();
-                    const uint32_t sa = smem_base + C::OFF_A + stage * A_STAGE_BYTES;
-                    const uint32_t sb = smem_base + C::OFF_B + stage * C::B_STAGE_BYTES;
+                if (elect_one_sync()) {
+                    const uint32_t a_lo = a_lo0 + stage * (A_STAGE_BYTES >> 4);
+                    const uint32_t b_lo = b_lo0 + stage * (C::B_STAGE_BYTES >> 4);
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-                        const uint64_t da = make_smem_desc(sa + k * a_kstep, a_lbo);
-                        const uint64_t db = make_smem_desc(sb + k * b_kstep, b_lbo);
+                        const uint64_t da = (static_cast<uint64_t>(a_hi) << 32) | (a_lo + k * a_kstep);
+                        const uint64_t db = (static_cast<uint64_t>(b_hi) << 32) | (b_lo + k * b_kstep);
                         umma_f16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
                     }
-                    umma_commit(bar_empty + stage * 8);            // frees the smem slot when the MMAs retire
-                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                    // frees the smem slot (in every CTA of the cluster) when these MMAs retire
+                    if (CL == 1) umma_commit(bar_empty + stage * 8);
+                    else umma_commit_multicast(bar_empty + stage * 8, 0x3);
+                    if (kb == kb1 - 1) umma_commit(bar_tfull + as * 8);    // accumulator complete -> epilogue
                 }
-                umma_commit(bar_tfull + as * 8);                   // accumulator complete -> epilogue
+                __syncwarp();
+                if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp >= 4) {
@@ -216,9 +248,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
         uint32_t buf = 0;
         int cached_n_blk = -1;
         int it = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-            const int m_blk = tile / tiles_per_m;
-            const int rem = tile - m_blk * tiles_per_m;
+        for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+            const int m_grp = tile / tiles_per_m;
+            const int m_blk = m_grp * CL + crank;                  // may lie past the last M-block (odd count): all
+            const int rem = tile - m_grp * tiles_per_m;            // rows are then >= M and every store is clipped
             const int split = rem / p.num_n_blocks;
             const int n_blk = rem - split * p.num_n_blocks;
             const uint32_t as = it & 1, aph = (it >> 1) & 1;
@@ -240,6 +273,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
             const int row0 = m_blk * BLOCK_M + ew * 32;            // first row of this warp's slab
             const int row = row0 + lane;
             const bool row_ok = row < p.M;
+            const bool tile_ok = m_blk < p.num_m_blocks;
             const uint32_t taddr = tmem_base + ((ew * 32u) << 16) + as * BLOCK_N;
             float* stg_f = reinterpret_cast<float*>(stg);
 
@@ -306,7 +340,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
                         const float cs = warp_transpose_sum(v, lane);
                         const float cq = warp_transpose_sum(sq, lane);
                         const int n = n0 + lane;
-                        if (n < p.N) {
+                        if (n < p.N && tile_ok) {
                             const long o = static_cast<long>(m_blk * 4 + ew) * p.N + n;
                             p.stat_sum[o] = cs;
                             p.stat_sq[o] = cq;
@@ -315,7 +349,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
                     if (half == 1) {
                         fence_proxy_async_smem();
                         __syncwarp();
-                        if (lane == 0) {
+                        if (lane == 0 && tile_ok) {
                             tma_store_2d(&p.tmD, stg_addr + buf * 4096, n_blk * BLOCK_N + (c >> 1) * 64, row0);
                             tma_store_commit();
                         }
@@ -335,7 +369,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
-                    if (lane == 0) {
+                    if (lane == 0 && tile_ok) {
                         tma_store_2d(&p.tmD, stg_addr + buf * 4096, n0, split * p.slab_rows + row0);
                         tma_store_commit();
                     }
@@ -362,7 +396,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
     }
 
     tcgen05_fence_before();
-    __syncthreads();
+    if (CL > 1) cluster_sync_all(); else __syncthreads();     // no CTA exits while its peer may still signal it
     if (warp == 2) {
         tcgen05_fence_after();
         tmem_dealloc<C::TMEM_COLS>(tmem_base);
@@ -414,21 +448,21 @@ int encode_2d(CUtensorMap* map, CUtensorMapDataType dt, int elem_bytes, const vo
     return LIFTER_OK;
 }
 
-template <int BLOCK_N>
+template <int BLOCK_N, int CL>
 int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     using C = Cfg<BLOCK_N>;
     static bool configured = false;
     if (!configured) {
-        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(lifter_gemm_kernel<BLOCK_N>,
+        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(lifter_gemm_kernel<BLOCK_N, CL>,
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         configured = true;
     }
     const CUtensorMapDataType dt16 =
         a.fmt == FMT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
-    // operand maps
+    // operand maps (with CL = 2 every CTA loads half of the K-major B tile)
     if (!a.a_mn_major) LIFTER_PROPAGATE(encode_2d(&p.tmA, dt16, 2, a.A, a.M, a.K, a.lda, BLOCK_K, BLOCK_M));
     else               LIFTER_PROPAGATE(encode_2d(&p.tmA, dt16, 2, a.A, a.K, a.M, a.lda, 64, BLOCK_K));
-    if (!a.b_mn_major) LIFTER_PROPAGATE(encode_2d(&p.tmB, dt16, 2, a.B, a.N, a.K, a.ldb, BLOCK_K, BLOCK_N));
+    if (!a.b_mn_major) LIFTER_PROPAGATE(encode_2d(&p.tmB, dt16, 2, a.B, a.N, a.K, a.ldb, BLOCK_K, BLOCK_N / CL));
     else               LIFTER_PROPAGATE(encode_2d(&p.tmB, dt16, 2, a.B, a.K, a.N, a.ldb, 64, BLOCK_K));
     if (a.out_mode == OUT_16_TMA) {
         LIFTER_PROPAGATE(encode_2d(&p.tmD, dt16, 2, a.D, a.M, a.N, a.ldd, 64, 32));
@@ -438,10 +472,22 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
                                    static_cast<long>(p.splits - 1) * p.slab_rows + a.M, a.N, a.ldd, 32, 32));
     }
     p.num_n_blocks = ceil_div(a.N, BLOCK_N);
-    p.num_tiles = p.num_m_blocks * p.num_n_blocks * p.splits;
-    const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-    lifter_gemm_kernel<BLOCK_N><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(p);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    p.num_tiles = ceil_div(p.num_m_blocks, CL) * p.num_n_blocks * p.splits;
+    const int max_clusters = num_sms() / CL;
+    const int clusters = p.num_tiles < max_clusters ? p.num_tiles : max_clusters;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(clusters * CL);
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = C::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    LIFTER_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lifter_gemm_kernel<BLOCK_N, CL>, p));
     return LIFTER_OK;
 }
 
@@ -489,9 +535,14 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     p.slab_rows = gemm_slab_rows(a.M);
     p.stat_sum = a.stat_sum; p.stat_sq = a.stat_sq;
 
-    if (a.N <= 64) return launch_impl<64>(p, a, stream);
-    if (a.N <= 128) return launch_impl<128>(p, a, stream);
-    return launch_impl<256>(p, a, stream);
+    // 2-CTA clusters (weight/B tile multicast) whenever there are at least two M-blocks to pair up
+    // (measured: worth it only when every CTA works through several tiles -- short launches lose more to the
+    //  cluster lock-step than they gain in L2 traffic)
+    const long tiles = static_cast<long>(p.num_m_blocks) * ceil_div(a.N, a.N <= 128 ? 128 : 256) * p.splits;
+    const bool pair = a.cluster != 0 && p.num_m_blocks >= 2 && a.N > 64 && (a.cluster == 2 || tiles >= 4L * num_sms());
+    if (a.N <= 64) return launch_impl<64, 1>(p, a, stream);
+    if (a.N <= 128) return pair ? launch_impl<128, 2>(p, a, stream) : launch_impl<128, 1>(p, a, stream);
+    return pair ? launch_impl<256, 2>(p, a, stream) : launch_impl<256, 1>(p, a, stream);
 }
 
 }  // namespace lifter

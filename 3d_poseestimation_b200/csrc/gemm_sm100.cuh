@@ -24,6 +24,7 @@ struct GemmArgs {
     int n_valid = 0;                          // OUT_32_DIRECT only
     int splits = 1;                           // split-K (OUT_32_TMA): slab s starts at row s * slab_rows(M)
     int relu = 0;
+    int cluster = 1;                          // 2-CTA clusters with B-tile multicast: 0 off, 1 auto (long launches), 2 force
     const float* scale = nullptr;             // per-column multiply (nullptr = 1)
     const float* shift = nullptr;             // per-column add      (nullptr = 0)
     const void* residual = nullptr; long ldr = 0;   // 16-bit [M][ldr], added after the activation

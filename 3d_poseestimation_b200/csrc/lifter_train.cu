@@ -186,7 +186,8 @@ int64_t lifter_train_bwd_sums_offset(const lifter_config_t* cfg, int64_t batch, 
 }
 
 // ---------------------------------------------------------------------------------------------- forward
-int lifter_train_fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+// fused = single-GPU path: the column-sum reduction is merged into the finalize kernel (no all-reduce between)
+static int fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, false));
     LIFTER_REQUIRE(l >= 0 && l < lay.L, "forward: layer %d out of range", l);
@@ -203,11 +204,12 @@ int lifter_train_fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_c
     g.M = B; g.N = H; g.K = lay.in_pad(l); g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.D = w.z[l]; g.ldd = H;
     if (stats) { g.stat_sum = w.psum; g.stat_sq = w.psq; }
     LIFTER_PROPAGATE(gemm_launch(g, st));
-    if (stats) LIFTER_PROPAGATE(reduce_rows_f64(w.psum, w.psq, gemm_stat_rows(B), H, H, w.sums[l], w.sums[l] + H, st));
+    if (stats && !fused)
+        LIFTER_PROPAGATE(reduce_rows_f64(w.psum, w.psq, gemm_stat_rows(B), H, H, w.sums[l], w.sums[l] + H, st));
     return LIFTER_OK;
 }
 
-int lifter_train_fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+static int fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, false));
     LIFTER_REQUIRE(l >= 0 && l < lay.L, "forward: layer %d out of range", l);
@@ -225,7 +227,10 @@ int lifter_train_fwd_layer_finish(const lifter_config_t* cfg, const lifter_train
     f.num_batches_tracked = t->num_batches_tracked ? reinterpret_cast<long long*>(t->num_batches_tracked) + l : nullptr;
     f.momentum = cfg->bn_momentum; f.eps = cfg->bn_eps; f.H = H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode;
     f.mean_z = w.mean_z[l]; f.rstd = w.rstd[l]; f.scale = w.scale[l]; f.shift = w.shift[l];
-    LIFTER_PROPAGATE(bn_finalize_fwd(f, st));
+    if (fused && cfg->use_bn && t->bn_mode == 0)
+        LIFTER_PROPAGATE(bn_reduce_finalize_fwd(w.psum, w.psq, gemm_stat_rows(static_cast<int>(t->batch)), f, w.sums[l], st));
+    else
+        LIFTER_PROPAGATE(bn_finalize_fwd(f, st));
     BnApplyFwd a;
     a.z = w.z[l]; a.scale = w.scale[l]; a.shift = w.shift[l];
     a.resid = (l >= 2 && l % 2 == 0) ? w.a[l - 2] : nullptr;                // out = x + y, baselineModel.py:45
@@ -235,6 +240,13 @@ int lifter_train_fwd_layer_finish(const lifter_config_t* cfg, const lifter_train
     a.a = w.a[l]; a.bits = w.bits[l];
     LIFTER_PROPAGATE(bn_apply_fwd(a, st));
     return LIFTER_OK;
+}
+
+int lifter_train_fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+    return fwd_layer_gemm(cfg, t, l, stream, false);
+}
+int lifter_train_fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+    return fwd_layer_finish(cfg, t, l, stream, false);
 }
 
 int lifter_train_fwd_output(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream) {
@@ -257,8 +269,8 @@ int lifter_train_forward(const lifter_config_t* cfg, const lifter_train_ctx_t* t
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, false));
     for (int l = 0; l < lay.L; ++l) {
-        LIFTER_PROPAGATE(lifter_train_fwd_layer_gemm(cfg, t, l, stream));
-        LIFTER_PROPAGATE(lifter_train_fwd_layer_finish(cfg, t, l, stream));
+        LIFTER_PROPAGATE(fwd_layer_gemm(cfg, t, l, stream, true));
+        LIFTER_PROPAGATE(fwd_layer_finish(cfg, t, l, stream, true));
     }
     return lifter_train_fwd_output(cfg, t, stream);
 }
@@ -306,7 +318,7 @@ static const uint16_t* g_in(const Layout& lay, const ScratchWs& b, int l) {
     return b.G[block_from_top & 1];
 }
 
-int lifter_train_bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+static int bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
     LIFTER_REQUIRE(l >= 0 && l < lay.L, "backward: layer %d out of range", l);
@@ -322,13 +334,22 @@ int lifter_train_bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_
     const bool drop = t->apply_dropout && cfg->p_dropout > 0.0f;
     c.inv_keep = drop ? (cfg->p_dropout < 1.0f ? 1.0f / (1.0f - cfg->p_dropout) : 0.0f) : 1.0f;
     LIFTER_PROPAGATE(bwd_stats(c, b.pA, b.pB, st));
+    if (fused) {                                                   // reduce + dgamma/dbeta + coefficients in one launch
+        BnBwdFinalize f;
+        f.sums = b.bsums[l]; f.count = static_cast<double>(t->global_batch);
+        f.gamma = t->params + lay.p_off[lay.t_gamma(l)]; f.rstd = w.rstd[l];
+        f.H = H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode; f.coef = b.coef;
+        return bn_reduce_finalize_bwd(b.pA, b.pB, ew_partial_rows(t->batch, H), f, b.bsums[l],
+                                      t->grad_params + lay.p_off[lay.t_gamma(l)],
+                                      t->grad_params + lay.p_off[lay.t_beta(l)], st);
+    }
     LIFTER_PROPAGATE(reduce_rows_f64(b.pA, b.pB, ew_partial_rows(t->batch, H), H, H, b.bsums[l], b.bsums[l] + H, st));
     // parameter gradients from the LOCAL sums (the data-parallel gradient all-reduce adds the shards)
     return bn_param_grads(b.bsums[l], H, t->grad_params + lay.p_off[lay.t_gamma(l)],
                           t->grad_params + lay.p_off[lay.t_beta(l)], st);
 }
 
-int lifter_train_bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
     LIFTER_REQUIRE(l >= 0 && l < lay.L, "backward: layer %d out of range", l);
@@ -343,7 +364,7 @@ int lifter_train_bwd_layer_finish(const lifter_config_t* cfg, const lifter_train
     f.sums = b.bsums[l]; f.count = static_cast<double>(t->global_batch);
     f.gamma = t->params + lay.p_off[lay.t_gamma(l)]; f.rstd = w.rstd[l];
     f.H = H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode; f.coef = b.coef;
-    LIFTER_PROPAGATE(bn_finalize_bwd(f, st));
+    if (!(fused && cfg->use_bn)) LIFTER_PROPAGATE(bn_finalize_bwd(f, st));   // fused: done by bwd_layer_stats
     if (!cfg->use_bn) {                                            // the BN affine exists but is unused: zero gradient
         LIFTER_CHECK_CUDA(cudaMemsetAsync(t->grad_params + lay.p_off[lay.t_gamma(l)], 0, H * 4, st));
         LIFTER_CHECK_CUDA(cudaMemsetAsync(t->grad_params + lay.p_off[lay.t_beta(l)], 0, H * 4, st));
@@ -388,13 +409,20 @@ int lifter_train_bwd_layer_finish(const lifter_config_t* cfg, const lifter_train
     return gemm_launch(g, st);
 }
 
+int lifter_train_bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+    return bwd_layer_stats(cfg, t, l, stream, false);
+}
+int lifter_train_bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream) {
+    return bwd_layer_finish(cfg, t, l, stream, false);
+}
+
 int lifter_train_backward(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
     LIFTER_PROPAGATE(lifter_train_bwd_begin(cfg, t, stream));
     for (int l = lay.L - 1; l >= 0; --l) {
-        LIFTER_PROPAGATE(lifter_train_bwd_layer_stats(cfg, t, l, stream));
-        LIFTER_PROPAGATE(lifter_train_bwd_layer_finish(cfg, t, l, stream));
+        LIFTER_PROPAGATE(bwd_layer_stats(cfg, t, l, stream, true));
+        LIFTER_PROPAGATE(bwd_layer_finish(cfg, t, l, stream, true));
     }
     return LIFTER_OK;
 }

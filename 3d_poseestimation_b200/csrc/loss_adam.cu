@@ -23,6 +23,8 @@ __global__ void __launch_bounds__(LOSS_THREADS) fused_loss_kernel(const float* _
                                                                   const float* __restrict__ stdv,
                                                                   float* __restrict__ dpred,
                                                                   float* __restrict__ partials) {
+    griddep_launch();
+    griddep_wait();
     __shared__ float sh_loss[LOSS_THREADS / 32];
     __shared__ float sh_metric[MAX_J];
     if (threadIdx.x < MAX_J) sh_metric[threadIdx.x] = 0.0f;
@@ -72,6 +74,8 @@ __global__ void __launch_bounds__(LOSS_THREADS) fused_loss_kernel(const float* _
 // single block: fixed-order reduction of the per-block partials
 __global__ void loss_finalize_kernel(const float* __restrict__ partials, int nblk, int J, float loss_scale,
                                      float* __restrict__ out, int accumulate_metric) {
+    griddep_launch();
+    griddep_wait();
     __shared__ double sh[32][MAX_J + 1];
     const int c = threadIdx.x % 32, lane_r = threadIdx.x / 32;          // 32 columns x 32 row lanes
     double s = 0.0;
@@ -94,6 +98,8 @@ constexpr int L1_PER_THREAD = 8;
 __global__ void __launch_bounds__(L1_THREADS) l1_sum_kernel(const float* __restrict__ a, const float* __restrict__ b,
                                                             long n, int row_len, int centre,
                                                             float* __restrict__ partials) {
+    griddep_launch();
+    griddep_wait();
     __shared__ float sh[L1_THREADS / 32];
     const long base = (static_cast<long>(blockIdx.x) * L1_THREADS + threadIdx.x) * L1_PER_THREAD;
     float s = 0.0f;
@@ -117,6 +123,8 @@ __global__ void __launch_bounds__(L1_THREADS) l1_sum_kernel(const float* __restr
 }
 
 __global__ void l1_finalize_kernel(const float* __restrict__ partials, int nblk, float scale, float* __restrict__ out) {
+    griddep_launch();
+    griddep_wait();
     __shared__ double sh[256];
     double s = 0.0;
     for (int b = threadIdx.x; b < nblk; b += 256) s += static_cast<double>(partials[b]);
@@ -132,6 +140,8 @@ __global__ void l1_finalize_kernel(const float* __restrict__ partials, int nblk,
 __global__ void l1_grad_kernel(const float* __restrict__ a, const float* __restrict__ b, long n, int row_len,
                                int centre, const float* __restrict__ gscale, float scale, float* __restrict__ da,
                                float* __restrict__ db) {
+    griddep_launch();
+    griddep_wait();
     const long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float gs = (gscale != nullptr ? gscale[0] : 1.0f) * scale;
@@ -154,6 +164,8 @@ __global__ void l1_grad_kernel(const float* __restrict__ a, const float* __restr
 }
 
 __global__ void __launch_bounds__(256) adam_kernel(AdamArgs a, float step_size, float inv_sqrt_bc2, float decay) {
+    griddep_launch();
+    griddep_wait();
     const long n4 = a.n >> 2;
     const long stride = static_cast<long>(gridDim.x) * blockDim.x;
     for (long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
@@ -189,11 +201,9 @@ int fused_loss(const float* pred, const float* target, int64_t rows, int J, int 
     LIFTER_REQUIRE(rows >= 1 && count >= 1.0, "fused_loss: empty batch");
     const int nblk = loss_partial_rows(rows);
     const float inv_count = static_cast<float>(1.0 / count);
-    fused_loss_kernel<<<nblk, LOSS_THREADS, 0, st>>>(pred, target, rows, J, kind, inv_count, stdv, dpred, partials);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(fused_loss_kernel, dim3(nblk), dim3(LOSS_THREADS), 0, st, pred, target, rows, J, kind, inv_count, stdv, dpred, partials));
     const double denom = kind == LOSS_MPJPE ? count * J : count * 3.0 * J;
-    loss_finalize_kernel<<<1, 1024, 0, st>>>(partials, nblk, J, static_cast<float>(1.0 / denom), out, accumulate_metric);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(loss_finalize_kernel, dim3(1), dim3(1024), 0, st, partials, nblk, J, static_cast<float>(1.0 / denom), out, accumulate_metric));
     return LIFTER_OK;
 }
 
@@ -201,18 +211,15 @@ int l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, f
            cudaStream_t st) {
     LIFTER_REQUIRE(n >= 1 && row_len >= 1 && n % row_len == 0, "l1_sum: bad shape");
     const int nblk = static_cast<int>((n + L1_THREADS * L1_PER_THREAD - 1) / (L1_THREADS * L1_PER_THREAD));
-    l1_sum_kernel<<<nblk, L1_THREADS, 0, st>>>(a, b, n, row_len, centre, partials);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
-    l1_finalize_kernel<<<1, 256, 0, st>>>(partials, nblk, scale, out);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(l1_sum_kernel, dim3(nblk), dim3(L1_THREADS), 0, st, a, b, n, row_len, centre, partials));
+    LIFTER_CHECK_CUDA(launch_pdl(l1_finalize_kernel, dim3(1), dim3(256), 0, st, partials, nblk, scale, out));
     return LIFTER_OK;
 }
 
 int l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, const float* gscale, float scale,
             float* da, float* db, cudaStream_t st) {
     LIFTER_REQUIRE(n >= 1 && row_len >= 1 && n % row_len == 0, "l1_grad: bad shape");
-    l1_grad_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a, b, n, row_len, centre, gscale, scale, da, db);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(l1_grad_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, a, b, n, row_len, centre, gscale, scale, da, db));
     return LIFTER_OK;
 }
 
@@ -228,8 +235,7 @@ int adam_step(const AdamArgs& a, cudaStream_t st) {
     long blocks = (n4 + 255) / 256;
     const long cap = static_cast<long>(num_sms()) * 8;             // grid = multiple of the SM count, grid-stride
     if (blocks > cap) blocks = cap;
-    adam_kernel<<<static_cast<unsigned>(blocks), 256, 0, st>>>(a, step_size, inv_sqrt_bc2, decay);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(adam_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st, a, step_size, inv_sqrt_bc2, decay));
     return LIFTER_OK;
 }
 

@@ -29,6 +29,8 @@ __device__ __forceinline__ void load8f(const float* p, float (&v)[8]) {
 template <typename OutT>
 __global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int P, int n, int ld,
                                    OutT* __restrict__ out_a, OutT* __restrict__ out_b) {
+    griddep_launch();
+    griddep_wait();
     __shared__ double sh[2][32][33];
     const int col = blockIdx.x * 32 + threadIdx.x;
     const int lane_r = threadIdx.y;
@@ -55,18 +57,15 @@ __global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __r
 }
 
 // ---------------------------------------------------------------------------------- BN finalize (forward)
-__global__ void bn_finalize_fwd_kernel(BnFwdFinalize a) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j == 0 && a.bn_mode == 0 && a.use_bn && a.num_batches_tracked != nullptr) *a.num_batches_tracked += 1;
-    if (j >= a.H) return;
+__device__ __forceinline__ void bn_finalize_fwd_col(const BnFwdFinalize& a, int j, double sum, double sumsq) {
     if (!a.use_bn) {
         a.mean_z[j] = 0.0f; a.rstd[j] = 1.0f; a.scale[j] = 1.0f; a.shift[j] = a.bias[j];
         return;
     }
     float mean, rstd;
     if (a.bn_mode == 0) {
-        const double m = a.sums[j] / a.count;
-        double var = a.sums[a.H + j] / a.count - m * m;              // biased batch variance (normalisation)
+        const double m = sum / a.count;
+        double var = sumsq / a.count - m * m;                        // biased batch variance (normalisation)
         if (var < 0.0) var = 0.0;
         mean = static_cast<float>(m);
         rstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(a.eps)));
@@ -87,52 +86,123 @@ __global__ void bn_finalize_fwd_kernel(BnFwdFinalize a) {
     a.shift[j] = a.beta[j] - mean * s;
 }
 
+__global__ void bn_finalize_fwd_kernel(BnFwdFinalize a) {
+    griddep_launch();
+    griddep_wait();
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j == 0 && a.bn_mode == 0 && a.use_bn && a.num_batches_tracked != nullptr) *a.num_batches_tracked += 1;
+    if (j >= a.H) return;
+    const bool batch = a.use_bn && a.bn_mode == 0;
+    bn_finalize_fwd_col(a, j, batch ? a.sums[j] : 0.0, batch ? a.sums[a.H + j] : 0.0);
+}
+
+// single-GPU path: second stage of the column reduction and the finalize in one launch
+// (block = 32 columns x 32 row lanes, like reduce_rows_kernel)
+__global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, const float* __restrict__ psq, int P,
+                                              BnFwdFinalize a, double* __restrict__ sums_out) {
+    griddep_launch();
+    griddep_wait();
+    __shared__ double sh[2][32][33];
+    const int col = blockIdx.x * 32 + threadIdx.x;
+    const int lane_r = threadIdx.y;
+    double sa = 0.0, sb = 0.0;
+    if (col < a.H) {
+        for (int p = lane_r; p < P; p += 32) {
+            sa += static_cast<double>(psum[static_cast<long>(p) * a.H + col]);
+            sb += static_cast<double>(psq[static_cast<long>(p) * a.H + col]);
+        }
+    }
+    sh[0][lane_r][threadIdx.x] = sa;
+    sh[1][lane_r][threadIdx.x] = sb;
+    __syncthreads();
+    if (lane_r == 0 && col < a.H) {
+        double ta = 0.0, tb = 0.0;
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) {
+            ta += sh[0][r][threadIdx.x];
+            tb += sh[1][r][threadIdx.x];
+        }
+        sums_out[col] = ta;
+        sums_out[a.H + col] = tb;
+        if (col == 0 && a.num_batches_tracked != nullptr) *a.num_batches_tracked += 1;
+        bn_finalize_fwd_col(a, col, ta, tb);
+    }
+}
+
 // ---------------------------------------------------------------------------------- BN apply + ReLU + dropout (+ residual)
-__global__ void bn_apply_fwd_kernel(BnApplyFwd a, uint32_t threshold, float inv_keep) {
+__global__ void __launch_bounds__(256) bn_apply_fwd_kernel(BnApplyFwd a, uint32_t threshold, float inv_keep) {
+    griddep_launch();
+    griddep_wait();
     const int groups = a.H >> 3;
-    const long idx = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (idx >= a.rows * groups) return;
-    const long row = idx / groups;
-    const int cg = static_cast<int>(idx - row * groups);
-    const long off = row * a.H + cg * 8;
-    float z[8], sc[8], sh[8];
-    unpack8(*reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(a.z) + off), a.fmt, z);
-    load8f(a.scale + cg * 8, sc);
-    load8f(a.shift + cg * 8, sh);
-    uint32_t keep = 0xFFu;
-    if (a.apply_dropout)
-        keep = dropout_keep_bits8(static_cast<uint32_t>(row + a.row_offset), static_cast<uint32_t>(cg), a.site, a.step,
-                                  a.seed, threshold);
-    float out[8];
-    uint32_t active = 0;
+    const long total = a.rows * groups;
+    const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+    const uint16_t* zp = static_cast<const uint16_t*>(a.z);
+    const uint16_t* rp = static_cast<const uint16_t*>(a.resid);
+    for (long i0 = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total; i0 += stride * EW_UNROLL) {
+        uint4 zq[EW_UNROLL], rq[EW_UNROLL];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-        const float y = fmaf(z[e], sc[e], sh[e]);
-        const bool on = (y > 0.0f) && ((keep >> e) & 1u);
-        active |= (on ? 1u : 0u) << e;
-        out[e] = on ? y * inv_keep : 0.0f;
-    }
-    if (a.resid != nullptr) {
-        float r[8];
-        unpack8(*reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(a.resid) + off), a.fmt, r);
+        for (int u = 0; u < EW_UNROLL; ++u) {                       // all loads of the group first
+            const long idx = i0 + u * stride;
+            zq[u] = make_uint4(0, 0, 0, 0);
+            rq[u] = make_uint4(0, 0, 0, 0);
+            if (idx < total) {
+                zq[u] = *reinterpret_cast<const uint4*>(zp + idx * 8);
+                if (rp != nullptr) rq[u] = *reinterpret_cast<const uint4*>(rp + idx * 8);
+            }
+        }
 #pragma unroll
-        for (int e = 0; e < 8; ++e) out[e] += r[e];
+        for (int u = 0; u < EW_UNROLL; ++u) {
+            const long idx = i0 + u * stride;
+            if (idx >= total) break;
+            const long row = idx / groups;
+            const int cg = static_cast<int>(idx - row * groups);
+            float z[8], sc[8], sh[8];
+            unpack8(zq[u], a.fmt, z);
+            load8f(a.scale + cg * 8, sc);
+            load8f(a.shift + cg * 8, sh);
+            uint32_t keep = 0xFFu;
+            if (a.apply_dropout)
+                keep = dropout_keep_bits8(static_cast<uint32_t>(row + a.row_offset), static_cast<uint32_t>(cg), a.site,
+                                          a.step, a.seed, threshold);
+            float out[8];
+            uint32_t active = 0;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const float y = fmaf(z[e], sc[e], sh[e]);
+                const bool on = (y > 0.0f) && ((keep >> e) & 1u);
+                active |= (on ? 1u : 0u) << e;
+                out[e] = on ? y * inv_keep : 0.0f;
+            }
+            if (rp != nullptr) {
+                float r[8];
+                unpack8(rq[u], a.fmt, r);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) out[e] += r[e];
+            }
+            *reinterpret_cast<uint4*>(static_cast<uint16_t*>(a.a) + idx * 8) = pack8(out, a.fmt);
+            a.bits[idx] = static_cast<uint8_t>(active);
+        }
     }
-    *reinterpret_cast<uint4*>(static_cast<uint16_t*>(a.a) + off) = pack8(out, a.fmt);
-    a.bits[idx] = static_cast<uint8_t>(active);
 }
 
 // ---------------------------------------------------------------------------------- backward passes
-// Shared tiling: TPR = H/8 threads cover a row, RPB = 256/TPR rows per iteration, EW_ITERS iterations per block.
+// Shared tiling: TPR = H/8 threads cover a row (16-byte vectors), RPB = 256/TPR rows per iteration.  A block owns
+// `rows_per_block` consecutive rows and walks them EW_UNROLL iterations at a time: all loads of a group are issued
+// before any arithmetic (2 x EW_UNROLL 16-byte loads in flight per thread), sums stay in registers, and one
+// partial row per block leaves through a fixed-order shared-memory reduction (deterministic).
 template <bool WRITE_DZ>
-__global__ void __launch_bounds__(EW_THREADS) bwd_pass_kernel(BwdCommon c, const float* __restrict__ coef,
+__global__ void __launch_bounds__(EW_THREADS) bwd_pass_kernel(BwdCommon c, int rows_per_block,
+                                                              const float* __restrict__ coef,
                                                               uint16_t* __restrict__ dz, float* __restrict__ psum0,
                                                               float* __restrict__ psum1) {
+    griddep_launch();
+    griddep_wait();
     __shared__ float sh[2][EW_THREADS][8];
     const int tpr = c.H >> 3;
     const int rpb = EW_THREADS / tpr;
     const int cg = threadIdx.x % tpr, rl = threadIdx.x / tpr;
-    const long base = static_cast<long>(blockIdx.x) * rpb * EW_ITERS;
+    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long end = min(base + rows_per_block, static_cast<long>(c.rows));
     float mean[8], rstd[8], k[8], c1[8], c2[8];
     load8f(c.mean_z + cg * 8, mean);
     load8f(c.rstd + cg * 8, rstd);
@@ -141,34 +211,52 @@ __global__ void __launch_bounds__(EW_THREADS) bwd_pass_kernel(BwdCommon c, const
         load8f(coef + c.H + cg * 8, c1);
         load8f(coef + 2 * c.H + cg * 8, c2);
     }
+    const uint16_t* gp = static_cast<const uint16_t*>(c.g);
+    const uint16_t* zp = static_cast<const uint16_t*>(c.z);
     float acc0[8] = {0, 0, 0, 0, 0, 0, 0, 0}, acc1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (long r0 = base + rl; r0 < end; r0 += static_cast<long>(rpb) * EW_UNROLL) {
+        uint4 gq[EW_UNROLL], zq[EW_UNROLL];
+        uint32_t act[EW_UNROLL];
 #pragma unroll
-    for (int it = 0; it < EW_ITERS; ++it) {
-        const long row = base + it * rpb + rl;
-        if (row < c.rows) {
-            const long off = row * c.H + cg * 8;
+        for (int u = 0; u < EW_UNROLL; ++u) {
+            const long row = r0 + static_cast<long>(u) * rpb;
+            if (row < end) {
+                const long off = row * c.H + cg * 8;
+                gq[u] = *reinterpret_cast<const uint4*>(gp + off);
+                zq[u] = *reinterpret_cast<const uint4*>(zp + off);
+                act[u] = c.bits[row * tpr + cg];
+            } else {
+                gq[u] = make_uint4(0, 0, 0, 0);
+                zq[u] = make_uint4(0, 0, 0, 0);
+                act[u] = 0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < EW_UNROLL; ++u) {
+            const long row = r0 + static_cast<long>(u) * rpb;
             float g[8], z[8];
-            unpack8(*reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(c.g) + off), c.fmt, g);
-            unpack8(*reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(c.z) + off), c.fmt, z);
-            const uint32_t active = c.bits[row * tpr + cg];
+            unpack8(gq[u], c.fmt, g);
+            unpack8(zq[u], c.fmt, z);
             if (WRITE_DZ) {
-                float o[8];
+                if (row < end) {
+                    float o[8];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const float dy = ((active >> e) & 1u) ? g[e] * c.inv_keep : 0.0f;
-                    const float zh = (z[e] - mean[e]) * rstd[e];
-                    o[e] = k[e] * (dy - c1[e] - zh * c2[e]);
+                    for (int e = 0; e < 8; ++e) {
+                        const float dy = ((act[u] >> e) & 1u) ? g[e] * c.inv_keep : 0.0f;
+                        const float zh = (z[e] - mean[e]) * rstd[e];
+                        o[e] = k[e] * (dy - c1[e] - zh * c2[e]);
+                    }
+                    const uint4 q = pack8(o, c.fmt);
+                    *reinterpret_cast<uint4*>(dz + row * c.H + cg * 8) = q;
+                    float r[8];
+                    unpack8(q, c.fmt, r);                          // bias gradient of the values the GEMMs consume
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) acc0[e] += r[e];
                 }
-                const uint4 q = pack8(o, c.fmt);
-                *reinterpret_cast<uint4*>(dz + off) = q;
-                float r[8];
-                unpack8(q, c.fmt, r);                              // bias gradient of the values the GEMMs consume
-#pragma unroll
-                for (int e = 0; e < 8; ++e) acc0[e] += r[e];
             } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const float dy = ((active >> e) & 1u) ? g[e] * c.inv_keep : 0.0f;
+                for (int e = 0; e < 8; ++e) {                      // rows past `end` carry act == 0: they add nothing
+                    const float dy = ((act[u] >> e) & 1u) ? g[e] * c.inv_keep : 0.0f;
                     acc0[e] += dy;
                     acc1[e] += dy * (z[e] - mean[e]) * rstd[e];
                 }
@@ -202,6 +290,8 @@ __global__ void __launch_bounds__(EW_THREADS) bwd_pass_kernel(BwdCommon c, const
 }
 
 __global__ void bn_finalize_bwd_kernel(BnBwdFinalize a) {
+    griddep_launch();
+    griddep_wait();
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= a.H) return;
     float k = 1.0f, c1 = 0.0f, c2 = 0.0f;
@@ -217,8 +307,47 @@ __global__ void bn_finalize_bwd_kernel(BnBwdFinalize a) {
     a.coef[2 * a.H + j] = c2;
 }
 
+// single-GPU path: reduce the pass-1 partials, write dgamma/dbeta and the pass-2 coefficients in one launch
+__global__ void bn_reduce_finalize_bwd_kernel(const float* __restrict__ pdy, const float* __restrict__ pdyz, int P,
+                                              BnBwdFinalize a, double* __restrict__ sums_out,
+                                              float* __restrict__ dgamma, float* __restrict__ dbeta) {
+    griddep_launch();
+    griddep_wait();
+    __shared__ double sh[2][32][33];
+    const int col = blockIdx.x * 32 + threadIdx.x;
+    const int lane_r = threadIdx.y;
+    double sa = 0.0, sb = 0.0;
+    if (col < a.H) {
+        for (int p = lane_r; p < P; p += 32) {
+            sa += static_cast<double>(pdy[static_cast<long>(p) * a.H + col]);
+            sb += static_cast<double>(pdyz[static_cast<long>(p) * a.H + col]);
+        }
+    }
+    sh[0][lane_r][threadIdx.x] = sa;
+    sh[1][lane_r][threadIdx.x] = sb;
+    __syncthreads();
+    if (lane_r == 0 && col < a.H) {
+        double ta = 0.0, tb = 0.0;
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) {
+            ta += sh[0][r][threadIdx.x];
+            tb += sh[1][r][threadIdx.x];
+        }
+        sums_out[col] = ta;
+        sums_out[a.H + col] = tb;
+        dbeta[col] = static_cast<float>(ta);
+        dgamma[col] = static_cast<float>(tb);
+        const float k = a.gamma[col] * a.rstd[col];
+        a.coef[col] = k;
+        a.coef[a.H + col] = a.bn_mode == 0 ? static_cast<float>(ta / a.count) : 0.0f;
+        a.coef[2 * a.H + col] = a.bn_mode == 0 ? static_cast<float>(tb / a.count) : 0.0f;
+    }
+}
+
 __global__ void bn_param_grads_kernel(const double* __restrict__ s, int H, float* __restrict__ dgamma,
                                       float* __restrict__ dbeta) {
+    griddep_launch();
+    griddep_wait();
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= H) return;
     dbeta[j] = static_cast<float>(s[j]);
@@ -227,6 +356,8 @@ __global__ void bn_param_grads_kernel(const double* __restrict__ s, int H, float
 
 __global__ void wgrad_reduce_kernel(const float* __restrict__ slabs, int splits, long slab_elems, int ld, int rows,
                                     int cols, float* __restrict__ grad) {
+    griddep_launch();
+    griddep_wait();
     const long idx = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= static_cast<long>(rows) * cols) return;
     const int r = static_cast<int>(idx / cols), c = static_cast<int>(idx - static_cast<long>(r) * cols);
@@ -237,29 +368,28 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ slabs, int splits,
 }
 
 __global__ void __launch_bounds__(EW_THREADS) prep_grad_out_kernel(const float* __restrict__ dout, long rows, int O,
-                                                                   int Op, int fmt, uint16_t* __restrict__ d16,
+                                                                   int Op, int fmt, int rows_per_block,
+                                                                   uint16_t* __restrict__ d16,
                                                                    float* __restrict__ psum) {
-    // Op == 64: 8 column groups per row, 32 rows per iteration, EW_ITERS iterations per block
+    griddep_launch();
+    griddep_wait();
+    // Op == 64: 8 column groups per row, 32 rows per iteration
     __shared__ float sh[EW_THREADS][8];
     const int tpr = Op >> 3, rpb = EW_THREADS / tpr;
     const int cg = threadIdx.x % tpr, rl = threadIdx.x / tpr;
-    const long base = static_cast<long>(blockIdx.x) * rpb * EW_ITERS;
+    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long end = min(base + rows_per_block, rows);
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (long row = base + rl; row < end; row += rpb) {
+        float v[8];
 #pragma unroll
-    for (int it = 0; it < EW_ITERS; ++it) {
-        const long row = base + it * rpb + rl;
-        if (row < rows) {
-            float v[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const int c = cg * 8 + e;
-                v[e] = c < O ? dout[row * O + c] : 0.0f;
-            }
-            const uint4 q = pack8(v, fmt);
-            *reinterpret_cast<uint4*>(d16 + row * Op + cg * 8) = q;
-#pragma unroll
-            for (int e = 0; e < 8; ++e) acc[e] += v[e];
+        for (int e = 0; e < 8; ++e) {
+            const int c = cg * 8 + e;
+            v[e] = c < O ? dout[row * O + c] : 0.0f;
         }
+        *reinterpret_cast<uint4*>(d16 + row * Op + cg * 8) = pack8(v, fmt);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] += v[e];
     }
 #pragma unroll
     for (int e = 0; e < 8; ++e) sh[threadIdx.x][e] = acc[e];
@@ -277,26 +407,45 @@ __global__ void __launch_bounds__(EW_THREADS) prep_grad_out_kernel(const float* 
 
 }  // namespace
 
-int ew_rows_per_block(int H) { return (EW_THREADS / (H / 8)) * EW_ITERS; }
+// rows owned by one block: a multiple of the rows one unrolled iteration covers, sized so that at most
+// 4 x SM-count blocks (= partial rows) exist
+int ew_rows_per_block(int64_t rows, int H) {
+    const int64_t step = static_cast<int64_t>(EW_THREADS / (H / 8)) * EW_UNROLL;
+    const int64_t steps = (rows + step - 1) / step;
+    const int64_t max_blocks = static_cast<int64_t>(num_sms()) * 4;
+    const int64_t steps_per_block = (steps + max_blocks - 1) / max_blocks;
+    return static_cast<int>(steps_per_block * step);
+}
 int ew_partial_rows(int64_t rows, int H) {
-    const int rpb = ew_rows_per_block(H);
+    const int rpb = ew_rows_per_block(rows, H);
     return static_cast<int>((rows + rpb - 1) / rpb);
 }
 
 int reduce_rows_f64(const float* a, const float* b, int P, int n, int ld, double* out_a, double* out_b, cudaStream_t st) {
-    reduce_rows_kernel<double><<<ceil_div(n, 32), dim3(32, 32), 0, st>>>(a, b, P, n, ld, out_a, out_b);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(reduce_rows_kernel<double>, dim3(ceil_div(n, 32)), dim3(32, 32), 0, st, a, b, P, n, ld, out_a, out_b));
     return LIFTER_OK;
 }
 int reduce_rows_f32(const float* a, int P, int n, int ld, float* out, cudaStream_t st) {
-    reduce_rows_kernel<float><<<ceil_div(n, 32), dim3(32, 32), 0, st>>>(a, nullptr, P, n, ld, out, nullptr);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(reduce_rows_kernel<float>, dim3(ceil_div(n, 32)), dim3(32, 32), 0, st, a, nullptr, P, n, ld, out, nullptr));
     return LIFTER_OK;
 }
 
 int bn_finalize_fwd(const BnFwdFinalize& a, cudaStream_t st) {
-    bn_finalize_fwd_kernel<<<ceil_div(a.H, 256), 256, 0, st>>>(a);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(bn_finalize_fwd_kernel, dim3(ceil_div(a.H, 256)), dim3(256), 0, st, a));
+    return LIFTER_OK;
+}
+
+int bn_reduce_finalize_fwd(const float* psum, const float* psq, int P, const BnFwdFinalize& a, double* sums_out,
+                           cudaStream_t st) {
+    LIFTER_CHECK_CUDA(launch_pdl(bn_reduce_finalize_fwd_kernel, dim3(ceil_div(a.H, 32)), dim3(32, 32), 0, st, psum, psq, P, a,
+                                 sums_out));
+    return LIFTER_OK;
+}
+
+int bn_reduce_finalize_bwd(const float* pdy, const float* pdyz, int P, const BnBwdFinalize& a, double* sums_out,
+                           float* dgamma, float* dbeta, cudaStream_t st) {
+    LIFTER_CHECK_CUDA(launch_pdl(bn_reduce_finalize_bwd_kernel, dim3(ceil_div(a.H, 32)), dim3(32, 32), 0, st, pdy, pdyz, P, a,
+                                 sums_out, dgamma, dbeta));
     return LIFTER_OK;
 }
 
@@ -305,52 +454,51 @@ int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st) {
     const uint32_t thr = dropout_threshold(a.p);
     const float inv_keep = (a.apply_dropout && a.p < 1.0f) ? 1.0f / (1.0f - a.p) : (a.apply_dropout ? 0.0f : 1.0f);
     const long n = a.rows * (a.H / 8);
-    bn_apply_fwd_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(a, thr, inv_keep);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    long blocks = (n + 256 * EW_UNROLL - 1) / (256 * EW_UNROLL);
+    const long cap = static_cast<long>(num_sms()) * 16;
+    if (blocks > cap) blocks = cap;
+    LIFTER_CHECK_CUDA(launch_pdl(bn_apply_fwd_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st, a, thr, inv_keep));
     return LIFTER_OK;
 }
 
 int bwd_stats(const BwdCommon& c, float* psum_dy, float* psum_dyz, cudaStream_t st) {
     LIFTER_REQUIRE(c.H >= 64 && c.H <= 2048 && (c.H & (c.H - 1)) == 0, "bwd_stats: unsupported H=%d", c.H);
-    bwd_pass_kernel<false><<<ew_partial_rows(c.rows, c.H), EW_THREADS, 0, st>>>(c, nullptr, nullptr, psum_dy, psum_dyz);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(bwd_pass_kernel<false>, dim3(ew_partial_rows(c.rows, c.H)), dim3(EW_THREADS), 0, st, c,
+                                 ew_rows_per_block(c.rows, c.H), nullptr, nullptr, psum_dy, psum_dyz));
     return LIFTER_OK;
 }
 
 int bn_finalize_bwd(const BnBwdFinalize& a, cudaStream_t st) {
-    bn_finalize_bwd_kernel<<<ceil_div(a.H, 256), 256, 0, st>>>(a);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(bn_finalize_bwd_kernel, dim3(ceil_div(a.H, 256)), dim3(256), 0, st, a));
     return LIFTER_OK;
 }
 
 int bn_param_grads(const double* local_sums, int H, float* dgamma, float* dbeta, cudaStream_t st) {
-    bn_param_grads_kernel<<<ceil_div(H, 256), 256, 0, st>>>(local_sums, H, dgamma, dbeta);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(bn_param_grads_kernel, dim3(ceil_div(H, 256)), dim3(256), 0, st, local_sums, H, dgamma, dbeta));
     return LIFTER_OK;
 }
 
 int bwd_dz(const BwdCommon& c, const float* coef, void* dz, float* psum_dz, cudaStream_t st) {
     LIFTER_REQUIRE(c.H >= 64 && c.H <= 2048 && (c.H & (c.H - 1)) == 0, "bwd_dz: unsupported H=%d", c.H);
-    bwd_pass_kernel<true><<<ew_partial_rows(c.rows, c.H), EW_THREADS, 0, st>>>(c, coef, static_cast<uint16_t*>(dz),
-                                                                            psum_dz, nullptr);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(bwd_pass_kernel<true>, dim3(ew_partial_rows(c.rows, c.H)), dim3(EW_THREADS), 0, st, c,
+                                 ew_rows_per_block(c.rows, c.H), coef, static_cast<uint16_t*>(dz),
+                                                                            psum_dz, nullptr));
     return LIFTER_OK;
 }
 
 int wgrad_reduce(const float* slabs, int splits, int slab_rows, int ld, int rows, int cols, float* grad,
                  cudaStream_t st) {
     const long n = static_cast<long>(rows) * cols;
-    wgrad_reduce_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(
-        slabs, splits, static_cast<long>(slab_rows) * ld, ld, rows, cols, grad);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(wgrad_reduce_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, 
+        slabs, splits, static_cast<long>(slab_rows) * ld, ld, rows, cols, grad));
     return LIFTER_OK;
 }
 
 int prep_grad_out(const float* dout, int64_t rows, int O, int Op, int fmt, void* d16, float* psum, cudaStream_t st) {
     LIFTER_REQUIRE(Op == 64, "prep_grad_out: padded output width must be 64");
-    prep_grad_out_kernel<<<ew_partial_rows(rows, Op), EW_THREADS, 0, st>>>(dout, rows, O, Op, fmt,
-                                                                       static_cast<uint16_t*>(d16), psum);
-    LIFTER_CHECK_CUDA(cudaGetLastError());
+    LIFTER_CHECK_CUDA(launch_pdl(prep_grad_out_kernel, dim3(ew_partial_rows(rows, Op)), dim3(EW_THREADS), 0, st, dout, rows, O, Op, fmt,
+                                 ew_rows_per_block(rows, Op),
+                                                                       static_cast<uint16_t*>(d16), psum));
     return LIFTER_OK;
 }
 

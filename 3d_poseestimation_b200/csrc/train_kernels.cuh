@@ -7,10 +7,10 @@
 namespace lifter {
 
 constexpr int EW_THREADS = 256;
-constexpr int EW_ITERS = 8;                 // row-iterations per block in the column-reducing kernels
+constexpr int EW_UNROLL = 4;                // row-iterations whose loads are issued together
 
 // rows handled by one block of the column-reducing elementwise kernels, and the partial-row count for `rows`
-int ew_rows_per_block(int H);
+int ew_rows_per_block(int64_t rows, int H);
 int ew_partial_rows(int64_t rows, int H);
 
 // out_a[j] = sum_p a[p * ld + j] for j < n (fp64 accumulate), same for b (nullable)
@@ -28,6 +28,9 @@ struct BnFwdFinalize {
     float* mean_z; float* rstd; float* scale; float* shift;                     // [H] each
 };
 int bn_finalize_fwd(const BnFwdFinalize& a, cudaStream_t st);
+// single-GPU shortcut: second reduction stage over the GEMM's partial rows + finalize in one launch (batch statistics)
+int bn_reduce_finalize_fwd(const float* psum, const float* psq, int P, const BnFwdFinalize& a, double* sums_out,
+                           cudaStream_t st);
 
 struct BnApplyFwd {
     const void* z; const float* scale; const float* shift; const void* resid;   // resid nullable
@@ -52,6 +55,9 @@ struct BnBwdFinalize {
     float* coef;               // [3][H]: k = gamma*rstd, c1 = sum dy / count, c2 = sum dy*zhat / count
 };
 int bn_finalize_bwd(const BnBwdFinalize& a, cudaStream_t st);
+// single-GPU shortcut: reduce pass-1 partials + dgamma/dbeta + pass-2 coefficients in one launch (use_bn only)
+int bn_reduce_finalize_bwd(const float* pdy, const float* pdyz, int P, const BnBwdFinalize& a, double* sums_out,
+                           float* dgamma, float* dbeta, cudaStream_t st);
 // dgamma = sum dy*zhat, dbeta = sum dy from the LOCAL sums (the gradient all-reduce adds the shards)
 int bn_param_grads(const double* local_sums, int H, float* dgamma, float* dbeta, cudaStream_t st);
 

@@ -151,6 +151,7 @@ typedef struct lifter_gemm_desc {
     void* D; int64_t ldd; int32_t n_valid; int32_t splits; int32_t relu;
     const float* scale; const float* shift; const void* residual; int64_t ldr;
     float* stat_sum; float* stat_sq;
+    int32_t no_cluster;          /* 1: disable the 2-CTA cluster / weight-tile multicast variant */
 } lifter_gemm_desc_t;
 int lifter_gemm(const lifter_gemm_desc_t* desc, void* stream);
 int lifter_gemm_slab_rows(int M);
