@@ -30,7 +30,8 @@ class GemmDesc(C.Structure):
                 ("b_mn_major", C.c_int32), ("fmt", C.c_int32), ("out_mode", C.c_int32),
                 ("D", C.c_void_p), ("ldd", C.c_int64), ("n_valid", C.c_int32), ("splits", C.c_int32),
                 ("relu", C.c_int32), ("scale", C.c_void_p), ("shift", C.c_void_p), ("residual", C.c_void_p),
-                ("ldr", C.c_int64), ("stat_sum", C.c_void_p), ("stat_sq", C.c_void_p), ("no_cluster", C.c_int32)]
+                ("ldr", C.c_int64), ("stat_sum", C.c_void_p), ("stat_sq", C.c_void_p), ("cluster", C.c_int32),
+                ("timeline", C.c_void_p), ("dbg", C.c_int32)]
 
 
 class TrainCtx(C.Structure):

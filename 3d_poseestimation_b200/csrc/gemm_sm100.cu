@@ -17,6 +17,9 @@
 // or MN-major (wgrad contracts over the batch, so both of its operands are MN-major).
 #include "gemm_sm100.cuh"
 
+#include <stdlib.h>
+#include <string.h>
+
 namespace lifter {
 
 namespace {
@@ -58,7 +61,19 @@ struct alignas(64) GemmParams {
     int slab_rows;
     float* stat_sum;
     float* stat_sq;
+    unsigned long long* timeline;      // debug hook: [gridDim.x][32] globaltimer stamps (nullptr in production)
+    int dbg;                           // debug hook: 1 = MMAs without operand loads, 2 = operand loads without MMAs
 };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define TL_STAMP(slot)                                                                     \
+    do {                                                                                   \
+        if (p.timeline != nullptr) p.timeline[blockIdx.x * 32 + (slot)] = globaltimer_ns(); \
+    } while (0)
 
 // 64-bit shared-memory matrix descriptor, SWIZZLE_128B, sm_100 version bit set.
 //   K-major : rows of 128 B (64 elements of K), 8-row groups 1024 B apart (SBO); LBO unused.
@@ -96,14 +111,17 @@ __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], uint32_t lan
     return v[0];
 }
 
-// CL = CTAs per cluster.  With CL = 2 the two CTAs of a cluster work on vertically adjacent M-blocks of the same
-// N-block and K-range: each loads its own A tile and HALF of the shared B tile, multicast into both CTAs' smem, so
-// the L2->SM operand traffic per stage drops from 16 KB + B to 16 KB + B/2 per SM.  The MMAs stay per-CTA
-// (cta_group::1); only the smem-slot release is cluster-wide (each CTA's commit arrives on both empty barriers).
+// CL = CTAs per cluster (1, 2, 4 or 8).  The CTAs of a cluster work on vertically adjacent M-blocks of the same
+// N-block and K-range: each loads its own A tile and 1/CL of the shared B tile, multicast into every CTA's smem, so
+// the L2-side operand traffic per stage drops from 16 KB + B to 16 KB + B/CL per SM (the L2 -> SM fabric, ~9.5 TB/s
+// measured, is what bounds these GEMMs: profiles/README.md).  The MMAs stay per-CTA (cta_group::1); only the
+// smem-slot release is cluster-wide (each CTA's commit arrives on the empty barrier of every CTA).
 template <int BLOCK_N, int CL>
 __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
     using C = Cfg<BLOCK_N>;
-    static_assert(CL == 1 || (CL == 2 && BLOCK_N >= 128), "cluster multicast splits the B tile in two");
+    static_assert(CL == 1 || ((CL == 2 || CL == 4 || CL == 8) && BLOCK_N / CL >= 32),
+                  "cluster multicast splits the B tile in CL parts of >= 32 rows");
+    constexpr uint16_t CL_MASK = static_cast<uint16_t>((1u << CL) - 1u);
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t smem_base = smem_u32(smem);
     const uint32_t warp = threadIdx.x >> 5;
@@ -116,6 +134,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + C::OFF_TMEM_PTR);
 
     if (threadIdx.x == 0 && (smem_base & 1023u) != 0) __trap();   // SWIZZLE_128B needs 1024 B alignment
+    if (threadIdx.x == 0) TL_STAMP(0);
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&p.tmA);
@@ -140,6 +159,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
     tcgen05_fence_after();
     griddep_wait();                                           // everything above touched no global data
     const uint32_t tmem_base = *tmem_ptr_smem;
+    if (threadIdx.x == 0) TL_STAMP(1);
 
     const int tiles_per_m = p.num_n_blocks * p.splits;
     const uint32_t crank = CL > 1 ? cluster_ctarank() : 0;
@@ -158,6 +178,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
                 const int kb0 = split * p.k_blocks_per_split;
                 const int kb1 = min(kb0 + p.k_blocks_per_split, p.k_blocks_total);
                 for (int kb = kb0; kb < kb1; ++kb) {
+                    if (p.dbg == 1) continue;
                     mbar_wait(bar_empty + stage * 8, phase ^ 1);
                     const uint32_t full = bar_full + stage * 8;
                     mbar_arrive_expect_tx(full, C::STAGE_BYTES);
@@ -178,17 +199,17 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
                             for (int j = 0; j < BLOCK_N / 64; ++j)
                                 tma_load_2d(&p.tmB, sb + j * 8192, full, n_blk * BLOCK_N + j * 64, kb * BLOCK_K);
                         }
-                    } else {                                       // my half of B, delivered to both CTAs
-                        constexpr int HALF = BLOCK_N / 2;
+                    } else {                                       // my part of B, delivered to every CTA
+                        constexpr int PART = BLOCK_N / CL;
                         if (!p.b_mn_major) {
-                            tma_load_2d_multicast(&p.tmB, sb + crank * (HALF * 128), full, kb * BLOCK_K,
-                                                  n_blk * BLOCK_N + crank * HALF, 0x3);
-                        } else {
+                            tma_load_2d_multicast(&p.tmB, sb + crank * (PART * 128), full, kb * BLOCK_K,
+                                                  n_blk * BLOCK_N + crank * PART, CL_MASK);
+                        } else if (PART >= 64) {                   // (MN-major B moves in 64-column atoms)
 #pragma unroll
-                            for (int j = 0; j < HALF / 64; ++j) {
-                                const int atom = crank * (HALF / 64) + j;
+                            for (int j = 0; j < PART / 64; ++j) {
+                                const int atom = crank * (PART / 64) + j;
                                 tma_load_2d_multicast(&p.tmB, sb + atom * 8192, full, n_blk * BLOCK_N + atom * 64,
-                                                      kb * BLOCK_K, 0x3);
+                                                      kb * BLOCK_K, CL_MASK);
                             }
                         }
                     }
@@ -217,9 +238,17 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
             tcgen05_fence_after();
             const uint32_t tmem_d = tmem_base + as * BLOCK_N;
             for (int kb = kb0; kb < kb1; ++kb) {
-                mbar_wait(bar_full + stage * 8, phase);            // TMA bytes landed
+                if (p.dbg != 1) mbar_wait(bar_full + stage * 8, phase);            // TMA bytes landed
                 tcgen05_fence_after();
-                if (elect_one_sync()) {
+                if (p.dbg == 2) {
+                    if (elect_one_sync()) {
+                        if (CL == 1) mbar_arrive(bar_empty + stage * 8);
+                        else for (uint32_t r = 0; r < CL; ++r) mbar_arrive_remote(bar_empty + stage * 8, r);
+                        if (kb == kb1 - 1) umma_commit(bar_tfull + as * 8);
+                        if (kb == kb0 && it == 0) TL_STAMP(2);
+                        if (kb == kb1 - 1 && it < 8) TL_STAMP(4 + 3 * it);
+                    }
+                } else if (elect_one_sync()) {
                     const uint32_t a_lo = a_lo0 + stage * (A_STAGE_BYTES >> 4);
                     const uint32_t b_lo = b_lo0 + stage * (C::B_STAGE_BYTES >> 4);
 #pragma unroll
@@ -230,8 +259,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
                     }
                     // frees the smem slot (in every CTA of the cluster) when these MMAs retire
                     if (CL == 1) umma_commit(bar_empty + stage * 8);
-                    else umma_commit_multicast(bar_empty + stage * 8, 0x3);
+                    else umma_commit_multicast(bar_empty + stage * 8, CL_MASK);
                     if (kb == kb1 - 1) umma_commit(bar_tfull + as * 8);    // accumulator complete -> epilogue
+                    if (kb == kb0 && it == 0) TL_STAMP(2);
+                    if (kb == kb1 - 1 && it < 8) TL_STAMP(4 + 3 * it);
                 }
                 __syncwarp();
                 if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
@@ -269,6 +300,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
 
             mbar_wait(bar_tfull + as * 8, aph);
             tcgen05_fence_after();
+            if (threadIdx.x == 128 && it < 8) TL_STAMP(5 + 3 * it);
 
             const int row0 = m_blk * BLOCK_M + ew * 32;            // first row of this warp's slab
             const int row = row0 + lane;
@@ -391,6 +423,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) lifter_gemm_kernel(const __gri
                 for (int i = lane; i < limit; i += 32) gout[i] = stg_f[i];
                 __syncwarp();
             }
+            if (threadIdx.x == 128 && it < 8) TL_STAMP(6 + 3 * it);
         }
         if (lane == 0) tma_store_wait_all<0>();                    // smem must outlive the last bulk store
     }
@@ -473,10 +506,7 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     }
     p.num_n_blocks = ceil_div(a.N, BLOCK_N);
     p.num_tiles = ceil_div(p.num_m_blocks, CL) * p.num_n_blocks * p.splits;
-    const int max_clusters = num_sms() / CL;
-    const int clusters = p.num_tiles < max_clusters ? p.num_tiles : max_clusters;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(clusters * CL);
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = C::SMEM_BYTES;
     cfg.stream = stream;
@@ -486,12 +516,36 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    // clusters that can be co-resident (GPC boundaries may leave a few SMs out for CL > 1); queried once per variant
+    static int max_clusters = 0;
+    if (max_clusters == 0) {
+        int n = 0;
+        cfg.gridDim = dim3(num_sms() / CL * CL);
+        if (CL == 1 || cudaOccupancyMaxActiveClusters(&n, lifter_gemm_kernel<BLOCK_N, CL>, &cfg) != cudaSuccess || n <= 0)
+            n = num_sms() / CL;
+        (void)cudaGetLastError();
+        max_clusters = n < num_sms() / CL ? n : num_sms() / CL;
+    }
+    const int clusters = p.num_tiles < max_clusters ? p.num_tiles : max_clusters;
+    cfg.gridDim = dim3(clusters * CL);
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
     LIFTER_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lifter_gemm_kernel<BLOCK_N, CL>, p));
     return LIFTER_OK;
 }
 
 }  // namespace
+
+// default cluster size of long launches (LIFTER_GEMM_CLUSTER=1/2/4/8 overrides it for experiments)
+static int gemm_auto_cluster() {
+    static int cached = 0;
+    if (cached == 0) {
+        const char* e = getenv("LIFTER_GEMM_CLUSTER");
+        const int v = e != nullptr ? atoi(e) : 0;
+        cached = (v == 1 || v == 2 || v == 4 || v == 8) ? v : 2;
+    }
+    return cached;
+}
 
 int gemm_slab_rows(int M) { return ceil_div(M, BLOCK_M) * BLOCK_M; }
 int gemm_effective_splits(int K, int splits) {
@@ -534,15 +588,29 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     p.out_direct = static_cast<float*>(a.D); p.n_valid = a.n_valid;
     p.slab_rows = gemm_slab_rows(a.M);
     p.stat_sum = a.stat_sum; p.stat_sq = a.stat_sq;
+    p.timeline = a.timeline;
+    p.dbg = a.dbg;
 
-    // 2-CTA clusters (weight/B tile multicast) whenever there are at least two M-blocks to pair up
-    // (measured: worth it only when every CTA works through several tiles -- short launches lose more to the
-    //  cluster lock-step than they gain in L2 traffic)
-    const long tiles = static_cast<long>(p.num_m_blocks) * ceil_div(a.N, a.N <= 128 ? 128 : 256) * p.splits;
-    const bool pair = a.cluster != 0 && p.num_m_blocks >= 2 && a.N > 64 && (a.cluster == 2 || tiles >= 4L * num_sms());
-    if (a.N <= 64) return launch_impl<64, 1>(p, a, stream);
-    if (a.N <= 128) return pair ? launch_impl<128, 2>(p, a, stream) : launch_impl<128, 1>(p, a, stream);
-    return pair ? launch_impl<256, 2>(p, a, stream) : launch_impl<256, 1>(p, a, stream);
+    // Cluster size (B-tile multicast across CL vertically adjacent M-blocks).  a.cluster: 0 = auto, 1 = none,
+    // 2 / 4 / 8 = forced (clamped to what the tile shape allows).  Auto: measured on B200, the lock-step of a
+    // cluster only pays once every CTA works through several tiles.
+    const int bn = a.N <= 64 ? 64 : (a.N <= 128 ? 128 : 256);
+    const long tiles = static_cast<long>(p.num_m_blocks) * ceil_div(a.N, bn) * p.splits;
+    int cl = a.cluster;
+    if (cl == 0) cl = tiles >= 4L * num_sms() ? gemm_auto_cluster() : 1;
+    int cl_max = a.b_mn_major ? bn / 64 : bn / 32;                 // MN-major B moves in 64-column atoms
+    if (cl_max > 8) cl_max = 8;
+    while (cl > 1 && (cl > cl_max || cl > p.num_m_blocks)) cl >>= 1;
+    if (bn == 64) return launch_impl<64, 1>(p, a, stream);
+    if (bn == 128) {
+        if (cl >= 4) return launch_impl<128, 4>(p, a, stream);
+        if (cl == 2) return launch_impl<128, 2>(p, a, stream);
+        return launch_impl<128, 1>(p, a, stream);
+    }
+    if (cl == 8) return launch_impl<256, 8>(p, a, stream);
+    if (cl == 4) return launch_impl<256, 4>(p, a, stream);
+    if (cl == 2) return launch_impl<256, 2>(p, a, stream);
+    return launch_impl<256, 1>(p, a, stream);
 }
 
 }  // namespace lifter

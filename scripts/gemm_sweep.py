@@ -12,7 +12,8 @@ lib = cabi.lib()
 dev = torch.device("cuda")
 
 
-def time_gemm(M, N, K, fmt=1, no_cluster=0, out_mode=0, nbuf=4, iters=20, affine=True, a_mn=0, b_mn=0, splits=1):
+def time_gemm(M, N, K, fmt=1, cluster=0, out_mode=0, nbuf=4, iters=20, affine=True, a_mn=0, b_mn=0, splits=1,
+              timeline=False, residual=False, dbg=0):
     dt = torch.bfloat16 if fmt else torch.float16
     As = [(torch.randn(K, M, device=dev) if a_mn else torch.randn(M, K, device=dev)).to(dt) for _ in range(nbuf)]
     W = ((torch.randn(K, N, device=dev) if b_mn else torch.randn(N, K, device=dev)) * 0.03).to(dt)
@@ -21,6 +22,8 @@ def time_gemm(M, N, K, fmt=1, no_cluster=0, out_mode=0, nbuf=4, iters=20, affine
     else:
         D = torch.empty(lib.lifter_gemm_effective_splits(K, splits) * lib.lifter_gemm_slab_rows(M), N, device=dev)
     scale, shift = torch.ones(N, device=dev), torch.zeros(N, device=dev)
+    R = torch.randn(M, N, device=dev).to(dt) if residual else None
+    tl = torch.zeros(160 * 32, dtype=torch.int64, device=dev) if timeline else None
     st = cabi.stream_ptr()
 
     def launch(i):
@@ -28,7 +31,12 @@ def time_gemm(M, N, K, fmt=1, no_cluster=0, out_mode=0, nbuf=4, iters=20, affine
         A = As[i % nbuf]
         d.A, d.lda, d.B, d.ldb = A.data_ptr(), A.stride(0), W.data_ptr(), W.stride(0)
         d.M, d.N, d.K, d.fmt, d.out_mode, d.D, d.ldd = M, N, K, fmt, out_mode, D.data_ptr(), N
-        d.a_mn_major, d.b_mn_major, d.splits, d.no_cluster = a_mn, b_mn, splits, no_cluster
+        d.a_mn_major, d.b_mn_major, d.splits, d.cluster = a_mn, b_mn, splits, cluster
+        d.dbg = dbg
+        if R is not None:
+            d.residual, d.ldr = R.data_ptr(), N
+        if tl is not None:
+            d.timeline = tl.data_ptr()
         if affine and out_mode == 0:
             d.relu, d.scale, d.shift = 1, scale.data_ptr(), shift.data_ptr()
         cabi.check(lib.lifter_gemm(C.byref(d), st))
@@ -42,22 +50,33 @@ def time_gemm(M, N, K, fmt=1, no_cluster=0, out_mode=0, nbuf=4, iters=20, affine
     e1.record()
     torch.cuda.synchronize()
     us = e0.elapsed_time(e1) / iters * 1e3
+    if tl is not None:
+        show_timeline(tl.cpu().view(160, 32))
     return us, 2.0 * M * N * K / us / 1e6
 
 
+def show_timeline(t):
+    """Phases of the last launch, per CTA, in us relative to the earliest CTA start (median / max over CTAs)."""
+    t = t[t[:, 0] > 0].double()
+    t0 = t[:, 0].min()
+    names = {0: "cta start", 1: "setup done", 2: "first MMA issued"}
+    for it in range(4):
+        names[4 + 3 * it] = f"tile {it}: last MMA issued"
+        names[5 + 3 * it] = f"tile {it}: accumulator ready"
+        names[6 + 3 * it] = f"tile {it}: epilogue done"
+    for slot in sorted(names):
+        col = t[:, slot]
+        col = col[col > 0]
+        if len(col) == 0:
+            continue
+        rel = (col - t0) / 1e3
+        print(f"      {names[slot]:28s} n={len(col):3d} median {rel.median():7.2f}  min {rel.min():7.2f}  max {rel.max():7.2f} us")
+
+
 if __name__ == "__main__":
-    print("M N K cluster | us TFLOP/s")
-    for nc in (1, 0):
-        for (M, N, K) in [(148 * 128, 256, 64), (148 * 128, 256, 1024), (148 * 128, 256, 4096), (148 * 128, 256, 16384),
-                          (148 * 128 * 4, 256, 1024), (9472, 1024, 1024), (8192, 1024, 1024), (9472 * 4, 1024, 1024),
-                          (65536, 1024, 1024), (9472, 1024, 4096)]:
-            us, tf = time_gemm(M, N, K, no_cluster=nc)
-            print(f"{M:7d} {N:5d} {K:6d} cl={'off' if nc else 'on '} | {us:9.2f} us {tf:8.1f} TF")
-    print("wgrad-shaped (MN-major both, split 4, fp32 slabs):")
-    for nc in (1, 0):
-        us, tf = time_gemm(1024, 1024, 8192, a_mn=1, b_mn=1, out_mode=1, splits=4, no_cluster=nc)
-        print(f"   1024  1024   8192 cl={'off' if nc else 'on '} | {us:9.2f} us {tf:8.1f} TF")
-    print("dgrad-shaped (B MN-major):")
-    for nc in (1, 0):
-        us, tf = time_gemm(8192, 1024, 1024, b_mn=1, no_cluster=nc)
-        print(f"   8192  1024   1024 cl={'off' if nc else 'on '} | {us:9.2f} us {tf:8.1f} TF")
+    for dbg in (0, 1, 2):
+        for cl in (1, 2):
+            for M in (8192, 65536):
+                print(f"dbg={dbg} (1: MMA only, 2: loads only) cl={cl} M={M}")
+                us, tf = time_gemm(M, 1024, 1024, cluster=cl, dbg=dbg, timeline=True, nbuf=2)
+                print(f"   -> {us:9.2f} us {tf:8.1f} TF")

@@ -24,12 +24,12 @@ def _dt(fmt):
 
 
 def run_gemm(c, A, B, M, N, K, a_mn, b_mn, fmt, out_mode, D, ldd, n_valid=0, splits=1, relu=0, scale=None,
-             shift=None, residual=None, stat=None, no_cluster=0):
+             shift=None, residual=None, stat=None, cluster=0):
     d = c.GemmDesc()
     d.A, d.lda, d.B, d.ldb = A.data_ptr(), A.stride(0), B.data_ptr(), B.stride(0)
     d.M, d.N, d.K, d.a_mn_major, d.b_mn_major, d.fmt = M, N, K, a_mn, b_mn, fmt
     d.out_mode, d.D, d.ldd, d.n_valid, d.splits, d.relu = out_mode, D.data_ptr(), ldd, n_valid, splits, relu
-    d.no_cluster = no_cluster
+    d.cluster = cluster
     d.scale = scale.data_ptr() if scale is not None else None
     d.shift = shift.data_ptr() if shift is not None else None
     if residual is not None:
@@ -50,30 +50,30 @@ def _operands(M, N, K, a_mn, b_mn, fmt, seed):
     return A, B, ref
 
 
-@pytest.mark.parametrize("no_cluster", [0, 1])
+@pytest.mark.parametrize("cluster", [1, 2, 4, 8])
 @pytest.mark.parametrize("fmt", [0, 1])
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (128, 256, 64), (256, 256, 256), (384, 1024, 1024), (640, 1024, 256),
                                    (1000, 128, 192), (77, 512, 128), (9472, 1024, 1024)])
-def test_kmajor_16bit_output(cabi, M, N, K, fmt, no_cluster):
+def test_kmajor_16bit_output(cabi, M, N, K, fmt, cluster):
     A, B, ref = _operands(M, N, K, 0, 0, fmt, 1)
     D = torch.full((M, N), float("nan"), device="cuda").to(_dt(fmt))
-    run_gemm(cabi, A, B, M, N, K, 0, 0, fmt, cabi.OUT_16, D, N, no_cluster=no_cluster)
+    run_gemm(cabi, A, B, M, N, K, 0, 0, fmt, cabi.OUT_16, D, N, cluster=cluster)
     err = (D.double() - ref).abs().max().item()
     tol = (2 ** -10 if fmt == 0 else 2 ** -7) * ref.abs().max().item() + 1e-3
     assert torch.isfinite(D.float()).all(), "unwritten / non-finite outputs"
     assert err <= tol, f"max err {err} > {tol}"
 
 
-@pytest.mark.parametrize("no_cluster", [0, 1])
+@pytest.mark.parametrize("cluster", [1, 2, 4, 8])
 @pytest.mark.parametrize("a_mn,b_mn", [(0, 1), (1, 0), (1, 1)])
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 256, 128), (1024, 1024, 512), (200, 320, 100), (200, 320, 104)])
-def test_mn_major_operands(cabi, M, N, K, a_mn, b_mn, no_cluster):
+def test_mn_major_operands(cabi, M, N, K, a_mn, b_mn, cluster):
     fmt = 1
     if (a_mn and M % 8) or (b_mn and N % 8) or ((not a_mn or not b_mn) and K % 8):
         pytest.skip("row stride must be a multiple of 16 bytes")
     A, B, ref = _operands(M, N, K, a_mn, b_mn, fmt, 2)
     D = torch.full((M, N), float("nan"), device="cuda").to(_dt(fmt))
-    run_gemm(cabi, A, B, M, N, K, a_mn, b_mn, fmt, cabi.OUT_16, D, N, no_cluster=no_cluster)
+    run_gemm(cabi, A, B, M, N, K, a_mn, b_mn, fmt, cabi.OUT_16, D, N, cluster=cluster)
     err = (D.double() - ref).abs().max().item()
     tol = 2 ** -7 * ref.abs().max().item() + 1e-3
     assert torch.isfinite(D.float()).all()
