@@ -31,7 +31,7 @@ class GemmDesc(C.Structure):
                 ("D", C.c_void_p), ("ldd", C.c_int64), ("n_valid", C.c_int32), ("splits", C.c_int32),
                 ("relu", C.c_int32), ("scale", C.c_void_p), ("shift", C.c_void_p), ("residual", C.c_void_p),
                 ("ldr", C.c_int64), ("stat_sum", C.c_void_p), ("stat_sq", C.c_void_p), ("cluster", C.c_int32),
-                ("timeline", C.c_void_p), ("dbg", C.c_int32)]
+                ("timeline", C.c_void_p), ("max_stages", C.c_int32)]
 
 
 class TrainCtx(C.Structure):

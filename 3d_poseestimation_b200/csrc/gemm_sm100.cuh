@@ -24,14 +24,14 @@ struct GemmArgs {
     int n_valid = 0;                          // OUT_32_DIRECT only
     int splits = 1;                           // split-K (OUT_32_TMA): slab s starts at row s * slab_rows(M)
     int relu = 0;
-    int cluster = 0;                          // B-tile multicast over a CTA cluster: 0 auto, 1 none, 2/4/8 forced size
+    int cluster = 0;                          // 0 auto, 1 single-CTA tiles (cta_group::1), 2 CTA pairs (cta_group::2)
     const float* scale = nullptr;             // per-column multiply (nullptr = 1)
     const float* shift = nullptr;             // per-column add      (nullptr = 0)
     const void* residual = nullptr; long ldr = 0;   // 16-bit [M][ldr], added after the activation
     float* stat_sum = nullptr;                // [4*ceil(M/128)][N] per-32-row-slab column sums of the stored values
     float* stat_sq = nullptr;                 // same, squares
     unsigned long long* timeline = nullptr;   // debug hook: [grid][32] globaltimer stamps
-    int dbg = 0;                              // debug hook: 1 = MMAs without loads, 2 = loads without MMAs (garbage output)
+    int max_stages = 0;                       // debug hook: cap the operand ring depth (0 = all that fit)
 };
 
 int gemm_slab_rows(int M);                    // rows of one split-K slab (M rounded up to 128)

@@ -191,9 +191,9 @@ int lifter_gemm(const lifter_gemm_desc_t* d, void* stream) {
     g.out_mode = d->out_mode; g.D = d->D; g.ldd = d->ldd; g.n_valid = d->n_valid; g.splits = d->splits < 1 ? 1 : d->splits;
     g.relu = d->relu; g.scale = d->scale; g.shift = d->shift; g.residual = d->residual; g.ldr = d->ldr;
     g.stat_sum = d->stat_sum; g.stat_sq = d->stat_sq;
-    g.cluster = d->cluster;                                        // test hook: 0 auto, 1 none, 2/4/8 forced
+    g.cluster = d->cluster;                                        // test hook: 0 auto, 1 single-CTA, 2 pairs
     g.timeline = static_cast<unsigned long long*>(d->timeline);
-    g.dbg = d->dbg;
+    g.max_stages = d->max_stages;
     return gemm_launch(g, static_cast<cudaStream_t>(stream));
 }
 int lifter_gemm_slab_rows(int M) { return gemm_slab_rows(M); }

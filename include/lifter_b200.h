@@ -151,9 +151,9 @@ typedef struct lifter_gemm_desc {
     void* D; int64_t ldd; int32_t n_valid; int32_t splits; int32_t relu;
     const float* scale; const float* shift; const void* residual; int64_t ldr;
     float* stat_sum; float* stat_sq;
-    int32_t cluster;             /* CTA cluster sharing the weight tile by TMA multicast: 0 auto, 1 none, 2/4/8 forced */
+    int32_t cluster;             /* 0 auto, 1 single-CTA tiles (cta_group::1), 2 CTA pairs (cta_group::2, 256-row tiles) */
     void* timeline;              /* debug: uint64 [grid][32] globaltimer stamps of the kernel's phases, or NULL */
-    int32_t dbg;                 /* debug: 0 normal; 1 = MMAs without operand loads, 2 = loads without MMAs (output is garbage) */
+    int32_t max_stages;          /* debug: cap on the operand ring depth (0 = all that fit in shared memory) */
 } lifter_gemm_desc_t;
 int lifter_gemm(const lifter_gemm_desc_t* desc, void* stream);
 int lifter_gemm_slab_rows(int M);

@@ -13,7 +13,7 @@ dev = torch.device("cuda")
 
 
 def time_gemm(M, N, K, fmt=1, cluster=0, out_mode=0, nbuf=4, iters=20, affine=True, a_mn=0, b_mn=0, splits=1,
-              timeline=False, residual=False, dbg=0):
+              timeline=False, residual=False, max_stages=0):
     dt = torch.bfloat16 if fmt else torch.float16
     As = [(torch.randn(K, M, device=dev) if a_mn else torch.randn(M, K, device=dev)).to(dt) for _ in range(nbuf)]
     W = ((torch.randn(K, N, device=dev) if b_mn else torch.randn(N, K, device=dev)) * 0.03).to(dt)
@@ -32,7 +32,7 @@ def time_gemm(M, N, K, fmt=1, cluster=0, out_mode=0, nbuf=4, iters=20, affine=Tr
         d.A, d.lda, d.B, d.ldb = A.data_ptr(), A.stride(0), W.data_ptr(), W.stride(0)
         d.M, d.N, d.K, d.fmt, d.out_mode, d.D, d.ldd = M, N, K, fmt, out_mode, D.data_ptr(), N
         d.a_mn_major, d.b_mn_major, d.splits, d.cluster = a_mn, b_mn, splits, cluster
-        d.dbg = dbg
+        d.max_stages = max_stages
         if R is not None:
             d.residual, d.ldr = R.data_ptr(), N
         if tl is not None:
@@ -74,9 +74,8 @@ def show_timeline(t):
 
 
 if __name__ == "__main__":
-    for dbg in (0, 1, 2):
-        for cl in (1, 2):
+    for cl in (2, 1):
+        for st in (2, 3, 4, 5):
             for M in (8192, 65536):
-                print(f"dbg={dbg} (1: MMA only, 2: loads only) cl={cl} M={M}")
-                us, tf = time_gemm(M, 1024, 1024, cluster=cl, dbg=dbg, timeline=True, nbuf=2)
-                print(f"   -> {us:9.2f} us {tf:8.1f} TF")
+                us, tf = time_gemm(M, 1024, 1024, cluster=cl, max_stages=st, nbuf=2)
+                print(f"cl={cl} stages<={st} M={M}: {us:9.2f} us {tf:8.1f} TF")
