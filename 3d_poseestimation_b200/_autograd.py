@@ -23,7 +23,7 @@ def _dist_world(model):
     return pg, dist.get_world_size(pg), dist.get_rank(pg)
 
 
-def _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offset):
+def _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offset, step_state=None):
     t = _cabi.TrainCtx()
     t.params = model._flat.data_ptr()
     t.operands = model._operands(fmt).data_ptr()
@@ -37,10 +37,11 @@ def _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offse
     t.batch, t.global_batch, t.row_offset = x.shape[0] if x is not None else 0, global_batch, row_offset
     t.fmt, t.bn_mode, t.apply_dropout = fmt, (0 if training else 1), (1 if training else 0)
     t.step, t.seed = step & 0xFFFFFFFF, model.dropout_seed & 0xFFFFFFFFFFFFFFFF
+    t.step_state = step_state.data_ptr() if step_state is not None else None
     return t
 
 
-def run_forward(model, x, training, saved=None, out=None, step=None):
+def run_forward(model, x, training, saved=None, out=None, step=None, step_state=None):
     """Forward with saved activations.  Returns (out, saved, ctx_struct)."""
     lib, cfg = _cabi.lib(), C.byref(model._cfg)
     fmt = model._fmt_code(model.train_format)
@@ -58,7 +59,7 @@ def run_forward(model, x, training, saved=None, out=None, step=None):
         saved = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
     if out is None:
         out = torch.empty(B, model.output_size, dtype=torch.float32, device=x.device)
-    t = _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offset)
+    t = _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offset, step_state)
     st = _cabi.stream_ptr()
     if not sync_bn:
         _cabi.check(lib.lifter_train_forward(cfg, C.byref(t), st))

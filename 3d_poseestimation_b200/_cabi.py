@@ -42,7 +42,7 @@ class TrainCtx(C.Structure):
                 ("global_batch", C.c_int64), ("row_offset", C.c_int64), ("fmt", C.c_int32), ("bn_mode", C.c_int32),
                 ("apply_dropout", C.c_int32), ("step", C.c_uint32), ("seed", C.c_uint64), ("grad_out", C.c_void_p),
                 ("grad_params", C.c_void_p), ("grad_x", C.c_void_p), ("scratch", C.c_void_p),
-                ("scratch_bytes", C.c_int64)]
+                ("scratch_bytes", C.c_int64), ("step_state", C.c_void_p)]
 
 
 LOSS_MSE, LOSS_L1, LOSS_MPJPE = 0, 1, 2
@@ -82,7 +82,11 @@ SIGNATURES = {
     "lifter_l1_sum": (_I32, [_P, _P, _I64, _I32, _I32, _F, _P, _P, _P]),
     "lifter_l1_grad": (_I32, [_P, _P, _I64, _I32, _I32, _P, _F, _P, _P, _P]),
     "lifter_adam_step": (_I32, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _I32, _F, _P]),
+    "lifter_step_advance": (_I32, [_P, _F, _F, _F, _P]),
+    "lifter_adam_step_packed": (_I32, [_CFG, _P, _P, _P, _P, _F, _F, _F, _F, _F, _I32, _I32, _F, _P, _P, _I32, _P]),
     "lifter_gemm": (_I32, [C.POINTER(GemmDesc), _P]),
+    "lifter_trace_begin": (_I32, [_P]),
+    "lifter_trace_end": (_I32, [C.c_char_p, _I32]),
     "lifter_gemm_slab_rows": (_I32, [_I32]),
     "lifter_gemm_stat_rows": (_I32, [_I32]),
     "lifter_gemm_effective_splits": (_I32, [_I32, _I32]),

@@ -3,6 +3,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <string>
+#include <vector>
+
 namespace lifter {
 
 static thread_local char g_error[512] = "";
@@ -35,6 +38,49 @@ bool pdl_enabled() {
         cached = (e != nullptr && e[0] == '1') ? 0 : 1;
     }
     return cached == 1;
+}
+
+// ---- debug trace -------------------------------------------------------------------------------------
+namespace {
+struct TraceRec { std::string name; cudaEvent_t ev; };
+std::vector<TraceRec> g_trace;
+bool g_trace_on = false;
+}  // namespace
+
+void trace_mark(const char* name, cudaStream_t st) {
+    if (!g_trace_on) return;
+    TraceRec r;
+    r.name = name;
+    if (cudaEventCreate(&r.ev) != cudaSuccess) return;
+    cudaEventRecord(r.ev, st);
+    g_trace.push_back(r);
+}
+
+int trace_begin(cudaStream_t st) {
+    for (auto& r : g_trace) cudaEventDestroy(r.ev);
+    g_trace.clear();
+    g_trace_on = true;
+    trace_mark("begin", st);
+    return LIFTER_OK;
+}
+
+// writes "name us\n" per launch since trace_begin (time from the previous mark to this launch's completion)
+int trace_end(char* buf, int len) {
+    g_trace_on = false;
+    if (buf == nullptr || len <= 0) return LIFTER_ERR_INVALID;
+    int off = 0;
+    buf[0] = 0;
+    for (size_t i = 1; i < g_trace.size(); ++i) {
+        if (cudaEventSynchronize(g_trace[i].ev) != cudaSuccess) return LIFTER_ERR_CUDA;
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, g_trace[i - 1].ev, g_trace[i].ev);
+        const int n = snprintf(buf + off, len - off, "%s %.3f\n", g_trace[i].name.c_str(), ms * 1e3);
+        if (n < 0 || n >= len - off) break;
+        off += n;
+    }
+    for (auto& r : g_trace) cudaEventDestroy(r.ev);
+    g_trace.clear();
+    return off;
 }
 
 }  // namespace lifter

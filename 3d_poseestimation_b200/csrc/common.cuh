@@ -58,9 +58,14 @@ enum : int { FMT_F16 = 0, FMT_BF16 = 1 };
 // Launch with programmatic stream serialization: the kernel may be scheduled while its predecessor in the stream
 // drains; every kernel of this library calls griddep_wait() before it touches global memory and
 // griddep_launch() first thing, so launch latency and prologues overlap the previous kernel's tail.
+// debug trace (lifter_trace_begin / lifter_trace_end): a CUDA event after every launch, read back as per-kernel times
+void trace_mark(const char* name, cudaStream_t st);
+int trace_begin(cudaStream_t st);
+int trace_end(char* buf, int len);
+
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
-                              Args&&... args) {
+inline cudaError_t launch_pdl(const char* name, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t st, Args&&... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = block;
@@ -71,7 +76,9 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl_enabled() ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+    trace_mark(name, st);
+    return e;
 }
 
 // ------------------------------------------------------------------------------------------------

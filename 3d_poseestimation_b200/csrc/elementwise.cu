@@ -90,14 +90,14 @@ __global__ void make_out_affine_kernel(const float* __restrict__ bias, const flo
 int convert_pad(const float* src, int rows, int cols, void* dst, int rows_p, int cols_p, int fmt, cudaStream_t st) {
     LIFTER_REQUIRE(cols_p % 8 == 0 && rows_p >= rows && cols_p >= cols, "convert_pad: bad padding");
     const long n = static_cast<long>(rows_p) * (cols_p / 8);
-    LIFTER_CHECK_CUDA(launch_pdl(convert_pad_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, src, rows, cols,
+    LIFTER_CHECK_CUDA(launch_pdl("convert_pad_kernel", convert_pad_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, src, rows, cols,
                                                                              static_cast<uint16_t*>(dst), rows_p, cols_p, fmt));
     return LIFTER_OK;
 }
 
 int fold_bn(const float* bias, const float* gamma, const float* beta, const float* rm, const float* rv, int H,
             int use_bn, float eps, float* scale, float* shift, cudaStream_t st) {
-    LIFTER_CHECK_CUDA(launch_pdl(fold_bn_kernel, dim3(ceil_div(H, 256)), dim3(256), 0, st, bias, gamma, beta, rm, rv, H, use_bn, eps, scale, shift));
+    LIFTER_CHECK_CUDA(launch_pdl("fold_bn_kernel", fold_bn_kernel, dim3(ceil_div(H, 256)), dim3(256), 0, st, bias, gamma, beta, rm, rv, H, use_bn, eps, scale, shift));
     return LIFTER_OK;
 }
 
@@ -106,14 +106,14 @@ int prep_input(const float* x, int64_t rows, int I, int Ip, const float* mean, c
     LIFTER_REQUIRE(Ip % 8 == 0 && Ip >= I, "prep_input: bad padding");
     LIFTER_REQUIRE((mean == nullptr) == (stdv == nullptr), "prep_input: mean and std come together");
     const long n = rows * (Ip / 8);
-    LIFTER_CHECK_CUDA(launch_pdl(prep_input_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, x, rows, I, Ip, mean, stdv,
+    LIFTER_CHECK_CUDA(launch_pdl("prep_input_kernel", prep_input_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, x, rows, I, Ip, mean, stdv,
                                                                             static_cast<uint16_t*>(dst), fmt));
     return LIFTER_OK;
 }
 
 int make_out_affine(const float* bias, const float* mean, const float* stdv, int O, int Op, float* scale, float* shift,
                     cudaStream_t st) {
-    LIFTER_CHECK_CUDA(launch_pdl(make_out_affine_kernel, dim3(1), dim3(64), 0, st, bias, mean, stdv, O, Op, scale, shift));
+    LIFTER_CHECK_CUDA(launch_pdl("make_out_affine_kernel", make_out_affine_kernel, dim3(1), dim3(64), 0, st, bias, mean, stdv, O, Op, scale, shift));
     return LIFTER_OK;
 }
 

@@ -73,7 +73,7 @@ struct alignas(64) GemmParams {
     CUtensorMap tmA, tmB, tmD, tmR;
     int M, N, K;
     int num_m_blocks, num_n_blocks, splits, k_blocks_total, k_blocks_per_split, num_tiles;   // num_tiles counts M-groups
-    int a_mn_major, b_mn_major, fmt, out_mode, relu, has_affine, has_residual;
+    int a_mn_major, b_mn_major, fmt, out_mode, relu, has_affine, has_residual, affine_n;
     const float* scale;
     const float* shift;
     float* out_direct;
@@ -305,8 +305,8 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                 named_bar_sync(1, 32 * C::EPI_WARPS);
                 for (int i = ew * 32 + lane; i < BLOCK_N; i += 32 * C::EPI_WARPS) {
                     const int n = n_blk * BLOCK_N + i;
-                    s_scale[i] = (p.scale != nullptr && n < p.N) ? p.scale[n] : 1.0f;
-                    s_shift[i] = (p.shift != nullptr && n < p.N) ? p.shift[n] : 0.0f;
+                    s_scale[i] = (p.scale != nullptr && n < p.affine_n) ? p.scale[n] : 1.0f;
+                    s_shift[i] = (p.shift != nullptr && n < p.affine_n) ? p.shift[n] : 0.0f;
                 }
                 named_bar_sync(1, 32 * C::EPI_WARPS);
                 cached_n_blk = n_blk;
@@ -557,6 +557,7 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     cfg.gridDim = dim3(clusters * CL);
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
     LIFTER_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lifter_gemm_kernel<BLOCK_N, TWO_SM>, p));
+    if (a.tag != nullptr) trace_mark(a.tag, stream); else trace_mark("gemm", stream);
     return LIFTER_OK;
 }
 
@@ -598,6 +599,7 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     p.has_affine = (a.scale != nullptr || a.shift != nullptr) ? 1 : 0;
     p.has_residual = a.residual != nullptr ? 1 : 0;
     p.scale = a.scale; p.shift = a.shift;
+    p.affine_n = (a.shift_valid > 0 && a.shift_valid < a.N) ? a.shift_valid : a.N;
     p.out_direct = static_cast<float*>(a.D); p.n_valid = a.n_valid;
     p.slab_rows = gemm_slab_rows(a.M);
     p.stat_sum = a.stat_sum; p.stat_sq = a.stat_sq;

@@ -27,10 +27,12 @@ struct GemmArgs {
     int cluster = 0;                          // 0 auto, 1 single-CTA tiles (cta_group::1), 2 CTA pairs (cta_group::2)
     const float* scale = nullptr;             // per-column multiply (nullptr = 1)
     const float* shift = nullptr;             // per-column add      (nullptr = 0)
+    int shift_valid = 0;                      // entries of scale/shift that exist (0 = N); columns past it use 1 / 0
     const void* residual = nullptr; long ldr = 0;   // 16-bit [M][ldr], added after the activation
     float* stat_sum = nullptr;                // [4*ceil(M/128)][N] per-32-row-slab column sums of the stored values
     float* stat_sq = nullptr;                 // same, squares
     unsigned long long* timeline = nullptr;   // debug hook: [grid][32] globaltimer stamps
+    const char* tag = nullptr;                // name in the debug trace
     int max_stages = 0;                       // debug hook: cap the operand ring depth (0 = all that fit)
 };
 

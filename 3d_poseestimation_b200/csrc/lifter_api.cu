@@ -196,6 +196,8 @@ int lifter_gemm(const lifter_gemm_desc_t* d, void* stream) {
     g.max_stages = d->max_stages;
     return gemm_launch(g, static_cast<cudaStream_t>(stream));
 }
+int lifter_trace_begin(void* stream) { return trace_begin(static_cast<cudaStream_t>(stream)); }
+int lifter_trace_end(char* buf, int len) { return trace_end(buf, len); }
 int lifter_gemm_slab_rows(int M) { return gemm_slab_rows(M); }
 int lifter_gemm_stat_rows(int M) { return gemm_stat_rows(M); }
 int lifter_gemm_effective_splits(int K, int splits) { return gemm_effective_splits(K, splits); }

@@ -203,6 +203,7 @@ static int fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_ctx_t* 
     g.B = ops + lay.w_off[l]; g.ldb = lay.in_pad(l);
     g.M = B; g.N = H; g.K = lay.in_pad(l); g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.D = w.z[l]; g.ldd = H;
     if (stats) { g.stat_sum = w.psum; g.stat_sq = w.psq; }
+    g.tag = "gemm_fwd";
     LIFTER_PROPAGATE(gemm_launch(g, st));
     if (stats && !fused)
         LIFTER_PROPAGATE(reduce_rows_f64(w.psum, w.psq, gemm_stat_rows(B), H, H, w.sums[l], w.sums[l] + H, st));
@@ -237,6 +238,7 @@ static int fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     a.rows = t->batch; a.H = H; a.fmt = t->fmt;
     a.apply_dropout = t->apply_dropout && cfg->p_dropout > 0.0f; a.p = cfg->p_dropout;
     a.seed = t->seed; a.step = t->step; a.site = static_cast<unsigned>(l); a.row_offset = t->row_offset;
+    a.step_dev = t->step_state != nullptr ? reinterpret_cast<const unsigned*>(t->step_state) : nullptr;
     a.a = w.a[l]; a.bits = w.bits[l];
     LIFTER_PROPAGATE(bn_apply_fwd(a, st));
     return LIFTER_OK;
@@ -255,13 +257,13 @@ int lifter_train_fwd_output(const lifter_config_t* cfg, const lifter_train_ctx_t
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     SavedWs w;
     carve_saved(lay, t->batch, t->saved, &w);
-    LIFTER_PROPAGATE(make_out_affine(t->params + lay.p_off[lay.t_b2()], nullptr, nullptr, lay.O, lay.Op, w.out_scale,
-                                     w.out_shift, st));
     GemmArgs g;
     g.A = w.a[lay.L - 1]; g.lda = lay.H;
     g.B = static_cast<const uint16_t*>(t->operands) + lay.w_off[lay.L]; g.ldb = lay.H;
     g.M = static_cast<int>(t->batch); g.N = lay.Op; g.K = lay.H; g.fmt = t->fmt; g.out_mode = OUT_32_DIRECT;
-    g.D = t->out; g.n_valid = lay.O; g.scale = w.out_scale; g.shift = w.out_shift;
+    g.D = t->out; g.n_valid = lay.O;
+    g.shift = t->params + lay.p_off[lay.t_b2()]; g.shift_valid = lay.O;   // + b2 (columns past o_dim are never stored)
+    g.tag = "gemm_fwd_out";
     return gemm_launch(g, st);
 }
 
@@ -284,6 +286,7 @@ static int wgrad(const Layout& lay, const lifter_train_ctx_t* t, const ScratchWs
     g.B = a_in; g.ldb = lda_in; g.b_mn_major = 1;
     g.M = M; g.N = N; g.K = B; g.fmt = t->fmt; g.out_mode = OUT_32_TMA; g.D = b.slabs; g.ldd = N;
     g.splits = wgrad_splits(M, N, B);
+    g.tag = "gemm_wgrad";
     LIFTER_PROPAGATE(gemm_launch(g, st));
     return wgrad_reduce(b.slabs, gemm_effective_splits(B, g.splits), gemm_slab_rows(M), N, rows_valid, cols_valid, grad, st);
 }
@@ -307,6 +310,7 @@ int lifter_train_bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t*
     GemmArgs g;
     g.A = b.dO; g.lda = lay.Op; g.B = ops + lay.w_off[lay.L]; g.ldb = H; g.b_mn_major = 1;
     g.M = B; g.N = H; g.K = lay.Op; g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.D = b.G[0]; g.ldd = H;
+    g.tag = "gemm_dgrad_top";
     return gemm_launch(g, st);
 }
 
@@ -316,6 +320,23 @@ static const uint16_t* g_in(const Layout& lay, const ScratchWs& b, int l) {
     if (l % 2 == 1) return b.Gh;                                  // first layer of a block: dh from the second
     const int block_from_top = (lay.L - 1 - l) / 2;               // l even: stream gradient dX
     return b.G[block_from_top & 1];
+}
+
+static float inv_keep_of(const lifter_config_t* cfg, const lifter_train_ctx_t* t) {
+    const bool drop = t->apply_dropout && cfg->p_dropout > 0.0f;
+    return drop ? (cfg->p_dropout < 1.0f ? 1.0f / (1.0f - cfg->p_dropout) : 0.0f) : 1.0f;
+}
+
+static BnBwdFinalize bwd_finalize_args(const lifter_config_t* cfg, const lifter_train_ctx_t* t, const Layout& lay,
+                                       const SavedWs& w, const ScratchWs& b, int l) {
+    BnBwdFinalize f;
+    f.sums = b.bsums[l]; f.count = static_cast<double>(t->global_batch);
+    f.gamma = t->params + lay.p_off[lay.t_gamma(l)]; f.rstd = w.rstd[l]; f.mean_z = w.mean_z[l];
+    f.inv_keep = inv_keep_of(cfg, t);
+    f.H = lay.H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode; f.coef = b.coef;
+    // batch-statistics BN cancels the Linear bias: its gradient is exactly zero
+    f.dbias = (cfg->use_bn && t->bn_mode == 0) ? t->grad_params + lay.p_off[lay.t_bias(l)] : nullptr;
+    return f;
 }
 
 static int bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
@@ -329,24 +350,13 @@ static int bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t*
     carve_scratch(lay, t->batch, t->scratch, &b);
     const int H = lay.H;
     BwdCommon c;
-    c.g = g_in(lay, b, l); c.z = w.z[l]; c.bits = w.bits[l]; c.mean_z = w.mean_z[l]; c.rstd = w.rstd[l];
+    c.g = g_in(lay, b, l); c.z = w.z[l]; c.bits = w.bits[l];
     c.rows = t->batch; c.H = H; c.fmt = t->fmt;
-    const bool drop = t->apply_dropout && cfg->p_dropout > 0.0f;
-    c.inv_keep = drop ? (cfg->p_dropout < 1.0f ? 1.0f / (1.0f - cfg->p_dropout) : 0.0f) : 1.0f;
     LIFTER_PROPAGATE(bwd_stats(c, b.pA, b.pB, st));
-    if (fused) {                                                   // reduce + dgamma/dbeta + coefficients in one launch
-        BnBwdFinalize f;
-        f.sums = b.bsums[l]; f.count = static_cast<double>(t->global_batch);
-        f.gamma = t->params + lay.p_off[lay.t_gamma(l)]; f.rstd = w.rstd[l];
-        f.H = H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode; f.coef = b.coef;
-        return bn_reduce_finalize_bwd(b.pA, b.pB, ew_partial_rows(t->batch, H), f, b.bsums[l],
-                                      t->grad_params + lay.p_off[lay.t_gamma(l)],
-                                      t->grad_params + lay.p_off[lay.t_beta(l)], st);
-    }
-    LIFTER_PROPAGATE(reduce_rows_f64(b.pA, b.pB, ew_partial_rows(t->batch, H), H, H, b.bsums[l], b.bsums[l] + H, st));
-    // parameter gradients from the LOCAL sums (the data-parallel gradient all-reduce adds the shards)
-    return bn_param_grads(b.bsums[l], H, t->grad_params + lay.p_off[lay.t_gamma(l)],
-                          t->grad_params + lay.p_off[lay.t_beta(l)], st);
+    // local sums (what a data-parallel run all-reduces), dgamma/dbeta from them; fused: also the pass-2 coefficients
+    const BnBwdFinalize f = bwd_finalize_args(cfg, t, lay, w, b, l);
+    return bn_bwd_reduce(b.pA, b.pB, ew_partial_rows(t->batch, H), f, b.bsums[l],
+                         t->grad_params + lay.p_off[lay.t_gamma(l)], t->grad_params + lay.p_off[lay.t_beta(l)], fused, st);
 }
 
 static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
@@ -360,10 +370,7 @@ static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     const int B = static_cast<int>(t->batch), H = lay.H;
     const uint16_t* ops = static_cast<const uint16_t*>(t->operands);
 
-    BnBwdFinalize f;
-    f.sums = b.bsums[l]; f.count = static_cast<double>(t->global_batch);
-    f.gamma = t->params + lay.p_off[lay.t_gamma(l)]; f.rstd = w.rstd[l];
-    f.H = H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode; f.coef = b.coef;
+    const BnBwdFinalize f = bwd_finalize_args(cfg, t, lay, w, b, l);
     if (!(fused && cfg->use_bn)) LIFTER_PROPAGATE(bn_finalize_bwd(f, st));   // fused: done by bwd_layer_stats
     if (!cfg->use_bn) {                                            // the BN affine exists but is unused: zero gradient
         LIFTER_CHECK_CUDA(cudaMemsetAsync(t->grad_params + lay.p_off[lay.t_gamma(l)], 0, H * 4, st));
@@ -371,12 +378,12 @@ static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     }
 
     BwdCommon c;
-    c.g = g_in(lay, b, l); c.z = w.z[l]; c.bits = w.bits[l]; c.mean_z = w.mean_z[l]; c.rstd = w.rstd[l];
+    c.g = g_in(lay, b, l); c.z = w.z[l]; c.bits = w.bits[l];
     c.rows = t->batch; c.H = H; c.fmt = t->fmt;
-    const bool drop = t->apply_dropout && cfg->p_dropout > 0.0f;
-    c.inv_keep = drop ? (cfg->p_dropout < 1.0f ? 1.0f / (1.0f - cfg->p_dropout) : 0.0f) : 1.0f;
-    LIFTER_PROPAGATE(bwd_dz(c, b.coef, b.dz, b.pA, st));
-    LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(t->batch, H), H, H, t->grad_params + lay.p_off[lay.t_bias(l)], st));
+    const bool need_bias = f.dbias == nullptr;                     // no BN, or BN on running statistics
+    LIFTER_PROPAGATE(bwd_dz(c, b.coef, b.dz, need_bias ? b.pA : nullptr, st));
+    if (need_bias)
+        LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(t->batch, H), H, H, t->grad_params + lay.p_off[lay.t_bias(l)], st));
 
     // dW_l = dz^T a_{l-1}
     const uint16_t* a_in = l == 0 ? w.a0 : w.a[l - 1];
@@ -387,7 +394,7 @@ static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
         if (t->grad_x == nullptr) return LIFTER_OK;
         GemmArgs g;                                                // dx = dz_0 W1   (input gradient, phase-5 call site)
         g.A = b.dz; g.lda = H; g.B = ops + lay.w_off[0]; g.ldb = lay.Ip; g.b_mn_major = 1;
-        g.M = B; g.N = lay.Ip; g.K = H; g.fmt = t->fmt;
+        g.M = B; g.N = lay.Ip; g.K = H; g.fmt = t->fmt; g.tag = "gemm_dx";
         if (lay.Ip <= 64) {
             g.out_mode = OUT_32_DIRECT; g.D = t->grad_x; g.n_valid = lay.I;
         } else {
@@ -398,7 +405,7 @@ static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     }
     GemmArgs g;                                                    // g_{l-1} = dz_l W_l (+ stream gradient)
     g.A = b.dz; g.lda = H; g.B = ops + lay.w_off[l]; g.ldb = H; g.b_mn_major = 1;
-    g.M = B; g.N = H; g.K = H; g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.ldd = H;
+    g.M = B; g.N = H; g.K = H; g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.ldd = H; g.tag = "gemm_dgrad";
     if (l % 2 == 0) {
         g.D = b.Gh;                                                // second layer of a block -> dh
     } else {
@@ -450,6 +457,37 @@ int lifter_l1_grad(const float* a, const float* b, int64_t n, int row_len, int c
                    float scale, float* da, float* db, void* stream) {
     LIFTER_REQUIRE(a && b && da, "l1_grad: null pointer");
     return l1_grad(a, b, n, row_len, centre, gscale, scale, da, db, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_step_advance(lifter_step_state_t* state, float beta1, float beta2, float weight_decay, void* stream) {
+    return step_advance(state, beta1, beta2, weight_decay, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_adam_step_packed(const lifter_config_t* cfg, float* p, const float* g, float* m, float* v, float lr, float beta1,
+                            float beta2, float eps, float weight_decay, int decoupled, int step, float grad_scale,
+                            const lifter_step_state_t* state, void* operands, int fmt, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(make_layout(cfg, &lay));
+    LIFTER_REQUIRE(p && g && m && v, "adam: null pointer");
+    LIFTER_REQUIRE(fmt == FMT_F16 || fmt == FMT_BF16, "adam: unknown operand format %d", fmt);
+    AdamArgs a;
+    a.p = p; a.g = g; a.m = m; a.v = v; a.n = lay.p_total; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
+    a.weight_decay = weight_decay; a.decoupled = decoupled; a.step = step; a.grad_scale = grad_scale;
+    a.dyn = reinterpret_cast<const float*>(state);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (operands != nullptr && lay.L + 1 <= ADAM_MAX_WEIGHTS) {
+        a.operands = operands; a.op_fmt = fmt; a.nw = lay.L + 1;
+        for (int l = 0; l <= lay.L; ++l) {
+            const int t = l < lay.L ? lay.t_weight(l) : lay.t_w2();
+            a.w_p_off[l] = lay.p_off[t]; a.w_numel[l] = lay.p_numel[t]; a.w_off[l] = lay.w_off[l];
+            a.w_in[l] = l < lay.L ? lay.in_dim(l) : lay.H;
+            a.w_pad[l] = l < lay.L ? lay.in_pad(l) : lay.H;
+        }
+        return adam_step(a, st);
+    }
+    LIFTER_PROPAGATE(adam_step(a, st));
+    if (operands != nullptr) return lifter_pack_weights(cfg, p, operands, fmt, stream);   // very deep models
+    return LIFTER_OK;
 }
 
 int lifter_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,

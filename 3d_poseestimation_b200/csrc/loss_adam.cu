@@ -166,8 +166,10 @@ __global__ void l1_grad_kernel(const float* __restrict__ a, const float* __restr
 __global__ void __launch_bounds__(256) adam_kernel(AdamArgs a, float step_size, float inv_sqrt_bc2, float decay) {
     griddep_launch();
     griddep_wait();
+    if (a.dyn != nullptr) { step_size = a.dyn[3]; inv_sqrt_bc2 = a.dyn[4]; decay = a.dyn[5]; }
     const long n4 = a.n >> 2;
     const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+    uint16_t* ops = static_cast<uint16_t*>(a.operands);
     for (long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
         float4 p = reinterpret_cast<float4*>(a.p)[i];
         const float4 g4 = reinterpret_cast<const float4*>(a.g)[i];
@@ -187,7 +189,43 @@ __global__ void __launch_bounds__(256) adam_kernel(AdamArgs a, float step_size, 
         reinterpret_cast<float4*>(a.p)[i] = p;
         reinterpret_cast<float4*>(a.m)[i] = m;
         reinterpret_cast<float4*>(a.v)[i] = v;
+        if (ops != nullptr) {                                           // 16-bit operand copy of a Linear weight
+            const long idx = i * 4;
+            for (int t = 0; t < a.nw; ++t) {
+                const long e0 = idx - a.w_p_off[t];
+                if (e0 < 0 || e0 >= a.w_numel[t]) continue;
+                if (a.w_in[t] == a.w_pad[t]) {                          // dense rows: same linear offset
+                    *reinterpret_cast<uint2*>(ops + a.w_off[t] + e0) =
+                        make_uint2(pack16(p.x, p.y, a.op_fmt), pack16(p.z, p.w, a.op_fmt));
+                } else {                                                // padded rows (the i_dim-wide first layer)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const long el = e0 + e;
+                        const long r = el / a.w_in[t];
+                        const int c = static_cast<int>(el - r * a.w_in[t]);
+                        ops[a.w_off[t] + r * a.w_pad[t] + c] = cvt16(pp[e], a.op_fmt);
+                    }
+                }
+                break;
+            }
+        }
     }
+}
+
+// state: [0] u32 dropout_step, [1] i32 adam_step, [2] f32 lr, [3] step_size, [4] inv_sqrt_bc2, [5] decay
+__global__ void step_advance_kernel(unsigned int* state, float beta1, float beta2, float weight_decay) {
+    griddep_launch();
+    griddep_wait();
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const int t = static_cast<int>(state[1]) + 1;
+    state[0] = static_cast<unsigned int>(t - 1);                       // dropout stream of this step
+    state[1] = static_cast<unsigned int>(t);
+    const float lr = __uint_as_float(state[2]);
+    const double bc1 = 1.0 - pow(static_cast<double>(beta1), static_cast<double>(t));
+    const double bc2 = 1.0 - pow(static_cast<double>(beta2), static_cast<double>(t));
+    state[3] = __float_as_uint(static_cast<float>(static_cast<double>(lr) / bc1));
+    state[4] = __float_as_uint(static_cast<float>(1.0 / sqrt(bc2)));
+    state[5] = __float_as_uint(1.0f - lr * weight_decay);
 }
 
 }  // namespace
@@ -201,9 +239,9 @@ int fused_loss(const float* pred, const float* target, int64_t rows, int J, int 
     LIFTER_REQUIRE(rows >= 1 && count >= 1.0, "fused_loss: empty batch");
     const int nblk = loss_partial_rows(rows);
     const float inv_count = static_cast<float>(1.0 / count);
-    LIFTER_CHECK_CUDA(launch_pdl(fused_loss_kernel, dim3(nblk), dim3(LOSS_THREADS), 0, st, pred, target, rows, J, kind, inv_count, stdv, dpred, partials));
+    LIFTER_CHECK_CUDA(launch_pdl("fused_loss_kernel", fused_loss_kernel, dim3(nblk), dim3(LOSS_THREADS), 0, st, pred, target, rows, J, kind, inv_count, stdv, dpred, partials));
     const double denom = kind == LOSS_MPJPE ? count * J : count * 3.0 * J;
-    LIFTER_CHECK_CUDA(launch_pdl(loss_finalize_kernel, dim3(1), dim3(1024), 0, st, partials, nblk, J, static_cast<float>(1.0 / denom), out, accumulate_metric));
+    LIFTER_CHECK_CUDA(launch_pdl("loss_finalize_kernel", loss_finalize_kernel, dim3(1), dim3(1024), 0, st, partials, nblk, J, static_cast<float>(1.0 / denom), out, accumulate_metric));
     return LIFTER_OK;
 }
 
@@ -211,23 +249,25 @@ int l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, f
            cudaStream_t st) {
     LIFTER_REQUIRE(n >= 1 && row_len >= 1 && n % row_len == 0, "l1_sum: bad shape");
     const int nblk = static_cast<int>((n + L1_THREADS * L1_PER_THREAD - 1) / (L1_THREADS * L1_PER_THREAD));
-    LIFTER_CHECK_CUDA(launch_pdl(l1_sum_kernel, dim3(nblk), dim3(L1_THREADS), 0, st, a, b, n, row_len, centre, partials));
-    LIFTER_CHECK_CUDA(launch_pdl(l1_finalize_kernel, dim3(1), dim3(256), 0, st, partials, nblk, scale, out));
+    LIFTER_CHECK_CUDA(launch_pdl("l1_sum_kernel", l1_sum_kernel, dim3(nblk), dim3(L1_THREADS), 0, st, a, b, n, row_len, centre, partials));
+    LIFTER_CHECK_CUDA(launch_pdl("l1_finalize_kernel", l1_finalize_kernel, dim3(1), dim3(256), 0, st, partials, nblk, scale, out));
     return LIFTER_OK;
 }
 
 int l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, const float* gscale, float scale,
             float* da, float* db, cudaStream_t st) {
     LIFTER_REQUIRE(n >= 1 && row_len >= 1 && n % row_len == 0, "l1_grad: bad shape");
-    LIFTER_CHECK_CUDA(launch_pdl(l1_grad_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, a, b, n, row_len, centre, gscale, scale, da, db));
+    LIFTER_CHECK_CUDA(launch_pdl("l1_grad_kernel", l1_grad_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, a, b, n, row_len, centre, gscale, scale, da, db));
     return LIFTER_OK;
 }
 
 int adam_step(const AdamArgs& a, cudaStream_t st) {
     LIFTER_REQUIRE(a.n % 4 == 0, "adam: flat buffer length must be a multiple of 4");
-    LIFTER_REQUIRE(a.step >= 1, "adam: step is 1-based");
-    const double bc1 = 1.0 - pow(static_cast<double>(a.beta1), a.step);
-    const double bc2 = 1.0 - pow(static_cast<double>(a.beta2), a.step);
+    LIFTER_REQUIRE(a.step >= 1 || a.dyn != nullptr, "adam: step is 1-based");
+    LIFTER_REQUIRE(a.operands == nullptr || (a.nw >= 1 && a.nw <= ADAM_MAX_WEIGHTS), "adam: bad operand table");
+    const int t = a.step >= 1 ? a.step : 1;
+    const double bc1 = 1.0 - pow(static_cast<double>(a.beta1), t);
+    const double bc2 = 1.0 - pow(static_cast<double>(a.beta2), t);
     const float step_size = static_cast<float>(a.lr / bc1);
     const float inv_sqrt_bc2 = static_cast<float>(1.0 / sqrt(bc2));
     const float decay = 1.0f - a.lr * a.weight_decay;
@@ -235,7 +275,14 @@ int adam_step(const AdamArgs& a, cudaStream_t st) {
     long blocks = (n4 + 255) / 256;
     const long cap = static_cast<long>(num_sms()) * 8;             // grid = multiple of the SM count, grid-stride
     if (blocks > cap) blocks = cap;
-    LIFTER_CHECK_CUDA(launch_pdl(adam_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st, a, step_size, inv_sqrt_bc2, decay));
+    LIFTER_CHECK_CUDA(launch_pdl("adam_kernel", adam_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st, a, step_size, inv_sqrt_bc2, decay));
+    return LIFTER_OK;
+}
+
+int step_advance(void* state, float beta1, float beta2, float weight_decay, cudaStream_t st) {
+    LIFTER_REQUIRE(state != nullptr, "step_advance: null state");
+    LIFTER_CHECK_CUDA(launch_pdl("step_advance_kernel", step_advance_kernel, dim3(1), dim3(32), 0, st,
+                                 static_cast<unsigned int*>(state), beta1, beta2, weight_decay));
     return LIFTER_OK;
 }
 

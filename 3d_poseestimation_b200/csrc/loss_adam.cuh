@@ -25,12 +25,21 @@ int l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, f
 int l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, const float* gscale, float scale,
             float* da, float* db, cudaStream_t st);
 
+constexpr int ADAM_MAX_WEIGHTS = 16;
 struct AdamArgs {
     float* p; const float* g; float* m; float* v; int64_t n;
     float lr, beta1, beta2, eps, weight_decay; int decoupled;     // AdamW: decoupled = 1
     int step;                                                     // 1-based
     float grad_scale;                                             // multiplies g first (1/world for DP means)
+    const float* dyn = nullptr;     // device lifter_step_state_t (nullable): step_size / inv_sqrt_bc2 / decay read from it
+    // optional: refresh the 16-bit zero-padded GEMM operand copies of the Linear weights in the same pass
+    void* operands = nullptr; int op_fmt = FMT_BF16; int nw = 0;
+    long long w_p_off[ADAM_MAX_WEIGHTS]; long long w_numel[ADAM_MAX_WEIGHTS]; long long w_off[ADAM_MAX_WEIGHTS];
+    int w_in[ADAM_MAX_WEIGHTS]; int w_pad[ADAM_MAX_WEIGHTS];
 };
 int adam_step(const AdamArgs& a, cudaStream_t st);
+// device step state (include/lifter_b200.h: lifter_step_state_t): dropout_step = adam_step; adam_step += 1; the Adam
+// bias corrections of the new step from the lr stored in the state
+int step_advance(void* state, float beta1, float beta2, float weight_decay, cudaStream_t st);
 
 }  // namespace lifter

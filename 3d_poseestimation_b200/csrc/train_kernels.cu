@@ -23,34 +23,63 @@ __device__ __forceinline__ void load8f(const float* p, float (&v)[8]) {
     const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 }
+// streaming 16-byte accesses: these tensors are touched once per kernel, keep them out of L1
+__device__ __forceinline__ uint4 ldg_stream(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
 
-// ---------------------------------------------------------------------------------- row reductions
-// block = 32 columns x 32 row-lanes; every thread sums its rows in order, then a fixed-order tree over lanes
-template <typename OutT>
-__global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int P, int n, int ld,
-                                   OutT* __restrict__ out_a, OutT* __restrict__ out_b) {
-    griddep_launch();
-    griddep_wait();
-    __shared__ double sh[2][32][33];
-    const int col = blockIdx.x * 32 + threadIdx.x;
+__device__ __forceinline__ float ldg_f32(const float* p) {
+    float r;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p));
+    return r;
+}
+
+// ---------------------------------------------------------------------------------- column reductions
+// Second stage of every column reduction: P partial rows -> one value per column, fixed order (deterministic),
+// fp64 accumulation.  Block = 8 columns x 128 row-lanes (a warp reads 4 rows x 32 B: whole sectors), one block per
+// 8 columns, so every thread issues only P/128 loads per array and the chain of dependent L2 round trips that made
+// the first version take ~10 us is gone; the row-lanes are combined by a fixed-pairing tree in shared memory.
+constexpr int RED_COLS = 8, RED_LANES = 128;
+
+__device__ __forceinline__ void reduce_partials_2(const float* __restrict__ a, const float* __restrict__ b, int P, int n,
+                                                  int ld, double (&sh)[2][RED_LANES][RED_COLS], double& ta, double& tb) {
+    const int col = blockIdx.x * RED_COLS + threadIdx.x;
     const int lane_r = threadIdx.y;
     double sa = 0.0, sb = 0.0;
     if (col < n) {
-        for (int p = lane_r; p < P; p += 32) {
-            sa += static_cast<double>(a[static_cast<long>(p) * ld + col]);
-            if (b != nullptr) sb += static_cast<double>(b[static_cast<long>(p) * ld + col]);
+        for (int p = lane_r; p < P; p += RED_LANES) {
+            sa += static_cast<double>(ldg_f32(a + static_cast<long>(p) * ld + col));
+            if (b != nullptr) sb += static_cast<double>(ldg_f32(b + static_cast<long>(p) * ld + col));
         }
     }
     sh[0][lane_r][threadIdx.x] = sa;
     sh[1][lane_r][threadIdx.x] = sb;
     __syncthreads();
-    if (lane_r == 0 && col < n) {
-        double ta = 0.0, tb = 0.0;
-#pragma unroll 8
-        for (int r = 0; r < 32; ++r) {
-            ta += sh[0][r][threadIdx.x];
-            tb += sh[1][r][threadIdx.x];
+#pragma unroll
+    for (int s = RED_LANES / 2; s >= 1; s >>= 1) {
+        if (lane_r < s) {
+            sh[0][lane_r][threadIdx.x] += sh[0][lane_r + s][threadIdx.x];
+            sh[1][lane_r][threadIdx.x] += sh[1][lane_r + s][threadIdx.x];
         }
+        __syncthreads();
+    }
+    ta = sh[0][0][threadIdx.x];
+    tb = sh[1][0][threadIdx.x];
+}
+
+template <typename OutT>
+__global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int P, int n, int ld,
+                                   OutT* __restrict__ out_a, OutT* __restrict__ out_b) {
+    griddep_launch();
+    griddep_wait();
+    __shared__ double sh[2][RED_LANES][RED_COLS];
+    double ta, tb;
+    reduce_partials_2(a, b, P, n, ld, sh, ta, tb);
+    const int col = blockIdx.x * RED_COLS + threadIdx.x;
+    if (threadIdx.y == 0 && col < n) {
         out_a[col] = static_cast<OutT>(ta);
         if (b != nullptr) out_b[col] = static_cast<OutT>(tb);
     }
@@ -97,31 +126,15 @@ __global__ void bn_finalize_fwd_kernel(BnFwdFinalize a) {
 }
 
 // single-GPU path: second stage of the column reduction and the finalize in one launch
-// (block = 32 columns x 32 row lanes, like reduce_rows_kernel)
 __global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, const float* __restrict__ psq, int P,
                                               BnFwdFinalize a, double* __restrict__ sums_out) {
     griddep_launch();
     griddep_wait();
-    __shared__ double sh[2][32][33];
-    const int col = blockIdx.x * 32 + threadIdx.x;
-    const int lane_r = threadIdx.y;
-    double sa = 0.0, sb = 0.0;
-    if (col < a.H) {
-        for (int p = lane_r; p < P; p += 32) {
-            sa += static_cast<double>(psum[static_cast<long>(p) * a.H + col]);
-            sb += static_cast<double>(psq[static_cast<long>(p) * a.H + col]);
-        }
-    }
-    sh[0][lane_r][threadIdx.x] = sa;
-    sh[1][lane_r][threadIdx.x] = sb;
-    __syncthreads();
-    if (lane_r == 0 && col < a.H) {
-        double ta = 0.0, tb = 0.0;
-#pragma unroll 8
-        for (int r = 0; r < 32; ++r) {
-            ta += sh[0][r][threadIdx.x];
-            tb += sh[1][r][threadIdx.x];
-        }
+    __shared__ double sh[2][RED_LANES][RED_COLS];
+    double ta, tb;
+    reduce_partials_2(psum, psq, P, a.H, a.H, sh, ta, tb);
+    const int col = blockIdx.x * RED_COLS + threadIdx.x;
+    if (threadIdx.y == 0 && col < a.H) {
         sums_out[col] = ta;
         sums_out[a.H + col] = tb;
         if (col == 0 && a.num_batches_tracked != nullptr) *a.num_batches_tracked += 1;
@@ -129,41 +142,59 @@ __global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, co
     }
 }
 
-// ---------------------------------------------------------------------------------- BN apply + ReLU + dropout (+ residual)
-__global__ void __launch_bounds__(256) bn_apply_fwd_kernel(BnApplyFwd a, uint32_t threshold, float inv_keep) {
+// ---------------------------------------------------------------------------------- streaming tiling
+// Shared by the three big elementwise kernels: TPR = H/8 threads cover a row (16-byte vectors), RPB = 256/TPR rows
+// per iteration; a block owns `rows_per_block` consecutive rows and walks them EW_UNROLL iterations at a time with
+// all loads of a group issued before any arithmetic.  A thread keeps the same 8 columns for its whole life, so
+// every per-column coefficient is loaded once into registers.
+
+// BN affine + ReLU + Philox dropout (+ block residual): a = drop(relu(z * scale + shift)) [+ resid], and one bit per
+// element "ReLU-active AND kept" for the backward pass.  1/(1-p) is folded into scale/shift (it is positive, so the
+// ReLU decision is unchanged).
+template <int FMT>
+__global__ void __launch_bounds__(EW_THREADS, 2) bn_apply_fwd_kernel(BnApplyFwd a, int rows_per_block, uint32_t threshold,
+                                                                  float inv_keep) {
     griddep_launch();
     griddep_wait();
-    const int groups = a.H >> 3;
-    const long total = a.rows * groups;
-    const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+    const int tpr = a.H >> 3;
+    const int rpb = EW_THREADS / tpr;
+    const int cg = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long end = min(base + rows_per_block, static_cast<long>(a.rows));
+    float sc[8], sh[8];
+    load8f(a.scale + cg * 8, sc);
+    load8f(a.shift + cg * 8, sh);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { sc[e] *= inv_keep; sh[e] *= inv_keep; }
+    const uint32_t dstep = a.step_dev != nullptr ? *a.step_dev : a.step;
     const uint16_t* zp = static_cast<const uint16_t*>(a.z);
     const uint16_t* rp = static_cast<const uint16_t*>(a.resid);
-    for (long i0 = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total; i0 += stride * EW_UNROLL) {
-        uint4 zq[EW_UNROLL], rq[EW_UNROLL];
-#pragma unroll
-        for (int u = 0; u < EW_UNROLL; ++u) {                       // all loads of the group first
-            const long idx = i0 + u * stride;
-            zq[u] = make_uint4(0, 0, 0, 0);
-            rq[u] = make_uint4(0, 0, 0, 0);
-            if (idx < total) {
-                zq[u] = *reinterpret_cast<const uint4*>(zp + idx * 8);
-                if (rp != nullptr) rq[u] = *reinterpret_cast<const uint4*>(rp + idx * 8);
-            }
-        }
+    uint16_t* ap = static_cast<uint16_t*>(a.a);
+    const long step = static_cast<long>(rpb) * EW_UNROLL;
+    auto load = [&](long r0, uint4 (&zq)[EW_UNROLL], uint4 (&rq)[EW_UNROLL]) {
 #pragma unroll
         for (int u = 0; u < EW_UNROLL; ++u) {
-            const long idx = i0 + u * stride;
-            if (idx >= total) break;
-            const long row = idx / groups;
-            const int cg = static_cast<int>(idx - row * groups);
-            float z[8], sc[8], sh[8];
-            unpack8(zq[u], a.fmt, z);
-            load8f(a.scale + cg * 8, sc);
-            load8f(a.shift + cg * 8, sh);
+            const long row = r0 + static_cast<long>(u) * rpb;
+            zq[u] = make_uint4(0, 0, 0, 0);
+            rq[u] = make_uint4(0, 0, 0, 0);
+            if (row < end) {
+                const long off = row * a.H + cg * 8;
+                zq[u] = ldg_stream(zp + off);
+                if (rp != nullptr) rq[u] = ldg_stream(rp + off);
+            }
+        }
+    };
+    auto compute = [&](long r0, const uint4 (&zq)[EW_UNROLL], const uint4 (&rq)[EW_UNROLL]) {
+#pragma unroll
+        for (int u = 0; u < EW_UNROLL; ++u) {
+            const long row = r0 + static_cast<long>(u) * rpb;
+            if (row >= end) break;
+            float z[8];
+            unpack8(zq[u], FMT, z);
             uint32_t keep = 0xFFu;
             if (a.apply_dropout)
                 keep = dropout_keep_bits8(static_cast<uint32_t>(row + a.row_offset), static_cast<uint32_t>(cg), a.site,
-                                          a.step, a.seed, threshold);
+                                          dstep, a.seed, threshold);
             float out[8];
             uint32_t active = 0;
 #pragma unroll
@@ -171,97 +202,110 @@ __global__ void __launch_bounds__(256) bn_apply_fwd_kernel(BnApplyFwd a, uint32_
                 const float y = fmaf(z[e], sc[e], sh[e]);
                 const bool on = (y > 0.0f) && ((keep >> e) & 1u);
                 active |= (on ? 1u : 0u) << e;
-                out[e] = on ? y * inv_keep : 0.0f;
+                out[e] = on ? y : 0.0f;
             }
             if (rp != nullptr) {
                 float r[8];
-                unpack8(rq[u], a.fmt, r);
+                unpack8(rq[u], FMT, r);
 #pragma unroll
                 for (int e = 0; e < 8; ++e) out[e] += r[e];
             }
-            *reinterpret_cast<uint4*>(static_cast<uint16_t*>(a.a) + idx * 8) = pack8(out, a.fmt);
-            a.bits[idx] = static_cast<uint8_t>(active);
+            *reinterpret_cast<uint4*>(ap + row * a.H + cg * 8) = pack8(out, FMT);
+            a.bits[row * tpr + cg] = static_cast<uint8_t>(active);
         }
+    };
+    // two register buffers: the loads of the next group are in flight while this one is computed
+    uint4 z0[EW_UNROLL], q0[EW_UNROLL], z1[EW_UNROLL], q1[EW_UNROLL];
+    long r = base + rl;
+    if (r < end) load(r, z0, q0);
+    while (r < end) {
+        if (r + step < end) load(r + step, z1, q1);
+        compute(r, z0, q0);
+        r += step;
+        if (r >= end) break;
+        if (r + step < end) load(r + step, z0, q0);
+        compute(r, z1, q1);
+        r += step;
     }
 }
 
 // ---------------------------------------------------------------------------------- backward passes
-// Shared tiling: TPR = H/8 threads cover a row (16-byte vectors), RPB = 256/TPR rows per iteration.  A block owns
-// `rows_per_block` consecutive rows and walks them EW_UNROLL iterations at a time: all loads of a group are issued
-// before any arithmetic (2 x EW_UNROLL 16-byte loads in flight per thread), sums stay in registers, and one
-// partial row per block leaves through a fixed-order shared-memory reduction (deterministic).
-template <bool WRITE_DZ>
-__global__ void __launch_bounds__(EW_THREADS) bwd_pass_kernel(BwdCommon c, int rows_per_block,
-                                                              const float* __restrict__ coef,
-                                                              uint16_t* __restrict__ dz, float* __restrict__ psum0,
-                                                              float* __restrict__ psum1) {
+// The saved bit per element selects dy = g * inv_keep or 0.  A 256-entry table in shared memory expands a byte of
+// eight bits into four 32-bit AND-masks for the four packed 16-bit pairs, so masking costs one LDS + four LOPs
+// per eight elements.
+__device__ __forceinline__ void fill_mask_lut(uint4* lut) {
+    for (int b = threadIdx.x; b < 256; b += blockDim.x) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            w[i] = (((b >> (2 * i)) & 1) ? 0x0000FFFFu : 0u) | (((b >> (2 * i + 1)) & 1) ? 0xFFFF0000u : 0u);
+        lut[b] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+__device__ __forceinline__ uint4 and4(const uint4& a, const uint4& m) {
+    return make_uint4(a.x & m.x, a.y & m.y, a.z & m.z, a.w & m.w);
+}
+
+// pass 1: partial column sums of gm = (g masked by the active bit) and of gm * z (raw z).  The finalize turns them
+// into sum dy = ik * S1 and sum dy * zhat = ik * rstd * (S2 - mean * S1) in fp64.
+template <int FMT>
+__global__ void __launch_bounds__(EW_THREADS, 2) bwd_stats_kernel(BwdCommon c, int rows_per_block,
+                                                               float* __restrict__ psum0, float* __restrict__ psum1) {
     griddep_launch();
-    griddep_wait();
+    __shared__ uint4 lut[256];
     __shared__ float sh[2][EW_THREADS][8];
+    fill_mask_lut(lut);
+    __syncthreads();
+    griddep_wait();
     const int tpr = c.H >> 3;
     const int rpb = EW_THREADS / tpr;
     const int cg = threadIdx.x % tpr, rl = threadIdx.x / tpr;
     const long base = static_cast<long>(blockIdx.x) * rows_per_block;
     const long end = min(base + rows_per_block, static_cast<long>(c.rows));
-    float mean[8], rstd[8], k[8], c1[8], c2[8];
-    load8f(c.mean_z + cg * 8, mean);
-    load8f(c.rstd + cg * 8, rstd);
-    if (WRITE_DZ) {
-        load8f(coef + cg * 8, k);
-        load8f(coef + c.H + cg * 8, c1);
-        load8f(coef + 2 * c.H + cg * 8, c2);
-    }
     const uint16_t* gp = static_cast<const uint16_t*>(c.g);
     const uint16_t* zp = static_cast<const uint16_t*>(c.z);
     float acc0[8] = {0, 0, 0, 0, 0, 0, 0, 0}, acc1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (long r0 = base + rl; r0 < end; r0 += static_cast<long>(rpb) * EW_UNROLL) {
-        uint4 gq[EW_UNROLL], zq[EW_UNROLL];
-        uint32_t act[EW_UNROLL];
+    const long step = static_cast<long>(rpb) * EW_UNROLL;
+    auto load = [&](long r0, uint4 (&gq)[EW_UNROLL], uint4 (&zq)[EW_UNROLL], uint32_t (&act)[EW_UNROLL]) {
 #pragma unroll
         for (int u = 0; u < EW_UNROLL; ++u) {
             const long row = r0 + static_cast<long>(u) * rpb;
+            gq[u] = make_uint4(0, 0, 0, 0);
+            zq[u] = make_uint4(0, 0, 0, 0);
+            act[u] = 0;
             if (row < end) {
                 const long off = row * c.H + cg * 8;
-                gq[u] = *reinterpret_cast<const uint4*>(gp + off);
-                zq[u] = *reinterpret_cast<const uint4*>(zp + off);
+                gq[u] = ldg_stream(gp + off);
+                zq[u] = ldg_stream(zp + off);
                 act[u] = c.bits[row * tpr + cg];
-            } else {
-                gq[u] = make_uint4(0, 0, 0, 0);
-                zq[u] = make_uint4(0, 0, 0, 0);
-                act[u] = 0;
             }
         }
+    };
+    auto compute = [&](const uint4 (&gq)[EW_UNROLL], const uint4 (&zq)[EW_UNROLL], const uint32_t (&act)[EW_UNROLL]) {
 #pragma unroll
-        for (int u = 0; u < EW_UNROLL; ++u) {
-            const long row = r0 + static_cast<long>(u) * rpb;
+        for (int u = 0; u < EW_UNROLL; ++u) {                       // rows past `end` carry act == 0: they add nothing
             float g[8], z[8];
-            unpack8(gq[u], c.fmt, g);
-            unpack8(zq[u], c.fmt, z);
-            if (WRITE_DZ) {
-                if (row < end) {
-                    float o[8];
+            unpack8(and4(gq[u], lut[act[u]]), FMT, g);
+            unpack8(zq[u], FMT, z);
 #pragma unroll
-                    for (int e = 0; e < 8; ++e) {
-                        const float dy = ((act[u] >> e) & 1u) ? g[e] * c.inv_keep : 0.0f;
-                        const float zh = (z[e] - mean[e]) * rstd[e];
-                        o[e] = k[e] * (dy - c1[e] - zh * c2[e]);
-                    }
-                    const uint4 q = pack8(o, c.fmt);
-                    *reinterpret_cast<uint4*>(dz + row * c.H + cg * 8) = q;
-                    float r[8];
-                    unpack8(q, c.fmt, r);                          // bias gradient of the values the GEMMs consume
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) acc0[e] += r[e];
-                }
-            } else {
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {                      // rows past `end` carry act == 0: they add nothing
-                    const float dy = ((act[u] >> e) & 1u) ? g[e] * c.inv_keep : 0.0f;
-                    acc0[e] += dy;
-                    acc1[e] += dy * (z[e] - mean[e]) * rstd[e];
-                }
+            for (int e = 0; e < 8; ++e) {
+                acc0[e] += g[e];
+                acc1[e] = fmaf(g[e], z[e], acc1[e]);
             }
         }
+    };
+    uint4 g0[EW_UNROLL], z0[EW_UNROLL], g1[EW_UNROLL], z1[EW_UNROLL];
+    uint32_t a0[EW_UNROLL], a1[EW_UNROLL];
+    long r = base + rl;
+    if (r < end) load(r, g0, z0, a0);
+    while (r < end) {
+        if (r + step < end) load(r + step, g1, z1, a1);
+        compute(g0, z0, a0);
+        r += step;
+        if (r >= end) break;
+        if (r + step < end) load(r + step, g0, z0, a0);
+        compute(g1, z1, a1);
+        r += step;
     }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
@@ -279,14 +323,123 @@ __global__ void __launch_bounds__(EW_THREADS) bwd_pass_kernel(BwdCommon c, int r
             }
         }
         float* o0 = psum0 + static_cast<long>(blockIdx.x) * c.H + cg * 8;
+        float* o1 = psum1 + static_cast<long>(blockIdx.x) * c.H + cg * 8;
         *reinterpret_cast<float4*>(o0) = make_float4(t0[0], t0[1], t0[2], t0[3]);
         *reinterpret_cast<float4*>(o0 + 4) = make_float4(t0[4], t0[5], t0[6], t0[7]);
-        if (!WRITE_DZ) {
-            float* o1 = psum1 + static_cast<long>(blockIdx.x) * c.H + cg * 8;
-            *reinterpret_cast<float4*>(o1) = make_float4(t1[0], t1[1], t1[2], t1[3]);
-            *reinterpret_cast<float4*>(o1 + 4) = make_float4(t1[4], t1[5], t1[6], t1[7]);
+        *reinterpret_cast<float4*>(o1) = make_float4(t1[0], t1[1], t1[2], t1[3]);
+        *reinterpret_cast<float4*>(o1 + 4) = make_float4(t1[4], t1[5], t1[6], t1[7]);
+    }
+}
+
+// pass 2: dz = A * gm + Bz * z + Cc per column (coef = [3][H], see bn_bwd_coefficients), 16-bit output.
+// WITH_BIAS also leaves partial column sums of the stored dz (bias gradient when BatchNorm does not cancel it).
+template <bool WITH_BIAS, int FMT>
+__global__ void __launch_bounds__(EW_THREADS, 2) bwd_dz_kernel(BwdCommon c, int rows_per_block,
+                                                            const float* __restrict__ coef, uint16_t* __restrict__ dz,
+                                                            float* __restrict__ psum) {
+    griddep_launch();
+    __shared__ uint4 lut[256];
+    __shared__ float sh[WITH_BIAS ? EW_THREADS : 1][8];
+    fill_mask_lut(lut);
+    __syncthreads();
+    griddep_wait();
+    const int tpr = c.H >> 3;
+    const int rpb = EW_THREADS / tpr;
+    const int cg = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long end = min(base + rows_per_block, static_cast<long>(c.rows));
+    float ka[8], kz[8], kc[8];
+    load8f(coef + cg * 8, ka);
+    load8f(coef + c.H + cg * 8, kz);
+    load8f(coef + 2 * c.H + cg * 8, kc);
+    const uint16_t* gp = static_cast<const uint16_t*>(c.g);
+    const uint16_t* zp = static_cast<const uint16_t*>(c.z);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long step = static_cast<long>(rpb) * EW_UNROLL;
+    auto load = [&](long r0, uint4 (&gq)[EW_UNROLL], uint4 (&zq)[EW_UNROLL], uint32_t (&act)[EW_UNROLL]) {
+#pragma unroll
+        for (int u = 0; u < EW_UNROLL; ++u) {
+            const long row = r0 + static_cast<long>(u) * rpb;
+            gq[u] = make_uint4(0, 0, 0, 0);
+            zq[u] = make_uint4(0, 0, 0, 0);
+            act[u] = 0;
+            if (row < end) {
+                const long off = row * c.H + cg * 8;
+                gq[u] = ldg_stream(gp + off);
+                zq[u] = ldg_stream(zp + off);
+                act[u] = c.bits[row * tpr + cg];
+            }
+        }
+    };
+    auto compute = [&](long r0, const uint4 (&gq)[EW_UNROLL], const uint4 (&zq)[EW_UNROLL],
+                       const uint32_t (&act)[EW_UNROLL]) {
+#pragma unroll
+        for (int u = 0; u < EW_UNROLL; ++u) {
+            const long row = r0 + static_cast<long>(u) * rpb;
+            if (row >= end) break;
+            float g[8], z[8], o[8];
+            unpack8(and4(gq[u], lut[act[u]]), FMT, g);
+            unpack8(zq[u], FMT, z);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] = fmaf(ka[e], g[e], fmaf(kz[e], z[e], kc[e]));
+            const uint4 q = pack8(o, FMT);
+            *reinterpret_cast<uint4*>(dz + row * c.H + cg * 8) = q;
+            if (WITH_BIAS) {
+                float rr[8];
+                unpack8(q, FMT, rr);                             // bias gradient of the values the GEMMs consume
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc[e] += rr[e];
+            }
+        }
+    };
+    uint4 g0[EW_UNROLL], z0[EW_UNROLL], g1[EW_UNROLL], z1[EW_UNROLL];
+    uint32_t a0[EW_UNROLL], a1[EW_UNROLL];
+    long r = base + rl;
+    if (r < end) load(r, g0, z0, a0);
+    while (r < end) {
+        if (r + step < end) load(r + step, g1, z1, a1);
+        compute(r, g0, z0, a0);
+        r += step;
+        if (r >= end) break;
+        if (r + step < end) load(r + step, g0, z0, a0);
+        compute(r, g1, z1, a1);
+        r += step;
+    }
+    if (WITH_BIAS) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) sh[threadIdx.x][e] = acc[e];
+        __syncthreads();
+        if (rl == 0) {
+            float t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int r = 0; r < rpb; ++r)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) t[e] += sh[r * tpr + cg][e];
+            float* o = psum + static_cast<long>(blockIdx.x) * c.H + cg * 8;
+            *reinterpret_cast<float4*>(o) = make_float4(t[0], t[1], t[2], t[3]);
+            *reinterpret_cast<float4*>(o + 4) = make_float4(t[4], t[5], t[6], t[7]);
         }
     }
+}
+
+// ---------------------------------------------------------------------------------- BN finalize (backward)
+// coefficients of pass 2 from the GLOBAL sums:  dz = k (dy - c1 - zhat c2),  dy = ik gm,  zhat = (z - mean) rstd
+//   =>  dz = A gm + Bz z + Cc   with  A = k ik,  Bz = -k c2 rstd,  Cc = -k c1 - Bz mean
+__device__ __forceinline__ void bn_bwd_coefficients(const BnBwdFinalize& a, int j, double sum_dy, double sum_dyz) {
+    float k = 1.0f, c1 = 0.0f, c2 = 0.0f, rstd = 1.0f, mean = 0.0f;
+    if (a.use_bn) {
+        rstd = a.rstd[j];
+        mean = a.mean_z[j];
+        k = a.gamma[j] * rstd;
+        if (a.bn_mode == 0) {
+            c1 = static_cast<float>(sum_dy / a.count);
+            c2 = static_cast<float>(sum_dyz / a.count);
+        }
+    }
+    const float bz = -k * c2 * rstd;
+    a.coef[j] = k * a.inv_keep;
+    a.coef[a.H + j] = bz;
+    a.coef[2 * a.H + j] = -k * c1 - bz * mean;
+    if (a.dbias != nullptr) a.dbias[j] = 0.0f;      // a bias in front of batch-statistics BN has zero gradient
 }
 
 __global__ void bn_finalize_bwd_kernel(BnBwdFinalize a) {
@@ -294,71 +447,55 @@ __global__ void bn_finalize_bwd_kernel(BnBwdFinalize a) {
     griddep_wait();
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= a.H) return;
-    float k = 1.0f, c1 = 0.0f, c2 = 0.0f;
-    if (a.use_bn) {
-        k = a.gamma[j] * a.rstd[j];
-        if (a.bn_mode == 0) {
-            c1 = static_cast<float>(a.sums[j] / a.count);
-            c2 = static_cast<float>(a.sums[a.H + j] / a.count);
-        }
-    }
-    a.coef[j] = k;
-    a.coef[a.H + j] = c1;
-    a.coef[2 * a.H + j] = c2;
+    const bool batch = a.use_bn && a.bn_mode == 0;
+    bn_bwd_coefficients(a, j, batch ? a.sums[j] : 0.0, batch ? a.sums[a.H + j] : 0.0);
 }
 
-// single-GPU path: reduce the pass-1 partials, write dgamma/dbeta and the pass-2 coefficients in one launch
-__global__ void bn_reduce_finalize_bwd_kernel(const float* __restrict__ pdy, const float* __restrict__ pdyz, int P,
-                                              BnBwdFinalize a, double* __restrict__ sums_out,
-                                              float* __restrict__ dgamma, float* __restrict__ dbeta) {
+// second stage of pass 1: LOCAL sums of dy and dy * zhat (fp64, what a data-parallel run all-reduces) and the
+// BatchNorm parameter gradients from them; FUSED also writes the pass-2 coefficients (single GPU: local == global)
+template <bool FUSED>
+__global__ void bn_bwd_reduce_kernel(const float* __restrict__ pg, const float* __restrict__ pgz, int P,
+                                     BnBwdFinalize a, double* __restrict__ sums_out, float* __restrict__ dgamma,
+                                     float* __restrict__ dbeta) {
     griddep_launch();
     griddep_wait();
-    __shared__ double sh[2][32][33];
-    const int col = blockIdx.x * 32 + threadIdx.x;
-    const int lane_r = threadIdx.y;
-    double sa = 0.0, sb = 0.0;
-    if (col < a.H) {
-        for (int p = lane_r; p < P; p += 32) {
-            sa += static_cast<double>(pdy[static_cast<long>(p) * a.H + col]);
-            sb += static_cast<double>(pdyz[static_cast<long>(p) * a.H + col]);
-        }
-    }
-    sh[0][lane_r][threadIdx.x] = sa;
-    sh[1][lane_r][threadIdx.x] = sb;
-    __syncthreads();
-    if (lane_r == 0 && col < a.H) {
-        double ta = 0.0, tb = 0.0;
-#pragma unroll 8
-        for (int r = 0; r < 32; ++r) {
-            ta += sh[0][r][threadIdx.x];
-            tb += sh[1][r][threadIdx.x];
-        }
-        sums_out[col] = ta;
-        sums_out[a.H + col] = tb;
-        dbeta[col] = static_cast<float>(ta);
-        dgamma[col] = static_cast<float>(tb);
-        const float k = a.gamma[col] * a.rstd[col];
-        a.coef[col] = k;
-        a.coef[a.H + col] = a.bn_mode == 0 ? static_cast<float>(ta / a.count) : 0.0f;
-        a.coef[2 * a.H + col] = a.bn_mode == 0 ? static_cast<float>(tb / a.count) : 0.0f;
+    __shared__ double sh[2][RED_LANES][RED_COLS];
+    double s1, s2;
+    reduce_partials_2(pg, pgz, P, a.H, a.H, sh, s1, s2);
+    const int col = blockIdx.x * RED_COLS + threadIdx.x;
+    if (threadIdx.y == 0 && col < a.H) {
+        const double ik = static_cast<double>(a.inv_keep);
+        const double sum_dy = ik * s1;
+        const double sum_dyz = ik * static_cast<double>(a.rstd[col]) * (s2 - static_cast<double>(a.mean_z[col]) * s1);
+        sums_out[col] = sum_dy;
+        sums_out[a.H + col] = sum_dyz;
+        dbeta[col] = static_cast<float>(sum_dy);
+        dgamma[col] = static_cast<float>(sum_dyz);
+        if (FUSED) bn_bwd_coefficients(a, col, sum_dy, sum_dyz);
     }
 }
 
-__global__ void bn_param_grads_kernel(const double* __restrict__ s, int H, float* __restrict__ dgamma,
-                                      float* __restrict__ dbeta) {
-    griddep_launch();
-    griddep_wait();
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= H) return;
-    dbeta[j] = static_cast<float>(s[j]);
-    dgamma[j] = static_cast<float>(s[H + j]);
-}
-
+// ---------------------------------------------------------------------------------- gradient packing
+// sum of the split-K slabs -> dense fp32 gradient [rows][cols]; fixed order, four columns per thread when the
+// shapes allow 16-byte accesses
 __global__ void wgrad_reduce_kernel(const float* __restrict__ slabs, int splits, long slab_elems, int ld, int rows,
                                     int cols, float* __restrict__ grad) {
     griddep_launch();
     griddep_wait();
     const long idx = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if ((cols & 3) == 0 && (ld & 3) == 0) {
+        const int c4 = cols >> 2;
+        if (idx >= static_cast<long>(rows) * c4) return;
+        const int r = static_cast<int>(idx / c4), c = static_cast<int>(idx - static_cast<long>(r) * c4) * 4;
+        const long src = static_cast<long>(r) * ld + c;
+        float4 s = *reinterpret_cast<const float4*>(slabs + src);
+        for (int k = 1; k < splits; ++k) {
+            const float4 v = *reinterpret_cast<const float4*>(slabs + k * slab_elems + src);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        *reinterpret_cast<float4*>(grad + static_cast<long>(r) * cols + c) = s;
+        return;
+    }
     if (idx >= static_cast<long>(rows) * cols) return;
     const int r = static_cast<int>(idx / cols), c = static_cast<int>(idx - static_cast<long>(r) * cols);
     const long src = static_cast<long>(r) * ld + c;
@@ -407,96 +544,116 @@ __global__ void __launch_bounds__(EW_THREADS) prep_grad_out_kernel(const float* 
 
 }  // namespace
 
-// rows owned by one block: a multiple of the rows one unrolled iteration covers, sized so that at most
-// 4 x SM-count blocks (= partial rows) exist
-int ew_rows_per_block(int64_t rows, int H) {
+// rows owned by one block of a column-reducing kernel: a multiple of the rows one unrolled iteration covers, sized
+// so that at most 2 x SM-count blocks (= partial rows) exist
+static int rows_per_block_for(int64_t rows, int H, int blocks_per_sm) {
     const int64_t step = static_cast<int64_t>(EW_THREADS / (H / 8)) * EW_UNROLL;
     const int64_t steps = (rows + step - 1) / step;
-    const int64_t max_blocks = static_cast<int64_t>(num_sms()) * 4;
+    const int64_t max_blocks = static_cast<int64_t>(num_sms()) * blocks_per_sm;
     const int64_t steps_per_block = (steps + max_blocks - 1) / max_blocks;
     return static_cast<int>(steps_per_block * step);
 }
+int ew_rows_per_block(int64_t rows, int H) { return rows_per_block_for(rows, H, 2); }
 int ew_partial_rows(int64_t rows, int H) {
     const int rpb = ew_rows_per_block(rows, H);
     return static_cast<int>((rows + rpb - 1) / rpb);
 }
 
 int reduce_rows_f64(const float* a, const float* b, int P, int n, int ld, double* out_a, double* out_b, cudaStream_t st) {
-    LIFTER_CHECK_CUDA(launch_pdl(reduce_rows_kernel<double>, dim3(ceil_div(n, 32)), dim3(32, 32), 0, st, a, b, P, n, ld, out_a, out_b));
+    LIFTER_CHECK_CUDA(launch_pdl("reduce_rows_kernel<double>", reduce_rows_kernel<double>, dim3(ceil_div(n, RED_COLS)), dim3(RED_COLS, RED_LANES), 0, st, a, b, P, n, ld, out_a, out_b));
     return LIFTER_OK;
 }
 int reduce_rows_f32(const float* a, int P, int n, int ld, float* out, cudaStream_t st) {
-    LIFTER_CHECK_CUDA(launch_pdl(reduce_rows_kernel<float>, dim3(ceil_div(n, 32)), dim3(32, 32), 0, st, a, nullptr, P, n, ld, out, nullptr));
+    LIFTER_CHECK_CUDA(launch_pdl("reduce_rows_kernel<float>", reduce_rows_kernel<float>, dim3(ceil_div(n, RED_COLS)), dim3(RED_COLS, RED_LANES), 0, st, a, nullptr, P, n, ld, out, nullptr));
     return LIFTER_OK;
 }
 
 int bn_finalize_fwd(const BnFwdFinalize& a, cudaStream_t st) {
-    LIFTER_CHECK_CUDA(launch_pdl(bn_finalize_fwd_kernel, dim3(ceil_div(a.H, 256)), dim3(256), 0, st, a));
+    LIFTER_CHECK_CUDA(launch_pdl("bn_finalize_fwd_kernel", bn_finalize_fwd_kernel, dim3(ceil_div(a.H, 256)), dim3(256), 0, st, a));
     return LIFTER_OK;
 }
 
 int bn_reduce_finalize_fwd(const float* psum, const float* psq, int P, const BnFwdFinalize& a, double* sums_out,
                            cudaStream_t st) {
-    LIFTER_CHECK_CUDA(launch_pdl(bn_reduce_finalize_fwd_kernel, dim3(ceil_div(a.H, 32)), dim3(32, 32), 0, st, psum, psq, P, a,
+    LIFTER_CHECK_CUDA(launch_pdl("bn_reduce_finalize_fwd_kernel", bn_reduce_finalize_fwd_kernel, dim3(ceil_div(a.H, RED_COLS)), dim3(RED_COLS, RED_LANES), 0, st, psum, psq, P, a,
                                  sums_out));
     return LIFTER_OK;
 }
 
-int bn_reduce_finalize_bwd(const float* pdy, const float* pdyz, int P, const BnBwdFinalize& a, double* sums_out,
-                           float* dgamma, float* dbeta, cudaStream_t st) {
-    LIFTER_CHECK_CUDA(launch_pdl(bn_reduce_finalize_bwd_kernel, dim3(ceil_div(a.H, 32)), dim3(32, 32), 0, st, pdy, pdyz, P, a,
-                                 sums_out, dgamma, dbeta));
+static int check_h(int H, const char* what) {
+    LIFTER_REQUIRE(H >= 64 && H <= 2048 && (H & (H - 1)) == 0, "%s: unsupported H=%d", what, H);
     return LIFTER_OK;
 }
 
 int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st) {
-    LIFTER_REQUIRE(a.H % 8 == 0, "bn_apply: H must be a multiple of 8");
+    LIFTER_PROPAGATE(check_h(a.H, "bn_apply"));
     const uint32_t thr = dropout_threshold(a.p);
     const float inv_keep = (a.apply_dropout && a.p < 1.0f) ? 1.0f / (1.0f - a.p) : (a.apply_dropout ? 0.0f : 1.0f);
-    const long n = a.rows * (a.H / 8);
-    long blocks = (n + 256 * EW_UNROLL - 1) / (256 * EW_UNROLL);
-    const long cap = static_cast<long>(num_sms()) * 16;
-    if (blocks > cap) blocks = cap;
-    LIFTER_CHECK_CUDA(launch_pdl(bn_apply_fwd_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st, a, thr, inv_keep));
+    const int rpb = rows_per_block_for(a.rows, a.H, 4);
+    const unsigned blocks = static_cast<unsigned>((a.rows + rpb - 1) / rpb);
+    if (a.fmt == FMT_BF16)
+        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_BF16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, thr, inv_keep));
+    else
+        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_F16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, thr, inv_keep));
     return LIFTER_OK;
 }
 
-int bwd_stats(const BwdCommon& c, float* psum_dy, float* psum_dyz, cudaStream_t st) {
-    LIFTER_REQUIRE(c.H >= 64 && c.H <= 2048 && (c.H & (c.H - 1)) == 0, "bwd_stats: unsupported H=%d", c.H);
-    LIFTER_CHECK_CUDA(launch_pdl(bwd_pass_kernel<false>, dim3(ew_partial_rows(c.rows, c.H)), dim3(EW_THREADS), 0, st, c,
-                                 ew_rows_per_block(c.rows, c.H), nullptr, nullptr, psum_dy, psum_dyz));
+int bwd_stats(const BwdCommon& c, float* psum_g, float* psum_gz, cudaStream_t st) {
+    LIFTER_PROPAGATE(check_h(c.H, "bwd_stats"));
+    const dim3 grid(ew_partial_rows(c.rows, c.H));
+    const int rpb = ew_rows_per_block(c.rows, c.H);
+    if (c.fmt == FMT_BF16)
+        LIFTER_CHECK_CUDA(launch_pdl("bwd_stats_kernel", bwd_stats_kernel<FMT_BF16>, grid, dim3(EW_THREADS), 0, st, c, rpb, psum_g, psum_gz));
+    else
+        LIFTER_CHECK_CUDA(launch_pdl("bwd_stats_kernel", bwd_stats_kernel<FMT_F16>, grid, dim3(EW_THREADS), 0, st, c, rpb, psum_g, psum_gz));
     return LIFTER_OK;
 }
 
 int bn_finalize_bwd(const BnBwdFinalize& a, cudaStream_t st) {
-    LIFTER_CHECK_CUDA(launch_pdl(bn_finalize_bwd_kernel, dim3(ceil_div(a.H, 256)), dim3(256), 0, st, a));
+    LIFTER_CHECK_CUDA(launch_pdl("bn_finalize_bwd_kernel", bn_finalize_bwd_kernel, dim3(ceil_div(a.H, 256)), dim3(256), 0, st, a));
     return LIFTER_OK;
 }
 
-int bn_param_grads(const double* local_sums, int H, float* dgamma, float* dbeta, cudaStream_t st) {
-    LIFTER_CHECK_CUDA(launch_pdl(bn_param_grads_kernel, dim3(ceil_div(H, 256)), dim3(256), 0, st, local_sums, H, dgamma, dbeta));
+int bn_bwd_reduce(const float* pg, const float* pgz, int P, const BnBwdFinalize& a, double* sums_out, float* dgamma,
+                  float* dbeta, bool fused, cudaStream_t st) {
+    if (fused)
+        LIFTER_CHECK_CUDA(launch_pdl("bn_bwd_reduce_kernel<fused>", bn_bwd_reduce_kernel<true>, dim3(ceil_div(a.H, RED_COLS)), dim3(RED_COLS, RED_LANES), 0, st, pg, pgz, P, a, sums_out, dgamma, dbeta));
+    else
+        LIFTER_CHECK_CUDA(launch_pdl("bn_bwd_reduce_kernel", bn_bwd_reduce_kernel<false>, dim3(ceil_div(a.H, RED_COLS)), dim3(RED_COLS, RED_LANES), 0, st, pg, pgz, P, a, sums_out, dgamma, dbeta));
     return LIFTER_OK;
 }
 
 int bwd_dz(const BwdCommon& c, const float* coef, void* dz, float* psum_dz, cudaStream_t st) {
-    LIFTER_REQUIRE(c.H >= 64 && c.H <= 2048 && (c.H & (c.H - 1)) == 0, "bwd_dz: unsupported H=%d", c.H);
-    LIFTER_CHECK_CUDA(launch_pdl(bwd_pass_kernel<true>, dim3(ew_partial_rows(c.rows, c.H)), dim3(EW_THREADS), 0, st, c,
-                                 ew_rows_per_block(c.rows, c.H), coef, static_cast<uint16_t*>(dz),
-                                                                            psum_dz, nullptr));
+    LIFTER_PROPAGATE(check_h(c.H, "bwd_dz"));
+    const dim3 grid(ew_partial_rows(c.rows, c.H));
+    const int rpb = ew_rows_per_block(c.rows, c.H);
+    uint16_t* d = static_cast<uint16_t*>(dz);
+    if (psum_dz != nullptr) {
+        if (c.fmt == FMT_BF16)
+            LIFTER_CHECK_CUDA(launch_pdl("bwd_dz_kernel<bias>", bwd_dz_kernel<true, FMT_BF16>, grid, dim3(EW_THREADS), 0, st, c, rpb, coef, d, psum_dz));
+        else
+            LIFTER_CHECK_CUDA(launch_pdl("bwd_dz_kernel<bias>", bwd_dz_kernel<true, FMT_F16>, grid, dim3(EW_THREADS), 0, st, c, rpb, coef, d, psum_dz));
+    } else {
+        if (c.fmt == FMT_BF16)
+            LIFTER_CHECK_CUDA(launch_pdl("bwd_dz_kernel", bwd_dz_kernel<false, FMT_BF16>, grid, dim3(EW_THREADS), 0, st, c, rpb, coef, d, psum_dz));
+        else
+            LIFTER_CHECK_CUDA(launch_pdl("bwd_dz_kernel", bwd_dz_kernel<false, FMT_F16>, grid, dim3(EW_THREADS), 0, st, c, rpb, coef, d, psum_dz));
+    }
     return LIFTER_OK;
 }
 
 int wgrad_reduce(const float* slabs, int splits, int slab_rows, int ld, int rows, int cols, float* grad,
                  cudaStream_t st) {
-    const long n = static_cast<long>(rows) * cols;
-    LIFTER_CHECK_CUDA(launch_pdl(wgrad_reduce_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, 
+    const bool vec = (cols & 3) == 0 && (ld & 3) == 0;
+    const long n = static_cast<long>(rows) * (vec ? cols / 4 : cols);
+    LIFTER_CHECK_CUDA(launch_pdl("wgrad_reduce_kernel", wgrad_reduce_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st,
         slabs, splits, static_cast<long>(slab_rows) * ld, ld, rows, cols, grad));
     return LIFTER_OK;
 }
 
 int prep_grad_out(const float* dout, int64_t rows, int O, int Op, int fmt, void* d16, float* psum, cudaStream_t st) {
     LIFTER_REQUIRE(Op == 64, "prep_grad_out: padded output width must be 64");
-    LIFTER_CHECK_CUDA(launch_pdl(prep_grad_out_kernel, dim3(ew_partial_rows(rows, Op)), dim3(EW_THREADS), 0, st, dout, rows, O, Op, fmt,
+    LIFTER_CHECK_CUDA(launch_pdl("prep_grad_out_kernel", prep_grad_out_kernel, dim3(ew_partial_rows(rows, Op)), dim3(EW_THREADS), 0, st, dout, rows, O, Op, fmt,
                                  ew_rows_per_block(rows, Op),
                                                                        static_cast<uint16_t*>(d16), psum));
     return LIFTER_OK;

@@ -36,32 +36,34 @@ struct BnApplyFwd {
     const void* z; const float* scale; const float* shift; const void* resid;   // resid nullable
     int64_t rows; int H; int fmt;
     int apply_dropout; float p; unsigned long long seed; unsigned step, site; long long row_offset;
+    const unsigned* step_dev;   // nullable: the dropout step is read from device memory (graph replay)
     void* a; uint8_t* bits;     // a [rows][H] 16-bit, bits [rows][H/8]: relu-active AND kept
 };
 int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st);
 
 struct BwdCommon {
-    const void* g; const void* z; const uint8_t* bits; const float* mean_z; const float* rstd;
-    int64_t rows; int H; int fmt; float inv_keep;
+    const void* g; const void* z; const uint8_t* bits;
+    int64_t rows; int H; int fmt;
 };
-// partial column sums of dy and dy * zhat: psum_dy / psum_dyz are [ew_partial_rows][H]
-int bwd_stats(const BwdCommon& c, float* psum_dy, float* psum_dyz, cudaStream_t st);
+// pass 1: partial column sums of gm = (g where the saved bit is set, else 0) and of gm * z: [ew_partial_rows][H] each
+int bwd_stats(const BwdCommon& c, float* psum_g, float* psum_gz, cudaStream_t st);
 
 struct BnBwdFinalize {
-    const double* sums;        // [2][H] (sum dy, sum dy*zhat) over the GLOBAL batch
+    const double* sums;        // [2][H] (sum dy, sum dy*zhat) over the GLOBAL batch (bn_finalize_bwd only)
     double count;
-    const float* gamma; const float* rstd;
+    const float* gamma; const float* rstd; const float* mean_z;
+    float inv_keep;            // dy = inv_keep * gm
     int H, use_bn, bn_mode;
-    float* coef;               // [3][H]: k = gamma*rstd, c1 = sum dy / count, c2 = sum dy*zhat / count
+    float* coef;               // [3][H]: dz = coef0 * gm + coef1 * z + coef2
+    float* dbias;              // nullable: zeroed (the Linear bias in front of batch-statistics BN has no gradient)
 };
 int bn_finalize_bwd(const BnBwdFinalize& a, cudaStream_t st);
-// single-GPU shortcut: reduce pass-1 partials + dgamma/dbeta + pass-2 coefficients in one launch (use_bn only)
-int bn_reduce_finalize_bwd(const float* pdy, const float* pdyz, int P, const BnBwdFinalize& a, double* sums_out,
-                           float* dgamma, float* dbeta, cudaStream_t st);
-// dgamma = sum dy*zhat, dbeta = sum dy from the LOCAL sums (the gradient all-reduce adds the shards)
-int bn_param_grads(const double* local_sums, int H, float* dgamma, float* dbeta, cudaStream_t st);
+// second stage of pass 1: local sums (sum dy, sum dy*zhat) in fp64 -> sums_out [2][H], dgamma/dbeta from them;
+// fused = also the pass-2 coefficients (single GPU, where the local sums are the global ones)
+int bn_bwd_reduce(const float* pg, const float* pgz, int P, const BnBwdFinalize& a, double* sums_out, float* dgamma,
+                  float* dbeta, bool fused, cudaStream_t st);
 
-// dz = k * (dy - c1 - zhat * c2) as 16-bit, plus partial column sums of dz (bias gradient)
+// pass 2: dz = coef0 * gm + coef1 * z + coef2 as 16-bit; psum_dz (nullable) receives partial column sums of dz
 int bwd_dz(const BwdCommon& c, const float* coef, void* dz, float* psum_dz, cudaStream_t st);
 
 // sum of split-K slabs -> dense fp32 gradient [rows][cols]

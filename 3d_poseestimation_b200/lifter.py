@@ -181,6 +181,12 @@ class LinearModel(torch.nn.Module):
             self._cache[key] = (ver, buf)
         return self._cache[key][1]
 
+    def _operands_refreshed(self, fmt):
+        """The fused Adam kernel rewrote the operand copy of format ``fmt`` together with the parameters."""
+        hit = self._cache.get(("op", fmt))
+        if hit is not None:
+            self._cache[("op", fmt)] = ((self._versions(), self._flat.data_ptr()), hit[1])
+
     def _folded_bn(self):
         """Eval-mode BatchNorm + bias folded to per-column scale/shift [L][2][H]."""
         ver = (self._versions(), self._stats_epoch, self._rm._version, self._rv._version,

@@ -28,7 +28,8 @@ class LifterTrainer:
     """
 
     def __init__(self, model, lr=1e-4, loss="mse", optimizer="adamw", betas=(0.9, 0.999), eps=1e-8,
-                 weight_decay=None, seed=0, process_group=None, world_size=None, rank=None, metric_std=None):
+                 weight_decay=None, seed=0, process_group=None, world_size=None, rank=None, metric_std=None,
+                 use_graph=True):
         if loss not in _LOSS:
             raise ValueError(f"unknown loss {loss!r}: use 'mse', 'l1' or 'mpjpe'")
         if optimizer not in ("adam", "adamw"):
@@ -63,6 +64,12 @@ class LifterTrainer:
         self.metric_std = None if metric_std is None else torch.as_tensor(
             metric_std, dtype=torch.float32, device=dev).reshape(-1).contiguous()
         self._bufs = {}
+        # device step state (lifter_step_state_t): lets ONE captured CUDA graph serve every step
+        self.state = torch.zeros(8, dtype=torch.int32, device=dev)
+        self.state.view(torch.float32)[2] = self.lr
+        self.use_graph = bool(use_graph)
+        self._state_stale = False
+        self._graphs = {}
 
     # ------------------------------------------------------------------ buffers sized by the batch
     def _buffers(self, B, dev):
@@ -82,27 +89,26 @@ class LifterTrainer:
     def launches_per_step(self, B):
         L = 2 * self.model.num_stage + 1
         use_bn = 1 if self.model.BN else 0
-        fwd = 1 + L * (1 + use_bn + 2) + 2
+        fwd = 1 + L * 3 + 1                      # prep_input, per layer GEMM + finalize + apply, output GEMM
         loss = 2
-        bwd = 2 + 2 + 1 + L * (2 * use_bn + use_bn + 1 + 1 + 1 + 2 + 1) - 1
-        return fwd + loss + bwd + 1 + (L + 1)
+        bwd = 2 + 2 + 1 + L * (2 * use_bn + 1 + 2 + 1) - 1 + (0 if use_bn else L)
+        return 1 + fwd + loss + bwd + 1          # + step_advance + Adam (which also packs the operands)
 
     # ------------------------------------------------------------------ one optimiser step
-    def step(self, x, y, accumulate_metric=False):
-        """x: (B, 17, 2) or (B, i_dim) fp32 CUDA, y: (B, 17, 3) or (B, o_dim).  Returns the device loss scalar."""
+    def _enqueue(self, x, y, b, accumulate_metric, state):
+        """The kernel sequence of one step on the current stream.  ``state`` (device step state) set: every
+        step-dependent scalar is read from device memory, so the sequence can be captured once and replayed."""
         model = self.model
         lib, cfg = _cabi.lib(), C.byref(model._cfg)
-        x = model._check_input(x)
-        y = y.reshape(y.shape[0], -1)
-        if y.shape != (x.shape[0], model.output_size) or y.dtype != torch.float32 or not y.is_cuda:
-            raise RuntimeError(f"target must be a float32 CUDA tensor of {x.shape[0]} x {model.output_size} values")
-        y = y.contiguous()
         B = x.shape[0]
-        b = self._buffers(B, x.device)
-        model.train()
         st = _cabi.stream_ptr()
+        fmt = model._fmt_code(model.train_format)
+        if state is not None:
+            _cabi.check(lib.lifter_step_advance(_cabi.ptr(state), self.betas[0], self.betas[1],
+                                                self.weight_decay if self.decoupled else 0.0, st))
         # forward (saved activations), dropout stream addressed by the optimiser step
-        out, _, t = _autograd.run_forward(model, x, True, saved=b["saved"], out=b["out"], step=self.step_count)
+        out, _, t = _autograd.run_forward(model, x, True, saved=b["saved"], out=b["out"], step=self.step_count,
+                                          step_state=state)
         # fused loss + dL/dpred + per-joint MPJPE sums; the mean is over the GLOBAL batch
         _cabi.check(lib.lifter_loss(_cabi.ptr(out), _cabi.ptr(y), B, self.joints, self.loss_kind, B * self.world,
                                     _cabi.ptr(self.metric_std), _cabi.ptr(b["dpred"]), _cabi.ptr(b["lscratch"]),
@@ -111,13 +117,75 @@ class LifterTrainer:
         if self.world > 1:
             import torch.distributed as dist
             dist.all_reduce(self.grad, group=self.pg)             # sum of shard gradients = global-batch gradient
+        ops = model._operands(fmt)
+        # Adam / AdamW over the flat buffer; the same pass rewrites the 16-bit operand copies of the weights
+        _cabi.check(lib.lifter_adam_step_packed(cfg, _cabi.ptr(model._flat), _cabi.ptr(self.grad), _cabi.ptr(self.m),
+                                                _cabi.ptr(self.v), self.lr, self.betas[0], self.betas[1], self.eps,
+                                                self.weight_decay, int(self.decoupled), self.step_count + 1, 1.0,
+                                                _cabi.ptr(state), _cabi.ptr(ops), fmt, st))
+
+    def _after_step(self):
+        model = self.model
         self.step_count += 1
-        _cabi.check(lib.lifter_adam_step(_cabi.ptr(model._flat), _cabi.ptr(self.grad), _cabi.ptr(self.m),
-                                         _cabi.ptr(self.v), model._flat.numel(), self.lr, self.betas[0], self.betas[1],
-                                         self.eps, self.weight_decay, int(self.decoupled), self.step_count, 1.0, st))
         model._param_epoch += 1                                   # the flat parameters changed under torch's feet
-        model._operands(model._fmt_code(model.train_format))      # refresh the 16-bit operand copies now
+        model._operands_refreshed(model._fmt_code(model.train_format))
+
+    def _check_xy(self, x, y):
+        model = self.model
+        x = model._check_input(x)
+        y = y.reshape(y.shape[0], -1)
+        if y.shape != (x.shape[0], model.output_size) or y.dtype != torch.float32 or not y.is_cuda:
+            raise RuntimeError(f"target must be a float32 CUDA tensor of {x.shape[0]} x {model.output_size} values")
+        return x, y.contiguous()
+
+    def step(self, x, y, accumulate_metric=False):
+        """x: (B, 17, 2) or (B, i_dim) fp32 CUDA, y: (B, 17, 3) or (B, o_dim).  Returns the device loss scalar."""
+        model = self.model
+        x, y = self._check_xy(x, y)
+        B = x.shape[0]
+        model.train()
+        if self.use_graph and self.world == 1 and B >= 2:
+            return self._step_graph(x, y, bool(accumulate_metric))
+        b = self._buffers(B, x.device)
+        self._enqueue(x, y, b, accumulate_metric, None)
+        self._after_step()
+        self._state_stale = True                                  # the device step state did not see this step
         return self.loss_out[0]
+
+    def _step_graph(self, x, y, accumulate_metric):
+        """Replay of the captured step (one CUDA graph per batch size): no per-kernel host work."""
+        model = self.model
+        B = x.shape[0]
+        key = (B, accumulate_metric, model._flat.data_ptr())
+        g = self._graphs.get(key)
+        if g is None:
+            b = self._buffers(B, x.device)
+            xs, ys = torch.empty_like(x), torch.empty_like(y)
+            model._operands(model._fmt_code(model.train_format))          # packed before the capture starts
+            self._sync_state()
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.graph(graph, stream=side):
+                self._enqueue(xs, ys, b, accumulate_metric, self.state)
+            g = (graph, xs, ys)
+            self._graphs = {key: g}                                       # keep one batch size resident
+        graph, xs, ys = g
+        if self._state_stale:
+            self._sync_state()
+        xs.copy_(x, non_blocking=True)
+        ys.copy_(y, non_blocking=True)
+        graph.replay()
+        model._stats_epoch += 1
+        self._after_step()
+        return self.loss_out[0]
+
+    def _sync_state(self):
+        """Host -> device: optimiser step count and learning rate."""
+        self.state[1] = self.step_count
+        self.state.view(torch.float32)[2] = self.lr
+        self._state_stale = False
 
     def loss_value(self):
         """Host read of the last step's loss (synchronises); with data parallelism, the sum over ranks."""
@@ -138,6 +206,7 @@ class LifterTrainer:
     def set_lr(self, lr):
         """The per-step host scalar ReduceLROnPlateau drives (train_1.py:41,106)."""
         self.lr = float(lr)
+        self.state.view(torch.float32)[2] = self.lr
 
     def state_dict(self):
         return {"step": self.step_count, "m": self.m, "v": self.v, "lr": self.lr}
@@ -146,3 +215,4 @@ class LifterTrainer:
         self.step_count, self.lr = int(sd["step"]), float(sd["lr"])
         self.m.copy_(sd["m"])
         self.v.copy_(sd["v"])
+        self._sync_state()

@@ -83,6 +83,19 @@ int lifter_forward_eval(const lifter_config_t* cfg, const void* operands, const 
  * Replaces the autograd graph of LinearModel.forward in train mode (baselineModel.py:87-102, 32-47),
  * loss.backward() and optimizer.step() (train_1.py:94-96).  One context describes one forward/backward
  * pair; `saved` is written by forward and read by backward.                                            */
+/* Per-step scalars that live in DEVICE memory so that one captured CUDA graph can be replayed for every step:
+ * lifter_step_advance() (first node of the step) moves the counters on and derives Adam's bias corrections from
+ * `lr`, which the host may overwrite between steps (ReduceLROnPlateau, train_1.py:41,106).                   */
+typedef struct lifter_step_state {
+    uint32_t dropout_step;   /* Philox step of this training step's masks (= adam_step - 1)        */
+    int32_t adam_step;       /* optimiser steps taken, 1-based after the first lifter_step_advance */
+    float lr;                /* host-written                                                       */
+    float step_size;         /* lr / (1 - beta1^t)                                                 */
+    float inv_sqrt_bc2;      /* 1 / sqrt(1 - beta2^t)                                              */
+    float decay;             /* 1 - lr * weight_decay (AdamW)                                      */
+    float reserved[2];
+} lifter_step_state_t;
+
 typedef struct lifter_train_ctx {
     const float* params;            /* flat fp32 parameters                                              */
     const void* operands;           /* 16-bit operand copies in `fmt` (lifter_pack_weights)              */
@@ -104,6 +117,8 @@ typedef struct lifter_train_ctx {
     float* grad_params;             /* backward: flat fp32, parameter layout; every tensor is overwritten */
     float* grad_x;                  /* backward: [batch][i_dim] fp32, nullable                            */
     void* scratch; int64_t scratch_bytes;      /* backward: lifter_train_scratch_bytes()                  */
+    const struct lifter_step_state* step_state; /* nullable, DEVICE memory: the dropout step is read from it at run
+                                                  time instead of `step` (a captured CUDA graph replays every step) */
 } lifter_train_ctx_t;
 
 int64_t lifter_train_saved_bytes(const lifter_config_t* cfg, int64_t batch);
@@ -143,6 +158,14 @@ int lifter_l1_grad(const float* a, const float* b, int64_t n, int row_len, int c
 int lifter_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                      float eps, float weight_decay, int decoupled, int step, float grad_scale, void* stream);
 
+/* Graph-replayable optimiser step: advances the device step state (call once at the top of every step) ...      */
+int lifter_step_advance(lifter_step_state_t* state, float beta1, float beta2, float weight_decay, void* stream);
+/* ... and Adam/AdamW over the flat buffer of `cfg` that ALSO refreshes the 16-bit GEMM operand copies of the Linear
+ * weights (operands nullable) in the same pass.  state (device, nullable) overrides lr/step with the step state.   */
+int lifter_adam_step_packed(const lifter_config_t* cfg, float* p, const float* g, float* m, float* v, float lr,
+                            float beta1, float beta2, float eps, float weight_decay, int decoupled, int step,
+                            float grad_scale, const lifter_step_state_t* state, void* operands, int fmt, void* stream);
+
 /* ---- test hook: one tcgen05 GEMM  D[M][N] = sum_k A(m,k) B(n,k) ------------------------------------ */
 typedef struct lifter_gemm_desc {
     const void* A; int64_t lda; const void* B; int64_t ldb;
@@ -156,6 +179,11 @@ typedef struct lifter_gemm_desc {
     int32_t max_stages;          /* debug: cap on the operand ring depth (0 = all that fit in shared memory) */
 } lifter_gemm_desc_t;
 int lifter_gemm(const lifter_gemm_desc_t* desc, void* stream);
+/* ---- debug hook: per-launch device times.  lifter_trace_begin() makes every later launch of this library record a
+ * CUDA event; lifter_trace_end() synchronises and writes one "kernel-name microseconds" line per launch into buf
+ * (returns the number of bytes written).  Not for production: the events serialise the launches.             */
+int lifter_trace_begin(void* stream);
+int lifter_trace_end(char* buf, int len);
 int lifter_gemm_slab_rows(int M);
 int lifter_gemm_stat_rows(int M);
 int lifter_gemm_effective_splits(int K, int splits);

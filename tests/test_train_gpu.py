@@ -69,7 +69,10 @@ def test_train_step_matches_reference_golden(pkg, golden_dir, tag, fmt):
         if not BN and "batch_norm" in name:
             assert prm.grad is None or float(prm.grad.abs().max()) == 0.0
             continue
-        if float(gm.norm()) < 1e-4 * scale:                      # bias in front of train-mode BN: analytically zero
+        lin_bias = BN and name.endswith(".bias") and "batch_norm" not in name and not name.startswith("w2.")
+        if lin_bias or float(gm.norm()) < 1e-4 * scale:
+            # a Linear bias in front of train-mode BN has an analytically zero gradient (the reference returns
+            # fp32 rounding noise, the rounding model 16-bit noise); the kernels write exact zeros
             assert float(prm.grad.norm()) < 1e-3 * scale, name
             continue
         assert rel_l2(prm.grad.cpu(), gm) < 5e-2, f"{name}: rel l2 vs model {rel_l2(prm.grad.cpu(), gm)}"
