@@ -38,6 +38,9 @@ def _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offse
     t.fmt, t.bn_mode, t.apply_dropout = fmt, (0 if training else 1), (1 if training else 0)
     t.step, t.seed = step & 0xFFFFFFFF, model.dropout_seed & 0xFFFFFFFFFFFFFFFF
     t.step_state = step_state.data_ptr() if step_state is not None else None
+    dp = getattr(model, "_dp", None)
+    if dp is not None and step_state is not None and training:
+        t.dp = C.pointer(dp)                 # in-kernel SyncBN exchange over the symmetric buffer
     return t
 
 
@@ -61,7 +64,7 @@ def run_forward(model, x, training, saved=None, out=None, step=None, step_state=
         out = torch.empty(B, model.output_size, dtype=torch.float32, device=x.device)
     t = _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offset, step_state)
     st = _cabi.stream_ptr()
-    if not sync_bn:
+    if not sync_bn or bool(t.dp):
         _cabi.check(lib.lifter_train_forward(cfg, C.byref(t), st))
     else:
         import torch.distributed as dist
@@ -90,7 +93,7 @@ def run_backward(model, t, grad_out, grad_flat, grad_x, scratch=None):
     st = _cabi.stream_ptr()
     pg, world, _ = _dist_world(model)
     sync_bn = t.bn_mode == 0 and model.BN and world > 1
-    if not sync_bn:
+    if not sync_bn or bool(t.dp):
         _cabi.check(lib.lifter_train_backward(cfg, C.byref(t), st))
     else:
         import torch.distributed as dist

@@ -34,6 +34,12 @@ class GemmDesc(C.Structure):
                 ("timeline", C.c_void_p), ("max_stages", C.c_int32)]
 
 
+class DpInfo(C.Structure):
+    """``lifter_dp_t``: peer pointers of the symmetric SyncBN exchange buffer."""
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("sync", C.c_void_p * 8), ("grad", C.c_void_p * 8),
+                ("params", C.c_void_p * 8), ("operands", C.c_void_p * 8), ("flags", C.c_void_p * 8)]
+
+
 class TrainCtx(C.Structure):
     """``lifter_train_ctx_t``: one forward/backward pair of the training path."""
     _fields_ = [("params", C.c_void_p), ("operands", C.c_void_p), ("running_mean", C.c_void_p),
@@ -42,10 +48,12 @@ class TrainCtx(C.Structure):
                 ("global_batch", C.c_int64), ("row_offset", C.c_int64), ("fmt", C.c_int32), ("bn_mode", C.c_int32),
                 ("apply_dropout", C.c_int32), ("step", C.c_uint32), ("seed", C.c_uint64), ("grad_out", C.c_void_p),
                 ("grad_params", C.c_void_p), ("grad_x", C.c_void_p), ("scratch", C.c_void_p),
-                ("scratch_bytes", C.c_int64), ("step_state", C.c_void_p)]
+                ("scratch_bytes", C.c_int64), ("step_state", C.c_void_p), ("dp", C.POINTER(DpInfo))]
 
 
 LOSS_MSE, LOSS_L1, LOSS_MPJPE = 0, 1, 2
+DP_MAX_WORLD = 8
+DP_FLAG_BYTES = 256
 
 _P, _I64, _I32, _F = C.c_void_p, C.c_int64, C.c_int32, C.c_float
 _CFG = C.POINTER(LifterConfig)
@@ -82,8 +90,10 @@ SIGNATURES = {
     "lifter_l1_sum": (_I32, [_P, _P, _I64, _I32, _I32, _F, _P, _P, _P]),
     "lifter_l1_grad": (_I32, [_P, _P, _I64, _I32, _I32, _P, _F, _P, _P, _P]),
     "lifter_adam_step": (_I32, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _I32, _F, _P]),
+    "lifter_dp_sync_bytes": (_I64, [_CFG, _I32]),
     "lifter_step_advance": (_I32, [_P, _F, _F, _F, _P]),
     "lifter_adam_step_packed": (_I32, [_CFG, _P, _P, _P, _P, _F, _F, _F, _F, _F, _I32, _I32, _F, _P, _P, _I32, _P]),
+    "lifter_dp_adam_step": (_I32, [_CFG, C.POINTER(DpInfo), _P, _P, _F, _F, _F, _F, _I32, _F, _P, _I32, _P]),
     "lifter_gemm": (_I32, [C.POINTER(GemmDesc), _P]),
     "lifter_trace_begin": (_I32, [_P]),
     "lifter_trace_end": (_I32, [C.c_char_p, _I32]),

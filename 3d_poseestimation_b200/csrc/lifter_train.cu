@@ -69,6 +69,27 @@ void carve_saved(const Layout& lay, int64_t B, void* base, SavedWs* w) {
     w->bytes = c.off;
 }
 
+// symmetric SyncBN exchange buffer: 2 parities x nsites x world slots x 2 x H values of 16 bytes (LL words)
+size_t dp_data_bytes(const Layout& lay, int world) {
+    return align_up(static_cast<size_t>(2) * (2 * lay.L) * world * 2 * lay.H * 16, 256);
+}
+size_t dp_flag_bytes(const Layout&, int) { return 0; }
+int fill_exchange(const Layout& lay, const lifter_train_ctx_t* t, int site, SyncExchange* ex) {
+    *ex = SyncExchange();
+    if (t->dp == nullptr || t->dp->world <= 1) return LIFTER_OK;
+    const lifter_dp_t* d = t->dp;
+    LIFTER_REQUIRE(d->world <= DP_MAX_WORLD && d->rank >= 0 && d->rank < d->world, "dp: world %d / rank %d out of range",
+                   d->world, d->rank);
+    LIFTER_REQUIRE(t->step_state != nullptr, "dp: the in-kernel BatchNorm exchange needs the device step state");
+    ex->world = d->world; ex->rank = d->rank; ex->site = site; ex->nsites = 2 * lay.L;
+    for (int p = 0; p < d->world; ++p) {
+        LIFTER_REQUIRE(d->sync[p] != nullptr, "dp: null peer buffer %d", p);
+        ex->data[p] = d->sync[p];
+    }
+    ex->epoch = reinterpret_cast<const unsigned*>(t->step_state) + 1;      // lifter_step_state_t.adam_step
+    return LIFTER_OK;
+}
+
 int wgrad_splits(int M, int N, int K) {
     const int bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
     const int tiles = ceil_div(M, 128) * ceil_div(N, bn);
@@ -168,6 +189,12 @@ int64_t lifter_train_scratch_bytes(const lifter_config_t* cfg, int64_t batch) {
     carve_scratch(lay, batch, nullptr, &s);
     return static_cast<int64_t>(s.bytes);
 }
+int64_t lifter_dp_sync_bytes(const lifter_config_t* cfg, int world) {
+    Layout lay;
+    if (make_layout(cfg, &lay) != 0) return LIFTER_ERR_INVALID;
+    if (world < 1 || world > DP_MAX_WORLD) { set_error("dp: world must be 1..%d", DP_MAX_WORLD); return LIFTER_ERR_INVALID; }
+    return static_cast<int64_t>(dp_data_bytes(lay, world) + dp_flag_bytes(lay, world));
+}
 int64_t lifter_train_fwd_sums_offset(const lifter_config_t* cfg, int64_t batch, int layer) {
     Layout lay;
     if (make_layout(cfg, &lay) != 0) return LIFTER_ERR_INVALID;
@@ -228,6 +255,7 @@ static int fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     f.num_batches_tracked = t->num_batches_tracked ? reinterpret_cast<long long*>(t->num_batches_tracked) + l : nullptr;
     f.momentum = cfg->bn_momentum; f.eps = cfg->bn_eps; f.H = H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode;
     f.mean_z = w.mean_z[l]; f.rstd = w.rstd[l]; f.scale = w.scale[l]; f.shift = w.shift[l];
+    if (fused) LIFTER_PROPAGATE(fill_exchange(lay, t, l, &f.ex));          // forward site l
     if (fused && cfg->use_bn && t->bn_mode == 0)
         LIFTER_PROPAGATE(bn_reduce_finalize_fwd(w.psum, w.psq, gemm_stat_rows(static_cast<int>(t->batch)), f, w.sums[l], st));
     else
@@ -338,6 +366,11 @@ static BnBwdFinalize bwd_finalize_args(const lifter_config_t* cfg, const lifter_
     f.dbias = (cfg->use_bn && t->bn_mode == 0) ? t->grad_params + lay.p_off[lay.t_bias(l)] : nullptr;
     return f;
 }
+static int bwd_exchange(const lifter_config_t* cfg, const lifter_train_ctx_t* t, const Layout& lay, int l, bool fused,
+                        BnBwdFinalize* f) {
+    if (fused && cfg->use_bn && t->bn_mode == 0) return fill_exchange(lay, t, lay.L + l, &f->ex);   // backward site
+    return LIFTER_OK;
+}
 
 static int bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
     Layout lay;
@@ -354,7 +387,8 @@ static int bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t*
     c.rows = t->batch; c.H = H; c.fmt = t->fmt;
     LIFTER_PROPAGATE(bwd_stats(c, b.pA, b.pB, st));
     // local sums (what a data-parallel run all-reduces), dgamma/dbeta from them; fused: also the pass-2 coefficients
-    const BnBwdFinalize f = bwd_finalize_args(cfg, t, lay, w, b, l);
+    BnBwdFinalize f = bwd_finalize_args(cfg, t, lay, w, b, l);
+    LIFTER_PROPAGATE(bwd_exchange(cfg, t, lay, l, fused, &f));
     return bn_bwd_reduce(b.pA, b.pB, ew_partial_rows(t->batch, H), f, b.bsums[l],
                          t->grad_params + lay.p_off[lay.t_gamma(l)], t->grad_params + lay.p_off[lay.t_beta(l)], fused, st);
 }
@@ -488,6 +522,40 @@ int lifter_adam_step_packed(const lifter_config_t* cfg, float* p, const float* g
     LIFTER_PROPAGATE(adam_step(a, st));
     if (operands != nullptr) return lifter_pack_weights(cfg, p, operands, fmt, stream);   // very deep models
     return LIFTER_OK;
+}
+
+int lifter_dp_adam_step(const lifter_config_t* cfg, const lifter_dp_t* dp, float* m, float* v, float beta1, float beta2,
+                        float eps, float weight_decay, int decoupled, float grad_scale,
+                        const lifter_step_state_t* state, int fmt, void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(make_layout(cfg, &lay));
+    LIFTER_REQUIRE(dp != nullptr && m && v && state, "dp_adam: null pointer");
+    LIFTER_REQUIRE(dp->world >= 2 && dp->world <= ADAM_DP_MAX_WORLD && dp->rank >= 0 && dp->rank < dp->world,
+                   "dp_adam: world %d / rank %d out of range", dp->world, dp->rank);
+    LIFTER_REQUIRE(fmt == FMT_F16 || fmt == FMT_BF16, "dp_adam: unknown operand format %d", fmt);
+    LIFTER_REQUIRE(lay.L + 1 <= ADAM_MAX_WEIGHTS, "dp_adam: too many layers for the fused operand refresh");
+    AdamDpArgs d;
+    d.world = dp->world; d.rank = dp->rank;
+    for (int q = 0; q < dp->world; ++q) {
+        LIFTER_REQUIRE(dp->grad[q] && dp->params[q] && dp->operands[q] && dp->flags[q], "dp_adam: null peer buffer %d", q);
+        d.g_peer[q] = static_cast<const float*>(dp->grad[q]);
+        d.p_peer[q] = static_cast<float*>(dp->params[q]);
+        d.op_peer[q] = dp->operands[q];
+        d.flag_peer[q] = static_cast<unsigned*>(dp->flags[q]);
+    }
+    AdamArgs& a = d.a;
+    a.p = d.p_peer[d.rank]; a.g = d.g_peer[d.rank]; a.m = m; a.v = v; a.n = lay.p_total;
+    a.lr = 0.0f; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay; a.decoupled = decoupled;
+    a.step = 1; a.grad_scale = grad_scale; a.dyn = reinterpret_cast<const float*>(state);
+    a.operands = d.op_peer[d.rank]; a.op_fmt = fmt; a.nw = lay.L + 1;
+    for (int l = 0; l <= lay.L; ++l) {
+        const int t = l < lay.L ? lay.t_weight(l) : lay.t_w2();
+        a.w_p_off[l] = lay.p_off[t]; a.w_numel[l] = lay.p_numel[t]; a.w_off[l] = lay.w_off[l];
+        a.w_in[l] = l < lay.L ? lay.in_dim(l) : lay.H;
+        a.w_pad[l] = l < lay.L ? lay.in_pad(l) : lay.H;
+    }
+    d.epoch = reinterpret_cast<const unsigned*>(state) + 1;
+    return adam_step_dp(d, static_cast<cudaStream_t>(stream));
 }
 
 int lifter_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,

@@ -212,6 +212,126 @@ __global__ void __launch_bounds__(256) adam_kernel(AdamArgs a, float step_size, 
     }
 }
 
+__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void wait_epoch(const unsigned* f, unsigned epoch) {
+    long long t0 = 0;
+    unsigned spins = 0;
+    while (static_cast<int>(ld_acquire_sys_u32(f) - epoch) < 0) {         // a lost peer traps after ~4 s, no hang
+        if ((++spins & 0xFF) == 0) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 8000000000LL) __trap();
+        }
+    }
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+    float4 r;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+    return r;
+}
+
+constexpr int DP_UNROLL = 2;
+__global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_size, float inv_sqrt_bc2, float decay) {
+    griddep_launch();
+    griddep_wait();
+    const AdamArgs& a = d.a;
+    if (a.dyn != nullptr) { step_size = a.dyn[3]; inv_sqrt_bc2 = a.dyn[4]; decay = a.dyn[5]; }
+    const unsigned epoch = *d.epoch;
+    unsigned* my_flags = d.flag_peer[d.rank];
+    // ---- barrier 1: every rank's gradient is complete (my predecessor kernels finished: this kernel runs)
+    if (threadIdx.x < d.world) {
+        if (blockIdx.x == 0) st_release_sys_u32(d.flag_peer[threadIdx.x] + d.rank, epoch);
+        wait_epoch(my_flags + threadIdx.x, epoch);
+    }
+    __syncthreads();
+    // ---- my slice: sum of the gradients in rank order, Adam, parameters to every rank
+    const long n4 = a.n >> 2;
+    const long slice = (n4 + d.world - 1) / d.world;
+    const long lo = slice * d.rank, hi = min(lo + slice, n4);
+    const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+    for (long i0 = lo + static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < hi; i0 += stride * DP_UNROLL) {
+        float4 gs[DP_UNROLL][ADAM_DP_MAX_WORLD];
+#pragma unroll
+        for (int u = 0; u < DP_UNROLL; ++u) {
+            const long i = i0 + u * stride;
+#pragma unroll
+            for (int q = 0; q < ADAM_DP_MAX_WORLD; ++q)
+                if (q < d.world && i < hi) gs[u][q] = ld_peer_f4(d.g_peer[q] + i * 4);
+        }
+#pragma unroll
+        for (int u = 0; u < DP_UNROLL; ++u) {
+            const long i = i0 + u * stride;
+            if (i >= hi) break;
+            float4 g4 = gs[u][0];
+#pragma unroll
+            for (int q = 1; q < ADAM_DP_MAX_WORLD; ++q)
+                if (q < d.world) { g4.x += gs[u][q].x; g4.y += gs[u][q].y; g4.z += gs[u][q].z; g4.w += gs[u][q].w; }
+            float4 p = reinterpret_cast<float4*>(a.p)[i];
+            float4 m = reinterpret_cast<float4*>(a.m)[i];
+            float4 v = reinterpret_cast<float4*>(a.v)[i];
+            float* pp = &p.x; const float* gp = &g4.x; float* mp = &m.x; float* vp = &v.x;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                float g = gp[e] * a.grad_scale;
+                if (a.decoupled) pp[e] *= decay;
+                else if (a.weight_decay != 0.0f) g = fmaf(a.weight_decay, pp[e], g);
+                mp[e] = a.beta1 * mp[e] + (1.0f - a.beta1) * g;
+                vp[e] = a.beta2 * vp[e] + (1.0f - a.beta2) * g * g;
+                const float denom = sqrtf(vp[e]) * inv_sqrt_bc2 + a.eps;
+                pp[e] -= step_size * (mp[e] / denom);
+            }
+            reinterpret_cast<float4*>(a.m)[i] = m;
+            reinterpret_cast<float4*>(a.v)[i] = v;
+            for (int q = 0; q < d.world; ++q) reinterpret_cast<float4*>(d.p_peer[q])[i] = p;
+            if (a.operands != nullptr) {
+                const long idx = i * 4;
+                for (int t = 0; t < a.nw; ++t) {
+                    const long e0 = idx - a.w_p_off[t];
+                    if (e0 < 0 || e0 >= a.w_numel[t]) continue;
+                    if (a.w_in[t] == a.w_pad[t]) {
+                        const uint2 w2 = make_uint2(pack16(p.x, p.y, a.op_fmt), pack16(p.z, p.w, a.op_fmt));
+                        for (int q = 0; q < d.world; ++q)
+                            *reinterpret_cast<uint2*>(static_cast<uint16_t*>(d.op_peer[q]) + a.w_off[t] + e0) = w2;
+                    } else {
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const long el = e0 + e;
+                            const long r = el / a.w_in[t];
+                            const int c = static_cast<int>(el - r * a.w_in[t]);
+                            const uint16_t h = cvt16(pp[e], a.op_fmt);
+                            for (int q = 0; q < d.world; ++q)
+                                static_cast<uint16_t*>(d.op_peer[q])[a.w_off[t] + r * a.w_pad[t] + c] = h;
+                        }
+                    }
+                    break;
+                }
+            }
+        }
+    }
+    // ---- barrier 2: the last block of this rank tells every peer "my stores are done" and waits for theirs
+    __threadfence_system();
+    __syncthreads();
+    __shared__ unsigned last;
+    unsigned* counter = my_flags + 2 * d.world;
+    if (threadIdx.x == 0) last = (atomicAdd(counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+    __syncthreads();
+    if (last) {
+        if (threadIdx.x == 0) *counter = 0;                                // ready for the next step
+        if (threadIdx.x < d.world) {
+            st_release_sys_u32(d.flag_peer[threadIdx.x] + d.world + d.rank, epoch);
+            wait_epoch(my_flags + d.world + threadIdx.x, epoch);
+        }
+    }
+}
+
 // state: [0] u32 dropout_step, [1] i32 adam_step, [2] f32 lr, [3] step_size, [4] inv_sqrt_bc2, [5] decay
 __global__ void step_advance_kernel(unsigned int* state, float beta1, float beta2, float weight_decay) {
     griddep_launch();
@@ -276,6 +396,20 @@ int adam_step(const AdamArgs& a, cudaStream_t st) {
     const long cap = static_cast<long>(num_sms()) * 8;             // grid = multiple of the SM count, grid-stride
     if (blocks > cap) blocks = cap;
     LIFTER_CHECK_CUDA(launch_pdl("adam_kernel", adam_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st, a, step_size, inv_sqrt_bc2, decay));
+    return LIFTER_OK;
+}
+
+int adam_step_dp(const AdamDpArgs& d, cudaStream_t st) {
+    const AdamArgs& a = d.a;
+    LIFTER_REQUIRE(a.n % 4 == 0, "adam: flat buffer length must be a multiple of 4");
+    LIFTER_REQUIRE(d.world >= 2 && d.world <= ADAM_DP_MAX_WORLD && d.rank >= 0 && d.rank < d.world, "adam_dp: bad world/rank");
+    LIFTER_REQUIRE(a.dyn != nullptr && d.epoch != nullptr, "adam_dp: needs the device step state");
+    const long slice4 = (a.n / 4 + d.world - 1) / d.world;
+    long blocks = (slice4 + 256 * DP_UNROLL - 1) / (256 * DP_UNROLL);
+    const long cap = static_cast<long>(num_sms()) * 4;                      // all blocks co-resident (flag barriers)
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    LIFTER_CHECK_CUDA(launch_pdl("adam_dp_kernel", adam_dp_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st, d, 0.0f, 1.0f, 1.0f));
     return LIFTER_OK;
 }
 

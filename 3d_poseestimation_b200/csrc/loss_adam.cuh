@@ -38,6 +38,24 @@ struct AdamArgs {
     int w_in[ADAM_MAX_WEIGHTS]; int w_pad[ADAM_MAX_WEIGHTS];
 };
 int adam_step(const AdamArgs& a, cudaStream_t st);
+// Data-parallel optimiser step as ONE kernel over NVLink peer memory (no NCCL call): rank r owns slice r of the flat
+// buffer.  After a flag barrier ("every rank's gradient is complete") it reads that slice of every rank's gradient
+// with P2P loads, adds them in rank order, runs Adam on the slice and stores the new parameters (fp32 + 16-bit
+// operand copies) into EVERY rank's buffers with P2P stores; a second flag barrier ends the kernel once all peers
+// have finished writing here.  Reduce-scatter + Adam + all-gather fused: each gradient crosses NVLink once, each
+// parameter once, and the Adam state traffic is 1/world of the replicated optimiser's.
+constexpr int ADAM_DP_MAX_WORLD = 8;
+struct AdamDpArgs {
+    AdamArgs a;                                  // p/g = THIS rank's buffers; operands = this rank's operand copy
+    int world, rank;
+    const float* g_peer[ADAM_DP_MAX_WORLD];      // every rank's gradient buffer (peer-mapped)
+    float* p_peer[ADAM_DP_MAX_WORLD];            // every rank's parameter buffer
+    void* op_peer[ADAM_DP_MAX_WORLD];            // every rank's operand buffer (nullable when a.operands == nullptr)
+    unsigned* flag_peer[ADAM_DP_MAX_WORLD];      // every rank's flag block: [2][world] epochs + [1] block counter
+    const unsigned* epoch;                       // device step counter
+};
+int adam_step_dp(const AdamDpArgs& a, cudaStream_t st);
+
 // device step state (include/lifter_b200.h: lifter_step_state_t): dropout_step = adam_step; adam_step += 1; the Adam
 // bias corrections of the new step from the lr stored in the state
 int step_advance(void* state, float beta1, float beta2, float weight_decay, cudaStream_t st);

@@ -70,6 +70,59 @@ __device__ __forceinline__ void reduce_partials_2(const float* __restrict__ a, c
     tb = sh[1][0][threadIdx.x];
 }
 
+// ---------------------------------------------------------------------------------- cross-GPU sum (SyncBN)
+// "LL" exchange (the low-latency protocol NCCL uses for small messages, written out here): every double travels as
+// one 16-byte store {lo, epoch, hi, epoch} into the writer's slot of every peer's symmetric buffer; each 8-byte half
+// validates itself through its epoch word, so no fence and no separate flag round trip are needed -- the receiver
+// polls its LOCAL memory until both halves carry this step's epoch.  One NVLink store latency per exchange.
+__device__ __forceinline__ void st_ll_f64(uint4* p, double v, unsigned epoch) {
+    const unsigned long long b = static_cast<unsigned long long>(__double_as_longlong(v));
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(static_cast<unsigned>(b)), "r"(epoch),
+                 "r"(static_cast<unsigned>(b >> 32)), "r"(epoch)
+                 : "memory");
+}
+__device__ __forceinline__ double ld_ll_f64(const uint4* p, unsigned epoch) {
+    uint4 w;
+    long long t0 = 0;
+    unsigned spins = 0;
+    while (true) {
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "l"(p) : "memory");
+        if (w.y == epoch && w.w == epoch) break;
+        if ((++spins & 0x3FF) == 0) {                                      // a lost peer traps after ~4 s, no hang
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 8000000000LL) __trap();
+        }
+    }
+    return __longlong_as_double(static_cast<long long>((static_cast<unsigned long long>(w.z) << 32) | w.x));
+}
+
+// Called by the first RED_COLS threads of a block (threadIdx.y == 0) holding the local sums (ta, tb) of column
+// `col`; returns the sums over all ranks, added in rank order (identical on every GPU).  See SyncExchange.
+__device__ __forceinline__ void exchange_column_sums(const SyncExchange& ex, int H, int col, bool active, double& ta,
+                                                     double& tb) {
+    if (!active) return;
+    const unsigned epoch = *ex.epoch;
+    // [parity][site][slot = writer rank][2][H] LL words
+    const size_t base = ((static_cast<size_t>(epoch & 1u) * ex.nsites + ex.site) * ex.world) * 2 * H;
+    const size_t mine = base + static_cast<size_t>(ex.rank) * 2 * H;
+    for (int p = 0; p < ex.world; ++p) {
+        if (p == ex.rank) continue;
+        uint4* d = reinterpret_cast<uint4*>(ex.data[p]) + mine;
+        st_ll_f64(d + col, ta, epoch);
+        st_ll_f64(d + H + col, tb, epoch);
+    }
+    const double la = ta, lb = tb;
+    ta = 0.0; tb = 0.0;
+    for (int r = 0; r < ex.world; ++r) {
+        if (r == ex.rank) { ta += la; tb += lb; continue; }
+        const uint4* d = reinterpret_cast<const uint4*>(ex.data[ex.rank]) + base + static_cast<size_t>(r) * 2 * H;
+        ta += ld_ll_f64(d + col, epoch);
+        tb += ld_ll_f64(d + H + col, epoch);
+    }
+}
+
 template <typename OutT>
 __global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int P, int n, int ld,
                                    OutT* __restrict__ out_a, OutT* __restrict__ out_b) {
@@ -134,6 +187,7 @@ __global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, co
     double ta, tb;
     reduce_partials_2(psum, psq, P, a.H, a.H, sh, ta, tb);
     const int col = blockIdx.x * RED_COLS + threadIdx.x;
+    if (a.ex.world > 1 && threadIdx.y == 0) exchange_column_sums(a.ex, a.H, col, col < a.H, ta, tb);
     if (threadIdx.y == 0 && col < a.H) {
         sums_out[col] = ta;
         sums_out[a.H + col] = tb;
@@ -463,14 +517,18 @@ __global__ void bn_bwd_reduce_kernel(const float* __restrict__ pg, const float* 
     double s1, s2;
     reduce_partials_2(pg, pgz, P, a.H, a.H, sh, s1, s2);
     const int col = blockIdx.x * RED_COLS + threadIdx.x;
+    double sum_dy = 0.0, sum_dyz = 0.0;
     if (threadIdx.y == 0 && col < a.H) {
         const double ik = static_cast<double>(a.inv_keep);
-        const double sum_dy = ik * s1;
-        const double sum_dyz = ik * static_cast<double>(a.rstd[col]) * (s2 - static_cast<double>(a.mean_z[col]) * s1);
+        sum_dy = ik * s1;
+        sum_dyz = ik * static_cast<double>(a.rstd[col]) * (s2 - static_cast<double>(a.mean_z[col]) * s1);
+        dbeta[col] = static_cast<float>(sum_dy);                            // parameter gradients: LOCAL sums
+        dgamma[col] = static_cast<float>(sum_dyz);
+    }
+    if (FUSED && a.ex.world > 1 && threadIdx.y == 0) exchange_column_sums(a.ex, a.H, col, col < a.H, sum_dy, sum_dyz);
+    if (threadIdx.y == 0 && col < a.H) {
         sums_out[col] = sum_dy;
         sums_out[a.H + col] = sum_dyz;
-        dbeta[col] = static_cast<float>(sum_dy);
-        dgamma[col] = static_cast<float>(sum_dyz);
         if (FUSED) bn_bwd_coefficients(a, col, sum_dy, sum_dyz);
     }
 }

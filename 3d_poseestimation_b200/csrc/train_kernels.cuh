@@ -18,7 +18,20 @@ int reduce_rows_f64(const float* a, const float* b, int P, int n, int ld, double
 // out[j] = sum_p a[p * ld + j] written as fp32 (bias gradients)
 int reduce_rows_f32(const float* a, int P, int n, int ld, float* out, cudaStream_t st);
 
+// Synchronised BatchNorm over the GPUs of one box WITHOUT a collective call: every rank stores its local column sums
+// into its slot of every peer's symmetric buffer (NVLink P2P stores, each value tagged with the step's epoch), polls
+// its own buffer for the peers' values and adds the slots in rank order -- identical, deterministic sums on every
+// rank after one NVLink store latency, inside the BatchNorm finalize kernel (include/lifter_b200.h: lifter_dp_t).
+constexpr int DP_MAX_WORLD = 8;
+struct SyncExchange {
+    int world = 1, rank = 0;           // world == 1: no exchange
+    int site = 0, nsites = 1;          // which of the step's exchange points this is (forward l, backward l)
+    void* data[DP_MAX_WORLD];          // peer p's buffer: [2 parities][nsites][world slots][2][H] 16-byte LL words
+    const unsigned* epoch;             // device: the step counter (lifter_step_state_t.adam_step), >= 1
+};
+
 struct BnFwdFinalize {
+    SyncExchange ex;
     const double* sums;        // [2][H] (sum z, sum z^2) over the GLOBAL batch; unused when bn_mode != 0
     double count;              // global batch rows
     const float* bias; const float* gamma; const float* beta;
@@ -49,6 +62,7 @@ struct BwdCommon {
 int bwd_stats(const BwdCommon& c, float* psum_g, float* psum_gz, cudaStream_t st);
 
 struct BnBwdFinalize {
+    SyncExchange ex;
     const double* sums;        // [2][H] (sum dy, sum dy*zhat) over the GLOBAL batch (bn_finalize_bwd only)
     double count;
     const float* gamma; const float* rstd; const float* mean_z;

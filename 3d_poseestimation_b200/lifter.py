@@ -142,6 +142,21 @@ class LinearModel(torch.nn.Module):
         self._flat, self._rm, self._rv, self._nbt = flat, rm, rv, nbt
         self._cache = {}
 
+    def _adopt_storage(self, flat, operands=None, fmt=None):
+        """Move the flat parameter buffer (and the operand copy of format ``fmt``) into caller-provided device
+        storage of the same size -- the data-parallel trainer places them in NVLink symmetric memory so that the
+        fused optimiser kernel of a peer GPU can write them."""
+        assert flat.numel() == self._flat.numel() and flat.dtype == torch.float32 and flat.device == self._flat.device
+        with torch.no_grad():
+            flat.copy_(self._flat)
+            for p, (off, n) in zip(self._ordered_params(), self._offsets):
+                p.data = flat[off:off + n].view(p.shape)
+        self._flat = flat
+        self._cache = {}
+        if operands is not None:
+            self._cache[("op", fmt)] = (None, operands)          # stale version: the next _operands() packs into it
+            self._operands(fmt)
+
     def _apply(self, fn, *args, **kwargs):
         super()._apply(fn, *args, **kwargs)
         self._flatten()                       # .to(device) / .cuda() / .float(): rebuild the flat views

@@ -10,6 +10,7 @@ The reference reads ``loss.cpu().item()`` every step (train_1.py:98); here the l
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -68,8 +69,65 @@ class LifterTrainer:
         self.state = torch.zeros(8, dtype=torch.int32, device=dev)
         self.state.view(torch.float32)[2] = self.lr
         self.use_graph = bool(use_graph)
+        # data parallel: capture the NCCL gradient all-reduce into the step graph too (LIFTER_DP_GRAPH=0 turns it off)
+        self.graph_collectives = os.environ.get("LIFTER_DP_GRAPH", "1") != "0"
         self._state_stale = False
+        self._sym = None
+        self._dp_adam = False
+        if self.world > 1:
+            self._setup_symmetric(dev)
         self._graphs = {}
+
+    # ------------------------------------------------------------------ data parallel: NVLink symmetric memory
+    def _setup_symmetric(self, dev):
+        """Symmetric (peer-mapped) buffer for the in-kernel SyncBN exchange; falls back to NCCL all-reduces of the
+        BatchNorm sums if symmetric memory is unavailable (more than 8 ranks, no P2P)."""
+        import torch.distributed as dist
+        model = self.model
+        model._dp = None
+        if self.world > _cabi.DP_MAX_WORLD:
+            return
+        lib, cfg = _cabi.lib(), C.byref(model._cfg)
+        fmt = model._fmt_code(model.train_format)
+        n = model._flat.numel()
+
+        def up(v):
+            return (v + 255) // 256 * 256
+        sync_b = up(_cabi.check(lib.lifter_dp_sync_bytes(cfg, self.world)))
+        op_b = up(lib.lifter_operand_bytes(cfg))
+        off_flags = sync_b
+        off_grad = off_flags + _cabi.DP_FLAG_BYTES
+        off_par = off_grad + up(4 * n)
+        off_ops = off_par + up(4 * n)
+        total = off_ops + op_b
+        try:
+            import torch.distributed._symmetric_memory as symm
+            buf = symm.empty(total, dtype=torch.uint8, device=dev)
+            buf.zero_()
+            hdl = symm.rendezvous(buf, self.pg)
+            torch.cuda.synchronize()
+            dist.barrier(group=self.pg)                          # every rank's buffer is zeroed before first use
+        except Exception as e:                                   # noqa: BLE001 -- plumbing fallback, kernels unchanged
+            import warnings
+            warnings.warn(f"symmetric memory unavailable ({e}); BatchNorm sums and gradients go through NCCL")
+            return
+        dp = _cabi.DpInfo()
+        dp.world, dp.rank = self.world, self.rank
+        for p in range(self.world):
+            base = int(hdl.buffer_ptrs[p])
+            dp.sync[p] = base
+            dp.flags[p] = base + off_flags
+            dp.grad[p] = base + off_grad
+            dp.params[p] = base + off_par
+            dp.operands[p] = base + off_ops
+        self._sym, self._sym_hdl = buf, hdl
+        # gradients, parameters and the training operand copy live in the symmetric buffer from now on
+        self.grad = buf[off_grad:off_grad + 4 * n].view(torch.float32)
+        model._adopt_storage(buf[off_par:off_par + 4 * n].view(torch.float32), buf[off_ops:off_ops + op_b], fmt)
+        torch.cuda.synchronize()
+        dist.barrier(group=self.pg)
+        model._dp = dp
+        self._dp_adam = os.environ.get("LIFTER_DP_NCCL_GRADS") != "1"      # (env: fall back to NCCL all-reduce + Adam)
 
     # ------------------------------------------------------------------ buffers sized by the batch
     def _buffers(self, B, dev):
@@ -114,10 +172,17 @@ class LifterTrainer:
                                     _cabi.ptr(self.metric_std), _cabi.ptr(b["dpred"]), _cabi.ptr(b["lscratch"]),
                                     _cabi.ptr(self.loss_out), int(accumulate_metric), st))
         _autograd.run_backward(model, t, b["dpred"], self.grad, None, scratch=b["scratch"])
+        ops = model._operands(fmt)
+        if self._dp_adam:
+            # data parallel: reduce-scatter of the gradients + Adam + all-gather of the parameters in ONE kernel over
+            # NVLink peer memory (sum of shard gradients = gradient of the global batch)
+            _cabi.check(lib.lifter_dp_adam_step(cfg, C.byref(model._dp), _cabi.ptr(self.m), _cabi.ptr(self.v),
+                                                self.betas[0], self.betas[1], self.eps, self.weight_decay,
+                                                int(self.decoupled), 1.0, _cabi.ptr(state), fmt, st))
+            return
         if self.world > 1:
             import torch.distributed as dist
             dist.all_reduce(self.grad, group=self.pg)             # sum of shard gradients = global-batch gradient
-        ops = model._operands(fmt)
         # Adam / AdamW over the flat buffer; the same pass rewrites the 16-bit operand copies of the weights
         _cabi.check(lib.lifter_adam_step_packed(cfg, _cabi.ptr(model._flat), _cabi.ptr(self.grad), _cabi.ptr(self.m),
                                                 _cabi.ptr(self.v), self.lr, self.betas[0], self.betas[1], self.eps,
@@ -144,9 +209,17 @@ class LifterTrainer:
         x, y = self._check_xy(x, y)
         B = x.shape[0]
         model.train()
-        if self.use_graph and self.world == 1 and B >= 2:
+        if self.use_graph and B >= 2 and (self.world == 1 or self.graph_collectives):
             return self._step_graph(x, y, bool(accumulate_metric))
         b = self._buffers(B, x.device)
+        if self.world > 1 and self.use_graph and B >= 2:
+            # data parallel: same kernel sequence driven by the device step state (it is also the epoch of the
+            # in-kernel BatchNorm exchange); launched eagerly because of the NCCL gradient all-reduce in the middle
+            if self._state_stale:
+                self._sync_state()
+            self._enqueue(x, y, b, accumulate_metric, self.state)
+            self._after_step()
+            return self.loss_out[0]
         self._enqueue(x, y, b, accumulate_metric, None)
         self._after_step()
         self._state_stale = True                                  # the device step state did not see this step

@@ -96,6 +96,25 @@ typedef struct lifter_step_state {
     float reserved[2];
 } lifter_step_state_t;
 
+/* Data parallelism inside one NVSwitch box without collective calls on the critical path: `sync` is a symmetric
+ * buffer (same size on every rank, peer-mapped over NVLink, e.g. torch.distributed._symmetric_memory) of
+ * lifter_dp_sync_bytes() bytes, zeroed once; sync[p] is rank p's copy as seen from this rank.  The BatchNorm
+ * finalize kernels exchange their column sums through it (forward and backward of every layer).  Needs
+ * step_state (its adam_step is the exchange epoch) and the single-call lifter_train_forward / _backward.      */
+#define LIFTER_DP_MAX_WORLD 8
+typedef struct lifter_dp {
+    int32_t world, rank;
+    void* sync[LIFTER_DP_MAX_WORLD];       /* BatchNorm exchange region, lifter_dp_sync_bytes()                      */
+    /* lifter_dp_adam_step only (else NULL): every rank's flat gradient, flat parameters, 16-bit operand copies and a
+     * zeroed flag block of LIFTER_DP_FLAG_BYTES, all inside symmetric (peer-mapped) memory                           */
+    void* grad[LIFTER_DP_MAX_WORLD];
+    void* params[LIFTER_DP_MAX_WORLD];
+    void* operands[LIFTER_DP_MAX_WORLD];
+    void* flags[LIFTER_DP_MAX_WORLD];
+} lifter_dp_t;
+#define LIFTER_DP_FLAG_BYTES 256
+int64_t lifter_dp_sync_bytes(const struct lifter_config* cfg, int world);
+
 typedef struct lifter_train_ctx {
     const float* params;            /* flat fp32 parameters                                              */
     const void* operands;           /* 16-bit operand copies in `fmt` (lifter_pack_weights)              */
@@ -119,6 +138,7 @@ typedef struct lifter_train_ctx {
     void* scratch; int64_t scratch_bytes;      /* backward: lifter_train_scratch_bytes()                  */
     const struct lifter_step_state* step_state; /* nullable, DEVICE memory: the dropout step is read from it at run
                                                   time instead of `step` (a captured CUDA graph replays every step) */
+    const lifter_dp_t* dp;          /* nullable: in-kernel synchronised BatchNorm over dp->world GPUs (host struct)   */
 } lifter_train_ctx_t;
 
 int64_t lifter_train_saved_bytes(const lifter_config_t* cfg, int64_t batch);
@@ -165,6 +185,14 @@ int lifter_step_advance(lifter_step_state_t* state, float beta1, float beta2, fl
 int lifter_adam_step_packed(const lifter_config_t* cfg, float* p, const float* g, float* m, float* v, float lr,
                             float beta1, float beta2, float eps, float weight_decay, int decoupled, int step,
                             float grad_scale, const lifter_step_state_t* state, void* operands, int fmt, void* stream);
+
+/* Data-parallel optimiser step as ONE kernel over NVLink peer memory (replaces gradient all-reduce + Adam): rank r
+ * sums slice r of every rank's gradient with P2P loads (rank order: deterministic), runs Adam/AdamW on that slice
+ * (m, v: only slice r is touched on rank r) and stores the new parameters and operand copies into every rank's
+ * buffers; flag barriers inside the kernel order it against the peers' backward and next forward.                 */
+int lifter_dp_adam_step(const lifter_config_t* cfg, const lifter_dp_t* dp, float* m, float* v, float beta1, float beta2,
+                        float eps, float weight_decay, int decoupled, float grad_scale,
+                        const lifter_step_state_t* state, int fmt, void* stream);
 
 /* ---- test hook: one tcgen05 GEMM  D[M][N] = sum_k A(m,k) B(n,k) ------------------------------------ */
 typedef struct lifter_gemm_desc {

@@ -1,0 +1,61 @@
+"""torchrun worker: data-parallel training steps (in-kernel SyncBN over symmetric memory + gradient all-reduce)
+must reproduce the single-process run on the concatenated global batch.  Launched by tests/test_dp_gpu.py."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    pkg = importlib.import_module("3d_poseestimation_b200")
+    trainer = importlib.import_module("3d_poseestimation_b200.trainer")
+    H, S, B, steps = 256, 1, 512, 6                                   # B rows per rank
+    rs = np.random.RandomState(0)
+    xg = torch.from_numpy(rs.normal(0, 1, (steps, world * B, 34)).astype(np.float32))
+    yg = torch.from_numpy(rs.normal(0, 1, (steps, world * B, 51)).astype(np.float32))
+
+    def build():
+        torch.manual_seed(3)
+        return pkg.LinearModel(34, 51, linear_size=H, num_stage=S, p_dropout=0.5, BN=True).to(dev)
+    # single process on the global batch (every rank computes it: cheap, and no cross-rank transfer of the answer)
+    ref = build()
+    tr_ref = trainer.LifterTrainer(ref, lr=1e-3, loss="mse", optimizer="adam", seed=5)
+    ref_losses = [float(tr_ref.step(xg[s].to(dev), yg[s].to(dev)).item()) for s in range(steps)]
+    # data parallel
+    m = build()
+    tr = trainer.LifterTrainer(m, lr=1e-3, loss="mse", optimizer="adam", seed=5, world_size=world, rank=rank)
+    assert (m._dp is not None) == (world > 1), "symmetric-memory SyncBN exchange was not set up"
+    losses = []
+    for s in range(steps):
+        tr.step(xg[s, rank * B:(rank + 1) * B].to(dev), yg[s, rank * B:(rank + 1) * B].to(dev))
+        losses.append(tr.loss_value())
+    torch.cuda.synchronize()
+    err = max(abs(a - b) / abs(b) for a, b in zip(losses, ref_losses))
+    pd = (m._flat - ref._flat).norm().item() / ref._flat.norm().item()
+    rm = (m._rm - ref._rm).abs().max().item()
+    # identical parameters on every rank (deterministic exchange + all-reduce)
+    mine = m._flat.clone()
+    other = mine.clone()
+    dist.broadcast(other, src=0)
+    same = bool(torch.equal(mine, other))
+    print(f"[rank {rank}] loss rel err {err:.2e}  param rel diff {pd:.2e}  running_mean diff {rm:.2e}  "
+          f"replicas identical {same}", flush=True)
+    ok = err < 2e-3 and pd < 2e-3 and rm < 1e-3 and same
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
