@@ -3,6 +3,10 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload train|eval] [--impl ours|reference]
 
+The default workload is BASELINE.json's metric, "lifted poses/sec (fwd+bwd)": the data-parallel training step of
+configs[2] (8,192 poses per GPU); with one GPU the line also carries an ``inference`` object with the eval-mode
+numbers of configs[1] (65,536 poses).  ``--workload eval`` makes configs[1] the headline instead.
+
 * ``value``  : lifted poses/s over all ranks, inputs resident in HBM, CUDA-event time, max over ranks.
 * ``e2e``    : the same metric through the public module API with HOST (pinned) inputs: H2D copy of the
                step's keypoints, the step, D2H of the step's result -- all inside the timed region.
@@ -145,7 +149,6 @@ def cpu_arm(workload, steps, warmup, budget_s=25.0):
 
 # ------------------------------------------------------------------------------------------------ GPU arm
 def gpu_arm(args, rank, world, local_rank):
-    import numpy as np
     import torch
     import torch.distributed as dist
 
@@ -156,125 +159,140 @@ def gpu_arm(args, rank, world, local_rank):
     cabi.check(cabi.lib().lifter_device_check())
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    pk = peaks()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    torch.manual_seed(1)
-    model = pkg.LinearModel(I_DIM, O_DIM, linear_size=H, num_stage=S, p_dropout=0.5, BN=True).to(dev)
-    workload = args.workload
-    flop_per_pose = FLOP_PER_POSE_INFER if workload == "eval" else FLOP_PER_POSE_TRAIN
-    pk = peaks()
+    def measure(workload, steps, warmup, with_clocks):
+        """One workload on this rank's GPU: device-resident throughput, end-to-end throughput, dominant kernel."""
+        torch.manual_seed(1)
+        model = pkg.LinearModel(I_DIM, O_DIM, linear_size=H, num_stage=S, p_dropout=0.5, BN=True).to(dev)
+        if workload == "eval":
+            batch = EVAL_BATCH
+            model.eval()
+            xh, _ = synth_batch(batch, rank)
+            xh = xh.pin_memory()
+            xd = xh.to(dev)
+            out = torch.empty(batch, O_DIM, device=dev)
+            outh = torch.empty(batch, O_DIM).pin_memory()
+            launches_per_step = 1 + (1 + 2 * S + 1)           # prep_input + one GEMM per Linear (65,536 rows = one chunk)
 
-    if workload == "eval":
-        batch = EVAL_BATCH
-        model.eval()
-        xh, _ = synth_batch(batch, rank)
-        xh = xh.pin_memory()
-        xd = xh.to(dev)
-        out = torch.empty(batch, O_DIM, device=dev)
-        outh = torch.empty(batch, O_DIM).pin_memory()
-        chunks = 1                                        # 65,536 rows fit one chunk (csrc/lifter_api.cu)
-        launches_per_step = 1 + chunks * (1 + 2 * S + 2)
+            def step():
+                model.infer(xd, out=out)
 
-        def step():
-            model.infer(xd, out=out)
+            def step_e2e():
+                x = xh.to(dev, non_blocking=True)
+                o = model.infer(x, out=out)
+                outh.copy_(o, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+            h2d, d2h = xh.numel() * 4, outh.numel() * 4
+            dtype = "fp16 operands, fp32 accumulate"
+            cfg = {"workload": f"configs[1]: eval-mode inference, batch {batch} synthetic H36M 2D poses per GPU "
+                               f"(17x2 -> 17x3, 1024-wide, 2 residual blocks)", "batch_per_gpu": batch,
+                   "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
+                   "l2": "activations of one step (3 x 134 MB) exceed the 126 MB L2; no flush needed"}
+            flop = FLOP_PER_POSE_INFER
+        else:
+            trainer_mod = importlib.import_module(PKG + ".trainer")
+            batch = TRAIN_BATCH
+            tr = trainer_mod.LifterTrainer(model, lr=1e-4, loss="mse", optimizer="adam", world_size=world, rank=rank,
+                                           seed=2)
+            xh, yh = synth_batch(batch, rank)
+            xh, yh = xh.pin_memory(), yh.pin_memory()
+            xd, yd = xh.to(dev), yh.to(dev)
+            launches_per_step = tr.launches_per_step(batch)
 
-        def step_e2e():
-            x = xh.to(dev, non_blocking=True)
-            o = model.infer(x, out=out)
-            outh.copy_(o, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-        h2d, d2h = xh.numel() * 4, outh.numel() * 4
-        dtype = "fp16 operands, fp32 accumulate"
-        cfg = {"workload": f"configs[1]: eval-mode inference, batch {batch} synthetic H36M 2D poses per GPU "
-                           f"(17x2 -> 17x3, 1024-wide, 2 residual blocks)", "batch_per_gpu": batch,
-               "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
-               "l2": "activations of one step (3 x 134 MB) exceed the 126 MB L2; no flush needed"}
-    else:
-        trainer_mod = importlib.import_module(PKG + ".trainer")
-        batch = TRAIN_BATCH
-        tr = trainer_mod.LifterTrainer(model, lr=1e-4, loss="mse", optimizer="adam", world_size=world, rank=rank,
-                                       seed=2)
-        xh, yh = synth_batch(batch, rank)
-        xh, yh = xh.pin_memory(), yh.pin_memory()
-        xd, yd = xh.to(dev), yh.to(dev)
-        launches_per_step = tr.launches_per_step(batch)
-        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+            def step():
+                tr.step(xd, yd)
 
-        def step():
-            tr.step(xd, yd)
+            def step_e2e():
+                x = xh.to(dev, non_blocking=True)
+                y = yh.to(dev, non_blocking=True)
+                tr.step(x, y)
+                tr.loss_value()                    # D2H read of the step's loss (synchronises)
+            h2d, d2h = (xh.numel() + yh.numel()) * 4, 4
+            dtype = "bf16 operands, fp32 accumulate/master weights"
+            par = f"dp{world}"
+            if world > 1:
+                par += (" (in-kernel SyncBN exchange + fused reduce-scatter/Adam/all-gather over NVLink symmetric memory)"
+                        if tr._dp_adam else " (NCCL all-reduce fallback)")
+            cfg = {"workload": f"configs[2]: training step fwd + MSE + bwd + Adam, dropout 0.5, batch {batch}/GPU, "
+                               f"synced BatchNorm, 1024-wide, 2 residual blocks", "batch_per_gpu": batch,
+                   "global_batch": batch * world, "parallelism": par,
+                   "cuda_graph": bool(tr.use_graph),
+                   "l2": "one step touches ~0.4 GB of saved activations and gradients per GPU (> 126 MB L2), so "
+                         "consecutive steps do not find their inputs in L2; no explicit flush"}
+            flop = FLOP_PER_POSE_TRAIN
 
-        def step_e2e():
-            x = xh.to(dev, non_blocking=True)
-            y = yh.to(dev, non_blocking=True)
-            tr.step(x, y)
-            tr.loss_value()                    # D2H read of the step's loss (synchronises)
-        h2d, d2h = (xh.numel() + yh.numel()) * 4, 4
-        dtype = "bf16 operands, fp32 accumulate/master weights"
-        cfg = {"workload": f"configs[2]: training step fwd + MSE + bwd + Adam, dropout 0.5, batch {batch}/GPU, "
-                           f"synced BatchNorm, 1024-wide, 2 residual blocks", "batch_per_gpu": batch,
-               "global_batch": batch * world, "parallelism": f"dp{world}",
-               "l2": "256 MB flush buffer written between timed steps would perturb the device clock less than "
-                     "the working set itself: one step touches ~0.4 GB of activations (> 126 MB L2)"}
+        def timed(fn, steps, warmup):
+            for _ in range(warmup):
+                fn()
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                fn()
+            e1.record()
+            barrier()
+            ms = e0.elapsed_time(e1) / steps
+            if world > 1:
+                t = torch.tensor([ms], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = t.item()
+            return ms
 
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            fn()
+        step()                                                 # builds buffers / captures the step graph untimed
         barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            fn()
-        e1.record()
+        if with_clocks:
+            with ClockSampler(local_rank) as clk:
+                ms = timed(step, steps, warmup)
+            clocks = clk.summary()
+        else:
+            ms, clocks = timed(step, steps, warmup), None
+
+        # end to end through the public API with host buffers (wall clock around synchronising steps)
+        for _ in range(max(1, warmup // 2)):
+            step_e2e()
         barrier()
-        ms = e0.elapsed_time(e1) / steps
+        t0 = time.perf_counter()
+        n_e2e = max(3, steps // 2)
+        for _ in range(n_e2e):
+            step_e2e()
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) / n_e2e * 1e3
         if world > 1:
-            t = torch.tensor([ms], device=dev)
+            t = torch.tensor([e2e_ms], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = t.item()
-        return ms
+            e2e_ms = t.item()
 
-    with ClockSampler(local_rank) as clk:
-        ms = timed(step, args.steps, args.warmup)
-    clocks = clk.summary()
+        roof = None
+        if rank == 0:   # dominant kernel alone: the H x H tcgen05 GEMM at this workload's per-launch shape
+            roof = gemm_roofline(cabi, dev, batch, cabi.FMT_F16 if workload == "eval" else cabi.FMT_BF16, pk)
+        value = batch * world / (ms / 1e3)
+        return {"metric": "lifted poses/sec" + (" (eval inference)" if workload == "eval" else " (fwd+bwd+Adam)"),
+                "value": value, "unit": "poses/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype,
+                "data": "synthetic (H36M-shaped keypoints from the repo's mean/std statistics, random-init weights)",
+                "config": cfg, "clocks": clocks,
+                "e2e": {"value": batch * world / (e2e_ms / 1e3), "unit": "poses/s", "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
+                "gpu_launches": launches_per_step * steps,
+                "model_flop_per_pose": flop,
+                "model_tflops": value * flop / 1e12 / world,
+                "roofline": roof}
 
-    # end to end through the public API with host buffers (wall clock around synchronising steps)
-    for _ in range(max(1, args.warmup // 2)):
-        step_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    n_e2e = max(3, args.steps // 2)
-    for _ in range(n_e2e):
-        step_e2e()
-    barrier()
-    e2e_ms = (time.perf_counter() - t0) / n_e2e * 1e3
-    if world > 1:
-        t = torch.tensor([e2e_ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = t.item()
-
-    # dominant kernel alone: the H x H tcgen05 GEMM at this workload's per-launch shape
-    roof = None
+    line = measure(args.workload, args.steps, args.warmup, True)
+    if args.workload == "train" and world == 1:
+        # the same lifter in eval mode (BASELINE.json configs[1]), reported beside the headline training number
+        inf = measure("eval", args.steps, args.warmup, False)
+        line["inference"] = {k: inf[k] for k in ("metric", "value", "unit", "ms_per_step", "dtype", "e2e", "roofline",
+                                                 "model_tflops")}
+        line["inference"]["workload"] = inf["config"]["workload"]
     if rank == 0:
-        roof = gemm_roofline(cabi, dev, batch, cabi.FMT_F16 if workload == "eval" else cabi.FMT_BF16, pk)
-
-    value = batch * world / (ms / 1e3)
-    line = {"metric": "lifted poses/sec" + (" (eval inference)" if workload == "eval" else " (fwd+bwd+Adam)"),
-            "value": value, "unit": "poses/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype,
-            "data": "synthetic (H36M-shaped keypoints from the repo's mean/std statistics, random-init weights)",
-            "config": cfg, "clocks": clocks,
-            "e2e": {"value": batch * world / (e2e_ms / 1e3), "unit": "poses/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
-            "gpu_launches": launches_per_step * args.steps,
-            "model_flop_per_pose": flop_per_pose,
-            "model_tflops": value * flop_per_pose / 1e12 / world}
-    if rank == 0:
-        line["roofline"] = roof
-        line["cpu_baseline"] = cpu_arm(workload, steps=8, warmup=1)
+        line["cpu_baseline"] = cpu_arm(args.workload, steps=8, warmup=1)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -324,7 +342,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("LIFTER_BENCH_WORKLOAD", "eval"), choices=["train", "eval"])
+    ap.add_argument("--workload", default=os.environ.get("LIFTER_BENCH_WORKLOAD", "train"), choices=["train", "eval"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
