@@ -51,6 +51,14 @@ class TrainCtx(C.Structure):
                 ("scratch_bytes", C.c_int64), ("step_state", C.c_void_p), ("dp", C.POINTER(DpInfo))]
 
 
+class PoseLossDesc(C.Structure):
+    """``lifter_pose_loss_t``"""
+    _fields_ = [("pred", C.c_void_p), ("target", C.c_void_p), ("mean", C.c_void_p), ("stdv", C.c_void_p),
+                ("root", C.c_void_p), ("intrinsics", C.c_void_p), ("target2d", C.c_void_p), ("rows", C.c_int64),
+                ("global_rows", C.c_int64), ("joints", C.c_int32), ("w_mpjpe", C.c_float), ("w_reproj", C.c_float),
+                ("w_bone", C.c_float), ("dpred", C.c_void_p), ("scratch", C.c_void_p), ("out", C.c_void_p)]
+
+
 LOSS_MSE, LOSS_L1, LOSS_MPJPE = 0, 1, 2
 DP_MAX_WORLD = 8
 DP_FLAG_BYTES = 256
@@ -87,6 +95,10 @@ SIGNATURES = {
     "lifter_train_backward": (_I32, [_CFG, _CTX, _P]),
     "lifter_loss_scratch_bytes": (_I64, [_I64, _I32]),
     "lifter_loss": (_I32, [_P, _P, _I64, _I32, _I32, _I64, _P, _P, _P, _P, _I32, _P]),
+    "lifter_flip_pose": (_I32, [_P, _P, _I64, _I32, _I32, _I32, _P]),
+    "lifter_affine_cols": (_I32, [_P, _P, _I64, _I32, _P, _P, _I32, _P]),
+    "lifter_pose_loss_scratch_bytes": (_I64, [_I64, _I32]),
+    "lifter_pose_loss": (_I32, [C.POINTER(PoseLossDesc), _P]),
     "lifter_l1_sum": (_I32, [_P, _P, _I64, _I32, _I32, _F, _P, _P, _P]),
     "lifter_l1_grad": (_I32, [_P, _P, _I64, _I32, _I32, _P, _F, _P, _P, _P]),
     "lifter_adam_step": (_I32, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _I32, _F, _P]),

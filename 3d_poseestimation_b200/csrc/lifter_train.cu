@@ -16,6 +16,7 @@
 #include "gemm_sm100.cuh"
 #include "layout.cuh"
 #include "loss_adam.cuh"
+#include "pose_ops.cuh"
 #include "train_kernels.cuh"
 
 using namespace lifter;
@@ -479,6 +480,33 @@ int lifter_loss(const float* pred, const float* target, int64_t rows, int joints
     LIFTER_REQUIRE(pred && target && scratch && out, "loss: null pointer");
     return fused_loss(pred, target, rows, joints, kind, static_cast<double>(global_rows), stdv, dpred, scratch, out,
                       accumulate_metric, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_flip_pose(const float* in, float* out, int64_t poses, int joints, int dims, int grad, void* stream) {
+    LIFTER_REQUIRE(in && out, "flip_pose: null pointer");
+    return flip_pose(in, out, poses, joints, dims, grad, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_affine_cols(const float* in, float* out, int64_t rows, int cols, const float* a, const float* b, int mode,
+                       void* stream) {
+    LIFTER_REQUIRE(in && out, "affine_cols: null pointer");
+    return affine_cols(in, out, rows, cols, a, b, mode, static_cast<cudaStream_t>(stream));
+}
+
+int64_t lifter_pose_loss_scratch_bytes(int64_t rows, int joints) {
+    if (rows < 1 || joints < 1) return LIFTER_ERR_INVALID;
+    return static_cast<int64_t>(pose_loss_partial_rows(rows)) * (4 + joints) * 4;
+}
+
+int lifter_pose_loss(const lifter_pose_loss_t* d, void* stream) {
+    LIFTER_REQUIRE(d != nullptr, "pose_loss: null descriptor");
+    PoseLossArgs a;
+    a.pred = d->pred; a.target = d->target; a.mean = d->mean; a.stdv = d->stdv; a.root = d->root;
+    a.intrinsics = d->intrinsics; a.target2d = d->target2d; a.rows = d->rows;
+    a.global_rows = d->global_rows > 0 ? d->global_rows : d->rows; a.J = d->joints;
+    a.w_mpjpe = d->w_mpjpe; a.w_reproj = d->w_reproj; a.w_bone = d->w_bone;
+    a.dpred = d->dpred; a.partials = d->scratch; a.out = d->out;
+    return pose_loss(a, static_cast<cudaStream_t>(stream));
 }
 
 int lifter_l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, float scale, float* scratch,

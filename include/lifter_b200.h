@@ -174,6 +174,33 @@ int lifter_l1_sum(const float* a, const float* b, int64_t n, int row_len, int ce
 int lifter_l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, const float* gscale,
                    float scale, float* da, float* db, void* stream);
 
+/* flip_pose (phase3_direct/my_HybrIK/utils.py:372-396): x -> 1 - x (2D) or -x (3D) and left/right joints swapped;
+ * in/out [poses][17][dims], dims 2 or 3, out != in.  grad = 1: the backward map (no "+1").                    */
+int lifter_flip_pose(const float* in, float* out, int64_t poses, int joints, int dims, int grad, void* stream);
+/* per-column statistics broadcast over rows: mode 0 (x - a) / b (main.py:334,337), 1 x * b + a (main.py:473-479,
+ * train_5.py:42-47), 2 2x - 1 (main.py:331), 3 x * (a - b) + b with a = max, b = min (train_5.py:35-40)        */
+int lifter_affine_cols(const float* in, float* out, int64_t rows, int cols, const float* a, const float* b, int mode,
+                       void* stream);
+/* ONE pass over the predicted and target joints: de-standardisation, mean MPJPE (two2three.py:389-392), per-joint
+ * MPJPE sums (losses.py:3-7), pinhole reprojection L1 against 2D keypoints in pixel/1000 and bone-length L1 over the
+ * 16 edges of the H36M-17 skeleton (utils.py:37,131-172; these two terms have no reference implementation: PARITY
+ * UNPINNED), and d total / d pred.  out[0] = w_mpjpe * out[1] + w_reproj * out[2] +
+ * w_bone * out[3]; out[4 .. 4 + joints) = per-joint sums over the local rows.                                  */
+typedef struct lifter_pose_loss {
+    const float* pred; const float* target;   /* [rows][joints][3]                                          */
+    const float* mean; const float* stdv;     /* [joints*3], nullable: joints = v * std + mean               */
+    const float* root;                        /* [rows][3], nullable: camera-frame root added before projecting */
+    const float* intrinsics;                  /* [rows][4] fx fy cx cy (pixels), nullable: no reprojection    */
+    const float* target2d;                    /* [rows][joints][2] pixel/1000                                */
+    int64_t rows, global_rows; int32_t joints;
+    float w_mpjpe, w_reproj, w_bone;
+    float* dpred;                             /* [rows][joints][3], nullable                                 */
+    float* scratch;                           /* lifter_pose_loss_scratch_bytes()                            */
+    float* out;                               /* [4 + joints]                                                */
+} lifter_pose_loss_t;
+int64_t lifter_pose_loss_scratch_bytes(int64_t rows, int joints);
+int lifter_pose_loss(const lifter_pose_loss_t* desc, void* stream);
+
 /* torch.optim.Adam / AdamW (train_1.py:39) over the flat buffer; step is 1-based; n %% 4 == 0.           */
 int lifter_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                      float eps, float weight_decay, int decoupled, int step, float grad_scale, void* stream);
