@@ -37,6 +37,8 @@ FLOP_PER_POSE_TRAIN = 25_618_432         # fwd + bwd (no input gradient)
 I_DIM, O_DIM, H, S = 34, 51, 1024, 2
 EVAL_BATCH = 65536                       # BASELINE.json configs[1]
 TRAIN_BATCH = 8192                       # BASELINE.json configs[2], per GPU
+WIDE = (16 * 34, 2048, 4)                # BASELINE.json configs[4]: i_dim, linear_size, num_stage
+FLOP_PER_POSE_WIDE_TRAIN = 206_409_728
 
 
 def peaks():
@@ -109,6 +111,7 @@ def cpu_arm(workload, steps, warmup, budget_s=25.0):
     from oracle.philox import dropout_keep_mask
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    I_DIM, H, S = WIDE if workload == "wide" else (globals()["I_DIM"], globals()["H"], globals()["S"])
     params, buffers = lo.numpy_init(I_DIM, O_DIM, H, S, seed=1, randomize_bn=False)
     if workload == "eval":
         batch = 8192                                            # bounded sample of the 65,536-pose workload
@@ -121,6 +124,8 @@ def cpu_arm(workload, steps, warmup, budget_s=25.0):
     else:
         batch = 512                                             # bounded sample of the 8,192-pose step
         x, y = synth_batch(batch, 0)
+        if workload == "wide":
+            x = torch.cat([synth_batch(batch, 100 * f)[0] for f in range(16)], dim=1).contiguous()
         masks = [dropout_keep_mask(batch, H, s, 0, 2, 0.5) for s in range(2 * S + 1)]
         m = {k: torch.zeros_like(v) for k, v in params.items()}
         v = {k: torch.zeros_like(w) for k, w in params.items()}
@@ -196,11 +201,16 @@ def gpu_arm(args, rank, world, local_rank):
                    "l2": "activations of one step (3 x 134 MB) exceed the 126 MB L2; no flush needed"}
             flop = FLOP_PER_POSE_INFER
         else:
+            if workload == "wide":            # BASELINE.json configs[4]: 16-frame window in, 2048 wide, 4 blocks
+                model = pkg.LinearModel(WIDE[0], O_DIM, linear_size=WIDE[1], num_stage=WIDE[2], p_dropout=0.5,
+                                        BN=True).to(dev)
             trainer_mod = importlib.import_module(PKG + ".trainer")
             batch = TRAIN_BATCH
             tr = trainer_mod.LifterTrainer(model, lr=1e-4, loss="mse", optimizer="adam", world_size=world, rank=rank,
                                            seed=2)
             xh, yh = synth_batch(batch, rank)
+            if workload == "wide":            # 16 iid frames concatenated
+                xh = torch.cat([synth_batch(batch, 100 * f + rank)[0] for f in range(16)], dim=1).contiguous()
             xh, yh = xh.pin_memory(), yh.pin_memory()
             xd, yd = xh.to(dev), yh.to(dev)
             launches_per_step = tr.launches_per_step(batch)
@@ -219,13 +229,15 @@ def gpu_arm(args, rank, world, local_rank):
             if world > 1:
                 par += (" (in-kernel SyncBN exchange + fused reduce-scatter/Adam/all-gather over NVLink symmetric memory)"
                         if tr._dp_adam else " (NCCL all-reduce fallback)")
-            cfg = {"workload": f"configs[2]: training step fwd + MSE + bwd + Adam, dropout 0.5, batch {batch}/GPU, "
-                               f"synced BatchNorm, 1024-wide, 2 residual blocks", "batch_per_gpu": batch,
+            shape = "1024-wide, 2 residual blocks" if workload == "train" else \
+                "widened lifter (16 x 34 inputs, 2048-wide, 4 residual blocks; configs[4])"
+            cfg = {"workload": f"configs[{2 if workload == 'train' else 4}]: training step fwd + MSE + bwd + Adam, dropout 0.5, batch {batch}/GPU, "
+                               f"synced BatchNorm, {shape}", "batch_per_gpu": batch,
                    "global_batch": batch * world, "parallelism": par,
                    "cuda_graph": bool(tr.use_graph),
                    "l2": "one step touches ~0.4 GB of saved activations and gradients per GPU (> 126 MB L2), so "
                          "consecutive steps do not find their inputs in L2; no explicit flush"}
-            flop = FLOP_PER_POSE_TRAIN
+            flop = FLOP_PER_POSE_TRAIN if workload == "train" else FLOP_PER_POSE_WIDE_TRAIN
 
         def timed(fn, steps, warmup):
             for _ in range(warmup):
@@ -270,7 +282,8 @@ def gpu_arm(args, rank, world, local_rank):
 
         roof = None
         if rank == 0:   # dominant kernel alone: the H x H tcgen05 GEMM at this workload's per-launch shape
-            roof = gemm_roofline(cabi, dev, batch, cabi.FMT_F16 if workload == "eval" else cabi.FMT_BF16, pk)
+            roof = gemm_roofline(cabi, dev, batch, cabi.FMT_F16 if workload == "eval" else cabi.FMT_BF16, pk,
+                                 WIDE[1] if workload == "wide" else H)
         value = batch * world / (ms / 1e3)
         return {"metric": "lifted poses/sec" + (" (eval inference)" if workload == "eval" else " (fwd+bwd+Adam)"),
                 "value": value, "unit": "poses/s", "n_gpus": world, "steps": steps, "warmup": warmup,
@@ -299,7 +312,7 @@ def gpu_arm(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
-def gemm_roofline(cabi, dev, rows, fmt, pk):
+def gemm_roofline(cabi, dev, rows, fmt, pk, H=H):
     """CUDA-event time of the dominant kernel (rows x 1024 x 1024 tcgen05 GEMM with the fused epilogue)."""
     import ctypes as C
 
@@ -331,7 +344,7 @@ def gemm_roofline(cabi, dev, rows, fmt, pk):
     us = e0.elapsed_time(e1) / n * 1e3
     flops = 2.0 * rows * H * H
     achieved = flops / (us * 1e-6) / 1e12
-    return {"bound": "tensor", "kernel": f"lifter_gemm_kernel<256> M={rows} N=K={H} (+affine+ReLU epilogue)",
+    return {"bound": "tensor", "kernel": f"lifter_gemm_kernel<256, 2-SM> M={rows} N=K={H} (+affine+ReLU epilogue)",
             "achieved": achieved, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"],
             "peak_source": pk["source"] + " burst bf16 (kernel timed alone)", "us_per_launch": us, "traffic": None}
 
@@ -342,7 +355,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("LIFTER_BENCH_WORKLOAD", "train"), choices=["train", "eval"])
+    ap.add_argument("--workload", default=os.environ.get("LIFTER_BENCH_WORKLOAD", "train"), choices=["train", "eval", "wide"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -357,7 +370,8 @@ def main():
                 "value": r["value"], "unit": "poses/s", "n_gpus": args.gpus, "steps": r["steps_timed"], "warmup": args.warmup,
                 "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "fp32", "data": "synthetic (same generator as the GPU arm)",
-                "config": {"workload": ("configs[1] eval inference" if args.workload == "eval" else "configs[2] training step") +
+                "config": {"workload": {"eval": "configs[1] eval inference", "train": "configs[2] training step",
+                                        "wide": "configs[4] widened-lifter training step"}[args.workload] +
                            "; CPU restatement of the reference module on the host cores, bounded sample: " + r["sample"]},
                 "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": r["value"], "unit": "poses/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
