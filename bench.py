@@ -298,14 +298,15 @@ def gpu_arm(args, rank, world, local_rank):
                 "roofline": roof}
 
     line = measure(args.workload, args.steps, args.warmup, True)
-    if args.workload == "train" and world == 1:
+    profiling = bool(os.environ.get("LIFTER_BENCH_NO_CPU"))     # under ncu: skip the untimed extras
+    if args.workload == "train" and world == 1 and not profiling:
         # the same lifter in eval mode (BASELINE.json configs[1]), reported beside the headline training number
         inf = measure("eval", args.steps, args.warmup, False)
         line["inference"] = {k: inf[k] for k in ("metric", "value", "unit", "ms_per_step", "dtype", "e2e", "roofline",
                                                  "model_tflops")}
         line["inference"]["workload"] = inf["config"]["workload"]
     if rank == 0:
-        line["cpu_baseline"] = cpu_arm(args.workload, steps=8, warmup=1)
+        line["cpu_baseline"] = None if profiling else cpu_arm(args.workload, steps=8, warmup=1)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
