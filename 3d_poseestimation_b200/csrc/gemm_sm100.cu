@@ -552,7 +552,8 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    const int max_clusters = num_sms() / CL;                       // a pair shares a TPC: 74 pairs on 148 SMs
+    const int sms = (a.max_ctas > 0 && a.max_ctas < num_sms()) ? a.max_ctas : num_sms();
+    const int max_clusters = sms / CL < 1 ? 1 : sms / CL;                       // a pair shares a TPC: 74 pairs on 148 SMs
     const int clusters = p.num_tiles < max_clusters ? p.num_tiles : max_clusters;
     cfg.gridDim = dim3(clusters * CL);
     cfg.numAttrs = pdl_enabled() ? 2 : 1;

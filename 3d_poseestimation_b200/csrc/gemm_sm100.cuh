@@ -34,6 +34,7 @@ struct GemmArgs {
     unsigned long long* timeline = nullptr;   // debug hook: [grid][32] globaltimer stamps
     const char* tag = nullptr;                // name in the debug trace
     int max_stages = 0;                       // debug hook: cap the operand ring depth (0 = all that fit)
+    int max_ctas = 0;                         // cap the persistent grid (0 = every SM), for kernels meant to run side by side
 };
 
 int gemm_slab_rows(int M);                    // rows of one split-K slab (M rounded up to 128)

@@ -101,7 +101,8 @@ int wgrad_splits(int M, int N, int K) {
 }
 
 struct ScratchWs {                      // backward workspace
-    uint16_t *dO, *G[2], *Gh, *dz;
+    uint16_t *dO, *G[2], *Gh, *dz[2];   // dz alternates by layer: the weight-gradient GEMM of layer l reads dz[l & 1]
+                                        // on the side stream while layer l-1 writes the other one
     float *pA, *pB, *coef, *slabs;
     std::vector<double*> bsums;
     std::vector<size_t> bsums_off;
@@ -115,7 +116,8 @@ void carve_scratch(const Layout& lay, int64_t B, void* base, ScratchWs* w) {
     w->G[0] = c.take<uint16_t>(act);
     w->G[1] = c.take<uint16_t>(act);
     w->Gh = c.take<uint16_t>(act);
-    w->dz = c.take<uint16_t>(act);
+    w->dz[0] = c.take<uint16_t>(act);
+    w->dz[1] = c.take<uint16_t>(act);
     size_t R = ew_partial_rows(B, lay.H);
     const size_t R64 = ew_partial_rows(B, 64);
     size_t pbytes = R * lay.H * 4;
@@ -307,6 +309,36 @@ int lifter_train_forward(const lifter_config_t* cfg, const lifter_train_ctx_t* t
 }
 
 // ---------------------------------------------------------------------------------------------- backward
+// The weight-gradient GEMMs feed nothing but the optimiser, so the whole-backward entry point runs them on a second
+// stream: dW_l overlaps the BatchNorm-backward passes and the data-gradient GEMM of the layers below it.  fork[i] is
+// recorded on the caller's stream once dz of layer i exists, done[i] on the side stream once dW_i is reduced; index L
+// is the output layer.  Works under stream capture (the side stream joins the caller's before the call returns).
+struct SideStream {
+    cudaStream_t st = nullptr;
+    std::vector<cudaEvent_t> fork, done;
+};
+static SideStream* side_stream(int slots) {
+    static SideStream per_device[64];
+    static const bool off = [] { const char* e = getenv("LIFTER_WGRAD_STREAM"); return e != nullptr && e[0] == '0'; }();
+    if (off) return nullptr;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    SideStream* s = &per_device[dev];
+    if (s->st == nullptr && cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    while (static_cast<int>(s->fork.size()) < slots) {
+        cudaEvent_t a, b;
+        if (cudaEventCreateWithFlags(&a, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        if (cudaEventCreateWithFlags(&b, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        s->fork.push_back(a); s->done.push_back(b);
+    }
+    return s;
+}
+static int side_fork(SideStream* s, int slot, cudaStream_t main_st) {
+    LIFTER_CHECK_CUDA(cudaEventRecord(s->fork[slot], main_st));
+    LIFTER_CHECK_CUDA(cudaStreamWaitEvent(s->st, s->fork[slot], 0));
+    return LIFTER_OK;
+}
+
 static int wgrad(const Layout& lay, const lifter_train_ctx_t* t, const ScratchWs& b, const uint16_t* dz, int M, long ldz,
                  const uint16_t* a_in, int N, long lda_in, int rows_valid, int cols_valid, float* grad, cudaStream_t st) {
     const int B = static_cast<int>(t->batch);
@@ -320,7 +352,7 @@ static int wgrad(const Layout& lay, const lifter_train_ctx_t* t, const ScratchWs
     return wgrad_reduce(b.slabs, gemm_effective_splits(B, g.splits), gemm_slab_rows(M), N, rows_valid, cols_valid, grad, st);
 }
 
-int lifter_train_bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream) {
+static int bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream, SideStream* side) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -333,14 +365,19 @@ int lifter_train_bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t*
     LIFTER_PROPAGATE(prep_grad_out(t->grad_out, B, lay.O, lay.Op, t->fmt, b.dO, b.pA, st));
     LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(B, lay.Op), lay.O, lay.Op, t->grad_params + lay.p_off[lay.t_b2()], st));
     // dW2 = dOut^T a_{L-1}
+    if (side != nullptr) LIFTER_PROPAGATE(side_fork(side, lay.L, st));
     LIFTER_PROPAGATE(wgrad(lay, t, b, b.dO, lay.Op, lay.Op, w.a[lay.L - 1], H, H, lay.O, H,
-                           t->grad_params + lay.p_off[lay.t_w2()], st));
+                           t->grad_params + lay.p_off[lay.t_w2()], side != nullptr ? side->st : st));
+    if (side != nullptr) LIFTER_CHECK_CUDA(cudaEventRecord(side->done[lay.L], side->st));
     // gradient of the residual stream at the top: g = dOut W2
     GemmArgs g;
     g.A = b.dO; g.lda = lay.Op; g.B = ops + lay.w_off[lay.L]; g.ldb = H; g.b_mn_major = 1;
     g.M = B; g.N = H; g.K = lay.Op; g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.D = b.G[0]; g.ldd = H;
     g.tag = "gemm_dgrad_top";
     return gemm_launch(g, st);
+}
+int lifter_train_bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream) {
+    return bwd_begin(cfg, t, stream, nullptr);
 }
 
 // which buffer holds the incoming gradient g_l of hidden layer l, given that the stream gradient after
@@ -394,7 +431,8 @@ static int bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t*
                          t->grad_params + lay.p_off[lay.t_gamma(l)], t->grad_params + lay.p_off[lay.t_beta(l)], fused, st);
 }
 
-static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
+static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused,
+                            SideStream* side = nullptr) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
     LIFTER_REQUIRE(l >= 0 && l < lay.L, "backward: layer %d out of range", l);
@@ -416,19 +454,24 @@ static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     c.g = g_in(lay, b, l); c.z = w.z[l]; c.bits = w.bits[l];
     c.rows = t->batch; c.H = H; c.fmt = t->fmt;
     const bool need_bias = f.dbias == nullptr;                     // no BN, or BN on running statistics
-    LIFTER_PROPAGATE(bwd_dz(c, b.coef, b.dz, need_bias ? b.pA : nullptr, st));
+    uint16_t* dz = b.dz[l & 1];
+    if (side != nullptr && l + 2 < lay.L)                          // dW_{l+2} still reads this buffer on the side stream
+        LIFTER_CHECK_CUDA(cudaStreamWaitEvent(st, side->done[l + 2], 0));
+    LIFTER_PROPAGATE(bwd_dz(c, b.coef, dz, need_bias ? b.pA : nullptr, st));
     if (need_bias)
         LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(t->batch, H), H, H, t->grad_params + lay.p_off[lay.t_bias(l)], st));
 
     // dW_l = dz^T a_{l-1}
     const uint16_t* a_in = l == 0 ? w.a0 : w.a[l - 1];
-    LIFTER_PROPAGATE(wgrad(lay, t, b, b.dz, H, H, a_in, lay.in_pad(l), lay.in_pad(l), H, lay.in_dim(l),
-                           t->grad_params + lay.p_off[lay.t_weight(l)], st));
+    if (side != nullptr) LIFTER_PROPAGATE(side_fork(side, l, st));
+    LIFTER_PROPAGATE(wgrad(lay, t, b, dz, H, H, a_in, lay.in_pad(l), lay.in_pad(l), H, lay.in_dim(l),
+                           t->grad_params + lay.p_off[lay.t_weight(l)], side != nullptr ? side->st : st));
+    if (side != nullptr) LIFTER_CHECK_CUDA(cudaEventRecord(side->done[l], side->st));
 
     if (l == 0) {
         if (t->grad_x == nullptr) return LIFTER_OK;
         GemmArgs g;                                                // dx = dz_0 W1   (input gradient, phase-5 call site)
-        g.A = b.dz; g.lda = H; g.B = ops + lay.w_off[0]; g.ldb = lay.Ip; g.b_mn_major = 1;
+        g.A = dz; g.lda = H; g.B = ops + lay.w_off[0]; g.ldb = lay.Ip; g.b_mn_major = 1;
         g.M = B; g.N = lay.Ip; g.K = H; g.fmt = t->fmt; g.tag = "gemm_dx";
         if (lay.Ip <= 64) {
             g.out_mode = OUT_32_DIRECT; g.D = t->grad_x; g.n_valid = lay.I;
@@ -439,7 +482,7 @@ static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
         return gemm_launch(g, st);
     }
     GemmArgs g;                                                    // g_{l-1} = dz_l W_l (+ stream gradient)
-    g.A = b.dz; g.lda = H; g.B = ops + lay.w_off[l]; g.ldb = H; g.b_mn_major = 1;
+    g.A = dz; g.lda = H; g.B = ops + lay.w_off[l]; g.ldb = H; g.b_mn_major = 1;
     g.M = B; g.N = H; g.K = H; g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.ldd = H; g.tag = "gemm_dgrad";
     if (l % 2 == 0) {
         g.D = b.Gh;                                                // second layer of a block -> dh
@@ -461,11 +504,14 @@ int lifter_train_bwd_layer_finish(const lifter_config_t* cfg, const lifter_train
 int lifter_train_backward(const lifter_config_t* cfg, const lifter_train_ctx_t* t, void* stream) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
-    LIFTER_PROPAGATE(lifter_train_bwd_begin(cfg, t, stream));
+    SideStream* side = side_stream(lay.L + 1);
+    LIFTER_PROPAGATE(bwd_begin(cfg, t, stream, side));
     for (int l = lay.L - 1; l >= 0; --l) {
         LIFTER_PROPAGATE(bwd_layer_stats(cfg, t, l, stream, true));
-        LIFTER_PROPAGATE(bwd_layer_finish(cfg, t, l, stream, true));
+        LIFTER_PROPAGATE(bwd_layer_finish(cfg, t, l, stream, true, side));
     }
+    if (side != nullptr)                                           // dW_0 is the last thing on the side stream
+        LIFTER_CHECK_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), side->done[0], 0));
     return LIFTER_OK;
 }
 
