@@ -205,82 +205,118 @@ __global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, co
 // BN affine + ReLU + Philox dropout (+ block residual): a = drop(relu(z * scale + shift)) [+ resid], and one bit per
 // element "ReLU-active AND kept" for the backward pass.  1/(1-p) is folded into scale/shift (it is positive, so the
 // ReLU decision is unchanged).
-template <int FMT>
-__global__ void __launch_bounds__(EW_THREADS, 2) bn_apply_fwd_kernel(BnApplyFwd a, int rows_per_block, uint32_t threshold,
-                                                                  float inv_keep) {
-    griddep_launch();
-    griddep_wait();
+// Per-thread cursor of the apply kernel: byte-free pointer bumps instead of 64-bit row * H products per access.
+struct ApplyCursor {
+    const uint16_t* z; const uint16_t* r; uint16_t* a; uint8_t* bits;
+    uint32_t row;              // global row of unroll slot 0 (Philox counter word 0)
+    long left;                 // rows of this thread's walk that are still in range, counted in units of `rpb` rows
+};
+
+template <int FMT, bool FULL>
+__device__ __forceinline__ void apply_load(const ApplyCursor& c, long su, long left, bool has_resid,
+                                           uint4 (&zq)[EW_UNROLL], uint4 (&rq)[EW_UNROLL]) {
+#pragma unroll
+    for (int u = 0; u < EW_UNROLL; ++u) {
+        if (!FULL) { zq[u] = make_uint4(0, 0, 0, 0); rq[u] = make_uint4(0, 0, 0, 0); }
+        if (FULL || u < left) {
+            zq[u] = ldg_stream(c.z + u * su);
+            if (has_resid) rq[u] = ldg_stream(c.r + u * su);
+        }
+    }
+}
+
+template <int FMT, bool FULL>
+__device__ __forceinline__ void apply_compute(const ApplyCursor& c, long su, long sb, long left, int rpb, bool has_resid,
+                                              bool dropout, uint32_t group, uint32_t site, uint32_t dstep,
+                                              uint32_t thr_hi, const PhiloxKeys& keys, const float (&sc)[8],
+                                              const float (&sh)[8], const uint4 (&zq)[EW_UNROLL],
+                                              const uint4 (&rq)[EW_UNROLL]) {
+#pragma unroll
+    for (int u = 0; u < EW_UNROLL; ++u) {
+        if (!FULL && u >= left) break;
+        float z[8];
+        unpack8(zq[u], FMT, z);
+        uint32_t w[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};     // no dropout: every lane keeps
+        if (dropout) {
+            const Philox4 r4 = philox4x32_10(c.row + static_cast<uint32_t>(u * rpb), group, site, dstep, keys);
+            w[0] = r4.x; w[1] = r4.y; w[2] = r4.z; w[3] = r4.w;
+        }
+        float out[8];
+        uint32_t active = 0;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const float y = fmaf(z[e], sc[e], sh[e]);
+            const bool on = dropout_keep_lane(w, e, thr_hi) && (y > 0.0f);
+            active |= on ? (1u << e) : 0u;
+            out[e] = on ? y : 0.0f;
+        }
+        if (has_resid) {
+            float r[8];
+            unpack8(rq[u], FMT, r);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) out[e] += r[e];
+        }
+        *reinterpret_cast<uint4*>(c.a + u * su) = pack8(out, FMT);
+        c.bits[u * sb] = static_cast<uint8_t>(active);
+    }
+}
+
+template <int FMT, bool FULL>
+__device__ __forceinline__ void apply_walk(const BnApplyFwd& a, long base, long end, uint32_t threshold, float inv_keep,
+                                           const PhiloxKeys& keys) {
     const int tpr = a.H >> 3;
     const int rpb = EW_THREADS / tpr;
     const int cg = threadIdx.x % tpr, rl = threadIdx.x / tpr;
-    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
-    const long end = min(base + rows_per_block, static_cast<long>(a.rows));
     float sc[8], sh[8];
     load8f(a.scale + cg * 8, sc);
     load8f(a.shift + cg * 8, sh);
 #pragma unroll
     for (int e = 0; e < 8; ++e) { sc[e] *= inv_keep; sh[e] *= inv_keep; }
     const uint32_t dstep = a.step_dev != nullptr ? *a.step_dev : a.step;
-    const uint16_t* zp = static_cast<const uint16_t*>(a.z);
-    const uint16_t* rp = static_cast<const uint16_t*>(a.resid);
-    uint16_t* ap = static_cast<uint16_t*>(a.a);
-    const long step = static_cast<long>(rpb) * EW_UNROLL;
-    auto load = [&](long r0, uint4 (&zq)[EW_UNROLL], uint4 (&rq)[EW_UNROLL]) {
-#pragma unroll
-        for (int u = 0; u < EW_UNROLL; ++u) {
-            const long row = r0 + static_cast<long>(u) * rpb;
-            zq[u] = make_uint4(0, 0, 0, 0);
-            rq[u] = make_uint4(0, 0, 0, 0);
-            if (row < end) {
-                const long off = row * a.H + cg * 8;
-                zq[u] = ldg_stream(zp + off);
-                if (rp != nullptr) rq[u] = ldg_stream(rp + off);
-            }
-        }
-    };
-    auto compute = [&](long r0, const uint4 (&zq)[EW_UNROLL], const uint4 (&rq)[EW_UNROLL]) {
-#pragma unroll
-        for (int u = 0; u < EW_UNROLL; ++u) {
-            const long row = r0 + static_cast<long>(u) * rpb;
-            if (row >= end) break;
-            float z[8];
-            unpack8(zq[u], FMT, z);
-            uint32_t keep = 0xFFu;
-            if (a.apply_dropout)
-                keep = dropout_keep_bits8(static_cast<uint32_t>(row + a.row_offset), static_cast<uint32_t>(cg), a.site,
-                                          dstep, a.seed, threshold);
-            float out[8];
-            uint32_t active = 0;
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const float y = fmaf(z[e], sc[e], sh[e]);
-                const bool on = (y > 0.0f) && ((keep >> e) & 1u);
-                active |= (on ? 1u : 0u) << e;
-                out[e] = on ? y : 0.0f;
-            }
-            if (rp != nullptr) {
-                float r[8];
-                unpack8(rq[u], FMT, r);
-#pragma unroll
-                for (int e = 0; e < 8; ++e) out[e] += r[e];
-            }
-            *reinterpret_cast<uint4*>(ap + row * a.H + cg * 8) = pack8(out, FMT);
-            a.bits[row * tpr + cg] = static_cast<uint8_t>(active);
-        }
-    };
+    const uint32_t thr_hi = threshold << 16;
+    const bool has_resid = a.resid != nullptr, dropout = a.apply_dropout != 0;
+    const long su = static_cast<long>(rpb) * a.H;                 // elements between unroll slots
+    const long sb = static_cast<long>(rpb) * tpr;                 // mask bytes between unroll slots
+    const long first = base + rl;
+    ApplyCursor c;
+    c.z = static_cast<const uint16_t*>(a.z) + first * a.H + cg * 8;
+    c.r = has_resid ? static_cast<const uint16_t*>(a.resid) + first * a.H + cg * 8 : nullptr;
+    c.a = static_cast<uint16_t*>(a.a) + first * a.H + cg * 8;
+    c.bits = a.bits + first * tpr + cg;
+    c.row = static_cast<uint32_t>(first + a.row_offset);
+    long left = first < end ? (end - first + rpb - 1) / rpb : 0;  // slots (of stride rpb rows) this thread owns
     // two register buffers: the loads of the next group are in flight while this one is computed
     uint4 z0[EW_UNROLL], q0[EW_UNROLL], z1[EW_UNROLL], q1[EW_UNROLL];
-    long r = base + rl;
-    if (r < end) load(r, z0, q0);
-    while (r < end) {
-        if (r + step < end) load(r + step, z1, q1);
-        compute(r, z0, q0);
-        r += step;
-        if (r >= end) break;
-        if (r + step < end) load(r + step, z0, q0);
-        compute(r, z1, q1);
-        r += step;
+    ApplyCursor n = c;
+    auto advance = [&](ApplyCursor& k) {
+        k.z += su * EW_UNROLL; if (has_resid) k.r += su * EW_UNROLL;
+        k.a += su * EW_UNROLL; k.bits += sb * EW_UNROLL; k.row += static_cast<uint32_t>(rpb * EW_UNROLL);
+    };
+    if (left > 0) apply_load<FMT, FULL>(n, su, left, has_resid, z0, q0);
+    while (left > 0) {
+        advance(n);
+        if (left > EW_UNROLL) apply_load<FMT, FULL>(n, su, left - EW_UNROLL, has_resid, z1, q1);
+        apply_compute<FMT, FULL>(c, su, sb, left, rpb, has_resid, dropout, cg, a.site, dstep, thr_hi, keys, sc, sh, z0, q0);
+        c = n; left -= EW_UNROLL;
+        if (left <= 0) break;
+        advance(n);
+        if (left > EW_UNROLL) apply_load<FMT, FULL>(n, su, left - EW_UNROLL, has_resid, z0, q0);
+        apply_compute<FMT, FULL>(c, su, sb, left, rpb, has_resid, dropout, cg, a.site, dstep, thr_hi, keys, sc, sh, z1, q1);
+        c = n; left -= EW_UNROLL;
     }
+}
+
+template <int FMT>
+__global__ void __launch_bounds__(EW_THREADS, 2) bn_apply_fwd_kernel(BnApplyFwd a, int rows_per_block, uint32_t threshold,
+                                                                  float inv_keep, const PhiloxKeys keys) {
+    griddep_launch();
+    griddep_wait();
+    const int rpb = EW_THREADS / (a.H >> 3);
+    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long end = min(base + rows_per_block, static_cast<long>(a.rows));
+    // a block whose row count is a whole number of (rpb * EW_UNROLL)-row groups needs no per-row range checks
+    if ((end - base) % (static_cast<long>(rpb) * EW_UNROLL) == 0) apply_walk<FMT, true>(a, base, end, threshold, inv_keep, keys);
+    else apply_walk<FMT, false>(a, base, end, threshold, inv_keep, keys);
 }
 
 // ---------------------------------------------------------------------------------- backward passes
@@ -646,13 +682,14 @@ static int check_h(int H, const char* what) {
 int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st) {
     LIFTER_PROPAGATE(check_h(a.H, "bn_apply"));
     const uint32_t thr = dropout_threshold(a.p);
+    const PhiloxKeys keys = philox_round_keys(a.seed);
     const float inv_keep = (a.apply_dropout && a.p < 1.0f) ? 1.0f / (1.0f - a.p) : (a.apply_dropout ? 0.0f : 1.0f);
     const int rpb = rows_per_block_for(a.rows, a.H, 4);
     const unsigned blocks = static_cast<unsigned>((a.rows + rpb - 1) / rpb);
     if (a.fmt == FMT_BF16)
-        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_BF16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, thr, inv_keep));
+        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_BF16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, thr, inv_keep, keys));
     else
-        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_F16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, thr, inv_keep));
+        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_F16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, thr, inv_keep, keys));
     return LIFTER_OK;
 }
 

@@ -313,6 +313,27 @@ def gpu_arm(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def ncu_traffic(rows, width):
+    """DRAM bytes of one launch of the dominant kernel from the committed `ncu --set full` capture (profiles/), which
+    was taken on the training bench (M=8192, N=K=1024); null for any other shape."""
+    path = os.path.join(ROOT, "profiles", "r01_train_gemm_ncu_full_raw_v3.csv")
+    if rows != TRAIN_BATCH or width != H or not os.path.exists(path):
+        return {"traffic": None}
+    import csv
+    with open(path, newline="") as f:
+        rows_ = list(csv.reader(f))
+    head, units, vals = rows_[0], rows_[1], rows_[2]
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total = 0.0
+    for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        i = head.index(name)
+        total += float(vals[i]) * scale[units[i]]
+    return {"traffic": total, "traffic_unit": "bytes/launch",
+            "traffic_source": "profiles/r01_train_gemm_ncu_full_raw_v3.csv (dram read + write; the 16 MB output was "
+                              "still in L2 when the kernel ended)",
+            "algorithmic_bytes": float(rows * width * 2 * 2 + width * width * 2)}
+
+
 def gemm_roofline(cabi, dev, rows, fmt, pk, H=H):
     """CUDA-event time of the dominant kernel (rows x 1024 x 1024 tcgen05 GEMM with the fused epilogue)."""
     import ctypes as C
@@ -347,7 +368,7 @@ def gemm_roofline(cabi, dev, rows, fmt, pk, H=H):
     achieved = flops / (us * 1e-6) / 1e12
     return {"bound": "tensor", "kernel": f"lifter_gemm_kernel<256, 2-SM> M={rows} N=K={H} (+affine+ReLU epilogue)",
             "achieved": achieved, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"],
-            "peak_source": pk["source"] + " burst bf16 (kernel timed alone)", "us_per_launch": us, "traffic": None}
+            "peak_source": pk["source"] + " burst bf16 (kernel timed alone)", "us_per_launch": us, **ncu_traffic(rows, H)}
 
 
 def main():
