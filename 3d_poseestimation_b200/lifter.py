@@ -275,6 +275,57 @@ class LinearModel(torch.nn.Module):
                                             int(chunk_rows), _cabi.stream_ptr()))
         return out
 
+    def infer_host(self, x, out=None, chunk_rows=16384, in_stats=None, out_stats=None):
+        """Host-to-host inference: the evaluation loop of ``train_1.py:112-125`` (``inputs.cuda()`` ... ``.cpu()``)
+        as a three-stage pipeline.  ``x`` is an fp32 CPU tensor (pinned for asynchronous copies), the result an fp32
+        CPU tensor (pinned when allocated here).  Chunk i+1 uploads and chunk i-1 downloads while chunk i computes.
+        """
+        if x.is_cuda or x.dtype != torch.float32:
+            raise RuntimeError("infer_host takes an fp32 CPU tensor; call infer() with device tensors")
+        dev = self._flat.device
+        if dev.type != "cuda":
+            raise RuntimeError("the lifter runs on a B200 only (no CPU path): move the model with .cuda() first")
+        x = x.reshape(x.shape[0], -1)
+        B, I, O = x.shape[0], self.input_size, self.output_size
+        if x.shape[1] != I:
+            raise RuntimeError(f"expected {I} input values per pose, got {x.shape[1]}")
+        if out is None:
+            out = torch.empty(B, O, dtype=torch.float32).pin_memory()
+        rows_max = max(1, min(int(chunk_rows), B))
+        pipe = self._cache.get("host_pipe")
+        if pipe is None or pipe["rows"] < rows_max or pipe["dev"] != dev:
+            pipe = {"rows": rows_max, "dev": dev, "up": torch.cuda.Stream(dev), "down": torch.cuda.Stream(dev),
+                    "x": [torch.empty(rows_max, I, device=dev) for _ in range(2)],
+                    "o": [torch.empty(rows_max, O, device=dev) for _ in range(2)],
+                    "x_ready": [torch.cuda.Event() for _ in range(2)], "x_free": [torch.cuda.Event() for _ in range(2)],
+                    "o_ready": [torch.cuda.Event() for _ in range(2)], "o_free": [torch.cuda.Event() for _ in range(2)]}
+            self._cache["host_pipe"] = pipe
+        cur = torch.cuda.current_stream(dev)
+        up, down = pipe["up"], pipe["down"]
+        up.wait_stream(cur)
+        down.wait_stream(cur)
+        for i, r0 in enumerate(range(0, B, rows_max)):
+            s, rows = i & 1, min(rows_max, B - r0)
+            xd, od = pipe["x"][s][:rows], pipe["o"][s][:rows]
+            with torch.cuda.stream(up):
+                if i >= 2:
+                    up.wait_event(pipe["x_free"][s])
+                xd.copy_(x[r0:r0 + rows], non_blocking=True)
+                pipe["x_ready"][s].record(up)
+            cur.wait_event(pipe["x_ready"][s])
+            if i >= 2:
+                cur.wait_event(pipe["o_free"][s])
+            self.infer(xd, in_stats=in_stats, out_stats=out_stats, out=od)
+            pipe["x_free"][s].record(cur)
+            pipe["o_ready"][s].record(cur)
+            with torch.cuda.stream(down):
+                down.wait_event(pipe["o_ready"][s])
+                out[r0:r0 + rows].copy_(od, non_blocking=True)
+                pipe["o_free"][s].record(down)
+        cur.wait_stream(down)
+        down.synchronize()                                         # the result is host memory: valid on return
+        return out
+
     def forward(self, x):
         y = self._check_input(x)
         needs_grad = torch.is_grad_enabled() and (y.requires_grad or any(p.requires_grad for p in self.parameters()))

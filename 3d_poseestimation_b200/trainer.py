@@ -254,6 +254,67 @@ class LifterTrainer:
         self._after_step()
         return self.loss_out[0]
 
+    def run_epoch(self, batches, accumulate_metric=False):
+        """The epoch loop of ``train_1.py:73-100`` over an iterable of HOST batches ``(x, y)`` (fp32 CPU tensors;
+        pinned, as a ``DataLoader(pin_memory=True)`` yields them, for the upload to be asynchronous).
+
+        The upload of batch i+1 runs on a copy stream while step i computes; each step's loss is read back into
+        pinned host memory without stalling the queue (the reference blocks on ``loss.cpu().item()`` every step,
+        train_1.py:98).  Returns the per-step losses as a float32 CPU tensor (data parallel: summed over ranks, like
+        ``loss_value``).
+        """
+        model = self.model
+        dev = model._flat.device
+        cur = torch.cuda.current_stream(dev)
+        pipe = self._bufs.get("pipe")
+        if pipe is None:
+            pipe = {"copy": torch.cuda.Stream(dev), "slots": {}, "ready": [torch.cuda.Event() for _ in range(2)],
+                    "free": [torch.cuda.Event() for _ in range(2)]}
+            self._bufs["pipe"] = pipe
+        copy = pipe["copy"]
+        copy.wait_stream(cur)
+        losses, n = None, 0
+        for i, (xh, yh) in enumerate(batches):
+            if xh.is_cuda or yh.is_cuda:
+                raise RuntimeError("run_epoch takes host batches; call step() with device tensors")
+            xh = xh.reshape(xh.shape[0], -1)
+            yh = yh.reshape(yh.shape[0], -1)
+            s = i & 1
+            key = (s, tuple(xh.shape), tuple(yh.shape))
+            slot = pipe["slots"].get(s)
+            if slot is None or slot[0] != key:
+                if slot is not None:
+                    torch.cuda.synchronize(dev)                    # a batch-size change: let the old slot drain
+                slot = (key, torch.empty(xh.shape, dtype=torch.float32, device=dev),
+                        torch.empty(yh.shape, dtype=torch.float32, device=dev))
+                pipe["slots"][s] = slot
+            _, xd, yd = slot
+            with torch.cuda.stream(copy):
+                if i >= 2:
+                    copy.wait_event(pipe["free"][s])               # step i-2 has consumed this slot
+                xd.copy_(xh, non_blocking=True)
+                yd.copy_(yh, non_blocking=True)
+                pipe["ready"][s].record(copy)
+            cur.wait_event(pipe["ready"][s])
+            self.step(xd, yd, accumulate_metric=accumulate_metric)
+            pipe["free"][s].record(cur)
+            if losses is None or n == losses.numel():
+                grown = torch.empty(max(256, 2 * n), dtype=torch.float32).pin_memory()
+                if n:
+                    cur.synchronize()
+                    grown[:n] = losses[:n]
+                losses = grown
+            losses[n:n + 1].copy_(self.loss_out[:1], non_blocking=True)    # D2H of this step's loss, no host stall
+            n += 1
+        cur.synchronize()
+        out = losses[:n].clone() if n else torch.empty(0)
+        if self.world > 1 and n:
+            import torch.distributed as dist
+            t = out.to(dev)
+            dist.all_reduce(t, group=self.pg)
+            out = t.cpu()
+        return out
+
     def _sync_state(self):
         """Host -> device: optimiser step count and learning rate."""
         self.state[1] = self.step_count

@@ -188,11 +188,10 @@ def gpu_arm(args, rank, world, local_rank):
             def step():
                 model.infer(xd, out=out)
 
-            def step_e2e():
-                x = xh.to(dev, non_blocking=True)
-                o = model.infer(x, out=out)
-                outh.copy_(o, non_blocking=True)
-                torch.cuda.current_stream().synchronize()
+            def run_e2e(n):                                  # host poses in, host predictions out, every step
+                for _ in range(n):
+                    model.infer_host(xh, out=outh)
+                    torch.cuda.current_stream().synchronize()
             h2d, d2h = xh.numel() * 4, outh.numel() * 4
             dtype = "fp16 operands, fp32 accumulate"
             cfg = {"workload": f"configs[1]: eval-mode inference, batch {batch} synthetic H36M 2D poses per GPU "
@@ -218,11 +217,10 @@ def gpu_arm(args, rank, world, local_rank):
             def step():
                 tr.step(xd, yd)
 
-            def step_e2e():
-                x = xh.to(dev, non_blocking=True)
-                y = yh.to(dev, non_blocking=True)
-                tr.step(x, y)
-                tr.loss_value()                    # D2H read of the step's loss (synchronises)
+            def run_e2e(n):
+                # the epoch loop over host batches: per step, an H2D copy of (x, y) and a D2H read of the loss
+                losses = tr.run_epoch([(xh, yh)] * n)
+                assert losses.numel() == n and bool(torch.isfinite(losses).all())
             h2d, d2h = (xh.numel() + yh.numel()) * 4, 4
             dtype = "bf16 operands, fp32 accumulate/master weights"
             par = f"dp{world}"
@@ -266,13 +264,11 @@ def gpu_arm(args, rank, world, local_rank):
             ms, clocks = timed(step, steps, warmup), None
 
         # end to end through the public API with host buffers (wall clock around synchronising steps)
-        for _ in range(max(1, warmup // 2)):
-            step_e2e()
+        run_e2e(max(2, warmup // 2))
         barrier()
         t0 = time.perf_counter()
         n_e2e = max(3, steps // 2)
-        for _ in range(n_e2e):
-            step_e2e()
+        run_e2e(n_e2e)
         barrier()
         e2e_ms = (time.perf_counter() - t0) / n_e2e * 1e3
         if world > 1:
