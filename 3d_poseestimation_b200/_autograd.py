@@ -80,8 +80,9 @@ def run_forward(model, x, training, saved=None, out=None, step=None, step_state=
     return out, saved, t
 
 
-def run_backward(model, t, grad_out, grad_flat, grad_x, scratch=None):
-    """Backward of the pair described by ``t``; writes ``grad_flat`` (parameter layout) and ``grad_x``."""
+def run_backward(model, t, grad_out, grad_flat, grad_x, scratch=None, optim=None):
+    """Backward of the pair described by ``t``; writes ``grad_flat`` (parameter layout) and ``grad_x``.
+    ``optim`` (``_cabi.Optim``): fold the optimiser into the backward pass (``lifter_train_backward_step``)."""
     lib, cfg = _cabi.lib(), C.byref(model._cfg)
     B = t.batch
     nbytes = _cabi.check(lib.lifter_train_scratch_bytes(cfg, B))
@@ -93,7 +94,11 @@ def run_backward(model, t, grad_out, grad_flat, grad_x, scratch=None):
     st = _cabi.stream_ptr()
     pg, world, _ = _dist_world(model)
     sync_bn = t.bn_mode == 0 and model.BN and world > 1
-    if not sync_bn or bool(t.dp):
+    if optim is not None:
+        if sync_bn and not bool(t.dp):
+            raise RuntimeError("the fused backward + optimiser step needs the in-kernel data-parallel exchange")
+        _cabi.check(lib.lifter_train_backward_step(cfg, C.byref(t), C.byref(optim), st))
+    elif not sync_bn or bool(t.dp):
         _cabi.check(lib.lifter_train_backward(cfg, C.byref(t), st))
     else:
         import torch.distributed as dist

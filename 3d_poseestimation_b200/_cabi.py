@@ -51,6 +51,13 @@ class TrainCtx(C.Structure):
                 ("scratch_bytes", C.c_int64), ("step_state", C.c_void_p), ("dp", C.POINTER(DpInfo))]
 
 
+class Optim(C.Structure):
+    """``lifter_optim_t``: the Adam/AdamW state ``lifter_train_backward_step`` updates range by range."""
+    _fields_ = [("params", C.c_void_p), ("operands", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p),
+                ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("weight_decay", C.c_float),
+                ("decoupled", C.c_int32), ("grad_scale", C.c_float)]
+
+
 class PoseLossDesc(C.Structure):
     """``lifter_pose_loss_t``"""
     _fields_ = [("pred", C.c_void_p), ("target", C.c_void_p), ("mean", C.c_void_p), ("stdv", C.c_void_p),
@@ -93,6 +100,7 @@ SIGNATURES = {
     "lifter_train_bwd_layer_stats": (_I32, [_CFG, _CTX, _I32, _P]),
     "lifter_train_bwd_layer_finish": (_I32, [_CFG, _CTX, _I32, _P]),
     "lifter_train_backward": (_I32, [_CFG, _CTX, _P]),
+    "lifter_train_backward_step": (_I32, [_CFG, _CTX, C.POINTER(Optim), _P]),
     "lifter_loss_scratch_bytes": (_I64, [_I64, _I32]),
     "lifter_loss": (_I32, [_P, _P, _I64, _I32, _I32, _I64, _P, _P, _P, _P, _I32, _P]),
     "lifter_flip_pose": (_I32, [_P, _P, _I64, _I32, _I32, _I32, _P]),

@@ -130,8 +130,13 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
+// 128 registers x 384 threads = 48 K of the SM's 64 K registers: the epilogue's two 32-column tcgen05.ld buffers fit
+// without spills, and a small kernel on another stream (optimiser range, split-K reduction) can share the SM.
+#ifndef LIFTER_GEMM_REGS
+#define LIFTER_GEMM_REGS __maxnreg__(128)
+#endif
 template <int BLOCK_N, bool TWO_SM>
-__global__ void __launch_bounds__(Cfg<BLOCK_N, TWO_SM>::NUM_THREADS, 1)
+__global__ void LIFTER_GEMM_REGS
 lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
     using C = Cfg<BLOCK_N, TWO_SM>;
     constexpr int CL = TWO_SM ? 2 : 1;

@@ -315,7 +315,9 @@ int lifter_train_forward(const lifter_config_t* cfg, const lifter_train_ctx_t* t
 // is the output layer.  Works under stream capture (the side stream joins the caller's before the call returns).
 struct SideStream {
     cudaStream_t st = nullptr;
-    std::vector<cudaEvent_t> fork, done;
+    cudaStream_t opt = nullptr;            // optimiser ranges (lifter_train_backward_step)
+    std::vector<cudaEvent_t> fork, done, mdone;   // mdone[i]: the caller's stream is done with layer i's old weights
+    cudaEvent_t odone = nullptr;
 };
 static SideStream* side_stream(int slots) {
     static SideStream per_device[64];
@@ -325,11 +327,14 @@ static SideStream* side_stream(int slots) {
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
     SideStream* s = &per_device[dev];
     if (s->st == nullptr && cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (s->opt == nullptr && cudaStreamCreateWithFlags(&s->opt, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (s->odone == nullptr && cudaEventCreateWithFlags(&s->odone, cudaEventDisableTiming) != cudaSuccess) return nullptr;
     while (static_cast<int>(s->fork.size()) < slots) {
-        cudaEvent_t a, b;
+        cudaEvent_t a, b, c;
         if (cudaEventCreateWithFlags(&a, cudaEventDisableTiming) != cudaSuccess) return nullptr;
         if (cudaEventCreateWithFlags(&b, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-        s->fork.push_back(a); s->done.push_back(b);
+        if (cudaEventCreateWithFlags(&c, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        s->fork.push_back(a); s->done.push_back(b); s->mdone.push_back(c);
     }
     return s;
 }
@@ -512,6 +517,87 @@ int lifter_train_backward(const lifter_config_t* cfg, const lifter_train_ctx_t* 
     }
     if (side != nullptr)                                           // dW_0 is the last thing on the side stream
         LIFTER_CHECK_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), side->done[0], 0));
+    return LIFTER_OK;
+}
+
+// ---- backward with the optimiser folded in -----------------------------------------------------------------------
+static void fill_operand_table(const Layout& lay, AdamArgs* a, void* operands, int fmt) {
+    a->operands = operands; a->op_fmt = fmt; a->nw = lay.L + 1;
+    for (int l = 0; l <= lay.L; ++l) {
+        const int t = l < lay.L ? lay.t_weight(l) : lay.t_w2();
+        a->w_p_off[l] = lay.p_off[t]; a->w_numel[l] = lay.p_numel[t]; a->w_off[l] = lay.w_off[l];
+        a->w_in[l] = l < lay.L ? lay.in_dim(l) : lay.H;
+        a->w_pad[l] = l < lay.L ? lay.in_pad(l) : lay.H;
+    }
+}
+
+// Adam over the flat-buffer range of layer l (W, b, gamma, beta are consecutive; l == L: the output layer W2, b2)
+static int optim_range(const Layout& lay, const lifter_train_ctx_t* t, const lifter_optim_t* o, int l, int phase, bool last,
+                       cudaStream_t st) {
+    const int64_t lo = lay.p_off[l < lay.L ? lay.t_weight(l) : lay.t_w2()];
+    const int64_t hi = l < lay.L ? lay.p_off[l + 1 < lay.L ? lay.t_weight(l + 1) : lay.t_w2()] : lay.p_total;
+    const bool dp = t->dp != nullptr && t->dp->world > 1;
+    AdamDpArgs d;
+    AdamArgs& a = d.a;
+    a.p = o->params; a.g = t->grad_params; a.m = o->m; a.v = o->v; a.base = lo; a.n = hi - lo;
+    a.lr = 0.0f; a.beta1 = o->beta1; a.beta2 = o->beta2; a.eps = o->eps; a.weight_decay = o->weight_decay;
+    a.decoupled = o->decoupled; a.step = 1; a.grad_scale = o->grad_scale;
+    a.dyn = reinterpret_cast<const float*>(t->step_state);
+    fill_operand_table(lay, &a, o->operands, t->fmt);
+    if (!dp) return adam_step(a, st);
+    const lifter_dp_t* g = t->dp;
+    d.world = g->world; d.rank = g->rank;
+    for (int q = 0; q < g->world; ++q) {
+        d.g_peer[q] = static_cast<const float*>(g->grad[q]);
+        d.p_peer[q] = static_cast<float*>(g->params[q]);
+        d.op_peer[q] = g->operands[q];
+        d.flag_peer[q] = static_cast<unsigned*>(g->flags[q]);
+    }
+    d.epoch = reinterpret_cast<const unsigned*>(t->step_state) + 1;
+    d.phase = phase; d.last = last ? 1 : 0;
+    return adam_step_dp(d, st);
+}
+
+int lifter_train_backward_step(const lifter_config_t* cfg, const lifter_train_ctx_t* t, const lifter_optim_t* o,
+                               void* stream) {
+    Layout lay;
+    LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
+    LIFTER_REQUIRE(o != nullptr && o->params && o->operands && o->m && o->v, "backward_step: null optimiser buffer");
+    LIFTER_REQUIRE(t->step_state != nullptr, "backward_step: needs the device step state (ctx->step_state)");
+    LIFTER_REQUIRE(lay.L + 1 <= ADAM_MAX_WEIGHTS, "backward_step: too many layers for the fused operand refresh");
+    LIFTER_REQUIRE(o->params == t->params && o->operands == t->operands,
+                   "backward_step: the optimiser must own the buffers the context reads");
+    if (t->dp != nullptr && t->dp->world > 1) {
+        const lifter_dp_t* g = t->dp;
+        LIFTER_REQUIRE(g->world <= ADAM_DP_MAX_WORLD && g->rank >= 0 && g->rank < g->world, "backward_step: bad world/rank");
+        for (int q = 0; q < g->world; ++q)
+            LIFTER_REQUIRE(g->grad[q] && g->params[q] && g->operands[q] && g->flags[q], "backward_step: null peer buffer %d", q);
+        LIFTER_REQUIRE(g->grad[g->rank] == t->grad_params && g->params[g->rank] == o->params &&
+                       g->operands[g->rank] == o->operands, "backward_step: this rank's peer entries must be its own buffers");
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    SideStream* side = side_stream(lay.L + 1);
+    // range i is safe to update once (a) dW_i is reduced [done[i], side stream] and (b) this stream has consumed the old
+    // W_i in the data-gradient GEMM [mdone[i]]
+    auto range = [&](int l, int phase, bool last) -> int {
+        if (side == nullptr) return optim_range(lay, t, o, l, phase, last, st);
+        LIFTER_CHECK_CUDA(cudaEventRecord(side->mdone[l], st));
+        LIFTER_CHECK_CUDA(cudaStreamWaitEvent(side->opt, side->mdone[l], 0));
+        LIFTER_CHECK_CUDA(cudaStreamWaitEvent(side->opt, side->done[l], 0));
+        return optim_range(lay, t, o, l, phase, last, side->opt);
+    };
+    LIFTER_PROPAGATE(bwd_begin(cfg, t, stream, side));
+    LIFTER_PROPAGATE(range(lay.L, 0, false));
+    for (int l = lay.L - 1; l >= 0; --l) {
+        LIFTER_PROPAGATE(bwd_layer_stats(cfg, t, l, stream, true));
+        LIFTER_PROPAGATE(bwd_layer_finish(cfg, t, l, stream, true, side));
+        LIFTER_PROPAGATE(range(l, lay.L - l, l == 0));
+    }
+    if (side != nullptr) {
+        LIFTER_CHECK_CUDA(cudaEventRecord(side->odone, side->opt));
+        LIFTER_CHECK_CUDA(cudaStreamWaitEvent(st, side->odone, 0));
+        LIFTER_CHECK_CUDA(cudaStreamWaitEvent(st, side->done[0], 0));
+    }
     return LIFTER_OK;
 }
 

@@ -167,10 +167,10 @@ __global__ void __launch_bounds__(256) adam_kernel(AdamArgs a, float step_size, 
     griddep_launch();
     griddep_wait();
     if (a.dyn != nullptr) { step_size = a.dyn[3]; inv_sqrt_bc2 = a.dyn[4]; decay = a.dyn[5]; }
-    const long n4 = a.n >> 2;
+    const long n4 = a.n >> 2, b4 = a.base >> 2;
     const long stride = static_cast<long>(gridDim.x) * blockDim.x;
     uint16_t* ops = static_cast<uint16_t*>(a.operands);
-    for (long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    for (long i = b4 + static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < b4 + n4; i += stride) {
         float4 p = reinterpret_cast<float4*>(a.p)[i];
         const float4 g4 = reinterpret_cast<const float4*>(a.g)[i];
         float4 m = reinterpret_cast<float4*>(a.m)[i];
@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
     griddep_wait();
     const AdamArgs& a = d.a;
     if (a.dyn != nullptr) { step_size = a.dyn[3]; inv_sqrt_bc2 = a.dyn[4]; decay = a.dyn[5]; }
-    const unsigned epoch = *d.epoch;
+    const unsigned epoch = *d.epoch * static_cast<unsigned>(ADAM_DP_PHASES) + static_cast<unsigned>(d.phase);
     unsigned* my_flags = d.flag_peer[d.rank];
     // ---- barrier 1: every rank's gradient is complete (my predecessor kernels finished: this kernel runs)
     if (threadIdx.x < d.world) {
@@ -253,9 +253,9 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
     }
     __syncthreads();
     // ---- my slice: sum of the gradients in rank order, Adam, parameters to every rank
-    const long n4 = a.n >> 2;
+    const long n4 = a.n >> 2, b4 = a.base >> 2;
     const long slice = (n4 + d.world - 1) / d.world;
-    const long lo = slice * d.rank, hi = min(lo + slice, n4);
+    const long lo = b4 + slice * d.rank, hi = min(lo + slice, b4 + n4);
     const long stride = static_cast<long>(gridDim.x) * blockDim.x;
     for (long i0 = lo + static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < hi; i0 += stride * DP_UNROLL) {
         float4 gs[DP_UNROLL][ADAM_DP_MAX_WORLD];
@@ -317,6 +317,7 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
         }
     }
     // ---- barrier 2: the last block of this rank tells every peer "my stores are done" and waits for theirs
+    if (!d.last) return;                 // an earlier range of the step: the closing launch orders all of them
     __threadfence_system();
     __syncthreads();
     __shared__ unsigned last;
@@ -382,7 +383,7 @@ int l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, 
 }
 
 int adam_step(const AdamArgs& a, cudaStream_t st) {
-    LIFTER_REQUIRE(a.n % 4 == 0, "adam: flat buffer length must be a multiple of 4");
+    LIFTER_REQUIRE(a.n % 4 == 0 && a.base % 4 == 0 && a.n > 0, "adam: range start / length must be multiples of 4");
     LIFTER_REQUIRE(a.step >= 1 || a.dyn != nullptr, "adam: step is 1-based");
     LIFTER_REQUIRE(a.operands == nullptr || (a.nw >= 1 && a.nw <= ADAM_MAX_WEIGHTS), "adam: bad operand table");
     const int t = a.step >= 1 ? a.step : 1;
@@ -401,7 +402,8 @@ int adam_step(const AdamArgs& a, cudaStream_t st) {
 
 int adam_step_dp(const AdamDpArgs& d, cudaStream_t st) {
     const AdamArgs& a = d.a;
-    LIFTER_REQUIRE(a.n % 4 == 0, "adam: flat buffer length must be a multiple of 4");
+    LIFTER_REQUIRE(a.n % 4 == 0 && a.base % 4 == 0 && a.n > 0, "adam: range start / length must be multiples of 4");
+    LIFTER_REQUIRE(d.phase >= 0 && d.phase < ADAM_DP_PHASES, "adam_dp: phase %d out of range", d.phase);
     LIFTER_REQUIRE(d.world >= 2 && d.world <= ADAM_DP_MAX_WORLD && d.rank >= 0 && d.rank < d.world, "adam_dp: bad world/rank");
     LIFTER_REQUIRE(a.dyn != nullptr && d.epoch != nullptr, "adam_dp: needs the device step state");
     const long slice4 = (a.n / 4 + d.world - 1) / d.world;

@@ -28,6 +28,7 @@ int l1_grad(const float* a, const float* b, int64_t n, int row_len, int centre, 
 constexpr int ADAM_MAX_WEIGHTS = 16;
 struct AdamArgs {
     float* p; const float* g; float* m; float* v; int64_t n;
+    long long base = 0;                                           // first element of the range (multiple of 4); n = its length
     float lr, beta1, beta2, eps, weight_decay; int decoupled;     // AdamW: decoupled = 1
     int step;                                                     // 1-based
     float grad_scale;                                             // multiplies g first (1/world for DP means)
@@ -53,7 +54,11 @@ struct AdamDpArgs {
     void* op_peer[ADAM_DP_MAX_WORLD];            // every rank's operand buffer (nullable when a.operands == nullptr)
     unsigned* flag_peer[ADAM_DP_MAX_WORLD];      // every rank's flag block: [2][world] epochs + [1] block counter
     const unsigned* epoch;                       // device step counter
+    // a step may run several launches (one per parameter range): launch `phase` of the step uses the barrier epoch
+    // step * ADAM_DP_PHASES + phase; only the `last` launch runs the closing "all stores have landed" barrier
+    int phase = 0, last = 1;
 };
+constexpr int ADAM_DP_PHASES = 64;
 int adam_step_dp(const AdamDpArgs& a, cudaStream_t st);
 
 // device step state (include/lifter_b200.h: lifter_step_state_t): dropout_step = adam_step; adam_step += 1; the Adam

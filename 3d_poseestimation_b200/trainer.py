@@ -71,6 +71,8 @@ class LifterTrainer:
         self.use_graph = bool(use_graph)
         # data parallel: capture the NCCL gradient all-reduce into the step graph too (LIFTER_DP_GRAPH=0 turns it off)
         self.graph_collectives = os.environ.get("LIFTER_DP_GRAPH", "1") != "0"
+        # per-layer optimiser ranges inside backward (LIFTER_FUSE_OPTIM=0: one Adam launch after backward)
+        self.fuse_optimizer = os.environ.get("LIFTER_FUSE_OPTIM", "1") != "0"
         self._state_stale = False
         self._sym = None
         self._dp_adam = False
@@ -150,7 +152,8 @@ class LifterTrainer:
         fwd = 1 + L * 3 + 1                      # prep_input, per layer GEMM + finalize + apply, output GEMM
         loss = 2
         bwd = 2 + 2 + 1 + L * (2 * use_bn + 1 + 2 + 1) - 1 + (0 if use_bn else L)
-        return 1 + fwd + loss + bwd + 1          # + step_advance + Adam (which also packs the operands)
+        adam = L + 1 if (self.fuse_optimizer and self.use_graph and (self.world == 1 or self._dp_adam)) else 1
+        return 1 + fwd + loss + bwd + adam       # + step_advance + Adam (which also packs the operands), per range
 
     # ------------------------------------------------------------------ one optimiser step
     def _enqueue(self, x, y, b, accumulate_metric, state):
@@ -171,8 +174,15 @@ class LifterTrainer:
         _cabi.check(lib.lifter_loss(_cabi.ptr(out), _cabi.ptr(y), B, self.joints, self.loss_kind, B * self.world,
                                     _cabi.ptr(self.metric_std), _cabi.ptr(b["dpred"]), _cabi.ptr(b["lscratch"]),
                                     _cabi.ptr(self.loss_out), int(accumulate_metric), st))
-        _autograd.run_backward(model, t, b["dpred"], self.grad, None, scratch=b["scratch"])
         ops = model._operands(fmt)
+        if state is not None and self.fuse_optimizer and (self.world == 1 or self._dp_adam):
+            # backward with the optimiser folded in: each layer's Adam range (data parallel: its NVLink reduce-scatter +
+            # Adam + all-gather) runs on a side stream as soon as that layer's gradients exist
+            opt = _cabi.Optim(model._flat.data_ptr(), ops.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
+                              self.betas[0], self.betas[1], self.eps, self.weight_decay, int(self.decoupled), 1.0)
+            _autograd.run_backward(model, t, b["dpred"], self.grad, None, scratch=b["scratch"], optim=opt)
+            return
+        _autograd.run_backward(model, t, b["dpred"], self.grad, None, scratch=b["scratch"])
         if self._dp_adam:
             # data parallel: reduce-scatter of the gradients + Adam + all-gather of the parameters in ONE kernel over
             # NVLink peer memory (sum of shard gradients = gradient of the global batch)

@@ -221,6 +221,23 @@ int lifter_dp_adam_step(const lifter_config_t* cfg, const lifter_dp_t* dp, float
                         float eps, float weight_decay, int decoupled, float grad_scale,
                         const lifter_step_state_t* state, int fmt, void* stream);
 
+/* Backward pass WITH the optimiser folded in (needs ctx->step_state): as soon as a layer's gradients are complete —
+ * weight gradient reduced, its data-gradient GEMM done with the old weights — Adam/AdamW runs on that layer's range of
+ * the flat buffer on a side stream while the layers below are still in backward.  With ctx->dp (world > 1, peer
+ * gradient / parameter / operand / flag buffers set) each range goes through the fused NVLink reduce-scatter + Adam +
+ * all-gather kernel instead, so the gradient exchange overlaps backward too.  Replaces lifter_train_backward followed
+ * by lifter_adam_step_packed / lifter_dp_adam_step; the caller still advances the step state once per step.        */
+typedef struct lifter_optim {
+    float* params;               /* writable flat fp32 parameters (the buffer ctx->params points at)              */
+    void* operands;              /* writable 16-bit operand copies (ctx->operands), refreshed in the same pass     */
+    float* m; float* v;          /* flat Adam state                                                                */
+    float beta1, beta2, eps, weight_decay;
+    int32_t decoupled;           /* 1: AdamW                                                                       */
+    float grad_scale;
+} lifter_optim_t;
+int lifter_train_backward_step(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, const lifter_optim_t* opt,
+                               void* stream);
+
 /* ---- test hook: one tcgen05 GEMM  D[M][N] = sum_k A(m,k) B(n,k) ------------------------------------ */
 typedef struct lifter_gemm_desc {
     const void* A; int64_t lda; const void* B; int64_t ldb;
