@@ -78,6 +78,9 @@ size_t dp_flag_bytes(const Layout&, int) { return 0; }
 int fill_exchange(const Layout& lay, const lifter_train_ctx_t* t, int site, SyncExchange* ex) {
     *ex = SyncExchange();
     if (t->dp == nullptr || t->dp->world <= 1) return LIFTER_OK;
+    // timing probe only (wrong numerics: local statistics): how much of a data-parallel step is the exchange
+    static const bool skip = [] { const char* e = getenv("LIFTER_DP_DEBUG_NO_EXCHANGE"); return e != nullptr && e[0] == '1'; }();
+    if (skip) return LIFTER_OK;
     const lifter_dp_t* d = t->dp;
     LIFTER_REQUIRE(d->world <= DP_MAX_WORLD && d->rank >= 0 && d->rank < d->world, "dp: world %d / rank %d out of range",
                    d->world, d->rank);

@@ -259,7 +259,16 @@ def gpu_arm(args, rank, world, local_rank):
         if with_clocks:
             with ClockSampler(local_rank) as clk:
                 ms = timed(step, steps, warmup)
+                in_region = len(clk.samples)
+                # nvidia-smi answers every ~0.1 s: a timed region shorter than that is extended with identical untimed
+                # steps (same load) until the sampler has a median to report
+                t_end = time.perf_counter() + 2.0
+                while len(clk.samples) < 5 and time.perf_counter() < t_end:
+                    for _ in range(20):
+                        step()
+                    torch.cuda.synchronize()
             clocks = clk.summary()
+            clocks["samples_in_timed_region"] = in_region
         else:
             ms, clocks = timed(step, steps, warmup), None
 
@@ -370,7 +379,7 @@ def gemm_roofline(cabi, dev, rows, fmt, pk, H=H):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=os.environ.get("LIFTER_BENCH_WORKLOAD", "train"), choices=["train", "eval", "wide"])

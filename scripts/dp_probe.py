@@ -34,6 +34,30 @@ for n in (5, 20):
     e1.record()
     torch.cuda.synchronize()
     print(f"[{rank}] {n} back-to-back steps: {e0.elapsed_time(e1) / n * 1e3:.1f} us/step", flush=True)
+if len(sys.argv) > 2 and sys.argv[2] == "trace":
+    # per-kernel device times (run with LIFTER_DP_GRAPH=0 LIFTER_WGRAD_STREAM=0: eager, single stream)
+    import ctypes as C
+    from collections import defaultdict
+    cabi = importlib.import_module("3d_poseestimation_b200._cabi")
+    lib = cabi.lib()
+    tot, cnt = defaultdict(float), defaultdict(int)
+    N = 5
+    for _ in range(N):
+        dist.barrier()
+        torch.cuda.synchronize()
+        lib.lifter_trace_begin(cabi.stream_ptr())
+        tr.step(x, y)
+        buf = C.create_string_buffer(1 << 16)
+        lib.lifter_trace_end(buf, len(buf))
+        for line in buf.value.decode().splitlines():
+            name, us = line.rsplit(" ", 1)
+            tot[name] += float(us)
+            cnt[name] += 1
+    if rank == 0:
+        ssum = sum(tot.values()) / N
+        print(f"traced step: {ssum:.1f} us over {sum(cnt.values()) // N} launches")
+        for k in sorted(tot, key=lambda k: -tot[k]):
+            print(f"{k:36s} n/step={cnt[k] / N:5.1f} total/step={tot[k] / N:8.1f} us  avg={tot[k] / cnt[k]:7.2f} us")
 g = torch.randn(4296768, device=dev)
 for _ in range(3):
     dist.all_reduce(g)
