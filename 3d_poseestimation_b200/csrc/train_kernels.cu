@@ -139,33 +139,48 @@ __global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __r
 }
 
 // ---------------------------------------------------------------------------------- BN finalize (forward)
-__device__ __forceinline__ void bn_finalize_fwd_col(const BnFwdFinalize& a, int j, double sum, double sumsq) {
+// Per-column inputs of the finalize that do not depend on the reduction: fetched before it so their latency hides.
+struct BnColumnInputs { float bias, gamma, beta, rmean, rvar; };
+__device__ __forceinline__ BnColumnInputs bn_column_inputs(const BnFwdFinalize& a, int j) {
+    BnColumnInputs c = {0.0f, 1.0f, 0.0f, 0.0f, 1.0f};
+    c.bias = a.bias[j];
+    if (a.use_bn) {
+        c.gamma = a.gamma[j]; c.beta = a.beta[j];
+        if (a.running_mean != nullptr) { c.rmean = a.running_mean[j]; c.rvar = a.running_var[j]; }
+    }
+    return c;
+}
+
+__device__ __forceinline__ void bn_finalize_fwd_col(const BnFwdFinalize& a, int j, double sum, double sumsq,
+                                                    const BnColumnInputs& c) {
     if (!a.use_bn) {
-        a.mean_z[j] = 0.0f; a.rstd[j] = 1.0f; a.scale[j] = 1.0f; a.shift[j] = a.bias[j];
+        a.mean_z[j] = 0.0f; a.rstd[j] = 1.0f; a.scale[j] = 1.0f; a.shift[j] = c.bias;
         return;
     }
     float mean, rstd;
     if (a.bn_mode == 0) {
-        const double m = sum / a.count;
-        double var = sumsq / a.count - m * m;                        // biased batch variance (normalisation)
+        // the difference sumsq/n - m^2 needs fp64; everything after it is fp32 (no fp64 divide or square root)
+        const double inv_n = 1.0 / a.count;                          // uniform: one divide per thread, off the chain
+        const double m = sum * inv_n;
+        double var = sumsq * inv_n - m * m;                          // biased batch variance (normalisation)
         if (var < 0.0) var = 0.0;
+        const float varf = static_cast<float>(var);
         mean = static_cast<float>(m);
-        rstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(a.eps)));
+        rstd = 1.0f / sqrtf(varf + a.eps);
         if (a.running_mean != nullptr) {                             // torch: momentum 0.1, unbiased running var
-            const double unbiased = a.count > 1.0 ? var * a.count / (a.count - 1.0) : var;
-            a.running_mean[j] = (1.0f - a.momentum) * a.running_mean[j] +
-                                a.momentum * static_cast<float>(m + static_cast<double>(a.bias[j]));
-            a.running_var[j] = (1.0f - a.momentum) * a.running_var[j] + a.momentum * static_cast<float>(unbiased);
+            const float unbias = a.count > 1.0 ? static_cast<float>(a.count / (a.count - 1.0)) : 1.0f;
+            a.running_mean[j] = (1.0f - a.momentum) * c.rmean + a.momentum * (mean + c.bias);
+            a.running_var[j] = (1.0f - a.momentum) * c.rvar + a.momentum * (varf * unbias);
         }
     } else {                                                         // running statistics; z excludes the bias
-        mean = a.running_mean[j] - a.bias[j];
-        rstd = 1.0f / sqrtf(a.running_var[j] + a.eps);
+        mean = c.rmean - c.bias;
+        rstd = 1.0f / sqrtf(c.rvar + a.eps);
     }
-    const float s = a.gamma[j] * rstd;
+    const float s = c.gamma * rstd;
     a.mean_z[j] = mean;
     a.rstd[j] = rstd;
     a.scale[j] = s;
-    a.shift[j] = a.beta[j] - mean * s;
+    a.shift[j] = c.beta - mean * s;
 }
 
 __global__ void bn_finalize_fwd_kernel(BnFwdFinalize a) {
@@ -175,7 +190,7 @@ __global__ void bn_finalize_fwd_kernel(BnFwdFinalize a) {
     if (j == 0 && a.bn_mode == 0 && a.use_bn && a.num_batches_tracked != nullptr) *a.num_batches_tracked += 1;
     if (j >= a.H) return;
     const bool batch = a.use_bn && a.bn_mode == 0;
-    bn_finalize_fwd_col(a, j, batch ? a.sums[j] : 0.0, batch ? a.sums[a.H + j] : 0.0);
+    bn_finalize_fwd_col(a, j, batch ? a.sums[j] : 0.0, batch ? a.sums[a.H + j] : 0.0, bn_column_inputs(a, j));
 }
 
 // single-GPU path: second stage of the column reduction and the finalize in one launch
@@ -185,14 +200,16 @@ __global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, co
     griddep_wait();
     __shared__ double sh[2][RED_LANES][RED_COLS];
     double ta, tb;
-    reduce_partials_2(psum, psq, P, a.H, a.H, sh, ta, tb);
     const int col = blockIdx.x * RED_COLS + threadIdx.x;
+    BnColumnInputs ci = {0.0f, 1.0f, 0.0f, 0.0f, 1.0f};
+    if (threadIdx.y == 0 && col < a.H) ci = bn_column_inputs(a, col);
+    reduce_partials_2(psum, psq, P, a.H, a.H, sh, ta, tb);
     if (a.ex.world > 1 && threadIdx.y == 0) exchange_column_sums(a.ex, a.H, col, col < a.H, ta, tb);
     if (threadIdx.y == 0 && col < a.H) {
         sums_out[col] = ta;
         sums_out[a.H + col] = tb;
         if (col == 0 && a.num_batches_tracked != nullptr) *a.num_batches_tracked += 1;
-        bn_finalize_fwd_col(a, col, ta, tb);
+        bn_finalize_fwd_col(a, col, ta, tb, ci);
     }
 }
 

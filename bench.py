@@ -260,10 +260,10 @@ def gpu_arm(args, rank, world, local_rank):
             with ClockSampler(local_rank) as clk:
                 ms = timed(step, steps, warmup)
                 in_region = len(clk.samples)
-                # nvidia-smi answers every ~0.1 s: a timed region shorter than ~0.6 s is extended with identical untimed
+                # nvidia-smi answers every ~0.1 s: a timed region shorter than ~1.5 s is extended with identical untimed
                 # steps (same load).  The count derives from the max-over-ranks step time, so every rank runs the same
                 # number of (collective) steps.
-                for _ in range(max(0, int(600.0 / max(ms, 1e-3)) - steps)):
+                for _ in range(max(0, int(1500.0 / max(ms, 1e-3)) - steps)):
                     step()
                 torch.cuda.synchronize()
             clocks = clk.summary()
