@@ -531,15 +531,23 @@ __global__ void __launch_bounds__(EW_THREADS, 2) bwd_dz_kernel(BwdCommon c, int 
 // ---------------------------------------------------------------------------------- BN finalize (backward)
 // coefficients of pass 2 from the GLOBAL sums:  dz = k (dy - c1 - zhat c2),  dy = ik gm,  zhat = (z - mean) rstd
 //   =>  dz = A gm + Bz z + Cc   with  A = k ik,  Bz = -k c2 rstd,  Cc = -k c1 - Bz mean
-__device__ __forceinline__ void bn_bwd_coefficients(const BnBwdFinalize& a, int j, double sum_dy, double sum_dyz) {
+struct BnBwdColumn { float rstd, mean, gamma; };         // fetched ahead of the reduction (latency off the chain)
+__device__ __forceinline__ BnBwdColumn bn_bwd_column(const BnBwdFinalize& a, int j) {
+    BnBwdColumn c = {1.0f, 0.0f, 1.0f};
+    if (a.use_bn) { c.rstd = a.rstd[j]; c.mean = a.mean_z[j]; c.gamma = a.gamma[j]; }
+    return c;
+}
+__device__ __forceinline__ void bn_bwd_coefficients(const BnBwdFinalize& a, int j, double sum_dy, double sum_dyz,
+                                                    const BnBwdColumn& cv) {
     float k = 1.0f, c1 = 0.0f, c2 = 0.0f, rstd = 1.0f, mean = 0.0f;
     if (a.use_bn) {
-        rstd = a.rstd[j];
-        mean = a.mean_z[j];
-        k = a.gamma[j] * rstd;
+        rstd = cv.rstd;
+        mean = cv.mean;
+        k = cv.gamma * rstd;
         if (a.bn_mode == 0) {
-            c1 = static_cast<float>(sum_dy / a.count);
-            c2 = static_cast<float>(sum_dyz / a.count);
+            const double inv_n = 1.0 / a.count;                 // uniform; the only fp64 divide, off the dependent chain
+            c1 = static_cast<float>(sum_dy * inv_n);
+            c2 = static_cast<float>(sum_dyz * inv_n);
         }
     }
     const float bz = -k * c2 * rstd;
@@ -555,7 +563,7 @@ __global__ void bn_finalize_bwd_kernel(BnBwdFinalize a) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= a.H) return;
     const bool batch = a.use_bn && a.bn_mode == 0;
-    bn_bwd_coefficients(a, j, batch ? a.sums[j] : 0.0, batch ? a.sums[a.H + j] : 0.0);
+    bn_bwd_coefficients(a, j, batch ? a.sums[j] : 0.0, batch ? a.sums[a.H + j] : 0.0, bn_bwd_column(a, j));
 }
 
 // second stage of pass 1: LOCAL sums of dy and dy * zhat (fp64, what a data-parallel run all-reduces) and the
@@ -568,13 +576,15 @@ __global__ void bn_bwd_reduce_kernel(const float* __restrict__ pg, const float* 
     griddep_wait();
     __shared__ double sh[2][RED_LANES][RED_COLS];
     double s1, s2;
-    reduce_partials_2(pg, pgz, P, a.H, a.H, sh, s1, s2);
     const int col = blockIdx.x * RED_COLS + threadIdx.x;
+    BnBwdColumn cv = {1.0f, 0.0f, 1.0f};
+    if (threadIdx.y == 0 && col < a.H) cv = bn_bwd_column(a, col);
+    reduce_partials_2(pg, pgz, P, a.H, a.H, sh, s1, s2);
     double sum_dy = 0.0, sum_dyz = 0.0;
     if (threadIdx.y == 0 && col < a.H) {
         const double ik = static_cast<double>(a.inv_keep);
         sum_dy = ik * s1;
-        sum_dyz = ik * static_cast<double>(a.rstd[col]) * (s2 - static_cast<double>(a.mean_z[col]) * s1);
+        sum_dyz = ik * static_cast<double>(cv.rstd) * (s2 - static_cast<double>(cv.mean) * s1);
         dbeta[col] = static_cast<float>(sum_dy);                            // parameter gradients: LOCAL sums
         dgamma[col] = static_cast<float>(sum_dyz);
     }
@@ -582,7 +592,7 @@ __global__ void bn_bwd_reduce_kernel(const float* __restrict__ pg, const float* 
     if (threadIdx.y == 0 && col < a.H) {
         sums_out[col] = sum_dy;
         sums_out[a.H + col] = sum_dyz;
-        if (FUSED) bn_bwd_coefficients(a, col, sum_dy, sum_dyz);
+        if (FUSED) bn_bwd_coefficients(a, col, sum_dy, sum_dyz, cv);
     }
 }
 
