@@ -622,6 +622,11 @@ int lifter_flip_pose(const float* in, float* out, int64_t poses, int joints, int
     return flip_pose(in, out, poses, joints, dims, grad, static_cast<cudaStream_t>(stream));
 }
 
+int lifter_coco2h36m(const float* in, int in_channels, float* out, int64_t poses, float scale, const float* mean,
+                     const float* stdv, int mode, void* stream) {
+    return coco2h36m(in, in_channels, out, poses, scale, mean, stdv, mode, static_cast<cudaStream_t>(stream));
+}
+
 int lifter_affine_cols(const float* in, float* out, int64_t rows, int cols, const float* a, const float* b, int mode,
                        void* stream) {
     LIFTER_REQUIRE(in && out, "affine_cols: null pointer");

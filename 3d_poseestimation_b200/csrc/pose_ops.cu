@@ -38,6 +38,31 @@ __global__ void affine_cols_kernel(const float* __restrict__ in, float* __restri
     }
 }
 
+// COCO-17 -> H36M-17 (video2keypoints.py:14-57): each H36M joint is one COCO joint or the midpoint of two; the belly
+// (7) is the midpoint of the two midpoints root (0) and neck (8), evaluated in the reference's order of operations.
+__constant__ int c_coco_a[17] = {11, 12, 14, 16, 11, 13, 15, -1, 5, 0, 1, 5, 7, 9, 6, 8, 10};
+__constant__ int c_coco_b[17] = {12, 12, 14, 16, 11, 13, 15, -1, 6, 0, 2, 5, 7, 9, 6, 8, 10};
+
+__global__ void coco2h36m_kernel(const float* __restrict__ in, int C, float* __restrict__ out, long poses, float scale,
+                                 const float* __restrict__ mean, const float* __restrict__ stdv, int mode) {
+    griddep_launch();
+    griddep_wait();
+    const long idx = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;      // one (pose, joint, coord)
+    if (idx >= poses * 34) return;
+    const long b = idx / 34;
+    const int r = static_cast<int>(idx - b * 34), j = r >> 1, d = r & 1;
+    const float* x = in + b * 17 * C + d;
+    auto mid = [&](int jj) {
+        const int a = c_coco_a[jj], bb = c_coco_b[jj];
+        return a == bb ? x[a * C] : (x[a * C] + x[bb * C]) * 0.5f;
+    };
+    float v = j == 7 ? (mid(0) + mid(8)) * 0.5f : mid(j);
+    v *= scale;
+    if (mode == COLS_NORMALISE) v = (v - mean[r]) / stdv[r];
+    else if (mode == COLS_MINMAX_NORM) v = 2.0f * v - 1.0f;
+    out[idx] = v;
+}
+
 constexpr int PL_ROWS = 64;             // rows (= threads) per block
 constexpr int PL_MAXJ = 21;
 
@@ -202,6 +227,19 @@ int flip_pose(const float* in, float* out, int64_t poses, int J, int D, int grad
     const long n = poses * J * D;
     if (n == 0) return LIFTER_OK;
     LIFTER_CHECK_CUDA(launch_pdl("flip_pose_kernel", flip_pose_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, in, out, n, D, grad));
+    return LIFTER_OK;
+}
+
+int coco2h36m(const float* in, int in_channels, float* out, int64_t poses, float scale, const float* mean,
+              const float* stdv, int mode, cudaStream_t st) {
+    if (poses <= 0) return LIFTER_OK;
+    LIFTER_REQUIRE(in != nullptr && out != nullptr && in != out, "coco2h36m: bad pointers");
+    LIFTER_REQUIRE(in_channels >= 2 && in_channels <= 4, "coco2h36m: %d values per keypoint (x, y[, conf])", in_channels);
+    LIFTER_REQUIRE(mode == -1 || mode == COLS_MINMAX_NORM || (mode == COLS_NORMALISE && mean && stdv),
+                   "coco2h36m: mode %d needs -1 (none), 0 with mean/std, or 2", mode);
+    const long n = poses * 34;
+    LIFTER_CHECK_CUDA(launch_pdl("coco2h36m_kernel", coco2h36m_kernel, dim3(static_cast<unsigned>((n + 255) / 256)),
+                                 dim3(256), 0, st, in, in_channels, out, static_cast<long>(poses), scale, mean, stdv, mode));
     return LIFTER_OK;
 }
 

@@ -15,6 +15,12 @@ enum : int { COLS_NORMALISE = 0, COLS_DENORMALISE = 1, COLS_MINMAX_NORM = 2, COL
 int affine_cols(const float* in, float* out, int64_t rows, int cols, const float* a, const float* b, int mode,
                 cudaStream_t st);
 
+// Keypoint ingest (video2keypoints.py:14-57 coco2h36m + the /1000 pixel scaling and the normalisation of main.py:331-337
+// in the same pass): in [poses][17][in_channels] COCO order (x, y[, confidence]) -> out [poses][17][2] H36M order,
+// out = norm(scale * joint);  mode -1: none, COLS_NORMALISE: (v - mean) / std with [34] statistics, COLS_MINMAX_NORM: 2v - 1
+int coco2h36m(const float* in, int in_channels, float* out, int64_t poses, float scale, const float* mean,
+              const float* stdv, int mode, cudaStream_t st);
+
 struct PoseLossArgs {
     const float* pred; const float* target;     // [rows][J][3] (standardised when mean/std are given)
     const float* mean; const float* stdv;       // [J*3] nullable: joints = v * std + mean on both tensors

@@ -99,6 +99,41 @@ def flip_average(model, x2d, n_joints=17):
     return (a + b) / 2
 
 
+# ------------------------------------------------------------------------------------------------ keypoint ingest
+_COCO_A = [11, 12, 14, 16, 11, 13, 15, -1, 5, 0, 1, 5, 7, 9, 6, 8, 10]
+_COCO_B = [12, 12, 14, 16, 11, 13, 15, -1, 6, 0, 2, 5, 7, 9, 6, 8, 10]
+
+
+def coco2h36m(x, scale=1.0, mean=None, std=None, minmax=False):
+    """COCO-17 -> H36M-17 joint order (``phase1_lifting/video2keypoints.py:14-57``, ``phase2_opp_mb/run.py``).
+
+    A numpy ``(17, d)`` array goes through the reference's dataset-side arithmetic in numpy, as there.  A CUDA tensor
+    ``[..., 17, C]`` (C = 2, or 3 with a confidence column as in the AlphaPose JSON) goes through ONE kernel that also
+    applies what the loader does next: ``scale`` (the ``/1000`` of pixel coordinates) and then either the mean/std
+    standardisation (``main.py:334``) or ``2x - 1`` (``main.py:331``); the result ``[..., 17, 2]`` is the lifter input.
+    """
+    if isinstance(x, np.ndarray):
+        y = np.zeros(x.shape)
+        for j in range(17):
+            if j != 7:
+                y[j, :] = x[_COCO_A[j], :] if _COCO_A[j] == _COCO_B[j] else (x[_COCO_A[j], :] + x[_COCO_B[j], :]) * 0.5
+        y[7, :] = (y[0, :] + y[8, :]) * 0.5
+        return y
+    x = _dev(x, "coco2h36m")
+    if x.dim() < 2 or x.shape[-2] != 17 or x.shape[-1] not in (2, 3, 4):
+        raise ValueError(f"coco2h36m expects [..., 17, 2|3] keypoints, got {tuple(x.shape)}")
+    if (mean is None) != (std is None) or (minmax and mean is not None):
+        raise ValueError("coco2h36m: pass mean AND std, or minmax=True, or neither")
+    poses = x.numel() // (17 * x.shape[-1])
+    out = torch.empty(x.shape[:-1] + (2,), dtype=torch.float32, device=x.device)
+    m = _vec(mean, 34, x.device, "coco2h36m mean") if mean is not None else None
+    sd = _vec(std, 34, x.device, "coco2h36m std") if std is not None else None
+    mode = 0 if mean is not None else (2 if minmax else -1)
+    _cabi.check(_cabi.lib().lifter_coco2h36m(_cabi.ptr(x), int(x.shape[-1]), _cabi.ptr(out), poses, float(scale),
+                                              _cabi.ptr(m), _cabi.ptr(sd), mode, _cabi.stream_ptr()))
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ (de)normalisation
 class _AffineCols(torch.autograd.Function):
     @staticmethod

@@ -360,3 +360,91 @@ class LifterTrainer:
         self.m.copy_(sd["m"])
         self.v.copy_(sd["v"])
         self._sync_state()
+
+
+def evaluate(model, batches, loss="mse", flip=None, metric_std=None, n_samples=None, zero_centre=True):
+    """The validation loop of ``train_1.py:112-145`` without its per-batch host syncs.
+
+    ``batches`` yields ``(x, y)`` -- CUDA tensors, or CPU tensors (pinned for overlap), which are uploaded on a copy
+    stream one batch ahead.  Per batch: eval-mode forward, optional flip test-time augmentation, then ONE fused kernel
+    for the loss and the per-joint MPJPE sums, accumulated on the device; the host reads the totals once at the end.
+
+    flip: ``None``; ``"output"`` = ``(flip_pose(model(x)) + model(x)) / 2``, literally what ``train_1.py:128-134`` computes
+    (it flips the input only AFTER the second forward); ``"input"`` = ``(flip_pose(model(flip_pose(x))) + model(x)) / 2``
+    (``train_5.py:153-168``).  Returns ``{"loss": mean of the batch losses, "per_joint": sums / n_samples (J,),
+    "mpjpe_mm": mean(per_joint[1:]) * J/(J-1) * 1000 when zero_centre else mean(per_joint) * 1000, "n": samples}``.
+    """
+    from . import pose_losses as pl
+    if loss not in _LOSS:
+        raise ValueError(f"unknown loss {loss!r}: use 'mse', 'l1' or 'mpjpe'")
+    if flip not in (None, "output", "input"):
+        raise ValueError("flip must be None, 'output' or 'input'")
+    if model.output_size % 3 != 0:
+        raise ValueError("the fused loss works on (J, 3) joint outputs: o_dim must be a multiple of 3")
+    dev = model._flat.device
+    if dev.type != "cuda":
+        raise RuntimeError("evaluate needs the model on a B200 (no CPU path)")
+    lib = _cabi.lib()
+    J = model.output_size // 3
+    std = None if metric_std is None else torch.as_tensor(metric_std, dtype=torch.float32, device=dev).reshape(-1).contiguous()
+    was_training = model.training
+    model.eval()
+    cur = torch.cuda.current_stream(dev)
+    copy = torch.cuda.Stream(dev)
+    copy.wait_stream(cur)
+    ready, free = [torch.cuda.Event() for _ in range(2)], [torch.cuda.Event() for _ in range(2)]
+    slots = {}
+    acc = torch.zeros(1 + J, dtype=torch.float32, device=dev)          # [sum of batch losses, per-joint sums]
+    out = torch.zeros(1 + J, dtype=torch.float32, device=dev)
+    scratch, n_batches, n = None, 0, 0
+    try:
+        for i, (x, y) in enumerate(batches):
+            B = x.shape[0]
+            if not x.is_cuda:                                          # host batch: upload one batch ahead
+                s = i & 1
+                xs, ys = x.reshape(B, -1), y.reshape(B, -1)
+                slot = slots.get(s)
+                if slot is None or slot[0].shape != xs.shape or slot[1].shape != ys.shape:
+                    if slot is not None:
+                        torch.cuda.synchronize(dev)
+                    slot = (torch.empty(xs.shape, dtype=torch.float32, device=dev),
+                            torch.empty(ys.shape, dtype=torch.float32, device=dev))
+                    slots[s] = slot
+                with torch.cuda.stream(copy):
+                    if i >= 2:
+                        copy.wait_event(free[s])
+                    slot[0].copy_(xs, non_blocking=True)
+                    slot[1].copy_(ys, non_blocking=True)
+                    ready[s].record(copy)
+                cur.wait_event(ready[s])
+                x, y = slot
+            x = x.reshape(B, -1).float()
+            y = y.reshape(B, -1).float().contiguous()
+            pred = model.infer(x)
+            if flip == "output":
+                pred = (pl.flip_pose(pred.reshape(B, J, 3)) + pred.reshape(B, J, 3)) * 0.5
+            elif flip == "input":
+                other = model.infer(pl.flip_pose(x.reshape(B, J, -1)).reshape(B, -1))
+                pred = (pl.flip_pose(other.reshape(B, J, 3)) + pred.reshape(B, J, 3)) * 0.5
+            pred = pred.reshape(B, -1).contiguous()
+            need = _cabi.check(lib.lifter_loss_scratch_bytes(B, J))
+            if scratch is None or scratch.numel() < need:
+                scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+            _cabi.check(lib.lifter_loss(_cabi.ptr(pred), _cabi.ptr(y), B, J, _LOSS[loss], B, _cabi.ptr(std), None,
+                                        _cabi.ptr(scratch), _cabi.ptr(out), 1, _cabi.stream_ptr()))
+            acc[0] += out[0]                                           # out[1:] accumulates inside the kernel
+            if slots:
+                free[i & 1].record(cur)
+            n_batches += 1
+            n += B
+    finally:
+        if was_training:
+            model.train()
+    if n_batches == 0:
+        raise ValueError("evaluate: no batches")
+    acc[1:] = out[1:]
+    host = acc.cpu()                                                   # the one host read
+    n_samples = n if n_samples is None else int(n_samples)
+    per_joint = host[1:] / n_samples
+    mm = (per_joint[1:].mean() * (J / (J - 1)) if zero_centre else per_joint.mean()) * 1000.0
+    return {"loss": float(host[0]) / n_batches, "per_joint": per_joint, "mpjpe_mm": float(mm), "n": n}

@@ -177,6 +177,11 @@ int lifter_l1_grad(const float* a, const float* b, int64_t n, int row_len, int c
 /* flip_pose (phase3_direct/my_HybrIK/utils.py:372-396): x -> 1 - x (2D) or -x (3D) and left/right joints swapped;
  * in/out [poses][17][dims], dims 2 or 3, out != in.  grad = 1: the backward map (no "+1").                    */
 int lifter_flip_pose(const float* in, float* out, int64_t poses, int joints, int dims, int grad, void* stream);
+/* Keypoint ingest: coco2h36m (phase1_lifting/video2keypoints.py:14-57) fused with the pixel scaling (/1000) and the
+ * input normalisation of main.py:331-337.  in [poses][17][in_channels] (x, y[, confidence]) in COCO order, out
+ * [poses][17][2] in H36M order = norm(scale * joint); mode -1 none, 0 (v - mean) / std (34 statistics), 2: 2v - 1. */
+int lifter_coco2h36m(const float* in, int in_channels, float* out, int64_t poses, float scale, const float* mean,
+                     const float* stdv, int mode, void* stream);
 /* per-column statistics broadcast over rows: mode 0 (x - a) / b (main.py:334,337), 1 x * b + a (main.py:473-479,
  * train_5.py:42-47), 2 2x - 1 (main.py:331), 3 x * (a - b) + b with a = max, b = min (train_5.py:35-40)        */
 int lifter_affine_cols(const float* in, float* out, int64_t rows, int cols, const float* a, const float* b, int mode,

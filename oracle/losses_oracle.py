@@ -22,6 +22,7 @@ SURVEY.md §0 D3 / §8c): ``pinhole_reprojection`` + ``reprojection_l1`` and ``b
 """
 from __future__ import annotations
 
+import numpy as np
 import torch
 
 LEFT_JOINTS = [4, 5, 6, 11, 12, 13]      # utils.py:382
@@ -162,3 +163,24 @@ def bone_lengths(joints):
 def bone_length_l1(pred, target):
     """PARITY UNPINNED.  mean |bone(pred) - bone(target)|."""
     return l1_mean(bone_lengths(pred), bone_lengths(target))
+
+
+def coco2h36m(x):
+    """COCO-17 -> H36M-17 joints, ``phase1_lifting/video2keypoints.py:14-57`` (x: (..., 17, d) array or tensor)."""
+    a = [11, 12, 14, 16, 11, 13, 15, None, 5, 0, 1, 5, 7, 9, 6, 8, 10]
+    b = [12, 12, 14, 16, 11, 13, 15, None, 6, 0, 2, 5, 7, 9, 6, 8, 10]
+    x = np.asarray(x) if not torch.is_tensor(x) else x.numpy()       # input dtype kept: the sums round as in the reference
+    y = np.zeros(x.shape)
+    for j in range(17):
+        if j != 7:
+            y[..., j, :] = x[..., a[j], :] if a[j] == b[j] else (x[..., a[j], :] + x[..., b[j], :]) * 0.5
+    y[..., 7, :] = (y[..., 0, :] + y[..., 8, :]) * 0.5
+    return y
+
+
+def ingest_keypoints(coco, mean=None, std=None, minmax=False, scale=1e-3):
+    """coco2h36m, pixel / 1000, then ``(x - mean) / std`` (main.py:334) or ``2x - 1`` (main.py:331)."""
+    y = coco2h36m(np.asarray(coco)[..., :2]) * scale
+    if mean is not None:
+        return (y - np.asarray(mean)) / np.asarray(std)
+    return 2 * y - 1 if minmax else y

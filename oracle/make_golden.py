@@ -44,6 +44,29 @@ def ref_flip_pose():
     return ns["flip_pose"]
 
 
+def ref_coco2h36m():
+    src = open(os.path.join(REF, "phase1_lifting/video2keypoints.py")).read().splitlines()
+    ns = {"np": np}
+    exec("\n".join(src[13:57]), ns)       # video2keypoints.py:14-57 (def coco2h36m; the file imports cv2/matplotlib)
+    return ns["coco2h36m"]
+
+
+def ingest_case():
+    """Keypoint ingest: the reference's coco2h36m on AlphaPose-shaped (17, 3) rows, then /1000 and the two
+    normalisations of main.py:331-337."""
+    f = ref_coco2h36m()
+    rs = np.random.RandomState(23)
+    N = 9
+    kp = np.concatenate([rs.uniform(0, 1000, (N, 17, 2)), rs.uniform(0, 1, (N, 17, 1))], axis=2).astype(np.float32)
+    h36m = np.stack([f(kp[i, :, :2]) for i in range(N)])                    # float64, reference arithmetic
+    P = os.path.join(REF, "phase1_lifting")
+    m2, s2 = np.load(os.path.join(P, "mean_train_2d.npy")), np.load(os.path.join(P, "std_train_2d.npy"))
+    scaled = h36m / 1000
+    np.savez(os.path.join(GOLD, "ingest.npz"), coco=kp, h36m=h36m, standardised=(scaled - m2) / s2,
+             minmax=2 * scaled - 1)
+    print("wrote ingest", h36m.shape)
+
+
 class MaskedDropout(torch.nn.Module):
     """Stands in for ``torch.nn.Dropout(p)`` in the reference module; same arithmetic, external mask."""
 
@@ -233,6 +256,9 @@ def train_curve_case():
 if __name__ == "__main__":
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(8)
+    if len(sys.argv) > 1 and sys.argv[1] == "ingest":      # only the keypoint-ingest vectors
+        ingest_case()
+        sys.exit(0)
     lifter_case("small", 34, 51, 64, 2, 16, 0.5, True, seed=1, store_weights=True)
     lifter_case("small_nobn", 34, 51, 64, 1, 8, 0.25, False, seed=2, store_weights=True)
     lifter_case("h1024", 34, 51, 1024, 2, 32, 0.5, True, seed=3, store_weights=False)
@@ -241,3 +267,4 @@ if __name__ == "__main__":
     losses_case()
     adam_case()
     train_curve_case()
+    ingest_case()

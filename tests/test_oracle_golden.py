@@ -187,3 +187,13 @@ def test_training_curve_matches_reference(golden_dir):
         losses.append(float(r["loss"]))
     np.testing.assert_allclose(losses, g["losses"], rtol=2e-3)
     np.testing.assert_allclose(params["w2.bias"].numpy(), g["final_w2_bias"], rtol=1e-2, atol=2e-4)
+
+
+def test_keypoint_ingest_matches_reference(golden_dir):
+    """coco2h36m (video2keypoints.py:14-57) + /1000 + the normalisations of main.py:331-337."""
+    g = dict(np.load(os.path.join(golden_dir, "ingest.npz")))
+    st = dict(np.load(os.path.join(golden_dir, "h36m_stats.npz")))
+    np.testing.assert_array_equal(L.coco2h36m(g["coco"][..., :2]), g["h36m"])
+    np.testing.assert_allclose(L.ingest_keypoints(g["coco"], st["mean_train_2d"], st["std_train_2d"]), g["standardised"],
+                               rtol=1e-12)
+    np.testing.assert_allclose(L.ingest_keypoints(g["coco"], minmax=True), g["minmax"], rtol=1e-12)
