@@ -93,3 +93,33 @@ def test_config4_phase5_loop_body(pkg):
     cos = torch.nn.functional.cosine_similarity(m.w2.weight.grad.cpu().reshape(-1), ps["w2.weight"].grad.reshape(-1), dim=0)
     assert float(cos) > 0.98
     assert int(m.state_dict()["batch_norm1.num_batches_tracked"]) == 4
+
+
+def test_learned_projector_shape(pkg):
+    """the phase-5 learned projector reuses the same module at a tiny width,
+    ``LinearModel(i_dim=51, o_dim=34, linear_size=64)`` (backup_june8.py:72): eval output and one training step's
+    gradients against the oracle."""
+    i_dim, o_dim, H, S, B, seed = 51, 34, 64, 2, 96, 13
+    params, buffers = lo.numpy_init(i_dim, o_dim, H, S, seed, randomize_bn=True)
+    m = pkg.LinearModel(i_dim, o_dim, linear_size=H, num_stage=S, p_dropout=0.5, BN=True)
+    m.load_state_dict({**params, **buffers})
+    m = m.cuda()
+    rs = np.random.RandomState(seed)
+    x, y = T(rs.normal(0, 1, (B, 17, 3)).astype(np.float32)), T(rs.normal(0, 1, (B, o_dim)).astype(np.float32))
+    m.eval()
+    with torch.no_grad():
+        out = m(x.cuda())
+        ref = lo.lifter_forward(params, buffers, x, num_stage=S, training=False)[0]
+    assert out.shape == (B, o_dim)
+    assert rel_l2(out.cpu(), ref) < 5e-3
+    m.train()
+    m.dropout_seed, m.dropout_step = 21, 0
+    loss = ((m(x.cuda()) - y.cuda()) ** 2).mean()
+    loss.backward()
+    masks = [dropout_keep_mask(B, H, site, 0, 21, 0.5) for site in range(2 * S + 1)]
+    r = lo.lifter_forward_backward(params, buffers, x, lambda o: ((o - y) ** 2).mean(), num_stage=S, training=True,
+                                   p_dropout=0.5, masks=masks)
+    np.testing.assert_allclose(float(loss), float(r["loss"]), rtol=2e-2)
+    g = {k: p.grad.cpu() for k, p in m.named_parameters()}
+    assert rel_l2(g["w2.weight"], r["grads"]["w2.weight"]) < 5e-2
+    assert rel_l2(g["w1.weight"], r["grads"]["w1.weight"]) < 0.15
