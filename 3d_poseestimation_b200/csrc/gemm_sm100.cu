@@ -462,7 +462,9 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
             }
             if (threadIdx.x == 128 && it < 8) TL_STAMP(6 + 3 * it);
         }
-        if (lane == 0) tma_store_wait_all<0>();                    // smem must outlive the last bulk store
+        // smem must outlive the READS of the last bulk stores; their global writes complete with the grid (what the
+        // next kernel's griddepcontrol.wait / stream order waits for), so the CTA need not sit through them
+        if (lane == 0) tma_store_wait_read<0>();
     }
 
     tcgen05_fence_before();
