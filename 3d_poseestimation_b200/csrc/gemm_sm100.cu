@@ -52,17 +52,20 @@ struct Cfg {
     static constexpr int NCH = COLS_PER_WARP / 32;                              // 32-column chunks per epilogue warp
     static constexpr int NUM_THREADS = 128 + 32 * EPI_WARPS;
     static constexpr int STG_BYTES = EPI_WARPS * STAGING_BYTES_PER_WARP;
-    static constexpr int FIXED_BYTES = STG_BYTES + 2 * BLOCK_N * 4 + 1024;      // staging + affine + barriers
-    static constexpr int STAGES_FIT = (SMEM_LIMIT - FIXED_BYTES) / STAGE_BYTES;
-    static constexpr int STAGES = STAGES_FIT > 8 ? 8 : STAGES_FIT;
-    static constexpr int OFF_A = 0;
-    static constexpr int OFF_B = OFF_A + STAGES * A_STAGE_BYTES;
-    static constexpr int OFF_STG = OFF_B + STAGES * B_STAGE_BYTES;
+    // shared memory: [staging | affine | barriers | TMEM pointer] then the operand ring, A stages followed by B stages.
+    // The ring is last so that a launch asking for fewer stages also asks for less shared memory (room for a small
+    // kernel of another stream on the same SM).
+    static constexpr int MAX_STAGES = 8;
+    static constexpr int OFF_STG = 0;
     static constexpr int OFF_AFFINE = OFF_STG + STG_BYTES;                      // scale[BLOCK_N], shift[BLOCK_N]
     static constexpr int OFF_BAR = OFF_AFFINE + 2 * BLOCK_N * 4;                // full[S], empty[S], tfull[2], tempty[2], resid[EPI_WARPS][2]
-    static constexpr int NUM_BARS = 2 * STAGES + 4 + 2 * EPI_WARPS;
+    static constexpr int NUM_BARS = 2 * MAX_STAGES + 4 + 2 * EPI_WARPS;
     static constexpr int OFF_TMEM_PTR = OFF_BAR + NUM_BARS * 8;
-    static constexpr int SMEM_BYTES = OFF_TMEM_PTR + 16;
+    static constexpr int OFF_RING = (OFF_TMEM_PTR + 16 + 1023) / 1024 * 1024;   // SWIZZLE_128B tiles: 1024 B aligned
+    static constexpr int STAGES_FIT = (SMEM_LIMIT - OFF_RING) / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_FIT > MAX_STAGES ? MAX_STAGES : STAGES_FIT;
+    static constexpr int smem_bytes(int stages) { return OFF_RING + stages * STAGE_BYTES; }
+    static constexpr int SMEM_BYTES = OFF_RING + STAGES * STAGE_BYTES;
     static constexpr int TMEM_COLS = 2 * BLOCK_N;                               // 128 / 256 / 512: powers of two
     static_assert(STAGES >= 3, "operand ring too shallow");
     static_assert(SMEM_BYTES <= SMEM_LIMIT, "exceeds 227 KB of shared memory");
@@ -146,8 +149,10 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
     const uint32_t lane = threadIdx.x & 31;
 
     const uint32_t bar_full = smem_base + C::OFF_BAR;
-    const uint32_t bar_empty = bar_full + C::STAGES * 8;
-    const uint32_t bar_tfull = bar_empty + C::STAGES * 8;
+    const uint32_t bar_empty = bar_full + C::MAX_STAGES * 8;
+    const uint32_t bar_tfull = bar_empty + C::MAX_STAGES * 8;
+    const uint32_t ring_a = smem_base + C::OFF_RING;                       // p.stages A tiles, then p.stages B tiles
+    const uint32_t ring_b = ring_a + static_cast<uint32_t>(p.stages) * A_STAGE_BYTES;
     const uint32_t bar_tempty = bar_tfull + 2 * 8;
     const uint32_t bar_resid = bar_tempty + 2 * 8;                 // [EPI_WARPS][2]
     uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem + C::OFF_TMEM_PTR);
@@ -161,7 +166,7 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
         if (p.out_mode != OUT_32_DIRECT) tma_prefetch_desc(&p.tmD);
         if (p.has_residual) tma_prefetch_desc(&p.tmR);
     } else if (warp == 1 && lane == 0) {
-        for (int i = 0; i < C::STAGES; ++i) {
+        for (int i = 0; i < p.stages; ++i) {
             mbar_init(bar_full + i * 8, 1);            // the (leader's) producer arms it; TMA bytes complete it
             mbar_init(bar_empty + i * 8, 1);           // one MMA-commit arrival
         }
@@ -206,8 +211,8 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                     // pair: only the leader arms its barrier, with the bytes of both CTAs
                     if (!TWO_SM) mbar_arrive_expect_tx(full, C::STAGE_BYTES);
                     else if (crank == 0) mbar_arrive_expect_tx(full, 2 * C::STAGE_BYTES);
-                    const uint32_t sa = smem_base + C::OFF_A + stage * A_STAGE_BYTES;
-                    const uint32_t sb = smem_base + C::OFF_B + stage * C::B_STAGE_BYTES;
+                    const uint32_t sa = ring_a + stage * A_STAGE_BYTES;
+                    const uint32_t sb = ring_b + stage * C::B_STAGE_BYTES;
                     if (!p.a_mn_major) {
                         if (TWO_SM) tma_load_2d_2sm(&p.tmA, sa, full, kb * BLOCK_K, m_blk * BLOCK_M);
                         else tma_load_2d(&p.tmA, sa, full, kb * BLOCK_K, m_blk * BLOCK_M);
@@ -238,8 +243,8 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
         if (!TWO_SM || crank == 0) {
             const uint32_t idesc = make_idesc(p.fmt, p.a_mn_major, p.b_mn_major, BLOCK_M * CL, BLOCK_N);
             const uint32_t a_kstep = (p.a_mn_major ? 2048u : 32u) >> 4, b_kstep = (p.b_mn_major ? 2048u : 32u) >> 4;
-            const uint64_t da0 = make_smem_desc(smem_base + C::OFF_A, p.a_mn_major ? 8192u : 0u);
-            const uint64_t db0 = make_smem_desc(smem_base + C::OFF_B, p.b_mn_major ? 8192u : 0u);
+            const uint64_t da0 = make_smem_desc(ring_a, p.a_mn_major ? 8192u : 0u);
+            const uint64_t db0 = make_smem_desc(ring_b, p.b_mn_major ? 8192u : 0u);
             const uint32_t a_hi = static_cast<uint32_t>(da0 >> 32), b_hi = static_cast<uint32_t>(db0 >> 32);
             const uint32_t a_lo0 = static_cast<uint32_t>(da0), b_lo0 = static_cast<uint32_t>(db0);
             uint32_t stage = 0, phase = 0;
@@ -551,7 +556,7 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     p.num_tiles = ceil_div(p.num_m_blocks, CL) * p.num_n_blocks * p.splits;
     cudaLaunchConfig_t cfg = {};
     cfg.blockDim = dim3(C::NUM_THREADS);
-    cfg.dynamicSmemBytes = C::SMEM_BYTES;
+    cfg.dynamicSmemBytes = C::smem_bytes(p.stages);
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
