@@ -299,7 +299,8 @@ def gpu_arm(args, rank, world, local_rank):
                 "gpu_launches": launches_per_step * steps,
                 "model_flop_per_pose": flop,
                 "model_tflops": value * flop / 1e12 / world,
-                "roofline": roof}
+                "roofline": roof,
+                "roofline_hbm": hbm_rooflines(cabi, dev, pk, batch) if (rank == 0 and workload != "eval") else None}
 
     line = measure(args.workload, args.steps, args.warmup, True)
     profiling = bool(os.environ.get("LIFTER_BENCH_NO_CPU"))     # under ncu: skip the untimed extras
@@ -373,6 +374,58 @@ def gemm_roofline(cabi, dev, rows, fmt, pk, H=H):
     return {"bound": "tensor", "kernel": f"lifter_gemm_kernel<256, 2-SM> M={rows} N=K={H} (+affine+ReLU epilogue)",
             "achieved": achieved, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"],
             "peak_source": pk["source"] + " burst bf16 (kernel timed alone)", "us_per_launch": us, **ncu_traffic(rows, H)}
+
+
+def hbm_rooflines(cabi, dev, pk, batch):
+    """The HBM-bound kernels of the step timed alone with CUDA events: fused Adam over the flat buffer
+    (28 B/param + 2 B operand copy) and the fused loss + gradient + metric kernel (612 B/pose)."""
+    import torch
+    lib = cabi.lib()
+    n = 4_296_768                                     # flat buffer of the 1024-wide, 2-block lifter (tensors padded to 32)
+    # three full sets of (p, g, m, v) = 206 MB, rotated: no launch finds its operands in the 126 MB L2
+    sets = [[torch.randn(n, device=dev) * 0.01 for _ in range(3)] + [torch.rand(n, device=dev) * 1e-4] for _ in range(3)]
+    st = cabi.stream_ptr()
+    tick = [0]
+
+    def time_us(fn, reps=30):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps * 1e3
+    out = []
+    def adam():
+        p, g, m, v = sets[tick[0] % 3]
+        tick[0] += 1
+        cabi.check(lib.lifter_adam_step(cabi.ptr(p), cabi.ptr(g), cabi.ptr(m), cabi.ptr(v), n, 1e-4, 0.9, 0.999, 1e-8,
+                                        0.0, 0, 1, 1.0, st))
+    us = time_us(adam)
+    gbs = 28.0 * n / (us * 1e-6) / 1e9
+    out.append({"bound": "hbm", "kernel": f"adam_kernel over {n} fp32 parameters (28 B/param = 120 MB per launch; "
+                "operand sets rotated past the L2 capacity)", "achieved": gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": gbs / pk["hbm"],
+                "us_per_launch": us, "traffic": None})
+    nrot = 40                                           # 40 x 5 MB of (pred, target, dpred): past the L2 capacity too
+    preds = [torch.randn(batch, O_DIM, device=dev) for _ in range(nrot)]
+    tgts = [torch.randn(batch, O_DIM, device=dev) for _ in range(nrot)]
+    dpreds = [torch.empty(batch, O_DIM, device=dev) for _ in range(nrot)]
+    scratch = torch.empty(cabi.check(lib.lifter_loss_scratch_bytes(batch, 17)), dtype=torch.uint8, device=dev)
+    res = torch.zeros(18, device=dev)
+    def loss():
+        i = tick[0] % nrot
+        tick[0] += 1
+        cabi.check(lib.lifter_loss(cabi.ptr(preds[i]), cabi.ptr(tgts[i]), batch, 17, cabi.LOSS_MSE, batch, None,
+                                   cabi.ptr(dpreds[i]), cabi.ptr(scratch), cabi.ptr(res), 0, st))
+    us = time_us(loss)
+    gbs = 612.0 * batch / (us * 1e-6) / 1e9
+    out.append({"bound": "hbm", "kernel": f"fused_loss_kernel + loss_finalize_kernel, {batch} poses (612 B/pose = "
+                f"{612 * batch / 1e6:.1f} MB: launch-latency-bound at this size)", "achieved": gbs, "peak": pk["hbm"],
+                "unit": "GB/s", "frac": gbs / pk["hbm"], "us_per_launch": us, "traffic": None})
+    return out
 
 
 def main():
