@@ -106,7 +106,7 @@ int wgrad_splits(int M, int N, int K) {
 struct ScratchWs {                      // backward workspace
     uint16_t *dO, *G[2], *Gh, *dz[2];   // dz alternates by layer: the weight-gradient GEMM of layer l reads dz[l & 1]
                                         // on the side stream while layer l-1 writes the other one
-    float *pA, *pB, *coef, *slabs;
+    float *pA, *pB, *pO, *coef, *slabs;    // pO: output-layer bias partials (read on the side stream)
     std::vector<double*> bsums;
     std::vector<size_t> bsums_off;
     size_t bytes;
@@ -127,6 +127,7 @@ void carve_scratch(const Layout& lay, int64_t B, void* base, ScratchWs* w) {
     if (R64 * 64 * 4 > pbytes) pbytes = R64 * 64 * 4;
     w->pA = c.take<float>(pbytes);
     w->pB = c.take<float>(pbytes);
+    w->pO = c.take<float>(R64 * 64 * 4);
     w->coef = c.take<float>(3 * lay.H * 4);
     w->bsums.resize(lay.L); w->bsums_off.resize(lay.L);
     for (int l = 0; l < lay.L; ++l) {
@@ -370,10 +371,11 @@ static int bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t* t, vo
     const int B = static_cast<int>(t->batch), H = lay.H;
     const uint16_t* ops = static_cast<const uint16_t*>(t->operands);
     // grad_out -> 16-bit padded, bias gradient of the output layer
-    LIFTER_PROPAGATE(prep_grad_out(t->grad_out, B, lay.O, lay.Op, t->fmt, b.dO, b.pA, st));
-    LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(B, lay.Op), lay.O, lay.Op, t->grad_params + lay.p_off[lay.t_b2()], st));
-    // dW2 = dOut^T a_{L-1}
+    LIFTER_PROPAGATE(prep_grad_out(t->grad_out, B, lay.O, lay.Op, t->fmt, b.dO, b.pO, st));
+    // db2 and dW2 = dOut^T a_{L-1} feed only the optimiser: side stream when there is one
     if (side != nullptr) LIFTER_PROPAGATE(side_fork(side, lay.L, st));
+    LIFTER_PROPAGATE(reduce_rows_f32(b.pO, ew_partial_rows(B, lay.Op), lay.O, lay.Op, t->grad_params + lay.p_off[lay.t_b2()],
+                                     side != nullptr ? side->st : st));
     LIFTER_PROPAGATE(wgrad(lay, t, b, b.dO, lay.Op, lay.Op, w.a[lay.L - 1], H, H, lay.O, H,
                            t->grad_params + lay.p_off[lay.t_w2()], side != nullptr ? side->st : st));
     if (side != nullptr) LIFTER_CHECK_CUDA(cudaEventRecord(side->done[lay.L], side->st));
