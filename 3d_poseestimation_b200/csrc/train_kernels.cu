@@ -667,14 +667,17 @@ __global__ void __launch_bounds__(EW_THREADS) prep_grad_out_kernel(const float* 
 
 // rows owned by one block of a column-reducing kernel: a multiple of the rows one unrolled iteration covers, sized
 // so that at most 2 x SM-count blocks (= partial rows) exist
-static int rows_per_block_for(int64_t rows, int H, int blocks_per_sm) {
-    const int64_t step = static_cast<int64_t>(EW_THREADS / (H / 8)) * EW_UNROLL;
+static int rows_per_block_for(int64_t rows, int H, int blocks_per_sm, bool whole_groups = true) {
+    const int64_t rpb = EW_THREADS / (H / 8);
+    // whole_groups: a multiple of the rows one unrolled iteration covers (the unchecked fast path of the apply kernel);
+    // otherwise a multiple of the rows of ONE iteration, which fills the resident block slots more evenly
+    const int64_t step = whole_groups ? rpb * EW_UNROLL : rpb;
     const int64_t steps = (rows + step - 1) / step;
     const int64_t max_blocks = static_cast<int64_t>(num_sms()) * blocks_per_sm;
     const int64_t steps_per_block = (steps + max_blocks - 1) / max_blocks;
     return static_cast<int>(steps_per_block * step);
 }
-int ew_rows_per_block(int64_t rows, int H) { return rows_per_block_for(rows, H, 2); }
+int ew_rows_per_block(int64_t rows, int H) { return rows_per_block_for(rows, H, 2, false); }
 int ew_partial_rows(int64_t rows, int H) {
     const int rpb = ew_rows_per_block(rows, H);
     return static_cast<int>((rows + rpb - 1) / rpb);
@@ -711,7 +714,11 @@ int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st) {
     const uint32_t thr = dropout_threshold(a.p);
     const PhiloxKeys keys = philox_round_keys(a.seed);
     const float inv_keep = (a.apply_dropout && a.p < 1.0f) ? 1.0f / (1.0f - a.p) : (a.apply_dropout ? 0.0f : 1.0f);
-    const int rpb = rows_per_block_for(a.rows, a.H, 4);
+    // whole unrolled groups per block keep the unchecked fast path; when that leaves more than a tenth of the resident
+    // block slots empty (small batches), even filling wins over the per-row range checks
+    int rpb = rows_per_block_for(a.rows, a.H, 4, true);
+    const long slots = static_cast<long>(num_sms()) * 4;
+    if ((a.rows + rpb - 1) / rpb < slots - slots / 10) rpb = rows_per_block_for(a.rows, a.H, 4, false);
     const unsigned blocks = static_cast<unsigned>((a.rows + rpb - 1) / rpb);
     if (a.fmt == FMT_BF16)
         LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_BF16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, thr, inv_keep, keys));
