@@ -213,14 +213,22 @@ class LifterTrainer:
             raise RuntimeError(f"target must be a float32 CUDA tensor of {x.shape[0]} x {model.output_size} values")
         return x, y.contiguous()
 
-    def step(self, x, y, accumulate_metric=False):
-        """x: (B, 17, 2) or (B, i_dim) fp32 CUDA, y: (B, 17, 3) or (B, o_dim).  Returns the device loss scalar."""
+    def step(self, x, y, accumulate_metric=False, _loss_copy=None):
+        """x: (B, 17, 2) or (B, i_dim) fp32 CUDA, y: (B, 17, 3) or (B, o_dim).  Returns the device loss scalar.
+        (``_loss_copy``: a one-element device tensor that also receives the loss -- ``run_epoch``'s per-slot mailbox.)"""
         model = self.model
         x, y = self._check_xy(x, y)
         B = x.shape[0]
         model.train()
         if self.use_graph and B >= 2 and (self.world == 1 or self.graph_collectives):
-            return self._step_graph(x, y, bool(accumulate_metric))
+            return self._step_graph(x, y, bool(accumulate_metric), _loss_copy)
+        loss = self._step_eager(x, y, B, accumulate_metric)
+        if _loss_copy is not None:
+            _loss_copy.copy_(loss.reshape(1))
+        return loss
+
+    def _step_eager(self, x, y, B, accumulate_metric):
+        model = self.model
         b = self._buffers(B, x.device)
         if self.world > 1 and self.use_graph and B >= 2:
             # data parallel: same kernel sequence driven by the device step state (it is also the epoch of the
@@ -235,31 +243,53 @@ class LifterTrainer:
         self._state_stale = True                                  # the device step state did not see this step
         return self.loss_out[0]
 
-    def _step_graph(self, x, y, accumulate_metric):
-        """Replay of the captured step (one CUDA graph per batch size): no per-kernel host work."""
+    def _capture(self, xin, yin, B, accumulate_metric, loss_copy=None):
+        model = self.model
+        b = self._buffers(B, xin.device)
+        model._operands(model._fmt_code(model.train_format))              # packed before the capture starts
+        self._sync_state()
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.graph(graph, stream=side):
+            self._enqueue(xin, yin, b, accumulate_metric, self.state)
+            if loss_copy is not None:
+                loss_copy.copy_(self.loss_out[:1])
+        return graph
+
+    def _step_graph(self, x, y, accumulate_metric, loss_copy=None):
+        """Replay of the captured step: no per-kernel host work.  One graph per batch size reads its inputs from static
+        buffers the batch is copied into; input tensors that come back at the same addresses (a prefetch slot of
+        ``run_epoch``, a resident benchmark batch) get a graph of their own that reads them in place."""
         model = self.model
         B = x.shape[0]
         key = (B, accumulate_metric, model._flat.data_ptr())
         g = self._graphs.get(key)
         if g is None:
-            b = self._buffers(B, x.device)
             xs, ys = torch.empty_like(x), torch.empty_like(y)
-            model._operands(model._fmt_code(model.train_format))          # packed before the capture starts
-            self._sync_state()
-            torch.cuda.synchronize()
-            graph = torch.cuda.CUDAGraph()
-            side = torch.cuda.Stream()
-            side.wait_stream(torch.cuda.current_stream())
-            with torch.cuda.graph(graph, stream=side):
-                self._enqueue(xs, ys, b, accumulate_metric, self.state)
-            g = (graph, xs, ys)
+            g = {"generic": (self._capture(xs, ys, B, accumulate_metric), xs, ys), "in_place": {}, "seen": {}}
             self._graphs = {key: g}                                       # keep one batch size resident
-        graph, xs, ys = g
         if self._state_stale:
             self._sync_state()
-        xs.copy_(x, non_blocking=True)
-        ys.copy_(y, non_blocking=True)
-        graph.replay()
+        ptrs = (x.data_ptr(), y.data_ptr(), 0 if loss_copy is None else loss_copy.data_ptr())
+        graph = g["in_place"].get(ptrs)
+        if graph is None:
+            seen = g["seen"]
+            seen[ptrs] = seen.get(ptrs, 0) + 1
+            if seen[ptrs] >= 3 and len(g["in_place"]) < 4:                # the same buffers for the third time
+                graph = g["in_place"][ptrs] = self._capture(x, y, B, accumulate_metric, loss_copy)
+            elif len(seen) > 256:
+                seen.clear()
+        if graph is None:
+            graph, xs, ys = g["generic"]
+            xs.copy_(x, non_blocking=True)
+            ys.copy_(y, non_blocking=True)
+            graph.replay()
+            if loss_copy is not None:
+                loss_copy.copy_(self.loss_out[:1])
+        else:
+            graph.replay()
         model._stats_epoch += 1
         self._after_step()
         return self.loss_out[0]
@@ -278,11 +308,13 @@ class LifterTrainer:
         cur = torch.cuda.current_stream(dev)
         pipe = self._bufs.get("pipe")
         if pipe is None:
-            pipe = {"copy": torch.cuda.Stream(dev), "slots": {}, "ready": [torch.cuda.Event() for _ in range(2)],
-                    "free": [torch.cuda.Event() for _ in range(2)]}
+            pipe = {"copy": torch.cuda.Stream(dev), "down": torch.cuda.Stream(dev), "slots": {},
+                    "ready": [torch.cuda.Event() for _ in range(2)], "free": [torch.cuda.Event() for _ in range(2)],
+                    "read": [torch.cuda.Event() for _ in range(2)]}
             self._bufs["pipe"] = pipe
-        copy = pipe["copy"]
+        copy, down = pipe["copy"], pipe["down"]
         copy.wait_stream(cur)
+        down.wait_stream(cur)
         losses, n = None, 0
         for i, (xh, yh) in enumerate(batches):
             if xh.is_cuda or yh.is_cuda:
@@ -296,26 +328,33 @@ class LifterTrainer:
                 if slot is not None:
                     torch.cuda.synchronize(dev)                    # a batch-size change: let the old slot drain
                 slot = (key, torch.empty(xh.shape, dtype=torch.float32, device=dev),
-                        torch.empty(yh.shape, dtype=torch.float32, device=dev))
+                        torch.empty(yh.shape, dtype=torch.float32, device=dev),
+                        torch.zeros(1, dtype=torch.float32, device=dev))
                 pipe["slots"][s] = slot
-            _, xd, yd = slot
+            _, xd, yd, lossd = slot
             with torch.cuda.stream(copy):
                 if i >= 2:
-                    copy.wait_event(pipe["free"][s])               # step i-2 has consumed this slot
+                    copy.wait_event(pipe["free"][s])               # step i-2 has consumed this slot ...
+                    copy.wait_event(pipe["read"][s])               # ... and its loss has left the slot's mailbox
                 xd.copy_(xh, non_blocking=True)
                 yd.copy_(yh, non_blocking=True)
                 pipe["ready"][s].record(copy)
             cur.wait_event(pipe["ready"][s])
-            self.step(xd, yd, accumulate_metric=accumulate_metric)
+            self.step(xd, yd, accumulate_metric=accumulate_metric, _loss_copy=lossd)   # the step leaves its loss in lossd
             pipe["free"][s].record(cur)
             if losses is None or n == losses.numel():
                 grown = torch.empty(max(256, 2 * n), dtype=torch.float32).pin_memory()
                 if n:
-                    cur.synchronize()
+                    torch.cuda.synchronize(dev)
                     grown[:n] = losses[:n]
                 losses = grown
-            losses[n:n + 1].copy_(self.loss_out[:1], non_blocking=True)    # D2H of this step's loss, no host stall
+            with torch.cuda.stream(down):
+                # D2H of this step's loss on a third stream: neither the compute stream nor the uploads wait for it
+                down.wait_event(pipe["free"][s])
+                losses[n:n + 1].copy_(lossd, non_blocking=True)
+                pipe["read"][s].record(down)
             n += 1
+        cur.wait_stream(down)
         cur.synchronize()
         out = losses[:n].clone() if n else torch.empty(0)
         if self.world > 1 and n:

@@ -272,7 +272,7 @@ def gpu_arm(args, rank, world, local_rank):
             ms, clocks = timed(step, steps, warmup), None
 
         # end to end through the public API with host buffers (wall clock around synchronising steps)
-        run_e2e(max(2, warmup // 2))
+        run_e2e(max(8, warmup))                                # also past the point where run_epoch's slots get their graphs
         barrier()
         t0 = time.perf_counter()
         n_e2e = max(3, steps // 2)
