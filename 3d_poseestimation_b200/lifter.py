@@ -280,51 +280,72 @@ class LinearModel(torch.nn.Module):
         as a three-stage pipeline.  ``x`` is an fp32 CPU tensor (pinned for asynchronous copies), the result an fp32
         CPU tensor (pinned when allocated here).  Chunk i+1 uploads and chunk i-1 downloads while chunk i computes.
         """
-        if x.is_cuda or x.dtype != torch.float32:
-            raise RuntimeError("infer_host takes an fp32 CPU tensor; call infer() with device tensors")
+        return self.infer_host_batches([x], None if out is None else [out], chunk_rows, in_stats, out_stats)[0]
+
+    def infer_host_batches(self, batches, outs=None, chunk_rows=65536, in_stats=None, out_stats=None):
+        """``infer_host`` over an iterable of host batches with ONE pipeline: the upload of the next batch's first chunk
+        and the download of the previous batch's last chunk overlap the compute across batch boundaries, and the host
+        waits once, at the end.  Returns the list of output tensors (``outs[i]`` when given).  Large chunks by default:
+        across batches the copies hide anyway, and each chunk costs ~0.1 ms of host-side launch work."""
         dev = self._flat.device
         if dev.type != "cuda":
             raise RuntimeError("the lifter runs on a B200 only (no CPU path): move the model with .cuda() first")
-        x = x.reshape(x.shape[0], -1)
-        B, I, O = x.shape[0], self.input_size, self.output_size
-        if x.shape[1] != I:
-            raise RuntimeError(f"expected {I} input values per pose, got {x.shape[1]}")
-        if out is None:
-            out = torch.empty(B, O, dtype=torch.float32).pin_memory()
-        rows_max = max(1, min(int(chunk_rows), B))
+        I, O = self.input_size, self.output_size
+        cur = torch.cuda.current_stream(dev)
+        pipe, results, i = None, [], 0
+        for k, x in enumerate(batches):
+            if x.is_cuda or x.dtype != torch.float32:
+                raise RuntimeError("infer_host takes fp32 CPU tensors; call infer() with device tensors")
+            x = x.reshape(x.shape[0], -1)
+            B = x.shape[0]
+            if x.shape[1] != I:
+                raise RuntimeError(f"expected {I} input values per pose, got {x.shape[1]}")
+            out = outs[k] if outs is not None else torch.empty(B, O, dtype=torch.float32).pin_memory()
+            results.append(out)
+            rows_max = max(1, min(int(chunk_rows), max(B, 1)))
+            if pipe is None or pipe["rows"] < rows_max:
+                if pipe is not None:
+                    torch.cuda.synchronize(dev)                    # a larger batch than the staging buffers: start over
+                    i = 0
+                pipe = self._host_pipe(rows_max, dev)
+                pipe["up"].wait_stream(cur)
+                pipe["down"].wait_stream(cur)
+            up, down = pipe["up"], pipe["down"]
+            for r0 in range(0, B, rows_max):
+                s, rows = i & 1, min(rows_max, B - r0)
+                xd, od = pipe["x"][s][:rows], pipe["o"][s][:rows]
+                with torch.cuda.stream(up):
+                    if i >= 2:
+                        up.wait_event(pipe["x_free"][s])
+                    xd.copy_(x[r0:r0 + rows], non_blocking=True)
+                    pipe["x_ready"][s].record(up)
+                cur.wait_event(pipe["x_ready"][s])
+                if i >= 2:
+                    cur.wait_event(pipe["o_free"][s])
+                self.infer(xd, in_stats=in_stats, out_stats=out_stats, out=od)
+                pipe["x_free"][s].record(cur)
+                pipe["o_ready"][s].record(cur)
+                with torch.cuda.stream(down):
+                    down.wait_event(pipe["o_ready"][s])
+                    out[r0:r0 + rows].copy_(od, non_blocking=True)
+                    pipe["o_free"][s].record(down)
+                i += 1
+        if pipe is not None:
+            cur.wait_stream(pipe["down"])
+            pipe["down"].synchronize()                             # the results are host memory: valid on return
+        return results
+
+    def _host_pipe(self, rows_max, dev):
         pipe = self._cache.get("host_pipe")
         if pipe is None or pipe["rows"] < rows_max or pipe["dev"] != dev:
+            I, O = self.input_size, self.output_size
             pipe = {"rows": rows_max, "dev": dev, "up": torch.cuda.Stream(dev), "down": torch.cuda.Stream(dev),
                     "x": [torch.empty(rows_max, I, device=dev) for _ in range(2)],
                     "o": [torch.empty(rows_max, O, device=dev) for _ in range(2)],
                     "x_ready": [torch.cuda.Event() for _ in range(2)], "x_free": [torch.cuda.Event() for _ in range(2)],
                     "o_ready": [torch.cuda.Event() for _ in range(2)], "o_free": [torch.cuda.Event() for _ in range(2)]}
             self._cache["host_pipe"] = pipe
-        cur = torch.cuda.current_stream(dev)
-        up, down = pipe["up"], pipe["down"]
-        up.wait_stream(cur)
-        down.wait_stream(cur)
-        for i, r0 in enumerate(range(0, B, rows_max)):
-            s, rows = i & 1, min(rows_max, B - r0)
-            xd, od = pipe["x"][s][:rows], pipe["o"][s][:rows]
-            with torch.cuda.stream(up):
-                if i >= 2:
-                    up.wait_event(pipe["x_free"][s])
-                xd.copy_(x[r0:r0 + rows], non_blocking=True)
-                pipe["x_ready"][s].record(up)
-            cur.wait_event(pipe["x_ready"][s])
-            if i >= 2:
-                cur.wait_event(pipe["o_free"][s])
-            self.infer(xd, in_stats=in_stats, out_stats=out_stats, out=od)
-            pipe["x_free"][s].record(cur)
-            pipe["o_ready"][s].record(cur)
-            with torch.cuda.stream(down):
-                down.wait_event(pipe["o_ready"][s])
-                out[r0:r0 + rows].copy_(od, non_blocking=True)
-                pipe["o_free"][s].record(down)
-        cur.wait_stream(down)
-        down.synchronize()                                         # the result is host memory: valid on return
-        return out
+        return pipe
 
     def forward(self, x):
         y = self._check_input(x)

@@ -189,9 +189,8 @@ def gpu_arm(args, rank, world, local_rank):
                 model.infer(xd, out=out)
 
             def run_e2e(n):                                  # host poses in, host predictions out, every step
-                for _ in range(n):
-                    model.infer_host(xh, out=outh)
-                    torch.cuda.current_stream().synchronize()
+                model.infer_host_batches([xh] * n, outs=[outh] * n)      # one pipeline across the batches, one wait
+                torch.cuda.current_stream().synchronize()
             h2d, d2h = xh.numel() * 4, outh.numel() * 4
             dtype = "fp16 operands, fp32 accumulate"
             cfg = {"workload": f"configs[1]: eval-mode inference, batch {batch} synthetic H36M 2D poses per GPU "

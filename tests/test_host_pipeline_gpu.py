@@ -48,3 +48,16 @@ def test_infer_host_equals_infer(pkg, B, chunk):
     assert m.infer_host(x, out=out, chunk_rows=chunk) is out and torch.equal(out, want)
     with pytest.raises(RuntimeError):
         m.infer_host(x.cuda())
+
+
+def test_infer_host_batches_is_one_pipeline(pkg):
+    m = _model(pkg).eval()
+    gen = torch.Generator().manual_seed(8)
+    xs = [torch.randn(b, 17, 2, generator=gen).pin_memory() for b in (700, 1, 3000, 1024)]
+    want = [m.infer(x.cuda()).cpu() for x in xs]
+    got = m.infer_host_batches(xs, chunk_rows=512)
+    assert len(got) == 4 and all(torch.equal(g, w) for g, w in zip(got, want))
+    outs = [torch.empty(x.shape[0], 51).pin_memory() for x in xs]
+    again = m.infer_host_batches(iter(xs), outs=outs, chunk_rows=4096)
+    assert all(a is o for a, o in zip(again, outs)) and all(torch.equal(g, w) for g, w in zip(outs, want))
+    assert m.infer_host_batches([]) == []
