@@ -105,6 +105,9 @@ SIGNATURES = {
     "lifter_loss": (_I32, [_P, _P, _I64, _I32, _I32, _I64, _P, _P, _P, _P, _I32, _P]),
     "lifter_flip_pose": (_I32, [_P, _P, _I64, _I32, _I32, _I32, _P]),
     "lifter_coco2h36m": (_I32, [_P, _I32, _P, _I64, _F, _P, _P, _I32, _P]),
+    "lifter_keypoint_stats_scratch_bytes": (_I64, [_I64, _I32, _I32]),
+    "lifter_keypoint_stats": (_I32, [_P, _I64, _I32, _I32, _I32, _P, _P, _P]),
+    "lifter_process_keypoints": (_I32, [_P, _P, _I64, _I32, _I32, _I32, _P, _I32, _I32, _P]),
     "lifter_affine_cols": (_I32, [_P, _P, _I64, _I32, _P, _P, _I32, _P]),
     "lifter_pose_loss_scratch_bytes": (_I64, [_I64, _I32]),
     "lifter_pose_loss": (_I32, [C.POINTER(PoseLossDesc), _P]),

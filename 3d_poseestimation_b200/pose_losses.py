@@ -15,6 +15,7 @@ Differences from the reference, all deliberate:
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -132,6 +133,68 @@ def coco2h36m(x, scale=1.0, mean=None, std=None, minmax=False):
     _cabi.check(_cabi.lib().lifter_coco2h36m(_cabi.ptr(x), int(x.shape[-1]), _cabi.ptr(out), poses, float(scale),
                                               _cabi.ptr(m), _cabi.ptr(sd), mode, _cabi.stream_ptr()))
     return out
+
+
+# ------------------------------------------------------------------------------------- dataset-side processing
+def keypoint_stats(dataset, z_c=True):
+    """Per (joint, coordinate) statistics of a key-point data set, ``phase1_lifting/main.py:275-289``.
+
+    ``dataset``: CUDA fp32 ``[frames, joints, dims]``.  Returns a CUDA fp64 tensor ``[4, joints, dims]``: mean,
+    POPULATION standard deviation (divide by the frame count, as the reference does), min and max
+    (``phase5_loop/train_5.py:35-40``) of the values after the optional root-centring ``frame[1:] -= frame[0]``.
+    One read of the data, fp64 accumulation, fixed summation order; nothing is copied to the host."""
+    x = _dev(dataset, "keypoint_stats")
+    if x.dim() != 3 or x.shape[0] < 1:
+        raise ValueError(f"keypoint_stats expects a non-empty [frames, joints, dims] array, got {tuple(x.shape)}")
+    n, J, D = (int(v) for v in x.shape)
+    nbytes = _cabi.lib().lifter_keypoint_stats_scratch_bytes(n, J, D)
+    if nbytes < 0:
+        raise ValueError(f"keypoint_stats: {J} joints x {D} dims unsupported (at most 64 values per frame)")
+    scratch = torch.empty(nbytes // 8, dtype=torch.float64, device=x.device)
+    out = torch.empty((4, J, D), dtype=torch.float64, device=x.device)
+    _cabi.check(_cabi.lib().lifter_keypoint_stats(_cabi.ptr(x), n, J, D, int(bool(z_c)), _cabi.ptr(scratch),
+                                                  _cabi.ptr(out), _cabi.stream_ptr()))
+    return out
+
+
+def process_data(dataset, stats=None, is_train=True, standardize=False, z_c=True, minmax=False, num_of_joints=17,
+                 save_dir=None):
+    """``H36_dataset.process_data`` (``phase1_lifting/main.py:271-355``) on the device: root-centring, the training
+    statistics, ``(x - mean) / std`` (``minmax=True`` on 2D data: ``2x - 1``, the reference's ``Normalize`` switch),
+    the root row zeroed (or dropped when ``num_of_joints == 16``).
+
+    ``dataset``: CUDA fp32 ``[frames, 17, dims]``.  ``is_train=True`` computes the statistics from this data (the
+    reference then writes ``{mean,std}_train_{2,3}d.npy``; ``save_dir`` does the same, as float64 ``(17, dims)``);
+    otherwise pass ``stats`` = what a training call returned (or a ``(mean, std)`` pair of arrays).  Returns
+    ``(processed [frames, 17 | 16, dims] fp32 CUDA, stats [4, 17, dims] fp64 CUDA)``."""
+    x = _dev(dataset, "process_data")
+    if x.dim() != 3:
+        raise ValueError(f"process_data expects [frames, joints, dims], got {tuple(x.shape)}")
+    n, J, D = (int(v) for v in x.shape)
+    if is_train:
+        stats = keypoint_stats(x, z_c)
+        if save_dir is not None:
+            host = stats[:2].cpu().numpy()
+            np.save(os.path.join(save_dir, f"mean_train_{D}d.npy"), host[0])
+            np.save(os.path.join(save_dir, f"std_train_{D}d.npy"), host[1])
+    elif stats is not None and not torch.is_tensor(stats):
+        mean, std = (torch.as_tensor(np.asarray(v), dtype=torch.float64).reshape(J, D) for v in stats)
+        stats = torch.stack([mean, std, mean, mean]).to(x.device)
+    mode = -1
+    if standardize:
+        mode = 2 if (minmax and D == 2) else 0
+        if mode == 0 and stats is None:
+            raise ValueError("process_data: standardize=True needs is_train=True or stats")
+    if stats is not None:
+        stats = stats.to(device=x.device, dtype=torch.float64).contiguous()
+        if stats.shape[0] < 2 or stats[0].numel() != J * D:
+            raise ValueError(f"process_data: stats must be [>=2, {J}, {D}], got {tuple(stats.shape)}")
+    root_mode = 2 if num_of_joints == 16 else (1 if z_c else 0)
+    out = torch.empty((n, J - (root_mode == 2), D), dtype=torch.float32, device=x.device)
+    _cabi.check(_cabi.lib().lifter_process_keypoints(_cabi.ptr(x), _cabi.ptr(out), n, J, D, int(bool(z_c)),
+                                                     _cabi.ptr(stats) if mode == 0 else None, mode, root_mode,
+                                                     _cabi.stream_ptr()))
+    return out, stats
 
 
 # ------------------------------------------------------------------------------------------------ (de)normalisation

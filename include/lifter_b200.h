@@ -182,6 +182,21 @@ int lifter_flip_pose(const float* in, float* out, int64_t poses, int joints, int
  * [poses][17][2] in H36M order = norm(scale * joint); mode -1 none, 0 (v - mean) / std (34 statistics), 2: 2v - 1. */
 int lifter_coco2h36m(const float* in, int in_channels, float* out, int64_t poses, float scale, const float* mean,
                      const float* stdv, int mode, void* stream);
+/* Dataset-side keypoint processing (phase1_lifting/main.py:271-355 process_data) without Python loops over frames.
+ * lifter_keypoint_stats: data [frames][joints][dims] fp32 -> out [4][joints*dims] fp64 = mean, population standard
+ * deviation (divide by frames, main.py:280-289), min, max (train_5.py:35-40) of the values after the optional
+ * root-centring "frame[1:] -= frame[0]" (main.py:275-277).  One read of the data; deterministic (no atomics).
+ * lifter_process_keypoints: root-centring, then mode 0 (v - mean) / std with `stats` = the array above (main.py:334,
+ * 337), 2: 2v - 1 (main.py:331), -1 none; root_mode 0 keep, 1 zero the root row (main.py:343-344), 2 drop it (the
+ * 16-joint variant, main.py:340-342: out is [frames][joints-1][dims]).  joints * dims <= 64.                     */
+#define LIFTER_ROOT_KEEP 0
+#define LIFTER_ROOT_ZERO 1
+#define LIFTER_ROOT_DROP 2
+int64_t lifter_keypoint_stats_scratch_bytes(int64_t frames, int joints, int dims);
+int lifter_keypoint_stats(const float* data, int64_t frames, int joints, int dims, int zero_centre, void* scratch,
+                          double* out, void* stream);
+int lifter_process_keypoints(const float* in, float* out, int64_t frames, int joints, int dims, int zero_centre,
+                             const double* stats, int mode, int root_mode, void* stream);
 /* per-column statistics broadcast over rows: mode 0 (x - a) / b (main.py:334,337), 1 x * b + a (main.py:473-479,
  * train_5.py:42-47), 2 2x - 1 (main.py:331), 3 x * (a - b) + b with a = max, b = min (train_5.py:35-40)        */
 int lifter_affine_cols(const float* in, float* out, int64_t rows, int cols, const float* a, const float* b, int mode,

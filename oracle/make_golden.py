@@ -67,6 +67,53 @@ def ingest_case():
     print("wrote ingest", h36m.shape)
 
 
+def ref_process_data(num_of_joints=17, normalize=False):
+    """main.py:271-355 (the method ``process_data``), taken by exec of the source slice: main.py itself imports cv2,
+    wandb and the dataset paths.  The method reads module globals (sample, zero_centre, Normalize, num_of_joints,
+    Samples) and writes / reads ``{mean,std}_train_{2,3}d.npy`` in the working directory."""
+    import textwrap
+    src = open(os.path.join(REF, "phase1_lifting", "main.py")).read().splitlines()
+    ns = {"np": np, "sample": False, "zero_centre": True, "Normalize": normalize, "num_of_joints": num_of_joints,
+          "Samples": None}
+    exec(textwrap.dedent("\n".join(src[270:355])), ns)
+    return ns["process_data"]
+
+
+def process_data_case():
+    """Dataset-side statistics and standardisation through the reference's own process_data."""
+    import tempfile
+    rs = np.random.RandomState(41)
+    N = 257
+    out = {}
+    cwd = os.getcwd()
+    with tempfile.TemporaryDirectory() as tmp:
+        os.chdir(tmp)
+        try:
+            for dim in (2, 3):
+                scale = np.array([0.25, 0.2] if dim == 2 else [0.6, 0.5, 0.4])
+                offs = np.array([0.5, 0.45] if dim == 2 else [1.8, -0.95, 4.7])
+                raw = (offs + scale * rs.normal(0, 1, (N, 17, dim))).astype(np.float32)
+                out[f"raw{dim}"] = raw
+                for zc in (0, 1):
+                    f = ref_process_data()
+                    got = f(None, raw.astype(np.float64).copy(), is_train=True, standardize=True, z_c=bool(zc))
+                    tag = f"d{dim}_zc{zc}"
+                    out[tag + "_std"] = got
+                    out[tag + "_mean"] = np.load(f"mean_train_{dim}d.npy")
+                    out[tag + "_sd"] = np.load(f"std_train_{dim}d.npy")
+                    out[tag + "_plain"] = ref_process_data()(None, raw.astype(np.float64).copy(), is_train=False,
+                                                             standardize=False, z_c=bool(zc))
+                # 16-joint variant (root dropped) and the 2x - 1 mode of main.py:331
+                out[f"d{dim}_j16"] = ref_process_data(num_of_joints=16)(None, raw.astype(np.float64).copy(), is_train=True,
+                                                                        standardize=True, z_c=True)
+            out["d2_minmax"] = ref_process_data(normalize=True)(None, out["raw2"].astype(np.float64).copy(), is_train=True,
+                                                               standardize=True, z_c=True)
+        finally:
+            os.chdir(cwd)
+    np.savez(os.path.join(GOLD, "process_data.npz"), **out)
+    print("wrote process_data", {k: v.shape for k, v in out.items()})
+
+
 class MaskedDropout(torch.nn.Module):
     """Stands in for ``torch.nn.Dropout(p)`` in the reference module; same arithmetic, external mask."""
 
@@ -259,6 +306,9 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "ingest":      # only the keypoint-ingest vectors
         ingest_case()
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "process_data":
+        process_data_case()
+        sys.exit(0)
     lifter_case("small", 34, 51, 64, 2, 16, 0.5, True, seed=1, store_weights=True)
     lifter_case("small_nobn", 34, 51, 64, 1, 8, 0.25, False, seed=2, store_weights=True)
     lifter_case("h1024", 34, 51, 1024, 2, 32, 0.5, True, seed=3, store_weights=False)
@@ -268,3 +318,4 @@ if __name__ == "__main__":
     adam_case()
     train_curve_case()
     ingest_case()
+    process_data_case()

@@ -1,0 +1,91 @@
+"""GPU parity of the dataset-side keypoint processing against the reference's own
+``process_data`` (golden vectors, ``phase1_lifting/main.py:271-355``) and the numpy oracle at larger sizes.
+Statistics are fp64 on the device: compared at 1e-9 relative (fp32 inputs are exact in fp64; only the summation
+order differs).  Processed key points are fp32: one rounding of the reference's float64 result (rtol 1e-6)."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import dataset_oracle as D
+
+pytestmark = pytest.mark.gpu
+T = torch.from_numpy
+
+
+@pytest.fixture(scope="module")
+def P():
+    return importlib.import_module("3d_poseestimation_b200.pose_losses")
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("zc", [0, 1])
+def test_process_data_matches_reference_golden(P, golden_dir, dim, zc, tmp_path):
+    g = dict(np.load(os.path.join(golden_dir, "process_data.npz")))
+    raw, tag = T(g[f"raw{dim}"]).cuda(), f"d{dim}_zc{zc}"
+    out, stats = P.process_data(raw, is_train=True, standardize=True, z_c=bool(zc), save_dir=str(tmp_path))
+    st = stats.cpu().numpy()
+    np.testing.assert_allclose(st[0], g[tag + "_mean"], rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(st[1], g[tag + "_sd"], rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(out.cpu().numpy(), g[tag + "_std"], rtol=2e-6, atol=2e-6)
+    # the files the reference writes (main.py:291-299), same names / dtype / shape
+    saved = np.load(os.path.join(tmp_path, f"mean_train_{dim}d.npy"))
+    assert saved.dtype == np.float64 and saved.shape == (17, dim)
+    np.testing.assert_allclose(saved, g[tag + "_mean"], rtol=1e-9, atol=1e-12)
+    # is_train=False, standardize=False: centring + root zeroing only; statistics passed as a (mean, std) pair
+    plain, _ = P.process_data(raw, stats=(g[tag + "_mean"], g[tag + "_sd"]), is_train=False, standardize=False, z_c=bool(zc))
+    np.testing.assert_allclose(plain.cpu().numpy(), g[tag + "_plain"], rtol=1e-6, atol=1e-7)
+    again, _ = P.process_data(raw, stats=stats, is_train=False, standardize=True, z_c=bool(zc))
+    assert torch.equal(again, out)
+    if zc:
+        j16, _ = P.process_data(raw, is_train=True, standardize=True, z_c=True, num_of_joints=16)
+        assert tuple(j16.shape) == (raw.shape[0], 16, dim)
+        np.testing.assert_allclose(j16.cpu().numpy(), g[f"d{dim}_j16"], rtol=2e-6, atol=2e-6)
+        assert float(out[:, 0].abs().max()) == 0.0
+        if dim == 2:
+            mm, _ = P.process_data(raw, is_train=True, standardize=True, z_c=True, minmax=True)
+            np.testing.assert_allclose(mm.cpu().numpy(), g["d2_minmax"], rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("frames,J,dim", [(1, 17, 3), (2, 17, 2), (6, 17, 3), (40, 17, 3), (4099, 17, 2), (390_001, 17, 3), (1000, 21, 3), (333, 1, 2)])
+def test_keypoint_stats_vs_oracle_ragged_sizes(P, frames, J, dim):
+    """One frame, fewer frames than row groups, sizes that are no multiple of any block shape, the H36M scale
+    (~390 k frames), the largest frame width."""
+    rs = np.random.RandomState(frames % 1000 + dim)
+    raw = (rs.normal(0, 1, (frames, J, dim)) * rs.uniform(0.1, 2, (J, dim)) + rs.uniform(-5, 5, (J, dim))).astype(np.float32)
+    for zc in (False, True):
+        st = P.keypoint_stats(T(raw).cuda(), z_c=zc).cpu().numpy()
+        mean, std, lo, hi = D.keypoint_stats(raw, zc)
+        np.testing.assert_allclose(st[0], mean, rtol=1e-9, atol=1e-10)
+        np.testing.assert_allclose(st[1], std, rtol=1e-7, atol=1e-10)
+        assert np.array_equal(st[2], lo) and np.array_equal(st[3], hi)          # min / max are exact
+        out, _ = P.process_data(T(raw).cuda(), is_train=True, standardize=frames > 1, z_c=zc)
+        exp, _, _ = D.process_data(raw, standardize=frames > 1, z_c=zc)
+        np.testing.assert_allclose(out.cpu().numpy(), exp, rtol=2e-5, atol=2e-5)
+
+
+def test_keypoint_stats_is_deterministic_and_shift_invariant(P):
+    """Same bits run after run (fixed-order partial sums); a large common offset does not cost precision (the sums
+    are taken around the first frame)."""
+    rs = np.random.RandomState(5)
+    raw = (1000.0 + 1e-2 * rs.normal(0, 1, (50_000, 17, 3))).astype(np.float32)
+    x = T(raw).cuda()
+    a, b = P.keypoint_stats(x, z_c=False), P.keypoint_stats(x, z_c=False)
+    assert torch.equal(a, b)
+    _, std, _, _ = D.keypoint_stats(raw, False)
+    np.testing.assert_allclose(a[1].cpu().numpy(), std, rtol=1e-7)
+
+
+def test_dataset_processing_errors(P):
+    with pytest.raises(RuntimeError):
+        P.keypoint_stats(torch.zeros(4, 17, 3))                                  # CPU tensor: no fallback
+    with pytest.raises(ValueError):
+        P.keypoint_stats(torch.zeros(0, 17, 3, device="cuda"))
+    with pytest.raises(ValueError):
+        P.keypoint_stats(torch.zeros(4, 33, 3, device="cuda"))                  # 99 values per frame
+    with pytest.raises(ValueError):
+        P.process_data(torch.zeros(4, 17, 3, device="cuda"), is_train=False, standardize=True)
+    out, _ = P.process_data(torch.zeros(0, 17, 3, device="cuda"), is_train=False, standardize=False)
+    assert tuple(out.shape) == (0, 17, 3)

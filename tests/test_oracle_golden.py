@@ -197,3 +197,27 @@ def test_keypoint_ingest_matches_reference(golden_dir):
     np.testing.assert_allclose(L.ingest_keypoints(g["coco"], st["mean_train_2d"], st["std_train_2d"]), g["standardised"],
                                rtol=1e-12)
     np.testing.assert_allclose(L.ingest_keypoints(g["coco"], minmax=True), g["minmax"], rtol=1e-12)
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("zc", [0, 1])
+def test_dataset_processing_matches_reference_process_data(golden_dir, dim, zc):
+    """oracle/dataset_oracle.py against the reference's own process_data (main.py:271-355)."""
+    from oracle import dataset_oracle as D
+    g = _load(golden_dir, "process_data.npz")
+    raw, tag = g[f"raw{dim}"], f"d{dim}_zc{zc}"
+    out, mean, std = D.process_data(raw, standardize=True, z_c=bool(zc))
+    np.testing.assert_allclose(mean, g[tag + "_mean"], rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(std, g[tag + "_sd"], rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(out, g[tag + "_std"], rtol=1e-10, atol=1e-12)
+    plain, _, _ = D.process_data(raw, mean, std, standardize=False, z_c=bool(zc))
+    np.testing.assert_allclose(plain, g[tag + "_plain"], rtol=1e-12, atol=1e-14)
+    if zc:
+        j16, _, _ = D.process_data(raw, standardize=True, z_c=True, num_of_joints=16)
+        np.testing.assert_allclose(j16, g[f"d{dim}_j16"], rtol=1e-10, atol=1e-12)
+        if dim == 2:
+            mm, _, _ = D.process_data(raw, standardize=True, z_c=True, minmax=True)
+            np.testing.assert_allclose(mm, g["d2_minmax"], rtol=1e-12, atol=1e-14)
+    m2, s2, lo_, hi_ = D.keypoint_stats(raw, bool(zc))
+    assert np.array_equal(m2, mean) and np.array_equal(s2, std)
+    assert np.all(lo_ <= m2) and np.all(m2 <= hi_)

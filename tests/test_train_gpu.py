@@ -234,3 +234,40 @@ def test_fused_trainer_follows_the_oracle_curve(pkg, optimizer):
     with torch.no_grad():
         out = m(xe.cuda()).cpu()
     assert rel_l2(out, ref) < 1e-1
+
+
+def test_fused_trainer_loss_curve_over_1k_steps(pkg):
+    """north_star: "training must agree on loss curves within 1 % over 1k steps with a fixed seed".
+
+    1,000 fused steps (train_1.py:73-100: forward, MSE, backward, Adam; dropout 0.5, batch statistics) against
+    the fp32 oracle on the same data, weights and dropout masks.  Tolerances: every 50-step window mean within
+    1 %; single steps within 3 % (a CPU simulation of the kernels' bf16 rounding points over the same 1,000
+    steps shows 0.17 % on the windows and 1.8 % on the worst single step)."""
+    trainer_mod = importlib.import_module("3d_poseestimation_b200.trainer")
+    i_dim, o_dim, H, S, B, seed, steps, win = 34, 51, 256, 2, 64, 31, 1000, 50
+    params, buffers = lo.numpy_init(i_dim, o_dim, H, S, seed, randomize_bn=False)
+    m = _model(pkg, params, buffers, i_dim, o_dim, H, S, 0.5, True)
+    tr = trainer_mod.LifterTrainer(m, lr=1e-3, loss="mse", optimizer="adam", seed=seed + 7)
+    rs = np.random.RandomState(seed + 1)
+    wtrue = rs.normal(0, 0.3, (i_dim, o_dim)).astype(np.float32)
+    mo = {k: torch.zeros_like(v) for k, v in params.items()}
+    vo = {k: torch.zeros_like(v) for k, v in params.items()}
+    got, exp = [], []
+    for s in range(steps):
+        x = rs.normal(0, 1, (B, i_dim)).astype(np.float32)
+        y = T(np.tanh(x @ wtrue).astype(np.float32))
+        got.append(tr.step(T(x).cuda(), y.cuda()).clone())          # no host read inside the loop
+        masks = [dropout_keep_mask(B, H, site, s, seed + 7, 0.5) for site in range(2 * S + 1)]
+        r = lo.lifter_forward_backward(params, buffers, T(x), lambda o: ((o - y) ** 2).mean(), num_stage=S,
+                                       training=True, p_dropout=0.5, masks=masks)
+        buffers = r["buffers"]
+        for k in params:
+            params[k], mo[k], vo[k] = adam_oracle.adam_step(params[k], r["grads"][k], mo[k], vo[k], s + 1, 1e-3)
+        exp.append(float(r["loss"]))
+    got = torch.stack([g.reshape(()) for g in got]).cpu().double().numpy()
+    exp = np.asarray(exp)
+    assert exp[-win:].mean() < 0.3 * exp[:win].mean()                 # the curve actually descends
+    gw, ew = got.reshape(-1, win).mean(1), exp.reshape(-1, win).mean(1)
+    np.testing.assert_allclose(gw, ew, rtol=1e-2, err_msg="50-step window means")
+    np.testing.assert_allclose(got, exp, rtol=3e-2, err_msg="single steps")
+    assert int(m.state_dict()["batch_norm1.num_batches_tracked"]) == steps
