@@ -1,7 +1,8 @@
 // Dataset-side keypoint processing: phase1_lifting/main.py:271-355 `process_data` as two
 // HBM-bound passes over the [frames][joints][dims] fp32 array instead of Python loops over frames.
-//   pass 1  keypoint_stats_kernel    root-centring on the fly, per (joint, coordinate) sum / sum of squares in fp64
-//                                    around the first frame's value (shifted one-pass variance), min, max;
+//   pass 1  keypoint_stats_kernel    root-centring on the fly, per (joint, coordinate) sum / sum of squares around
+//                                    the first frame's value (shifted one-pass variance; fp32 groups of eight folded
+//                                    into fp64 accumulators), min, max;
 //                                    fixed-order block partials -> keypoint_stats_finalize_kernel (no float atomics)
 //   pass 2  process_keypoints_kernel root-centring, (x - mean) / std or 2x - 1, root row zeroed or dropped
 // Algorithmic traffic: pass 1 reads 4 B per element; pass 2 reads 4 B and writes 4 B per element.
@@ -14,66 +15,106 @@ constexpr int DS_MAXC = 64;          // joints * dims of one frame (17 x 2 = 34,
 
 namespace {
 
-__device__ __forceinline__ double centred(const float* __restrict__ row, int c, int d, bool sub_root) {
-    const double v = static_cast<double>(row[c]);
-    return sub_root ? v - static_cast<double>(row[d]) : v;           // main.py:275-277, exact in fp64
-}
+// Thread mapping of both passes: block = G row groups x cols columns (G = 256 / cols); thread (g, c) walks rows
+// r0 + g, r0 + g + G, ... of ITS column c, so everything that depends on the column (root coordinate, shift, mean,
+// 1 / std) sits in registers, and one iteration of the block covers G consecutive frames = one contiguous span.
+// The root coordinate is loaded unconditionally (it is in the same 128-byte lines) and selected, not branched on.
 
-// Block = G row groups x cols columns (G = 256 / cols); thread (g, c) walks rows r0 + g, r0 + g + G, ... of column c,
-// so the block's loads of one iteration cover G consecutive frames = one contiguous span of the array.
-__global__ void __launch_bounds__(DS_THREADS) keypoint_stats_kernel(const float* __restrict__ data, long frames, int cols,
+__global__ void __launch_bounds__(DS_THREADS, 2) keypoint_stats_kernel(const float* __restrict__ data, long frames, int cols,
                                                                     int D, int zc, long rows_per_block,
                                                                     double* __restrict__ partials) {
     griddep_launch();
     griddep_wait();
-    __shared__ double s_red[4][DS_THREADS];
+    __shared__ double s_sum[2][DS_THREADS];
+    __shared__ float s_mm[2][DS_THREADS];
     const int G = DS_THREADS / cols;
     const int t = threadIdx.x, c = t % cols, g = t / cols, d = c % D;
-    const bool sub_root = zc != 0 && c >= D;
-    double sum = 0.0, sq = 0.0, mn = CUDART_INF, mx = -CUDART_INF;
+    const float w = (zc != 0 && c >= D) ? 1.0f : 0.0f;               // main.py:275-277: joints 1.. minus the root
+    double sum = 0.0, sq = 0.0;
+    float mn = CUDART_INF_F, mx = -CUDART_INF_F;
     if (g < G) {
-        const double shift = centred(data, c, d, sub_root);          // first frame: the same on every block
+        // Non-tensor fp64 runs at a few operations per clock per SM on this part (measured: an all-fp64 version of this
+        // loop reached 0.76 TB/s), so the stream is fp32: x = (v - root) - shift rounds twice at the magnitude of the
+        // CENTRED value (below the input's own quantisation), eight of them are summed in fp32 and each such group
+        // is folded into the fp64 accumulators with one add.
+        const float shift = data[c] - w * data[d];                    // first frame: any constant near the mean works
         const long r0 = static_cast<long>(blockIdx.x) * rows_per_block;
         const long r1 = min(frames, r0 + rows_per_block);
-#pragma unroll 8
-        for (long r = r0 + g; r < r1; r += G) {
-            const double v = centred(data + r * cols, c, d, sub_root);
-            const double x = v - shift;
-            sum += x;
-            sq = fma(x, x, sq);
-            mn = fmin(mn, v);
-            mx = fmax(mx, v);
+        const long n_it = r1 > r0 + g ? (r1 - r0 - g + G - 1) / G : 0;
+        const float* pv = data + (r0 + g) * cols + c;
+        const float* pr = data + (r0 + g) * cols + d;
+        const long step = static_cast<long>(G) * cols;
+        long it = 0;
+        for (; it + 8 <= n_it; it += 8) {
+            float v[8], rt[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) { v[u] = pv[(it + u) * step]; rt[u] = pr[(it + u) * step]; }
+            float fs = 0.0f, fq = 0.0f;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const float vf = v[u] - w * rt[u];
+                mn = fminf(mn, vf);
+                mx = fmaxf(mx, vf);
+                const float x = vf - shift;
+                fs += x;
+                fq = fmaf(x, x, fq);
+            }
+            sum += static_cast<double>(fs);
+            sq += static_cast<double>(fq);
         }
+        float fs = 0.0f, fq = 0.0f;
+        for (; it < n_it; ++it) {
+            const float vf = pv[it * step] - w * pr[it * step];
+            mn = fminf(mn, vf);
+            mx = fmaxf(mx, vf);
+            const float x = vf - shift;
+            fs += x;
+            fq = fmaf(x, x, fq);
+        }
+        sum += static_cast<double>(fs);
+        sq += static_cast<double>(fq);
     }
-    s_red[0][t] = sum; s_red[1][t] = sq; s_red[2][t] = mn; s_red[3][t] = mx;
+    s_sum[0][t] = sum; s_sum[1][t] = sq; s_mm[0][t] = mn; s_mm[1][t] = mx;
     __syncthreads();
     if (t < cols) {
         for (int k = 1; k < G; ++k) {                                 // fixed order
             const int o = k * cols + t;
-            sum += s_red[0][o]; sq += s_red[1][o];
-            mn = fmin(mn, s_red[2][o]); mx = fmax(mx, s_red[3][o]);
+            sum += s_sum[0][o]; sq += s_sum[1][o];
+            mn = fminf(mn, s_mm[0][o]); mx = fmaxf(mx, s_mm[1][o]);
         }
         double* p = partials + static_cast<long>(blockIdx.x) * 4 * cols;
-        p[t] = sum; p[cols + t] = sq; p[2 * cols + t] = mn; p[3 * cols + t] = mx;
+        p[t] = sum; p[cols + t] = sq; p[2 * cols + t] = static_cast<double>(mn); p[3 * cols + t] = static_cast<double>(mx);
     }
 }
 
-// out [4][cols] fp64: mean, population std (main.py:280-289: divide by n_frames), min, max
-__global__ void __launch_bounds__(DS_MAXC) keypoint_stats_finalize_kernel(const float* __restrict__ data, long frames,
-                                                                          int cols, int D, int zc,
-                                                                          const double* __restrict__ partials, int nblk,
-                                                                          double* __restrict__ out) {
+// out [4][cols] fp64: mean, population std (main.py:280-289: divide by n_frames), min, max.  16 groups of 64 lanes
+// each fold every 16th partial row, then lane c of group 0 folds the 16 group results: a fixed order again.
+constexpr int FIN_GROUPS = 16;
+__global__ void __launch_bounds__(FIN_GROUPS * DS_MAXC) keypoint_stats_finalize_kernel(
+    const float* __restrict__ data, long frames, int cols, int D, int zc, const double* __restrict__ partials, int nblk,
+    double* __restrict__ out) {
     griddep_launch();
     griddep_wait();
-    const int c = threadIdx.x;
-    if (c >= cols) return;
+    __shared__ double s_part[4][FIN_GROUPS][DS_MAXC];
+    const int c = threadIdx.x % DS_MAXC, grp = threadIdx.x / DS_MAXC;
     double sum = 0.0, sq = 0.0, mn = CUDART_INF, mx = -CUDART_INF;
-    for (int b = 0; b < nblk; ++b) {
-        const double* p = partials + static_cast<long>(b) * 4 * cols;
-        sum += p[c]; sq += p[cols + c];
-        mn = fmin(mn, p[2 * cols + c]); mx = fmax(mx, p[3 * cols + c]);
+    if (c < cols) {
+#pragma unroll 4
+        for (int b = grp; b < nblk; b += FIN_GROUPS) {
+            const double* p = partials + static_cast<long>(b) * 4 * cols;
+            sum += p[c]; sq += p[cols + c];
+            mn = fmin(mn, p[2 * cols + c]); mx = fmax(mx, p[3 * cols + c]);
+        }
     }
-    const double shift = centred(data, c, c % D, zc != 0 && c >= D);
+    s_part[0][grp][c] = sum; s_part[1][grp][c] = sq; s_part[2][grp][c] = mn; s_part[3][grp][c] = mx;
+    __syncthreads();
+    if (grp != 0 || c >= cols) return;
+    for (int k = 1; k < FIN_GROUPS; ++k) {
+        sum += s_part[0][k][c]; sq += s_part[1][k][c];
+        mn = fmin(mn, s_part[2][k][c]); mx = fmax(mx, s_part[3][k][c]);
+    }
+    const float w = (zc != 0 && c >= D) ? 1.0f : 0.0f;
+    const double shift = static_cast<double>(data[c] - w * data[c % D]);          // the kernel's fp32 constant
     const double n = static_cast<double>(frames);
     const double m = sum / n;
     const double var = fmax(0.0, (sq - sum * m) / n);
@@ -83,38 +124,38 @@ __global__ void __launch_bounds__(DS_MAXC) keypoint_stats_finalize_kernel(const 
     out[3 * cols + c] = mx;
 }
 
-// out [frames][Jout][D]; Jout = J - (root_mode == ROOT_DROP)
-__global__ void __launch_bounds__(DS_THREADS) process_keypoints_kernel(const float* __restrict__ in, float* __restrict__ out,
+// out [frames][Jout][D]; Jout = J - (root_mode == ROOT_DROP).  Same thread mapping over the OUTPUT columns.
+__global__ void __launch_bounds__(DS_THREADS, 2) process_keypoints_kernel(const float* __restrict__ in, float* __restrict__ out,
                                                                        long frames, int J, int D, int zc,
                                                                        const double* __restrict__ stats, int mode,
-                                                                       int root_mode) {
+                                                                       int root_mode, long rows_per_block) {
     griddep_launch();
     griddep_wait();
-    __shared__ double s_mean[DS_MAXC], s_rstd[DS_MAXC];
-    const int cols = J * D;
-    if (mode == COLS_NORMALISE) {
-        for (int c = threadIdx.x; c < cols; c += blockDim.x) {
-            s_mean[c] = stats[c];
-            s_rstd[c] = 1.0 / stats[cols + c];
-        }
-        __syncthreads();
-    }
-    const int skip = root_mode == ROOT_DROP ? D : 0, ocols = cols - skip;
-    const long n = frames * ocols, stride = static_cast<long>(gridDim.x) * blockDim.x;
-    // (row, column) of this thread's element advance by a fixed step: no 64-bit division in the loop
-    const unsigned first = blockIdx.x * blockDim.x + threadIdx.x;                     // < 2^31 (grid <= 8 * SMs)
-    const unsigned step = static_cast<unsigned>(stride);
-    long r = first / static_cast<unsigned>(ocols);
-    int oc = static_cast<int>(first % static_cast<unsigned>(ocols));
-    const int step_r = static_cast<int>(step / static_cast<unsigned>(ocols)), step_c = static_cast<int>(step % static_cast<unsigned>(ocols));
-    for (long i = first; i < n; i += stride, r += step_r, oc += step_c) {
-        if (oc >= ocols) { oc -= ocols; ++r; }
-        const int c = oc + skip, d = c % D;
-        double v = centred(in + r * cols, c, d, zc != 0 && c >= D);
-        if (mode == COLS_NORMALISE) v = (v - s_mean[c]) * s_rstd[c];               // main.py:334,337
-        else if (mode == COLS_MINMAX_NORM) v = 2.0 * v - 1.0;                       // main.py:331
-        if (root_mode == ROOT_ZERO && c < D) v = 0.0;                               // main.py:343-344
-        out[i] = static_cast<float>(v);
+    const int cols = J * D, skip = root_mode == ROOT_DROP ? D : 0, ocols = cols - skip;
+    const int G = DS_THREADS / ocols;
+    const int t = threadIdx.x, oc = t % ocols, g = t / ocols, c = oc + skip, d = c % D;
+    if (g >= G) return;
+    const float w = (zc != 0 && c >= D) ? 1.0f : 0.0f;
+    // out = ((v - root) - a) * b in fp32, a = mean carried as a two-float (hi + lo) so its fp32 rounding does not show
+    float a_hi = 0.0f, a_lo = 0.0f, b = 1.0f;
+    if (mode == COLS_NORMALISE) {                                                   // main.py:334,337
+        const double mean = stats[c];
+        a_hi = static_cast<float>(mean);
+        a_lo = static_cast<float>(mean - static_cast<double>(a_hi));
+        b = static_cast<float>(1.0 / stats[cols + c]);
+    } else if (mode == COLS_MINMAX_NORM) { a_hi = 0.5f; b = 2.0f; }                 // main.py:331: 2v - 1
+    if (root_mode == ROOT_ZERO && c < D) { a_hi = 0.0f; a_lo = 0.0f; b = 0.0f; }    // main.py:343-344
+    const long r0 = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long r1 = min(frames, r0 + rows_per_block);
+    const long n_it = r1 > r0 + g ? (r1 - r0 - g + G - 1) / G : 0;
+    const float* pv = in + (r0 + g) * cols + c;
+    const float* pr = in + (r0 + g) * cols + d;
+    float* po = out + (r0 + g) * ocols + oc;
+    const long istep = static_cast<long>(G) * cols, ostep = static_cast<long>(G) * ocols;
+#pragma unroll 8
+    for (long it = 0; it < n_it; ++it) {
+        const float v = pv[it * istep], rt = w * pr[it * istep];
+        po[it * ostep] = (((v - rt) - a_hi) - a_lo) * b;
     }
 }
 
@@ -124,7 +165,7 @@ int keypoint_stats_blocks(int64_t frames, int cols) {
     if (frames <= 0 || cols <= 0 || cols > DS_MAXC) return 0;
     const long G = DS_THREADS / cols;
     long blocks = (frames + G * 8 - 1) / (G * 8);                    // at least eight rows per thread
-    const long cap = static_cast<long>(num_sms()) * 8;
+    const long cap = static_cast<long>(num_sms()) * 4;              // 1,024 threads per SM, 16 loads in flight each
     if (blocks > cap) blocks = cap;
     return static_cast<int>(blocks < 1 ? 1 : blocks);
 }
@@ -141,7 +182,7 @@ int keypoint_stats(const float* data, int64_t frames, int J, int D, int zc, doub
     rpb = (rpb + G - 1) / G * G;
     LIFTER_CHECK_CUDA(launch_pdl("keypoint_stats_kernel", keypoint_stats_kernel, dim3(blocks), dim3(DS_THREADS), 0, st, data,
                                  static_cast<long>(frames), cols, D, zc, rpb, scratch));
-    LIFTER_CHECK_CUDA(launch_pdl("keypoint_stats_finalize_kernel", keypoint_stats_finalize_kernel, dim3(1), dim3(DS_MAXC), 0,
+    LIFTER_CHECK_CUDA(launch_pdl("keypoint_stats_finalize_kernel", keypoint_stats_finalize_kernel, dim3(1), dim3(FIN_GROUPS * DS_MAXC), 0,
                                  st, data, static_cast<long>(frames), cols, D, zc, static_cast<const double*>(scratch), blocks, out));
     return LIFTER_OK;
 }
@@ -156,12 +197,15 @@ int process_keypoints(const float* in, float* out, int64_t frames, int J, int D,
     LIFTER_REQUIRE(root_mode != ROOT_DROP || J >= 2, "process_keypoints: nothing left after dropping the root");
     if (frames <= 0) return LIFTER_OK;
     LIFTER_REQUIRE(in && out && in != out, "process_keypoints: bad pointers");
-    const long n = frames * (cols - (root_mode == ROOT_DROP ? D : 0));
-    long blocks = (n + DS_THREADS * 4 - 1) / (DS_THREADS * 4);
+    const int ocols = cols - (root_mode == ROOT_DROP ? D : 0);
+    const long G = DS_THREADS / ocols;
+    long blocks = (frames + G * 8 - 1) / (G * 8);
     const long cap = static_cast<long>(num_sms()) * 8;
     if (blocks > cap) blocks = cap;
+    long rpb = (frames + blocks - 1) / blocks;
+    rpb = (rpb + G - 1) / G * G;
     LIFTER_CHECK_CUDA(launch_pdl("process_keypoints_kernel", process_keypoints_kernel, dim3(static_cast<unsigned>(blocks)),
-                                 dim3(DS_THREADS), 0, st, in, out, static_cast<long>(frames), J, D, zc, stats, mode, root_mode));
+                                 dim3(DS_THREADS), 0, st, in, out, static_cast<long>(frames), J, D, zc, stats, mode, root_mode, rpb));
     return LIFTER_OK;
 }
 

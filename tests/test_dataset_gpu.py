@@ -1,7 +1,9 @@
 """GPU parity of the dataset-side keypoint processing against the reference's own
 ``process_data`` (golden vectors, ``phase1_lifting/main.py:271-355``) and the numpy oracle at larger sizes.
-Statistics are fp64 on the device: compared at 1e-9 relative (fp32 inputs are exact in fp64; only the summation
-order differs).  Processed key points are fp32: one rounding of the reference's float64 result (rtol 1e-6)."""
+Tolerances: the kernels stream in fp32 (non-tensor fp64 is a few operations per clock per SM on B200) and fold groups
+of eight shifted values into fp64 accumulators, so the mean agrees to ~1e-6 of the column's standard deviation and the
+standard deviation to 1e-5 relative -- both below the quantisation of the fp32 key points themselves.  Processed key
+points are fp32 against the reference's float64 result: 2e-6 (absolute, in units of the standard deviation)."""
 import importlib
 import os
 
@@ -27,13 +29,13 @@ def test_process_data_matches_reference_golden(P, golden_dir, dim, zc, tmp_path)
     raw, tag = T(g[f"raw{dim}"]).cuda(), f"d{dim}_zc{zc}"
     out, stats = P.process_data(raw, is_train=True, standardize=True, z_c=bool(zc), save_dir=str(tmp_path))
     st = stats.cpu().numpy()
-    np.testing.assert_allclose(st[0], g[tag + "_mean"], rtol=1e-9, atol=1e-12)
-    np.testing.assert_allclose(st[1], g[tag + "_sd"], rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(st[0], g[tag + "_mean"], rtol=1e-7, atol=1e-6 * g[tag + "_sd"].max())
+    np.testing.assert_allclose(st[1], g[tag + "_sd"], rtol=1e-5, atol=1e-12)
     np.testing.assert_allclose(out.cpu().numpy(), g[tag + "_std"], rtol=2e-6, atol=2e-6)
     # the files the reference writes (main.py:291-299), same names / dtype / shape
     saved = np.load(os.path.join(tmp_path, f"mean_train_{dim}d.npy"))
     assert saved.dtype == np.float64 and saved.shape == (17, dim)
-    np.testing.assert_allclose(saved, g[tag + "_mean"], rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(saved, g[tag + "_mean"], rtol=1e-7, atol=1e-6 * g[tag + "_sd"].max())
     # is_train=False, standardize=False: centring + root zeroing only; statistics passed as a (mean, std) pair
     plain, _ = P.process_data(raw, stats=(g[tag + "_mean"], g[tag + "_sd"]), is_train=False, standardize=False, z_c=bool(zc))
     np.testing.assert_allclose(plain.cpu().numpy(), g[tag + "_plain"], rtol=1e-6, atol=1e-7)
@@ -58,9 +60,10 @@ def test_keypoint_stats_vs_oracle_ragged_sizes(P, frames, J, dim):
     for zc in (False, True):
         st = P.keypoint_stats(T(raw).cuda(), z_c=zc).cpu().numpy()
         mean, std, lo, hi = D.keypoint_stats(raw, zc)
-        np.testing.assert_allclose(st[0], mean, rtol=1e-9, atol=1e-10)
-        np.testing.assert_allclose(st[1], std, rtol=1e-7, atol=1e-10)
-        assert np.array_equal(st[2], lo) and np.array_equal(st[3], hi)          # min / max are exact
+        np.testing.assert_allclose(st[0], mean, rtol=1e-7, atol=1e-6 * max(std.max(), 1e-3))
+        np.testing.assert_allclose(st[1], std, rtol=1e-5, atol=1e-10)
+        # min / max: exact, up to the fp32 rounding of the centred difference (rounding is monotone)
+        assert np.array_equal(st[2], lo.astype(np.float32)) and np.array_equal(st[3], hi.astype(np.float32))
         out, _ = P.process_data(T(raw).cuda(), is_train=True, standardize=frames > 1, z_c=zc)
         exp, _, _ = D.process_data(raw, standardize=frames > 1, z_c=zc)
         np.testing.assert_allclose(out.cpu().numpy(), exp, rtol=2e-5, atol=2e-5)
@@ -75,7 +78,7 @@ def test_keypoint_stats_is_deterministic_and_shift_invariant(P):
     a, b = P.keypoint_stats(x, z_c=False), P.keypoint_stats(x, z_c=False)
     assert torch.equal(a, b)
     _, std, _, _ = D.keypoint_stats(raw, False)
-    np.testing.assert_allclose(a[1].cpu().numpy(), std, rtol=1e-7)
+    np.testing.assert_allclose(a[1].cpu().numpy(), std, rtol=1e-5)
 
 
 def test_dataset_processing_errors(P):
