@@ -66,6 +66,14 @@ class PoseLossDesc(C.Structure):
                 ("w_bone", C.c_float), ("dpred", C.c_void_p), ("scratch", C.c_void_p), ("out", C.c_void_p)]
 
 
+class VitDesc(C.Structure):
+    """``lifter_vit_t``: shapes, fp32 parameters and 16-bit GEMM operands of the MyViT lifter."""
+    _fields_ = [(k, C.c_int32) for k in ("tokens", "in_dim", "hidden", "heads", "blocks", "mlp_dim", "head_dim", "out_dim",
+                                         "fmt")] + [("ln_eps", C.c_float)] + \
+               [(k, C.c_void_p) for k in ("map_w", "map_b", "pos", "ln", "mlp_b1", "mlp_b2", "head_b1", "head_b2", "w_qkv",
+                                          "w_out", "w_mlp1", "w_mlp2", "w_head1", "w_head2")]
+
+
 LOSS_MSE, LOSS_L1, LOSS_MPJPE = 0, 1, 2
 DP_MAX_WORLD = 8
 DP_FLAG_BYTES = 256
@@ -118,6 +126,8 @@ SIGNATURES = {
     "lifter_step_advance": (_I32, [_P, _F, _F, _F, _P]),
     "lifter_adam_step_packed": (_I32, [_CFG, _P, _P, _P, _P, _F, _F, _F, _F, _F, _I32, _I32, _F, _P, _P, _I32, _P]),
     "lifter_dp_adam_step": (_I32, [_CFG, C.POINTER(DpInfo), _P, _P, _F, _F, _F, _F, _I32, _F, _P, _I32, _P]),
+    "lifter_vit_workspace_bytes": (_I64, [C.POINTER(VitDesc), _I64]),
+    "lifter_vit_forward": (_I32, [C.POINTER(VitDesc), _P, _I64, _P, _P, _P]),
     "lifter_gemm": (_I32, [C.POINTER(GemmDesc), _P]),
     "lifter_trace_begin": (_I32, [_P]),
     "lifter_trace_end": (_I32, [C.c_char_p, _I32]),

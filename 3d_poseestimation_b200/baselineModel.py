@@ -7,6 +7,7 @@ inside the package it is ``3d_poseestimation_b200.baselineModel``.
 """
 try:
     from .lifter import Linear, LinearModel, weight_init
+    from .vit import Attention, MyViT, MyViTBlock, get_positional_embeddings
 except ImportError:                      # imported as top-level ``baselineModel`` through sys.path
     import importlib as _il
     import os as _os
@@ -16,5 +17,7 @@ except ImportError:                      # imported as top-level ``baselineModel
         _sys.path.insert(0, _os.path.dirname(_here))
     _m = _il.import_module(_os.path.basename(_here) + ".lifter")
     Linear, LinearModel, weight_init = _m.Linear, _m.LinearModel, _m.weight_init
+    _v = _il.import_module(_os.path.basename(_here) + ".vit")
+    Attention, MyViT, MyViTBlock, get_positional_embeddings = _v.Attention, _v.MyViT, _v.MyViTBlock, _v.get_positional_embeddings
 
-__all__ = ["LinearModel", "Linear", "weight_init"]
+__all__ = ["LinearModel", "Linear", "weight_init", "MyViT", "MyViTBlock", "Attention", "get_positional_embeddings"]

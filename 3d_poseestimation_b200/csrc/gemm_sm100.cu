@@ -138,6 +138,22 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 #ifndef LIFTER_GEMM_REGS
 #define LIFTER_GEMM_REGS __maxnreg__(128)
 #endif
+// torch.nn.GELU() (exact erf form) for the epilogue: x * Phi(x) with Phi(-|x|) = erfc(|x| / sqrt 2) / 2 from Abramowitz &
+// Stegun 7.1.26 (|error| <= 1.5e-7 on erf): one rcp.approx, one ex2.approx and eight FMA-class operations, against ~25
+// for erff() -- with K = 256 the epilogue, not the MMA, bounds the MLP-up GEMM of the transformer lifter.
+__device__ __forceinline__ float gelu_erf(float x) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    float t, e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -1.4426950408889634f));
+    const float hl = 0.5f * p * t * e;                                // Phi(-|x|)
+    return x >= 0.0f ? fmaf(-x, hl, x) : x * hl;
+}
+
 template <int BLOCK_N, bool TWO_SM>
 __global__ void LIFTER_GEMM_REGS
 lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
@@ -370,9 +386,12 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                     for (int j = 0; j < 32; ++j)
                         x[j] = fmaf(x[j], s_scale[col_base + c * 32 + j], s_shift[col_base + c * 32 + j]);
                 }
-                if (p.relu) {
+                if (p.relu == 1) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.0f);
+                } else if (p.relu == 2) {                            // torch.nn.GELU(): 0.5 x (1 + erf(x / sqrt 2))
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) x[j] = gelu_erf(x[j]);
                 }
 
                 if (p.out_mode == OUT_16_TMA) {

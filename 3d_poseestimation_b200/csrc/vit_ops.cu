@@ -1,0 +1,385 @@
+// MyViT lifter, eval-mode forward (phase1_lifting/baselineModel.py:228-254, 286-362).
+// Tokens = joints: a pose is 17 tokens of width `hidden` (256).  All Linear layers over the flattened [poses * 17][.]
+// token matrix run on the tcgen05 GEMM of gemm_sm100.cu (bias, ReLU / GELU and the residual add in its epilogue); the
+// kernels here are what sits between the GEMMs:
+//   vit_embed_kernel      Linear(2 -> hidden) + positional embedding -> residual stream (16-bit)            [HBM]
+//   vit_layernorm_kernel  one or two LayerNorms in a row (block.norm1 then mhsa.norm; block.norm2)          [HBM]
+//   vit_attention_kernel  softmax(q k^T / sqrt(d_head)) v for the 17 x 17 token pairs of one (pose, head)   [FP32 pipe]
+#include "vit_ops.cuh"
+
+#include "gemm_sm100.cuh"
+
+namespace lifter {
+
+namespace {
+
+constexpr int VIT_MAX_TOKENS = 32;
+
+__device__ __forceinline__ float wsum(float v) {
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+    return v;
+}
+
+// A warp owns one token row of width Hd = NV * 256: lane l holds columns v * 256 + l * 8 + [0, 8), v < NV.
+template <int NV>
+__device__ __forceinline__ void warp_layernorm(float (&x)[NV][8], const float* __restrict__ g, const float* __restrict__ b,
+                                               float eps, int lane) {
+    constexpr float inv = 1.0f / (NV * 256);
+    float s = 0.0f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s += x[v][e];
+    const float mean = wsum(s) * inv;
+    float q = 0.0f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { const float d = x[v][e] - mean; q = fmaf(d, d, q); }
+    const float rstd = rsqrtf(wsum(q) * inv + eps);                  // biased variance, torch.nn.LayerNorm
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        const int c0 = v * 256 + lane * 8;
+        const float4 g0 = *reinterpret_cast<const float4*>(g + c0), g1 = *reinterpret_cast<const float4*>(g + c0 + 4);
+        const float4 b0 = *reinterpret_cast<const float4*>(b + c0), b1 = *reinterpret_cast<const float4*>(b + c0 + 4);
+        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) x[v][e] = fmaf((x[v][e] - mean) * rstd, gg[e], bb[e]);
+    }
+}
+
+template <int NV>
+__device__ __forceinline__ void store_row16(void* out, long row, int lane, const float (&x)[NV][8], int fmt) {
+    uint4* dst = reinterpret_cast<uint4*>(static_cast<unsigned short*>(out) + row * (NV * 256));
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+        dst[v * 32 + lane] = make_uint4(pack16(x[v][0], x[v][1], fmt), pack16(x[v][2], x[v][3], fmt),
+                                        pack16(x[v][4], x[v][5], fmt), pack16(x[v][6], x[v][7], fmt));
+}
+
+// baselineModel.py:349-354: tokens = linear_mapper(x) + pos_embed -> h (16-bit residual stream), and in the same pass the
+// first block's two LayerNorms (norm1, mhsa.norm; :303, :244) taken from the fp32 values -> u (g1 == nullptr: h only).
+// x [T][in_d] fp32, w [Hd][in_d], pos [tokens][Hd].  IND = in_d when the lane's weight slice is loaded as float4s
+// (in_d == 2, the reference's input), 0 = any in_d <= 4 with scalar loads.
+template <int NV, int IND>
+__global__ void __launch_bounds__(256) vit_embed_kernel(const float* __restrict__ x, long T, int tokens, int in_d,
+                                                        const float* __restrict__ w, const float* __restrict__ bias,
+                                                        const float* __restrict__ pos, void* __restrict__ h,
+                                                        const float* __restrict__ g1, const float* __restrict__ b1,
+                                                        const float* __restrict__ g2, const float* __restrict__ b2, float eps,
+                                                        void* __restrict__ u, int fmt) {
+    griddep_launch();
+    griddep_wait();
+    const int lane = threadIdx.x & 31;
+    const long t = static_cast<long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (t >= T) return;
+    const int n = static_cast<int>(t % tokens);
+    float v[NV][8];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const int c0 = k * 256 + lane * 8;
+        const float4 q0 = *reinterpret_cast<const float4*>(bias + c0), q1 = *reinterpret_cast<const float4*>(bias + c0 + 4);
+        const float4 p0 = *reinterpret_cast<const float4*>(pos + n * (NV * 256) + c0);
+        const float4 p1 = *reinterpret_cast<const float4*>(pos + n * (NV * 256) + c0 + 4);
+        const float a[8] = {q0.x + p0.x, q0.y + p0.y, q0.z + p0.z, q0.w + p0.w, q1.x + p1.x, q1.y + p1.y, q1.z + p1.z, q1.w + p1.w};
+        if constexpr (IND == 2) {
+            const float2 xi = *reinterpret_cast<const float2*>(x + t * 2);
+            const float4* wv = reinterpret_cast<const float4*>(w + c0 * 2);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float4 ww = wv[e];                                        // columns c0 + 2e, c0 + 2e + 1
+                v[k][2 * e] = fmaf(xi.y, ww.y, fmaf(xi.x, ww.x, a[2 * e]));
+                v[k][2 * e + 1] = fmaf(xi.y, ww.w, fmaf(xi.x, ww.z, a[2 * e + 1]));
+            }
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                float acc = a[e];
+                for (int i = 0; i < in_d; ++i) acc = fmaf(x[t * in_d + i], w[(c0 + e) * in_d + i], acc);
+                v[k][e] = acc;
+            }
+        }
+    }
+    store_row16<NV>(h, t, lane, v, fmt);
+    if (g1 == nullptr) return;
+    warp_layernorm<NV>(v, g1, b1, eps, lane);
+    warp_layernorm<NV>(v, g2, b2, eps, lane);
+    store_row16<NV>(u, t, lane, v, fmt);
+}
+
+// out = LN2(LN1(in)) (g2 == nullptr: one LayerNorm).  in / out 16-bit [T][Hd]; statistics and affine in fp32, no
+// 16-bit rounding between the two norms.
+template <int NV>
+__global__ void __launch_bounds__(256) vit_layernorm_kernel(const void* __restrict__ in, long T, const float* __restrict__ g1,
+                                                            const float* __restrict__ b1, const float* __restrict__ g2,
+                                                            const float* __restrict__ b2, float eps, void* __restrict__ out,
+                                                            int fmt) {
+    griddep_launch();
+    griddep_wait();
+    const int lane = threadIdx.x & 31;
+    const long t = static_cast<long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (t >= T) return;
+    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const unsigned short*>(in) + t * (NV * 256));
+    float v[NV][8];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const uint4 r = src[k * 32 + lane];
+        const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float2 f = unpack16(wd[e], fmt);
+            v[k][2 * e] = f.x;
+            v[k][2 * e + 1] = f.y;
+        }
+    }
+    warp_layernorm<NV>(v, g1, b1, eps, lane);
+    if (g2 != nullptr) warp_layernorm<NV>(v, g2, b2, eps, lane);
+    store_row16<NV>(out, t, lane, v, fmt);
+}
+
+// baselineModel.py:243-253.  qkv 16-bit [T][3 * Hd] = [q | k | v], each (head, d) major; o 16-bit [T][Hd].
+// One warp per (pose, head): the head's q, k, v slices (N x DH each) are staged in shared memory with coalesced 16-byte
+// loads; lane i < N owns query row i: scores against every key (key rows are read as broadcasts), softmax in fp32,
+// then the weighted sum of the value rows.
+constexpr int ATT_WARPS = 4;
+template <int DH>
+__global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const void* __restrict__ qkv, long pose_heads,
+                                                                       int tokens, int heads, float scale_log2e,
+                                                                       void* __restrict__ o, int fmt) {
+    griddep_launch();
+    griddep_wait();
+    constexpr int LDS = DH + 8;                                       // halfs per staged row: 16-byte aligned, bank-skewed
+    extern __shared__ __align__(16) unsigned char att_smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long ph = static_cast<long>(blockIdx.x) * ATT_WARPS + wid;
+    if (ph >= pose_heads) return;
+    const long pose = ph / heads;
+    const int head = static_cast<int>(ph - pose * heads);
+    const int Hd = heads * DH;
+    unsigned short* sq = reinterpret_cast<unsigned short*>(att_smem) + static_cast<size_t>(wid) * (3 * tokens * LDS);
+    float* ss = reinterpret_cast<float*>(att_smem + static_cast<size_t>(ATT_WARPS) * 3 * tokens * LDS * 2) + wid * (VIT_MAX_TOKENS * 32);
+    const unsigned short* src = static_cast<const unsigned short*>(qkv) + pose * tokens * (3L * Hd) + head * DH;
+    constexpr int VPR = DH / 8;                                        // 16-byte vectors per row slice
+    for (int i = lane; i < 3 * tokens * VPR; i += 32) {
+        const int vec = i % VPR, rs = i / VPR, slice = rs / tokens, n = rs - slice * tokens;
+        const uint4 val = *reinterpret_cast<const uint4*>(src + n * (3L * Hd) + slice * Hd + vec * 8);
+        *reinterpret_cast<uint4*>(sq + (slice * tokens + n) * LDS + vec * 8) = val;
+    }
+    __syncwarp();
+    const unsigned short* sk = sq + tokens * LDS;
+    const unsigned short* sv = sk + tokens * LDS;
+    if (lane < tokens) {
+        float acc[DH];
+#pragma unroll
+        for (int v = 0; v < VPR; ++v) {
+            const uint4 r = *reinterpret_cast<const uint4*>(sq + lane * LDS + v * 8);
+            const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack16(wd[e], fmt);
+                acc[v * 8 + 2 * e] = f.x * scale_log2e;                // q / sqrt(d_head), in log2 units for exp2f
+                acc[v * 8 + 2 * e + 1] = f.y * scale_log2e;
+            }
+        }
+        float mx = -CUDART_INF_F;
+        for (int j = 0; j < tokens; ++j) {
+            float s = 0.0f;
+#pragma unroll
+            for (int v = 0; v < VPR; ++v) {
+                const uint4 r = *reinterpret_cast<const uint4*>(sk + j * LDS + v * 8);
+                const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 f = unpack16(wd[e], fmt);
+                    s = fmaf(acc[v * 8 + 2 * e], f.x, s);
+                    s = fmaf(acc[v * 8 + 2 * e + 1], f.y, s);
+                }
+            }
+            ss[j * 32 + lane] = s;
+            mx = fmaxf(mx, s);
+        }
+#pragma unroll
+        for (int d = 0; d < DH; ++d) acc[d] = 0.0f;
+        float den = 0.0f;
+        for (int j = 0; j < tokens; ++j) {
+            const float p = exp2f(ss[j * 32 + lane] - mx);
+            den += p;
+#pragma unroll
+            for (int v = 0; v < VPR; ++v) {
+                const uint4 r = *reinterpret_cast<const uint4*>(sv + j * LDS + v * 8);
+                const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 f = unpack16(wd[e], fmt);
+                    acc[v * 8 + 2 * e] = fmaf(p, f.x, acc[v * 8 + 2 * e]);
+                    acc[v * 8 + 2 * e + 1] = fmaf(p, f.y, acc[v * 8 + 2 * e + 1]);
+                }
+            }
+        }
+        const float inv = 1.0f / den;
+        uint4* dst = reinterpret_cast<uint4*>(static_cast<unsigned short*>(o) + (pose * tokens + lane) * Hd + head * DH);
+#pragma unroll
+        for (int v = 0; v < VPR; ++v)
+            dst[v] = make_uint4(pack16(acc[v * 8] * inv, acc[v * 8 + 1] * inv, fmt), pack16(acc[v * 8 + 2] * inv, acc[v * 8 + 3] * inv, fmt),
+                                pack16(acc[v * 8 + 4] * inv, acc[v * 8 + 5] * inv, fmt), pack16(acc[v * 8 + 6] * inv, acc[v * 8 + 7] * inv, fmt));
+    }
+}
+
+size_t att_smem_bytes(int tokens, int dh) {
+    return static_cast<size_t>(ATT_WARPS) * (3 * tokens * (dh + 8) * 2 + VIT_MAX_TOKENS * 32 * 4);
+}
+
+}  // namespace
+
+#define VIT_DISPATCH_NV(nv, CALL)                     \
+    switch (nv) {                                     \
+        case 1: { constexpr int NV = 1; CALL; break; } \
+        case 2: { constexpr int NV = 2; CALL; break; } \
+        case 3: { constexpr int NV = 3; CALL; break; } \
+        default: { constexpr int NV = 4; CALL; break; } \
+    }
+
+int vit_validate(const VitDesc& d) {
+    LIFTER_REQUIRE(d.tokens >= 1 && d.tokens <= VIT_MAX_TOKENS, "vit: %d tokens per pose unsupported (1..%d)", d.tokens, VIT_MAX_TOKENS);
+    LIFTER_REQUIRE(d.in_dim >= 1 && d.in_dim <= 4, "vit: %d input values per token unsupported (1..4)", d.in_dim);
+    LIFTER_REQUIRE(d.hidden >= 256 && d.hidden <= 1024 && d.hidden % 256 == 0, "vit: hidden width %d unsupported (256, 512, 768, 1024)", d.hidden);
+    LIFTER_REQUIRE(d.heads >= 1 && d.hidden % d.heads == 0 && (d.hidden / d.heads == 32 || d.hidden / d.heads == 64),
+                   "vit: %d heads over width %d unsupported (head width must be 32 or 64)", d.heads, d.hidden);
+    LIFTER_REQUIRE(d.blocks >= 0 && d.blocks <= 64, "vit: %d blocks", d.blocks);
+    LIFTER_REQUIRE(d.mlp_dim >= 64 && d.mlp_dim % 64 == 0, "vit: MLP width %d must be a multiple of 64", d.mlp_dim);
+    LIFTER_REQUIRE(d.head_dim >= 64 && d.head_dim % 64 == 0, "vit: head MLP width %d must be a multiple of 64", d.head_dim);
+    LIFTER_REQUIRE(d.out_dim >= 1 && d.out_dim <= 64, "vit: %d outputs per token unsupported (1..64)", d.out_dim);
+    LIFTER_REQUIRE(d.fmt == FMT_F16 || d.fmt == FMT_BF16, "vit: unknown operand format %d", d.fmt);
+    return LIFTER_OK;
+}
+
+// 16-bit elements per token in the workspace: h0, h1, u, o (hidden each), qkv (3 hidden), m (mlp_dim), r (head_dim)
+static long vit_ws_halfs_per_token(const VitDesc& d) { return 7L * d.hidden + d.mlp_dim + d.head_dim; }
+
+int64_t vit_workspace_bytes(const VitDesc& d, int64_t poses) {
+    if (vit_validate(d) != LIFTER_OK || poses < 0) return LIFTER_ERR_INVALID;
+    return poses * d.tokens * vit_ws_halfs_per_token(d) * 2 + 256;
+}
+
+int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace, float* out, cudaStream_t st) {
+    LIFTER_PROPAGATE(vit_validate(d));
+    if (poses <= 0) return LIFTER_OK;
+    LIFTER_REQUIRE(x && workspace && out, "vit_forward: null pointer");
+    LIFTER_REQUIRE(d.map_w && d.map_b && d.pos && d.head_b1 && d.head_b2 && d.w_head1 && d.w_head2, "vit_forward: null parameter");
+    LIFTER_REQUIRE(d.blocks == 0 || (d.ln && d.mlp_b1 && d.mlp_b2 && d.w_qkv && d.w_out && d.w_mlp1 && d.w_mlp2), "vit_forward: null block parameter");
+    LIFTER_REQUIRE(reinterpret_cast<uintptr_t>(workspace) % 16 == 0, "vit_forward: workspace must be 16-byte aligned");
+    const long T = poses * d.tokens;
+    LIFTER_REQUIRE(T <= 0x7fffffffL, "vit_forward: %ld tokens in one call; process the batch in chunks", T);
+    const int H = d.hidden, nv = H / 256, dh = H / d.heads, M = static_cast<int>(T);
+    unsigned short* ws = static_cast<unsigned short*>(workspace);
+    unsigned short* h0 = ws;
+    unsigned short* h1 = h0 + T * H;
+    unsigned short* u = h1 + T * H;
+    unsigned short* o = u + T * H;
+    unsigned short* qkv = o + T * H;
+    unsigned short* m = qkv + T * 3L * H;
+    unsigned short* r = m + T * static_cast<long>(d.mlp_dim);
+    const unsigned row_blocks = static_cast<unsigned>((T + 7) / 8);                   // 8 warps = 8 token rows per block
+
+    {   // embedding (+ the first block's LayerNorm pair)
+        const float* ln0 = d.blocks > 0 ? d.ln : nullptr;
+        const float* l1 = ln0 ? ln0 + H : nullptr;
+        const float* l2 = ln0 ? ln0 + 2 * H : nullptr;
+        const float* l3 = ln0 ? ln0 + 3 * H : nullptr;
+        if (d.in_dim == 2) {
+            VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_kernel", vit_embed_kernel<NV, 2>, dim3(row_blocks), dim3(256), 0, st, x, T,
+                                                             d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, static_cast<void*>(h0), ln0, l1, l2, l3,
+                                                             d.ln_eps, static_cast<void*>(u), d.fmt)));
+        } else {
+            VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_kernel", vit_embed_kernel<NV, 0>, dim3(row_blocks), dim3(256), 0, st, x, T,
+                                                             d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, static_cast<void*>(h0), ln0, l1, l2, l3,
+                                                             d.ln_eps, static_cast<void*>(u), d.fmt)));
+        }
+    }
+    const size_t smem = att_smem_bytes(d.tokens, dh);
+    if (smem > 48 * 1024) {
+        if (dh == 64) LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        else          LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    }
+    const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(dh));
+    const long pose_heads = poses * d.heads;
+    const size_t esz = 2;
+    for (int b = 0; b < d.blocks; ++b) {
+        const float* ln = d.ln + static_cast<long>(b) * 6 * H;
+        const char* wqkv = static_cast<const char*>(d.w_qkv) + static_cast<long>(b) * 3 * H * H * esz;
+        const char* wout = static_cast<const char*>(d.w_out) + static_cast<long>(b) * H * H * esz;
+        const char* w1 = static_cast<const char*>(d.w_mlp1) + static_cast<long>(b) * d.mlp_dim * H * esz;
+        const char* w2 = static_cast<const char*>(d.w_mlp2) + static_cast<long>(b) * H * d.mlp_dim * esz;
+        // u = mhsa.norm(norm1(h0))   (block 0: done by the embedding kernel)      baselineModel.py:303, 244
+        if (b > 0) VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_layernorm_kernel", vit_layernorm_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
+                                                         static_cast<const void*>(h0), T, ln, ln + H, ln + 2 * H, ln + 3 * H, d.ln_eps,
+                                                         static_cast<void*>(u), d.fmt)));
+        GemmArgs g;                                                             // qkv = u Wqkv^T (no bias)   :246
+        g.A = u; g.lda = H; g.B = wqkv; g.ldb = H; g.M = M; g.N = 3 * H; g.K = H; g.fmt = d.fmt;
+        g.out_mode = OUT_16_TMA; g.D = qkv; g.ldd = 3 * H; g.tag = "vit_qkv";
+        LIFTER_PROPAGATE(gemm_launch(g, st));
+        if (dh == 64)
+            LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<64>, dim3(static_cast<unsigned>((pose_heads + ATT_WARPS - 1) / ATT_WARPS)),
+                                         dim3(ATT_WARPS * 32), smem, st, static_cast<const void*>(qkv), pose_heads, d.tokens, d.heads, scale_log2e, static_cast<void*>(o), d.fmt));
+        else
+            LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<32>, dim3(static_cast<unsigned>((pose_heads + ATT_WARPS - 1) / ATT_WARPS)),
+                                         dim3(ATT_WARPS * 32), smem, st, static_cast<const void*>(qkv), pose_heads, d.tokens, d.heads, scale_log2e, static_cast<void*>(o), d.fmt));
+        GemmArgs go;                                                            // h1 = h0 + o Wout^T        :254, 303
+        go.A = o; go.lda = H; go.B = wout; go.ldb = H; go.M = M; go.N = H; go.K = H; go.fmt = d.fmt;
+        go.out_mode = OUT_16_TMA; go.D = h1; go.ldd = H; go.residual = h0; go.ldr = H; go.tag = "vit_attn_out";
+        LIFTER_PROPAGATE(gemm_launch(go, st));
+        VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_layernorm_kernel", vit_layernorm_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
+                                                         static_cast<const void*>(h1), T, ln + 4 * H, ln + 5 * H, static_cast<const float*>(nullptr),
+                                                         static_cast<const float*>(nullptr), d.ln_eps, static_cast<void*>(u), d.fmt)));
+        GemmArgs g1;                                                            // m = GELU(u W1^T + b1)     :296-298
+        g1.A = u; g1.lda = H; g1.B = w1; g1.ldb = H; g1.M = M; g1.N = d.mlp_dim; g1.K = H; g1.fmt = d.fmt;
+        g1.out_mode = OUT_16_TMA; g1.D = m; g1.ldd = d.mlp_dim; g1.shift = d.mlp_b1 + static_cast<long>(b) * d.mlp_dim; g1.relu = 2;
+        g1.tag = "vit_mlp1";
+        LIFTER_PROPAGATE(gemm_launch(g1, st));
+        GemmArgs g2;                                                            // h0 = h1 + m W2^T + b2     :299, 304
+        g2.A = m; g2.lda = d.mlp_dim; g2.B = w2; g2.ldb = d.mlp_dim; g2.M = M; g2.N = H; g2.K = d.mlp_dim; g2.fmt = d.fmt;
+        g2.out_mode = OUT_16_TMA; g2.D = h0; g2.ldd = H; g2.shift = d.mlp_b2 + static_cast<long>(b) * H; g2.residual = h1; g2.ldr = H;
+        g2.tag = "vit_mlp2";
+        LIFTER_PROPAGATE(gemm_launch(g2, st));
+    }
+    GemmArgs gh;                                                                // r = ReLU(h0 Wh1^T + b)    :336-338
+    gh.A = h0; gh.lda = H; gh.B = d.w_head1; gh.ldb = H; gh.M = M; gh.N = d.head_dim; gh.K = H; gh.fmt = d.fmt;
+    gh.out_mode = OUT_16_TMA; gh.D = r; gh.ldd = d.head_dim; gh.shift = d.head_b1; gh.relu = 1; gh.tag = "vit_head1";
+    LIFTER_PROPAGATE(gemm_launch(gh, st));
+    GemmArgs gf;                                                                // out = r Wh2^T + b (fp32)  :339
+    gf.A = r; gf.lda = d.head_dim; gf.B = d.w_head2; gf.ldb = d.head_dim; gf.M = M; gf.N = 64; gf.K = d.head_dim; gf.fmt = d.fmt;
+    gf.out_mode = OUT_32_DIRECT; gf.D = out; gf.n_valid = d.out_dim; gf.shift = d.head_b2; gf.tag = "vit_head2";
+    LIFTER_PROPAGATE(gemm_launch(gf, st));
+    return LIFTER_OK;
+}
+
+}  // namespace lifter
+
+// ---- C ABI (include/lifter_b200.h) ---------------------------------------------------------------------------------
+#include "../../include/lifter_b200.h"
+
+static lifter::VitDesc to_desc(const lifter_vit_t* v) {
+    lifter::VitDesc d;
+    d.tokens = v->tokens; d.in_dim = v->in_dim; d.hidden = v->hidden; d.heads = v->heads; d.blocks = v->blocks;
+    d.mlp_dim = v->mlp_dim; d.head_dim = v->head_dim; d.out_dim = v->out_dim; d.fmt = v->fmt; d.ln_eps = v->ln_eps;
+    d.map_w = v->map_w; d.map_b = v->map_b; d.pos = v->pos; d.ln = v->ln; d.mlp_b1 = v->mlp_b1; d.mlp_b2 = v->mlp_b2;
+    d.head_b1 = v->head_b1; d.head_b2 = v->head_b2; d.w_qkv = v->w_qkv; d.w_out = v->w_out; d.w_mlp1 = v->w_mlp1;
+    d.w_mlp2 = v->w_mlp2; d.w_head1 = v->w_head1; d.w_head2 = v->w_head2;
+    return d;
+}
+
+extern "C" {
+
+int64_t lifter_vit_workspace_bytes(const lifter_vit_t* vit, int64_t poses) {
+    if (vit == nullptr) return LIFTER_ERR_INVALID;
+    return lifter::vit_workspace_bytes(to_desc(vit), poses);
+}
+
+int lifter_vit_forward(const lifter_vit_t* vit, const float* x, int64_t poses, void* workspace, float* out, void* stream) {
+    LIFTER_REQUIRE(vit != nullptr, "vit_forward: null descriptor");
+    return lifter::vit_forward(to_desc(vit), x, poses, workspace, out, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

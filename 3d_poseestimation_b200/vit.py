@@ -1,0 +1,181 @@
+"""``MyViT`` behind the drop-in import name (``from baselineModel import MyViT``: ``train_1.py:35``, ``train_5.py:58,63``).
+
+Mirror of ``phase1_lifting/baselineModel.py:220-362``: ``get_positional_embeddings``, ``Attention``, ``MyViTBlock``,
+``MyViT`` -- same constructor arguments, sub-module names, ``state_dict`` keys / shapes / dtypes, and the same order of
+torch-RNG consumption at construction (same seed => same initial weights).  ``forward(images)`` takes ``(B, 17, 2)`` fp32
+CUDA and returns ``(B, 17, 3)`` fp32.
+
+Scope of this round: the EVAL-MODE forward (``model.eval()`` / ``torch.no_grad()``, the inference and validation call
+sites ``train_1.py:112-134``) runs on the sm_100a kernels behind ``lifter_vit_forward`` (tcgen05 GEMMs with fused
+bias / GELU / ReLU / residual epilogues, LayerNorm, attention and embedding kernels).  The training backward of the
+transformer is not built yet: ``forward`` with autograd enabled raises instead of falling back to PyTorch.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _cabi
+
+__all__ = ["get_positional_embeddings", "Attention", "MyViTBlock", "MyViT"]
+
+
+def get_positional_embeddings(sequence_length, d=2):
+    """``baselineModel.py:220-225`` (vectorised; the reference fills a float32 tensor element by element)."""
+    i = np.arange(sequence_length, dtype=np.float64)[:, None]
+    j = np.arange(d)[None, :]
+    table = np.where(j % 2 == 0, np.sin(i / (1e4 ** (j / d))), np.cos(i / (1e4 ** ((j - 1) / d))))
+    return torch.from_numpy(table.astype(np.float32))
+
+
+def _fused_only(name):
+    raise RuntimeError(f"{name} runs fused inside MyViT.forward (sm_100a kernels); it has no standalone or CPU path")
+
+
+class Attention(torch.nn.Module):
+    """Parameter holder of ``baselineModel.py:228-254``: ``norm``, bias-free ``to_qkv`` and ``to_out``."""
+
+    def __init__(self, dim, heads=8, dim_head=64):
+        super().__init__()
+        inner_dim = dim_head * heads
+        self.heads = heads
+        self.scale = dim_head ** -0.5
+        self.norm = torch.nn.LayerNorm(dim)
+        self.attend = torch.nn.Softmax(dim=-1)
+        self.to_qkv = torch.nn.Linear(dim, inner_dim * 3, bias=False)
+        self.to_out = torch.nn.Linear(inner_dim, dim, bias=False)
+
+    def forward(self, x):
+        _fused_only("Attention")
+
+
+class MyViTBlock(torch.nn.Module):
+    """Parameter holder of ``baselineModel.py:286-305``."""
+
+    def __init__(self, hidden_d, n_heads, mlp_ratio=4):
+        super().__init__()
+        self.hidden_d = hidden_d
+        self.n_heads = n_heads
+        self.norm1 = torch.nn.LayerNorm(hidden_d)
+        self.mhsa = Attention(hidden_d, n_heads, int(hidden_d / n_heads))
+        self.norm2 = torch.nn.LayerNorm(hidden_d)
+        self.mlp = torch.nn.Sequential(torch.nn.Linear(hidden_d, mlp_ratio * hidden_d), torch.nn.GELU(),
+                                       torch.nn.Linear(mlp_ratio * hidden_d, hidden_d))
+
+    def forward(self, x):
+        _fused_only("MyViTBlock")
+
+
+class MyViT(torch.nn.Module):
+    """``baselineModel.py:307-362``.  ``MyViT(chw=(1, 17, 2), n_blocks=2, hidden_d=256, n_heads=4, out_d=3)``."""
+
+    def __init__(self, chw=(1, 17, 2), n_blocks=2, hidden_d=256, n_heads=4, out_d=3):
+        super().__init__()
+        if hidden_d % 256 or not 256 <= hidden_d <= 1024:
+            raise ValueError(f"MyViT (sm_100a build): hidden_d must be 256, 512, 768 or 1024, got {hidden_d}")
+        if hidden_d % n_heads or hidden_d // n_heads not in (32, 64):
+            raise ValueError(f"MyViT (sm_100a build): hidden_d / n_heads must be 32 or 64, got {hidden_d}/{n_heads}")
+        if not 1 <= chw[1] <= 32 or not 1 <= chw[2] <= 4 or not 1 <= out_d <= 64:
+            raise ValueError("MyViT (sm_100a build): at most 32 joints, 4 input values and 64 outputs per joint")
+        self.chw = chw
+        self.n_block = n_blocks
+        self.n_heads = n_heads
+        self.hidden_d = hidden_d
+        self.out_d = out_d
+        self.input_d = chw[2]
+        self.linear_mapper = torch.nn.Linear(self.input_d, self.hidden_d)
+        self.pos_embed = torch.nn.Parameter(get_positional_embeddings(chw[1], self.hidden_d))
+        self.pos_embed.requires_grad = False
+        self.blocks = torch.nn.ModuleList([MyViTBlock(hidden_d, n_heads) for _ in range(n_blocks)])
+        self.mlp = torch.nn.Sequential(torch.nn.Linear(self.hidden_d, int(self.hidden_d / 2)), torch.nn.ReLU(),
+                                       torch.nn.Linear(int(self.hidden_d / 2), out_d))
+        self.infer_format = "fp16"        # GEMM operand / activation format of the eval path ("fp16" or "bf16")
+        self.chunk_poses = 2048           # poses per pass of the kernel sequence (activations of a pass stay near L2)
+        self._packed = None               # (key, tensors, descriptor)
+        self._workspace = None
+
+    # ------------------------------------------------------------------------------------------------ packing
+    def _pack_key(self):
+        return tuple((p.data_ptr(), p._version) for p in self.parameters()) + (self.infer_format,)
+
+    def _pack(self, dev):
+        """fp32 side tables and 16-bit GEMM operands in the layout of ``lifter_vit_t``; rebuilt when a parameter changed."""
+        key = self._pack_key()
+        if self._packed is not None and self._packed[0] == key:
+            return self._packed[2]
+        H, nb = self.hidden_d, self.n_block
+        dt = torch.float16 if self.infer_format == "fp16" else torch.bfloat16
+        f32 = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()
+
+        def stack(fn, shape):
+            return torch.stack([fn(b) for b in self.blocks]) if nb else torch.zeros((0,) + shape, device=dev)
+
+        t = {}
+        t["map_w"], t["map_b"], t["pos"] = f32(self.linear_mapper.weight), f32(self.linear_mapper.bias), f32(self.pos_embed)
+        t["ln"] = f32(stack(lambda b: torch.stack([b.norm1.weight, b.norm1.bias, b.mhsa.norm.weight, b.mhsa.norm.bias,
+                                                   b.norm2.weight, b.norm2.bias]), (6, H)))
+        t["mlp_b1"] = f32(stack(lambda b: b.mlp[0].bias, (4 * H,)))
+        t["mlp_b2"] = f32(stack(lambda b: b.mlp[2].bias, (H,)))
+        t["head_b1"] = f32(self.mlp[0].bias)
+        hb2 = torch.zeros(64, device=dev)
+        hb2[:self.out_d] = f32(self.mlp[2].bias)
+        t["head_b2"] = hb2
+        op = lambda w: w.detach().to(device=dev, dtype=dt).contiguous()
+        t["w_qkv"] = op(stack(lambda b: b.mhsa.to_qkv.weight, (3 * H, H)))
+        t["w_out"] = op(stack(lambda b: b.mhsa.to_out.weight, (H, H)))
+        t["w_mlp1"] = op(stack(lambda b: b.mlp[0].weight, (4 * H, H)))
+        t["w_mlp2"] = op(stack(lambda b: b.mlp[2].weight, (H, 4 * H)))
+        t["w_head1"] = op(self.mlp[0].weight)
+        wh2 = torch.zeros(64, H // 2, device=dev, dtype=dt)
+        wh2[:self.out_d] = op(self.mlp[2].weight)
+        t["w_head2"] = wh2
+        d = _cabi.VitDesc()
+        d.tokens, d.in_dim, d.hidden, d.heads, d.blocks = self.chw[1], self.input_d, H, self.n_heads, nb
+        d.mlp_dim, d.head_dim, d.out_dim = 4 * H, H // 2, self.out_d
+        d.fmt = 0 if self.infer_format == "fp16" else 1
+        d.ln_eps = 1e-5
+        for k, v in t.items():
+            setattr(d, k, v.data_ptr() if v.numel() else None)
+        self._packed = (key, t, d)
+        return d
+
+    # ------------------------------------------------------------------------------------------------ forward
+    def forward(self, images):
+        if not torch.is_tensor(images) or not images.is_cuda:
+            raise RuntimeError("MyViT: the sm_100a build has no CPU path; move the model and the input to a B200")
+        if images.dim() != 3 or images.shape[1] != self.chw[1] or images.shape[2] != self.input_d:
+            raise ValueError(f"MyViT expects (B, {self.chw[1]}, {self.input_d}) key points, got {tuple(images.shape)}")
+        if torch.is_grad_enabled() and (self.training or images.requires_grad):
+            raise NotImplementedError("MyViT (sm_100a build): only the eval-mode forward is built so far; call "
+                                      "model.eval() and run under torch.no_grad() (training backward: next round)")
+        return self.infer(images)
+
+    @torch.no_grad()
+    def infer(self, images, chunk_poses=None):
+        """Eval-mode forward, ``chunk_poses`` poses per pass of the kernel sequence."""
+        x = images.detach().to(torch.float32).contiguous()
+        dev = x.device
+        if self.linear_mapper.weight.device != dev:
+            raise RuntimeError("MyViT: parameters and input live on different devices")
+        B = int(x.shape[0])
+        out = torch.empty((B, self.chw[1], self.out_d), dtype=torch.float32, device=dev)
+        if B == 0:
+            return out
+        d = self._pack(dev)
+        lib = _cabi.lib()
+        chunk = int(chunk_poses or self.chunk_poses)
+        chunk = max(1, min(chunk, B))
+        need = lib.lifter_vit_workspace_bytes(C.byref(d), chunk)
+        if need < 0:
+            raise ValueError("MyViT: " + _cabi.last_error())
+        if self._workspace is None or self._workspace.numel() < need or self._workspace.device != dev:
+            self._workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+        st = _cabi.stream_ptr()
+        in_row, out_row = self.chw[1] * self.input_d * 4, self.chw[1] * self.out_d * 4
+        for b0 in range(0, B, chunk):
+            n = min(chunk, B - b0)
+            _cabi.check(lib.lifter_vit_forward(C.byref(d), C.c_void_p(x.data_ptr() + b0 * in_row), n,
+                                               _cabi.ptr(self._workspace), C.c_void_p(out.data_ptr() + b0 * out_row), st))
+        return out

@@ -258,12 +258,40 @@ typedef struct lifter_optim {
 int lifter_train_backward_step(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, const lifter_optim_t* opt,
                                void* stream);
 
+/* ---- MyViT lifter, eval-mode forward (phase1_lifting/baselineModel.py:307-362: the model train_1.py:35 and
+ * train_5.py:58,63 instantiate).  Joints are tokens: Linear(in_dim -> hidden) + positional embedding, `blocks` x
+ * [x + to_out(softmax(q k^T / sqrt(d)) v) with q, k, v = to_qkv(mhsa.norm(norm1(x))); x + mlp(norm2(x)), exact GELU],
+ * then Linear(hidden -> hidden / 2) -> ReLU -> Linear(-> out_dim) per token.  Every Linear over the [poses * tokens][.]
+ * token matrix is the tcgen05 GEMM with bias / ReLU / GELU / residual in its epilogue; LayerNorm, attention and the
+ * embedding are separate kernels.  16-bit activations live in `workspace` (lifter_vit_workspace_bytes).  Limits:
+ * tokens <= 32, in_dim <= 4, hidden in {256, 512, 768, 1024}, head width 32 or 64, out_dim <= 64.               */
+typedef struct lifter_vit {
+    int32_t tokens, in_dim, hidden, heads, blocks, mlp_dim, head_dim, out_dim;
+    int32_t fmt;                  /* LIFTER_FMT_F16 / LIFTER_FMT_BF16: GEMM operands and stored activations       */
+    float ln_eps;                 /* torch.nn.LayerNorm default 1e-5                                              */
+    const float* map_w; const float* map_b; const float* pos;   /* [hidden][in_dim], [hidden], [tokens][hidden]     */
+    const float* ln;              /* [blocks][6][hidden]: norm1 w, b; mhsa.norm w, b; norm2 w, b                   */
+    const float* mlp_b1;          /* [blocks][mlp_dim]                                                             */
+    const float* mlp_b2;          /* [blocks][hidden]                                                              */
+    const float* head_b1;         /* [head_dim]                                                                    */
+    const float* head_b2;         /* [64], zero past out_dim                                                       */
+    const void* w_qkv;            /* 16-bit [blocks][3 * hidden][hidden]   (Linear.weight layout: [out][in])       */
+    const void* w_out;            /* 16-bit [blocks][hidden][hidden]                                               */
+    const void* w_mlp1;           /* 16-bit [blocks][mlp_dim][hidden]                                              */
+    const void* w_mlp2;           /* 16-bit [blocks][hidden][mlp_dim]                                              */
+    const void* w_head1;          /* 16-bit [head_dim][hidden]                                                     */
+    const void* w_head2;          /* 16-bit [64][head_dim], rows past out_dim zero                                 */
+} lifter_vit_t;
+int64_t lifter_vit_workspace_bytes(const lifter_vit_t* vit, int64_t poses);
+/* x [poses][tokens][in_dim] fp32 -> out [poses][tokens][out_dim] fp32; asynchronous on `stream`.                  */
+int lifter_vit_forward(const lifter_vit_t* vit, const float* x, int64_t poses, void* workspace, float* out, void* stream);
+
 /* ---- test hook: one tcgen05 GEMM  D[M][N] = sum_k A(m,k) B(n,k) ------------------------------------ */
 typedef struct lifter_gemm_desc {
     const void* A; int64_t lda; const void* B; int64_t ldb;
     int32_t M, N, K, a_mn_major, b_mn_major, fmt;
     int32_t out_mode;            /* 0: 16-bit [M][ldd], 1: fp32 split-K slabs, 2: fp32 [M][n_valid] */
-    void* D; int64_t ldd; int32_t n_valid; int32_t splits; int32_t relu;
+    void* D; int64_t ldd; int32_t n_valid; int32_t splits; int32_t relu;   /* relu: 0 none, 1 ReLU, 2 exact GELU */
     const float* scale; const float* shift; const void* residual; int64_t ldr;
     float* stat_sum; float* stat_sq;
     int32_t cluster;             /* 0 auto, 1 single-CTA tiles (cta_group::1), 2 CTA pairs (cta_group::2, 256-row tiles) */

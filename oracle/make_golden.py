@@ -114,6 +114,36 @@ def process_data_case():
     print("wrote process_data", {k: v.shape for k, v in out.items()})
 
 
+def vit_case():
+    """MyViT (baselineModel.py:307-362) through the imported reference module: default configuration with the oracle's
+    numpy-seeded weights, a torch-seeded default construction (pins the constructor's RNG consumption and the positional
+    embedding), and a 3-block / 8-head variant."""
+    from oracle import vit_oracle as V
+    out = {}
+    rs = np.random.RandomState(77)
+    for tag, cfg, B in (("default", dict(), 5), ("b3h8", dict(n_blocks=3, n_heads=8), 3)):
+        params = V.numpy_init(11, **cfg)
+        m = ref_model.MyViT(**cfg)
+        m.load_state_dict({k: v.clone() for k, v in params.items()}, strict=True)
+        m.eval()
+        x = rs.normal(0, 1, (B, 17, 2)).astype(np.float32)
+        with torch.no_grad():
+            y = m(torch.from_numpy(x))
+        out[tag + "_x"], out[tag + "_y"] = x, y.numpy()
+    torch.manual_seed(5)
+    m = ref_model.MyViT()
+    sd = m.state_dict()
+    out["seeded_names"] = np.array(list(sd.keys()))
+    out["seeded_sums"] = np.array([float(v.double().sum()) for v in sd.values()])
+    out["seeded_abs"] = np.array([float(v.double().abs().sum()) for v in sd.values()])
+    out["pos_embed"] = sd["pos_embed"].numpy()
+    x = rs.normal(0, 1, (4, 17, 2)).astype(np.float32)
+    with torch.no_grad():
+        out["seeded_x"], out["seeded_y"] = x, m.eval()(torch.from_numpy(x)).numpy()
+    np.savez(os.path.join(GOLD, "vit.npz"), **out)
+    print("wrote vit", {k: v.shape for k, v in out.items()})
+
+
 class MaskedDropout(torch.nn.Module):
     """Stands in for ``torch.nn.Dropout(p)`` in the reference module; same arithmetic, external mask."""
 
@@ -306,6 +336,9 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "ingest":      # only the keypoint-ingest vectors
         ingest_case()
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "vit":
+        vit_case()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "process_data":
         process_data_case()
         sys.exit(0)
@@ -319,3 +352,4 @@ if __name__ == "__main__":
     train_curve_case()
     ingest_case()
     process_data_case()
+    vit_case()

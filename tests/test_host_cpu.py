@@ -134,3 +134,26 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f"{f} imports the oracle"
+
+
+def test_myvit_constructor_mirrors_the_reference(pkg, golden_dir):
+    """baselineModel.py:307-342: same state_dict keys / shapes, same torch-RNG consumption (seed 5 => the reference's
+    initial weights, pinned by per-tensor checksums from the imported reference), same positional embedding; no CPU
+    path and no silent PyTorch fallback for training."""
+    import numpy as np
+    g = np.load(os.path.join(golden_dir, "vit.npz"))
+    torch.manual_seed(5)
+    m = pkg.MyViT()
+    sd = m.state_dict()
+    assert list(sd.keys()) == [str(k) for k in g["seeded_names"]]
+    np.testing.assert_allclose([float(v.double().sum()) for v in sd.values()], g["seeded_sums"], rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose([float(v.double().abs().sum()) for v in sd.values()], g["seeded_abs"], rtol=1e-9)
+    np.testing.assert_allclose(sd["pos_embed"].numpy(), g["pos_embed"], atol=1e-7)
+    assert not m.pos_embed.requires_grad and sum(p.numel() for p in m.parameters()) == sum(v.numel() for v in sd.values())
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(2, 17, 2))                                   # CPU tensor
+    with pytest.raises(ValueError):
+        pkg.MyViT(hidden_d=100)
+    from importlib import import_module
+    bm = import_module("3d_poseestimation_b200.baselineModel")
+    assert bm.MyViT is pkg.MyViT and callable(bm.get_positional_embeddings)

@@ -221,3 +221,14 @@ def test_dataset_processing_matches_reference_process_data(golden_dir, dim, zc):
     m2, s2, lo_, hi_ = D.keypoint_stats(raw, bool(zc))
     assert np.array_equal(m2, mean) and np.array_equal(s2, std)
     assert np.all(lo_ <= m2) and np.all(m2 <= hi_)
+
+
+@pytest.mark.parametrize("tag,cfg", [("default", {}), ("b3h8", dict(n_blocks=3, n_heads=8))])
+def test_vit_oracle_matches_reference_module(golden_dir, tag, cfg):
+    """oracle/vit_oracle.py against the imported reference MyViT (baselineModel.py:307-362)."""
+    from oracle import vit_oracle as V
+    g = np.load(os.path.join(golden_dir, "vit.npz"), allow_pickle=False)
+    params = V.numpy_init(11, **cfg)
+    y = V.vit_forward(params, T(g[tag + "_x"]), **cfg).numpy()
+    np.testing.assert_allclose(y, g[tag + "_y"], rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(V.positional_embeddings(17, 256).numpy(), g["pos_embed"], rtol=0, atol=1e-7)

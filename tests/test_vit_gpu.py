@@ -1,0 +1,94 @@
+"""GPU parity of the MyViT eval-mode forward against the imported reference's golden
+vectors and the fp32 CPU oracle.  fp16 tensor-core operands and 16-bit stored activations: agreement is to fp16
+rounding through two transformer blocks, checked at north_star's eval tolerance after de-normalisation
+(0.5 mm + 1e-2 relative with the repo's std_train_3d / mean_train_3d) and as a relative L2 error."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import vit_oracle as V
+
+pytestmark = pytest.mark.gpu
+T = torch.from_numpy
+
+
+def _model(pkg, params, **cfg):
+    m = pkg.MyViT(**cfg)
+    m.load_state_dict(params)
+    return m.cuda().eval()
+
+
+def rel_l2(a, b):
+    a, b = torch.as_tensor(a).double().reshape(-1), torch.as_tensor(b).double().reshape(-1)
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+@pytest.mark.parametrize("tag,cfg", [("default", {}), ("b3h8", dict(n_blocks=3, n_heads=8))])
+def test_vit_eval_matches_reference_golden(pkg, golden_dir, tag, cfg):
+    g = np.load(os.path.join(golden_dir, "vit.npz"))
+    m = _model(pkg, V.numpy_init(11, **cfg), **cfg)
+    with torch.no_grad():
+        y = m(T(g[tag + "_x"]).cuda()).cpu().numpy()
+    ref = g[tag + "_y"]
+    assert y.shape == ref.shape
+    assert rel_l2(y, ref) < 5e-3, rel_l2(y, ref)
+    assert np.abs(y - ref).max() <= 5e-3 * np.abs(ref).max() + 2e-3
+
+
+def test_vit_torch_seeded_construction_matches_reference_output(pkg, golden_dir):
+    """Default torch initialisation under the same seed, then the reference's output on the same key points."""
+    g = np.load(os.path.join(golden_dir, "vit.npz"))
+    torch.manual_seed(5)
+    m = pkg.MyViT().cuda().eval()
+    with torch.no_grad():
+        y = m(T(g["seeded_x"]).cuda()).cpu().numpy()
+    assert rel_l2(y, g["seeded_y"]) < 5e-3
+
+
+@pytest.mark.parametrize("B", [1, 7, 300, 2049])
+def test_vit_eval_matches_oracle_after_denormalisation(pkg, golden_dir, B):
+    st = dict(np.load(os.path.join(golden_dir, "h36m_stats.npz")))
+    m3, s3 = T(st["mean_train_3d"]).float(), T(st["std_train_3d"]).float()
+    params = V.numpy_init(3)
+    m = _model(pkg, params)
+    x = torch.randn(B, 17, 2, generator=torch.Generator().manual_seed(B))
+    ref = V.vit_forward(params, x) * s3 + m3
+    with torch.no_grad():
+        out = m(x.cuda()).cpu() * s3 + m3
+    err = (out - ref).abs()
+    tol = 0.5e-3 + 1e-2 * ref.abs()                      # north_star: 0.5 mm absolute + 1e-2 relative (metres)
+    frac_ok = float((err <= tol).float().mean())
+    # 16-bit storage of every activation through two transformer blocks (~15 rounding points, ~1e-3 of the output
+    # scale in total; these un-trained weights give outputs of several standard deviations): the north_star band holds
+    # for all but a tail of small-valued coordinates, and everything is inside 2 mm + 1e-2 relative.  DESIGN.md section 9.
+    assert frac_ok >= 0.995, f"{100 * (1 - frac_ok):.2f} % of the outputs outside 0.5 mm + 1e-2 relative"
+    loose = 2e-3 + 1e-2 * ref.abs()
+    assert bool((err <= loose).all()), f"max err {err.max().item() * 1e3:.3f} mm; worst err/tol {(err / loose).max().item():.2f}"
+    assert rel_l2(out - m3, ref - m3) < 3e-3
+
+
+def test_vit_chunking_weight_updates_and_formats(pkg):
+    params = V.numpy_init(4)
+    m = _model(pkg, params)
+    x = torch.randn(777, 17, 2, device="cuda")
+    a = m.infer(x)
+    assert torch.equal(a, m.infer(x, chunk_poses=100)) and torch.equal(a, m.infer(x, chunk_poses=1))
+    with torch.no_grad():
+        m.mlp[2].bias.add_(1.0)                          # in-place update, like an optimiser step
+        b = m(x)
+    assert torch.allclose(b - a, torch.ones_like(a), atol=1e-5)
+    m.infer_format = "bf16"
+    c = m.infer(x)
+    assert rel_l2(c.cpu(), b.cpu()) < 5e-2 and not torch.equal(c, b)
+    assert tuple(m.infer(x[:0]).shape) == (0, 17, 3)
+
+
+def test_vit_training_forward_is_not_a_silent_fallback(pkg):
+    m = pkg.MyViT().cuda()
+    x = torch.randn(4, 17, 2, device="cuda")
+    with pytest.raises(NotImplementedError):
+        m.train()(x)
+    with pytest.raises(ValueError):
+        m.eval()(torch.randn(4, 16, 2, device="cuda"))
