@@ -154,7 +154,7 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return x >= 0.0f ? fmaf(-x, hl, x) : x * hl;
 }
 
-template <int BLOCK_N, bool TWO_SM>
+template <int BLOCK_N, bool TWO_SM, bool GELU>
 __global__ void LIFTER_GEMM_REGS
 lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
     using C = Cfg<BLOCK_N, TWO_SM>;
@@ -386,12 +386,12 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                     for (int j = 0; j < 32; ++j)
                         x[j] = fmaf(x[j], s_scale[col_base + c * 32 + j], s_shift[col_base + c * 32 + j]);
                 }
-                if (p.relu == 1) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.0f);
-                } else if (p.relu == 2) {                            // torch.nn.GELU(): 0.5 x (1 + erf(x / sqrt 2))
+                if constexpr (GELU) {          // torch.nn.GELU(); its own instantiation: the lifter's kernels carry none of it
 #pragma unroll
                     for (int j = 0; j < 32; ++j) x[j] = gelu_erf(x[j]);
+                } else if (p.relu) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.0f);
                 }
 
                 if (p.out_mode == OUT_16_TMA) {
@@ -545,13 +545,13 @@ int encode_2d(CUtensorMap* map, CUtensorMapDataType dt, int elem_bytes, const vo
     return LIFTER_OK;
 }
 
-template <int BLOCK_N, bool TWO_SM>
+template <int BLOCK_N, bool TWO_SM, bool GELU = false>
 int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     using C = Cfg<BLOCK_N, TWO_SM>;
     constexpr int CL = TWO_SM ? 2 : 1;
     static bool configured = false;
     if (!configured) {
-        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(lifter_gemm_kernel<BLOCK_N, TWO_SM>,
+        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(lifter_gemm_kernel<BLOCK_N, TWO_SM, GELU>,
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         configured = true;
     }
@@ -588,7 +588,7 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     const int clusters = p.num_tiles < max_clusters ? p.num_tiles : max_clusters;
     cfg.gridDim = dim3(clusters * CL);
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    LIFTER_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lifter_gemm_kernel<BLOCK_N, TWO_SM>, p));
+    LIFTER_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lifter_gemm_kernel<BLOCK_N, TWO_SM, GELU>, p));
     if (a.tag != nullptr) trace_mark(a.tag, stream); else trace_mark("gemm", stream);
     return LIFTER_OK;
 }
@@ -640,6 +640,11 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     // CTA pairs (cta_group::2, 256-row tiles) whenever there are two M-blocks to pair up.
     // a.cluster: 0 = auto, 1 = single-CTA tiles, 2 = pairs (when the shape allows).
     const bool pair = a.cluster != 1 && p.num_m_blocks >= 2 && a.N > 64;
+    LIFTER_REQUIRE(a.relu >= 0 && a.relu <= 2, "gemm: activation %d (0 none, 1 ReLU, 2 GELU)", a.relu);
+    if (a.relu == 2) {                                     // GELU epilogue: the transformer lifter's MLP-up projection
+        LIFTER_REQUIRE(a.N > 128, "gemm: the GELU epilogue is built for N > 128 (got %d)", a.N);
+        return pair ? launch_impl<256, true, true>(p, a, stream) : launch_impl<256, false, true>(p, a, stream);
+    }
     if (a.N <= 64) return launch_impl<64, false>(p, a, stream);
     if (a.N <= 128) return pair ? launch_impl<128, true>(p, a, stream) : launch_impl<128, false>(p, a, stream);
     return pair ? launch_impl<256, true>(p, a, stream) : launch_impl<256, false>(p, a, stream);

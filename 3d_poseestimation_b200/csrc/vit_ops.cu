@@ -140,17 +140,38 @@ __global__ void __launch_bounds__(256) vit_layernorm_kernel(const void* __restri
 }
 
 // baselineModel.py:243-253.  qkv 16-bit [T][3 * Hd] = [q | k | v], each (head, d) major; o 16-bit [T][Hd].
-// One warp per (pose, head): the head's q, k, v slices (N x DH each) are staged in shared memory with coalesced 16-byte
-// loads; lane i < N owns query row i: scores against every key (key rows are read as broadcasts), softmax in fp32,
-// then the weighted sum of the value rows.
+// One warp per (pose, head), on the warp-level tensor-core MMA (mma.sync m16n8k16, fp32 accumulate; a 17 x 17 x 64
+// problem is far below a tcgen05 tile): the head's q, k, v slices are staged in shared memory with coalesced 16-byte loads
+// (rows past the token count zeroed), S = q k^T by ldmatrix + MMA per 16-row tile, softmax in fp32 on the accumulator
+// fragments (columns past the token count masked), P re-used in registers as the A operand of P v, the output rows
+// normalised and staged through the (now dead) q rows for coalesced 16-byte stores.
 constexpr int ATT_WARPS = 4;
+
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1, int fmt) {
+    if (fmt == FMT_BF16)
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                     : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+    else
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                     : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
 template <int DH>
 __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const void* __restrict__ qkv, long pose_heads,
                                                                        int tokens, int heads, float scale_log2e,
                                                                        void* __restrict__ o, int fmt) {
     griddep_launch();
     griddep_wait();
-    constexpr int LDS = DH + 8;                                       // halfs per staged row: 16-byte aligned, bank-skewed
+    constexpr int LDS = DH + 8;                        // halfs per staged row: 16-byte aligned, conflict-free for ldmatrix
+    constexpr int VPR = DH / 8;                        // 16-byte vectors per row slice
     extern __shared__ __align__(16) unsigned char att_smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const long ph = static_cast<long>(blockIdx.x) * ATT_WARPS + wid;
@@ -158,77 +179,111 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
     const long pose = ph / heads;
     const int head = static_cast<int>(ph - pose * heads);
     const int Hd = heads * DH;
-    unsigned short* sq = reinterpret_cast<unsigned short*>(att_smem) + static_cast<size_t>(wid) * (3 * tokens * LDS);
-    float* ss = reinterpret_cast<float*>(att_smem + static_cast<size_t>(ATT_WARPS) * 3 * tokens * LDS * 2) + wid * (VIT_MAX_TOKENS * 32);
+    const int R = tokens > 16 ? 32 : 16;               // staged rows per slice (MMA tiles are 16 rows / 16 keys)
+    const int MT = R / 16, NT = (tokens + 7) / 8;
+    unsigned short* sq = reinterpret_cast<unsigned short*>(att_smem) + static_cast<size_t>(wid) * (3 * R * LDS);
     const unsigned short* src = static_cast<const unsigned short*>(qkv) + pose * tokens * (3L * Hd) + head * DH;
-    constexpr int VPR = DH / 8;                                        // 16-byte vectors per row slice
-    for (int i = lane; i < 3 * tokens * VPR; i += 32) {
-        const int vec = i % VPR, rs = i / VPR, slice = rs / tokens, n = rs - slice * tokens;
-        const uint4 val = *reinterpret_cast<const uint4*>(src + n * (3L * Hd) + slice * Hd + vec * 8);
-        *reinterpret_cast<uint4*>(sq + (slice * tokens + n) * LDS + vec * 8) = val;
+    for (int i = lane; i < 3 * R * VPR; i += 32) {
+        const int vec = i % VPR, rs = i / VPR, slice = rs / R, n = rs - slice * R;
+        uint4 val = make_uint4(0u, 0u, 0u, 0u);
+        if (n < tokens) val = *reinterpret_cast<const uint4*>(src + n * (3L * Hd) + slice * Hd + vec * 8);
+        *reinterpret_cast<uint4*>(sq + (slice * R + n) * LDS + vec * 8) = val;
     }
     __syncwarp();
-    const unsigned short* sk = sq + tokens * LDS;
-    const unsigned short* sv = sk + tokens * LDS;
-    if (lane < tokens) {
-        float acc[DH];
+    const uint32_t q_addr = smem_u32(sq), k_addr = q_addr + R * LDS * 2, v_addr = k_addr + R * LDS * 2;
+    const int g = lane >> 2, t4 = lane & 3;
+    for (int mt = 0; mt < MT; ++mt) {
+        // ---- S = q k^T for query rows mt * 16 .. + 15 ----------------------------------------------------------
+        float sc[4][4];
 #pragma unroll
-        for (int v = 0; v < VPR; ++v) {
-            const uint4 r = *reinterpret_cast<const uint4*>(sq + lane * LDS + v * 8);
-            const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) sc[nt][e] = 0.0f;
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) {
+            uint32_t a[4];
+            ldsm_x4(a, q_addr + ((mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + ks * 16 + (lane >> 4) * 8) * 2);
+#pragma unroll
+            for (int np = 0; np < 2; ++np) {           // key tiles 2 np, 2 np + 1 (keys np * 16 .. + 15)
+                if (np * 2 < NT) {
+                    uint32_t bk[4];                    // [0], [1]: tile 2 np (k lo, k hi); [2], [3]: tile 2 np + 1
+                    ldsm_x4(bk, k_addr + ((np * 16 + (lane & 7) + (lane >> 4) * 8) * LDS + ks * 16 + ((lane >> 3) & 1) * 8) * 2);
+                    mma16816(sc[np * 2], a, bk[0], bk[1], fmt);
+                    if (np * 2 + 1 < NT) mma16816(sc[np * 2 + 1], a, bk[2], bk[3], fmt);
+                }
+            }
+        }
+        // ---- softmax over the keys, rows g and g + 8 of the tile ----------------------------------------------------
+        float mx[2] = {-CUDART_INF_F, -CUDART_INF_F};
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                const float2 f = unpack16(wd[e], fmt);
-                acc[v * 8 + 2 * e] = f.x * scale_log2e;                // q / sqrt(d_head), in log2 units for exp2f
-                acc[v * 8 + 2 * e + 1] = f.y * scale_log2e;
+                const int col = nt * 8 + t4 * 2 + (e & 1);
+                sc[nt][e] = col < tokens ? sc[nt][e] * scale_log2e : -CUDART_INF_F;
+                mx[e >> 1] = fmaxf(mx[e >> 1], sc[nt][e]);
             }
+        float den[2] = {0.0f, 0.0f};
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 1));
+            mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 2));
         }
-        float mx = -CUDART_INF_F;
-        for (int j = 0; j < tokens; ++j) {
-            float s = 0.0f;
 #pragma unroll
-            for (int v = 0; v < VPR; ++v) {
-                const uint4 r = *reinterpret_cast<const uint4*>(sk + j * LDS + v * 8);
-                const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
+        for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float2 f = unpack16(wd[e], fmt);
-                    s = fmaf(acc[v * 8 + 2 * e], f.x, s);
-                    s = fmaf(acc[v * 8 + 2 * e + 1], f.y, s);
+            for (int e = 0; e < 4; ++e) {
+                sc[nt][e] = exp2f(sc[nt][e] - mx[e >> 1]);          // masked columns: exp2(-inf) = 0
+                den[e >> 1] += sc[nt][e];
+            }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            den[h] += __shfl_xor_sync(0xffffffffu, den[h], 1);
+            den[h] += __shfl_xor_sync(0xffffffffu, den[h], 2);
+            den[h] = 1.0f / den[h];
+        }
+        // ---- O = P v ------------------------------------------------------------------------------------------------
+        float oc[DH / 8][4];
+#pragma unroll
+        for (int dn = 0; dn < DH / 8; ++dn)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) oc[dn][e] = 0.0f;
+#pragma unroll
+        for (int kt = 0; kt < 2; ++kt) {               // keys kt * 16 .. + 15 = score tiles 2 kt, 2 kt + 1
+            if (kt * 2 < NT) {
+                uint32_t pa[4];
+                pa[0] = pack16(sc[kt * 2][0], sc[kt * 2][1], fmt);
+                pa[1] = pack16(sc[kt * 2][2], sc[kt * 2][3], fmt);
+                pa[2] = pack16(sc[kt * 2 + 1][0], sc[kt * 2 + 1][1], fmt);
+                pa[3] = pack16(sc[kt * 2 + 1][2], sc[kt * 2 + 1][3], fmt);
+#pragma unroll
+                for (int dp = 0; dp < DH / 16; ++dp) {                 // value column tiles 2 dp, 2 dp + 1
+                    uint32_t bv[4];
+                    ldsm_x4_trans(bv, v_addr + ((kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + dp * 16 + (lane >> 4) * 8) * 2);
+                    mma16816(oc[dp * 2], pa, bv[0], bv[1], fmt);
+                    mma16816(oc[dp * 2 + 1], pa, bv[2], bv[3], fmt);
                 }
             }
-            ss[j * 32 + lane] = s;
-            mx = fmaxf(mx, s);
         }
+        // ---- normalise, stage through the q rows of this tile (no longer read) -------------------------------------------
+        __syncwarp();
 #pragma unroll
-        for (int d = 0; d < DH; ++d) acc[d] = 0.0f;
-        float den = 0.0f;
-        for (int j = 0; j < tokens; ++j) {
-            const float p = exp2f(ss[j * 32 + lane] - mx);
-            den += p;
-#pragma unroll
-            for (int v = 0; v < VPR; ++v) {
-                const uint4 r = *reinterpret_cast<const uint4*>(sv + j * LDS + v * 8);
-                const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float2 f = unpack16(wd[e], fmt);
-                    acc[v * 8 + 2 * e] = fmaf(p, f.x, acc[v * 8 + 2 * e]);
-                    acc[v * 8 + 2 * e + 1] = fmaf(p, f.y, acc[v * 8 + 2 * e + 1]);
-                }
-            }
+        for (int dn = 0; dn < DH / 8; ++dn) {
+            *reinterpret_cast<uint32_t*>(sq + (mt * 16 + g) * LDS + dn * 8 + t4 * 2) = pack16(oc[dn][0] * den[0], oc[dn][1] * den[0], fmt);
+            *reinterpret_cast<uint32_t*>(sq + (mt * 16 + g + 8) * LDS + dn * 8 + t4 * 2) = pack16(oc[dn][2] * den[1], oc[dn][3] * den[1], fmt);
         }
-        const float inv = 1.0f / den;
-        uint4* dst = reinterpret_cast<uint4*>(static_cast<unsigned short*>(o) + (pose * tokens + lane) * Hd + head * DH);
-#pragma unroll
-        for (int v = 0; v < VPR; ++v)
-            dst[v] = make_uint4(pack16(acc[v * 8] * inv, acc[v * 8 + 1] * inv, fmt), pack16(acc[v * 8 + 2] * inv, acc[v * 8 + 3] * inv, fmt),
-                                pack16(acc[v * 8 + 4] * inv, acc[v * 8 + 5] * inv, fmt), pack16(acc[v * 8 + 6] * inv, acc[v * 8 + 7] * inv, fmt));
+    }
+    __syncwarp();
+    unsigned short* dst = static_cast<unsigned short*>(o) + pose * tokens * static_cast<long>(Hd) + head * DH;
+    for (int i = lane; i < tokens * VPR; i += 32) {
+        const int vec = i % VPR, n = i / VPR;
+        *reinterpret_cast<uint4*>(dst + n * static_cast<long>(Hd) + vec * 8) = *reinterpret_cast<const uint4*>(sq + n * LDS + vec * 8);
     }
 }
 
 size_t att_smem_bytes(int tokens, int dh) {
-    return static_cast<size_t>(ATT_WARPS) * (3 * tokens * (dh + 8) * 2 + VIT_MAX_TOKENS * 32 * 4);
+    const int R = tokens > 16 ? 32 : 16;
+    return static_cast<size_t>(ATT_WARPS) * 3 * R * (dh + 8) * 2;
 }
 
 }  // namespace
@@ -248,7 +303,7 @@ int vit_validate(const VitDesc& d) {
     LIFTER_REQUIRE(d.heads >= 1 && d.hidden % d.heads == 0 && (d.hidden / d.heads == 32 || d.hidden / d.heads == 64),
                    "vit: %d heads over width %d unsupported (head width must be 32 or 64)", d.heads, d.hidden);
     LIFTER_REQUIRE(d.blocks >= 0 && d.blocks <= 64, "vit: %d blocks", d.blocks);
-    LIFTER_REQUIRE(d.mlp_dim >= 64 && d.mlp_dim % 64 == 0, "vit: MLP width %d must be a multiple of 64", d.mlp_dim);
+    LIFTER_REQUIRE(d.mlp_dim >= 192 && d.mlp_dim % 64 == 0, "vit: MLP width %d must be a multiple of 64, at least 192", d.mlp_dim);
     LIFTER_REQUIRE(d.head_dim >= 64 && d.head_dim % 64 == 0, "vit: head MLP width %d must be a multiple of 64", d.head_dim);
     LIFTER_REQUIRE(d.out_dim >= 1 && d.out_dim <= 64, "vit: %d outputs per token unsupported (1..64)", d.out_dim);
     LIFTER_REQUIRE(d.fmt == FMT_F16 || d.fmt == FMT_BF16, "vit: unknown operand format %d", d.fmt);
@@ -299,7 +354,7 @@ int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace
         }
     }
     const size_t smem = att_smem_bytes(d.tokens, dh);
-    if (smem > 48 * 1024) {
+    if (smem > 48 * 1024) {                         // static would do below 48 KB; cheap enough to set every call
         if (dh == 64) LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
         else          LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     }
