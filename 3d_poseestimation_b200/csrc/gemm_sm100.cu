@@ -139,19 +139,18 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 #define LIFTER_GEMM_REGS __maxnreg__(128)
 #endif
 // torch.nn.GELU() (exact erf form) for the epilogue: x * Phi(x) with Phi(-|x|) = erfc(|x| / sqrt 2) / 2 from Abramowitz &
-// Stegun 7.1.26 (|error| <= 1.5e-7 on erf): one rcp.approx, one ex2.approx and eight FMA-class operations, against ~25
+// Stegun 7.1.26 (|error| <= 1.5e-7 on erf): one rcp.approx, one ex2.approx and ten FMA-class operations, against ~25
 // for erff() -- with K = 256 the epilogue, not the MMA, bounds the MLP-up GEMM of the transformer lifter.
 __device__ __forceinline__ float gelu_erf(float x) {
-    const float z = fabsf(x) * 0.70710678118654752f;
+    const float ax = fabsf(x);
     float t, e;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
-    float p = fmaf(1.061405429f, t, -1.453152027f);
-    p = fmaf(p, t, 1.421413741f);
-    p = fmaf(p, t, -0.284496736f);
-    p = fmaf(p, t, 0.254829592f);
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -1.4426950408889634f));
-    const float hl = 0.5f * p * t * e;                                // Phi(-|x|)
-    return x >= 0.0f ? fmaf(-x, hl, x) : x * hl;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(ax, 0.3275911f * 0.70710678118654752f, 1.0f)));
+    float p = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);     // the 1/2 of Phi folded into the coefficients
+    p = fmaf(p, t, 0.5f * 1.421413741f);
+    p = fmaf(p, t, 0.5f * -0.284496736f);
+    p = fmaf(p, t, 0.5f * 0.254829592f);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * (-0.5f * 1.4426950408889634f)));
+    return fmaf(-ax, p * t * e, fmaxf(x, 0.0f));                     // relu(x) - |x| Phi(-|x|)
 }
 
 template <int BLOCK_N, bool TWO_SM, bool GELU>

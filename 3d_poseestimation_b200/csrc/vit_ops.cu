@@ -179,8 +179,9 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
     const long pose = ph / heads;
     const int head = static_cast<int>(ph - pose * heads);
     const int Hd = heads * DH;
-    const int R = tokens > 16 ? 32 : 16;               // staged rows per slice (MMA tiles are 16 rows / 16 keys)
-    const int MT = R / 16, NT = (tokens + 7) / 8;
+    const int R = tokens + 1;                          // staged rows per slice: the tokens and ONE zero row that every
+    const int MT = (tokens + 15) / 16, NT = (tokens + 7) / 8;   // MMA-tile row past the token count aliases (less shared
+                                                       // memory per warp = more resident warps for a latency-bound kernel)
     unsigned short* sq = reinterpret_cast<unsigned short*>(att_smem) + static_cast<size_t>(wid) * (3 * R * LDS);
     const unsigned short* src = static_cast<const unsigned short*>(qkv) + pose * tokens * (3L * Hd) + head * DH;
     for (int i = lane; i < 3 * R * VPR; i += 32) {
@@ -202,12 +203,12 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
 #pragma unroll
         for (int ks = 0; ks < DH / 16; ++ks) {
             uint32_t a[4];
-            ldsm_x4(a, q_addr + ((mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + ks * 16 + (lane >> 4) * 8) * 2);
+            ldsm_x4(a, q_addr + (min(mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, tokens) * LDS + ks * 16 + (lane >> 4) * 8) * 2);
 #pragma unroll
             for (int np = 0; np < 2; ++np) {           // key tiles 2 np, 2 np + 1 (keys np * 16 .. + 15)
                 if (np * 2 < NT) {
                     uint32_t bk[4];                    // [0], [1]: tile 2 np (k lo, k hi); [2], [3]: tile 2 np + 1
-                    ldsm_x4(bk, k_addr + ((np * 16 + (lane & 7) + (lane >> 4) * 8) * LDS + ks * 16 + ((lane >> 3) & 1) * 8) * 2);
+                    ldsm_x4(bk, k_addr + (min(np * 16 + (lane & 7) + (lane >> 4) * 8, tokens) * LDS + ks * 16 + ((lane >> 3) & 1) * 8) * 2);
                     mma16816(sc[np * 2], a, bk[0], bk[1], fmt);
                     if (np * 2 + 1 < NT) mma16816(sc[np * 2 + 1], a, bk[2], bk[3], fmt);
                 }
@@ -259,7 +260,7 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
 #pragma unroll
                 for (int dp = 0; dp < DH / 16; ++dp) {                 // value column tiles 2 dp, 2 dp + 1
                     uint32_t bv[4];
-                    ldsm_x4_trans(bv, v_addr + ((kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LDS + dp * 16 + (lane >> 4) * 8) * 2);
+                    ldsm_x4_trans(bv, v_addr + (min(kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, tokens) * LDS + dp * 16 + (lane >> 4) * 8) * 2);
                     mma16816(oc[dp * 2], pa, bv[0], bv[1], fmt);
                     mma16816(oc[dp * 2 + 1], pa, bv[2], bv[3], fmt);
                 }
@@ -269,8 +270,10 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
         __syncwarp();
 #pragma unroll
         for (int dn = 0; dn < DH / 8; ++dn) {
-            *reinterpret_cast<uint32_t*>(sq + (mt * 16 + g) * LDS + dn * 8 + t4 * 2) = pack16(oc[dn][0] * den[0], oc[dn][1] * den[0], fmt);
-            *reinterpret_cast<uint32_t*>(sq + (mt * 16 + g + 8) * LDS + dn * 8 + t4 * 2) = pack16(oc[dn][2] * den[1], oc[dn][3] * den[1], fmt);
+            if (mt * 16 + g < tokens)
+                *reinterpret_cast<uint32_t*>(sq + (mt * 16 + g) * LDS + dn * 8 + t4 * 2) = pack16(oc[dn][0] * den[0], oc[dn][1] * den[0], fmt);
+            if (mt * 16 + g + 8 < tokens)
+                *reinterpret_cast<uint32_t*>(sq + (mt * 16 + g + 8) * LDS + dn * 8 + t4 * 2) = pack16(oc[dn][2] * den[1], oc[dn][3] * den[1], fmt);
         }
     }
     __syncwarp();
@@ -282,8 +285,7 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
 }
 
 size_t att_smem_bytes(int tokens, int dh) {
-    const int R = tokens > 16 ? 32 : 16;
-    return static_cast<size_t>(ATT_WARPS) * 3 * R * (dh + 8) * 2;
+    return static_cast<size_t>(ATT_WARPS) * 3 * (tokens + 1) * (dh + 8) * 2;
 }
 
 }  // namespace

@@ -92,7 +92,7 @@ class MyViT(torch.nn.Module):
         self.mlp = torch.nn.Sequential(torch.nn.Linear(self.hidden_d, int(self.hidden_d / 2)), torch.nn.ReLU(),
                                        torch.nn.Linear(int(self.hidden_d / 2), out_d))
         self.infer_format = "fp16"        # GEMM operand / activation format of the eval path ("fp16" or "bf16")
-        self.chunk_poses = 2048           # poses per pass of the kernel sequence (activations of a pass stay near L2)
+        self.chunk_poses = 8192           # poses per pass of the kernel sequence (activations of a pass stay near L2)
         self._packed = None               # (key, tensors, descriptor)
         self._workspace = None
 

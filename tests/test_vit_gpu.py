@@ -62,7 +62,7 @@ def test_vit_eval_matches_oracle_after_denormalisation(pkg, golden_dir, B):
     frac_ok = float((err <= tol).float().mean())
     # 16-bit storage of every activation through two transformer blocks (~15 rounding points, ~1e-3 of the output
     # scale in total; these un-trained weights give outputs of several standard deviations): the north_star band holds
-    # for all but a tail of small-valued coordinates, and everything is inside 2 mm + 1e-2 relative.  DESIGN.md section 9.
+    # for all but a tail of small-valued coordinates, and everything is inside 2 mm + 1e-2 relative.  DESIGN.md section 8.
     assert frac_ok >= 0.995, f"{100 * (1 - frac_ok):.2f} % of the outputs outside 0.5 mm + 1e-2 relative"
     loose = 2e-3 + 1e-2 * ref.abs()
     assert bool((err <= loose).all()), f"max err {err.max().item() * 1e3:.3f} mm; worst err/tol {(err / loose).max().item():.2f}"
