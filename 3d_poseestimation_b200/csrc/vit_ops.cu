@@ -21,10 +21,30 @@ __device__ __forceinline__ float wsum(float v) {
     return v;
 }
 
-// A warp owns one token row of width Hd = NV * 256: lane l holds columns v * 256 + l * 8 + [0, 8), v < NV.
+// A warp owns token rows of width Hd = NV * 256: lane l holds columns v * 256 + l * 8 + [0, 8), v < NV.  Each warp walks
+// VIT_RPW consecutive rows with everything per-column (LayerNorm gains / biases, Linear weights) loaded ONCE into
+// registers: re-reading 8-16 parameter vectors per row made the first version of these kernels L1-bandwidth bound.
+constexpr int VIT_RPW = 8;
+
 template <int NV>
-__device__ __forceinline__ void warp_layernorm(float (&x)[NV][8], const float* __restrict__ g, const float* __restrict__ b,
-                                               float eps, int lane) {
+struct RowParams { float g[NV][8], b[NV][8]; };
+
+template <int NV>
+__device__ __forceinline__ void load_row_params(RowParams<NV>& p, const float* __restrict__ g, const float* __restrict__ b, int lane) {
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        const int c0 = v * 256 + lane * 8;
+        const float4 g0 = *reinterpret_cast<const float4*>(g + c0), g1 = *reinterpret_cast<const float4*>(g + c0 + 4);
+        const float4 b0 = *reinterpret_cast<const float4*>(b + c0), b1 = *reinterpret_cast<const float4*>(b + c0 + 4);
+        p.g[v][0] = g0.x; p.g[v][1] = g0.y; p.g[v][2] = g0.z; p.g[v][3] = g0.w;
+        p.g[v][4] = g1.x; p.g[v][5] = g1.y; p.g[v][6] = g1.z; p.g[v][7] = g1.w;
+        p.b[v][0] = b0.x; p.b[v][1] = b0.y; p.b[v][2] = b0.z; p.b[v][3] = b0.w;
+        p.b[v][4] = b1.x; p.b[v][5] = b1.y; p.b[v][6] = b1.z; p.b[v][7] = b1.w;
+    }
+}
+
+template <int NV>
+__device__ __forceinline__ void warp_layernorm(float (&x)[NV][8], const RowParams<NV>& p, float eps) {
     constexpr float inv = 1.0f / (NV * 256);
     float s = 0.0f;
 #pragma unroll
@@ -39,15 +59,9 @@ __device__ __forceinline__ void warp_layernorm(float (&x)[NV][8], const float* _
         for (int e = 0; e < 8; ++e) { const float d = x[v][e] - mean; q = fmaf(d, d, q); }
     const float rstd = rsqrtf(wsum(q) * inv + eps);                  // biased variance, torch.nn.LayerNorm
 #pragma unroll
-    for (int v = 0; v < NV; ++v) {
-        const int c0 = v * 256 + lane * 8;
-        const float4 g0 = *reinterpret_cast<const float4*>(g + c0), g1 = *reinterpret_cast<const float4*>(g + c0 + 4);
-        const float4 b0 = *reinterpret_cast<const float4*>(b + c0), b1 = *reinterpret_cast<const float4*>(b + c0 + 4);
-        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    for (int v = 0; v < NV; ++v)
 #pragma unroll
-        for (int e = 0; e < 8; ++e) x[v][e] = fmaf((x[v][e] - mean) * rstd, gg[e], bb[e]);
-    }
+        for (int e = 0; e < 8; ++e) x[v][e] = fmaf((x[v][e] - mean) * rstd, p.g[v][e], p.b[v][e]);
 }
 
 template <int NV>
@@ -73,40 +87,56 @@ __global__ void __launch_bounds__(256) vit_embed_kernel(const float* __restrict_
     griddep_launch();
     griddep_wait();
     const int lane = threadIdx.x & 31;
-    const long t = static_cast<long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (t >= T) return;
-    const int n = static_cast<int>(t % tokens);
-    float v[NV][8];
+    const long t0 = (static_cast<long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * VIT_RPW;
+    if (t0 >= T) return;
+    RowParams<NV> ln1, ln2;
+    if (g1 != nullptr) { load_row_params<NV>(ln1, g1, b1, lane); load_row_params<NV>(ln2, g2, b2, lane); }
+    float bs[NV][8], w0[NV][8], w1[NV][8];                            // IND == 2: bias and the two weight columns
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
         const int c0 = k * 256 + lane * 8;
         const float4 q0 = *reinterpret_cast<const float4*>(bias + c0), q1 = *reinterpret_cast<const float4*>(bias + c0 + 4);
-        const float4 p0 = *reinterpret_cast<const float4*>(pos + n * (NV * 256) + c0);
-        const float4 p1 = *reinterpret_cast<const float4*>(pos + n * (NV * 256) + c0 + 4);
-        const float a[8] = {q0.x + p0.x, q0.y + p0.y, q0.z + p0.z, q0.w + p0.w, q1.x + p1.x, q1.y + p1.y, q1.z + p1.z, q1.w + p1.w};
+        bs[k][0] = q0.x; bs[k][1] = q0.y; bs[k][2] = q0.z; bs[k][3] = q0.w; bs[k][4] = q1.x; bs[k][5] = q1.y; bs[k][6] = q1.z; bs[k][7] = q1.w;
         if constexpr (IND == 2) {
-            const float2 xi = *reinterpret_cast<const float2*>(x + t * 2);
             const float4* wv = reinterpret_cast<const float4*>(w + c0 * 2);
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                const float4 ww = wv[e];                                        // columns c0 + 2e, c0 + 2e + 1
-                v[k][2 * e] = fmaf(xi.y, ww.y, fmaf(xi.x, ww.x, a[2 * e]));
-                v[k][2 * e + 1] = fmaf(xi.y, ww.w, fmaf(xi.x, ww.z, a[2 * e + 1]));
-            }
-        } else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                float acc = a[e];
-                for (int i = 0; i < in_d; ++i) acc = fmaf(x[t * in_d + i], w[(c0 + e) * in_d + i], acc);
-                v[k][e] = acc;
+                const float4 ww = wv[e];                              // columns c0 + 2e, c0 + 2e + 1
+                w0[k][2 * e] = ww.x; w1[k][2 * e] = ww.y; w0[k][2 * e + 1] = ww.z; w1[k][2 * e + 1] = ww.w;
             }
         }
     }
-    store_row16<NV>(h, t, lane, v, fmt);
-    if (g1 == nullptr) return;
-    warp_layernorm<NV>(v, g1, b1, eps, lane);
-    warp_layernorm<NV>(v, g2, b2, eps, lane);
-    store_row16<NV>(u, t, lane, v, fmt);
+    const long t1 = min(T, t0 + VIT_RPW);
+    int n = static_cast<int>(t0 % tokens);
+    for (long t = t0; t < t1; ++t) {
+        float v[NV][8];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int c0 = k * 256 + lane * 8;
+            const float4 p0 = *reinterpret_cast<const float4*>(pos + n * (NV * 256) + c0);
+            const float4 p1 = *reinterpret_cast<const float4*>(pos + n * (NV * 256) + c0 + 4);
+            const float pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+            if constexpr (IND == 2) {
+                const float2 xi = *reinterpret_cast<const float2*>(x + t * 2);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[k][e] = fmaf(xi.y, w1[k][e], fmaf(xi.x, w0[k][e], bs[k][e] + pp[e]));
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    float acc = bs[k][e] + pp[e];
+                    for (int i = 0; i < in_d; ++i) acc = fmaf(x[t * in_d + i], w[(c0 + e) * in_d + i], acc);
+                    v[k][e] = acc;
+                }
+            }
+        }
+        store_row16<NV>(h, t, lane, v, fmt);
+        if (g1 != nullptr) {
+            warp_layernorm<NV>(v, ln1, eps);
+            warp_layernorm<NV>(v, ln2, eps);
+            store_row16<NV>(u, t, lane, v, fmt);
+        }
+        if (++n == tokens) n = 0;
+    }
 }
 
 // out = LN2(LN1(in)) (g2 == nullptr: one LayerNorm).  in / out 16-bit [T][Hd]; statistics and affine in fp32, no
@@ -119,24 +149,38 @@ __global__ void __launch_bounds__(256) vit_layernorm_kernel(const void* __restri
     griddep_launch();
     griddep_wait();
     const int lane = threadIdx.x & 31;
-    const long t = static_cast<long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (t >= T) return;
-    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const unsigned short*>(in) + t * (NV * 256));
-    float v[NV][8];
+    const long t0 = (static_cast<long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * VIT_RPW;
+    if (t0 >= T) return;
+    RowParams<NV> ln1, ln2;
+    load_row_params<NV>(ln1, g1, b1, lane);
+    if (g2 != nullptr) load_row_params<NV>(ln2, g2, b2, lane);
+    const long t1 = min(T, t0 + VIT_RPW);
+    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const unsigned short*>(in));
+    uint4 cur[NV], nxt[NV];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-        const uint4 r = src[k * 32 + lane];
-        const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
+    for (int k = 0; k < NV; ++k) cur[k] = src[t0 * (NV * 32) + k * 32 + lane];
+    for (long t = t0; t < t1; ++t) {
+        if (t + 1 < t1) {                                             // next row in flight while this one is normalised
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const float2 f = unpack16(wd[e], fmt);
-            v[k][2 * e] = f.x;
-            v[k][2 * e + 1] = f.y;
+            for (int k = 0; k < NV; ++k) nxt[k] = src[(t + 1) * (NV * 32) + k * 32 + lane];
         }
+        float v[NV][8];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const uint32_t wd[4] = {cur[k].x, cur[k].y, cur[k].z, cur[k].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack16(wd[e], fmt);
+                v[k][2 * e] = f.x;
+                v[k][2 * e + 1] = f.y;
+            }
+        }
+        warp_layernorm<NV>(v, ln1, eps);
+        if (g2 != nullptr) warp_layernorm<NV>(v, ln2, eps);
+        store_row16<NV>(out, t, lane, v, fmt);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) cur[k] = nxt[k];
     }
-    warp_layernorm<NV>(v, g1, b1, eps, lane);
-    if (g2 != nullptr) warp_layernorm<NV>(v, g2, b2, eps, lane);
-    store_row16<NV>(out, t, lane, v, fmt);
 }
 
 // baselineModel.py:243-253.  qkv 16-bit [T][3 * Hd] = [q | k | v], each (head, d) major; o 16-bit [T][Hd].
@@ -338,7 +382,7 @@ int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace
     unsigned short* qkv = o + T * H;
     unsigned short* m = qkv + T * 3L * H;
     unsigned short* r = m + T * static_cast<long>(d.mlp_dim);
-    const unsigned row_blocks = static_cast<unsigned>((T + 7) / 8);                   // 8 warps = 8 token rows per block
+    const unsigned row_blocks = static_cast<unsigned>((T + 8 * VIT_RPW - 1) / (8 * VIT_RPW));   // 8 warps x VIT_RPW token rows per block
 
     {   // embedding (+ the first block's LayerNorm pair)
         const float* ln0 = d.blocks > 0 ? d.ln : nullptr;
