@@ -87,6 +87,101 @@ __global__ void __launch_bounds__(DS_THREADS, 2) keypoint_stats_kernel(const flo
     }
 }
 
+// Same pass with the frames staged through shared memory by the bulk-copy engine: one elected thread keeps DS_STAGES
+// spans of DS_TR frames (contiguous, 224 * cols bytes each) in flight per block with cp.async.bulk + mbarrier, so the
+// bytes in flight no longer depend on registers or occupancy; the 256 threads consume a span from shared memory with the
+// same (row group, column) mapping.  Frames past the last full span are read with plain loads by the last block.
+constexpr int DS_TR = 56;
+constexpr int DS_STAGES = 4;
+
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+__global__ void __launch_bounds__(DS_THREADS, 4) keypoint_stats_tma_kernel(const float* __restrict__ data, long frames, int cols,
+                                                                           int D, int zc, long tiles_per_block,
+                                                                           double* __restrict__ partials) {
+    griddep_launch();
+    extern __shared__ __align__(128) unsigned char ds_smem[];
+    __shared__ double s_sum[2][DS_THREADS];
+    __shared__ float s_mm[2][DS_THREADS];
+    __shared__ __align__(8) unsigned long long s_bar[DS_STAGES];
+    const int tile_elems = DS_TR * cols;
+    const uint32_t tile_bytes = static_cast<uint32_t>(tile_elems) * 4u;
+    float* tiles = reinterpret_cast<float*>(ds_smem);
+    const int G = DS_THREADS / cols;
+    const int t = threadIdx.x, c = t % cols, g = t / cols, d = c % D;
+    const float w = (zc != 0 && c >= D) ? 1.0f : 0.0f;
+    const long full_tiles = frames / DS_TR;
+    const long tile0 = static_cast<long>(blockIdx.x) * tiles_per_block;
+    const long tile1 = min(full_tiles, tile0 + tiles_per_block);
+    const int n_tiles = tile1 > tile0 ? static_cast<int>(tile1 - tile0) : 0;
+    if (t == 0) {
+        for (int s = 0; s < DS_STAGES; ++s) mbar_init(smem_u32(&s_bar[s]), 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    griddep_wait();
+    if (t == 0) {
+        for (int s = 0; s < DS_STAGES && s < n_tiles; ++s) {
+            mbar_arrive_expect_tx(smem_u32(&s_bar[s]), tile_bytes);
+            bulk_g2s(smem_u32(tiles + s * tile_elems), data + (tile0 + s) * tile_elems, tile_bytes, smem_u32(&s_bar[s]));
+        }
+    }
+    double sum = 0.0, sq = 0.0;
+    float mn = CUDART_INF_F, mx = -CUDART_INF_F;
+    const float shift = g < G ? data[c] - w * data[d] : 0.0f;        // first frame: any constant near the mean works
+    for (int i = 0; i < n_tiles; ++i) {
+        const int slot = i % DS_STAGES;
+        mbar_wait(smem_u32(&s_bar[slot]), (i / DS_STAGES) & 1);
+        if (g < G) {
+            const float* tp = tiles + slot * tile_elems;
+            float fs = 0.0f, fq = 0.0f;
+#pragma unroll 4
+            for (int r = g; r < DS_TR; r += G) {                      // <= 56 terms in fp32, then one fp64 add per span
+                const float vf = tp[r * cols + c] - w * tp[r * cols + d];
+                mn = fminf(mn, vf);
+                mx = fmaxf(mx, vf);
+                const float x = vf - shift;
+                fs += x;
+                fq = fmaf(x, x, fq);
+            }
+            sum += static_cast<double>(fs);
+            sq += static_cast<double>(fq);
+        }
+        __syncthreads();                                              // every thread is done with this slot
+        if (t == 0 && i + DS_STAGES < n_tiles) {
+            mbar_arrive_expect_tx(smem_u32(&s_bar[slot]), tile_bytes);
+            bulk_g2s(smem_u32(tiles + slot * tile_elems), data + (tile0 + i + DS_STAGES) * tile_elems, tile_bytes, smem_u32(&s_bar[slot]));
+        }
+    }
+    if (blockIdx.x == gridDim.x - 1 && g < G) {                       // frames past the last full span
+        float fs = 0.0f, fq = 0.0f;
+        for (long r = full_tiles * DS_TR + g; r < frames; r += G) {
+            const float vf = data[r * cols + c] - w * data[r * cols + d];
+            mn = fminf(mn, vf);
+            mx = fmaxf(mx, vf);
+            const float x = vf - shift;
+            fs += x;
+            fq = fmaf(x, x, fq);
+        }
+        sum += static_cast<double>(fs);
+        sq += static_cast<double>(fq);
+    }
+    s_sum[0][t] = sum; s_sum[1][t] = sq; s_mm[0][t] = mn; s_mm[1][t] = mx;
+    __syncthreads();
+    if (t < cols) {
+        for (int k = 1; k < G; ++k) {                                 // fixed order
+            const int o = k * cols + t;
+            sum += s_sum[0][o]; sq += s_sum[1][o];
+            mn = fminf(mn, s_mm[0][o]); mx = fmaxf(mx, s_mm[1][o]);
+        }
+        double* p = partials + static_cast<long>(blockIdx.x) * 4 * cols;
+        p[t] = sum; p[cols + t] = sq; p[2 * cols + t] = static_cast<double>(mn); p[3 * cols + t] = static_cast<double>(mx);
+    }
+}
+
 // out [4][cols] fp64: mean, population std (main.py:280-289: divide by n_frames), min, max.  16 groups of 64 lanes
 // each fold every 16th partial row, then lane c of group 0 folds the 16 group results: a fixed order again.
 constexpr int FIN_GROUPS = 16;
@@ -163,9 +258,8 @@ __global__ void __launch_bounds__(DS_THREADS, 2) process_keypoints_kernel(const 
 
 int keypoint_stats_blocks(int64_t frames, int cols) {
     if (frames <= 0 || cols <= 0 || cols > DS_MAXC) return 0;
-    const long G = DS_THREADS / cols;
-    long blocks = (frames + G * 8 - 1) / (G * 8);                    // at least eight rows per thread
-    const long cap = static_cast<long>(num_sms()) * 4;              // 1,024 threads per SM, 16 loads in flight each
+    long blocks = frames / DS_TR;                                    // at least one staged span per block
+    const long cap = static_cast<long>(num_sms()) * 4;               // four resident blocks per SM
     if (blocks > cap) blocks = cap;
     return static_cast<int>(blocks < 1 ? 1 : blocks);
 }
@@ -177,11 +271,25 @@ int keypoint_stats(const float* data, int64_t frames, int J, int D, int zc, doub
     LIFTER_REQUIRE(J >= 1 && D >= 1 && cols <= DS_MAXC, "keypoint_stats: %d joints x %d dims unsupported (<= %d values per frame)", J, D, DS_MAXC);
     LIFTER_REQUIRE(data && scratch && out, "keypoint_stats: null pointer");
     const int blocks = keypoint_stats_blocks(frames, cols);
-    const long G = DS_THREADS / cols;
-    long rpb = (frames + blocks - 1) / blocks;
-    rpb = (rpb + G - 1) / G * G;
-    LIFTER_CHECK_CUDA(launch_pdl("keypoint_stats_kernel", keypoint_stats_kernel, dim3(blocks), dim3(DS_THREADS), 0, st, data,
-                                 static_cast<long>(frames), cols, D, zc, rpb, scratch));
+    if (reinterpret_cast<uintptr_t>(data) % 16 == 0) {               // bulk copies need a 16-byte aligned source
+        const size_t smem = static_cast<size_t>(DS_STAGES) * DS_TR * cols * sizeof(float);
+        static bool configured = false;
+        if (!configured) {
+            LIFTER_CHECK_CUDA(cudaFuncSetAttribute(keypoint_stats_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   DS_STAGES * DS_TR * DS_MAXC * static_cast<int>(sizeof(float))));
+            configured = true;
+        }
+        const long full_tiles = frames / DS_TR;
+        const long tpb = (full_tiles + blocks - 1) / blocks;
+        LIFTER_CHECK_CUDA(launch_pdl("keypoint_stats_tma_kernel", keypoint_stats_tma_kernel, dim3(blocks), dim3(DS_THREADS), smem, st,
+                                     data, static_cast<long>(frames), cols, D, zc, tpb, scratch));
+    } else {
+        const long G = DS_THREADS / cols;
+        long rpb = (frames + blocks - 1) / blocks;
+        rpb = (rpb + G - 1) / G * G;
+        LIFTER_CHECK_CUDA(launch_pdl("keypoint_stats_kernel", keypoint_stats_kernel, dim3(blocks), dim3(DS_THREADS), 0, st, data,
+                                     static_cast<long>(frames), cols, D, zc, rpb, scratch));
+    }
     LIFTER_CHECK_CUDA(launch_pdl("keypoint_stats_finalize_kernel", keypoint_stats_finalize_kernel, dim3(1), dim3(FIN_GROUPS * DS_MAXC), 0,
                                  st, data, static_cast<long>(frames), cols, D, zc, static_cast<const double*>(scratch), blocks, out));
     return LIFTER_OK;

@@ -320,7 +320,7 @@ def gpu_arm(args, rank, world, local_rank):
 def ncu_traffic(rows, width):
     """DRAM bytes of one launch of the dominant kernel from the committed `ncu --set full` capture (profiles/), which
     was taken on the training bench (M=8192, N=K=1024); null for any other shape."""
-    path = os.path.join(ROOT, "profiles", "r01_train_gemm_ncu_full_raw_v4.csv")
+    path = os.path.join(ROOT, "profiles", "r01_train_gemm_ncu_full_raw_v6.csv")
     if rows != TRAIN_BATCH or width != H or not os.path.exists(path):
         return {"traffic": None}
     import csv
@@ -333,7 +333,7 @@ def ncu_traffic(rows, width):
         i = head.index(name)
         total += float(vals[i]) * scale[units[i]]
     return {"traffic": total, "traffic_unit": "bytes/launch",
-            "traffic_source": "profiles/r01_train_gemm_ncu_full_raw_v4.csv (dram read + write; the 16 MB output was "
+            "traffic_source": "profiles/r01_train_gemm_ncu_full_raw_v6.csv (dram read + write; the 16 MB output was "
                               "still in L2 when the kernel ended)",
             "algorithmic_bytes": float(rows * width * 2 * 2 + width * width * 2)}
 

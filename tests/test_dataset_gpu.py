@@ -81,6 +81,24 @@ def test_keypoint_stats_is_deterministic_and_shift_invariant(P):
     np.testing.assert_allclose(a[1].cpu().numpy(), std, rtol=1e-5)
 
 
+def test_keypoint_stats_unaligned_input_takes_the_plain_load_kernel(P):
+    """The statistics pass stages frames with bulk copies, which need a 16-byte aligned source; a view that starts 4
+    bytes into an allocation goes through the plain-load kernel and must give the same numbers."""
+    rs = np.random.RandomState(9)
+    raw = rs.normal(0.3, 0.7, (5000, 17, 3)).astype(np.float32)
+    base = torch.empty(raw.size + 1, device="cuda")
+    x = base[1:].view(5000, 17, 3)
+    x.copy_(T(raw))
+    assert x.data_ptr() % 16 != 0 and x.is_contiguous()
+    a = P.keypoint_stats(x).cpu().numpy()
+    b = P.keypoint_stats(T(raw).cuda()).cpu().numpy()
+    mean, std, lo, hi = D.keypoint_stats(raw)
+    for st in (a, b):
+        np.testing.assert_allclose(st[0], mean, rtol=1e-7, atol=1e-6 * std.max())
+        np.testing.assert_allclose(st[1], std, rtol=1e-5)
+        assert np.array_equal(st[2], lo.astype(np.float32)) and np.array_equal(st[3], hi.astype(np.float32))
+
+
 def test_dataset_processing_errors(P):
     with pytest.raises(RuntimeError):
         P.keypoint_stats(torch.zeros(4, 17, 3))                                  # CPU tensor: no fallback
