@@ -254,6 +254,67 @@ __global__ void __launch_bounds__(DS_THREADS, 2) process_keypoints_kernel(const 
     }
 }
 
+// The apply pass with the same bulk-copy staging of the input frames (outputs go out as plain coalesced stores).
+__global__ void __launch_bounds__(DS_THREADS, 4) process_keypoints_tma_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                                              long frames, int J, int D, int zc,
+                                                                              const double* __restrict__ stats, int mode,
+                                                                              int root_mode, long tiles_per_block) {
+    griddep_launch();
+    extern __shared__ __align__(128) unsigned char ds_smem[];
+    __shared__ __align__(8) unsigned long long s_bar[DS_STAGES];
+    const int cols = J * D, skip = root_mode == ROOT_DROP ? D : 0, ocols = cols - skip;
+    const int tile_elems = DS_TR * cols;
+    const uint32_t tile_bytes = static_cast<uint32_t>(tile_elems) * 4u;
+    float* tiles = reinterpret_cast<float*>(ds_smem);
+    const int G = DS_THREADS / ocols;
+    const int t = threadIdx.x, oc = t % ocols, g = t / ocols, c = oc + skip, d = c % D;
+    const long full_tiles = frames / DS_TR;
+    const long tile0 = static_cast<long>(blockIdx.x) * tiles_per_block;
+    const long tile1 = min(full_tiles, tile0 + tiles_per_block);
+    const int n_tiles = tile1 > tile0 ? static_cast<int>(tile1 - tile0) : 0;
+    if (t == 0) {
+        for (int s = 0; s < DS_STAGES; ++s) mbar_init(smem_u32(&s_bar[s]), 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    griddep_wait();
+    if (t == 0) {
+        for (int s = 0; s < DS_STAGES && s < n_tiles; ++s) {
+            mbar_arrive_expect_tx(smem_u32(&s_bar[s]), tile_bytes);
+            bulk_g2s(smem_u32(tiles + s * tile_elems), in + (tile0 + s) * tile_elems, tile_bytes, smem_u32(&s_bar[s]));
+        }
+    }
+    const float w = (zc != 0 && c >= D) ? 1.0f : 0.0f;
+    float a_hi = 0.0f, a_lo = 0.0f, b = 1.0f;                                       // out = ((v - root) - a) * b
+    if (mode == COLS_NORMALISE) {                                                   // main.py:334,337
+        const double mean = stats[c];
+        a_hi = static_cast<float>(mean);
+        a_lo = static_cast<float>(mean - static_cast<double>(a_hi));
+        b = static_cast<float>(1.0 / stats[cols + c]);
+    } else if (mode == COLS_MINMAX_NORM) { a_hi = 0.5f; b = 2.0f; }                 // main.py:331: 2v - 1
+    if (root_mode == ROOT_ZERO && c < D) { a_hi = 0.0f; a_lo = 0.0f; b = 0.0f; }    // main.py:343-344
+    for (int i = 0; i < n_tiles; ++i) {
+        const int slot = i % DS_STAGES;
+        mbar_wait(smem_u32(&s_bar[slot]), (i / DS_STAGES) & 1);
+        if (g < G) {
+            const float* tp = tiles + slot * tile_elems;
+            float* po = out + (tile0 + i) * DS_TR * ocols + oc;
+#pragma unroll 4
+            for (int r = g; r < DS_TR; r += G)
+                po[static_cast<long>(r) * ocols] = (((tp[r * cols + c] - w * tp[r * cols + d]) - a_hi) - a_lo) * b;
+        }
+        __syncthreads();
+        if (t == 0 && i + DS_STAGES < n_tiles) {
+            mbar_arrive_expect_tx(smem_u32(&s_bar[slot]), tile_bytes);
+            bulk_g2s(smem_u32(tiles + slot * tile_elems), in + (tile0 + i + DS_STAGES) * tile_elems, tile_bytes, smem_u32(&s_bar[slot]));
+        }
+    }
+    if (blockIdx.x == gridDim.x - 1 && g < G) {                                     // frames past the last full span
+        for (long r = full_tiles * DS_TR + g; r < frames; r += G)
+            out[r * ocols + oc] = (((in[r * cols + c] - w * in[r * cols + d]) - a_hi) - a_lo) * b;
+    }
+}
+
 }  // namespace
 
 int keypoint_stats_blocks(int64_t frames, int cols) {
@@ -306,6 +367,21 @@ int process_keypoints(const float* in, float* out, int64_t frames, int J, int D,
     if (frames <= 0) return LIFTER_OK;
     LIFTER_REQUIRE(in && out && in != out, "process_keypoints: bad pointers");
     const int ocols = cols - (root_mode == ROOT_DROP ? D : 0);
+    if (reinterpret_cast<uintptr_t>(in) % 16 == 0) {                 // bulk copies need a 16-byte aligned source
+        const size_t smem = static_cast<size_t>(DS_STAGES) * DS_TR * cols * sizeof(float);
+        static bool configured = false;
+        if (!configured) {
+            LIFTER_CHECK_CUDA(cudaFuncSetAttribute(process_keypoints_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                   DS_STAGES * DS_TR * DS_MAXC * static_cast<int>(sizeof(float))));
+            configured = true;
+        }
+        const int blocks = keypoint_stats_blocks(frames, cols);
+        const long full_tiles = frames / DS_TR;
+        const long tpb = (full_tiles + blocks - 1) / blocks;
+        LIFTER_CHECK_CUDA(launch_pdl("process_keypoints_tma_kernel", process_keypoints_tma_kernel, dim3(blocks), dim3(DS_THREADS), smem, st,
+                                     in, out, static_cast<long>(frames), J, D, zc, stats, mode, root_mode, tpb));
+        return LIFTER_OK;
+    }
     const long G = DS_THREADS / ocols;
     long blocks = (frames + G * 8 - 1) / (G * 8);
     const long cap = static_cast<long>(num_sms()) * 8;

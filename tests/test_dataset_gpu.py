@@ -92,6 +92,10 @@ def test_keypoint_stats_unaligned_input_takes_the_plain_load_kernel(P):
     assert x.data_ptr() % 16 != 0 and x.is_contiguous()
     a = P.keypoint_stats(x).cpu().numpy()
     b = P.keypoint_stats(T(raw).cuda()).cpu().numpy()
+    pa, _ = P.process_data(x, is_train=True, standardize=True)
+    pb, _ = P.process_data(T(raw).cuda(), is_train=True, standardize=True)
+    np.testing.assert_allclose(pa.cpu().numpy(), pb.cpu().numpy(), rtol=0, atol=2e-6)
+    np.testing.assert_allclose(pb.cpu().numpy(), D.process_data(raw, standardize=True)[0], rtol=2e-5, atol=2e-5)
     mean, std, lo, hi = D.keypoint_stats(raw)
     for st in (a, b):
         np.testing.assert_allclose(st[0], mean, rtol=1e-7, atol=1e-6 * std.max())
