@@ -69,6 +69,29 @@ def test_vit_eval_matches_oracle_after_denormalisation(pkg, golden_dir, B):
     assert rel_l2(out - m3, ref - m3) < 3e-3
 
 
+@pytest.mark.parametrize("joints,in_d,hidden,heads,blocks,out_d", [
+    (16, 2, 256, 4, 1, 3),      # one 16-row MMA tile, no padding rows
+    (21, 3, 512, 8, 2, 3),      # 512 wide (two 256-column groups per lane), generic input width, 21 joints
+    (32, 4, 256, 8, 1, 2),      # 32 tokens = the largest pose, head width 32
+    (1, 2, 256, 4, 1, 5),       # a single token: softmax over one key
+    (17, 2, 768, 12, 1, 3),     # 768 wide, twelve heads
+    (17, 2, 256, 4, 0, 3),      # no transformer block at all: embedding + head
+])
+def test_vit_shapes_beyond_the_default(pkg, joints, in_d, hidden, heads, blocks, out_d):
+    """Every template instantiation / shape branch of the transformer kernels against the fp32 oracle."""
+    cfg = dict(n_joints=joints, in_d=in_d, n_blocks=blocks, hidden_d=hidden, n_heads=heads, out_d=out_d)
+    params = V.numpy_init(21, **cfg)
+    m = pkg.MyViT(chw=(1, joints, in_d), n_blocks=blocks, hidden_d=hidden, n_heads=heads, out_d=out_d)
+    m.load_state_dict(params)
+    m = m.cuda().eval()
+    x = torch.randn(37, joints, in_d, generator=torch.Generator().manual_seed(joints))
+    ref = V.vit_forward(params, x, n_blocks=blocks, n_heads=heads)
+    with torch.no_grad():
+        out = m(x.cuda()).cpu()
+    assert tuple(out.shape) == (37, joints, out_d)
+    assert rel_l2(out, ref) < 5e-3, rel_l2(out, ref)
+
+
 def test_vit_chunking_weight_updates_and_formats(pkg):
     params = V.numpy_init(4)
     m = _model(pkg, params)
