@@ -420,7 +420,7 @@ def evaluate(model, batches, loss="mse", flip=None, metric_std=None, n_samples=N
         raise ValueError("flip must be None, 'output' or 'input'")
     if model.output_size % 3 != 0:
         raise ValueError("the fused loss works on (J, 3) joint outputs: o_dim must be a multiple of 3")
-    dev = model._flat.device
+    dev = next(model.parameters()).device                   # LinearModel or MyViT (train_1.py:35 validates either)
     if dev.type != "cuda":
         raise RuntimeError("evaluate needs the model on a B200 (no CPU path)")
     lib = _cabi.lib()

@@ -91,6 +91,7 @@ class MyViT(torch.nn.Module):
         self.blocks = torch.nn.ModuleList([MyViTBlock(hidden_d, n_heads) for _ in range(n_blocks)])
         self.mlp = torch.nn.Sequential(torch.nn.Linear(self.hidden_d, int(self.hidden_d / 2)), torch.nn.ReLU(),
                                        torch.nn.Linear(int(self.hidden_d / 2), out_d))
+        self.input_size, self.output_size = chw[1] * chw[2], chw[1] * out_d    # flat sizes, as LinearModel names them
         self.infer_format = "fp16"        # GEMM operand / activation format of the eval path ("fp16" or "bf16")
         self.chunk_poses = 8192           # poses per pass of the kernel sequence (activations of a pass stay near L2)
         self._packed = None               # (key, tensors, descriptor)
@@ -156,6 +157,10 @@ class MyViT(torch.nn.Module):
     def infer(self, images, chunk_poses=None):
         """Eval-mode forward, ``chunk_poses`` poses per pass of the kernel sequence."""
         x = images.detach().to(torch.float32).contiguous()
+        if x.dim() == 2 and x.shape[1] == self.input_size:           # flat (B, joints * in_d) rows, as the validation loop feeds
+            x = x.view(x.shape[0], self.chw[1], self.input_d)
+        if x.dim() != 3 or x.shape[1] != self.chw[1] or x.shape[2] != self.input_d:
+            raise ValueError(f"MyViT expects (B, {self.chw[1]}, {self.input_d}) key points, got {tuple(images.shape)}")
         dev = x.device
         if self.linear_mapper.weight.device != dev:
             raise RuntimeError("MyViT: parameters and input live on different devices")

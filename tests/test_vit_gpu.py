@@ -115,3 +115,31 @@ def test_vit_training_forward_is_not_a_silent_fallback(pkg):
         m.train()(x)
     with pytest.raises(ValueError):
         m.eval()(torch.randn(4, 16, 2, device="cuda"))
+
+
+@pytest.mark.parametrize("flip", [None, "input"])
+def test_evaluate_drives_the_transformer_lifter(pkg, golden_dir, flip):
+    """The validation loop train_1.py:112-145 with MyViT as `model_lift` (train_1.py:35): eval forward, flip TTA, fused
+    loss + per-joint MPJPE with one host read, against the same loop on the CPU oracle."""
+    import importlib
+    from oracle import losses_oracle as L
+    trainer = importlib.import_module("3d_poseestimation_b200.trainer")
+    st = dict(np.load(os.path.join(golden_dir, "h36m_stats.npz")))
+    s3 = T(st["std_train_3d"].astype(np.float32)).reshape(-1)
+    params = V.numpy_init(8)
+    m = _model(pkg, params)
+    gen = torch.Generator().manual_seed(4)
+    sizes = [300, 300, 77]
+    batches = [(torch.rand(b, 17, 2, generator=gen), torch.randn(b, 17, 3, generator=gen)) for b in sizes]
+    res = trainer.evaluate(m, [(x.pin_memory(), y.pin_memory()) for x, y in batches], loss="mse", flip=flip, metric_std=s3,
+                           n_samples=sum(sizes))
+    loss, metric = 0.0, torch.zeros(17)
+    for x, y in batches:
+        p = V.vit_forward(params, x)
+        if flip == "input":
+            p = (L.flip_pose(V.vit_forward(params, L.flip_pose(x))) + p) / 2
+        loss += float(torch.nn.functional.mse_loss(p, y)) / len(batches)
+        metric += L.mpjpe_per_joint_sum(p * s3.view(17, 3), y * s3.view(17, 3)) / sum(sizes)
+    np.testing.assert_allclose(res["loss"], loss, rtol=3e-3)
+    np.testing.assert_allclose(res["per_joint"].numpy(), metric.numpy(), rtol=3e-3)
+    np.testing.assert_allclose(res["mpjpe_mm"], float(metric[1:].mean() * (17 / 16) * 1000), rtol=3e-3)
