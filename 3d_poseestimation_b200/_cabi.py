@@ -74,6 +74,12 @@ class VitDesc(C.Structure):
                                           "w_out", "w_mlp1", "w_mlp2", "w_head1", "w_head2")]
 
 
+class VitGrads(C.Structure):
+    """``lifter_vit_grads_t``"""
+    _fields_ = [(k, C.c_void_p) for k in ("map", "ln", "w_qkv", "w_out", "w_mlp1", "mlp_b1", "w_mlp2", "mlp_b2", "w_head1",
+                                          "head_b1", "w_head2", "head_b2")]
+
+
 LOSS_MSE, LOSS_L1, LOSS_MPJPE = 0, 1, 2
 DP_MAX_WORLD = 8
 DP_FLAG_BYTES = 256
@@ -128,6 +134,10 @@ SIGNATURES = {
     "lifter_dp_adam_step": (_I32, [_CFG, C.POINTER(DpInfo), _P, _P, _F, _F, _F, _F, _I32, _F, _P, _I32, _P]),
     "lifter_vit_workspace_bytes": (_I64, [C.POINTER(VitDesc), _I64]),
     "lifter_vit_forward": (_I32, [C.POINTER(VitDesc), _P, _I64, _P, _P, _P]),
+    "lifter_vit_saved_bytes": (_I64, [C.POINTER(VitDesc), _I64]),
+    "lifter_vit_bwd_scratch_bytes": (_I64, [C.POINTER(VitDesc), _I64]),
+    "lifter_vit_train_forward": (_I32, [C.POINTER(VitDesc), _P, _I64, _P, _P, _P]),
+    "lifter_vit_backward": (_I32, [C.POINTER(VitDesc), _P, _I64, _P, _P, _P, C.POINTER(VitGrads), _P]),
     "lifter_gemm": (_I32, [C.POINTER(GemmDesc), _P]),
     "lifter_trace_begin": (_I32, [_P]),
     "lifter_trace_end": (_I32, [C.c_char_p, _I32]),

@@ -8,70 +8,11 @@
 #include "vit_ops.cuh"
 
 #include "gemm_sm100.cuh"
+#include "vit_common.cuh"
 
 namespace lifter {
 
 namespace {
-
-constexpr int VIT_MAX_TOKENS = 32;
-
-__device__ __forceinline__ float wsum(float v) {
-#pragma unroll
-    for (int s = 16; s >= 1; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
-    return v;
-}
-
-// A warp owns token rows of width Hd = NV * 256: lane l holds columns v * 256 + l * 8 + [0, 8), v < NV.  Each warp walks
-// VIT_RPW consecutive rows with everything per-column (LayerNorm gains / biases, Linear weights) loaded ONCE into
-// registers: re-reading 8-16 parameter vectors per row made the first version of these kernels L1-bandwidth bound.
-constexpr int VIT_RPW = 8;
-
-template <int NV>
-struct RowParams { float g[NV][8], b[NV][8]; };
-
-template <int NV>
-__device__ __forceinline__ void load_row_params(RowParams<NV>& p, const float* __restrict__ g, const float* __restrict__ b, int lane) {
-#pragma unroll
-    for (int v = 0; v < NV; ++v) {
-        const int c0 = v * 256 + lane * 8;
-        const float4 g0 = *reinterpret_cast<const float4*>(g + c0), g1 = *reinterpret_cast<const float4*>(g + c0 + 4);
-        const float4 b0 = *reinterpret_cast<const float4*>(b + c0), b1 = *reinterpret_cast<const float4*>(b + c0 + 4);
-        p.g[v][0] = g0.x; p.g[v][1] = g0.y; p.g[v][2] = g0.z; p.g[v][3] = g0.w;
-        p.g[v][4] = g1.x; p.g[v][5] = g1.y; p.g[v][6] = g1.z; p.g[v][7] = g1.w;
-        p.b[v][0] = b0.x; p.b[v][1] = b0.y; p.b[v][2] = b0.z; p.b[v][3] = b0.w;
-        p.b[v][4] = b1.x; p.b[v][5] = b1.y; p.b[v][6] = b1.z; p.b[v][7] = b1.w;
-    }
-}
-
-template <int NV>
-__device__ __forceinline__ void warp_layernorm(float (&x)[NV][8], const RowParams<NV>& p, float eps) {
-    constexpr float inv = 1.0f / (NV * 256);
-    float s = 0.0f;
-#pragma unroll
-    for (int v = 0; v < NV; ++v)
-#pragma unroll
-        for (int e = 0; e < 8; ++e) s += x[v][e];
-    const float mean = wsum(s) * inv;
-    float q = 0.0f;
-#pragma unroll
-    for (int v = 0; v < NV; ++v)
-#pragma unroll
-        for (int e = 0; e < 8; ++e) { const float d = x[v][e] - mean; q = fmaf(d, d, q); }
-    const float rstd = rsqrtf(wsum(q) * inv + eps);                  // biased variance, torch.nn.LayerNorm
-#pragma unroll
-    for (int v = 0; v < NV; ++v)
-#pragma unroll
-        for (int e = 0; e < 8; ++e) x[v][e] = fmaf((x[v][e] - mean) * rstd, p.g[v][e], p.b[v][e]);
-}
-
-template <int NV>
-__device__ __forceinline__ void store_row16(void* out, long row, int lane, const float (&x)[NV][8], int fmt) {
-    uint4* dst = reinterpret_cast<uint4*>(static_cast<unsigned short*>(out) + row * (NV * 256));
-#pragma unroll
-    for (int v = 0; v < NV; ++v)
-        dst[v * 32 + lane] = make_uint4(pack16(x[v][0], x[v][1], fmt), pack16(x[v][2], x[v][3], fmt),
-                                        pack16(x[v][4], x[v][5], fmt), pack16(x[v][6], x[v][7], fmt));
-}
 
 // baselineModel.py:349-354: tokens = linear_mapper(x) + pos_embed -> h (16-bit residual stream), and in the same pass the
 // first block's two LayerNorms (norm1, mhsa.norm; :303, :244) taken from the fp32 values -> u (g1 == nullptr: h only).
@@ -334,14 +275,6 @@ size_t att_smem_bytes(int tokens, int dh) {
 
 }  // namespace
 
-#define VIT_DISPATCH_NV(nv, CALL)                     \
-    switch (nv) {                                     \
-        case 1: { constexpr int NV = 1; CALL; break; } \
-        case 2: { constexpr int NV = 2; CALL; break; } \
-        case 3: { constexpr int NV = 3; CALL; break; } \
-        default: { constexpr int NV = 4; CALL; break; } \
-    }
-
 int vit_validate(const VitDesc& d) {
     LIFTER_REQUIRE(d.tokens >= 1 && d.tokens <= VIT_MAX_TOKENS, "vit: %d tokens per pose unsupported (1..%d)", d.tokens, VIT_MAX_TOKENS);
     LIFTER_REQUIRE(d.in_dim >= 1 && d.in_dim <= 4, "vit: %d input values per token unsupported (1..4)", d.in_dim);
@@ -353,6 +286,45 @@ int vit_validate(const VitDesc& d) {
     LIFTER_REQUIRE(d.head_dim >= 64 && d.head_dim % 64 == 0, "vit: head MLP width %d must be a multiple of 64", d.head_dim);
     LIFTER_REQUIRE(d.out_dim >= 1 && d.out_dim <= 64, "vit: %d outputs per token unsupported (1..64)", d.out_dim);
     LIFTER_REQUIRE(d.fmt == FMT_F16 || d.fmt == FMT_BF16, "vit: unknown operand format %d", d.fmt);
+    return LIFTER_OK;
+}
+
+// ---- launch wrappers shared with the training path (vit_train.cu) ---------------------------------------------------------
+int vit_embed(const VitDesc& d, const float* x, long T, void* h, const float* ln0, void* u, cudaStream_t st) {
+    const int H = d.hidden, nv = H / 256;
+    const unsigned row_blocks = static_cast<unsigned>((T + 8 * VIT_RPW - 1) / (8 * VIT_RPW));   // 8 warps x VIT_RPW token rows per block
+    const float* l1 = ln0 ? ln0 + H : nullptr;
+    const float* l2 = ln0 ? ln0 + 2 * H : nullptr;
+    const float* l3 = ln0 ? ln0 + 3 * H : nullptr;
+    if (d.in_dim == 2) {
+        VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_kernel", vit_embed_kernel<NV, 2>, dim3(row_blocks), dim3(256), 0, st, x, T,
+                                                         d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, h, ln0, l1, l2, l3, d.ln_eps, u, d.fmt)));
+    } else {
+        VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_kernel", vit_embed_kernel<NV, 0>, dim3(row_blocks), dim3(256), 0, st, x, T,
+                                                         d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, h, ln0, l1, l2, l3, d.ln_eps, u, d.fmt)));
+    }
+    return LIFTER_OK;
+}
+
+int vit_layernorm(const void* in, long T, const float* g1, const float* b1, const float* g2, const float* b2, float eps, void* out,
+                  int H, int fmt, cudaStream_t st) {
+    const unsigned row_blocks = static_cast<unsigned>((T + 8 * VIT_RPW - 1) / (8 * VIT_RPW));
+    VIT_DISPATCH_NV(H / 256, LIFTER_CHECK_CUDA(launch_pdl("vit_layernorm_kernel", vit_layernorm_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
+                                                          in, T, g1, b1, g2, b2, eps, out, fmt)));
+    return LIFTER_OK;
+}
+
+int vit_attention(const void* qkv, long pose_heads, int tokens, int heads, int dh, void* o, int fmt, cudaStream_t st) {
+    const size_t smem = att_smem_bytes(tokens, dh);
+    const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(dh));
+    const dim3 grid(static_cast<unsigned>((pose_heads + ATT_WARPS - 1) / ATT_WARPS));
+    if (dh == 64) {
+        if (smem > 48 * 1024) LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<64>, grid, dim3(ATT_WARPS * 32), smem, st, qkv, pose_heads, tokens, heads, scale_log2e, o, fmt));
+    } else {
+        if (smem > 48 * 1024) LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+        LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<32>, grid, dim3(ATT_WARPS * 32), smem, st, qkv, pose_heads, tokens, heads, scale_log2e, o, fmt));
+    }
     return LIFTER_OK;
 }
 
@@ -461,7 +433,7 @@ int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace
 // ---- C ABI (include/lifter_b200.h) ---------------------------------------------------------------------------------
 #include "../../include/lifter_b200.h"
 
-static lifter::VitDesc to_desc(const lifter_vit_t* v) {
+lifter::VitDesc lifter_vit_to_desc(const lifter_vit_t* v) {
     lifter::VitDesc d;
     d.tokens = v->tokens; d.in_dim = v->in_dim; d.hidden = v->hidden; d.heads = v->heads; d.blocks = v->blocks;
     d.mlp_dim = v->mlp_dim; d.head_dim = v->head_dim; d.out_dim = v->out_dim; d.fmt = v->fmt; d.ln_eps = v->ln_eps;
@@ -475,12 +447,12 @@ extern "C" {
 
 int64_t lifter_vit_workspace_bytes(const lifter_vit_t* vit, int64_t poses) {
     if (vit == nullptr) return LIFTER_ERR_INVALID;
-    return lifter::vit_workspace_bytes(to_desc(vit), poses);
+    return lifter::vit_workspace_bytes(lifter_vit_to_desc(vit), poses);
 }
 
 int lifter_vit_forward(const lifter_vit_t* vit, const float* x, int64_t poses, void* workspace, float* out, void* stream) {
     LIFTER_REQUIRE(vit != nullptr, "vit_forward: null descriptor");
-    return lifter::vit_forward(to_desc(vit), x, poses, workspace, out, static_cast<cudaStream_t>(stream));
+    return lifter::vit_forward(lifter_vit_to_desc(vit), x, poses, workspace, out, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -31,4 +31,28 @@ int64_t vit_workspace_bytes(const VitDesc& d, int64_t poses);
 // x [poses][tokens][in_dim] fp32 -> out [poses][tokens][out_dim] fp32.  Activations live in `workspace`.
 int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace, float* out, cudaStream_t st);
 
+// launch wrappers (vit_ops.cu) re-used by the training path
+int vit_embed(const VitDesc& d, const float* x, long T, void* h, const float* ln0, void* u, cudaStream_t st);
+int vit_layernorm(const void* in, long T, const float* g1, const float* b1, const float* g2, const float* b2, float eps, void* out,
+                  int H, int fmt, cudaStream_t st);
+int vit_attention(const void* qkv, long pose_heads, int tokens, int heads, int dh, void* o, int fmt, cudaStream_t st);
+
+// ---- training path (vit_train.cu) ----
+struct VitGrads {                        // fp32 gradients, stacked per block like the parameters of VitDesc
+    float* map = nullptr;                // [1 + in_dim][hidden]: d bias, then d weight column by input
+    float* ln = nullptr;                 // [blocks][6][hidden]
+    float* w_qkv = nullptr; float* w_out = nullptr; float* w_mlp1 = nullptr; float* mlp_b1 = nullptr;
+    float* w_mlp2 = nullptr; float* mlp_b2 = nullptr;
+    float* w_head1 = nullptr; float* head_b1 = nullptr;
+    float* w_head2 = nullptr;            // [out_dim][head_dim]
+    float* head_b2 = nullptr;            // [out_dim]
+};
+int64_t vit_saved_bytes(const VitDesc& d, int64_t poses);
+int64_t vit_bwd_scratch_bytes(const VitDesc& d, int64_t poses);
+// forward that keeps every GEMM input in `saved`; out [poses][tokens][out_dim] fp32
+int vit_train_forward(const VitDesc& d, const float* x, int64_t poses, void* saved, float* out, cudaStream_t st);
+// dout [poses][tokens][out_dim] fp32 -> gradients of every parameter
+int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* saved, const float* dout, void* scratch,
+                 const VitGrads& G, cudaStream_t st);
+
 }  // namespace lifter

@@ -1,0 +1,720 @@
+// MyViT lifter, training path (phase1_lifting/baselineModel.py:228-362 under loss.backward(),
+// the loop body train_1.py:73-100 with model_lift = MyViT).  The transformer has no dropout and no BatchNorm, so the
+// train-mode forward is the eval arithmetic with every GEMM input kept for backward; backward re-uses the tcgen05 GEMM
+// for all data gradients (dX = dZ W: MN-major B) and weight gradients (dW = dZ^T X: both operands MN-major, split-K
+// slabs) and adds the kernels between them:
+//   vit_gelu_fwd / vit_gelu_bwd     m = GELU(z1);  dz1 = dm * GELU'(z1)   (z1 is saved: GELU is not invertible)
+//   vit_relu_bwd                    head: dz = dr * (r > 0)
+//   vit_ln_bwd                      one or two LayerNorms back to back, + the residual gradient, + d gain / d bias partials
+//   vit_attention_bwd               dq, dk, dv of softmax(q k^T / sqrt d) v per (pose, head), probabilities recomputed
+//   vit_colsum16 / vit_embed_bwd    bias gradients; d linear_mapper
+// Every column reduction is two-stage and fixed-order (per-block partial rows, then reduce_rows_f32): deterministic.
+#include "vit_ops.cuh"
+
+#include "gemm_sm100.cuh"
+#include "train_kernels.cuh"
+#include "vit_common.cuh"
+
+namespace lifter {
+
+// split-K factor of a weight-gradient GEMM: enough slabs to give every SM a tile (as lifter_train.cu does)
+static int wgrad_splits(int M, int N, int K) {
+    const int bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
+    const int tiles = ceil_div(M, 128) * ceil_div(N, bn);
+    int s = num_sms() / tiles;
+    if (s < 1) s = 1;
+    if (s > 16) s = 16;
+    return gemm_effective_splits(K, s);
+}
+
+namespace {
+
+// Phi(x), phi(x) of the standard normal with the erf polynomial of the forward epilogue (gemm_sm100.cu gelu_erf)
+__device__ __forceinline__ void normal_cdf_pdf(float x, float& cdf, float& pdf) {
+    const float ax = fabsf(x);
+    float t, e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(ax, 0.3275911f * 0.70710678118654752f, 1.0f)));
+    float p = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);
+    p = fmaf(p, t, 0.5f * 1.421413741f);
+    p = fmaf(p, t, 0.5f * -0.284496736f);
+    p = fmaf(p, t, 0.5f * 0.254829592f);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * (-0.5f * 1.4426950408889634f)));
+    const float tail = p * t * e;                                   // Phi(-|x|)
+    cdf = x >= 0.0f ? 1.0f - tail : tail;
+    pdf = e * 0.3989422804014327f;
+}
+
+// mode 0: out = GELU(a)   mode 1: out = b * GELU'(a)   mode 2: out = b * (a > 0).   16-bit, 8 elements per thread.
+__global__ void __launch_bounds__(256) vit_pointwise_kernel(const uint4* __restrict__ a, const uint4* b, uint4* out, long n8,
+                                                            int mode, int fmt) {       // out may be b (in place)
+    griddep_launch();
+    griddep_wait();
+    const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+    for (long i = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+        const uint4 ra = a[i];
+        const uint4 rb = mode == 0 ? ra : b[i];
+        const uint32_t wa[4] = {ra.x, ra.y, ra.z, ra.w}, wb[4] = {rb.x, rb.y, rb.z, rb.w};
+        uint32_t wo[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float2 x = unpack16(wa[e], fmt), g = unpack16(wb[e], fmt);
+            float2 y;
+            if (mode == 2) {
+                y.x = x.x > 0.0f ? g.x : 0.0f;
+                y.y = x.y > 0.0f ? g.y : 0.0f;
+            } else {
+                float c0, p0, c1, p1;
+                normal_cdf_pdf(x.x, c0, p0);
+                normal_cdf_pdf(x.y, c1, p1);
+                if (mode == 0) { y.x = x.x * c0; y.y = x.y * c1; }
+                else { y.x = g.x * fmaf(x.x, p0, c0); y.y = g.y * fmaf(x.y, p1, c1); }
+            }
+            wo[e] = pack16(y.x, y.y, fmt);
+        }
+        out[i] = make_uint4(wo[0], wo[1], wo[2], wo[3]);
+    }
+}
+
+// partial column sums of a 16-bit matrix [T][W] (W % 8 == 0, W <= 2048): block b sums rows b * rpb .. into part[b][W]
+constexpr int CS_THREADS = 256;
+__global__ void __launch_bounds__(CS_THREADS) vit_colsum16_kernel(const unsigned short* __restrict__ m, long T, int W, long rpb,
+                                                                  float* __restrict__ part, int fmt) {
+    griddep_launch();
+    griddep_wait();
+    __shared__ float sh[CS_THREADS][8];
+    const int vpr = W / 8, G = CS_THREADS / vpr > 0 ? CS_THREADS / vpr : 1;      // row groups per block
+    const int t = threadIdx.x, vec = t % vpr, g = t / vpr;
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long r0 = static_cast<long>(blockIdx.x) * rpb, r1 = min(T, r0 + rpb);
+    if (g < G && t < G * vpr) {
+        for (long r = r0 + g; r < r1; r += G) {
+            const uint4 v = *reinterpret_cast<const uint4*>(m + r * W + vec * 8);
+            const uint32_t wd[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack16(wd[e], fmt);
+                acc[2 * e] += f.x;
+                acc[2 * e + 1] += f.y;
+            }
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sh[t][e] = acc[e];
+    __syncthreads();
+    if (t < vpr) {
+        for (int k = 1; k < G; ++k)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] += sh[k * vpr + t][e];
+        float* p = part + static_cast<long>(blockIdx.x) * W + t * 8;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) p[e] = acc[e];
+    }
+}
+
+}  // namespace
+}  // namespace lifter
+
+namespace lifter {
+namespace {
+
+// Sum one per-lane column accumulator over the 8 warps of a block (fixed order) and store the block's partial row.
+template <int NV>
+__device__ __forceinline__ void block_colsum_store(const float (&acc)[NV][8], float* sh /* [8][NV * 256] */, float* dst) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    __syncthreads();                                                  // previous round's readers are done with sh
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) sh[wid * (NV * 256) + v * 256 + lane * 8 + e] = acc[v][e];
+    __syncthreads();
+    for (int c = threadIdx.x; c < NV * 256; c += blockDim.x) {
+        float s = 0.0f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += sh[w * (NV * 256) + c];
+        dst[c] = s;
+    }
+}
+
+template <int NV>
+__device__ __forceinline__ void ln_stats(const float (&x)[NV][8], float& mean, float& rstd, float eps) {
+    constexpr float inv = 1.0f / (NV * 256);
+    float s = 0.0f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s += x[v][e];
+    mean = wsum(s) * inv;
+    float q = 0.0f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { const float d = x[v][e] - mean; q = fmaf(d, d, q); }
+    rstd = rsqrtf(wsum(q) * inv + eps);
+}
+
+// dy (in/out: becomes dx), xh = normalised input, g = gain.  dx = rstd (a - mean(a) - xh mean(a xh)), a = dy g;
+// dg += dy xh, db += dy.
+template <int NV>
+__device__ __forceinline__ void ln_bwd_row(float (&dy)[NV][8], const float (&xh)[NV][8], const float (&g)[NV][8], float rstd,
+                                           float (&dg)[NV][8], float (&db)[NV][8]) {
+    constexpr float inv = 1.0f / (NV * 256);
+    float s1 = 0.0f, s2 = 0.0f;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            dg[v][e] = fmaf(dy[v][e], xh[v][e], dg[v][e]);
+            db[v][e] += dy[v][e];
+            dy[v][e] *= g[v][e];
+            s1 += dy[v][e];
+            s2 = fmaf(dy[v][e], xh[v][e], s2);
+        }
+    const float c1 = wsum(s1) * inv, c2 = wsum(s2) * inv;
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dy[v][e] = rstd * (dy[v][e] - c1 - xh[v][e] * c2);
+}
+
+// dx_out = dres + d/dx [ LN2(LN1(x)) ] . dy   (g2 == nullptr: one LayerNorm; dres nullable).
+// part [gridDim.x][4][Hd]: block partials of d gain1, d bias1, d gain2, d bias2.
+template <int NV>
+__global__ void __launch_bounds__(256) vit_ln_bwd_kernel(const void* __restrict__ x, const void* __restrict__ dy_in,
+                                                         const void* __restrict__ dres, long T, const float* __restrict__ g1,
+                                                         const float* __restrict__ b1, const float* __restrict__ g2,
+                                                         const float* __restrict__ b2, float eps, void* __restrict__ dx_out,
+                                                         float* __restrict__ part, int fmt) {
+    griddep_launch();
+    griddep_wait();
+    __shared__ float sh[8 * NV * 256];
+    constexpr int Hd = NV * 256;
+    const int lane = threadIdx.x & 31;
+    const long t0 = (static_cast<long>(blockIdx.x) * 8 + (threadIdx.x >> 5)) * VIT_RPW;
+    const long t1 = min(T, t0 + VIT_RPW);
+    RowParams<NV> p1, p2;
+    load_row_params<NV>(p1, g1, b1, lane);
+    if (g2 != nullptr) load_row_params<NV>(p2, g2, b2, lane);
+    float dg1[NV][8], db1[NV][8], dg2[NV][8], db2[NV][8];
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dg1[v][e] = db1[v][e] = dg2[v][e] = db2[v][e] = 0.0f;
+    for (long t = t0; t < t1; ++t) {
+        float xh1[NV][8], d[NV][8];
+        load_row16<NV>(x, t, lane, xh1, fmt);
+        load_row16<NV>(dy_in, t, lane, d, fmt);
+        float mean, rstd1;
+        ln_stats<NV>(xh1, mean, rstd1, eps);
+#pragma unroll
+        for (int v = 0; v < NV; ++v)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) xh1[v][e] = (xh1[v][e] - mean) * rstd1;
+        if (g2 != nullptr) {
+            float xh2[NV][8];
+#pragma unroll
+            for (int v = 0; v < NV; ++v)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) xh2[v][e] = fmaf(xh1[v][e], p1.g[v][e], p1.b[v][e]);
+            float mean2, rstd2;
+            ln_stats<NV>(xh2, mean2, rstd2, eps);
+#pragma unroll
+            for (int v = 0; v < NV; ++v)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) xh2[v][e] = (xh2[v][e] - mean2) * rstd2;
+            ln_bwd_row<NV>(d, xh2, p2.g, rstd2, dg2, db2);
+        }
+        ln_bwd_row<NV>(d, xh1, p1.g, rstd1, dg1, db1);
+        if (dres != nullptr) {
+            float r[NV][8];
+            load_row16<NV>(dres, t, lane, r, fmt);
+#pragma unroll
+            for (int v = 0; v < NV; ++v)
+#pragma unroll
+                for (int e = 0; e < 8; ++e) d[v][e] += r[v][e];
+        }
+        store_row16<NV>(dx_out, t, lane, d, fmt);
+    }
+    float* dst = part + static_cast<long>(blockIdx.x) * 4 * Hd;
+    block_colsum_store<NV>(dg1, sh, dst);
+    block_colsum_store<NV>(db1, sh, dst + Hd);
+    block_colsum_store<NV>(dg2, sh, dst + 2 * Hd);
+    block_colsum_store<NV>(db2, sh, dst + 3 * Hd);
+}
+
+// d linear_mapper: part [gridDim.x][1 + in_d][Hd]: block partials of sum_t dh[t][c] (bias) and sum_t dh[t][c] x[t][i]
+template <int NV>
+__global__ void __launch_bounds__(256) vit_embed_bwd_kernel(const void* __restrict__ dh, const float* __restrict__ x, long T,
+                                                            int in_d, float* __restrict__ part, int fmt) {
+    griddep_launch();
+    griddep_wait();
+    __shared__ float sh[8 * NV * 256];
+    constexpr int Hd = NV * 256;
+    const int lane = threadIdx.x & 31;
+    const long t0 = (static_cast<long>(blockIdx.x) * 8 + (threadIdx.x >> 5)) * VIT_RPW;
+    const long t1 = min(T, t0 + VIT_RPW);
+    float acc[5][NV][8];
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+#pragma unroll
+        for (int v = 0; v < NV; ++v)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[k][v][e] = 0.0f;
+    for (long t = t0; t < t1; ++t) {
+        float d[NV][8];
+        load_row16<NV>(dh, t, lane, d, fmt);
+        float xi[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) xi[i] = i < in_d ? x[t * in_d + i] : 0.0f;
+#pragma unroll
+        for (int v = 0; v < NV; ++v)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                acc[0][v][e] += d[v][e];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[1 + i][v][e] = fmaf(d[v][e], xi[i], acc[1 + i][v][e]);
+            }
+    }
+    float* dst = part + static_cast<long>(blockIdx.x) * (1 + in_d) * Hd;
+#pragma unroll
+    for (int k = 0; k < 5; ++k)
+        if (k <= in_d) block_colsum_store<NV>(acc[k], sh, dst + k * Hd);
+}
+
+}  // namespace
+}  // namespace lifter
+
+namespace lifter {
+namespace {
+
+// Backward of softmax(q k^T / sqrt d) v for one (pose, head) per warp (fp32 FMAs; first version: correctness over speed).
+// qkv, dqkv 16-bit [T][3 Hd]; dO 16-bit [T][Hd].  Lane i owns query row i for P, dP, dS, dq; lane j owns key row j for
+// dk, dv (the transposed reads of P / dS come from shared memory rows padded to 33 floats).
+constexpr int ATTB_WARPS = 4;
+template <int DH>
+__global__ void __launch_bounds__(ATTB_WARPS * 32) vit_attention_bwd_kernel(const void* __restrict__ qkv, const void* __restrict__ dO,
+                                                                            long pose_heads, int tokens, int heads, float scale,
+                                                                            void* __restrict__ dqkv, int fmt) {
+    griddep_launch();
+    griddep_wait();
+    constexpr int LDS = DH + 8, VPR = DH / 8;
+    extern __shared__ __align__(16) unsigned char attb_smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long ph = static_cast<long>(blockIdx.x) * ATTB_WARPS + wid;
+    if (ph >= pose_heads) return;
+    const long pose = ph / heads;
+    const int head = static_cast<int>(ph - pose * heads);
+    const int Hd = heads * DH, N = tokens;
+    const size_t per_warp = (static_cast<size_t>(4) * N * LDS * 2 + static_cast<size_t>(2) * N * 33 * 4 + 15) / 16 * 16;
+    unsigned short* sq = reinterpret_cast<unsigned short*>(attb_smem + wid * per_warp);
+    unsigned short* sk = sq + N * LDS;
+    unsigned short* sv = sk + N * LDS;
+    unsigned short* sdo = sv + N * LDS;
+    float* sP = reinterpret_cast<float*>(sdo + N * LDS);
+    float* sS = sP + N * 33;
+    const unsigned short* src = static_cast<const unsigned short*>(qkv) + pose * N * (3L * Hd) + head * DH;
+    const unsigned short* srcdo = static_cast<const unsigned short*>(dO) + pose * N * static_cast<long>(Hd) + head * DH;
+    for (int i = lane; i < 4 * N * VPR; i += 32) {
+        const int vec = i % VPR, rs = i / VPR, slice = rs / N, n = rs - slice * N;
+        const uint4 val = slice < 3 ? *reinterpret_cast<const uint4*>(src + n * (3L * Hd) + slice * Hd + vec * 8)
+                                    : *reinterpret_cast<const uint4*>(srcdo + n * static_cast<long>(Hd) + vec * 8);
+        *reinterpret_cast<uint4*>(sq + (slice * N + n) * LDS + vec * 8) = val;
+    }
+    __syncwarp();
+    auto load_row = [&](const unsigned short* base, int row, float (&r)[DH], float mul) {
+#pragma unroll
+        for (int v = 0; v < VPR; ++v) {
+            const uint4 w = *reinterpret_cast<const uint4*>(base + row * LDS + v * 8);
+            const uint32_t wd[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack16(wd[e], fmt);
+                r[v * 8 + 2 * e] = f.x * mul;
+                r[v * 8 + 2 * e + 1] = f.y * mul;
+            }
+        }
+    };
+    auto dot_row = [&](const unsigned short* base, int row, const float (&r)[DH]) {
+        float s = 0.0f;
+#pragma unroll
+        for (int v = 0; v < VPR; ++v) {
+            const uint4 w = *reinterpret_cast<const uint4*>(base + row * LDS + v * 8);
+            const uint32_t wd[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack16(wd[e], fmt);
+                s = fmaf(r[v * 8 + 2 * e], f.x, s);
+                s = fmaf(r[v * 8 + 2 * e + 1], f.y, s);
+            }
+        }
+        return s;
+    };
+    auto axpy_row = [&](const unsigned short* base, int row, float a, float (&r)[DH]) {
+#pragma unroll
+        for (int v = 0; v < VPR; ++v) {
+            const uint4 w = *reinterpret_cast<const uint4*>(base + row * LDS + v * 8);
+            const uint32_t wd[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack16(wd[e], fmt);
+                r[v * 8 + 2 * e] = fmaf(a, f.x, r[v * 8 + 2 * e]);
+                r[v * 8 + 2 * e + 1] = fmaf(a, f.y, r[v * 8 + 2 * e + 1]);
+            }
+        }
+    };
+    auto store_row = [&](int slice, int row, const float (&r)[DH]) {
+        uint4* dst = reinterpret_cast<uint4*>(static_cast<unsigned short*>(dqkv) + (pose * N + row) * (3L * Hd) + slice * Hd + head * DH);
+#pragma unroll
+        for (int v = 0; v < VPR; ++v)
+            dst[v] = make_uint4(pack16(r[v * 8], r[v * 8 + 1], fmt), pack16(r[v * 8 + 2], r[v * 8 + 3], fmt),
+                                pack16(r[v * 8 + 4], r[v * 8 + 5], fmt), pack16(r[v * 8 + 6], r[v * 8 + 7], fmt));
+    };
+    float acc[DH];
+    if (lane < N) {
+        const int i = lane;
+        load_row(sq, i, acc, scale * 1.4426950408889634f);               // q_i / sqrt(d) in log2 units
+        float mx = -CUDART_INF_F;
+        for (int j = 0; j < N; ++j) {
+            const float s = dot_row(sk, j, acc);
+            sP[i * 33 + j] = s;
+            mx = fmaxf(mx, s);
+        }
+        float den = 0.0f;
+        for (int j = 0; j < N; ++j) {
+            const float p = exp2f(sP[i * 33 + j] - mx);
+            sP[i * 33 + j] = p;
+            den += p;
+        }
+        const float inv = 1.0f / den;
+        load_row(sdo, i, acc, 1.0f);                                      // dO_i
+        float Di = 0.0f;
+        for (int j = 0; j < N; ++j) {
+            const float p = sP[i * 33 + j] * inv;
+            const float dp = dot_row(sv, j, acc);                         // dP_ij = dO_i . v_j
+            sP[i * 33 + j] = p;
+            sS[i * 33 + j] = dp;
+            Di = fmaf(dp, p, Di);
+        }
+#pragma unroll
+        for (int d = 0; d < DH; ++d) acc[d] = 0.0f;
+        for (int j = 0; j < N; ++j) {
+            const float ds = sP[i * 33 + j] * (sS[i * 33 + j] - Di) * scale;     // d S_ij (with the 1 / sqrt d of the forward)
+            sS[i * 33 + j] = ds;
+            axpy_row(sk, j, ds, acc);                                     // dq_i += dS_ij k_j
+        }
+        store_row(0, i, acc);
+    }
+    __syncwarp();
+    if (lane < N) {
+        const int j = lane;
+#pragma unroll
+        for (int d = 0; d < DH; ++d) acc[d] = 0.0f;
+        for (int i = 0; i < N; ++i) axpy_row(sq, i, sS[i * 33 + j], acc);     // dk_j = sum_i dS_ij q_i
+        store_row(1, j, acc);
+#pragma unroll
+        for (int d = 0; d < DH; ++d) acc[d] = 0.0f;
+        for (int i = 0; i < N; ++i) axpy_row(sdo, i, sP[i * 33 + j], acc);    // dv_j = sum_i P_ij dO_i
+        store_row(2, j, acc);
+    }
+}
+
+size_t attb_smem_bytes(int tokens, int dh) {
+    return static_cast<size_t>(ATTB_WARPS) * ((static_cast<size_t>(4) * tokens * (dh + 8) * 2 + static_cast<size_t>(2) * tokens * 33 * 4 + 15) / 16 * 16);
+}
+
+}  // namespace
+}  // namespace lifter
+
+namespace lifter {
+
+namespace {
+
+struct SavedLayout {                       // 16-bit matrices kept by the train-mode forward, element offsets
+    long T; int H, M, Hh, nb;
+    long h0, blocks, block_stride, r, total;
+    long u1(int b) const { return blocks + b * block_stride; }
+    long qkv(int b) const { return u1(b) + T * H; }
+    long o(int b) const { return qkv(b) + T * 3L * H; }
+    long h1(int b) const { return o(b) + T * H; }
+    long u2(int b) const { return h1(b) + T * H; }
+    long z1(int b) const { return u2(b) + T * H; }
+    long m(int b) const { return z1(b) + T * static_cast<long>(M); }
+    long hout(int b) const { return m(b) + T * static_cast<long>(M); }
+    long hin(int b) const { return b == 0 ? h0 : hout(b - 1); }
+    long hlast() const { return nb == 0 ? h0 : hout(nb - 1); }
+};
+
+SavedLayout saved_layout(const VitDesc& d, int64_t poses) {
+    SavedLayout s;
+    s.T = poses * d.tokens; s.H = d.hidden; s.M = d.mlp_dim; s.Hh = d.head_dim; s.nb = d.blocks;
+    s.h0 = 0;
+    s.blocks = s.T * s.H;
+    s.block_stride = s.T * (8L * s.H + 2L * s.M);
+    s.r = s.blocks + s.nb * s.block_stride;
+    s.total = s.r + s.T * s.Hh;
+    return s;
+}
+
+long slab_floats(int M_out, int N_in, int K) {
+    return static_cast<long>(gemm_effective_splits(K, wgrad_splits(M_out, N_in, K))) * gemm_slab_rows(M_out) * N_in;
+}
+
+struct BwdScratch {
+    unsigned short *dout16, *dr, *dhA, *dhB, *du, *dO, *dm, *dqkv;
+    float *slabs, *part;
+    size_t bytes;
+};
+
+int part_rows(long T) { return static_cast<int>((T + 8 * VIT_RPW - 1) / (8 * VIT_RPW)); }
+int colsum_blocks(long T) { const long b = (T + 63) / 64; return static_cast<int>(b < 592 ? b : 592); }
+
+BwdScratch bwd_scratch(const VitDesc& d, int64_t poses, void* base) {
+    const long T = poses * d.tokens;
+    const int H = d.hidden, M = d.mlp_dim, Hh = d.head_dim, K = static_cast<int>(T);
+    BwdScratch s;
+    char* p = static_cast<char*>(base);
+    auto take = [&](size_t bytes) { char* q = p; p += (bytes + 255) / 256 * 256; return q; };
+    s.dout16 = reinterpret_cast<unsigned short*>(take(T * 64 * 2));
+    s.dr = reinterpret_cast<unsigned short*>(take(T * Hh * 2L));
+    s.dhA = reinterpret_cast<unsigned short*>(take(T * H * 2L));
+    s.dhB = reinterpret_cast<unsigned short*>(take(T * H * 2L));
+    s.du = reinterpret_cast<unsigned short*>(take(T * H * 2L));
+    s.dO = reinterpret_cast<unsigned short*>(take(T * H * 2L));
+    s.dm = reinterpret_cast<unsigned short*>(take(T * M * 2L));
+    s.dqkv = reinterpret_cast<unsigned short*>(take(T * 3L * H * 2));
+    long slab = slab_floats(64, Hh, K);
+    const long cands[5] = {slab_floats(Hh, H, K), slab_floats(3 * H, H, K), slab_floats(H, H, K), slab_floats(M, H, K), slab_floats(H, M, K)};
+    for (long c : cands) slab = c > slab ? c : slab;
+    s.slabs = reinterpret_cast<float*>(take(slab * 4));
+    long part = static_cast<long>(part_rows(T)) * 5 * H;                          // LayerNorm (4 H) / embedding (<= 5 H) partial rows
+    const long cs = static_cast<long>(colsum_blocks(T)) * (M > 3 * H ? M : 3 * H);
+    part = cs > part ? cs : part;
+    const long po = static_cast<long>(ew_partial_rows(T, 64)) * 64;
+    part = po > part ? po : part;
+    s.part = reinterpret_cast<float*>(take(part * 4));
+    s.bytes = static_cast<size_t>(p - static_cast<char*>(base));
+    return s;
+}
+
+int pointwise(const void* a, const void* b, void* out, long n, int mode, int fmt, cudaStream_t st) {
+    const long n8 = n / 8;
+    long blocks = (n8 + 255) / 256;
+    const long cap = static_cast<long>(num_sms()) * 8;
+    if (blocks > cap) blocks = cap;
+    LIFTER_CHECK_CUDA(launch_pdl("vit_pointwise_kernel", vit_pointwise_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st,
+                                 static_cast<const uint4*>(a), static_cast<const uint4*>(b), static_cast<uint4*>(out), n8, mode, fmt));
+    return LIFTER_OK;
+}
+
+// out[W] = column sums of the 16-bit matrix m [T][W]
+int colsum16(const unsigned short* m, long T, int W, float* part, float* out, int fmt, cudaStream_t st) {
+    const int blocks = colsum_blocks(T);
+    const long rpb = (T + blocks - 1) / blocks;
+    LIFTER_CHECK_CUDA(launch_pdl("vit_colsum16_kernel", vit_colsum16_kernel, dim3(blocks), dim3(CS_THREADS), 0, st, m, T, W, rpb, part, fmt));
+    return reduce_rows_f32(part, blocks, W, W, out, st);
+}
+
+// dW [M_out][N_in] (dense fp32, rows_valid x N_in) = dZ^T X over the T rows
+int wgrad16(const unsigned short* dZ, int M_out, const unsigned short* X, int N_in, int T, int rows_valid, float* slabs, float* grad,
+            int fmt, cudaStream_t st) {
+    GemmArgs g;
+    g.A = dZ; g.lda = M_out; g.a_mn_major = 1;
+    g.B = X; g.ldb = N_in; g.b_mn_major = 1;
+    g.M = M_out; g.N = N_in; g.K = T; g.fmt = fmt; g.out_mode = OUT_32_TMA; g.D = slabs; g.ldd = N_in;
+    g.splits = wgrad_splits(M_out, N_in, T);
+    g.tag = "vit_wgrad";
+    LIFTER_PROPAGATE(gemm_launch(g, st));
+    return wgrad_reduce(slabs, gemm_effective_splits(T, g.splits), gemm_slab_rows(M_out), N_in, rows_valid, N_in, grad, st);
+}
+
+// dX [T][N_in] (16-bit) = dZ [T][M_out] W [M_out][N_in] (+ residual)
+int dgrad16(const unsigned short* dZ, int M_out, const void* W, int N_in, int T, unsigned short* dX, const unsigned short* residual,
+            int fmt, cudaStream_t st) {
+    GemmArgs g;
+    g.A = dZ; g.lda = M_out;
+    g.B = W; g.ldb = N_in; g.b_mn_major = 1;
+    g.M = T; g.N = N_in; g.K = M_out; g.fmt = fmt; g.out_mode = OUT_16_TMA; g.D = dX; g.ldd = N_in;
+    if (residual != nullptr) { g.residual = residual; g.ldr = N_in; }
+    g.tag = "vit_dgrad";
+    return gemm_launch(g, st);
+}
+
+int validate_train(const VitDesc& d) {
+    LIFTER_PROPAGATE(vit_validate(d));
+    LIFTER_REQUIRE(d.mlp_dim <= 2048 && 3 * d.hidden <= 2048, "vit training: hidden width %d unsupported (256 or 512)", d.hidden);
+    return LIFTER_OK;
+}
+
+}  // namespace
+
+int64_t vit_saved_bytes(const VitDesc& d, int64_t poses) {
+    if (validate_train(d) != LIFTER_OK || poses < 0) return LIFTER_ERR_INVALID;
+    return saved_layout(d, poses).total * 2 + 256;
+}
+
+int64_t vit_bwd_scratch_bytes(const VitDesc& d, int64_t poses) {
+    if (validate_train(d) != LIFTER_OK || poses < 1) return LIFTER_ERR_INVALID;
+    return static_cast<int64_t>(bwd_scratch(d, poses, nullptr).bytes) + 256;
+}
+
+}  // namespace lifter
+
+namespace lifter {
+
+int vit_train_forward(const VitDesc& d, const float* x, int64_t poses, void* saved, float* out, cudaStream_t st) {
+    LIFTER_PROPAGATE(validate_train(d));
+    if (poses <= 0) return LIFTER_OK;
+    LIFTER_REQUIRE(x && saved && out, "vit_train_forward: null pointer");
+    LIFTER_REQUIRE(reinterpret_cast<uintptr_t>(saved) % 16 == 0, "vit_train_forward: saved-activation buffer must be 16-byte aligned");
+    const SavedLayout L = saved_layout(d, poses);
+    LIFTER_REQUIRE(L.T <= 0x7fffffffL, "vit_train_forward: %ld tokens in one call", L.T);
+    const int H = d.hidden, dh = H / d.heads, M = static_cast<int>(L.T);
+    unsigned short* S = static_cast<unsigned short*>(saved);
+    const long T = L.T;
+    LIFTER_PROPAGATE(vit_embed(d, x, T, S + L.h0, d.blocks > 0 ? d.ln : nullptr, d.blocks > 0 ? static_cast<void*>(S + L.u1(0)) : nullptr, st));
+    const long pose_heads = poses * d.heads;
+    for (int b = 0; b < d.blocks; ++b) {
+        const float* ln = d.ln + static_cast<long>(b) * 6 * H;
+        const char* wqkv = static_cast<const char*>(d.w_qkv) + static_cast<long>(b) * 3 * H * H * 2;
+        const char* wout = static_cast<const char*>(d.w_out) + static_cast<long>(b) * H * H * 2;
+        const char* w1 = static_cast<const char*>(d.w_mlp1) + static_cast<long>(b) * d.mlp_dim * H * 2;
+        const char* w2 = static_cast<const char*>(d.w_mlp2) + static_cast<long>(b) * H * d.mlp_dim * 2;
+        unsigned short *hin = S + L.hin(b), *u1 = S + L.u1(b), *qkv = S + L.qkv(b), *o = S + L.o(b), *h1 = S + L.h1(b),
+                       *u2 = S + L.u2(b), *z1 = S + L.z1(b), *m = S + L.m(b), *hout = S + L.hout(b);
+        if (b > 0) LIFTER_PROPAGATE(vit_layernorm(hin, T, ln, ln + H, ln + 2 * H, ln + 3 * H, d.ln_eps, u1, H, d.fmt, st));
+        GemmArgs g;
+        g.A = u1; g.lda = H; g.B = wqkv; g.ldb = H; g.M = M; g.N = 3 * H; g.K = H; g.fmt = d.fmt; g.D = qkv; g.ldd = 3 * H; g.tag = "vit_qkv";
+        LIFTER_PROPAGATE(gemm_launch(g, st));
+        LIFTER_PROPAGATE(vit_attention(qkv, pose_heads, d.tokens, d.heads, dh, o, d.fmt, st));
+        GemmArgs go;
+        go.A = o; go.lda = H; go.B = wout; go.ldb = H; go.M = M; go.N = H; go.K = H; go.fmt = d.fmt; go.D = h1; go.ldd = H;
+        go.residual = hin; go.ldr = H; go.tag = "vit_attn_out";
+        LIFTER_PROPAGATE(gemm_launch(go, st));
+        LIFTER_PROPAGATE(vit_layernorm(h1, T, ln + 4 * H, ln + 5 * H, nullptr, nullptr, d.ln_eps, u2, H, d.fmt, st));
+        GemmArgs g1;                                              // z1 = u2 W1^T + b1 kept (GELU is not invertible), then m = GELU(z1)
+        g1.A = u2; g1.lda = H; g1.B = w1; g1.ldb = H; g1.M = M; g1.N = d.mlp_dim; g1.K = H; g1.fmt = d.fmt; g1.D = z1; g1.ldd = d.mlp_dim;
+        g1.shift = d.mlp_b1 + static_cast<long>(b) * d.mlp_dim; g1.tag = "vit_mlp1";
+        LIFTER_PROPAGATE(gemm_launch(g1, st));
+        LIFTER_PROPAGATE(pointwise(z1, nullptr, m, T * d.mlp_dim, 0, d.fmt, st));
+        GemmArgs g2;
+        g2.A = m; g2.lda = d.mlp_dim; g2.B = w2; g2.ldb = d.mlp_dim; g2.M = M; g2.N = H; g2.K = d.mlp_dim; g2.fmt = d.fmt; g2.D = hout; g2.ldd = H;
+        g2.shift = d.mlp_b2 + static_cast<long>(b) * H; g2.residual = h1; g2.ldr = H; g2.tag = "vit_mlp2";
+        LIFTER_PROPAGATE(gemm_launch(g2, st));
+    }
+    GemmArgs gh;
+    gh.A = S + L.hlast(); gh.lda = H; gh.B = d.w_head1; gh.ldb = H; gh.M = M; gh.N = d.head_dim; gh.K = H; gh.fmt = d.fmt;
+    gh.D = S + L.r; gh.ldd = d.head_dim; gh.shift = d.head_b1; gh.relu = 1; gh.tag = "vit_head1";
+    LIFTER_PROPAGATE(gemm_launch(gh, st));
+    GemmArgs gf;
+    gf.A = S + L.r; gf.lda = d.head_dim; gf.B = d.w_head2; gf.ldb = d.head_dim; gf.M = M; gf.N = 64; gf.K = d.head_dim; gf.fmt = d.fmt;
+    gf.out_mode = OUT_32_DIRECT; gf.D = out; gf.n_valid = d.out_dim; gf.shift = d.head_b2; gf.tag = "vit_head2";
+    return gemm_launch(gf, st);
+}
+
+int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* saved, const float* dout, void* scratch,
+                 const VitGrads& G, cudaStream_t st) {
+    LIFTER_PROPAGATE(validate_train(d));
+    LIFTER_REQUIRE(poses >= 1, "vit_backward: empty batch");
+    LIFTER_REQUIRE(x && saved && dout && scratch, "vit_backward: null pointer");
+    LIFTER_REQUIRE(G.map && G.w_head1 && G.head_b1 && G.w_head2 && G.head_b2, "vit_backward: null gradient pointer");
+    LIFTER_REQUIRE(d.blocks == 0 || (G.ln && G.w_qkv && G.w_out && G.w_mlp1 && G.mlp_b1 && G.w_mlp2 && G.mlp_b2), "vit_backward: null block gradient pointer");
+    LIFTER_REQUIRE(reinterpret_cast<uintptr_t>(scratch) % 256 == 0, "vit_backward: scratch must be 256-byte aligned");
+    const SavedLayout L = saved_layout(d, poses);
+    const BwdScratch B = bwd_scratch(d, poses, scratch);
+    const int H = d.hidden, nv = H / 256, dh = H / d.heads, Mm = d.mlp_dim, Hh = d.head_dim, fmt = d.fmt;
+    const long T = L.T;
+    const int Ti = static_cast<int>(T);
+    const unsigned short* S = static_cast<const unsigned short*>(saved);
+    const unsigned row_blocks = static_cast<unsigned>(part_rows(T));
+    // ---- head -------------------------------------------------------------------------------------------------------------
+    LIFTER_PROPAGATE(prep_grad_out(dout, T, d.out_dim, 64, fmt, B.dout16, B.part, st));
+    LIFTER_PROPAGATE(reduce_rows_f32(B.part, ew_partial_rows(T, 64), d.out_dim, 64, G.head_b2, st));
+    LIFTER_PROPAGATE(wgrad16(B.dout16, 64, S + L.r, Hh, Ti, d.out_dim, B.slabs, G.w_head2, fmt, st));
+    LIFTER_PROPAGATE(dgrad16(B.dout16, 64, d.w_head2, Hh, Ti, B.dr, nullptr, fmt, st));
+    LIFTER_PROPAGATE(pointwise(S + L.r, B.dr, B.dr, T * Hh, 2, fmt, st));
+    LIFTER_PROPAGATE(colsum16(B.dr, T, Hh, B.part, G.head_b1, fmt, st));
+    LIFTER_PROPAGATE(wgrad16(B.dr, Hh, S + L.hlast(), H, Ti, Hh, B.slabs, G.w_head1, fmt, st));
+    LIFTER_PROPAGATE(dgrad16(B.dr, Hh, d.w_head1, H, Ti, B.dhA, nullptr, fmt, st));
+    // ---- blocks, last to first; dhA holds d loss / d (block output) -------------------------------------------------------------
+    const size_t smem = attb_smem_bytes(d.tokens, dh);
+    if (dh == 64) LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_bwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    else          LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    const long pose_heads = poses * d.heads;
+    const float att_scale = 1.0f / sqrtf(static_cast<float>(dh));
+    for (int b = d.blocks - 1; b >= 0; --b) {
+        const float* ln = d.ln + static_cast<long>(b) * 6 * H;
+        float* gln = G.ln + static_cast<long>(b) * 6 * H;
+        const char* wqkv = static_cast<const char*>(d.w_qkv) + static_cast<long>(b) * 3 * H * H * 2;
+        const char* wout = static_cast<const char*>(d.w_out) + static_cast<long>(b) * H * H * 2;
+        const char* w1 = static_cast<const char*>(d.w_mlp1) + static_cast<long>(b) * Mm * H * 2;
+        const char* w2 = static_cast<const char*>(d.w_mlp2) + static_cast<long>(b) * H * Mm * 2;
+        // MLP: hout = h1 + W2 GELU(W1 LN2(h1) + b1) + b2
+        LIFTER_PROPAGATE(colsum16(B.dhA, T, H, B.part, G.mlp_b2 + static_cast<long>(b) * H, fmt, st));
+        LIFTER_PROPAGATE(wgrad16(B.dhA, H, S + L.m(b), Mm, Ti, H, B.slabs, G.w_mlp2 + static_cast<long>(b) * H * Mm, fmt, st));
+        LIFTER_PROPAGATE(dgrad16(B.dhA, H, w2, Mm, Ti, B.dm, nullptr, fmt, st));
+        LIFTER_PROPAGATE(pointwise(S + L.z1(b), B.dm, B.dm, T * Mm, 1, fmt, st));
+        LIFTER_PROPAGATE(colsum16(B.dm, T, Mm, B.part, G.mlp_b1 + static_cast<long>(b) * Mm, fmt, st));
+        LIFTER_PROPAGATE(wgrad16(B.dm, Mm, S + L.u2(b), H, Ti, Mm, B.slabs, G.w_mlp1 + static_cast<long>(b) * Mm * H, fmt, st));
+        LIFTER_PROPAGATE(dgrad16(B.dm, Mm, w1, H, Ti, B.du, nullptr, fmt, st));
+        VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_ln_bwd_kernel", vit_ln_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
+                                                         static_cast<const void*>(S + L.h1(b)), static_cast<const void*>(B.du), static_cast<const void*>(B.dhA), T,
+                                                         ln + 4 * H, ln + 5 * H, static_cast<const float*>(nullptr), static_cast<const float*>(nullptr), d.ln_eps,
+                                                         static_cast<void*>(B.dhB), B.part, fmt)));
+        LIFTER_PROPAGATE(reduce_rows_f32(B.part, static_cast<int>(row_blocks), 2 * H, 4 * H, gln + 4 * H, st));
+        // attention: h1 = hin + Wout attn(Wqkv LN(LN(hin)))
+        LIFTER_PROPAGATE(wgrad16(B.dhB, H, S + L.o(b), H, Ti, H, B.slabs, G.w_out + static_cast<long>(b) * H * H, fmt, st));
+        LIFTER_PROPAGATE(dgrad16(B.dhB, H, wout, H, Ti, B.dO, nullptr, fmt, st));
+        if (dh == 64)
+            LIFTER_CHECK_CUDA(launch_pdl("vit_attention_bwd_kernel", vit_attention_bwd_kernel<64>, dim3(static_cast<unsigned>((pose_heads + ATTB_WARPS - 1) / ATTB_WARPS)),
+                                         dim3(ATTB_WARPS * 32), smem, st, static_cast<const void*>(S + L.qkv(b)), static_cast<const void*>(B.dO), pose_heads, d.tokens,
+                                         d.heads, att_scale, static_cast<void*>(B.dqkv), fmt));
+        else
+            LIFTER_CHECK_CUDA(launch_pdl("vit_attention_bwd_kernel", vit_attention_bwd_kernel<32>, dim3(static_cast<unsigned>((pose_heads + ATTB_WARPS - 1) / ATTB_WARPS)),
+                                         dim3(ATTB_WARPS * 32), smem, st, static_cast<const void*>(S + L.qkv(b)), static_cast<const void*>(B.dO), pose_heads, d.tokens,
+                                         d.heads, att_scale, static_cast<void*>(B.dqkv), fmt));
+        LIFTER_PROPAGATE(wgrad16(B.dqkv, 3 * H, S + L.u1(b), H, Ti, 3 * H, B.slabs, G.w_qkv + static_cast<long>(b) * 3 * H * H, fmt, st));
+        LIFTER_PROPAGATE(dgrad16(B.dqkv, 3 * H, wqkv, H, Ti, B.du, nullptr, fmt, st));
+        VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_ln_bwd_kernel", vit_ln_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
+                                                         static_cast<const void*>(S + L.hin(b)), static_cast<const void*>(B.du), static_cast<const void*>(B.dhB), T,
+                                                         ln, ln + H, ln + 2 * H, ln + 3 * H, d.ln_eps, static_cast<void*>(B.dhA), B.part, fmt)));
+        LIFTER_PROPAGATE(reduce_rows_f32(B.part, static_cast<int>(row_blocks), 4 * H, 4 * H, gln, st));
+    }
+    // ---- embedding: d linear_mapper (positional table has requires_grad = False, baselineModel.py:330) -------------------------------
+    VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_bwd_kernel", vit_embed_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
+                                                     static_cast<const void*>(B.dhA), x, T, d.in_dim, B.part, fmt)));
+    return reduce_rows_f32(B.part, static_cast<int>(row_blocks), (1 + d.in_dim) * H, (1 + d.in_dim) * H, G.map, st);
+}
+
+}  // namespace lifter
+
+// ---- C ABI (include/lifter_b200.h) ---------------------------------------------------------------------------------
+#include "../../include/lifter_b200.h"
+
+lifter::VitDesc lifter_vit_to_desc(const lifter_vit_t* v);        // vit_ops.cu
+
+extern "C" {
+
+int64_t lifter_vit_saved_bytes(const lifter_vit_t* vit, int64_t poses) {
+    if (vit == nullptr) return LIFTER_ERR_INVALID;
+    return lifter::vit_saved_bytes(lifter_vit_to_desc(vit), poses);
+}
+
+int64_t lifter_vit_bwd_scratch_bytes(const lifter_vit_t* vit, int64_t poses) {
+    if (vit == nullptr) return LIFTER_ERR_INVALID;
+    return lifter::vit_bwd_scratch_bytes(lifter_vit_to_desc(vit), poses);
+}
+
+int lifter_vit_train_forward(const lifter_vit_t* vit, const float* x, int64_t poses, void* saved, float* out, void* stream) {
+    LIFTER_REQUIRE(vit != nullptr, "vit_train_forward: null descriptor");
+    return lifter::vit_train_forward(lifter_vit_to_desc(vit), x, poses, saved, out, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_vit_backward(const lifter_vit_t* vit, const float* x, int64_t poses, const void* saved, const float* dout, void* scratch,
+                        const lifter_vit_grads_t* g, void* stream) {
+    LIFTER_REQUIRE(vit != nullptr && g != nullptr, "vit_backward: null descriptor");
+    lifter::VitGrads G;
+    G.map = g->map; G.ln = g->ln; G.w_qkv = g->w_qkv; G.w_out = g->w_out; G.w_mlp1 = g->w_mlp1; G.mlp_b1 = g->mlp_b1;
+    G.w_mlp2 = g->w_mlp2; G.mlp_b2 = g->mlp_b2; G.w_head1 = g->w_head1; G.head_b1 = g->head_b1; G.w_head2 = g->w_head2; G.head_b2 = g->head_b2;
+    return lifter::vit_backward(lifter_vit_to_desc(vit), x, poses, saved, dout, scratch, G, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -5,10 +5,13 @@ Mirror of ``phase1_lifting/baselineModel.py:220-362``: ``get_positional_embeddin
 torch-RNG consumption at construction (same seed => same initial weights).  ``forward(images)`` takes ``(B, 17, 2)`` fp32
 CUDA and returns ``(B, 17, 3)`` fp32.
 
-Scope of this round: the EVAL-MODE forward (``model.eval()`` / ``torch.no_grad()``, the inference and validation call
-sites ``train_1.py:112-134``) runs on the sm_100a kernels behind ``lifter_vit_forward`` (tcgen05 GEMMs with fused
-bias / GELU / ReLU / residual epilogues, LayerNorm, attention and embedding kernels).  The training backward of the
-transformer is not built yet: ``forward`` with autograd enabled raises instead of falling back to PyTorch.
+Without autograd (``torch.no_grad()``, the inference and validation call sites ``train_1.py:112-134``) ``forward`` runs
+``lifter_vit_forward`` (tcgen05 GEMMs with fused bias / GELU / ReLU / residual epilogues, LayerNorm, attention and embedding
+kernels; fp16 operands).  With autograd enabled it goes through ``_VitFunction``: ``lifter_vit_train_forward`` keeps every GEMM
+input and ``lifter_vit_backward`` fills ``.grad`` of every trainable parameter (bf16 operands), so the loop body
+``train_1.py:73-100`` -- ``loss.backward(); optimizer_lift.step()`` with a ``torch.optim`` optimiser -- runs unchanged.  The
+model has no dropout and no BatchNorm, so train and eval mode compute the same function.  Not built: the gradient with
+respect to the input key points (raises).  No PyTorch or CPU fallback anywhere.
 """
 from __future__ import annotations
 
@@ -32,6 +35,65 @@ def get_positional_embeddings(sequence_length, d=2):
 
 def _fused_only(name):
     raise RuntimeError(f"{name} runs fused inside MyViT.forward (sm_100a kernels); it has no standalone or CPU path")
+
+
+class _VitFunction(torch.autograd.Function):
+    """autograd bridge of the training path: ``lifter_vit_train_forward`` keeps every GEMM input, ``lifter_vit_backward``
+    returns the gradient of every trainable parameter (``loss.backward()`` / ``optimizer.step()`` of train_1.py:94-96)."""
+
+    @staticmethod
+    def forward(ctx, model, names, images, *params):
+        x = images.detach().to(torch.float32).contiguous()
+        dev = x.device
+        if model.linear_mapper.weight.device != dev:
+            raise RuntimeError("MyViT: parameters and input live on different devices")
+        B = int(x.shape[0])
+        out = torch.empty((B, model.chw[1], model.out_d), dtype=torch.float32, device=dev)
+        ctx.model, ctx.names, ctx.B = model, names, B
+        if B == 0:
+            return out
+        d = model._pack(dev, model.train_format)
+        lib = _cabi.lib()
+        need = lib.lifter_vit_saved_bytes(C.byref(d), B)
+        if need < 0:
+            raise ValueError("MyViT: " + _cabi.last_error())
+        saved = torch.empty(need, dtype=torch.uint8, device=dev)
+        _cabi.check(lib.lifter_vit_train_forward(C.byref(d), _cabi.ptr(x), B, _cabi.ptr(saved), _cabi.ptr(out), _cabi.stream_ptr()))
+        ctx.x, ctx.saved, ctx.desc, ctx.pack = x, saved, d, model._packed[model.train_format]   # keeps the operand copies alive
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        model, B = ctx.model, ctx.B
+        H, nb, J, ind, od = model.hidden_d, model.n_block, model.chw[1], model.input_d, model.out_d
+        dev = dout.device
+        z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev)
+        g = dict(map=z(1 + ind, H), ln=z(nb, 6, H), w_qkv=z(nb, 3 * H, H), w_out=z(nb, H, H), w_mlp1=z(nb, 4 * H, H),
+                 mlp_b1=z(nb, 4 * H), w_mlp2=z(nb, H, 4 * H), mlp_b2=z(nb, H), w_head1=z(H // 2, H), head_b1=z(H // 2),
+                 w_head2=z(od, H // 2), head_b2=z(od))
+        if B > 0:
+            lib = _cabi.lib()
+            G = _cabi.VitGrads()
+            for k, v in g.items():
+                setattr(G, k, v.data_ptr() if v.numel() else None)
+            need = lib.lifter_vit_bwd_scratch_bytes(C.byref(ctx.desc), B)
+            if need < 0:
+                raise ValueError("MyViT: " + _cabi.last_error())
+            scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+            dout = dout.detach().to(torch.float32).contiguous()
+            _cabi.check(lib.lifter_vit_backward(C.byref(ctx.desc), _cabi.ptr(ctx.x), B, _cabi.ptr(ctx.saved), _cabi.ptr(dout),
+                                                _cabi.ptr(scratch), C.byref(G), _cabi.stream_ptr()))
+        by_name = {"linear_mapper.weight": g["map"][1:].t(), "linear_mapper.bias": g["map"][0], "pos_embed": None,
+                   "mlp.0.weight": g["w_head1"], "mlp.0.bias": g["head_b1"], "mlp.2.weight": g["w_head2"], "mlp.2.bias": g["head_b2"]}
+        for b in range(nb):
+            p = f"blocks.{b}."
+            by_name.update({p + "norm1.weight": g["ln"][b, 0], p + "norm1.bias": g["ln"][b, 1], p + "mhsa.norm.weight": g["ln"][b, 2],
+                            p + "mhsa.norm.bias": g["ln"][b, 3], p + "norm2.weight": g["ln"][b, 4], p + "norm2.bias": g["ln"][b, 5],
+                            p + "mhsa.to_qkv.weight": g["w_qkv"][b], p + "mhsa.to_out.weight": g["w_out"][b],
+                            p + "mlp.0.weight": g["w_mlp1"][b], p + "mlp.0.bias": g["mlp_b1"][b],
+                            p + "mlp.2.weight": g["w_mlp2"][b], p + "mlp.2.bias": g["mlp_b2"][b]})
+        grads = tuple(by_name[n] for n in ctx.names)
+        return (None, None, None) + grads
 
 
 class Attention(torch.nn.Module):
@@ -94,20 +156,25 @@ class MyViT(torch.nn.Module):
         self.input_size, self.output_size = chw[1] * chw[2], chw[1] * out_d    # flat sizes, as LinearModel names them
         self.infer_format = "fp16"        # GEMM operand / activation format of the eval path ("fp16" or "bf16")
         self.chunk_poses = 8192           # poses per pass of the kernel sequence (activations of a pass stay near L2)
-        self._packed = None               # (key, tensors, descriptor)
+        self.train_format = "bf16"        # operand format of the training forward / backward (gradient range)
+        self._packed = {}                 # format -> (key, tensors, descriptor)
         self._workspace = None
 
     # ------------------------------------------------------------------------------------------------ packing
     def _pack_key(self):
-        return tuple((p.data_ptr(), p._version) for p in self.parameters()) + (self.infer_format,)
+        return tuple((p.data_ptr(), p._version) for p in self.parameters())
 
-    def _pack(self, dev):
+    def _pack(self, dev, fmt=None):
         """fp32 side tables and 16-bit GEMM operands in the layout of ``lifter_vit_t``; rebuilt when a parameter changed."""
+        fmt = fmt or self.infer_format
+        if fmt not in ("fp16", "bf16"):
+            raise ValueError(f"MyViT: operand format must be 'fp16' or 'bf16', got {fmt!r}")
         key = self._pack_key()
-        if self._packed is not None and self._packed[0] == key:
-            return self._packed[2]
+        hit = self._packed.get(fmt)
+        if hit is not None and hit[0] == key:
+            return hit[2]
         H, nb = self.hidden_d, self.n_block
-        dt = torch.float16 if self.infer_format == "fp16" else torch.bfloat16
+        dt = torch.float16 if fmt == "fp16" else torch.bfloat16
         f32 = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()
 
         def stack(fn, shape):
@@ -135,11 +202,11 @@ class MyViT(torch.nn.Module):
         d = _cabi.VitDesc()
         d.tokens, d.in_dim, d.hidden, d.heads, d.blocks = self.chw[1], self.input_d, H, self.n_heads, nb
         d.mlp_dim, d.head_dim, d.out_dim = 4 * H, H // 2, self.out_d
-        d.fmt = 0 if self.infer_format == "fp16" else 1
+        d.fmt = 0 if fmt == "fp16" else 1
         d.ln_eps = 1e-5
         for k, v in t.items():
             setattr(d, k, v.data_ptr() if v.numel() else None)
-        self._packed = (key, t, d)
+        self._packed[fmt] = (key, t, d)
         return d
 
     # ------------------------------------------------------------------------------------------------ forward
@@ -148,9 +215,11 @@ class MyViT(torch.nn.Module):
             raise RuntimeError("MyViT: the sm_100a build has no CPU path; move the model and the input to a B200")
         if images.dim() != 3 or images.shape[1] != self.chw[1] or images.shape[2] != self.input_d:
             raise ValueError(f"MyViT expects (B, {self.chw[1]}, {self.input_d}) key points, got {tuple(images.shape)}")
-        if torch.is_grad_enabled() and (self.training or images.requires_grad):
-            raise NotImplementedError("MyViT (sm_100a build): only the eval-mode forward is built so far; call "
-                                      "model.eval() and run under torch.no_grad() (training backward: next round)")
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            if images.requires_grad:
+                raise NotImplementedError("MyViT (sm_100a build): the gradient with respect to the key points is not built")
+            names, params = zip(*self.named_parameters())
+            return _VitFunction.apply(self, names, images, *params)
         return self.infer(images)
 
     @torch.no_grad()

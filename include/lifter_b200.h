@@ -286,6 +286,25 @@ int64_t lifter_vit_workspace_bytes(const lifter_vit_t* vit, int64_t poses);
 /* x [poses][tokens][in_dim] fp32 -> out [poses][tokens][out_dim] fp32; asynchronous on `stream`.                  */
 int lifter_vit_forward(const lifter_vit_t* vit, const float* x, int64_t poses, void* workspace, float* out, void* stream);
 
+/* ---- MyViT lifter, training path (loss.backward() through baselineModel.py:228-362; loop body train_1.py:73-100 with
+ * model_lift = MyViT).  No dropout and no BatchNorm in this model: lifter_vit_train_forward is the eval arithmetic that
+ * keeps every GEMM input in `saved` (lifter_vit_saved_bytes); lifter_vit_backward turns d loss / d out into the gradient
+ * of every trainable parameter (the positional table has requires_grad = False, baselineModel.py:330).  vit->fmt is the
+ * operand format of forward AND backward (bf16 for the gradient range).  hidden 256 or 512.                       */
+typedef struct lifter_vit_grads {            /* fp32, stacked per block exactly like the parameters of lifter_vit_t   */
+    float* map;                              /* [1 + in_dim][hidden]: d linear_mapper.bias, then d weight[:, i] per i  */
+    float* ln;                               /* [blocks][6][hidden]                                                  */
+    float* w_qkv; float* w_out; float* w_mlp1; float* mlp_b1; float* w_mlp2; float* mlp_b2;
+    float* w_head1; float* head_b1;
+    float* w_head2;                          /* [out_dim][head_dim]                                                  */
+    float* head_b2;                          /* [out_dim]                                                            */
+} lifter_vit_grads_t;
+int64_t lifter_vit_saved_bytes(const lifter_vit_t* vit, int64_t poses);
+int64_t lifter_vit_bwd_scratch_bytes(const lifter_vit_t* vit, int64_t poses);
+int lifter_vit_train_forward(const lifter_vit_t* vit, const float* x, int64_t poses, void* saved, float* out, void* stream);
+int lifter_vit_backward(const lifter_vit_t* vit, const float* x, int64_t poses, const void* saved, const float* dout,
+                        void* scratch, const lifter_vit_grads_t* grads, void* stream);
+
 /* ---- test hook: one tcgen05 GEMM  D[M][N] = sum_k A(m,k) B(n,k) ------------------------------------ */
 typedef struct lifter_gemm_desc {
     const void* A; int64_t lda; const void* B; int64_t ldb;

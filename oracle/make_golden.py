@@ -130,6 +130,20 @@ def vit_case():
         with torch.no_grad():
             y = m(torch.from_numpy(x))
         out[tag + "_x"], out[tag + "_y"] = x, y.numpy()
+        # training: MSE against a random target, loss.backward() on the reference module (train_1.py:94-95)
+        tgt = rs.normal(0, 1, y.shape).astype(np.float32)
+        m.train()
+        m.zero_grad()
+        loss = torch.nn.functional.mse_loss(m(torch.from_numpy(x)), torch.from_numpy(tgt))
+        loss.backward()
+        names = [n for n, p_ in m.named_parameters() if p_.grad is not None]
+        out[tag + "_target"], out[tag + "_loss"] = tgt, np.float32(loss.item())
+        out[tag + "_grad_names"] = np.array(names)
+        out[tag + "_grad_sums"] = np.array([float(dict(m.named_parameters())[n].grad.double().sum()) for n in names])
+        out[tag + "_grad_abs"] = np.array([float(dict(m.named_parameters())[n].grad.double().abs().sum()) for n in names])
+        out[tag + "_grad_map_w"] = m.linear_mapper.weight.grad.numpy().copy()
+        out[tag + "_grad_head_w"] = m.mlp[2].weight.grad.numpy().copy()
+        m.eval()
     torch.manual_seed(5)
     m = ref_model.MyViT()
     sd = m.state_dict()

@@ -232,3 +232,20 @@ def test_vit_oracle_matches_reference_module(golden_dir, tag, cfg):
     y = V.vit_forward(params, T(g[tag + "_x"]), **cfg).numpy()
     np.testing.assert_allclose(y, g[tag + "_y"], rtol=1e-5, atol=1e-5)
     np.testing.assert_allclose(V.positional_embeddings(17, 256).numpy(), g["pos_embed"], rtol=0, atol=1e-7)
+
+
+@pytest.mark.parametrize("tag,cfg", [("default", {}), ("b3h8", dict(n_blocks=3, n_heads=8))])
+def test_vit_oracle_gradients_match_reference_module(golden_dir, tag, cfg):
+    """autograd through oracle/vit_oracle.py == loss.backward() on the imported reference MyViT (train_1.py:94-95)."""
+    from oracle import vit_oracle as V
+    g = np.load(os.path.join(golden_dir, "vit.npz"), allow_pickle=False)
+    params = {k: v.clone().requires_grad_(k != "pos_embed") for k, v in V.numpy_init(11, **cfg).items()}
+    loss = torch.nn.functional.mse_loss(V.vit_forward(params, T(g[tag + "_x"]), **cfg), T(g[tag + "_target"]))
+    loss.backward()
+    np.testing.assert_allclose(loss.item(), float(g[tag + "_loss"]), rtol=1e-5)
+    names = [str(n) for n in g[tag + "_grad_names"]]
+    assert names == [k for k in params if k != "pos_embed"]
+    np.testing.assert_allclose([float(params[n].grad.double().abs().sum()) for n in names], g[tag + "_grad_abs"], rtol=1e-4)
+    np.testing.assert_allclose([float(params[n].grad.double().sum()) for n in names], g[tag + "_grad_sums"], rtol=1e-3, atol=1e-5)
+    np.testing.assert_allclose(params["linear_mapper.weight"].grad.numpy(), g[tag + "_grad_map_w"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(params["mlp.2.weight"].grad.numpy(), g[tag + "_grad_head_w"], rtol=1e-4, atol=1e-6)

@@ -108,11 +108,10 @@ def test_vit_chunking_weight_updates_and_formats(pkg):
     assert tuple(m.infer(x[:0]).shape) == (0, 17, 3)
 
 
-def test_vit_training_forward_is_not_a_silent_fallback(pkg):
+def test_vit_unsupported_calls_raise(pkg):
     m = pkg.MyViT().cuda()
-    x = torch.randn(4, 17, 2, device="cuda")
     with pytest.raises(NotImplementedError):
-        m.train()(x)
+        m(torch.randn(4, 17, 2, device="cuda", requires_grad=True))          # gradient w.r.t. the key points: not built
     with pytest.raises(ValueError):
         m.eval()(torch.randn(4, 16, 2, device="cuda"))
 
@@ -143,3 +142,99 @@ def test_evaluate_drives_the_transformer_lifter(pkg, golden_dir, flip):
     np.testing.assert_allclose(res["loss"], loss, rtol=3e-3)
     np.testing.assert_allclose(res["per_joint"].numpy(), metric.numpy(), rtol=3e-3)
     np.testing.assert_allclose(res["mpjpe_mm"], float(metric[1:].mean() * (17 / 16) * 1000), rtol=3e-3)
+
+
+# ---------------------------------------------------------------------------------------------------- training path
+def _oracle_grads(params, x, y, **cfg):
+    p = {k: v.clone().requires_grad_(k != "pos_embed") for k, v in params.items()}
+    loss = torch.nn.functional.mse_loss(V.vit_forward(p, x, **cfg), y)
+    loss.backward()
+    return float(loss.detach()), {k: v.grad for k, v in p.items() if k != "pos_embed"}
+
+
+def _check_grads(m, ref, rel_tol=3e-2):
+    for n, p in m.named_parameters():
+        if n == "pos_embed":
+            assert p.grad is None                                     # requires_grad = False (baselineModel.py:330)
+            continue
+        g, r = p.grad.cpu().double().reshape(-1), ref[n].double().reshape(-1)
+        assert tuple(p.grad.shape) == tuple(ref[n].shape), n
+        cos = torch.nn.functional.cosine_similarity(g, r, dim=0).item()
+        assert rel_l2(g, r) < rel_tol and cos > 0.999, f"{n}: rel {rel_l2(g, r):.3e} cos {cos:.6f}"
+
+
+@pytest.mark.parametrize("fmt", ["bf16", "fp16"])
+@pytest.mark.parametrize("tag,cfg", [("default", {}), ("b3h8", dict(n_blocks=3, n_heads=8))])
+def test_vit_backward_matches_reference_golden(pkg, golden_dir, tag, cfg, fmt):
+    """loss.backward() (train_1.py:94-95) on the reference's golden inputs: the loss against the imported reference's,
+    every parameter gradient against autograd through the oracle (itself pinned to the reference's gradients), and two
+    gradient tensors directly against the reference's.  16-bit operands and stored gradients: agreement to ~1e-2."""
+    g = np.load(os.path.join(golden_dir, "vit.npz"))
+    params = V.numpy_init(11, **cfg)
+    m = pkg.MyViT(**cfg)
+    m.load_state_dict(params)
+    m = m.cuda().train()
+    m.train_format = fmt
+    x, y = T(g[tag + "_x"]), T(g[tag + "_target"])
+    loss = torch.nn.functional.mse_loss(m(x.cuda()), y.cuda())
+    loss.backward()
+    np.testing.assert_allclose(loss.item(), float(g[tag + "_loss"]), rtol=1e-2)
+    _, ref = _oracle_grads(params, x, y, **cfg)
+    _check_grads(m, ref, 3e-2)       # fp16 has more mantissa but small gradients reach its subnormals (no loss scaling): same band
+    assert rel_l2(m.linear_mapper.weight.grad.cpu(), g[tag + "_grad_map_w"]) < 3e-2
+    assert rel_l2(m.mlp[2].weight.grad.cpu(), g[tag + "_grad_head_w"]) < 3e-2
+
+
+@pytest.mark.parametrize("joints,in_d,hidden,heads,blocks,out_d,B", [(21, 3, 512, 8, 2, 3, 9), (16, 2, 256, 8, 1, 2, 300), (1, 2, 256, 4, 1, 3, 5)])
+def test_vit_backward_other_shapes(pkg, joints, in_d, hidden, heads, blocks, out_d, B):
+    cfg = dict(n_joints=joints, in_d=in_d, n_blocks=blocks, hidden_d=hidden, n_heads=heads, out_d=out_d)
+    params = V.numpy_init(13, **cfg)
+    m = pkg.MyViT(chw=(1, joints, in_d), n_blocks=blocks, hidden_d=hidden, n_heads=heads, out_d=out_d)
+    m.load_state_dict(params)
+    m = m.cuda().train()
+    x = torch.randn(B, joints, in_d, generator=torch.Generator().manual_seed(B))
+    y = torch.randn(B, joints, out_d, generator=torch.Generator().manual_seed(B + 1))
+    torch.nn.functional.mse_loss(m(x.cuda()), y.cuda()).backward()
+    _, ref = _oracle_grads(params, x, y, n_blocks=blocks, n_heads=heads)
+    _check_grads(m, ref)
+
+
+def test_vit_training_loop_follows_the_oracle_curve(pkg):
+    """The loop body train_1.py:73-100 with model_lift = MyViT and torch.optim.Adam over model.parameters(): 150 steps
+    against the same loop on the fp32 oracle (same data, same initial weights).  30-step window means within 2 % (measured:
+    0.2-1.2 %; bf16 activations put ~0.7 % on the evaluated loss itself once it is small), single steps within 8 % (measured worst 5.1 %); afterwards
+    the no-grad forward sees the trained weights."""
+    params = V.numpy_init(17)
+    m = pkg.MyViT()
+    m.load_state_dict(params)
+    m = m.cuda().train()
+    lr = 3e-4        # at 1e-3 this un-warmed-up transformer is chaotic: 1 % gradient noise moves the fp32 curve itself by 15 %
+    opt = torch.optim.Adam(m.parameters(), lr=lr)
+    ref_p = {k: v.clone().requires_grad_(k != "pos_embed") for k, v in params.items()}
+    ref_opt = torch.optim.Adam([v for k, v in ref_p.items() if k != "pos_embed"], lr=lr)
+    rs = np.random.RandomState(3)
+    wtrue = rs.normal(0, 0.5, (2, 3)).astype(np.float32)
+    steps, B, got, exp = 150, 64, [], []
+    for s in range(steps):
+        x = rs.normal(0, 1, (B, 17, 2)).astype(np.float32)
+        y = np.tanh(x @ wtrue + 0.3 * x.sum(1, keepdims=True) @ wtrue).astype(np.float32)
+        opt.zero_grad()
+        loss = torch.nn.functional.mse_loss(m(T(x).cuda()), T(y).cuda())
+        loss.backward()
+        opt.step()
+        got.append(loss.detach())
+        ref_opt.zero_grad()
+        rl = torch.nn.functional.mse_loss(V.vit_forward(ref_p, T(x)), T(y))
+        rl.backward()
+        ref_opt.step()
+        exp.append(float(rl.detach()))
+    got = torch.stack(got).cpu().double().numpy()
+    exp = np.asarray(exp)
+    assert exp[-20:].mean() < 0.5 * exp[:20].mean()                  # the curve actually descends
+    np.testing.assert_allclose(got.reshape(-1, 30).mean(1), exp.reshape(-1, 30).mean(1), rtol=2e-2)
+    np.testing.assert_allclose(got, exp, rtol=8e-2)
+    xe = torch.randn(33, 17, 2)
+    with torch.no_grad():
+        out = m.eval()(xe.cuda()).cpu()
+        ref = V.vit_forward({k: v.detach() for k, v in ref_p.items()}, xe)
+    assert rel_l2(out, ref) < 3e-2
