@@ -286,10 +286,32 @@ __global__ void __launch_bounds__(256) vit_embed_bwd_kernel(const void* __restri
 namespace lifter {
 namespace {
 
-// Backward of softmax(q k^T / sqrt d) v for one (pose, head) per warp (fp32 FMAs; first version: correctness over speed).
-// qkv, dqkv 16-bit [T][3 Hd]; dO 16-bit [T][Hd].  Lane i owns query row i for P, dP, dS, dq; lane j owns key row j for
-// dk, dv (the transposed reads of P / dS come from shared memory rows padded to 33 floats).
+// Backward of softmax(q k^T / sqrt d) v for one (pose, head) per warp on mma.sync m16n8k16 (fp32 accumulate), the layout
+// of the forward kernel: q, k, v, dO slices staged with `tokens + 1` rows (every MMA-tile row past the token count aliases
+// the zero row).  Per 16-row query tile: S = q k^T and dP = dO v^T as accumulator fragments, softmax and
+// dS = P (dP - rowsum(dP P)) / sqrt d in fp32 on the fragments, dq = dS k with dS re-used in registers as the A operand;
+// P and dS also go to shared memory as 16-bit [query][key] tiles, from which dk = dS^T q and dv = P^T dO read their A
+// operands TRANSPOSED with ldmatrix.trans.  qkv, dqkv 16-bit [T][3 Hd]; dO 16-bit [T][Hd].
 constexpr int ATTB_WARPS = 4;
+constexpr int ATTB_LDP = 40;                           // halfs per row of the P / dS tiles (32 keys + 8: conflict-free ldmatrix)
+
+__device__ __forceinline__ void attb_ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void attb_ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void attb_mma(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1, int fmt) {
+    if (fmt == FMT_BF16)
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                     : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+    else
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                     : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
 template <int DH>
 __global__ void __launch_bounds__(ATTB_WARPS * 32) vit_attention_bwd_kernel(const void* __restrict__ qkv, const void* __restrict__ dO,
                                                                             long pose_heads, int tokens, int heads, float scale,
@@ -303,122 +325,169 @@ __global__ void __launch_bounds__(ATTB_WARPS * 32) vit_attention_bwd_kernel(cons
     if (ph >= pose_heads) return;
     const long pose = ph / heads;
     const int head = static_cast<int>(ph - pose * heads);
-    const int Hd = heads * DH, N = tokens;
-    const size_t per_warp = (static_cast<size_t>(4) * N * LDS * 2 + static_cast<size_t>(2) * N * 33 * 4 + 15) / 16 * 16;
+    const int Hd = heads * DH, N = tokens, R = tokens + 1;
+    const int MT = (N + 15) / 16, NT = (N + 7) / 8;
+    const size_t per_warp = static_cast<size_t>(4) * R * LDS * 2 + static_cast<size_t>(2) * 32 * ATTB_LDP * 2;
     unsigned short* sq = reinterpret_cast<unsigned short*>(attb_smem + wid * per_warp);
-    unsigned short* sk = sq + N * LDS;
-    unsigned short* sv = sk + N * LDS;
-    unsigned short* sdo = sv + N * LDS;
-    float* sP = reinterpret_cast<float*>(sdo + N * LDS);
-    float* sS = sP + N * 33;
+    unsigned short* sP = sq + 4 * R * LDS;
+    unsigned short* sS = sP + 32 * ATTB_LDP;
     const unsigned short* src = static_cast<const unsigned short*>(qkv) + pose * N * (3L * Hd) + head * DH;
     const unsigned short* srcdo = static_cast<const unsigned short*>(dO) + pose * N * static_cast<long>(Hd) + head * DH;
-    for (int i = lane; i < 4 * N * VPR; i += 32) {
-        const int vec = i % VPR, rs = i / VPR, slice = rs / N, n = rs - slice * N;
-        const uint4 val = slice < 3 ? *reinterpret_cast<const uint4*>(src + n * (3L * Hd) + slice * Hd + vec * 8)
-                                    : *reinterpret_cast<const uint4*>(srcdo + n * static_cast<long>(Hd) + vec * 8);
-        *reinterpret_cast<uint4*>(sq + (slice * N + n) * LDS + vec * 8) = val;
+    for (int i = lane; i < 4 * R * VPR; i += 32) {
+        const int vec = i % VPR, rs = i / VPR, slice = rs / R, n = rs - slice * R;
+        uint4 val = make_uint4(0u, 0u, 0u, 0u);
+        if (n < N) val = slice < 3 ? *reinterpret_cast<const uint4*>(src + n * (3L * Hd) + slice * Hd + vec * 8)
+                                   : *reinterpret_cast<const uint4*>(srcdo + n * static_cast<long>(Hd) + vec * 8);
+        *reinterpret_cast<uint4*>(sq + (slice * R + n) * LDS + vec * 8) = val;
     }
     __syncwarp();
-    auto load_row = [&](const unsigned short* base, int row, float (&r)[DH], float mul) {
+    const uint32_t q_addr = smem_u32(sq), k_addr = q_addr + R * LDS * 2, v_addr = k_addr + R * LDS * 2, do_addr = v_addr + R * LDS * 2;
+    const uint32_t p_addr = smem_u32(sP), s_addr = smem_u32(sS);
+    const int g = lane >> 2, t4 = lane & 3;
+    const float scale_log2e = scale * 1.4426950408889634f;
+    unsigned short* out_base = static_cast<unsigned short*>(dqkv) + pose * N * (3L * Hd) + head * DH;
+    auto store_frags = [&](int slice, int row0, const float (&oc)[DH / 8][4]) {      // accumulator tile -> dqkv rows row0 .. + 15
 #pragma unroll
-        for (int v = 0; v < VPR; ++v) {
-            const uint4 w = *reinterpret_cast<const uint4*>(base + row * LDS + v * 8);
-            const uint32_t wd[4] = {w.x, w.y, w.z, w.w};
+        for (int dn = 0; dn < DH / 8; ++dn) {
+            if (row0 + g < N)
+                *reinterpret_cast<uint32_t*>(out_base + (row0 + g) * (3L * Hd) + slice * Hd + dn * 8 + t4 * 2) = pack16(oc[dn][0], oc[dn][1], fmt);
+            if (row0 + g + 8 < N)
+                *reinterpret_cast<uint32_t*>(out_base + (row0 + g + 8) * (3L * Hd) + slice * Hd + dn * 8 + t4 * 2) = pack16(oc[dn][2], oc[dn][3], fmt);
+        }
+    };
+    for (int mt = 0; mt < MT; ++mt) {
+        float sc[4][4], dp[4][4];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const float2 f = unpack16(wd[e], fmt);
-                r[v * 8 + 2 * e] = f.x * mul;
-                r[v * 8 + 2 * e + 1] = f.y * mul;
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) sc[nt][e] = dp[nt][e] = 0.0f;
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) {
+            uint32_t aq[4], ad[4];
+            const int arow = min(mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, N);
+            attb_ldsm_x4(aq, q_addr + (arow * LDS + ks * 16 + (lane >> 4) * 8) * 2);
+            attb_ldsm_x4(ad, do_addr + (arow * LDS + ks * 16 + (lane >> 4) * 8) * 2);
+#pragma unroll
+            for (int np = 0; np < 2; ++np) {
+                if (np * 2 < NT) {
+                    uint32_t bk[4], bv[4];
+                    const int brow = min(np * 16 + (lane & 7) + (lane >> 4) * 8, N);
+                    attb_ldsm_x4(bk, k_addr + (brow * LDS + ks * 16 + ((lane >> 3) & 1) * 8) * 2);
+                    attb_ldsm_x4(bv, v_addr + (brow * LDS + ks * 16 + ((lane >> 3) & 1) * 8) * 2);
+                    attb_mma(sc[np * 2], aq, bk[0], bk[1], fmt);
+                    attb_mma(dp[np * 2], ad, bv[0], bv[1], fmt);
+                    if (np * 2 + 1 < NT) {
+                        attb_mma(sc[np * 2 + 1], aq, bk[2], bk[3], fmt);
+                        attb_mma(dp[np * 2 + 1], ad, bv[2], bv[3], fmt);
+                    }
+                }
             }
         }
-    };
-    auto dot_row = [&](const unsigned short* base, int row, const float (&r)[DH]) {
-        float s = 0.0f;
+        // softmax rows g, g + 8
+        float mx[2] = {-CUDART_INF_F, -CUDART_INF_F}, den[2] = {0.0f, 0.0f}, D[2] = {0.0f, 0.0f};
 #pragma unroll
-        for (int v = 0; v < VPR; ++v) {
-            const uint4 w = *reinterpret_cast<const uint4*>(base + row * LDS + v * 8);
-            const uint32_t wd[4] = {w.x, w.y, w.z, w.w};
+        for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                const float2 f = unpack16(wd[e], fmt);
-                s = fmaf(r[v * 8 + 2 * e], f.x, s);
-                s = fmaf(r[v * 8 + 2 * e + 1], f.y, s);
+                const int col = nt * 8 + t4 * 2 + (e & 1);
+                sc[nt][e] = col < N ? sc[nt][e] * scale_log2e : -CUDART_INF_F;
+                mx[e >> 1] = fmaxf(mx[e >> 1], sc[nt][e]);
             }
-        }
-        return s;
-    };
-    auto axpy_row = [&](const unsigned short* base, int row, float a, float (&r)[DH]) {
 #pragma unroll
-        for (int v = 0; v < VPR; ++v) {
-            const uint4 w = *reinterpret_cast<const uint4*>(base + row * LDS + v * 8);
-            const uint32_t wd[4] = {w.x, w.y, w.z, w.w};
+        for (int h = 0; h < 2; ++h) {
+            mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 1));
+            mx[h] = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 2));
+        }
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                const float2 f = unpack16(wd[e], fmt);
-                r[v * 8 + 2 * e] = fmaf(a, f.x, r[v * 8 + 2 * e]);
-                r[v * 8 + 2 * e + 1] = fmaf(a, f.y, r[v * 8 + 2 * e + 1]);
+                sc[nt][e] = exp2f(sc[nt][e] - mx[e >> 1]);
+                den[e >> 1] += sc[nt][e];
+            }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            den[h] += __shfl_xor_sync(0xffffffffu, den[h], 1);
+            den[h] += __shfl_xor_sync(0xffffffffu, den[h], 2);
+            den[h] = (mt * 16 + g + h * 8 < N) ? 1.0f / den[h] : 0.0f;          // query rows past the token count: P = 0
+        }
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                sc[nt][e] *= den[e >> 1];                                         // P
+                D[e >> 1] = fmaf(sc[nt][e], dp[nt][e], D[e >> 1]);
+            }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            D[h] += __shfl_xor_sync(0xffffffffu, D[h], 1);
+            D[h] += __shfl_xor_sync(0xffffffffu, D[h], 2);
+        }
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) dp[nt][e] = sc[nt][e] * (dp[nt][e] - D[e >> 1]) * scale;      // dS
+            const int col = nt * 8 + t4 * 2;
+            *reinterpret_cast<uint32_t*>(sP + (mt * 16 + g) * ATTB_LDP + col) = pack16(sc[nt][0], sc[nt][1], fmt);
+            *reinterpret_cast<uint32_t*>(sP + (mt * 16 + g + 8) * ATTB_LDP + col) = pack16(sc[nt][2], sc[nt][3], fmt);
+            *reinterpret_cast<uint32_t*>(sS + (mt * 16 + g) * ATTB_LDP + col) = pack16(dp[nt][0], dp[nt][1], fmt);
+            *reinterpret_cast<uint32_t*>(sS + (mt * 16 + g + 8) * ATTB_LDP + col) = pack16(dp[nt][2], dp[nt][3], fmt);
+        }
+        // dq = dS k
+        float oc[DH / 8][4];
+#pragma unroll
+        for (int dn = 0; dn < DH / 8; ++dn)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) oc[dn][e] = 0.0f;
+#pragma unroll
+        for (int kt = 0; kt < 2; ++kt) {
+            if (kt * 2 < NT) {
+                uint32_t pa[4];
+                pa[0] = pack16(dp[kt * 2][0], dp[kt * 2][1], fmt);
+                pa[1] = pack16(dp[kt * 2][2], dp[kt * 2][3], fmt);
+                pa[2] = pack16(dp[kt * 2 + 1][0], dp[kt * 2 + 1][1], fmt);
+                pa[3] = pack16(dp[kt * 2 + 1][2], dp[kt * 2 + 1][3], fmt);
+#pragma unroll
+                for (int dq = 0; dq < DH / 16; ++dq) {
+                    uint32_t bk[4];
+                    attb_ldsm_x4_trans(bk, k_addr + (min(kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, N) * LDS + dq * 16 + (lane >> 4) * 8) * 2);
+                    attb_mma(oc[dq * 2], pa, bk[0], bk[1], fmt);
+                    attb_mma(oc[dq * 2 + 1], pa, bk[2], bk[3], fmt);
+                }
             }
         }
-    };
-    auto store_row = [&](int slice, int row, const float (&r)[DH]) {
-        uint4* dst = reinterpret_cast<uint4*>(static_cast<unsigned short*>(dqkv) + (pose * N + row) * (3L * Hd) + slice * Hd + head * DH);
-#pragma unroll
-        for (int v = 0; v < VPR; ++v)
-            dst[v] = make_uint4(pack16(r[v * 8], r[v * 8 + 1], fmt), pack16(r[v * 8 + 2], r[v * 8 + 3], fmt),
-                                pack16(r[v * 8 + 4], r[v * 8 + 5], fmt), pack16(r[v * 8 + 6], r[v * 8 + 7], fmt));
-    };
-    float acc[DH];
-    if (lane < N) {
-        const int i = lane;
-        load_row(sq, i, acc, scale * 1.4426950408889634f);               // q_i / sqrt(d) in log2 units
-        float mx = -CUDART_INF_F;
-        for (int j = 0; j < N; ++j) {
-            const float s = dot_row(sk, j, acc);
-            sP[i * 33 + j] = s;
-            mx = fmaxf(mx, s);
-        }
-        float den = 0.0f;
-        for (int j = 0; j < N; ++j) {
-            const float p = exp2f(sP[i * 33 + j] - mx);
-            sP[i * 33 + j] = p;
-            den += p;
-        }
-        const float inv = 1.0f / den;
-        load_row(sdo, i, acc, 1.0f);                                      // dO_i
-        float Di = 0.0f;
-        for (int j = 0; j < N; ++j) {
-            const float p = sP[i * 33 + j] * inv;
-            const float dp = dot_row(sv, j, acc);                         // dP_ij = dO_i . v_j
-            sP[i * 33 + j] = p;
-            sS[i * 33 + j] = dp;
-            Di = fmaf(dp, p, Di);
-        }
-#pragma unroll
-        for (int d = 0; d < DH; ++d) acc[d] = 0.0f;
-        for (int j = 0; j < N; ++j) {
-            const float ds = sP[i * 33 + j] * (sS[i * 33 + j] - Di) * scale;     // d S_ij (with the 1 / sqrt d of the forward)
-            sS[i * 33 + j] = ds;
-            axpy_row(sk, j, ds, acc);                                     // dq_i += dS_ij k_j
-        }
-        store_row(0, i, acc);
+        store_frags(0, mt * 16, oc);
     }
     __syncwarp();
-    if (lane < N) {
-        const int j = lane;
+    // dk = dS^T q, dv = P^T dO: key rows jt * 16 .. + 15, contraction over the queries
+    for (int jt = 0; jt < MT; ++jt) {
 #pragma unroll
-        for (int d = 0; d < DH; ++d) acc[d] = 0.0f;
-        for (int i = 0; i < N; ++i) axpy_row(sq, i, sS[i * 33 + j], acc);     // dk_j = sum_i dS_ij q_i
-        store_row(1, j, acc);
+        for (int which = 0; which < 2; ++which) {
+            const uint32_t a_base = which == 0 ? s_addr : p_addr;
+            const uint32_t b_base = which == 0 ? q_addr : do_addr;
+            float oc[DH / 8][4];
 #pragma unroll
-        for (int d = 0; d < DH; ++d) acc[d] = 0.0f;
-        for (int i = 0; i < N; ++i) axpy_row(sdo, i, sP[i * 33 + j], acc);    // dv_j = sum_i P_ij dO_i
-        store_row(2, j, acc);
+            for (int dn = 0; dn < DH / 8; ++dn)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) oc[dn][e] = 0.0f;
+            for (int it = 0; it < MT; ++it) {                                   // queries it * 16 .. + 15
+                uint32_t a[4];                                                   // A = (tile stored [query][key])^T
+                attb_ldsm_x4_trans(a, a_base + ((it * 16 + (lane & 7) + ((lane >> 4) & 1) * 8) * ATTB_LDP + jt * 16 + ((lane >> 3) & 1) * 8) * 2);
+#pragma unroll
+                for (int dq = 0; dq < DH / 16; ++dq) {
+                    uint32_t b[4];
+                    attb_ldsm_x4_trans(b, b_base + (min(it * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, N) * LDS + dq * 16 + (lane >> 4) * 8) * 2);
+                    attb_mma(oc[dq * 2], a, b[0], b[1], fmt);
+                    attb_mma(oc[dq * 2 + 1], a, b[2], b[3], fmt);
+                }
+            }
+            store_frags(which == 0 ? 1 : 2, jt * 16, oc);
+        }
     }
 }
 
 size_t attb_smem_bytes(int tokens, int dh) {
-    return static_cast<size_t>(ATTB_WARPS) * ((static_cast<size_t>(4) * tokens * (dh + 8) * 2 + static_cast<size_t>(2) * tokens * 33 * 4 + 15) / 16 * 16);
+    return static_cast<size_t>(ATTB_WARPS) * (static_cast<size_t>(4) * (tokens + 1) * (dh + 8) * 2 + static_cast<size_t>(2) * 32 * ATTB_LDP * 2);
 }
 
 }  // namespace
