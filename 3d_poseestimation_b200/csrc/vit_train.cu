@@ -199,10 +199,39 @@ __global__ void __launch_bounds__(256) vit_ln_bwd_kernel(const void* __restrict_
     for (int v = 0; v < NV; ++v)
 #pragma unroll
         for (int e = 0; e < 8; ++e) dg1[v][e] = db1[v][e] = dg2[v][e] = db2[v][e] = 0.0f;
+    // raw rows of the NEXT iteration are in flight while this one is processed (the kernel is latency-bound otherwise)
+    auto load_raw = [&](const void* base, long row, uint4 (&r)[NV]) {
+        const uint4* src = reinterpret_cast<const uint4*>(static_cast<const unsigned short*>(base) + row * Hd);
+#pragma unroll
+        for (int v = 0; v < NV; ++v) r[v] = src[v * 32 + lane];
+    };
+    auto unpack_raw = [&](const uint4 (&r)[NV], float (&f)[NV][8]) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            const uint32_t wd[4] = {r[v].x, r[v].y, r[v].z, r[v].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 p = unpack16(wd[e], fmt);
+                f[v][2 * e] = p.x;
+                f[v][2 * e + 1] = p.y;
+            }
+        }
+    };
+    uint4 cx[NV], cd[NV], cr[NV], nx[NV], nd[NV], nr[NV];
+    if (t0 < t1) {
+        load_raw(x, t0, cx);
+        load_raw(dy_in, t0, cd);
+        if (dres != nullptr) load_raw(dres, t0, cr);
+    }
     for (long t = t0; t < t1; ++t) {
+        if (t + 1 < t1) {
+            load_raw(x, t + 1, nx);
+            load_raw(dy_in, t + 1, nd);
+            if (dres != nullptr) load_raw(dres, t + 1, nr);
+        }
         float xh1[NV][8], d[NV][8];
-        load_row16<NV>(x, t, lane, xh1, fmt);
-        load_row16<NV>(dy_in, t, lane, d, fmt);
+        unpack_raw(cx, xh1);
+        unpack_raw(cd, d);
         float mean, rstd1;
         ln_stats<NV>(xh1, mean, rstd1, eps);
 #pragma unroll
@@ -226,13 +255,15 @@ __global__ void __launch_bounds__(256) vit_ln_bwd_kernel(const void* __restrict_
         ln_bwd_row<NV>(d, xh1, p1.g, rstd1, dg1, db1);
         if (dres != nullptr) {
             float r[NV][8];
-            load_row16<NV>(dres, t, lane, r, fmt);
+            unpack_raw(cr, r);
 #pragma unroll
             for (int v = 0; v < NV; ++v)
 #pragma unroll
                 for (int e = 0; e < 8; ++e) d[v][e] += r[v][e];
         }
         store_row16<NV>(dx_out, t, lane, d, fmt);
+#pragma unroll
+        for (int v = 0; v < NV; ++v) { cx[v] = nx[v]; cd[v] = nd[v]; cr[v] = nr[v]; }
     }
     float* dst = part + static_cast<long>(blockIdx.x) * 4 * Hd;
     block_colsum_store<NV>(dg1, sh, dst);
