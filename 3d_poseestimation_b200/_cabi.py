@@ -137,7 +137,7 @@ SIGNATURES = {
     "lifter_vit_saved_bytes": (_I64, [C.POINTER(VitDesc), _I64]),
     "lifter_vit_bwd_scratch_bytes": (_I64, [C.POINTER(VitDesc), _I64]),
     "lifter_vit_train_forward": (_I32, [C.POINTER(VitDesc), _P, _I64, _P, _P, _P]),
-    "lifter_vit_backward": (_I32, [C.POINTER(VitDesc), _P, _I64, _P, _P, _P, C.POINTER(VitGrads), _P]),
+    "lifter_vit_backward": (_I32, [C.POINTER(VitDesc), _P, _I64, _P, _P, _P, C.POINTER(VitGrads), _P, _P]),
     "lifter_gemm": (_I32, [C.POINTER(GemmDesc), _P]),
     "lifter_trace_begin": (_I32, [_P]),
     "lifter_trace_end": (_I32, [C.c_char_p, _I32]),

@@ -51,8 +51,8 @@ int64_t vit_saved_bytes(const VitDesc& d, int64_t poses);
 int64_t vit_bwd_scratch_bytes(const VitDesc& d, int64_t poses);
 // forward that keeps every GEMM input in `saved`; out [poses][tokens][out_dim] fp32
 int vit_train_forward(const VitDesc& d, const float* x, int64_t poses, void* saved, float* out, cudaStream_t st);
-// dout [poses][tokens][out_dim] fp32 -> gradients of every parameter
+// dout [poses][tokens][out_dim] fp32 -> gradients of every parameter, and (dx non-null) of the key points [poses][tokens][in_dim]
 int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* saved, const float* dout, void* scratch,
-                 const VitGrads& G, cudaStream_t st);
+                 const VitGrads& G, float* dx, cudaStream_t st);
 
 }  // namespace lifter

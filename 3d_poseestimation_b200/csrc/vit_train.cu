@@ -275,7 +275,8 @@ __global__ void __launch_bounds__(256) vit_ln_bwd_kernel(const void* __restrict_
 // d linear_mapper: part [gridDim.x][1 + in_d][Hd]: block partials of sum_t dh[t][c] (bias) and sum_t dh[t][c] x[t][i]
 template <int NV>
 __global__ void __launch_bounds__(256) vit_embed_bwd_kernel(const void* __restrict__ dh, const float* __restrict__ x, long T,
-                                                            int in_d, float* __restrict__ part, int fmt) {
+                                                            int in_d, float* __restrict__ part, const float* __restrict__ w,
+                                                            float* __restrict__ dx, int fmt) {
     griddep_launch();
     griddep_wait();
     __shared__ float sh[8 * NV * 256];
@@ -304,6 +305,17 @@ __global__ void __launch_bounds__(256) vit_embed_bwd_kernel(const void* __restri
 #pragma unroll
                 for (int i = 0; i < 4; ++i) acc[1 + i][v][e] = fmaf(d[v][e], xi[i], acc[1 + i][v][e]);
             }
+        if (dx != nullptr) {                                          // d loss / d key points: dx[t][i] = sum_c dh[t][c] W[c][i]
+            for (int i = 0; i < in_d; ++i) {
+                float sx = 0.0f;
+#pragma unroll
+                for (int v = 0; v < NV; ++v)
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) sx = fmaf(d[v][e], w[(v * 256 + lane * 8 + e) * in_d + i], sx);
+                sx = wsum(sx);
+                if (lane == 0) dx[t * in_d + i] = sx;
+            }
+        }
     }
     float* dst = part + static_cast<long>(blockIdx.x) * (1 + in_d) * Hd;
 #pragma unroll
@@ -711,7 +723,7 @@ int vit_train_forward(const VitDesc& d, const float* x, int64_t poses, void* sav
 }
 
 int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* saved, const float* dout, void* scratch,
-                 const VitGrads& G, cudaStream_t st) {
+                 const VitGrads& G, float* dx, cudaStream_t st) {
     LIFTER_PROPAGATE(validate_train(d));
     LIFTER_REQUIRE(poses >= 1, "vit_backward: empty batch");
     LIFTER_REQUIRE(x && saved && dout && scratch, "vit_backward: null pointer");
@@ -780,7 +792,7 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
     }
     // ---- embedding: d linear_mapper (positional table has requires_grad = False, baselineModel.py:330) -------------------------------
     VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_bwd_kernel", vit_embed_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
-                                                     static_cast<const void*>(B.dhA), x, T, d.in_dim, B.part, fmt)));
+                                                     static_cast<const void*>(B.dhA), x, T, d.in_dim, B.part, d.map_w, dx, fmt)));
     return reduce_rows_f32(B.part, static_cast<int>(row_blocks), (1 + d.in_dim) * H, (1 + d.in_dim) * H, G.map, st);
 }
 
@@ -809,12 +821,12 @@ int lifter_vit_train_forward(const lifter_vit_t* vit, const float* x, int64_t po
 }
 
 int lifter_vit_backward(const lifter_vit_t* vit, const float* x, int64_t poses, const void* saved, const float* dout, void* scratch,
-                        const lifter_vit_grads_t* g, void* stream) {
+                        const lifter_vit_grads_t* g, float* dx, void* stream) {
     LIFTER_REQUIRE(vit != nullptr && g != nullptr, "vit_backward: null descriptor");
     lifter::VitGrads G;
     G.map = g->map; G.ln = g->ln; G.w_qkv = g->w_qkv; G.w_out = g->w_out; G.w_mlp1 = g->w_mlp1; G.mlp_b1 = g->mlp_b1;
     G.w_mlp2 = g->w_mlp2; G.mlp_b2 = g->mlp_b2; G.w_head1 = g->w_head1; G.head_b1 = g->head_b1; G.w_head2 = g->w_head2; G.head_b2 = g->head_b2;
-    return lifter::vit_backward(lifter_vit_to_desc(vit), x, poses, saved, dout, scratch, G, static_cast<cudaStream_t>(stream));
+    return lifter::vit_backward(lifter_vit_to_desc(vit), x, poses, saved, dout, scratch, G, dx, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

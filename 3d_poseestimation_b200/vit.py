@@ -10,8 +10,9 @@ Without autograd (``torch.no_grad()``, the inference and validation call sites `
 kernels; fp16 operands).  With autograd enabled it goes through ``_VitFunction``: ``lifter_vit_train_forward`` keeps every GEMM
 input and ``lifter_vit_backward`` fills ``.grad`` of every trainable parameter (bf16 operands), so the loop body
 ``train_1.py:73-100`` -- ``loss.backward(); optimizer_lift.step()`` with a ``torch.optim`` optimiser -- runs unchanged.  The
-model has no dropout and no BatchNorm, so train and eval mode compute the same function.  Not built: the gradient with
-respect to the input key points (raises).  No PyTorch or CPU fallback anywhere.
+model has no dropout and no BatchNorm, so train and eval mode compute the same function.  The gradient with respect to the
+input key points is returned too (the phase-5 loop feeds the lifter from a 2D model, train_5.py:58,63).  No PyTorch or CPU
+fallback anywhere.
 """
 from __future__ import annotations
 
@@ -49,7 +50,7 @@ class _VitFunction(torch.autograd.Function):
             raise RuntimeError("MyViT: parameters and input live on different devices")
         B = int(x.shape[0])
         out = torch.empty((B, model.chw[1], model.out_d), dtype=torch.float32, device=dev)
-        ctx.model, ctx.names, ctx.B = model, names, B
+        ctx.model, ctx.names, ctx.B, ctx.want_dx, ctx.in_shape = model, names, B, images.requires_grad, tuple(images.shape)
         if B == 0:
             return out
         d = model._pack(dev, model.train_format)
@@ -81,8 +82,11 @@ class _VitFunction(torch.autograd.Function):
                 raise ValueError("MyViT: " + _cabi.last_error())
             scratch = torch.empty(need, dtype=torch.uint8, device=dev)
             dout = dout.detach().to(torch.float32).contiguous()
+            dx = torch.empty(ctx.in_shape, dtype=torch.float32, device=dev) if ctx.want_dx else None
             _cabi.check(lib.lifter_vit_backward(C.byref(ctx.desc), _cabi.ptr(ctx.x), B, _cabi.ptr(ctx.saved), _cabi.ptr(dout),
-                                                _cabi.ptr(scratch), C.byref(G), _cabi.stream_ptr()))
+                                                _cabi.ptr(scratch), C.byref(G), _cabi.ptr(dx), _cabi.stream_ptr()))
+        else:
+            dx = torch.zeros(ctx.in_shape, dtype=torch.float32, device=dev) if ctx.want_dx else None
         by_name = {"linear_mapper.weight": g["map"][1:].t(), "linear_mapper.bias": g["map"][0], "pos_embed": None,
                    "mlp.0.weight": g["w_head1"], "mlp.0.bias": g["head_b1"], "mlp.2.weight": g["w_head2"], "mlp.2.bias": g["head_b2"]}
         for b in range(nb):
@@ -93,7 +97,7 @@ class _VitFunction(torch.autograd.Function):
                             p + "mlp.0.weight": g["w_mlp1"][b], p + "mlp.0.bias": g["mlp_b1"][b],
                             p + "mlp.2.weight": g["w_mlp2"][b], p + "mlp.2.bias": g["mlp_b2"][b]})
         grads = tuple(by_name[n] for n in ctx.names)
-        return (None, None, None) + grads
+        return (None, None, dx) + grads
 
 
 class Attention(torch.nn.Module):
@@ -215,9 +219,7 @@ class MyViT(torch.nn.Module):
             raise RuntimeError("MyViT: the sm_100a build has no CPU path; move the model and the input to a B200")
         if images.dim() != 3 or images.shape[1] != self.chw[1] or images.shape[2] != self.input_d:
             raise ValueError(f"MyViT expects (B, {self.chw[1]}, {self.input_d}) key points, got {tuple(images.shape)}")
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            if images.requires_grad:
-                raise NotImplementedError("MyViT (sm_100a build): the gradient with respect to the key points is not built")
+        if torch.is_grad_enabled() and (images.requires_grad or any(p.requires_grad for p in self.parameters())):
             names, params = zip(*self.named_parameters())
             return _VitFunction.apply(self, names, images, *params)
         return self.infer(images)

@@ -289,7 +289,7 @@ int lifter_vit_forward(const lifter_vit_t* vit, const float* x, int64_t poses, v
 /* ---- MyViT lifter, training path (loss.backward() through baselineModel.py:228-362; loop body train_1.py:73-100 with
  * model_lift = MyViT).  No dropout and no BatchNorm in this model: lifter_vit_train_forward is the eval arithmetic that
  * keeps every GEMM input in `saved` (lifter_vit_saved_bytes); lifter_vit_backward turns d loss / d out into the gradient
- * of every trainable parameter (the positional table has requires_grad = False, baselineModel.py:330).  vit->fmt is the
+ * of every trainable parameter (the positional table has requires_grad = False, baselineModel.py:330) and of the input.  vit->fmt is the
  * operand format of forward AND backward (bf16 for the gradient range).  hidden 256 or 512.                       */
 typedef struct lifter_vit_grads {            /* fp32, stacked per block exactly like the parameters of lifter_vit_t   */
     float* map;                              /* [1 + in_dim][hidden]: d linear_mapper.bias, then d weight[:, i] per i  */
@@ -302,8 +302,9 @@ typedef struct lifter_vit_grads {            /* fp32, stacked per block exactly 
 int64_t lifter_vit_saved_bytes(const lifter_vit_t* vit, int64_t poses);
 int64_t lifter_vit_bwd_scratch_bytes(const lifter_vit_t* vit, int64_t poses);
 int lifter_vit_train_forward(const lifter_vit_t* vit, const float* x, int64_t poses, void* saved, float* out, void* stream);
+/* dx: nullable, [poses][tokens][in_dim] fp32 = d loss / d key points (the phase-5 loop feeds the lifter from a 2D model) */
 int lifter_vit_backward(const lifter_vit_t* vit, const float* x, int64_t poses, const void* saved, const float* dout,
-                        void* scratch, const lifter_vit_grads_t* grads, void* stream);
+                        void* scratch, const lifter_vit_grads_t* grads, float* dx, void* stream);
 
 /* ---- test hook: one tcgen05 GEMM  D[M][N] = sum_k A(m,k) B(n,k) ------------------------------------ */
 typedef struct lifter_gemm_desc {

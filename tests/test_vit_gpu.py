@@ -110,8 +110,8 @@ def test_vit_chunking_weight_updates_and_formats(pkg):
 
 def test_vit_unsupported_calls_raise(pkg):
     m = pkg.MyViT().cuda()
-    with pytest.raises(NotImplementedError):
-        m(torch.randn(4, 17, 2, device="cuda", requires_grad=True))          # gradient w.r.t. the key points: not built
+    with pytest.raises(RuntimeError):
+        m(torch.randn(4, 17, 2))                                             # CPU tensor: no fallback
     with pytest.raises(ValueError):
         m.eval()(torch.randn(4, 16, 2, device="cuda"))
 
@@ -147,9 +147,12 @@ def test_evaluate_drives_the_transformer_lifter(pkg, golden_dir, flip):
 # ---------------------------------------------------------------------------------------------------- training path
 def _oracle_grads(params, x, y, **cfg):
     p = {k: v.clone().requires_grad_(k != "pos_embed") for k, v in params.items()}
-    loss = torch.nn.functional.mse_loss(V.vit_forward(p, x, **cfg), y)
+    xr = x.clone().requires_grad_(True)
+    loss = torch.nn.functional.mse_loss(V.vit_forward(p, xr, **cfg), y)
     loss.backward()
-    return float(loss.detach()), {k: v.grad for k, v in p.items() if k != "pos_embed"}
+    g = {k: v.grad for k, v in p.items() if k != "pos_embed"}
+    g["__x__"] = xr.grad
+    return float(loss.detach()), g
 
 
 def _check_grads(m, ref, rel_tol=3e-2):
@@ -194,9 +197,15 @@ def test_vit_backward_other_shapes(pkg, joints, in_d, hidden, heads, blocks, out
     m = m.cuda().train()
     x = torch.randn(B, joints, in_d, generator=torch.Generator().manual_seed(B))
     y = torch.randn(B, joints, out_d, generator=torch.Generator().manual_seed(B + 1))
-    torch.nn.functional.mse_loss(m(x.cuda()), y.cuda()).backward()
+    xg = x.cuda().requires_grad_(True)          # the phase-5 loop feeds the lifter from a 2D model: gradient w.r.t. the key points
+    torch.nn.functional.mse_loss(m(xg), y.cuda()).backward()
     _, ref = _oracle_grads(params, x, y, n_blocks=blocks, n_heads=heads)
     _check_grads(m, ref)
+    assert tuple(xg.grad.shape) == tuple(x.shape)
+    cos = torch.nn.functional.cosine_similarity(xg.grad.cpu().reshape(-1), ref["__x__"].reshape(-1), dim=0).item()
+    # dx = dh0 W_map projects 256-512 bf16-stored gradient columns onto 2-4 inputs with heavy cancellation: the 4e-3 storage
+    # rounding of dh0 shows as several percent here (measured 6e-2), against ~1e-2 on the parameter gradients
+    assert rel_l2(xg.grad.cpu(), ref["__x__"]) < 0.3 and cos > 0.95, (rel_l2(xg.grad.cpu(), ref["__x__"]), cos)
 
 
 def test_vit_training_loop_follows_the_oracle_curve(pkg):
