@@ -44,6 +44,7 @@ def _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offse
     return t
 
 
+@_cabi.device_guard
 def run_forward(model, x, training, saved=None, out=None, step=None, step_state=None):
     """Forward with saved activations.  Returns (out, saved, ctx_struct)."""
     lib, cfg = _cabi.lib(), C.byref(model._cfg)
@@ -80,6 +81,7 @@ def run_forward(model, x, training, saved=None, out=None, step=None, step_state=
     return out, saved, t
 
 
+@_cabi.device_guard
 def run_backward(model, t, grad_out, grad_flat, grad_x, scratch=None, optim=None):
     """Backward of the pair described by ``t``; writes ``grad_flat`` (parameter layout) and ``grad_x``.
     ``optim`` (``_cabi.Optim``): fold the optimiser into the backward pass (``lifter_train_backward_step``)."""

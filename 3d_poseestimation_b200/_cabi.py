@@ -6,6 +6,7 @@ without a B200, this module raises.
 from __future__ import annotations
 
 import ctypes as C
+import functools
 import os
 
 from . import build as _build
@@ -93,6 +94,8 @@ SIGNATURES = {
     "lifter_version": (_I32, []),
     "lifter_last_error": (C.c_char_p, []),
     "lifter_device_check": (_I32, []),
+    "lifter_source_digest": (C.c_char_p, []),
+    "lifter_launch_count": (C.c_longlong, []),
     "lifter_num_param_tensors": (_I32, [_CFG]),
     "lifter_param_offset": (_I64, [_CFG, _I32]),
     "lifter_param_numel": (_I64, [_CFG, _I32]),
@@ -185,5 +188,51 @@ def ptr(t):
 
 
 def stream_ptr():
+    """The current stream of the CURRENT device (entry points run under ``device_guard``, which makes the device of
+    their tensors current first)."""
     import torch
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _cuda_device_of(obj, depth=0):
+    import torch
+    if torch.is_tensor(obj):
+        return obj.device if obj.is_cuda else None
+    flat = getattr(obj, "_flat", None)                       # LinearModel
+    if torch.is_tensor(flat):
+        return flat.device if flat.is_cuda else None
+    if depth == 0:
+        model = getattr(obj, "model", None)                  # trainers
+        if model is not None:
+            return _cuda_device_of(model, 1)
+        if isinstance(obj, torch.nn.Module):                 # MyViT and friends: device of the first parameter
+            for p in obj.parameters():
+                return p.device if p.is_cuda else None
+        if isinstance(obj, (list, tuple)) and obj:
+            return _cuda_device_of(obj[0], 1)
+    return None
+
+
+def device_guard(fn):
+    """Every kernel launch, ``cudaGetDevice`` (SM count, side streams) and ``current_stream`` of the library refers to the
+    CURRENT CUDA device.  This decorator makes the device of the call's first CUDA tensor / model current for the
+    duration of the call, so a model on ``cuda:1`` works while ``cuda:0`` is current (it used to launch on GPU 0 with
+    GPU-1 pointers)."""
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        import torch
+        dev = None
+        for a in args:
+            dev = _cuda_device_of(a)
+            if dev is not None:
+                break
+        if dev is None:
+            for a in kwargs.values():
+                dev = _cuda_device_of(a)
+                if dev is not None:
+                    break
+        if dev is None or dev.index is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(dev):
+            return fn(*args, **kwargs)
+    return wrapper

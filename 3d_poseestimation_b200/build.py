@@ -1,8 +1,16 @@
-"""Builds the sm_100a C-ABI library ``_lib/liblifter_b200.so`` from ``csrc/*.cu`` with nvcc (in-tree)."""
+"""Builds the sm_100a C-ABI library ``_lib/liblifter_b200.so`` from ``csrc/*.cu`` with nvcc (in-tree).
+
+Staleness is decided from the BINARY: the build passes the sha256 of its sources to the compiler, which stores it in the
+library as ``LIFTER_SRC_DIGEST=<hex>`` (``lifter_source_digest()``); ``is_stale()`` scans the file for that marker, so a
+library left over from another checkout is never loaded, whatever side files say.  Concurrent builders (N torchrun ranks
+on a fresh checkout) serialise on a file lock and compile into per-process temporaries.
+"""
 from __future__ import annotations
 
+import fcntl
 import hashlib
 import os
+import re
 import shutil
 import subprocess
 import sys
@@ -13,6 +21,7 @@ LIBDIR = os.path.join(HERE, "_lib")
 LIBNAME = "liblifter_b200.so"
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
+_MARKER = re.compile(rb"LIFTER_SRC_DIGEST=([0-9a-f]{64})")
 
 
 def lib_path():
@@ -36,11 +45,18 @@ def source_digest():
     return h.hexdigest()
 
 
+def built_digest(path=None):
+    """The source digest recorded INSIDE the library file (None: no library, or one that predates the marker)."""
+    path = path or lib_path()
+    if not os.path.exists(path):
+        return None
+    with open(path, "rb") as f:
+        m = _MARKER.search(f.read())
+    return m.group(1).decode() if m else None
+
+
 def is_stale():
-    stamp = lib_path() + ".sha256"
-    if not (os.path.exists(lib_path()) and os.path.exists(stamp)):
-        return True
-    return open(stamp).read().strip() != source_digest()
+    return built_digest() != source_digest()
 
 
 def build(force=False, verbose=False):
@@ -51,17 +67,27 @@ def build(force=False, verbose=False):
     if not os.path.exists(nvcc):
         raise RuntimeError("nvcc not found: cannot build the sm_100a lifter library")
     os.makedirs(LIBDIR, exist_ok=True)
-    srcs, _ = _sources()
-    tmp = lib_path() + ".tmp"
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", tmp] + srcs
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
-    if verbose:
-        print(r.stderr)
-    os.replace(tmp, lib_path())
-    with open(lib_path() + ".sha256", "w") as f:
-        f.write(source_digest())
+    with open(os.path.join(LIBDIR, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)                     # one builder at a time; the others find a fresh library
+        try:
+            if not force and not is_stale():
+                return lib_path()
+            digest = source_digest()
+            srcs, _ = _sources()
+            tmp = f"{lib_path()}.{os.getpid()}.tmp"
+            jobs = str(min(len(srcs), os.cpu_count() or 1))
+            cmd = [nvcc] + NVCC_FLAGS + ["--threads", jobs, f"-DLIFTER_SOURCE_DIGEST=\"{digest}\""] + \
+                  (["-Xptxas", "-v"] if verbose else []) + ["-o", tmp] + srcs
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            if r.returncode != 0:
+                if os.path.exists(tmp):
+                    os.remove(tmp)
+                raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+            if verbose:
+                print(r.stderr)
+            os.replace(tmp, lib_path())
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return lib_path()
 
 

@@ -3,6 +3,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -47,7 +48,26 @@ std::vector<TraceRec> g_trace;
 bool g_trace_on = false;
 }  // namespace
 
+static std::atomic<long long> g_launches{0};
+long long launch_count() { return g_launches.load(); }
+
+// Peer waits of the data-parallel kernels (SyncBN exchange, optimiser flag barriers) give up after this many SM clocks
+// and trap -- a peer that died must not hang the box for good -- but a healthy peer may be late by whole seconds
+// (checkpoint on rank 0, a DataLoader respawn).  LIFTER_DP_TIMEOUT_S: seconds (default 300, like a collective
+// watchdog; 0 = wait forever).
+long long dp_spin_limit_clocks() {
+    static long long cached = -2;
+    if (cached == -2) {
+        double s = 300.0;
+        const char* e = getenv("LIFTER_DP_TIMEOUT_S");
+        if (e != nullptr && e[0] != 0) s = atof(e);
+        cached = s <= 0.0 ? 0 : static_cast<long long>(s * 2.0e9);
+    }
+    return cached;
+}
+
 void trace_mark(const char* name, cudaStream_t st) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);     // every launch of the library passes through here
     if (!g_trace_on) return;
     TraceRec r;
     r.name = name;

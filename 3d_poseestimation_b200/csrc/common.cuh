@@ -50,6 +50,8 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 
 int num_sms();   // cached SM count of the current device
 bool pdl_enabled();   // programmatic dependent launch on every kernel (LIFTER_NO_PDL=1 turns it off)
+long long launch_count();           // kernel launches issued by this library so far (captured launches count once)
+long long dp_spin_limit_clocks();   // give-up time of the cross-GPU waits in SM clocks (0 = never); LIFTER_DP_TIMEOUT_S
 
 // 16-bit operand formats (UMMA a_format/b_format values for kind::f16)
 enum : int { FMT_F16 = 0, FMT_BF16 = 1 };

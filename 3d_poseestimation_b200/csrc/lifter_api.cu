@@ -35,7 +35,17 @@ static int64_t eval_ws_bytes(const Layout& lay, int64_t chunk) {
 
 extern "C" {
 
-int lifter_version(void) { return 1; }
+int lifter_version(void) { return 2; }
+
+// digest of the sources this binary was compiled from (build.py passes it in; the marker lets the loader find it in the
+// file without dlopen, so a stale binary is never mapped)
+#ifndef LIFTER_SOURCE_DIGEST
+#define LIFTER_SOURCE_DIGEST "unknown"
+#endif
+extern const char lifter_source_digest_marker[] = "LIFTER_SRC_DIGEST=" LIFTER_SOURCE_DIGEST;
+const char* lifter_source_digest(void) { return lifter_source_digest_marker + 18; }
+
+long long lifter_launch_count(void) { return launch_count(); }
 
 const char* lifter_last_error(void) { return get_error(); }
 

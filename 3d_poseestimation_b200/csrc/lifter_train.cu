@@ -91,6 +91,7 @@ int fill_exchange(const Layout& lay, const lifter_train_ctx_t* t, int site, Sync
         ex->data[p] = d->sync[p];
     }
     ex->epoch = reinterpret_cast<const unsigned*>(t->step_state) + 1;      // lifter_step_state_t.adam_step
+    ex->spin_limit = dp_spin_limit_clocks();
     return LIFTER_OK;
 }
 

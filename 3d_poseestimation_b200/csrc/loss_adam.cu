@@ -220,14 +220,14 @@ __device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void wait_epoch(const unsigned* f, unsigned epoch) {
+__device__ __forceinline__ void wait_epoch(const unsigned* f, unsigned epoch, long long spin_limit) {
     long long t0 = 0;
     unsigned spins = 0;
-    while (static_cast<int>(ld_acquire_sys_u32(f) - epoch) < 0) {         // a lost peer traps after ~4 s, no hang
-        if ((++spins & 0xFF) == 0) {
+    while (static_cast<int>(ld_acquire_sys_u32(f) - epoch) < 0) {         // a DEAD peer traps after LIFTER_DP_TIMEOUT_S
+        if ((++spins & 0xFF) == 0 && spin_limit > 0) {
             const long long now = clock64();
             if (t0 == 0) t0 = now;
-            else if (now - t0 > 8000000000LL) __trap();
+            else if (now - t0 > spin_limit) __trap();
         }
     }
 }
@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
     // ---- barrier 1: every rank's gradient is complete (my predecessor kernels finished: this kernel runs)
     if (threadIdx.x < d.world) {
         if (blockIdx.x == 0) st_release_sys_u32(d.flag_peer[threadIdx.x] + d.rank, epoch);
-        wait_epoch(my_flags + threadIdx.x, epoch);
+        wait_epoch(my_flags + threadIdx.x, epoch, d.spin_limit);
     }
     __syncthreads();
     // ---- my slice: sum of the gradients in rank order, Adam, parameters to every rank
@@ -328,7 +328,7 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
         if (threadIdx.x == 0) *counter = 0;                                // ready for the next step
         if (threadIdx.x < d.world) {
             st_release_sys_u32(d.flag_peer[threadIdx.x] + d.world + d.rank, epoch);
-            wait_epoch(my_flags + d.world + threadIdx.x, epoch);
+            wait_epoch(my_flags + d.world + threadIdx.x, epoch, d.spin_limit);
         }
     }
 }
@@ -400,7 +400,9 @@ int adam_step(const AdamArgs& a, cudaStream_t st) {
     return LIFTER_OK;
 }
 
-int adam_step_dp(const AdamDpArgs& d, cudaStream_t st) {
+int adam_step_dp(const AdamDpArgs& d_in, cudaStream_t st) {
+    AdamDpArgs d = d_in;
+    d.spin_limit = dp_spin_limit_clocks();
     const AdamArgs& a = d.a;
     LIFTER_REQUIRE(a.n % 4 == 0 && a.base % 4 == 0 && a.n > 0, "adam: range start / length must be multiples of 4");
     LIFTER_REQUIRE(d.phase >= 0 && d.phase < ADAM_DP_PHASES, "adam_dp: phase %d out of range", d.phase);

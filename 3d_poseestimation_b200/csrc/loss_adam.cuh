@@ -57,6 +57,7 @@ struct AdamDpArgs {
     // a step may run several launches (one per parameter range): launch `phase` of the step uses the barrier epoch
     // step * ADAM_DP_PHASES + phase; only the `last` launch runs the closing "all stores have landed" barrier
     int phase = 0, last = 1;
+    long long spin_limit = 0;                    // SM clocks a peer is waited for (0 = forever); set by adam_step_dp
 };
 constexpr int ADAM_DP_PHASES = 64;
 int adam_step_dp(const AdamDpArgs& a, cudaStream_t st);

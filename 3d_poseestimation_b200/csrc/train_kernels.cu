@@ -81,7 +81,7 @@ __device__ __forceinline__ void st_ll_f64(uint4* p, double v, unsigned epoch) {
                  "r"(static_cast<unsigned>(b >> 32)), "r"(epoch)
                  : "memory");
 }
-__device__ __forceinline__ double ld_ll_f64(const uint4* p, unsigned epoch) {
+__device__ __forceinline__ double ld_ll_f64(const uint4* p, unsigned epoch, long long spin_limit) {
     uint4 w;
     long long t0 = 0;
     unsigned spins = 0;
@@ -89,10 +89,10 @@ __device__ __forceinline__ double ld_ll_f64(const uint4* p, unsigned epoch) {
         asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
                      : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "l"(p) : "memory");
         if (w.y == epoch && w.w == epoch) break;
-        if ((++spins & 0x3FF) == 0) {                                      // a lost peer traps after ~4 s, no hang
+        if ((++spins & 0x3FF) == 0 && spin_limit > 0) {     // a DEAD peer traps after LIFTER_DP_TIMEOUT_S; a late one is waited for
             const long long now = clock64();
             if (t0 == 0) t0 = now;
-            else if (now - t0 > 8000000000LL) __trap();
+            else if (now - t0 > spin_limit) __trap();
         }
     }
     return __longlong_as_double(static_cast<long long>((static_cast<unsigned long long>(w.z) << 32) | w.x));
@@ -118,8 +118,8 @@ __device__ __forceinline__ void exchange_column_sums(const SyncExchange& ex, int
     for (int r = 0; r < ex.world; ++r) {
         if (r == ex.rank) { ta += la; tb += lb; continue; }
         const uint4* d = reinterpret_cast<const uint4*>(ex.data[ex.rank]) + base + static_cast<size_t>(r) * 2 * H;
-        ta += ld_ll_f64(d + col, epoch);
-        tb += ld_ll_f64(d + H + col, epoch);
+        ta += ld_ll_f64(d + col, epoch, ex.spin_limit);
+        tb += ld_ll_f64(d + H + col, epoch, ex.spin_limit);
     }
 }
 

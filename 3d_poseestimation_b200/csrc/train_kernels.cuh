@@ -28,6 +28,7 @@ struct SyncExchange {
     int site = 0, nsites = 1;          // which of the step's exchange points this is (forward l, backward l)
     void* data[DP_MAX_WORLD];          // peer p's buffer: [2 parities][nsites][world slots][2][H] 16-byte LL words
     const unsigned* epoch;             // device: the step counter (lifter_step_state_t.adam_step), >= 1
+    long long spin_limit = 0;          // SM clocks a peer is waited for before the kernel traps (0 = forever)
 };
 
 struct BnFwdFinalize {

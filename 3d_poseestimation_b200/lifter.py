@@ -49,6 +49,7 @@ class Linear(torch.nn.Module):
         self.batch_norm2 = torch.nn.BatchNorm1d(self.l_size)
         self.BN = BN
 
+    @_cabi.device_guard
     def forward(self, x):
         raise RuntimeError("the residual block runs fused inside LinearModel.forward (sm_100a kernels); "
                            "it has no standalone or CPU path")
@@ -181,6 +182,7 @@ class LinearModel(torch.nn.Module):
         except KeyError:
             raise ValueError(f"unknown operand format {name!r}: use 'fp16' or 'bf16'") from None
 
+    @_cabi.device_guard
     def _operands(self, fmt):
         """16-bit zero-padded copies of the Linear weights, refreshed when a parameter changed."""
         if not self._flat_is_intact():
@@ -202,6 +204,7 @@ class LinearModel(torch.nn.Module):
         if hit is not None:
             self._cache[("op", fmt)] = ((self._versions(), self._flat.data_ptr()), hit[1])
 
+    @_cabi.device_guard
     def _folded_bn(self):
         """Eval-mode BatchNorm + bias folded to per-column scale/shift [L][2][H]."""
         ver = (self._versions(), self._stats_epoch, self._rm._version, self._rv._version,
@@ -234,6 +237,7 @@ class LinearModel(torch.nn.Module):
             raise RuntimeError(f"expected a float32 input (the reference calls .float(), train_1.py:80), got {y.dtype}")
         return y.contiguous()
 
+    @_cabi.device_guard
     def infer(self, x, in_stats=None, out_stats=None, out=None, chunk_rows=0):
         """Inference without autograd: ``model.eval()`` + ``torch.no_grad()`` forward (train_1.py:112-118).
 
@@ -275,6 +279,14 @@ class LinearModel(torch.nn.Module):
                                             int(chunk_rows), _cabi.stream_ptr()))
         return out
 
+    def infer_launches(self, batch):
+        """Kernel launches of one ``infer`` call on ``batch`` rows (counted by the library, not assumed)."""
+        x = torch.zeros(batch, self.input_size, device=self._flat.device)
+        self.infer(x)                                             # operands packed, BN folded: not part of the count
+        before = _cabi.lib().lifter_launch_count()
+        self.infer(x)
+        return int(_cabi.lib().lifter_launch_count() - before)
+
     def infer_host(self, x, out=None, chunk_rows=16384, in_stats=None, out_stats=None):
         """Host-to-host inference: the evaluation loop of ``train_1.py:112-125`` (``inputs.cuda()`` ... ``.cpu()``)
         as a three-stage pipeline.  ``x`` is an fp32 CPU tensor (pinned for asynchronous copies), the result an fp32
@@ -282,6 +294,7 @@ class LinearModel(torch.nn.Module):
         """
         return self.infer_host_batches([x], None if out is None else [out], chunk_rows, in_stats, out_stats)[0]
 
+    @_cabi.device_guard
     def infer_host_batches(self, batches, outs=None, chunk_rows=65536, in_stats=None, out_stats=None):
         """``infer_host`` over an iterable of host batches with ONE pipeline: the upload of the next batch's first chunk
         and the download of the previous batch's last chunk overlap the compute across batch boundaries, and the host
@@ -347,6 +360,7 @@ class LinearModel(torch.nn.Module):
             self._cache["host_pipe"] = pipe
         return pipe
 
+    @_cabi.device_guard
     def forward(self, x):
         y = self._check_input(x)
         needs_grad = torch.is_grad_enabled() and (y.requires_grad or any(p.requires_grad for p in self.parameters()))

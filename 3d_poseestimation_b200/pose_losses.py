@@ -459,3 +459,13 @@ class TriangleLoss_sep(torch.nn.Module):
               float(sum(self.loss_lift) / len(self.loss_lift)),
               float(sum(self.loss_domain_gap) / len(self.loss_domain_gap)))
         self.loss_2d, self.loss_3d, self.loss_lift, self.loss_domain_gap = [], [], [], []
+
+
+# Every entry point launches on the device of its first CUDA tensor, whatever device is current (_cabi.device_guard).
+for _name in ("coco2h36m", "keypoint_stats", "process_data", "normalise", "denormalise", "normalise_minmax",
+              "denormalise_minmax", "loss_MPJPE", "_pose_loss_call", "l1_loss"):
+    globals()[_name] = _cabi.device_guard(globals()[_name])
+for _cls in (_FlipPose, _AffineCols, _MinMaxNorm, _PoseLoss, _L1Mean):
+    _cls.forward = staticmethod(_cabi.device_guard(_cls.forward))
+    _cls.backward = staticmethod(_cabi.device_guard(_cls.backward))
+del _name, _cls

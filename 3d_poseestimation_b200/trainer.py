@@ -30,7 +30,7 @@ class LifterTrainer:
 
     def __init__(self, model, lr=1e-4, loss="mse", optimizer="adamw", betas=(0.9, 0.999), eps=1e-8,
                  weight_decay=None, seed=0, process_group=None, world_size=None, rank=None, metric_std=None,
-                 use_graph=True):
+                 use_graph=True, require_symmetric=False):
         if loss not in _LOSS:
             raise ValueError(f"unknown loss {loss!r}: use 'mse', 'l1' or 'mpjpe'")
         if optimizer not in ("adam", "adamw"):
@@ -76,8 +76,12 @@ class LifterTrainer:
         self._state_stale = False
         self._sym = None
         self._dp_adam = False
+        self._pipe = None
+        self._launches = None                    # kernel launches of one step (counted by the library at capture)
+        self.require_symmetric = bool(require_symmetric)
         if self.world > 1:
-            self._setup_symmetric(dev)
+            with torch.cuda.device(dev):
+                self._setup_symmetric(dev)
         self._graphs = {}
 
     # ------------------------------------------------------------------ data parallel: NVLink symmetric memory
@@ -87,7 +91,17 @@ class LifterTrainer:
         import torch.distributed as dist
         model = self.model
         model._dp = None
+        # every replica starts from rank 0's parameters and BatchNorm buffers (what DistributedDataParallel does at
+        # construction): ranks built from different seeds would otherwise run the first step on diverging weights
+        with torch.no_grad():
+            for t in (model._flat, model._rm, model._rv, model._nbt):
+                dist.broadcast(t, src=dist.get_global_rank(self.pg, 0), group=self.pg)
+        model._param_epoch += 1
+        model._stats_epoch += 1
         if self.world > _cabi.DP_MAX_WORLD:
+            if self.require_symmetric:
+                raise RuntimeError(f"data parallel over {self.world} ranks: the in-kernel NVLink exchange serves at most "
+                                   f"{_cabi.DP_MAX_WORLD} (one NVSwitch box)")
             return
         lib, cfg = _cabi.lib(), C.byref(model._cfg)
         fmt = model._fmt_code(model.train_format)
@@ -95,7 +109,7 @@ class LifterTrainer:
 
         def up(v):
             return (v + 255) // 256 * 256
-        sync_b = up(_cabi.check(lib.lifter_dp_sync_bytes(cfg, self.world)))
+        sync_b = up(_cabi.check(lib.lifter_dp_sync_bytes(cfg, self.world)) * self._bn_calls_per_step())
         op_b = up(lib.lifter_operand_bytes(cfg))
         off_flags = sync_b
         off_grad = off_flags + _cabi.DP_FLAG_BYTES
@@ -110,6 +124,9 @@ class LifterTrainer:
             torch.cuda.synchronize()
             dist.barrier(group=self.pg)                          # every rank's buffer is zeroed before first use
         except Exception as e:                                   # noqa: BLE001 -- plumbing fallback, kernels unchanged
+            if self.require_symmetric:
+                raise RuntimeError(f"NVLink symmetric memory is unavailable ({e}) and require_symmetric=True: refusing "
+                                   "to fall back to NCCL all-reduces under the same configuration name") from e
             import warnings
             warnings.warn(f"symmetric memory unavailable ({e}); BatchNorm sums and gradients go through NCCL")
             return
@@ -131,34 +148,48 @@ class LifterTrainer:
         model._dp = dp
         self._dp_adam = os.environ.get("LIFTER_DP_NCCL_GRADS") != "1"      # (env: fall back to NCCL all-reduce + Adam)
 
+    def _bn_calls_per_step(self):
+        """Lifter forwards per optimiser step: each needs its own slots in the SyncBN exchange buffer."""
+        return 1
+
     # ------------------------------------------------------------------ buffers sized by the batch
+    MAX_RESIDENT_BATCH_SIZES = 3
+
+    def _alloc_buffers(self, B, dev):
+        lib, cfg = _cabi.lib(), C.byref(self.model._cfg)
+        return dict(
+            saved=torch.empty(_cabi.check(lib.lifter_train_saved_bytes(cfg, B)), dtype=torch.uint8, device=dev),
+            scratch=torch.empty(_cabi.check(lib.lifter_train_scratch_bytes(cfg, B)), dtype=torch.uint8, device=dev),
+            out=torch.empty(B, self.model.output_size, dtype=torch.float32, device=dev),
+            dpred=torch.empty(B, self.model.output_size, dtype=torch.float32, device=dev),
+            lscratch=torch.empty(_cabi.check(lib.lifter_loss_scratch_bytes(B, self.joints)), dtype=torch.uint8,
+                                 device=dev))
+
     def _buffers(self, B, dev):
-        b = self._bufs.get(B)
+        """Workspaces of batch size B.  The last few batch sizes stay resident (a trailing partial batch does not evict
+        the full-size buffers); a captured graph holds the ADDRESSES of its buffers, so graphs are dropped together with
+        the buffers they were captured on."""
+        b = self._bufs.pop(B, None)
         if b is None:
-            lib, cfg = _cabi.lib(), C.byref(self.model._cfg)
-            b = dict(
-                saved=torch.empty(_cabi.check(lib.lifter_train_saved_bytes(cfg, B)), dtype=torch.uint8, device=dev),
-                scratch=torch.empty(_cabi.check(lib.lifter_train_scratch_bytes(cfg, B)), dtype=torch.uint8, device=dev),
-                out=torch.empty(B, self.model.output_size, dtype=torch.float32, device=dev),
-                dpred=torch.empty(B, self.model.output_size, dtype=torch.float32, device=dev),
-                lscratch=torch.empty(_cabi.check(lib.lifter_loss_scratch_bytes(B, self.joints)), dtype=torch.uint8,
-                                     device=dev))
-            self._bufs = {B: b}                       # keep one batch size resident
+            b = self._alloc_buffers(B, dev)
+            while len(self._bufs) >= self.MAX_RESIDENT_BATCH_SIZES:
+                old = next(iter(self._bufs))                      # least recently used
+                torch.cuda.synchronize(dev)                       # nothing in flight may still use it
+                del self._bufs[old]
+                for key in [k for k in self._graphs if k[0] == old]:
+                    del self._graphs[key]
+        self._bufs[B] = b                                         # most recently used last
         return b
 
-    def launches_per_step(self, B):
-        L = 2 * self.model.num_stage + 1
-        use_bn = 1 if self.model.BN else 0
-        fwd = 1 + L * 3 + 1                      # prep_input, per layer GEMM + finalize + apply, output GEMM
-        loss = 2
-        bwd = 2 + 2 + 1 + L * (2 * use_bn + 1 + 2 + 1) - 1 + (0 if use_bn else L)
-        adam = L + 1 if (self.fuse_optimizer and self.use_graph and (self.world == 1 or self._dp_adam)) else 1
-        return 1 + fwd + loss + bwd + adam       # + step_advance + Adam (which also packs the operands), per range
+    def graph_launches(self):
+        """Kernel launches of one training step as the library counted them while the step was enqueued (captured)."""
+        return self._launches
 
     # ------------------------------------------------------------------ one optimiser step
-    def _enqueue(self, x, y, b, accumulate_metric, state):
+    def _enqueue(self, inputs, b, accumulate_metric, state):
         """The kernel sequence of one step on the current stream.  ``state`` (device step state) set: every
         step-dependent scalar is read from device memory, so the sequence can be captured once and replayed."""
+        x, y = inputs
         model = self.model
         lib, cfg = _cabi.lib(), C.byref(model._cfg)
         B = x.shape[0]
@@ -174,16 +205,26 @@ class LifterTrainer:
         _cabi.check(lib.lifter_loss(_cabi.ptr(out), _cabi.ptr(y), B, self.joints, self.loss_kind, B * self.world,
                                     _cabi.ptr(self.metric_std), _cabi.ptr(b["dpred"]), _cabi.ptr(b["lscratch"]),
                                     _cabi.ptr(self.loss_out), int(accumulate_metric), st))
+        self._optimise(t, b["dpred"], b["scratch"], state, fused_backward=True)
+
+    def _optimise(self, t, dpred, scratch, state, fused_backward):
+        """Backward of the forward described by ``t`` + the optimiser step.  ``fused_backward``: the backward pass has not
+        run yet and may carry the per-layer optimiser ranges; otherwise ``self.grad`` already holds the gradient."""
+        model = self.model
+        lib, cfg = _cabi.lib(), C.byref(model._cfg)
+        st = _cabi.stream_ptr()
+        fmt = model._fmt_code(model.train_format)
         ops = model._operands(fmt)
-        if state is not None and self.fuse_optimizer and (self.world == 1 or self._dp_adam):
-            # backward with the optimiser folded in: each layer's Adam range (data parallel: its NVLink reduce-scatter +
-            # Adam + all-gather) runs on a side stream as soon as that layer's gradients exist
-            opt = _cabi.Optim(model._flat.data_ptr(), ops.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
-                              self.betas[0], self.betas[1], self.eps, self.weight_decay, int(self.decoupled), 1.0)
-            _autograd.run_backward(model, t, b["dpred"], self.grad, None, scratch=b["scratch"], optim=opt)
-            return
-        _autograd.run_backward(model, t, b["dpred"], self.grad, None, scratch=b["scratch"])
-        if self._dp_adam:
+        if fused_backward:
+            if state is not None and self.fuse_optimizer and (self.world == 1 or self._dp_adam):
+                # backward with the optimiser folded in: each layer's Adam range (data parallel: its NVLink reduce-scatter
+                # + Adam + all-gather) runs on a side stream as soon as that layer's gradients exist
+                opt = _cabi.Optim(model._flat.data_ptr(), ops.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
+                                  self.betas[0], self.betas[1], self.eps, self.weight_decay, int(self.decoupled), 1.0)
+                _autograd.run_backward(model, t, dpred, self.grad, None, scratch=scratch, optim=opt)
+                return
+            _autograd.run_backward(model, t, dpred, self.grad, None, scratch=scratch)
+        if self._dp_adam and state is not None:
             # data parallel: reduce-scatter of the gradients + Adam + all-gather of the parameters in ONE kernel over
             # NVLink peer memory (sum of shard gradients = gradient of the global batch)
             _cabi.check(lib.lifter_dp_adam_step(cfg, C.byref(model._dp), _cabi.ptr(self.m), _cabi.ptr(self.v),
@@ -191,7 +232,7 @@ class LifterTrainer:
                                                 int(self.decoupled), 1.0, _cabi.ptr(state), fmt, st))
             return
         if self.world > 1:
-            import torch.distributed as dist
+            import torch.distributed as dist                      # (use_graph=False, or no symmetric memory)
             dist.all_reduce(self.grad, group=self.pg)             # sum of shard gradients = global-batch gradient
         # Adam / AdamW over the flat buffer; the same pass rewrites the 16-bit operand copies of the weights
         _cabi.check(lib.lifter_adam_step_packed(cfg, _cabi.ptr(model._flat), _cabi.ptr(self.grad), _cabi.ptr(self.m),
@@ -205,7 +246,7 @@ class LifterTrainer:
         model._param_epoch += 1                                   # the flat parameters changed under torch's feet
         model._operands_refreshed(model._fmt_code(model.train_format))
 
-    def _check_xy(self, x, y):
+    def _check_inputs(self, x, y):
         model = self.model
         x = model._check_input(x)
         y = y.reshape(y.shape[0], -1)
@@ -213,78 +254,91 @@ class LifterTrainer:
             raise RuntimeError(f"target must be a float32 CUDA tensor of {x.shape[0]} x {model.output_size} values")
         return x, y.contiguous()
 
-    def step(self, x, y, accumulate_metric=False, _loss_copy=None):
+    @_cabi.device_guard
+    def step(self, *tensors, accumulate_metric=False, _loss_copy=None):
         """x: (B, 17, 2) or (B, i_dim) fp32 CUDA, y: (B, 17, 3) or (B, o_dim).  Returns the device loss scalar.
         (``_loss_copy``: a one-element device tensor that also receives the loss -- ``run_epoch``'s per-slot mailbox.)"""
         model = self.model
-        x, y = self._check_xy(x, y)
-        B = x.shape[0]
+        inputs = self._check_inputs(*tensors)
+        B = inputs[0].shape[0]
         model.train()
         if self.use_graph and B >= 2 and (self.world == 1 or self.graph_collectives):
-            return self._step_graph(x, y, bool(accumulate_metric), _loss_copy)
-        loss = self._step_eager(x, y, B, accumulate_metric)
+            return self._step_graph(inputs, bool(accumulate_metric), _loss_copy)
+        loss = self._step_eager(inputs, B, accumulate_metric)
         if _loss_copy is not None:
             _loss_copy.copy_(loss.reshape(1))
         return loss
 
-    def _step_eager(self, x, y, B, accumulate_metric):
-        model = self.model
-        b = self._buffers(B, x.device)
+    def _counted(self, fn):
+        before = _cabi.lib().lifter_launch_count()
+        fn()
+        self._launches = int(_cabi.lib().lifter_launch_count() - before)
+
+    def _step_eager(self, inputs, B, accumulate_metric):
+        b = self._buffers(B, inputs[0].device)
         if self.world > 1 and self.use_graph and B >= 2:
             # data parallel: same kernel sequence driven by the device step state (it is also the epoch of the
             # in-kernel BatchNorm exchange); launched eagerly because of the NCCL gradient all-reduce in the middle
             if self._state_stale:
                 self._sync_state()
-            self._enqueue(x, y, b, accumulate_metric, self.state)
+            self._counted(lambda: self._enqueue(inputs, b, accumulate_metric, self.state))
             self._after_step()
             return self.loss_out[0]
-        self._enqueue(x, y, b, accumulate_metric, None)
+        self._counted(lambda: self._enqueue(inputs, b, accumulate_metric, None))
         self._after_step()
         self._state_stale = True                                  # the device step state did not see this step
         return self.loss_out[0]
 
-    def _capture(self, xin, yin, B, accumulate_metric, loss_copy=None):
+    def _capture(self, inputs, B, accumulate_metric, loss_copy=None):
         model = self.model
-        b = self._buffers(B, xin.device)
+        b = self._buffers(B, inputs[0].device)
         model._operands(model._fmt_code(model.train_format))              # packed before the capture starts
         self._sync_state()
         torch.cuda.synchronize()
         graph = torch.cuda.CUDAGraph()
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.graph(graph, stream=side):
-            self._enqueue(xin, yin, b, accumulate_metric, self.state)
+
+        def body():
+            self._enqueue(inputs, b, accumulate_metric, self.state)
             if loss_copy is not None:
                 loss_copy.copy_(self.loss_out[:1])
+        with torch.cuda.graph(graph, stream=side):
+            self._counted(body)
         return graph
 
-    def _step_graph(self, x, y, accumulate_metric, loss_copy=None):
+    def _step_graph(self, inputs, accumulate_metric, loss_copy=None):
         """Replay of the captured step: no per-kernel host work.  One graph per batch size reads its inputs from static
         buffers the batch is copied into; input tensors that come back at the same addresses (a prefetch slot of
         ``run_epoch``, a resident benchmark batch) get a graph of their own that reads them in place."""
         model = self.model
-        B = x.shape[0]
+        B = inputs[0].shape[0]
         key = (B, accumulate_metric, model._flat.data_ptr())
         g = self._graphs.get(key)
         if g is None:
-            xs, ys = torch.empty_like(x), torch.empty_like(y)
-            g = {"generic": (self._capture(xs, ys, B, accumulate_metric), xs, ys), "in_place": {}, "seen": {}}
-            self._graphs = {key: g}                                       # keep one batch size resident
+            static = tuple(torch.empty_like(t) for t in inputs)
+            g = {"generic": (self._capture(static, B, accumulate_metric), static), "in_place": {}, "seen": {}}
+            self._graphs[key] = g
+        else:
+            self._buffers(B, inputs[0].device)                            # LRU touch
         if self._state_stale:
             self._sync_state()
-        ptrs = (x.data_ptr(), y.data_ptr(), 0 if loss_copy is None else loss_copy.data_ptr())
+        # the graph reads the 16-bit operand copy: re-validate it against the fp32 parameters (load_state_dict,
+        # .apply(weight_init) or an in-place edit between steps re-packs into the same buffer; otherwise a version check)
+        model._operands(model._fmt_code(model.train_format))
+        ptrs = tuple(t.data_ptr() for t in inputs) + (0 if loss_copy is None else loss_copy.data_ptr(),)
         graph = g["in_place"].get(ptrs)
         if graph is None:
             seen = g["seen"]
             seen[ptrs] = seen.get(ptrs, 0) + 1
             if seen[ptrs] >= 3 and len(g["in_place"]) < 4:                # the same buffers for the third time
-                graph = g["in_place"][ptrs] = self._capture(x, y, B, accumulate_metric, loss_copy)
+                graph = g["in_place"][ptrs] = self._capture(inputs, B, accumulate_metric, loss_copy)
             elif len(seen) > 256:
                 seen.clear()
         if graph is None:
-            graph, xs, ys = g["generic"]
-            xs.copy_(x, non_blocking=True)
-            ys.copy_(y, non_blocking=True)
+            graph, static = g["generic"]
+            for dst, src in zip(static, inputs):
+                dst.copy_(src, non_blocking=True)
             graph.replay()
             if loss_copy is not None:
                 loss_copy.copy_(self.loss_out[:1])
@@ -294,6 +348,7 @@ class LifterTrainer:
         self._after_step()
         return self.loss_out[0]
 
+    @_cabi.device_guard
     def run_epoch(self, batches, accumulate_metric=False):
         """The epoch loop of ``train_1.py:73-100`` over an iterable of HOST batches ``(x, y)`` (fp32 CPU tensors;
         pinned, as a ``DataLoader(pin_memory=True)`` yields them, for the upload to be asynchronous).
@@ -301,46 +356,48 @@ class LifterTrainer:
         The upload of batch i+1 runs on a copy stream while step i computes; each step's loss is read back into
         pinned host memory without stalling the queue (the reference blocks on ``loss.cpu().item()`` every step,
         train_1.py:98).  Returns the per-step losses as a float32 CPU tensor (data parallel: summed over ranks, like
-        ``loss_value``).
+        ``loss_value``).  Data parallel: the ranks meet at a host barrier first, so that an epoch never starts against
+        a peer that is still checkpointing or validating (the in-kernel exchange waits, but not for ever).
         """
         model = self.model
         dev = model._flat.device
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self.pg)
         cur = torch.cuda.current_stream(dev)
-        pipe = self._bufs.get("pipe")
+        pipe = self._pipe
         if pipe is None:
             pipe = {"copy": torch.cuda.Stream(dev), "down": torch.cuda.Stream(dev), "slots": {},
                     "ready": [torch.cuda.Event() for _ in range(2)], "free": [torch.cuda.Event() for _ in range(2)],
                     "read": [torch.cuda.Event() for _ in range(2)]}
-            self._bufs["pipe"] = pipe
+            self._pipe = pipe
         copy, down = pipe["copy"], pipe["down"]
         copy.wait_stream(cur)
         down.wait_stream(cur)
         losses, n = None, 0
-        for i, (xh, yh) in enumerate(batches):
-            if xh.is_cuda or yh.is_cuda:
+        for i, host in enumerate(batches):
+            if any(t.is_cuda for t in host):
                 raise RuntimeError("run_epoch takes host batches; call step() with device tensors")
-            xh = xh.reshape(xh.shape[0], -1)
-            yh = yh.reshape(yh.shape[0], -1)
+            host = [t.reshape(t.shape[0], -1) for t in host]
             s = i & 1
-            key = (s, tuple(xh.shape), tuple(yh.shape))
+            key = (s,) + tuple((tuple(t.shape), t.dtype) for t in host)
             slot = pipe["slots"].get(s)
             if slot is None or slot[0] != key:
                 if slot is not None:
                     torch.cuda.synchronize(dev)                    # a batch-size change: let the old slot drain
-                slot = (key, torch.empty(xh.shape, dtype=torch.float32, device=dev),
-                        torch.empty(yh.shape, dtype=torch.float32, device=dev),
+                slot = (key, [torch.empty(t.shape, dtype=t.dtype, device=dev) for t in host],
                         torch.zeros(1, dtype=torch.float32, device=dev))
                 pipe["slots"][s] = slot
-            _, xd, yd, lossd = slot
+            _, devt, lossd = slot
             with torch.cuda.stream(copy):
                 if i >= 2:
                     copy.wait_event(pipe["free"][s])               # step i-2 has consumed this slot ...
                     copy.wait_event(pipe["read"][s])               # ... and its loss has left the slot's mailbox
-                xd.copy_(xh, non_blocking=True)
-                yd.copy_(yh, non_blocking=True)
+                for d, h in zip(devt, host):
+                    d.copy_(h, non_blocking=True)
                 pipe["ready"][s].record(copy)
             cur.wait_event(pipe["ready"][s])
-            self.step(xd, yd, accumulate_metric=accumulate_metric, _loss_copy=lossd)   # the step leaves its loss in lossd
+            self.step(*devt, accumulate_metric=accumulate_metric, _loss_copy=lossd)   # the step leaves its loss in lossd
             pipe["free"][s].record(cur)
             if losses is None or n == losses.numel():
                 grown = torch.empty(max(256, 2 * n), dtype=torch.float32).pin_memory()
@@ -401,6 +458,7 @@ class LifterTrainer:
         self._sync_state()
 
 
+@_cabi.device_guard
 def evaluate(model, batches, loss="mse", flip=None, metric_std=None, n_samples=None, zero_centre=True):
     """The validation loop of ``train_1.py:112-145`` without its per-batch host syncs.
 

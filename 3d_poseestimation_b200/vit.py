@@ -214,6 +214,7 @@ class MyViT(torch.nn.Module):
         return d
 
     # ------------------------------------------------------------------------------------------------ forward
+    @_cabi.device_guard
     def forward(self, images):
         if not torch.is_tensor(images) or not images.is_cuda:
             raise RuntimeError("MyViT: the sm_100a build has no CPU path; move the model and the input to a B200")
@@ -224,6 +225,7 @@ class MyViT(torch.nn.Module):
             return _VitFunction.apply(self, names, images, *params)
         return self.infer(images)
 
+    @_cabi.device_guard
     @torch.no_grad()
     def infer(self, images, chunk_poses=None):
         """Eval-mode forward, ``chunk_poses`` poses per pass of the kernel sequence."""

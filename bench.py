@@ -1,24 +1,31 @@
 #!/usr/bin/env python
-"""Benchmark of the B200-native lifter hot path (contract: see the task statement / DESIGN.md §Measurement).
+"""Benchmark of the B200-native lifter hot path (contract: see the task statement / DESIGN.md §7).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload train|eval] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload train|eval|wide|phase5] [--impl ours|reference]
 
 The default workload is BASELINE.json's metric, "lifted poses/sec (fwd+bwd)": the data-parallel training step of
 configs[2] (8,192 poses per GPU); with one GPU the line also carries an ``inference`` object with the eval-mode
-numbers of configs[1] (65,536 poses).  ``--workload eval`` makes configs[1] the headline instead.
+numbers of configs[1] (65,536 poses).  ``--workload eval`` makes configs[1] the headline, ``--workload phase5`` is
+configs[3] (the phase-5 loop body around the lifter), ``--workload wide`` configs[4] (2,048 wide, 4 blocks).
 
-* ``value``  : lifted poses/s over all ranks, inputs resident in HBM, CUDA-event time, max over ranks.
-* ``e2e``    : the same metric through the public module API with HOST (pinned) inputs: H2D copy of the
-               step's keypoints, the step, D2H of the step's result -- all inside the timed region.
-* ``roofline``: the dominant kernel (the 1024-wide tcgen05 GEMM) timed alone with CUDA events, against the
-               measured bf16 peak of MEASURED_PEAKS.json.
-* ``cpu_baseline`` / ``--impl reference``: the oracle's PyTorch-fp32 CPU restatement of the reference module
-               (the reference itself is Python and does not travel to the GPU box) on the host cores.
+* ``value``     : lifted poses/s over all ranks, inputs resident in HBM, CUDA-event time, max over ranks.
+* ``e2e``       : the same metric through the public module API with HOST (pinned) inputs: H2D copy of the
+                  step's keypoints, the step, D2H of the step's result -- all inside the timed region.
+* ``sustained`` : the same step repeated for >= 1.5 s (CUDA-event time, nvidia-smi clock samples INSIDE the region).
+* ``roofline``  : the dominant kernel (the H x H tcgen05 GEMM) timed alone with CUDA events, against the measured
+                  bf16 peak of MEASURED_PEAKS.json; ``library_point`` is cuBLAS (torch.matmul) at the same shape.
+* ``dp_check``  : N > 1 only.  After the timed loops every rank replays 3 steps from a fixed seed, data parallel, and
+                  the same 3 steps single-process on the concatenated global batch: losses, parameters and replica
+                  identity are compared; a failed check makes the process exit non-zero.
+* ``cpu_baseline`` / ``--impl reference``: the UNMODIFIED reference module (staged from /root/reference into
+                  oracle/_ref/ by oracle/make_ref.sh) on the host cores, at the GPU arm's configuration.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import importlib
+import importlib.util
 import json
 import os
 import statistics
@@ -39,6 +46,10 @@ EVAL_BATCH = 65536                       # BASELINE.json configs[1]
 TRAIN_BATCH = 8192                       # BASELINE.json configs[2], per GPU
 WIDE = (16 * 34, 2048, 4)                # BASELINE.json configs[4]: i_dim, linear_size, num_stage
 FLOP_PER_POSE_WIDE_TRAIN = 206_409_728
+# configs[3]: four lifter forwards per pose (pred / gt keypoints, each plus its flipped twin) and the backward of the
+# two that reach the loss, with the gradient into the predicted 2D input (SURVEY §3.3, §8d "25,688,064 if input grad")
+FLOP_PER_POSE_PHASE5 = 4 * FLOP_PER_POSE_INFER + 2 * (25_688_064 - FLOP_PER_POSE_INFER)
+WORKLOADS = {"eval": "configs[1]", "train": "configs[2]", "phase5": "configs[3]", "wide": "configs[4]"}
 
 
 def peaks():
@@ -78,18 +89,19 @@ class ClockSampler:
         self.stop.set()
         self.thread.join(timeout=6)
 
-    def summary(self):
-        if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
-        sm = [float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit()]
-        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+    def summary(self, first=0, last=None):
+        samples = self.samples[first:last]
+        if not samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"], "samples": 0}
+        sm = [float(s[0]) for s in samples if s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in samples if s[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
+        reasons = sorted({n for s in samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.samples)}
+                "reasons": reasons, "samples": len(samples)}
 
 
-# ------------------------------------------------------------------------------------------------ CPU arm
+# ------------------------------------------------------------------------------------------------ synthetic data
 def synth_batch(batch, seed):
     """Synthetic H36M-shaped keypoints from the repo statistics: normalised 2D in, normalised 3D target."""
     import numpy as np
@@ -103,42 +115,49 @@ def synth_batch(batch, seed):
     return xn, yn
 
 
-def cpu_arm(workload, steps, warmup, budget_s=25.0):
-    """Times the oracle (CPU restatement of the reference LinearModel, PyTorch fp32) on the host cores."""
+def synth_wide(batch, seed):
+    """configs[4]: 16 iid frames concatenated into a 544-wide input."""
     import torch
+    x = torch.cat([synth_batch(batch, 100 * f + seed)[0] for f in range(16)], dim=1).contiguous()
+    return x, synth_batch(batch, seed)[1]
 
-    from oracle import adam_oracle, lifter_oracle as lo
-    from oracle.philox import dropout_keep_mask
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    I_DIM, H, S = WIDE if workload == "wide" else (globals()["I_DIM"], globals()["H"], globals()["S"])
-    params, buffers = lo.numpy_init(I_DIM, O_DIM, H, S, seed=1, randomize_bn=False)
-    if workload == "eval":
-        batch = 8192                                            # bounded sample of the 65,536-pose workload
-        x, _ = synth_batch(batch, 0)
 
-        def step():
-            with torch.no_grad():
-                lo.lifter_forward(params, buffers, x, num_stage=S, training=False)
-        sample = f"{batch} of {EVAL_BATCH} poses per step, eval forward"
-    else:
-        batch = 512                                             # bounded sample of the 8,192-pose step
-        x, y = synth_batch(batch, 0)
-        if workload == "wide":
-            x = torch.cat([synth_batch(batch, 100 * f)[0] for f in range(16)], dim=1).contiguous()
-        masks = [dropout_keep_mask(batch, H, s, 0, 2, 0.5) for s in range(2 * S + 1)]
-        m = {k: torch.zeros_like(v) for k, v in params.items()}
-        v = {k: torch.zeros_like(w) for k, w in params.items()}
-        state = {"t": 0}
+def synth_phase5(batch, seed):
+    """configs[3]: what the phase-5 loop hands the lifter per step (backup_june8.py:128-138): the 2D model's prediction
+    ``y1_hat`` and the 3D model's ``y2_hat`` (stand-ins: ground truth + noise, the image CNNs are out of scope), the
+    ground truth ``y1`` / ``y2``, and a camera id per pose for the (parity-unpinned) reprojection term."""
+    import torch
+    y1, y2 = synth_batch(batch, seed)
+    g = torch.Generator().manual_seed(seed + 7919)
+    y1_hat = y1 + 0.05 * torch.randn(y1.shape, generator=g)
+    y2_hat = y2 + 0.10 * torch.randn(y2.shape, generator=g)
+    cam = torch.randint(0, 4, (batch,), generator=g)
+    return y1_hat.contiguous(), y2_hat.contiguous(), y1, y2, cam
 
-        def step():
-            r = lo.lifter_forward_backward(params, buffers, x, lambda o: ((o - y) ** 2).mean(), num_stage=S,
-                                           training=True, p_dropout=0.5, masks=masks)
-            state["t"] += 1
-            for k in params:
-                params[k], m[k], v[k] = adam_oracle.adam_step(params[k], r["grads"][k], m[k], v[k], state["t"], 1e-4)
-        sample = f"{batch} of {TRAIN_BATCH} poses per step, fwd+MSE+bwd+Adam"
-    for _ in range(max(1, min(warmup, 3))):
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def load_reference():
+    """The UNMODIFIED reference modules staged by oracle/make_ref.sh (oracle/_ref/, git-ignored, travels with the
+    snapshot).  Returns (baselineModel, losses, info) or None when they are not there."""
+    d = os.path.join(ROOT, "oracle", "_ref")
+    paths = {n: os.path.join(d, n + ".py") for n in ("baselineModel", "losses")}
+    if not all(os.path.exists(p) for p in paths.values()):
+        return None
+    mods, shas = {}, {}
+    for n, p in paths.items():
+        spec = importlib.util.spec_from_file_location("_reference_" + n, p)
+        mods[n] = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mods[n])
+        shas[n + ".py"] = hashlib.sha256(open(p, "rb").read()).hexdigest()
+    want = {}
+    rec = os.path.join(ROOT, "oracle", "ref_sha256.txt")
+    if os.path.exists(rec):
+        want = {ln.split()[1]: ln.split()[0] for ln in open(rec) if ln.strip()}
+    return mods["baselineModel"], mods["losses"], {"sha256": shas, "matches_recorded": all(want.get(k) == v for k, v in shas.items())}
+
+
+def _time_cpu(step, steps, warmup, budget_s):
+    for _ in range(max(1, warmup)):
         step()
     times, t_begin = [], time.perf_counter()
     for _ in range(max(1, steps)):
@@ -147,9 +166,128 @@ def cpu_arm(workload, steps, warmup, budget_s=25.0):
         times.append(time.perf_counter() - t0)
         if time.perf_counter() - t_begin > budget_s:
             break
-    ms = statistics.median(times) * 1e3
+    return statistics.median(times) * 1e3, len(times)
+
+
+def cpu_arm(workload, steps, warmup, budget_s=25.0, with_c1=True):
+    """The reference's own CPU implementation of the workload on the host cores (PyTorch fp32, every host thread):
+    the imported ``LinearModel`` (baselineModel.py:50-102) driven by the loop body of train_1.py:73-100
+    (``MSELoss(mean)``, ``torch.optim.Adam``, lr 1e-4) at the GPU arm's batch.  Falls back to the oracle port (kind
+    "port") only when oracle/_ref/ is absent."""
+    import warnings
+
+    import torch
+    warnings.filterwarnings("ignore")
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ref = load_reference()
+    if ref is None:
+        return cpu_arm_port(workload, steps, warmup, budget_s)
+    rm, rl, info = ref
+    i_dim, h, s = WIDE if workload == "wide" else (I_DIM, H, S)
+    torch.manual_seed(1)
+    model = rm.LinearModel(i_dim=i_dim, o_dim=O_DIM, p_dropout=0.5, linear_size=h, num_stage=s, BN=True)
+    out = {"unit": "poses/s", "cores": cores, "threads": torch.get_num_threads(), "kind": "reference",
+           "reference_files": info, "torch": torch.__version__}
+    if workload == "eval":
+        batch = EVAL_BATCH
+        x, _ = synth_batch(batch, 0)
+        model.eval()
+
+        def step():
+            with torch.no_grad():
+                model(x)
+        sample = f"full configs[1] step: {batch} poses, eval forward under no_grad (train_1.py:112-118)"
+    elif workload == "phase5":
+        from oracle import losses_oracle as L          # flip_pose: my_HybrIK/utils.py imports matplotlib (absent)
+        batch = TRAIN_BATCH
+        y1_hat, y2_hat, y1, y2, _ = synth_phase5(batch, 0)
+        model.train()
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-4)
+        tri = rl.TriangleLoss()
+        B = batch
+
+        def step():
+            opt.zero_grad()
+            a = y1_hat.reshape(B, 17, 2).clone().requires_grad_(True)
+            b3 = y2_hat.reshape(B, 17, 3).clone().requires_grad_(True)
+            lp = model(a).reshape(B, 17, 3)
+            lg = model(y1.reshape(B, 17, 2)).reshape(B, 17, 3)
+            lp = (L.flip_pose(model(L.flip_pose(a)).reshape(B, 17, 3)) + lp) / 2
+            lg = (L.flip_pose(model(L.flip_pose(y1.reshape(B, 17, 2))).reshape(B, 17, 3)) + lg) / 2
+            loss = tri(a, b3, lg, lp, y1.reshape(B, 17, 2), y2.reshape(B, 17, 3))[0]
+            loss.backward()
+            opt.step()
+        sample = (f"full configs[3] step: {batch} poses, 4 lifter forwards + flip averaging + TriangleLoss + backward "
+                  "+ AdamW (backup_june8.py:120-175; flip_pose from the oracle restatement)")
+    else:
+        batch = TRAIN_BATCH
+        x, y = synth_wide(batch, 0) if workload == "wide" else synth_batch(batch, 0)
+        model.train()
+        opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+        loss_fn = torch.nn.MSELoss(reduction="mean")
+
+        def step():
+            opt.zero_grad()
+            loss = loss_fn(model(x), y)
+            loss.backward()
+            opt.step()
+        sample = f"full {WORKLOADS[workload]} step: {batch} poses, fwd + MSELoss + backward + Adam.step (train_1.py:73-100)"
+    ms, n = _time_cpu(step, steps, min(warmup, 2), budget_s)
+    out.update({"value": batch / (ms / 1e3), "sample": sample, "ms_per_step": ms, "steps_timed": n, "batch": batch})
+    if with_c1 and workload in ("train", "eval"):
+        # SURVEY §8d / BASELINE.md §2, C1: batch 64 fwd + MSE + bwd + Adam.step, 5 warm-up + 50 timed, median
+        torch.manual_seed(1)
+        m1 = rm.LinearModel(i_dim=I_DIM, o_dim=O_DIM, p_dropout=0.5, linear_size=H, BN=True).train()
+        o1 = torch.optim.Adam(m1.parameters(), lr=1e-4)
+        x1, y1_ = synth_batch(64, 0)
+        lf = torch.nn.MSELoss(reduction="mean")
+
+        def c1():
+            o1.zero_grad()
+            lf(m1(x1), y1_).backward()
+            o1.step()
+        ms1, n1 = _time_cpu(c1, 50, 5, 20.0)
+        out["c1"] = {"config": "configs[0]: batch 64 fwd+MSE+bwd+Adam on CPU, 5 warm-up + 50 timed, median",
+                     "ms_per_step": ms1, "value": 64 / (ms1 / 1e3), "unit": "poses/s", "steps_timed": n1}
+    return out
+
+
+def cpu_arm_port(workload, steps, warmup, budget_s=25.0):
+    """Fallback when oracle/_ref/ is absent: the oracle's functional restatement of the reference (kind "port")."""
+    import torch
+
+    from oracle import adam_oracle, lifter_oracle as lo
+    from oracle.philox import dropout_keep_mask
+    cores = os.cpu_count() or 1
+    i_dim, h, s = WIDE if workload == "wide" else (I_DIM, H, S)
+    params, buffers = lo.numpy_init(i_dim, O_DIM, h, s, seed=1, randomize_bn=False)
+    if workload == "eval":
+        batch = EVAL_BATCH
+        x, _ = synth_batch(batch, 0)
+
+        def step():
+            with torch.no_grad():
+                lo.lifter_forward(params, buffers, x, num_stage=s, training=False)
+        sample = f"full configs[1] step: {batch} poses, eval forward"
+    else:
+        batch = TRAIN_BATCH
+        x, y = synth_wide(batch, 0) if workload == "wide" else synth_batch(batch, 0)
+        masks = [dropout_keep_mask(batch, h, k, 0, 2, 0.5) for k in range(2 * s + 1)]
+        m = {k: torch.zeros_like(v) for k, v in params.items()}
+        v = {k: torch.zeros_like(w) for k, w in params.items()}
+        state = {"t": 0}
+
+        def step():
+            r = lo.lifter_forward_backward(params, buffers, x, lambda o: ((o - y) ** 2).mean(), num_stage=s,
+                                           training=True, p_dropout=0.5, masks=masks)
+            state["t"] += 1
+            for k in params:
+                params[k], m[k], v[k] = adam_oracle.adam_step(params[k], r["grads"][k], m[k], v[k], state["t"], 1e-4)
+        sample = f"full {WORKLOADS.get(workload, workload)} step: {batch} poses, fwd+MSE+bwd+Adam (oracle port; phase5 runs the plain step)"
+    ms, n = _time_cpu(step, steps, min(warmup, 2), budget_s)
     return {"value": batch / (ms / 1e3), "unit": "poses/s", "cores": cores, "kind": "port", "sample": sample,
-            "ms_per_step": ms, "steps_timed": len(times)}
+            "ms_per_step": ms, "steps_timed": n, "batch": batch}
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
@@ -159,22 +297,48 @@ def gpu_arm(args, rank, world, local_rank):
 
     pkg = importlib.import_module(PKG)
     cabi = importlib.import_module(PKG + "._cabi")
+    trainer_mod = importlib.import_module(PKG + ".trainer")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     cabi.check(cabi.lib().lifter_device_check())
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     pk = peaks()
+    profiling = bool(os.environ.get("LIFTER_BENCH_NO_CPU"))     # under ncu: skip the untimed extras
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(v):
+        if world > 1:
+            t = torch.tensor([v], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return v
+
+    def build_model(workload):
+        torch.manual_seed(1)
+        if workload == "wide":
+            return pkg.LinearModel(WIDE[0], O_DIM, linear_size=WIDE[1], num_stage=WIDE[2], p_dropout=0.5, BN=True).to(dev)
+        return pkg.LinearModel(I_DIM, O_DIM, linear_size=H, num_stage=S, p_dropout=0.5, BN=True).to(dev)
+
+    def build_trainer(workload, model, lr=1e-4, dp=True):
+        kw = dict(world_size=world, rank=rank, require_symmetric=True) if (dp and world > 1) else {}
+        if workload == "phase5":
+            return trainer_mod.Phase5Trainer(model, lr=lr, optimizer="adamw", seed=2, w_reproj=0.1, w_bone=0.1, **kw)
+        return trainer_mod.LifterTrainer(model, lr=lr, loss="mse", optimizer="adam", seed=2, **kw)
+
+    def host_batch(workload, batch, seed):
+        if workload == "phase5":
+            return synth_phase5(batch, seed)
+        return synth_wide(batch, seed) if workload == "wide" else synth_batch(batch, seed)
+
     def measure(workload, steps, warmup, with_clocks):
         """One workload on this rank's GPU: device-resident throughput, end-to-end throughput, dominant kernel."""
-        torch.manual_seed(1)
-        model = pkg.LinearModel(I_DIM, O_DIM, linear_size=H, num_stage=S, p_dropout=0.5, BN=True).to(dev)
+        model = build_model(workload)
+        tr = None
         if workload == "eval":
             batch = EVAL_BATCH
             model.eval()
@@ -183,7 +347,6 @@ def gpu_arm(args, rank, world, local_rank):
             xd = xh.to(dev)
             out = torch.empty(batch, O_DIM, device=dev)
             outh = torch.empty(batch, O_DIM).pin_memory()
-            launches_per_step = 1 + (1 + 2 * S + 1)           # prep_input + one GEMM per Linear (65,536 rows = one chunk)
 
             def step():
                 model.infer(xd, out=out)
@@ -199,42 +362,36 @@ def gpu_arm(args, rank, world, local_rank):
                    "l2": "activations of one step (3 x 134 MB) exceed the 126 MB L2; no flush needed"}
             flop = FLOP_PER_POSE_INFER
         else:
-            if workload == "wide":            # BASELINE.json configs[4]: 16-frame window in, 2048 wide, 4 blocks
-                model = pkg.LinearModel(WIDE[0], O_DIM, linear_size=WIDE[1], num_stage=WIDE[2], p_dropout=0.5,
-                                        BN=True).to(dev)
-            trainer_mod = importlib.import_module(PKG + ".trainer")
             batch = TRAIN_BATCH
-            tr = trainer_mod.LifterTrainer(model, lr=1e-4, loss="mse", optimizer="adam", world_size=world, rank=rank,
-                                           seed=2)
-            xh, yh = synth_batch(batch, rank)
-            if workload == "wide":            # 16 iid frames concatenated
-                xh = torch.cat([synth_batch(batch, 100 * f + rank)[0] for f in range(16)], dim=1).contiguous()
-            xh, yh = xh.pin_memory(), yh.pin_memory()
-            xd, yd = xh.to(dev), yh.to(dev)
-            launches_per_step = tr.launches_per_step(batch)
+            tr = build_trainer(workload, model)
+            host = [t.pin_memory() for t in host_batch(workload, batch, rank)]
+            devt = [t.to(dev) for t in host]
 
             def step():
-                tr.step(xd, yd)
+                tr.step(*devt)
 
             def run_e2e(n):
-                # the epoch loop over host batches: per step, an H2D copy of (x, y) and a D2H read of the loss
-                losses = tr.run_epoch([(xh, yh)] * n)
+                # the epoch loop over host batches: per step, an H2D copy of the inputs and a D2H read of the loss
+                losses = tr.run_epoch([tuple(host)] * n)
                 assert losses.numel() == n and bool(torch.isfinite(losses).all())
-            h2d, d2h = (xh.numel() + yh.numel()) * 4, 4
+            h2d, d2h = sum(t.numel() * t.element_size() for t in host), 4
             dtype = "bf16 operands, fp32 accumulate/master weights"
             par = f"dp{world}"
             if world > 1:
-                par += (" (in-kernel SyncBN exchange + fused reduce-scatter/Adam/all-gather over NVLink symmetric memory)"
-                        if tr._dp_adam else " (NCCL all-reduce fallback)")
-            shape = "1024-wide, 2 residual blocks" if workload == "train" else \
-                "widened lifter (16 x 34 inputs, 2048-wide, 4 residual blocks; configs[4])"
-            cfg = {"workload": f"configs[{2 if workload == 'train' else 4}]: training step fwd + MSE + bwd + Adam, dropout 0.5, batch {batch}/GPU, "
-                               f"synced BatchNorm, {shape}", "batch_per_gpu": batch,
-                   "global_batch": batch * world, "parallelism": par,
-                   "cuda_graph": bool(tr.use_graph),
-                   "l2": "one step touches ~0.4 GB of saved activations and gradients per GPU (> 126 MB L2), so "
+                par += " (in-kernel SyncBN exchange + fused reduce-scatter/Adam/all-gather over NVLink symmetric memory)"
+            what = {"train": "training step fwd + MSE + bwd + Adam, dropout 0.5, batch {b}/GPU, synced BatchNorm, 1024-wide, "
+                             "2 residual blocks",
+                    "wide": "training step fwd + MSE + bwd + Adam, dropout 0.5, batch {b}/GPU, synced BatchNorm, widened lifter "
+                            "(16 x 34 inputs, 2048-wide, 4 residual blocks)",
+                    "phase5": "phase-5 loop body around the lifter (backup_june8.py:120-175), {b} poses/GPU: 4 train-mode lifter "
+                              "forwards (predicted / ground-truth 2D, each with its flipped twin), flip averaging, TriangleLoss "
+                              "+ pinhole-reprojection and bone-length terms (parity unpinned) on synthetic H36M intrinsics, "
+                              "backward into the lifter and the predicted 2D / 3D inputs, AdamW"}[workload].format(b=batch)
+            cfg = {"workload": f"{WORKLOADS[workload]}: {what}", "batch_per_gpu": batch, "global_batch": batch * world,
+                   "parallelism": par, "cuda_graph": bool(tr.use_graph),
+                   "l2": "one step touches >= 0.4 GB of saved activations and gradients per GPU (> 126 MB L2), so "
                          "consecutive steps do not find their inputs in L2; no explicit flush"}
-            flop = FLOP_PER_POSE_TRAIN if workload == "train" else FLOP_PER_POSE_WIDE_TRAIN
+            flop = {"train": FLOP_PER_POSE_TRAIN, "wide": FLOP_PER_POSE_WIDE_TRAIN, "phase5": FLOP_PER_POSE_PHASE5}[workload]
 
         def timed(fn, steps, warmup):
             for _ in range(warmup):
@@ -246,27 +403,28 @@ def gpu_arm(args, rank, world, local_rank):
                 fn()
             e1.record()
             barrier()
-            ms = e0.elapsed_time(e1) / steps
-            if world > 1:
-                t = torch.tensor([ms], device=dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                ms = t.item()
-            return ms
+            return max_over_ranks(e0.elapsed_time(e1) / steps)
 
         step()                                                 # builds buffers / captures the step graph untimed
         barrier()
+        sustained = None
         if with_clocks:
             with ClockSampler(local_rank) as clk:
                 ms = timed(step, steps, warmup)
                 in_region = len(clk.samples)
-                # nvidia-smi answers every ~0.1 s: a timed region shorter than ~1.5 s is extended with identical untimed
-                # steps (same load).  The count derives from the max-over-ranks step time, so every rank runs the same
-                # number of (collective) steps.
-                for _ in range(max(0, int(1500.0 / max(ms, 1e-3)) - steps)):
-                    step()
-                torch.cuda.synchronize()
+                # nvidia-smi answers every ~0.1 s, so a 20-step region sees no sample.  The same step therefore runs on
+                # for >= 1.5 s as a second, separately timed region ("sustained").  Its step count derives from the
+                # max-over-ranks step time, so every rank runs the same number of (exchanging) steps.
+                n_sus = max(steps, int(1500.0 / max(ms, 1e-3)))
+                first = len(clk.samples)
+                ms_sus = timed(step, n_sus, 0)
+                last = len(clk.samples)
             clocks = clk.summary()
             clocks["samples_in_timed_region"] = in_region
+            sc = clk.summary(first, last)
+            sc["samples_in_timed_region"] = sc.pop("samples")
+            sustained = {"ms_per_step": ms_sus, "steps": n_sus, "seconds": ms_sus * n_sus / 1e3,
+                         "value": batch * world / (ms_sus / 1e3), "unit": "poses/s", "clocks": sc}
         else:
             ms, clocks = timed(step, steps, warmup), None
 
@@ -277,51 +435,101 @@ def gpu_arm(args, rank, world, local_rank):
         n_e2e = max(3, steps // 2)
         run_e2e(n_e2e)
         barrier()
-        e2e_ms = (time.perf_counter() - t0) / n_e2e * 1e3
-        if world > 1:
-            t = torch.tensor([e2e_ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            e2e_ms = t.item()
+        e2e_ms = max_over_ranks((time.perf_counter() - t0) / n_e2e * 1e3)
 
         roof = None
         if rank == 0:   # dominant kernel alone: the H x H tcgen05 GEMM at this workload's per-launch shape
             roof = gemm_roofline(cabi, dev, batch, cabi.FMT_F16 if workload == "eval" else cabi.FMT_BF16, pk,
-                                 WIDE[1] if workload == "wide" else H)
+                                 WIDE[1] if workload == "wide" else H, profiling)
+        launches = tr.graph_launches() if tr is not None else model.infer_launches(batch)
         value = batch * world / (ms / 1e3)
         return {"metric": "lifted poses/sec" + (" (eval inference)" if workload == "eval" else " (fwd+bwd+Adam)"),
                 "value": value, "unit": "poses/s", "n_gpus": world, "steps": steps, "warmup": warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype,
                 "data": "synthetic (H36M-shaped keypoints from the repo's mean/std statistics, random-init weights)",
-                "config": cfg, "clocks": clocks,
+                "config": cfg, "clocks": clocks, "sustained": sustained,
                 "e2e": {"value": batch * world / (e2e_ms / 1e3), "unit": "poses/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
-                "gpu_launches": launches_per_step * steps,
+                "gpu_launches": launches * steps, "gpu_launches_per_step": launches,
                 "model_flop_per_pose": flop,
                 "model_tflops": value * flop / 1e12 / world,
+                "step_roofline_frac": {"burst": value * flop / 1e12 / world / pk["bf16"],
+                                       "sustained": value * flop / 1e12 / world / pk["bf16_sustained"]},
                 "roofline": roof,
-                "roofline_hbm": hbm_rooflines(cabi, dev, pk, batch) if (rank == 0 and workload != "eval") else None}
+                "roofline_hbm": hbm_rooflines(cabi, dev, pk, batch) if (rank == 0 and workload == "train" and not profiling) else None}
+
+    def dp_check(workload, k=3):
+        """N data-parallel ranks == one process on the concatenated global batch (SURVEY §8c multi-GPU oracle), on the
+        exact path that was just timed (graph replay, in-kernel SyncBN exchange, per-layer reduce-scatter/Adam/all-gather
+        on the side stream)."""
+        batch, lr = TRAIN_BATCH, 1e-3
+        glob = [[torch.cat([t for t in col]) for col in zip(*[host_batch(workload, batch, 1000 * s + r) for r in range(world)])]
+                for s in range(k)]
+        # data parallel
+        m = build_model(workload)
+        p0 = m._flat.clone()
+        tr = build_trainer(workload, m, lr=lr)
+        losses = []
+        for s in range(k):
+            tr.step(*[t[rank * batch:(rank + 1) * batch].to(dev) for t in glob[s]])
+            losses.append(tr.loss_value())
+        torch.cuda.synchronize()
+        dp_flat, dp_rm = m._flat.clone(), m._rm.clone()
+        del tr
+        # single process, global batch (every rank computes it: same answer everywhere, nothing to ship)
+        ref = build_model(workload)
+        tr_ref = build_trainer(workload, ref, lr=lr, dp=False)
+        ref_losses = []
+        for s in range(k):
+            tr_ref.step(*[t.to(dev) for t in glob[s]])
+            ref_losses.append(tr_ref.loss_value())
+        torch.cuda.synchronize()
+        loss_err = max(abs(a - b) / abs(b) for a, b in zip(losses, ref_losses))
+        pd = ((dp_flat - ref._flat).norm() / ref._flat.norm()).item()
+        ud = ((dp_flat - ref._flat).norm() / (ref._flat - p0).norm()).item()
+        rmd = (dp_rm - ref._rm).abs().max().item()
+        other = dp_flat.clone()
+        dist.broadcast(other, src=0)
+        same = torch.tensor([1.0 if torch.equal(other, dp_flat) else 0.0], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        vals = torch.tensor([loss_err, pd, ud, rmd], device=dev, dtype=torch.float64)
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+        loss_err, pd, ud, rmd = [float(v) for v in vals]
+        ok = loss_err < 2e-3 and pd < 2e-3 and rmd < 1e-3 and bool(same.item())
+        return {"world": world, "steps": k, "batch_per_gpu": batch, "lr": lr, "loss_rel_err": loss_err, "param_rel_diff": pd,
+                "update_rel_diff": ud, "running_mean_max_diff": rmd, "replicas_identical": bool(same.item()),
+                "tolerance": {"loss_rel_err": 2e-3, "param_rel_diff": 2e-3, "running_mean_max_diff": 1e-3}, "ok": ok,
+                "losses_dp": losses, "losses_single_process": ref_losses}
 
     line = measure(args.workload, args.steps, args.warmup, True)
-    profiling = bool(os.environ.get("LIFTER_BENCH_NO_CPU"))     # under ncu: skip the untimed extras
     if args.workload == "train" and world == 1 and not profiling:
         # the same lifter in eval mode (BASELINE.json configs[1]), reported beside the headline training number
         inf = measure("eval", args.steps, args.warmup, False)
         line["inference"] = {k: inf[k] for k in ("metric", "value", "unit", "ms_per_step", "dtype", "e2e", "roofline",
-                                                 "model_tflops")}
+                                                 "model_tflops", "gpu_launches_per_step")}
         line["inference"]["workload"] = inf["config"]["workload"]
+    ok = True
+    if world > 1 and args.workload != "eval" and not profiling:
+        line["dp_check"] = dp_check(args.workload)
+        ok = line["dp_check"]["ok"]
     if rank == 0:
-        line["cpu_baseline"] = None if profiling else cpu_arm(args.workload, steps=8, warmup=1)
+        line["cpu_baseline"] = None if (profiling or world > 1) else cpu_arm(args.workload, steps=4, warmup=1, budget_s=20.0)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if not ok:
+        sys.exit(1)
 
 
 def ncu_traffic(rows, width):
     """DRAM bytes of one launch of the dominant kernel from the committed `ncu --set full` capture (profiles/), which
-    was taken on the training bench (M=8192, N=K=1024); null for any other shape."""
-    path = os.path.join(ROOT, "profiles", "r01_train_gemm_ncu_full_raw_v6.csv")
-    if rows != TRAIN_BATCH or width != H or not os.path.exists(path):
+    was taken on the training bench (M=8192, N=K=1024) or the eval bench (M=65536); null for any other shape."""
+    name = {TRAIN_BATCH: "train", EVAL_BATCH: "eval"}.get(rows)
+    cands = [os.path.join(ROOT, "profiles", f"r02_{name}_gemm_ncu_full_raw.csv"),
+             os.path.join(ROOT, "profiles", "r01_train_gemm_ncu_full_raw_v6.csv") if name == "train" else ""]
+    path = next((p for p in cands if p and os.path.exists(p)), None)
+    if name is None or width != H or path is None:
         return {"traffic": None}
     import csv
     with open(path, newline="") as f:
@@ -329,17 +537,17 @@ def ncu_traffic(rows, width):
     head, units, vals = rows_[0], rows_[1], rows_[2]
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     total = 0.0
-    for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-        i = head.index(name)
+    for nm in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        i = head.index(nm)
         total += float(vals[i]) * scale[units[i]]
     return {"traffic": total, "traffic_unit": "bytes/launch",
-            "traffic_source": "profiles/r01_train_gemm_ncu_full_raw_v6.csv (dram read + write; the 16 MB output was "
-                              "still in L2 when the kernel ended)",
+            "traffic_source": os.path.relpath(path, ROOT) + " (dram read + write of one launch)",
             "algorithmic_bytes": float(rows * width * 2 * 2 + width * width * 2)}
 
 
-def gemm_roofline(cabi, dev, rows, fmt, pk, H=H):
-    """CUDA-event time of the dominant kernel (rows x 1024 x 1024 tcgen05 GEMM with the fused epilogue)."""
+def gemm_roofline(cabi, dev, rows, fmt, pk, H=H, profiling=False):
+    """CUDA-event time of the dominant kernel (rows x H x H tcgen05 GEMM with the fused epilogue), and cuBLAS
+    (torch.matmul, library reference point -- not on any product path) at the same shape, timed the same way."""
     import ctypes as C
 
     import torch
@@ -357,22 +565,31 @@ def gemm_roofline(cabi, dev, rows, fmt, pk, H=H):
         d.M, d.N, d.K, d.fmt, d.out_mode, d.D, d.ldd = rows, H, H, fmt, cabi.OUT_16, D.data_ptr(), H
         d.splits, d.relu, d.scale, d.shift = 1, 1, scale.data_ptr(), shift.data_ptr()
         cabi.check(cabi.lib().lifter_gemm(C.byref(d), stream))
-    for i in range(5):
-        launch(i)
-    torch.cuda.synchronize()
-    n = 30
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(n):
-        launch(i)
-    e1.record()
-    torch.cuda.synchronize()
-    us = e0.elapsed_time(e1) / n * 1e3
+
+    def time_us(fn, n=30):
+        for i in range(5):
+            fn(i)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(n):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n * 1e3
+    us = time_us(launch)
     flops = 2.0 * rows * H * H
     achieved = flops / (us * 1e-6) / 1e12
-    return {"bound": "tensor", "kernel": f"lifter_gemm_kernel<256, 2-SM> M={rows} N=K={H} (+affine+ReLU epilogue)",
-            "achieved": achieved, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"],
-            "peak_source": pk["source"] + " burst bf16 (kernel timed alone)", "us_per_launch": us, **ncu_traffic(rows, H)}
+    out = {"bound": "tensor", "kernel": f"lifter_gemm_kernel<256, 2-SM> M={rows} N=K={H} (+affine+ReLU epilogue)",
+           "achieved": achieved, "peak": pk["bf16"], "unit": "TFLOP/s", "frac": achieved / pk["bf16"],
+           "peak_source": pk["source"] + " burst bf16 (kernel timed alone)", "us_per_launch": us, **ncu_traffic(rows, H)}
+    if not profiling:
+        Wt = W.t()
+        us_lib = time_us(lambda i: torch.matmul(As[i % nbuf], Wt, out=D))
+        out["library_point"] = {"what": "cuBLAS via torch.matmul at the same shape and operand type, no epilogue; context "
+                                        "only, not on any product path", "us_per_launch": us_lib,
+                                "achieved": flops / (us_lib * 1e-6) / 1e12, "unit": "TFLOP/s"}
+    return out
 
 
 def hbm_rooflines(cabi, dev, pk, batch):
@@ -398,6 +615,7 @@ def hbm_rooflines(cabi, dev, pk, batch):
         torch.cuda.synchronize()
         return e0.elapsed_time(e1) / reps * 1e3
     out = []
+
     def adam():
         p, g, m, v = sets[tick[0] % 3]
         tick[0] += 1
@@ -414,6 +632,7 @@ def hbm_rooflines(cabi, dev, pk, batch):
     dpreds = [torch.empty(batch, O_DIM, device=dev) for _ in range(nrot)]
     scratch = torch.empty(cabi.check(lib.lifter_loss_scratch_bytes(batch, 17)), dtype=torch.uint8, device=dev)
     res = torch.zeros(18, device=dev)
+
     def loss():
         i = tick[0] % nrot
         tick[0] += 1
@@ -421,7 +640,7 @@ def hbm_rooflines(cabi, dev, pk, batch):
                                    cabi.ptr(dpreds[i]), cabi.ptr(scratch), cabi.ptr(res), 0, st))
     us = time_us(loss)
     gbs = 612.0 * batch / (us * 1e-6) / 1e9
-    out.append({"bound": "hbm", "kernel": f"fused_loss_kernel + loss_finalize_kernel, {batch} poses (612 B/pose = "
+    out.append({"bound": "hbm", "kernel": f"fused loss + gradient + metric, {batch} poses (612 B/pose = "
                 f"{612 * batch / 1e6:.1f} MB: launch-latency-bound at this size)", "achieved": gbs, "peak": pk["hbm"],
                 "unit": "GB/s", "frac": gbs / pk["hbm"], "us_per_launch": us, "traffic": None})
     return out
@@ -433,7 +652,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("LIFTER_BENCH_WORKLOAD", "train"), choices=["train", "eval", "wide"])
+    ap.add_argument("--workload", default=os.environ.get("LIFTER_BENCH_WORKLOAD", "train"), choices=sorted(WORKLOADS))
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -443,16 +662,22 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        r = cpu_arm(args.workload, steps=args.steps, warmup=args.warmup, budget_s=120.0)
+        r = cpu_arm(args.workload, steps=args.steps, warmup=args.warmup, budget_s=100.0)
+        what = {"eval": "configs[1] eval inference, batch 65536", "train": "configs[2] training step, batch 8192",
+                "wide": "configs[4] widened-lifter training step, batch 8192",
+                "phase5": "configs[3] phase-5 loop body around the lifter, batch 8192"}[args.workload]
         line = {"impl": "reference", "metric": "lifted poses/sec" + (" (eval inference)" if args.workload == "eval" else " (fwd+bwd+Adam)"),
                 "value": r["value"], "unit": "poses/s", "n_gpus": args.gpus, "steps": r["steps_timed"], "warmup": args.warmup,
                 "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "fp32", "data": "synthetic (same generator as the GPU arm)",
-                "config": {"workload": {"eval": "configs[1] eval inference", "train": "configs[2] training step",
-                                        "wide": "configs[4] widened-lifter training step"}[args.workload] +
-                           "; CPU restatement of the reference module on the host cores, bounded sample: " + r["sample"]},
-                "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "config": {"workload": what + "; the reference's own PyTorch CPU path on the host cores (one process: the "
+                                              "reference has no data parallelism, n_gpus is the arm it is compared with): " + r["sample"],
+                           "batch_per_gpu": r["batch"]},
+                "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample") if k in r},
                 "e2e": {"value": r["value"], "unit": "poses/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        for k in ("c1", "reference_files", "threads", "torch"):
+            if k in r:
+                line[k] = r[k]
         print(json.dumps(line), flush=True)
         return
     gpu_arm(args, rank, world, local_rank)

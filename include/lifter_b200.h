@@ -49,6 +49,10 @@ typedef struct lifter_config {
 int lifter_version(void);
 const char* lifter_last_error(void);
 int lifter_device_check(void);                       /* 0 if the current device is sm_100 */
+const char* lifter_source_digest(void);              /* sha256 of the sources this binary was built from (build.py) */
+/* Kernel launches issued by the library so far, host-side count (a launch captured into a CUDA graph counts once, at
+ * capture): what bench.py reports as gpu_launches per step.                                                        */
+long long lifter_launch_count(void);
 
 /* ---- layout queries (host only) -------------------------------------------------------------- */
 /* Flat fp32 parameter buffer.  tensor index t: per hidden layer l (0 .. 2*num_stage):
