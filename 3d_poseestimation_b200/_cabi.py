@@ -49,7 +49,8 @@ class TrainCtx(C.Structure):
                 ("global_batch", C.c_int64), ("row_offset", C.c_int64), ("fmt", C.c_int32), ("bn_mode", C.c_int32),
                 ("apply_dropout", C.c_int32), ("step", C.c_uint32), ("seed", C.c_uint64), ("grad_out", C.c_void_p),
                 ("grad_params", C.c_void_p), ("grad_x", C.c_void_p), ("scratch", C.c_void_p),
-                ("scratch_bytes", C.c_int64), ("step_state", C.c_void_p), ("dp", C.POINTER(DpInfo))]
+                ("scratch_bytes", C.c_int64), ("step_state", C.c_void_p), ("dp", C.POINTER(DpInfo)),
+                ("calls_per_step", C.c_int32), ("call_index", C.c_int32)]
 
 
 class Optim(C.Structure):

@@ -85,7 +85,9 @@ int fill_exchange(const Layout& lay, const lifter_train_ctx_t* t, int site, Sync
     LIFTER_REQUIRE(d->world <= DP_MAX_WORLD && d->rank >= 0 && d->rank < d->world, "dp: world %d / rank %d out of range",
                    d->world, d->rank);
     LIFTER_REQUIRE(t->step_state != nullptr, "dp: the in-kernel BatchNorm exchange needs the device step state");
-    ex->world = d->world; ex->rank = d->rank; ex->site = site; ex->nsites = 2 * lay.L;
+    const int calls = t->calls_per_step > 0 ? t->calls_per_step : 1;
+    ex->world = d->world; ex->rank = d->rank;
+    ex->site = t->call_index * 2 * lay.L + site; ex->nsites = 2 * lay.L * calls;
     for (int p = 0; p < d->world; ++p) {
         LIFTER_REQUIRE(d->sync[p] != nullptr, "dp: null peer buffer %d", p);
         ex->data[p] = d->sync[p];
@@ -152,6 +154,8 @@ int check_ctx(const lifter_config_t* cfg, const lifter_train_ctx_t* t, Layout* l
     LIFTER_REQUIRE(t->batch >= 1 && t->batch < (1ll << 31), "train: batch %lld out of range", static_cast<long long>(t->batch));
     LIFTER_REQUIRE(t->global_batch >= t->batch, "train: global_batch < batch");
     LIFTER_REQUIRE(t->fmt == FMT_F16 || t->fmt == FMT_BF16, "train: unknown operand format %d", t->fmt);
+    LIFTER_REQUIRE(t->calls_per_step >= 0 && t->call_index >= 0 && t->call_index < (t->calls_per_step > 0 ? t->calls_per_step : 1),
+                   "train: call_index %d outside calls_per_step %d", t->call_index, t->calls_per_step);
     LIFTER_REQUIRE(t->params && t->operands && t->saved, "train: null pointer");
     LIFTER_REQUIRE((reinterpret_cast<uintptr_t>(t->saved) & 255) == 0, "train: workspace must be 256-byte aligned");
     SavedWs s;
@@ -275,6 +279,8 @@ static int fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     a.apply_dropout = t->apply_dropout && cfg->p_dropout > 0.0f; a.p = cfg->p_dropout;
     a.seed = t->seed; a.step = t->step; a.site = static_cast<unsigned>(l); a.row_offset = t->row_offset;
     a.step_dev = t->step_state != nullptr ? reinterpret_cast<const unsigned*>(t->step_state) : nullptr;
+    a.step_mul = t->calls_per_step > 0 ? static_cast<unsigned>(t->calls_per_step) : 1u;
+    a.step_add = static_cast<unsigned>(t->call_index);
     a.a = w.a[l]; a.bits = w.bits[l];
     LIFTER_PROPAGATE(bn_apply_fwd(a, st));
     return LIFTER_OK;

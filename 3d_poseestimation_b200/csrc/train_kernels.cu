@@ -222,118 +222,92 @@ __global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, co
 // BN affine + ReLU + Philox dropout (+ block residual): a = drop(relu(z * scale + shift)) [+ resid], and one bit per
 // element "ReLU-active AND kept" for the backward pass.  1/(1-p) is folded into scale/shift (it is positive, so the
 // ReLU decision is unchanged).
-// Per-thread cursor of the apply kernel: byte-free pointer bumps instead of 64-bit row * H products per access.
-struct ApplyCursor {
-    const uint16_t* z; const uint16_t* r; uint16_t* a; uint8_t* bits;
-    uint32_t row;              // global row of unroll slot 0 (Philox counter word 0)
-    long left;                 // rows of this thread's walk that are still in range, counted in units of `rpb` rows
-};
+//
+// A thread owns 8 columns and walks AP_ROWS = 16 CONSECUTIVE rows per group: that is the footprint of one Philox call
+// with one-bit lanes (p = 0.5, philox.cuh), so the generator costs one call per 128 elements instead of one per 8 and
+// the kernel is bound by its loads and stores, not by instruction issue (round 1: 13.7 us per 8,192 x 1,024 layer at
+// 50 % issue utilisation).  The rows of a group are loaded AP_SUB at a time, the next sub-batch in flight while the
+// current one is computed; a warp instruction still touches 32 x 16 contiguous bytes of one row.
+constexpr int AP_ROWS = 16;
+constexpr int AP_SUB = 4;
 
-template <int FMT, bool FULL>
-__device__ __forceinline__ void apply_load(const ApplyCursor& c, long su, long left, bool has_resid,
-                                           uint4 (&zq)[EW_UNROLL], uint4 (&rq)[EW_UNROLL]) {
-#pragma unroll
-    for (int u = 0; u < EW_UNROLL; ++u) {
-        if (!FULL) { zq[u] = make_uint4(0, 0, 0, 0); rq[u] = make_uint4(0, 0, 0, 0); }
-        if (FULL || u < left) {
-            zq[u] = ldg_stream(c.z + u * su);
-            if (has_resid) rq[u] = ldg_stream(c.r + u * su);
-        }
-    }
-}
-
-template <int FMT, bool FULL>
-__device__ __forceinline__ void apply_compute(const ApplyCursor& c, long su, long sb, long left, int rpb, bool has_resid,
-                                              bool dropout, uint32_t group, uint32_t site, uint32_t dstep,
-                                              uint32_t thr_hi, const PhiloxKeys& keys, const float (&sc)[8],
-                                              const float (&sh)[8], const uint4 (&zq)[EW_UNROLL],
-                                              const uint4 (&rq)[EW_UNROLL]) {
-#pragma unroll
-    for (int u = 0; u < EW_UNROLL; ++u) {
-        if (!FULL && u >= left) break;
-        float z[8];
-        unpack8(zq[u], FMT, z);
-        uint32_t w[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};     // no dropout: every lane keeps
-        if (dropout) {
-            const Philox4 r4 = philox4x32_10(c.row + static_cast<uint32_t>(u * rpb), group, site, dstep, keys);
-            w[0] = r4.x; w[1] = r4.y; w[2] = r4.z; w[3] = r4.w;
-        }
-        float out[8];
-        uint32_t active = 0;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const float y = fmaf(z[e], sc[e], sh[e]);
-            const bool on = dropout_keep_lane(w, e, thr_hi) && (y > 0.0f);
-            active |= on ? (1u << e) : 0u;
-            out[e] = on ? y : 0.0f;
-        }
-        if (has_resid) {
-            float r[8];
-            unpack8(rq[u], FMT, r);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) out[e] += r[e];
-        }
-        *reinterpret_cast<uint4*>(c.a + u * su) = pack8(out, FMT);
-        c.bits[u * sb] = static_cast<uint8_t>(active);
-    }
-}
-
-template <int FMT, bool FULL>
-__device__ __forceinline__ void apply_walk(const BnApplyFwd& a, long base, long end, uint32_t threshold, float inv_keep,
-                                           const PhiloxKeys& keys) {
+template <int FMT>
+__global__ void __launch_bounds__(EW_THREADS, 2) bn_apply_fwd_kernel(BnApplyFwd a, int rows_per_block, DropoutLanes lanes,
+                                                                  float inv_keep, const PhiloxKeys keys) {
+    griddep_launch();
+    griddep_wait();
     const int tpr = a.H >> 3;
     const int rpb = EW_THREADS / tpr;
     const int cg = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long end = min(base + rows_per_block, static_cast<long>(a.rows));
     float sc[8], sh[8];
     load8f(a.scale + cg * 8, sc);
     load8f(a.shift + cg * 8, sh);
 #pragma unroll
     for (int e = 0; e < 8; ++e) { sc[e] *= inv_keep; sh[e] *= inv_keep; }
-    const uint32_t dstep = a.step_dev != nullptr ? *a.step_dev : a.step;
-    const uint32_t thr_hi = threshold << 16;
+    const uint32_t dstep = (a.step_dev != nullptr ? *a.step_dev : a.step) * a.step_mul + a.step_add;
     const bool has_resid = a.resid != nullptr, dropout = a.apply_dropout != 0;
-    const long su = static_cast<long>(rpb) * a.H;                 // elements between unroll slots
-    const long sb = static_cast<long>(rpb) * tpr;                 // mask bytes between unroll slots
-    const long first = base + rl;
-    ApplyCursor c;
-    c.z = static_cast<const uint16_t*>(a.z) + first * a.H + cg * 8;
-    c.r = has_resid ? static_cast<const uint16_t*>(a.resid) + first * a.H + cg * 8 : nullptr;
-    c.a = static_cast<uint16_t*>(a.a) + first * a.H + cg * 8;
-    c.bits = a.bits + first * tpr + cg;
-    c.row = static_cast<uint32_t>(first + a.row_offset);
-    long left = first < end ? (end - first + rpb - 1) / rpb : 0;  // slots (of stride rpb rows) this thread owns
-    // two register buffers: the loads of the next group are in flight while this one is computed
-    uint4 z0[EW_UNROLL], q0[EW_UNROLL], z1[EW_UNROLL], q1[EW_UNROLL];
-    ApplyCursor n = c;
-    auto advance = [&](ApplyCursor& k) {
-        k.z += su * EW_UNROLL; if (has_resid) k.r += su * EW_UNROLL;
-        k.a += su * EW_UNROLL; k.bits += sb * EW_UNROLL; k.row += static_cast<uint32_t>(rpb * EW_UNROLL);
-    };
-    if (left > 0) apply_load<FMT, FULL>(n, su, left, has_resid, z0, q0);
-    while (left > 0) {
-        advance(n);
-        if (left > EW_UNROLL) apply_load<FMT, FULL>(n, su, left - EW_UNROLL, has_resid, z1, q1);
-        apply_compute<FMT, FULL>(c, su, sb, left, rpb, has_resid, dropout, cg, a.site, dstep, thr_hi, keys, sc, sh, z0, q0);
-        c = n; left -= EW_UNROLL;
-        if (left <= 0) break;
-        advance(n);
-        if (left > EW_UNROLL) apply_load<FMT, FULL>(n, su, left - EW_UNROLL, has_resid, z0, q0);
-        apply_compute<FMT, FULL>(c, su, sb, left, rpb, has_resid, dropout, cg, a.site, dstep, thr_hi, keys, sc, sh, z1, q1);
-        c = n; left -= EW_UNROLL;
-    }
-}
+    const uint32_t rmask = (1u << lanes.rows_shift) - 1u;
+    const long H = a.H;
 
-template <int FMT>
-__global__ void __launch_bounds__(EW_THREADS, 2) bn_apply_fwd_kernel(BnApplyFwd a, int rows_per_block, uint32_t threshold,
-                                                                  float inv_keep, const PhiloxKeys keys) {
-    griddep_launch();
-    griddep_wait();
-    const int rpb = EW_THREADS / (a.H >> 3);
-    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
-    const long end = min(base + rows_per_block, static_cast<long>(a.rows));
-    // a block whose row count is a whole number of (rpb * EW_UNROLL)-row groups needs no per-row range checks
-    if ((end - base) % (static_cast<long>(rpb) * EW_UNROLL) == 0) apply_walk<FMT, true>(a, base, end, threshold, inv_keep, keys);
-    else apply_walk<FMT, false>(a, base, end, threshold, inv_keep, keys);
+    for (long g0 = base + static_cast<long>(rl) * AP_ROWS; g0 < end; g0 += static_cast<long>(rpb) * AP_ROWS) {
+        const int n = static_cast<int>(min(static_cast<long>(AP_ROWS), end - g0));
+        const uint16_t* zp = static_cast<const uint16_t*>(a.z) + g0 * H + cg * 8;
+        const uint16_t* rp = has_resid ? static_cast<const uint16_t*>(a.resid) + g0 * H + cg * 8 : nullptr;
+        uint16_t* ap = static_cast<uint16_t*>(a.a) + g0 * H + cg * 8;
+        uint8_t* bp = a.bits + g0 * tpr + cg;
+        const uint32_t grow0 = static_cast<uint32_t>(g0 + a.row_offset);          // global row of this group's first row
+        uint4 zq[2][AP_SUB], rq[2][AP_SUB];
+        auto load = [&](int s, uint4 (&zb)[AP_SUB], uint4 (&rb)[AP_SUB]) {
+#pragma unroll
+            for (int u = 0; u < AP_SUB; ++u) {
+                const int r = s * AP_SUB + u;
+                zb[u] = make_uint4(0, 0, 0, 0);
+                rb[u] = make_uint4(0, 0, 0, 0);
+                if (r < n) {
+                    zb[u] = ldg_stream(zp + r * H);
+                    if (has_resid) rb[u] = ldg_stream(rp + r * H);
+                }
+            }
+        };
+        Philox4 rnd = {0u, 0u, 0u, 0u};
+        load(0, zq[0], rq[0]);
+#pragma unroll
+        for (int s = 0; s < AP_ROWS / AP_SUB; ++s) {
+            if ((s + 1) * AP_SUB < n) load(s + 1, zq[(s + 1) & 1], rq[(s + 1) & 1]);
+#pragma unroll
+            for (int u = 0; u < AP_SUB; ++u) {
+                const int r = s * AP_SUB + u;
+                if (r >= n) break;
+                const uint32_t grow = grow0 + static_cast<uint32_t>(r);
+                uint32_t keep = 0xFFu;
+                if (dropout) {
+                    if (r == 0 || (grow & rmask) == 0u)                      // first row of a call's footprint
+                        rnd = philox4x32_10(grow >> lanes.rows_shift, static_cast<uint32_t>(cg), a.site, dstep, keys);
+                    keep = dropout_keep8(rnd, grow, lanes.bits, lanes.threshold);
+                }
+                float z[8], out[8];
+                unpack8(zq[s & 1][u], FMT, z);
+                uint32_t active = 0;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const float y = fmaf(z[e], sc[e], sh[e]);
+                    const bool on = ((keep >> e) & 1u) && (y > 0.0f);
+                    active |= on ? (1u << e) : 0u;
+                    out[e] = on ? y : 0.0f;
+                }
+                if (has_resid) {
+                    float rr[8];
+                    unpack8(rq[s & 1][u], FMT, rr);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) out[e] += rr[e];
+                }
+                *reinterpret_cast<uint4*>(ap + r * H) = pack8(out, FMT);
+                bp[static_cast<long>(r) * tpr] = static_cast<uint8_t>(active);
+            }
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------- backward passes
@@ -711,19 +685,20 @@ static int check_h(int H, const char* what) {
 
 int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st) {
     LIFTER_PROPAGATE(check_h(a.H, "bn_apply"));
-    const uint32_t thr = dropout_threshold(a.p);
+    const DropoutLanes lanes = dropout_lanes(a.p);
     const PhiloxKeys keys = philox_round_keys(a.seed);
     const float inv_keep = (a.apply_dropout && a.p < 1.0f) ? 1.0f / (1.0f - a.p) : (a.apply_dropout ? 0.0f : 1.0f);
-    // whole unrolled groups per block keep the unchecked fast path; when that leaves more than a tenth of the resident
-    // block slots empty (small batches), even filling wins over the per-row range checks
-    int rpb = rows_per_block_for(a.rows, a.H, 4, true);
-    const long slots = static_cast<long>(num_sms()) * 4;
-    if ((a.rows + rpb - 1) / rpb < slots - slots / 10) rpb = rows_per_block_for(a.rows, a.H, 4, false);
+    // a block owns whole 16-row groups; up to four blocks per SM's worth of them, filled evenly
+    const int64_t group = static_cast<int64_t>(EW_THREADS / (a.H / 8)) * AP_ROWS;
+    const int64_t groups = (a.rows + group - 1) / group;
+    const int64_t max_blocks = static_cast<int64_t>(num_sms()) * 4;
+    const int64_t per_block = (groups + max_blocks - 1) / max_blocks;
+    const int rpb = static_cast<int>(per_block * group);
     const unsigned blocks = static_cast<unsigned>((a.rows + rpb - 1) / rpb);
     if (a.fmt == FMT_BF16)
-        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_BF16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, thr, inv_keep, keys));
+        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_BF16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, lanes, inv_keep, keys));
     else
-        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_F16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, thr, inv_keep, keys));
+        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_kernel", bn_apply_fwd_kernel<FMT_F16>, dim3(blocks), dim3(EW_THREADS), 0, st, a, rpb, lanes, inv_keep, keys));
     return LIFTER_OK;
 }
 

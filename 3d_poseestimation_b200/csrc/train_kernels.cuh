@@ -51,6 +51,8 @@ struct BnApplyFwd {
     int64_t rows; int H; int fmt;
     int apply_dropout; float p; unsigned long long seed; unsigned step, site; long long row_offset;
     const unsigned* step_dev;   // nullable: the dropout step is read from device memory (graph replay)
+    unsigned step_mul = 1, step_add = 0;   // Philox step = (device or host step) * step_mul + step_add: a training step
+                                           // that runs several lifter forwards (phase-5 loop) gives each its own masks
     void* a; uint8_t* bits;     // a [rows][H] 16-bit, bits [rows][H/8]: relu-active AND kept
 };
 int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st);

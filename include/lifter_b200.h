@@ -143,6 +143,12 @@ typedef struct lifter_train_ctx {
     const struct lifter_step_state* step_state; /* nullable, DEVICE memory: the dropout step is read from it at run
                                                   time instead of `step` (a captured CUDA graph replays every step) */
     const lifter_dp_t* dp;          /* nullable: in-kernel synchronised BatchNorm over dp->world GPUs (host struct)   */
+    /* A training step that runs SEVERAL lifter forwards (the phase-5 loop: predicted / ground-truth key points and their
+     * flipped twins, backup_june8.py:137-154) gives each call its own dropout masks and its own slots of the SyncBN
+     * exchange buffer: Philox step = step * calls_per_step + call_index; dp->sync must then hold calls_per_step times
+     * lifter_dp_sync_bytes().  0 / 0 = one call per step.                                                           */
+    int32_t calls_per_step;
+    int32_t call_index;
 } lifter_train_ctx_t;
 
 int64_t lifter_train_saved_bytes(const lifter_config_t* cfg, int64_t batch);

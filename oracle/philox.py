@@ -7,11 +7,14 @@ that a data-parallel run sees the masks of the single-process global batch.  Thi
 is the bit-exact CPU twin of ``csrc/philox.cuh``; ``oracle/make_golden.py`` feeds these
 masks into the *reference* module (dropout patched) to pin training parity.
 
-Stream definition (one call yields eight 16-bit lanes = eight consecutive columns):
-    counter = (row, col // 8, site, step)      key = (seed_lo, seed_hi)
-    r0..r3  = Philox4x32-10(counter, key)
-    u16[e]  = (r[e // 2] >> (16 * (e % 2))) & 0xFFFF           e = col % 8
-    keep    = u16 >= floor(float32(p) * 65536 + 0.5)
+Stream definition.  One call yields 128 bits, cut into lanes of k bits, one lane per keep
+decision; k is the smallest of {1, 8, 16} that represents p exactly (p == 0.5: k = 1;
+p a multiple of 1/256: k = 8; else k = 16, p rounded to 1/65536).  A call covers
+R = 16 / k consecutive rows of 8 consecutive columns:
+    counter = (row // R, col // 8, site, step)      key = (seed_lo, seed_hi)
+    r0..r3  = Philox4x32-10(counter, key)           bits = r0 | r1 << 32 | r2 << 64 | r3 << 96
+    lane    = (row % R) * 8 + col % 8               value = (bits >> (lane * k)) & (2^k - 1)
+    keep    = value >= floor(float32(p) * 2^k + 0.5)
 """
 import numpy as np
 
@@ -39,10 +42,18 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
     return tuple(c.astype(np.uint32) for c in (c0, c1, c2, c3))
 
 
-def dropout_threshold(p):
-    """round-half-up of float32(p) * 65536, clipped to [0, 65536] (same expression as csrc/philox.cuh)."""
-    t = float(np.float32(p)) * 65536.0
-    return int(min(max(int(np.floor(t + 0.5)), 0), 65536))
+def dropout_lanes(p):
+    """(k, R, threshold) for dropout probability p: lane width in bits, rows per call, keep <=> value >= threshold
+    (same expressions as ``dropout_lanes`` in csrc/philox.cuh)."""
+    p = float(np.float32(p))
+    if p == 0.5:
+        k = 1
+    elif p * 256.0 == np.floor(p * 256.0):
+        k = 8
+    else:
+        k = 16
+    t = int(min(max(int(np.floor(p * float(1 << k) + 0.5)), 0), 1 << k))
+    return k, 16 // k, t
 
 
 def dropout_keep_mask(rows, cols, site, step, seed, p, row_offset=0):
@@ -51,11 +62,18 @@ def dropout_keep_mask(rows, cols, site, step, seed, p, row_offset=0):
     ``row_offset`` is the global index of row 0 (data-parallel shards pass their offset).
     """
     assert cols % 8 == 0
-    r = (np.arange(rows, dtype=np.uint64) + np.uint64(row_offset))[:, None]
+    k, R, thr = dropout_lanes(p)
+    grow = np.arange(rows, dtype=np.uint64) + np.uint64(row_offset)
+    r = (grow // np.uint64(R))[:, None]
     g = np.arange(cols // 8, dtype=np.uint64)[None, :]
     out = philox4x32_10(r, g, np.uint64(site), np.uint64(step & 0xFFFFFFFF),
                         seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
-    u16 = np.empty((rows, cols // 8, 8), dtype=np.uint32)
+    words = np.stack([o.astype(np.uint64) for o in out], axis=-1)          # (rows, cols/8, 4)
+    keep = np.empty((rows, cols // 8, 8), dtype=bool)
+    sub = (grow % np.uint64(R)).astype(np.int64)[:, None]                   # row inside the call
     for e in range(8):
-        u16[:, :, e] = (out[e // 2] >> np.uint32(16 * (e % 2))) & np.uint32(0xFFFF)
-    return (u16.reshape(rows, cols) >= np.uint32(dropout_threshold(p)))
+        bit = (sub * 8 + e) * k                                            # first bit of the lane, (rows, 1)
+        w = np.take_along_axis(words, np.broadcast_to((bit // 32)[..., None], (rows, cols // 8, 1)), axis=-1)[..., 0]
+        val = (w >> (bit % 32).astype(np.uint64)) & np.uint64((1 << k) - 1)
+        keep[:, :, e] = val >= np.uint64(thr)
+    return keep.reshape(rows, cols)

@@ -249,3 +249,23 @@ def test_vit_oracle_gradients_match_reference_module(golden_dir, tag, cfg):
     np.testing.assert_allclose([float(params[n].grad.double().sum()) for n in names], g[tag + "_grad_sums"], rtol=1e-3, atol=1e-5)
     np.testing.assert_allclose(params["linear_mapper.weight"].grad.numpy(), g[tag + "_grad_map_w"], rtol=1e-4, atol=1e-6)
     np.testing.assert_allclose(params["mlp.2.weight"].grad.numpy(), g[tag + "_grad_head_w"], rtol=1e-4, atol=1e-6)
+
+
+def test_dropout_stream_lane_widths_and_shards():
+    """oracle/philox.py (twin of csrc/philox.cuh): the lane width follows p, the keep rate is 1 - p, a data-parallel
+    shard reproduces its rows of the global stream at any offset, and sixteen-bit lanes are the round-1 definition."""
+    from oracle.philox import dropout_lanes
+    assert dropout_lanes(0.5) == (1, 16, 1) and dropout_lanes(0.25) == (8, 2, 64) and dropout_lanes(0.3)[:2] == (16, 1)
+    for p in (0.5, 0.25, 0.3, 0.0, 1.0):
+        g = dropout_keep_mask(4096, 64, 3, 11, 0x1234_5678_9ABC, p)
+        assert abs(g.mean() - (1 - p)) < 0.01
+        for off, n in ((0, 100), (16, 50), (23, 77), (4000, 96)):
+            assert (dropout_keep_mask(n, 64, 3, 11, 0x1234_5678_9ABC, p, row_offset=off) == g[off:off + n]).all()
+    # k = 16: counter (row, col // 8, site, step), lane e = (r[e // 2] >> 16 (e % 2)) & 0xFFFF, keep = lane >= round(p 65536)
+    rows, cols, site, step, seed, p = 9, 24, 2, 7, 99, 0.3
+    r = philox4x32_10(np.arange(rows, dtype=np.uint64)[:, None], np.arange(cols // 8, dtype=np.uint64)[None, :], site, step,
+                      seed & 0xFFFFFFFF, seed >> 32)
+    want = np.empty((rows, cols // 8, 8), dtype=bool)
+    for e in range(8):
+        want[:, :, e] = ((r[e // 2] >> np.uint32(16 * (e % 2))) & np.uint32(0xFFFF)) >= np.uint32(19661)
+    assert (dropout_keep_mask(rows, cols, site, step, seed, p) == want.reshape(rows, cols)).all()

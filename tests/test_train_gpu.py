@@ -125,6 +125,24 @@ def test_dropout_stream_and_no_grad_train_forward(pkg):
     assert int(m.batch_norm1.num_batches_tracked) == 3
 
 
+@pytest.mark.parametrize("p", [0.5, 0.25, 0.3])
+@pytest.mark.parametrize("row_offset", [0, 16, 24, 7])
+def test_dropout_lane_widths_and_row_offsets(pkg, p, row_offset):
+    """The mask stream of csrc/philox.cuh for every lane width (p = 0.5: 1-bit lanes, 16 rows per call; 0.25: 8-bit, 2
+    rows; 0.3: 16-bit, 1 row), with a shard offset that is / is not a multiple of the call's row footprint and a row
+    count that is not a multiple of anything: a single wrong keep decision moves an output by O(1)."""
+    H, S, B, seed = 128, 1, 203, 12
+    params, buffers = lo.numpy_init(34, 51, H, S, seed)
+    m = _model(pkg, params, buffers, 34, 51, H, S, p, True).train()
+    m.dropout_seed, m.dropout_step, m.row_offset = 77, 5, row_offset
+    x = T(np.random.RandomState(3).normal(0, 1, (B, 34)).astype(np.float32))
+    with torch.no_grad():
+        out = m(x.cuda()).cpu()
+    masks = [dropout_keep_mask(B, H, s, 5, 77, p, row_offset=row_offset) for s in range(2 * S + 1)]
+    ref, _ = lo.lifter_forward(params, buffers, x, num_stage=S, training=True, p_dropout=p, masks=masks)
+    assert rel_l2(out, ref) < 2e-2, rel_l2(out, ref)
+
+
 @pytest.mark.parametrize("kind", ["mse", "l1", "mpjpe"])
 def test_fused_loss_matches_oracle(pkg, golden_dir, kind):
     cabi = importlib.import_module("3d_poseestimation_b200._cabi")
