@@ -298,6 +298,33 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
+// ---- one-shot grid barrier -----------------------------------------------------------------------
+// Every block of a 1-D grid arrives once on `counter`, which an earlier kernel of the same stream left at zero (the
+// first kernel of a forward / backward pass zeroes the pass's barrier words).  Needs every block of the grid resident at
+// the same time: the launchers size such grids from the occupancy query, and nothing that is resident beside them waits
+// on them.  Release / acquire at gpu scope orders the blocks' global writes before the readers' loads; data written by
+// other blocks of the same launch must still be read past L1 (ld.global.cg / __ldcg).
+constexpr int GRID_BARRIER_WORDS = 32;      // barrier words reserved per pass (layers x barriers per layer)
+__device__ __forceinline__ void grid_barrier_once(unsigned* counter, unsigned nblocks) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned seen;
+        asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(seen) : "l"(counter) : "memory");
+        long long t0 = 0;
+        unsigned spins = 0;
+        while (true) {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
+            if (seen >= nblocks) break;
+            if ((++spins & 0x3FF) == 0) {                    // a grid that cannot become co-resident traps, no hang
+                const long long now = clock64();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 8000000000LL) __trap();
+            }
+        }
+    }
+    __syncthreads();
+}
+
 // ---- 16-bit packing ----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t pack16(float lo, float hi, int fmt) {
     if (fmt == FMT_BF16) {

@@ -46,9 +46,10 @@ __global__ void fold_bn_kernel(const float* __restrict__ bias, const float* __re
 
 __global__ void prep_input_kernel(const float* __restrict__ x, long rows, int I, int Ip,
                                   const float* __restrict__ mean, const float* __restrict__ stdv,
-                                  uint16_t* __restrict__ dst, int fmt) {
+                                  uint16_t* __restrict__ dst, int fmt, unsigned* __restrict__ zero_words, int n_zero) {
     griddep_launch();
     griddep_wait();
+    if (blockIdx.x == 0 && static_cast<int>(threadIdx.x) < n_zero) zero_words[threadIdx.x] = 0u;   // the pass's barrier words
     const int groups = Ip >> 3;
     const long idx = static_cast<long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= rows * groups) return;
@@ -102,12 +103,12 @@ int fold_bn(const float* bias, const float* gamma, const float* beta, const floa
 }
 
 int prep_input(const float* x, int64_t rows, int I, int Ip, const float* mean, const float* stdv, void* dst, int fmt,
-               cudaStream_t st) {
+               cudaStream_t st, unsigned* zero_words, int n_zero) {
     LIFTER_REQUIRE(Ip % 8 == 0 && Ip >= I, "prep_input: bad padding");
     LIFTER_REQUIRE((mean == nullptr) == (stdv == nullptr), "prep_input: mean and std come together");
     const long n = rows * (Ip / 8);
     LIFTER_CHECK_CUDA(launch_pdl("prep_input_kernel", prep_input_kernel, dim3(static_cast<unsigned>((n + 255) / 256)), dim3(256), 0, st, x, rows, I, Ip, mean, stdv,
-                                                                            static_cast<uint16_t*>(dst), fmt));
+                                                                            static_cast<uint16_t*>(dst), fmt, zero_words, zero_words != nullptr ? n_zero : 0));
     return LIFTER_OK;
 }
 

@@ -14,8 +14,9 @@ int fold_bn(const float* bias, const float* gamma, const float* beta, const floa
 
 // x fp32 [rows][I] (row stride I) -> 16-bit [rows][Ip] zero padded; optional (x - mean) / std per column
 // (main.py:334, the 2D keypoint standardisation).
+// zero_words (nullable): n_zero <= 256 words that the kernel also zeroes -- the grid-barrier words of the pass it opens.
 int prep_input(const float* x, int64_t rows, int I, int Ip, const float* mean, const float* stdv, void* dst, int fmt,
-               cudaStream_t st);
+               cudaStream_t st, unsigned* zero_words = nullptr, int n_zero = 0);
 
 // scale[j] = std[j] (or 1), shift[j] = bias[j] * std[j] + mean[j]  for j < O, zero beyond: the final layer's
 // bias with the de-standardisation y * std + mean (main.py:473-479) folded in.

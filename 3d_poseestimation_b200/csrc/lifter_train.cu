@@ -41,6 +41,7 @@ struct SavedWs {                        // forward workspace kept for backward
     std::vector<double*> sums;
     std::vector<size_t> sums_off;
     float *psum, *psq, *out_scale, *out_shift;
+    unsigned* bars;                     // grid-barrier words of the forward pass (zeroed by its first kernel)
     size_t bytes;
 };
 
@@ -67,6 +68,7 @@ void carve_saved(const Layout& lay, int64_t B, void* base, SavedWs* w) {
     w->psq = c.take<float>(P * lay.H * 4);
     w->out_scale = c.take<float>(64 * 4);
     w->out_shift = c.take<float>(64 * 4);
+    w->bars = c.take<unsigned>(GRID_BARRIER_WORDS * 4);
     w->bytes = c.off;
 }
 
@@ -97,6 +99,13 @@ int fill_exchange(const Layout& lay, const lifter_train_ctx_t* t, int site, Sync
     return LIFTER_OK;
 }
 
+// LIFTER_FUSE_BN=0: the BatchNorm passes of the single-call forward / backward run as separate launches again
+// (reduce + finalize, apply; stats, reduce, dz) instead of the grid-barrier kernels -- for A/B timing and bisection.
+bool fuse_bn_launches() {
+    static const bool on = [] { const char* e = getenv("LIFTER_FUSE_BN"); return !(e != nullptr && e[0] == '0'); }();
+    return on;
+}
+
 int wgrad_splits(int M, int N, int K) {
     const int bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
     const int tiles = ceil_div(M, 128) * ceil_div(N, bn);
@@ -112,6 +121,7 @@ struct ScratchWs {                      // backward workspace
     float *pA, *pB, *pO, *coef, *slabs;    // pO: output-layer bias partials (read on the side stream)
     std::vector<double*> bsums;
     std::vector<size_t> bsums_off;
+    unsigned* bars;                     // grid-barrier words of the backward pass (zeroed by its first kernel)
     size_t bytes;
 };
 
@@ -125,6 +135,8 @@ void carve_scratch(const Layout& lay, int64_t B, void* base, ScratchWs* w) {
     w->dz[0] = c.take<uint16_t>(act);
     w->dz[1] = c.take<uint16_t>(act);
     size_t R = ew_partial_rows(B, lay.H);
+    const size_t Rf = bn_bwd_fused_partial_rows(B, lay.H);
+    if (Rf > R) R = Rf;
     const size_t R64 = ew_partial_rows(B, 64);
     size_t pbytes = R * lay.H * 4;
     if (R64 * 64 * 4 > pbytes) pbytes = R64 * 64 * 4;
@@ -145,6 +157,7 @@ void carve_scratch(const Layout& lay, int64_t B, void* base, ScratchWs* w) {
     if (lay.S > 0 && hh > slab) slab = hh;
     if (oh > slab) slab = oh;
     w->slabs = c.take<float>(slab);
+    w->bars = c.take<unsigned>(GRID_BARRIER_WORDS * 4);
     w->bytes = c.off;
 }
 
@@ -235,7 +248,7 @@ static int fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_ctx_t* 
     carve_saved(lay, t->batch, t->saved, &w);
     const int B = static_cast<int>(t->batch), H = lay.H;
     const uint16_t* ops = static_cast<const uint16_t*>(t->operands);
-    if (l == 0) LIFTER_PROPAGATE(prep_input(t->x, B, lay.I, lay.Ip, nullptr, nullptr, w.a0, t->fmt, st));
+    if (l == 0) LIFTER_PROPAGATE(prep_input(t->x, B, lay.I, lay.Ip, nullptr, nullptr, w.a0, t->fmt, st, w.bars, GRID_BARRIER_WORDS));
     const bool stats = cfg->use_bn && t->bn_mode == 0;
     GemmArgs g;
     g.A = l == 0 ? w.a0 : w.a[l - 1]; g.lda = lay.in_pad(l);
@@ -268,9 +281,11 @@ static int fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     f.momentum = cfg->bn_momentum; f.eps = cfg->bn_eps; f.H = H; f.use_bn = cfg->use_bn; f.bn_mode = t->bn_mode;
     f.mean_z = w.mean_z[l]; f.rstd = w.rstd[l]; f.scale = w.scale[l]; f.shift = w.shift[l];
     if (fused) LIFTER_PROPAGATE(fill_exchange(lay, t, l, &f.ex));          // forward site l
-    if (fused && cfg->use_bn && t->bn_mode == 0)
+    const bool batch_stats = fused && cfg->use_bn && t->bn_mode == 0;
+    const bool one_launch = batch_stats && l < GRID_BARRIER_WORDS && fuse_bn_launches();
+    if (batch_stats && !one_launch)
         LIFTER_PROPAGATE(bn_reduce_finalize_fwd(w.psum, w.psq, gemm_stat_rows(static_cast<int>(t->batch)), f, w.sums[l], st));
-    else
+    else if (!batch_stats)
         LIFTER_PROPAGATE(bn_finalize_fwd(f, st));
     BnApplyFwd a;
     a.z = w.z[l]; a.scale = w.scale[l]; a.shift = w.shift[l];
@@ -282,6 +297,8 @@ static int fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     a.step_mul = t->calls_per_step > 0 ? static_cast<unsigned>(t->calls_per_step) : 1u;
     a.step_add = static_cast<unsigned>(t->call_index);
     a.a = w.a[l]; a.bits = w.bits[l];
+    if (one_launch)     // column reduction + statistics + apply behind one grid barrier: one launch instead of two
+        return bn_fwd_fused(w.psum, w.psq, gemm_stat_rows(static_cast<int>(t->batch)), f, w.sums[l], a, w.bars + l, st);
     LIFTER_PROPAGATE(bn_apply_fwd(a, st));
     return LIFTER_OK;
 }
@@ -378,7 +395,7 @@ static int bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t* t, vo
     const int B = static_cast<int>(t->batch), H = lay.H;
     const uint16_t* ops = static_cast<const uint16_t*>(t->operands);
     // grad_out -> 16-bit padded, bias gradient of the output layer
-    LIFTER_PROPAGATE(prep_grad_out(t->grad_out, B, lay.O, lay.Op, t->fmt, b.dO, b.pO, st));
+    LIFTER_PROPAGATE(prep_grad_out(t->grad_out, B, lay.O, lay.Op, t->fmt, b.dO, b.pO, st, b.bars, GRID_BARRIER_WORDS));
     // db2 and dW2 = dOut^T a_{L-1} feed only the optimiser: side stream when there is one
     if (side != nullptr) LIFTER_PROPAGATE(side_fork(side, lay.L, st));
     LIFTER_PROPAGATE(reduce_rows_f32(b.pO, ew_partial_rows(B, lay.Op), lay.O, lay.Op, t->grad_params + lay.p_off[lay.t_b2()],
@@ -427,11 +444,17 @@ static int bwd_exchange(const lifter_config_t* cfg, const lifter_train_ctx_t* t,
     return LIFTER_OK;
 }
 
+// single-call backward, batch-statistics BatchNorm: stats -> reduce -> dz of a layer run as ONE grid-barrier launch
+static bool bwd_one_launch(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, bool fused) {
+    return fused && cfg->use_bn && t->bn_mode == 0 && 2 * l + 1 < GRID_BARRIER_WORDS && fuse_bn_launches();
+}
+
 static int bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, true));
     LIFTER_REQUIRE(l >= 0 && l < lay.L, "backward: layer %d out of range", l);
     if (!cfg->use_bn) return LIFTER_OK;
+    if (bwd_one_launch(cfg, t, l, fused)) return LIFTER_OK;       // done by bwd_layer_finish
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     SavedWs w; ScratchWs b;
     carve_saved(lay, t->batch, t->saved, &w);
@@ -460,7 +483,8 @@ static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     const int B = static_cast<int>(t->batch), H = lay.H;
     const uint16_t* ops = static_cast<const uint16_t*>(t->operands);
 
-    const BnBwdFinalize f = bwd_finalize_args(cfg, t, lay, w, b, l);
+    BnBwdFinalize f = bwd_finalize_args(cfg, t, lay, w, b, l);
+    const bool one_launch = bwd_one_launch(cfg, t, l, fused);
     if (!(fused && cfg->use_bn)) LIFTER_PROPAGATE(bn_finalize_bwd(f, st));   // fused: done by bwd_layer_stats
     if (!cfg->use_bn) {                                            // the BN affine exists but is unused: zero gradient
         LIFTER_CHECK_CUDA(cudaMemsetAsync(t->grad_params + lay.p_off[lay.t_gamma(l)], 0, H * 4, st));
@@ -474,7 +498,13 @@ static int bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     uint16_t* dz = b.dz[l & 1];
     if (side != nullptr && l + 2 < lay.L)                          // dW_{l+2} still reads this buffer on the side stream
         LIFTER_CHECK_CUDA(cudaStreamWaitEvent(st, side->done[l + 2], 0));
-    LIFTER_PROPAGATE(bwd_dz(c, b.coef, dz, need_bias ? b.pA : nullptr, st));
+    if (one_launch) {
+        LIFTER_PROPAGATE(bwd_exchange(cfg, t, lay, l, fused, &f));
+        LIFTER_PROPAGATE(bn_bwd_fused(c, b.pA, b.pB, f, b.bsums[l], t->grad_params + lay.p_off[lay.t_gamma(l)],
+                                      t->grad_params + lay.p_off[lay.t_beta(l)], dz, b.bars + 2 * l, st));
+    } else {
+        LIFTER_PROPAGATE(bwd_dz(c, b.coef, dz, need_bias ? b.pA : nullptr, st));
+    }
     if (need_bias)
         LIFTER_PROPAGATE(reduce_rows_f32(b.pA, ew_partial_rows(t->batch, H), H, H, t->grad_params + lay.p_off[lay.t_bias(l)], st));
 

@@ -232,20 +232,18 @@ constexpr int AP_ROWS = 16;
 constexpr int AP_SUB = 4;
 
 template <int FMT>
-__global__ void __launch_bounds__(EW_THREADS, 2) bn_apply_fwd_kernel(BnApplyFwd a, int rows_per_block, DropoutLanes lanes,
-                                                                  float inv_keep, const PhiloxKeys keys) {
-    griddep_launch();
-    griddep_wait();
+__device__ __forceinline__ void apply_rows(const BnApplyFwd& a, long base, long end, const DropoutLanes& lanes, float inv_keep,
+                                           const PhiloxKeys& keys, const float* __restrict__ scale,
+                                           const float* __restrict__ shift) {
     const int tpr = a.H >> 3;
     const int rpb = EW_THREADS / tpr;
     const int cg = threadIdx.x % tpr, rl = threadIdx.x / tpr;
-    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
-    const long end = min(base + rows_per_block, static_cast<long>(a.rows));
     float sc[8], sh[8];
-    load8f(a.scale + cg * 8, sc);
-    load8f(a.shift + cg * 8, sh);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) { sc[e] *= inv_keep; sh[e] *= inv_keep; }
+    for (int e = 0; e < 8; ++e) {                   // past L1: another block of this launch may have written them
+        sc[e] = __ldcg(scale + cg * 8 + e) * inv_keep;
+        sh[e] = __ldcg(shift + cg * 8 + e) * inv_keep;
+    }
     const uint32_t dstep = (a.step_dev != nullptr ? *a.step_dev : a.step) * a.step_mul + a.step_add;
     const bool has_resid = a.resid != nullptr, dropout = a.apply_dropout != 0;
     const uint32_t rmask = (1u << lanes.rows_shift) - 1u;
@@ -308,6 +306,80 @@ __global__ void __launch_bounds__(EW_THREADS, 2) bn_apply_fwd_kernel(BnApplyFwd 
             }
         }
     }
+}
+
+template <int FMT>
+__global__ void __launch_bounds__(EW_THREADS, 2) bn_apply_fwd_kernel(BnApplyFwd a, int rows_per_block, DropoutLanes lanes,
+                                                                  float inv_keep, const PhiloxKeys keys) {
+    griddep_launch();
+    griddep_wait();
+    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long end = min(base + rows_per_block, static_cast<long>(a.rows));
+    apply_rows<FMT>(a, base, end, lanes, inv_keep, keys, a.scale, a.shift);
+}
+
+// ---- the column sums of the GEMM epilogue -> batch statistics -> apply, in ONE launch --------------------------------
+// Blocks first share out the second stage of the column reduction (8 columns each: fp64 sums over the GEMM's partial
+// rows, SyncBN exchange, scale / shift, running statistics), meet at a grid barrier, then every block applies
+// BN + ReLU + dropout to its rows.  Against finalize + apply as two launches this drops one kernel boundary per layer
+// from the step's critical path (~3 us each at this size).
+constexpr int FRED_LANES = EW_THREADS / RED_COLS;        // 32 row-lanes x 8 columns per block
+
+__device__ __forceinline__ void reduce_partials_block(const float* __restrict__ a, const float* __restrict__ b, int P,
+                                                      int n, int ld, int col, int lane_r,
+                                                      double (&sh)[2][FRED_LANES][RED_COLS], double& ta, double& tb) {
+    double sa = 0.0, sb = 0.0;
+    if (col < n) {
+        for (int p = lane_r; p < P; p += FRED_LANES) {
+            sa += static_cast<double>(ldg_f32(a + static_cast<long>(p) * ld + col));
+            sb += static_cast<double>(ldg_f32(b + static_cast<long>(p) * ld + col));
+        }
+    }
+    const int c = threadIdx.x % RED_COLS;
+    sh[0][lane_r][c] = sa;
+    sh[1][lane_r][c] = sb;
+    __syncthreads();
+#pragma unroll
+    for (int s = FRED_LANES / 2; s >= 1; s >>= 1) {
+        if (lane_r < s) {
+            sh[0][lane_r][c] += sh[0][lane_r + s][c];
+            sh[1][lane_r][c] += sh[1][lane_r + s][c];
+        }
+        __syncthreads();
+    }
+    ta = sh[0][0][c];
+    tb = sh[1][0][c];
+    __syncthreads();                                     // sh is reused by the caller's next column group
+}
+
+template <int FMT>
+__global__ void __launch_bounds__(EW_THREADS, 2) bn_fwd_fused_kernel(const float* __restrict__ psum,
+                                                                  const float* __restrict__ psq, int P, BnFwdFinalize f,
+                                                                  double* __restrict__ sums_out, BnApplyFwd a,
+                                                                  int rows_per_block, DropoutLanes lanes, float inv_keep,
+                                                                  const PhiloxKeys keys, unsigned* __restrict__ barrier) {
+    griddep_launch();
+    griddep_wait();
+    __shared__ double sh[2][FRED_LANES][RED_COLS];
+    const int c = threadIdx.x % RED_COLS, lane_r = threadIdx.x / RED_COLS;
+    for (int cb = blockIdx.x; cb * RED_COLS < f.H; cb += gridDim.x) {
+        const int col = cb * RED_COLS + c;
+        BnColumnInputs ci = {0.0f, 1.0f, 0.0f, 0.0f, 1.0f};
+        if (lane_r == 0 && col < f.H) ci = bn_column_inputs(f, col);
+        double ta, tb;
+        reduce_partials_block(psum, psq, P, f.H, f.H, col, lane_r, sh, ta, tb);
+        if (f.ex.world > 1 && lane_r == 0) exchange_column_sums(f.ex, f.H, col, col < f.H, ta, tb);
+        if (lane_r == 0 && col < f.H) {
+            sums_out[col] = ta;
+            sums_out[f.H + col] = tb;
+            if (col == 0 && f.num_batches_tracked != nullptr) *f.num_batches_tracked += 1;
+            bn_finalize_fwd_col(f, col, ta, tb, ci);
+        }
+    }
+    grid_barrier_once(barrier, gridDim.x);
+    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long end = min(base + rows_per_block, static_cast<long>(a.rows));
+    apply_rows<FMT>(a, base, end, lanes, inv_keep, keys, a.scale, a.shift);
 }
 
 // ---------------------------------------------------------------------------------- backward passes
@@ -570,6 +642,166 @@ __global__ void bn_bwd_reduce_kernel(const float* __restrict__ pg, const float* 
     }
 }
 
+// ---- BatchNorm backward of one layer in ONE launch: pass 1 -> column reduction -> coefficients -> pass 2 ----------------
+// The three launches it replaces (bwd_stats, bn_bwd_reduce<fused>, bwd_dz) are serial links of the step's critical
+// path; here they are phases of one grid separated by two grid barriers.  Phase 1: every block leaves one partial row of
+// sum gm and sum gm z over its rows.  Phase 2: the blocks share out the columns (8 each): fp64 sums over the partial
+// rows, dgamma / dbeta, SyncBN exchange, the pass-2 coefficients.  Phase 3: dz = A gm + Bz z + Cc over the same rows --
+// the second read of (g, z, bits) comes from L2, where phase 1 just left them.
+template <int FMT>
+__global__ void __launch_bounds__(EW_THREADS, 2) bn_bwd_fused_kernel(BwdCommon c, int rows_per_block,
+                                                                  float* __restrict__ psum0, float* __restrict__ psum1,
+                                                                  BnBwdFinalize f, double* __restrict__ sums_out,
+                                                                  float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                                  uint16_t* __restrict__ dz, unsigned* __restrict__ barrier) {
+    griddep_launch();
+    __shared__ uint4 lut[256];
+    __shared__ union { float part[2][EW_THREADS][8]; double red[2][FRED_LANES][RED_COLS]; } sm;
+    fill_mask_lut(lut);
+    __syncthreads();
+    griddep_wait();
+    const int tpr = c.H >> 3;
+    const int rpb = EW_THREADS / tpr;
+    const int cg = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+    const long base = static_cast<long>(blockIdx.x) * rows_per_block;
+    const long end = min(base + rows_per_block, static_cast<long>(c.rows));
+    const uint16_t* gp = static_cast<const uint16_t*>(c.g);
+    const uint16_t* zp = static_cast<const uint16_t*>(c.z);
+    const long step = static_cast<long>(rpb) * EW_UNROLL;
+    auto load = [&](long r0, uint4 (&gq)[EW_UNROLL], uint4 (&zq)[EW_UNROLL], uint32_t (&act)[EW_UNROLL]) {
+#pragma unroll
+        for (int u = 0; u < EW_UNROLL; ++u) {
+            const long row = r0 + static_cast<long>(u) * rpb;
+            gq[u] = make_uint4(0, 0, 0, 0);
+            zq[u] = make_uint4(0, 0, 0, 0);
+            act[u] = 0;
+            if (row < end) {
+                const long off = row * c.H + cg * 8;
+                gq[u] = ldg_stream(gp + off);
+                zq[u] = ldg_stream(zp + off);
+                act[u] = c.bits[row * tpr + cg];
+            }
+        }
+    };
+    uint4 g0[EW_UNROLL], z0[EW_UNROLL], g1[EW_UNROLL], z1[EW_UNROLL];
+    uint32_t a0[EW_UNROLL], a1[EW_UNROLL];
+
+    // ---------------- phase 1: partial column sums
+    {
+        float acc0[8] = {0, 0, 0, 0, 0, 0, 0, 0}, acc1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        auto compute = [&](const uint4 (&gq)[EW_UNROLL], const uint4 (&zq)[EW_UNROLL], const uint32_t (&act)[EW_UNROLL]) {
+#pragma unroll
+            for (int u = 0; u < EW_UNROLL; ++u) {                   // rows past `end` carry act == 0: they add nothing
+                float g[8], z[8];
+                unpack8(and4(gq[u], lut[act[u]]), FMT, g);
+                unpack8(zq[u], FMT, z);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    acc0[e] += g[e];
+                    acc1[e] = fmaf(g[e], z[e], acc1[e]);
+                }
+            }
+        };
+        long r = base + rl;
+        if (r < end) load(r, g0, z0, a0);
+        while (r < end) {
+            if (r + step < end) load(r + step, g1, z1, a1);
+            compute(g0, z0, a0);
+            r += step;
+            if (r >= end) break;
+            if (r + step < end) load(r + step, g0, z0, a0);
+            compute(g1, z1, a1);
+            r += step;
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            sm.part[0][threadIdx.x][e] = acc0[e];
+            sm.part[1][threadIdx.x][e] = acc1[e];
+        }
+        __syncthreads();
+        if (rl == 0) {
+            float t0[8] = {0, 0, 0, 0, 0, 0, 0, 0}, t1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int q = 0; q < rpb; ++q) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    t0[e] += sm.part[0][q * tpr + cg][e];
+                    t1[e] += sm.part[1][q * tpr + cg][e];
+                }
+            }
+            float* o0 = psum0 + static_cast<long>(blockIdx.x) * c.H + cg * 8;
+            float* o1 = psum1 + static_cast<long>(blockIdx.x) * c.H + cg * 8;
+            *reinterpret_cast<float4*>(o0) = make_float4(t0[0], t0[1], t0[2], t0[3]);
+            *reinterpret_cast<float4*>(o0 + 4) = make_float4(t0[4], t0[5], t0[6], t0[7]);
+            *reinterpret_cast<float4*>(o1) = make_float4(t1[0], t1[1], t1[2], t1[3]);
+            *reinterpret_cast<float4*>(o1 + 4) = make_float4(t1[4], t1[5], t1[6], t1[7]);
+        }
+    }
+    grid_barrier_once(barrier, gridDim.x);
+
+    // ---------------- phase 2: column totals, parameter gradients, exchange, coefficients
+    {
+        const int cc = threadIdx.x % RED_COLS, lane_r = threadIdx.x / RED_COLS;
+        for (int cb = blockIdx.x; cb * RED_COLS < f.H; cb += gridDim.x) {
+            const int col = cb * RED_COLS + cc;
+            BnBwdColumn cv = {1.0f, 0.0f, 1.0f};
+            if (lane_r == 0 && col < f.H) cv = bn_bwd_column(f, col);
+            double s1, s2;
+            reduce_partials_block(psum0, psum1, static_cast<int>(gridDim.x), f.H, f.H, col, lane_r, sm.red, s1, s2);
+            double sum_dy = 0.0, sum_dyz = 0.0;
+            if (lane_r == 0 && col < f.H) {
+                const double ik = static_cast<double>(f.inv_keep);
+                sum_dy = ik * s1;
+                sum_dyz = ik * static_cast<double>(cv.rstd) * (s2 - static_cast<double>(cv.mean) * s1);
+                dbeta[col] = static_cast<float>(sum_dy);                        // parameter gradients: LOCAL sums
+                dgamma[col] = static_cast<float>(sum_dyz);
+            }
+            if (f.ex.world > 1 && lane_r == 0) exchange_column_sums(f.ex, f.H, col, col < f.H, sum_dy, sum_dyz);
+            if (lane_r == 0 && col < f.H) {
+                sums_out[col] = sum_dy;
+                sums_out[f.H + col] = sum_dyz;
+                bn_bwd_coefficients(f, col, sum_dy, sum_dyz, cv);
+            }
+        }
+    }
+    grid_barrier_once(barrier + 1, gridDim.x);
+
+    // ---------------- phase 3: dz
+    {
+        float ka[8], kz[8], kc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {                               // written by other blocks of this launch: past L1
+            ka[e] = __ldcg(f.coef + cg * 8 + e);
+            kz[e] = __ldcg(f.coef + c.H + cg * 8 + e);
+            kc[e] = __ldcg(f.coef + 2 * c.H + cg * 8 + e);
+        }
+        auto compute = [&](long r0, const uint4 (&gq)[EW_UNROLL], const uint4 (&zq)[EW_UNROLL],
+                           const uint32_t (&act)[EW_UNROLL]) {
+#pragma unroll
+            for (int u = 0; u < EW_UNROLL; ++u) {
+                const long row = r0 + static_cast<long>(u) * rpb;
+                if (row >= end) break;
+                float g[8], z[8], o[8];
+                unpack8(and4(gq[u], lut[act[u]]), FMT, g);
+                unpack8(zq[u], FMT, z);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) o[e] = fmaf(ka[e], g[e], fmaf(kz[e], z[e], kc[e]));
+                *reinterpret_cast<uint4*>(dz + row * c.H + cg * 8) = pack8(o, FMT);
+            }
+        };
+        long r = base + rl;
+        if (r < end) load(r, g0, z0, a0);
+        while (r < end) {
+            if (r + step < end) load(r + step, g1, z1, a1);
+            compute(r, g0, z0, a0);
+            r += step;
+            if (r >= end) break;
+            if (r + step < end) load(r + step, g0, z0, a0);
+            compute(r, g1, z1, a1);
+            r += step;
+        }
+    }
+}
+
 // ---------------------------------------------------------------------------------- gradient packing
 // sum of the split-K slabs -> dense fp32 gradient [rows][cols]; fixed order, four columns per thread when the
 // shapes allow 16-byte accesses
@@ -602,9 +834,11 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ slabs, int splits,
 __global__ void __launch_bounds__(EW_THREADS) prep_grad_out_kernel(const float* __restrict__ dout, long rows, int O,
                                                                    int Op, int fmt, int rows_per_block,
                                                                    uint16_t* __restrict__ d16,
-                                                                   float* __restrict__ psum) {
+                                                                   float* __restrict__ psum,
+                                                                   unsigned* __restrict__ zero_words, int n_zero) {
     griddep_launch();
     griddep_wait();
+    if (blockIdx.x == 0 && static_cast<int>(threadIdx.x) < n_zero) zero_words[threadIdx.x] = 0u;   // the pass's barrier words
     // Op == 64: 8 column groups per row, 32 rows per iteration
     __shared__ float sh[EW_THREADS][8];
     const int tpr = Op >> 3, rpb = EW_THREADS / tpr;
@@ -702,6 +936,78 @@ int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st) {
     return LIFTER_OK;
 }
 
+// Blocks of a grid-barrier kernel that fit on the device at once (occupancy query, cached per device and kernel).
+template <typename K>
+static int resident_blocks(K kernel, int slot) {
+    static int cached[2][64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return num_sms();
+    if (cached[slot][dev] == 0) {
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EW_THREADS, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+        if (per_sm > 2) per_sm = 2;
+        cached[slot][dev] = per_sm * num_sms();
+    }
+    return cached[slot][dev];
+}
+
+// rows per block of a barrier kernel: whole `group`-row units, at most `max_blocks` blocks, every block non-empty
+static int barrier_rows_per_block(int64_t rows, int64_t group, int max_blocks) {
+    const int64_t groups = (rows + group - 1) / group;
+    const int64_t per_block = (groups + max_blocks - 1) / max_blocks;
+    return static_cast<int>(per_block * group);
+}
+
+int bn_fwd_fused(const float* psum, const float* psq, int P, const BnFwdFinalize& f, double* sums_out,
+                 const BnApplyFwd& a, unsigned* barrier, cudaStream_t st) {
+    LIFTER_PROPAGATE(check_h(a.H, "bn_fwd_fused"));
+    LIFTER_REQUIRE(barrier != nullptr, "bn_fwd_fused: null barrier word");
+    const DropoutLanes lanes = dropout_lanes(a.p);
+    const PhiloxKeys keys = philox_round_keys(a.seed);
+    const float inv_keep = (a.apply_dropout && a.p < 1.0f) ? 1.0f / (1.0f - a.p) : (a.apply_dropout ? 0.0f : 1.0f);
+    const int64_t group = static_cast<int64_t>(EW_THREADS / (a.H / 8)) * AP_ROWS;
+    if (a.fmt == FMT_BF16) {
+        const int rpb = barrier_rows_per_block(a.rows, group, resident_blocks(bn_fwd_fused_kernel<FMT_BF16>, 0));
+        const unsigned blocks = static_cast<unsigned>((a.rows + rpb - 1) / rpb);
+        LIFTER_CHECK_CUDA(launch_pdl("bn_fwd_fused_kernel", bn_fwd_fused_kernel<FMT_BF16>, dim3(blocks), dim3(EW_THREADS), 0, st,
+                                     psum, psq, P, f, sums_out, a, rpb, lanes, inv_keep, keys, barrier));
+    } else {
+        const int rpb = barrier_rows_per_block(a.rows, group, resident_blocks(bn_fwd_fused_kernel<FMT_F16>, 1));
+        const unsigned blocks = static_cast<unsigned>((a.rows + rpb - 1) / rpb);
+        LIFTER_CHECK_CUDA(launch_pdl("bn_fwd_fused_kernel", bn_fwd_fused_kernel<FMT_F16>, dim3(blocks), dim3(EW_THREADS), 0, st,
+                                     psum, psq, P, f, sums_out, a, rpb, lanes, inv_keep, keys, barrier));
+    }
+    return LIFTER_OK;
+}
+
+int bn_bwd_fused_partial_rows(int64_t rows, int H) {
+    // upper bound over the two operand formats (the scratch buffers are sized before the format is known)
+    const int cap = 2 * num_sms();
+    const int64_t group = EW_THREADS / (H / 8);
+    const int rpb = barrier_rows_per_block(rows, group, cap);
+    return static_cast<int>((rows + rpb - 1) / rpb);
+}
+
+int bn_bwd_fused(const BwdCommon& c, float* psum_g, float* psum_gz, const BnBwdFinalize& f, double* sums_out,
+                 float* dgamma, float* dbeta, void* dz, unsigned* barrier, cudaStream_t st) {
+    LIFTER_PROPAGATE(check_h(c.H, "bn_bwd_fused"));
+    LIFTER_REQUIRE(barrier != nullptr, "bn_bwd_fused: null barrier words");
+    const int64_t group = EW_THREADS / (c.H / 8);
+    uint16_t* d = static_cast<uint16_t*>(dz);
+    if (c.fmt == FMT_BF16) {
+        const int rpb = barrier_rows_per_block(c.rows, group, resident_blocks(bn_bwd_fused_kernel<FMT_BF16>, 0));
+        const unsigned blocks = static_cast<unsigned>((c.rows + rpb - 1) / rpb);
+        LIFTER_CHECK_CUDA(launch_pdl("bn_bwd_fused_kernel", bn_bwd_fused_kernel<FMT_BF16>, dim3(blocks), dim3(EW_THREADS), 0, st,
+                                     c, rpb, psum_g, psum_gz, f, sums_out, dgamma, dbeta, d, barrier));
+    } else {
+        const int rpb = barrier_rows_per_block(c.rows, group, resident_blocks(bn_bwd_fused_kernel<FMT_F16>, 1));
+        const unsigned blocks = static_cast<unsigned>((c.rows + rpb - 1) / rpb);
+        LIFTER_CHECK_CUDA(launch_pdl("bn_bwd_fused_kernel", bn_bwd_fused_kernel<FMT_F16>, dim3(blocks), dim3(EW_THREADS), 0, st,
+                                     c, rpb, psum_g, psum_gz, f, sums_out, dgamma, dbeta, d, barrier));
+    }
+    return LIFTER_OK;
+}
+
 int bwd_stats(const BwdCommon& c, float* psum_g, float* psum_gz, cudaStream_t st) {
     LIFTER_PROPAGATE(check_h(c.H, "bwd_stats"));
     const dim3 grid(ew_partial_rows(c.rows, c.H));
@@ -755,11 +1061,13 @@ int wgrad_reduce(const float* slabs, int splits, int slab_rows, int ld, int rows
     return LIFTER_OK;
 }
 
-int prep_grad_out(const float* dout, int64_t rows, int O, int Op, int fmt, void* d16, float* psum, cudaStream_t st) {
+int prep_grad_out(const float* dout, int64_t rows, int O, int Op, int fmt, void* d16, float* psum, cudaStream_t st,
+                  unsigned* zero_words, int n_zero) {
     LIFTER_REQUIRE(Op == 64, "prep_grad_out: padded output width must be 64");
     LIFTER_CHECK_CUDA(launch_pdl("prep_grad_out_kernel", prep_grad_out_kernel, dim3(ew_partial_rows(rows, Op)), dim3(EW_THREADS), 0, st, dout, rows, O, Op, fmt,
                                  ew_rows_per_block(rows, Op),
-                                                                       static_cast<uint16_t*>(d16), psum));
+                                                                       static_cast<uint16_t*>(d16), psum, zero_words,
+                                                                       zero_words != nullptr ? n_zero : 0));
     return LIFTER_OK;
 }
 

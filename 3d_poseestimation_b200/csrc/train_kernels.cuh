@@ -56,6 +56,10 @@ struct BnApplyFwd {
     void* a; uint8_t* bits;     // a [rows][H] 16-bit, bits [rows][H/8]: relu-active AND kept
 };
 int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st);
+// bn_reduce_finalize_fwd + bn_apply_fwd as ONE launch with a grid barrier between the two (batch statistics only).
+// `barrier`: one word, zero when the kernel starts (common.cuh: grid_barrier_once).
+int bn_fwd_fused(const float* psum, const float* psq, int P, const BnFwdFinalize& f, double* sums_out,
+                 const BnApplyFwd& a, unsigned* barrier, cudaStream_t st);
 
 struct BwdCommon {
     const void* g; const void* z; const uint8_t* bits;
@@ -83,11 +87,19 @@ int bn_bwd_reduce(const float* pg, const float* pgz, int P, const BnBwdFinalize&
 // pass 2: dz = coef0 * gm + coef1 * z + coef2 as 16-bit; psum_dz (nullable) receives partial column sums of dz
 int bwd_dz(const BwdCommon& c, const float* coef, void* dz, float* psum_dz, cudaStream_t st);
 
+// bwd_stats + bn_bwd_reduce<fused> + bwd_dz (no bias sums) as ONE launch with two grid barriers.  psum_g / psum_gz hold
+// bn_bwd_fused_partial_rows(rows, H) rows of H floats; `barrier`: two words, zero when the kernel starts.
+int bn_bwd_fused_partial_rows(int64_t rows, int H);
+int bn_bwd_fused(const BwdCommon& c, float* psum_g, float* psum_gz, const BnBwdFinalize& f, double* sums_out,
+                 float* dgamma, float* dbeta, void* dz, unsigned* barrier, cudaStream_t st);
+
 // sum of split-K slabs -> dense fp32 gradient [rows][cols]
 int wgrad_reduce(const float* slabs, int splits, int slab_rows, int ld, int rows, int cols, float* grad,
                  cudaStream_t st);
 
 // grad_out fp32 [rows][O] -> 16-bit [rows][Op] zero padded, plus partial column sums (output-layer bias gradient)
-int prep_grad_out(const float* dout, int64_t rows, int O, int Op, int fmt, void* d16, float* psum, cudaStream_t st);
+// zero_words (nullable): n_zero <= 256 words the kernel also zeroes -- the grid-barrier words of the backward pass it opens
+int prep_grad_out(const float* dout, int64_t rows, int O, int Op, int fmt, void* d16, float* psum, cudaStream_t st,
+                  unsigned* zero_words = nullptr, int n_zero = 0);
 
 }  // namespace lifter

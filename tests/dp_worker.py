@@ -20,7 +20,9 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     pkg = importlib.import_module("3d_poseestimation_b200")
     trainer = importlib.import_module("3d_poseestimation_b200.trainer")
-    H, S, B, steps = 256, 1, 512, 6                                   # B rows per rank
+    # B rows per rank; the defaults are the small case, DP_CASE=bench is the shape bench.py times (configs[2])
+    H, S, B, steps = (1024, 2, 8192, 4) if os.environ.get("DP_CASE") == "bench" else (256, 1, 512, 6)
+    use_graph = os.environ.get("DP_USE_GRAPH", "1") != "0"
     rs = np.random.RandomState(0)
     xg = torch.from_numpy(rs.normal(0, 1, (steps, world * B, 34)).astype(np.float32))
     yg = torch.from_numpy(rs.normal(0, 1, (steps, world * B, 51)).astype(np.float32))
@@ -30,11 +32,17 @@ def main():
         return pkg.LinearModel(34, 51, linear_size=H, num_stage=S, p_dropout=0.5, BN=True).to(dev)
     # single process on the global batch (every rank computes it: cheap, and no cross-rank transfer of the answer)
     ref = build()
-    tr_ref = trainer.LifterTrainer(ref, lr=1e-3, loss="mse", optimizer="adam", seed=5)
+    tr_ref = trainer.LifterTrainer(ref, lr=1e-3, loss="mse", optimizer="adam", seed=5, use_graph=use_graph)
     ref_losses = [float(tr_ref.step(xg[s].to(dev), yg[s].to(dev)).item()) for s in range(steps)]
     # data parallel
     m = build()
-    tr = trainer.LifterTrainer(m, lr=1e-3, loss="mse", optimizer="adam", seed=5, world_size=world, rank=rank)
+    if os.environ.get("DP_DIVERGENT_INIT") == "1":                    # replicas built from different seeds: the trainer
+        torch.manual_seed(100 + rank)                                 # must broadcast rank 0's
+        m2 = pkg.LinearModel(34, 51, linear_size=H, num_stage=S, p_dropout=0.5, BN=True).to(dev)
+        if rank != 0:
+            m = m2
+    tr = trainer.LifterTrainer(m, lr=1e-3, loss="mse", optimizer="adam", seed=5, world_size=world, rank=rank,
+                               use_graph=use_graph, require_symmetric=True)
     assert (m._dp is not None) == (world > 1), "symmetric-memory SyncBN exchange was not set up"
     losses = []
     for s in range(steps):

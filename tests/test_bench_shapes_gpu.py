@@ -1,0 +1,144 @@
+"""Parity on the EXACT shapes and code paths bench.py times ("the benched shapes are not the tested
+shapes"): configs[2] = LifterTrainer.step at 8,192 poses, 1,024 wide, 2 blocks, CUDA-graph replay, split-K weight
+gradients over K = 8,192, side-stream weight gradients + per-layer Adam ranges; configs[1] = eval inference of 65,536
+poses in one chunk.  Oracle: the CPU restatement pinned to the reference (oracle/), same weights, inputs and dropout
+masks; one oracle step at this size is ~1 s of CPU."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import adam_oracle, lifter_oracle as lo, losses_oracle as L
+from oracle.philox import dropout_keep_mask
+
+pytestmark = pytest.mark.gpu
+T = torch.from_numpy
+
+
+def rel_l2(a, b):
+    a, b = torch.as_tensor(a).double().reshape(-1), torch.as_tensor(b).double().reshape(-1)
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+@pytest.mark.parametrize("fuse_optimizer", [True, False])
+def test_config2_training_step_at_bench_shape(pkg, fuse_optimizer):
+    trainer_mod = importlib.import_module("3d_poseestimation_b200.trainer")
+    i_dim, o_dim, H, S, B, seed, steps = 34, 51, 1024, 2, 8192, 41, 3
+    params, buffers = lo.numpy_init(i_dim, o_dim, H, S, seed, randomize_bn=False)
+    m = pkg.LinearModel(i_dim, o_dim, linear_size=H, num_stage=S, p_dropout=0.5, BN=True)
+    m.load_state_dict({**params, **buffers})
+    m = m.cuda()
+    tr = trainer_mod.LifterTrainer(m, lr=1e-3, loss="mse", optimizer="adam", seed=seed + 7)
+    tr.fuse_optimizer = fuse_optimizer
+    assert tr.use_graph
+    rs = np.random.RandomState(seed + 1)
+    wtrue = rs.normal(0, 0.3, (i_dim, o_dim)).astype(np.float32)
+    mo = {k: torch.zeros_like(v) for k, v in params.items()}
+    vo = {k: torch.zeros_like(v) for k, v in params.items()}
+    got, exp = [], []
+    for s in range(steps):
+        x = rs.normal(0, 1, (B, i_dim)).astype(np.float32)
+        y = T(np.tanh(x @ wtrue).astype(np.float32))
+        got.append(float(tr.step(T(x).cuda(), y.cuda()).item()))
+        masks = [dropout_keep_mask(B, H, site, s, seed + 7, 0.5) for site in range(2 * S + 1)]
+        r = lo.lifter_forward_backward(params, buffers, T(x), lambda o: ((o - y) ** 2).mean(), num_stage=S,
+                                       training=True, p_dropout=0.5, masks=masks)
+        buffers = r["buffers"]
+        for k in params:
+            params[k], mo[k], vo[k] = adam_oracle.adam_step(params[k], r["grads"][k], mo[k], vo[k], s + 1, 1e-3)
+        exp.append(float(r["loss"]))
+    assert tr.graph_launches() and tr.graph_launches() > 20          # the step was captured, launches counted
+    np.testing.assert_allclose(got, exp, rtol=1e-2)                  # north_star: loss curves within 1 %
+    sd = m.state_dict()
+    # three Adam steps at lr 1e-3 move every weight by ~3e-3: compare the UPDATE, not just the weights
+    for name in ("w2.weight", "linear_stages.1.w2.weight", "linear_stages.0.w1.weight", "w1.weight"):
+        p0 = lo.numpy_init(i_dim, o_dim, H, S, seed, randomize_bn=False)[0][name]
+        upd, upd_ref = sd[name].cpu() - p0, params[name] - p0
+        # Adam's first steps are sign-like (m / sqrt(v) ~ +-1): a gradient entry within bf16 noise of zero flips its
+        # whole step, so the updates agree in direction (cosine), not entry by entry
+        cos = torch.nn.functional.cosine_similarity(upd.reshape(-1), upd_ref.reshape(-1), dim=0).item()
+        assert cos > 0.9, f"{name}: update cosine {cos}"
+        assert rel_l2(sd[name].cpu(), params[name]) < 3e-2, name
+    assert rel_l2(sd["batch_norm1.running_var"].cpu(), buffers["batch_norm1.running_var"]) < 1e-2
+    assert rel_l2(sd["linear_stages.1.batch_norm2.running_mean"].cpu(), buffers["linear_stages.1.batch_norm2.running_mean"]) < 2e-2
+    assert int(sd["batch_norm1.num_batches_tracked"]) == steps
+
+
+def test_config2_gradients_at_bench_shape(pkg):
+    """One forward/backward at 8,192 x 1,024 through the autograd bridge (the same kernels the fused step replays): every
+    parameter gradient against the oracle's autograd.  At this batch the per-sample ReLU flips of 16-bit storage average
+    out, so the gradients agree to the bf16 level."""
+    i_dim, o_dim, H, S, B, seed = 34, 51, 1024, 2, 8192, 43
+    params, buffers = lo.numpy_init(i_dim, o_dim, H, S, seed, randomize_bn=True)
+    m = pkg.LinearModel(i_dim, o_dim, linear_size=H, num_stage=S, p_dropout=0.5, BN=True)
+    m.load_state_dict({**params, **buffers})
+    m = m.cuda().train()
+    m.dropout_seed, m.dropout_step = 9, 0
+    rs = np.random.RandomState(seed)
+    x, y = T(rs.normal(0, 1, (B, i_dim)).astype(np.float32)), T(rs.normal(0, 1, (B, o_dim)).astype(np.float32))
+    loss = torch.nn.functional.mse_loss(m(x.cuda()), y.cuda())
+    loss.backward()
+    masks = [dropout_keep_mask(B, H, site, 0, 9, 0.5) for site in range(2 * S + 1)]
+    r = lo.lifter_forward_backward(params, buffers, x, lambda o: ((o - y) ** 2).mean(), num_stage=S, training=True,
+                                   p_dropout=0.5, masks=masks)
+    assert abs(loss.item() - float(r["loss"])) < 5e-3 * float(r["loss"])
+    for name, prm in m.named_parameters():
+        ref = r["grads"][name]
+        if name.endswith(".bias") and "batch_norm" not in name and not name.startswith("w2."):
+            assert float(prm.grad.abs().max()) == 0.0, name             # cancelled by train-mode BN
+            continue
+        assert rel_l2(prm.grad.cpu(), ref) < 4e-2, f"{name}: {rel_l2(prm.grad.cpu(), ref)}"
+
+
+def test_config1_eval_at_bench_shape(pkg, golden_dir):
+    """65,536 poses in one infer() call (one chunk, as bench.py runs it), against the oracle after de-normalisation:
+    north_star's 0.5 mm + 1e-2 on EVERY coordinate."""
+    st = dict(np.load(os.path.join(golden_dir, "h36m_stats.npz")))
+    m2, s2 = T(st["mean_train_2d"]).float(), T(st["std_train_2d"]).float()
+    m3, s3 = T(st["mean_train_3d"]).float(), T(st["std_train_3d"]).float()
+    B = 65536
+    params, buffers = lo.numpy_init(34, 51, 1024, 2, seed=19)
+    m = pkg.LinearModel(34, 51, linear_size=1024, num_stage=2, p_dropout=0.5, BN=True)
+    m.load_state_dict({**params, **buffers})
+    m = m.cuda().eval()
+    gen = torch.Generator().manual_seed(1)
+    x = (m2 + s2 * torch.randn(B, 17, 2, generator=gen)).clamp(0, 1)
+    xn = L.normalise(x, m2, s2)
+    with torch.no_grad():
+        ref, _ = lo.lifter_forward(params, buffers, xn, num_stage=2, training=False)
+    ref = L.denormalise(ref.reshape(B, 17, 3), m3, s3)
+    out = torch.empty(B, 51, device="cuda")
+    m.infer(xn.cuda(), out=out)                                         # bench.py's call
+    out = L.denormalise(out.cpu().reshape(B, 17, 3), m3, s3)
+    err = (out - ref).abs()
+    tol = 0.5e-3 + 1e-2 * ref.abs()
+    assert bool((err <= tol).all()), f"max err {err.max().item() * 1e3:.3f} mm; worst err/tol {(err / tol).max().item():.2f}"
+    # the host pipeline bench.py's e2e leg goes through gives the same bits
+    outh = torch.empty(B, 51).pin_memory()
+    m.infer_host_batches([xn.reshape(B, 34).contiguous().pin_memory()], outs=[outh])
+    assert torch.equal(outh, m.infer(xn.cuda()).cpu())
+
+
+def test_model_on_another_device_than_the_current_one(pkg):
+    """every entry point must launch on the device of its tensors, whatever device is current."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    trainer_mod = importlib.import_module("3d_poseestimation_b200.trainer")
+    params, buffers = lo.numpy_init(34, 51, 256, 1, seed=5)
+    x = T(np.random.RandomState(0).normal(0, 1, (64, 34)).astype(np.float32))
+    y = T(np.random.RandomState(1).normal(0, 1, (64, 51)).astype(np.float32))
+    outs = []
+    for dev in ("cuda:0", "cuda:1"):
+        torch.cuda.set_device(0)                                        # current device stays 0 throughout
+        m = pkg.LinearModel(34, 51, linear_size=256, num_stage=1, p_dropout=0.5, BN=True)
+        m.load_state_dict({**params, **buffers})
+        m = m.to(dev).eval()
+        with torch.no_grad():
+            e = m(x.to(dev)).cpu()
+        tr = trainer_mod.LifterTrainer(m, lr=1e-3, seed=3)
+        l = [float(tr.step(x.to(dev), y.to(dev)).item()) for _ in range(3)]
+        outs.append((e, l, m._flat.cpu()))
+        assert torch.cuda.current_device() == 0
+    assert torch.equal(outs[0][0], outs[1][0]) and outs[0][1] == outs[1][1] and torch.equal(outs[0][2], outs[1][2])
