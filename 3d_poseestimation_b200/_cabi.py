@@ -126,6 +126,7 @@ SIGNATURES = {
     "lifter_keypoint_stats_scratch_bytes": (_I64, [_I64, _I32, _I32]),
     "lifter_keypoint_stats": (_I32, [_P, _I64, _I32, _I32, _I32, _P, _P, _P]),
     "lifter_process_keypoints": (_I32, [_P, _P, _I64, _I32, _I32, _I32, _P, _I32, _I32, _P]),
+    "lifter_keypoint_heatmaps": (_I32, [_P, _I32, _I64, C.c_double, _P, _P, _P]),
     "lifter_affine_cols": (_I32, [_P, _P, _I64, _I32, _P, _P, _I32, _P]),
     "lifter_pose_loss_scratch_bytes": (_I64, [_I64, _I32]),
     "lifter_pose_loss": (_I32, [C.POINTER(PoseLossDesc), _P]),

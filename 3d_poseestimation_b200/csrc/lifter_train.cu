@@ -14,6 +14,7 @@
 #include "../../include/lifter_b200.h"
 #include "elementwise.cuh"
 #include "gemm_sm100.cuh"
+#include "heatmap_ops.cuh"
 #include "layout.cuh"
 #include "loss_adam.cuh"
 #include "pose_ops.cuh"
@@ -99,11 +100,14 @@ int fill_exchange(const Layout& lay, const lifter_train_ctx_t* t, int site, Sync
     return LIFTER_OK;
 }
 
-// LIFTER_FUSE_BN=0: the BatchNorm passes of the single-call forward / backward run as separate launches again
-// (reduce + finalize, apply; stats, reduce, dz) instead of the grid-barrier kernels -- for A/B timing and bisection.
-bool fuse_bn_launches() {
-    static const bool on = [] { const char* e = getenv("LIFTER_FUSE_BN"); return !(e != nullptr && e[0] == '0'); }();
-    return on;
+// LIFTER_FUSE_BN_FWD=1 / LIFTER_FUSE_BN_BWD=1: the BatchNorm passes of the single-call forward / backward run as ONE
+// grid-barrier launch per layer instead of separate launches (reduce + finalize, apply; stats, reduce, dz).  Off by
+// default: measured on B200 (profiles/README.md, round 2) the barrier kernels are SLOWER inside the step -- a grid that
+// must be fully resident cannot start while the side stream's persistent weight-gradient GEMM holds the SMs.
+bool fuse_bn_launches(bool forward) {
+    static const bool fwd = [] { const char* e = getenv("LIFTER_FUSE_BN_FWD"); return e != nullptr && e[0] == '1'; }();
+    static const bool bwd = [] { const char* e = getenv("LIFTER_FUSE_BN_BWD"); return e != nullptr && e[0] == '1'; }();
+    return forward ? fwd : bwd;
 }
 
 int wgrad_splits(int M, int N, int K) {
@@ -282,7 +286,7 @@ static int fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     f.mean_z = w.mean_z[l]; f.rstd = w.rstd[l]; f.scale = w.scale[l]; f.shift = w.shift[l];
     if (fused) LIFTER_PROPAGATE(fill_exchange(lay, t, l, &f.ex));          // forward site l
     const bool batch_stats = fused && cfg->use_bn && t->bn_mode == 0;
-    const bool one_launch = batch_stats && l < GRID_BARRIER_WORDS && fuse_bn_launches();
+    const bool one_launch = batch_stats && l < GRID_BARRIER_WORDS && fuse_bn_launches(true);
     if (batch_stats && !one_launch)
         LIFTER_PROPAGATE(bn_reduce_finalize_fwd(w.psum, w.psq, gemm_stat_rows(static_cast<int>(t->batch)), f, w.sums[l], st));
     else if (!batch_stats)
@@ -446,7 +450,7 @@ static int bwd_exchange(const lifter_config_t* cfg, const lifter_train_ctx_t* t,
 
 // single-call backward, batch-statistics BatchNorm: stats -> reduce -> dz of a layer run as ONE grid-barrier launch
 static bool bwd_one_launch(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, bool fused) {
-    return fused && cfg->use_bn && t->bn_mode == 0 && 2 * l + 1 < GRID_BARRIER_WORDS && fuse_bn_launches();
+    return fused && cfg->use_bn && t->bn_mode == 0 && 2 * l + 1 < GRID_BARRIER_WORDS && fuse_bn_launches(false);
 }
 
 static int bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
@@ -664,6 +668,11 @@ int lifter_flip_pose(const float* in, float* out, int64_t poses, int joints, int
 int lifter_coco2h36m(const float* in, int in_channels, float* out, int64_t poses, float scale, const float* mean,
                      const float* stdv, int mode, void* stream) {
     return coco2h36m(in, in_channels, out, poses, scale, mean, stdv, mode, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_keypoint_heatmaps(const void* keypoints, int keypoints_are_f64, int64_t n, double sigma, float* out,
+                             int* status, void* stream) {
+    return keypoint_heatmaps(keypoints, keypoints_are_f64, n, sigma, out, status, static_cast<cudaStream_t>(stream));
 }
 
 int lifter_affine_cols(const float* in, float* out, int64_t rows, int cols, const float* a, const float* b, int mode,

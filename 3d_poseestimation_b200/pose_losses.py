@@ -198,6 +198,37 @@ def process_data(dataset, stats=None, is_train=True, standardize=False, z_c=True
 
 
 # ------------------------------------------------------------------------------------------------ (de)normalisation
+def keypoints_to_heatmap_3D(keypoints, sigma=0.5, out=None, check=True):
+    """Volumetric Gaussian heat-map targets, ``phase3_direct/my_HybrIK/H36_dataset.py:143-202`` (``xyz_to_uvw``,
+    ``_keypoint_to_heatmap_3D``, ``keypoints_to_heatmap_3D``): key points ``[..., 3]`` in [-1, 1] (fp32 or fp64, CUDA)
+    -> fp32 ``[..., 64, 64, 64]``, one volume per key point; the dataset calls it per frame with ``(17, 3)``.
+
+    ONE streaming kernel writes every volume exactly once (1 MB per key point).  ``check``: mirror the reference's
+    asserts on the coordinate range (one host read of a status word); ``check=False`` keeps the call asynchronous.
+    A numpy array is uploaded, processed on the GPU and downloaded again (there is no CPU implementation)."""
+    if isinstance(keypoints, np.ndarray):
+        dev = torch.device("cuda", torch.cuda.current_device())
+        return keypoints_to_heatmap_3D(torch.from_numpy(np.ascontiguousarray(keypoints)).to(dev), sigma, None, check).cpu().numpy()
+    if not torch.is_tensor(keypoints) or not keypoints.is_cuda:
+        raise RuntimeError("keypoints_to_heatmap_3D: the sm_100a build has no CPU path; pass a CUDA tensor or a numpy array")
+    if keypoints.shape[-1] != 3:
+        raise ValueError(f"keypoints_to_heatmap_3D expects [..., 3] key points, got {tuple(keypoints.shape)}")
+    kp = keypoints if keypoints.dtype in (torch.float32, torch.float64) else keypoints.float()
+    kp = kp.contiguous()
+    n = kp.numel() // 3
+    shape = tuple(kp.shape[:-1]) + (64, 64, 64)
+    if out is None:
+        out = torch.empty(shape, dtype=torch.float32, device=kp.device)
+    elif tuple(out.shape) != shape or out.dtype != torch.float32 or not out.is_contiguous() or out.device != kp.device:
+        raise ValueError(f"keypoints_to_heatmap_3D: out must be a contiguous fp32 tensor of shape {shape} on {kp.device}")
+    status = torch.zeros(1, dtype=torch.int32, device=kp.device) if check else None
+    _cabi.check(_cabi.lib().lifter_keypoint_heatmaps(_cabi.ptr(kp), int(kp.dtype == torch.float64), n, float(sigma),
+                                                     _cabi.ptr(out), _cabi.ptr(status), _cabi.stream_ptr()))
+    if check and int(status.item()) & 1:
+        raise AssertionError("keypoints_to_heatmap_3D: key points must lie in [-1, 1] (H36_dataset.py:156-157)")
+    return out
+
+
 class _AffineCols(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, a, b, mode):
@@ -462,7 +493,7 @@ class TriangleLoss_sep(torch.nn.Module):
 
 
 # Every entry point launches on the device of its first CUDA tensor, whatever device is current (_cabi.device_guard).
-for _name in ("coco2h36m", "keypoint_stats", "process_data", "normalise", "denormalise", "normalise_minmax",
+for _name in ("coco2h36m", "keypoint_stats", "process_data", "keypoints_to_heatmap_3D", "normalise", "denormalise", "normalise_minmax",
               "denormalise_minmax", "loss_MPJPE", "_pose_loss_call", "l1_loss"):
     globals()[_name] = _cabi.device_guard(globals()[_name])
 for _cls in (_FlipPose, _AffineCols, _MinMaxNorm, _PoseLoss, _L1Mean):

@@ -207,6 +207,15 @@ int lifter_keypoint_stats(const float* data, int64_t frames, int joints, int dim
                           double* out, void* stream);
 int lifter_process_keypoints(const float* in, float* out, int64_t frames, int joints, int dims, int zero_centre,
                              const double* stats, int mode, int root_mode, void* stream);
+/* Volumetric Gaussian heat-map targets of the dataset (phase3_direct/my_HybrIK/H36_dataset.py:143-202:
+ * xyz_to_uvw, _keypoint_to_heatmap_3D, keypoints_to_heatmap_3D).  keypoints [n][3] (x, y, z) in [-1, 1], fp32 or fp64
+ * (keypoints_are_f64), n = frames * joints -> out [n][64][64][64] fp32: (u, v, w) = (-y, -z, x), k = 31.5 (1 + uvw),
+ * c = rint(k); the cube of ceil(6 sigma) (made odd) voxels around c holds exp(-|voxel - k|^2 / (2 sigma^2)), clipped
+ * at the borders, zero elsewhere (the reference's sigma is 0.5: 3 x 3 x 3 voxels).  fp64 arithmetic like the numpy
+ * original, fp32 on the store; one streaming pass, 1 MB per key point.  status: nullable device int, bit 0 set when a
+ * coordinate is outside [-1, 1] (the reference asserts, :156-157).                                                  */
+int lifter_keypoint_heatmaps(const void* keypoints, int keypoints_are_f64, int64_t n, double sigma, float* out,
+                             int* status, void* stream);
 /* per-column statistics broadcast over rows: mode 0 (x - a) / b (main.py:334,337), 1 x * b + a (main.py:473-479,
  * train_5.py:42-47), 2 2x - 1 (main.py:331), 3 x * (a - b) + b with a = max, b = min (train_5.py:35-40)        */
 int lifter_affine_cols(const float* in, float* out, int64_t rows, int cols, const float* a, const float* b, int mode,

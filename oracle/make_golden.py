@@ -158,6 +158,44 @@ def vit_case():
     print("wrote vit", {k: v.shape for k, v in out.items()})
 
 
+def ref_heatmap_methods():
+    """H36_dataset.py:143-202 (xyz_to_uvw, _keypoint_to_heatmap_3D, keypoints_to_heatmap_3D) by exec of the source slice
+    inside a stand-in class: the file itself imports cv2 and the dataset paths."""
+    import math
+    import textwrap
+    src = open(os.path.join(REF, "phase3_direct/my_HybrIK/H36_dataset.py")).read().splitlines()
+    body = textwrap.dedent("\n".join(src[142:202]))
+    ns = {"np": np, "math": math}
+    exec("class _Ref:\n" + textwrap.indent(body, "    "), ns)
+    return ns["_Ref"]()
+
+
+def heatmaps_case():
+    """Heat-map targets through the reference's own methods; volumes stored sparsely (the 27
+    non-zero voxels of each 64^3 volume)."""
+    from oracle import heatmap_oracle as HO
+    ref = ref_heatmap_methods()
+    rs = np.random.RandomState(57)
+    poses = rs.uniform(-1, 1, (6, 17, 3))
+    # border cases: exactly +-1 (window clipped on one, two and three faces), half-integer voxel coordinates (np.rint
+    # rounds half to even), the centre
+    poses[0, 0] = [1.0, 1.0, 1.0]
+    poses[0, 1] = [-1.0, -1.0, -1.0]
+    poses[0, 2] = [1.0, -1.0, 0.3]
+    poses[0, 3] = [0.0, 0.0, 0.0]
+    poses[0, 4] = [(16.5 / 31.5) - 1, -((20.5 / 31.5) - 1), -((2.5 / 31.5) - 1)]
+    poses[0, 5] = [0.999, -0.999, 0.97]
+    poses32 = poses.astype(np.float32)
+    out = {"poses64": poses, "poses32": poses32}
+    for tag, arr in (("f64", poses), ("f32", poses32)):
+        vols = np.stack([ref.keypoints_to_heatmap_3D(arr[i]) for i in range(arr.shape[0])])      # (6, 17, 64, 64, 64)
+        assert vols.dtype == np.float32
+        kp_i, vox_i, val = HO.to_sparse(vols.reshape(-1, 64, 64, 64))
+        out[tag + "_kp"], out[tag + "_vox"], out[tag + "_val"] = kp_i, vox_i, val
+    np.savez_compressed(os.path.join(GOLD, "heatmaps.npz"), **out)
+    print("wrote heatmaps", {k: v.shape for k, v in out.items()})
+
+
 class MaskedDropout(torch.nn.Module):
     """Stands in for ``torch.nn.Dropout(p)`` in the reference module; same arithmetic, external mask."""
 
@@ -353,6 +391,9 @@ if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "vit":
         vit_case()
         sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "heatmaps":
+        heatmaps_case()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "process_data":
         process_data_case()
         sys.exit(0)
@@ -367,3 +408,4 @@ if __name__ == "__main__":
     ingest_case()
     process_data_case()
     vit_case()
+    heatmaps_case()

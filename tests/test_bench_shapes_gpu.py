@@ -84,12 +84,21 @@ def test_config2_gradients_at_bench_shape(pkg):
     r = lo.lifter_forward_backward(params, buffers, x, lambda o: ((o - y) ** 2).mean(), num_stage=S, training=True,
                                    p_dropout=0.5, masks=masks)
     assert abs(loss.item() - float(r["loss"])) < 5e-3 * float(r["loss"])
+    # tight: the oracle's arithmetic with the kernels' 16-bit rounding points (tests/rounding_model.py); loose: fp32 oracle
+    import rounding_model as rm
+    mod = rm.forward_backward(params, buffers, x, y, masks, num_stage=S, use_bn=True, p=0.5, dtype=torch.bfloat16)
+    report, bad = [], []
     for name, prm in m.named_parameters():
         ref = r["grads"][name]
         if name.endswith(".bias") and "batch_norm" not in name and not name.startswith("w2."):
             assert float(prm.grad.abs().max()) == 0.0, name             # cancelled by train-mode BN
             continue
-        assert rel_l2(prm.grad.cpu(), ref) < 4e-2, f"{name}: {rel_l2(prm.grad.cpu(), ref)}"
+        e_model, e_fp32 = rel_l2(prm.grad.cpu(), mod["grads"][name]), rel_l2(prm.grad.cpu(), ref)
+        report.append(f"{name}: vs rounding model {e_model:.3e}, vs fp32 oracle {e_fp32:.3e}")
+        if e_model > 2e-2 or e_fp32 > 1e-1:
+            bad.append(name)
+    print("\n".join(report))
+    assert not bad, "\n".join(report)
 
 
 def test_config1_eval_at_bench_shape(pkg, golden_dir):

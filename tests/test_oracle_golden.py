@@ -269,3 +269,20 @@ def test_dropout_stream_lane_widths_and_shards():
     for e in range(8):
         want[:, :, e] = ((r[e // 2] >> np.uint32(16 * (e % 2))) & np.uint32(0xFFFF)) >= np.uint32(19661)
     assert (dropout_keep_mask(rows, cols, site, step, seed, p) == want.reshape(rows, cols)).all()
+
+
+def test_heatmap_oracle_matches_reference_golden(golden_dir):
+    """oracle/heatmap_oracle.py against volumes produced by the reference's own keypoints_to_heatmap_3D
+    (H36_dataset.py:143-202, exec of the source slice; stored as their non-zero voxels): bit for bit, for float64 and
+    float32 key points, including windows clipped at one, two and three faces and half-integer voxel coordinates."""
+    from oracle import heatmap_oracle as HO
+    g = dict(np.load(os.path.join(golden_dir, "heatmaps.npz")))
+    for tag, key in (("f64", "poses64"), ("f32", "poses32")):
+        vol = HO.keypoints_to_heatmap_3d(g[key])
+        assert vol.shape == (6, 17, 64, 64, 64) and vol.dtype == np.float32
+        kp_i, vox_i, val = HO.to_sparse(vol.reshape(-1, 64, 64, 64))
+        assert np.array_equal(kp_i, g[tag + "_kp"]) and np.array_equal(vox_i, g[tag + "_vox"])
+        assert np.array_equal(val, g[tag + "_val"])
+    assert HO.window(0.5) == 3 and HO.window(1.75) == 11
+    with pytest.raises(AssertionError):
+        HO.keypoints_to_heatmap_3d(np.array([[0.0, 1.5, 0.0]]))
