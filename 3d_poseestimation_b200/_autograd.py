@@ -23,7 +23,7 @@ def _dist_world(model):
     return pg, dist.get_world_size(pg), dist.get_rank(pg)
 
 
-def _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offset, step_state=None):
+def _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offset, step_state=None, calls=None):
     t = _cabi.TrainCtx()
     t.params = model._flat.data_ptr()
     t.operands = model._operands(fmt).data_ptr()
@@ -38,6 +38,8 @@ def _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offse
     t.fmt, t.bn_mode, t.apply_dropout = fmt, (0 if training else 1), (1 if training else 0)
     t.step, t.seed = step & 0xFFFFFFFF, model.dropout_seed & 0xFFFFFFFFFFFFFFFF
     t.step_state = step_state.data_ptr() if step_state is not None else None
+    if calls is not None:                    # (calls per optimiser step, index of this call): own masks, own exchange slots
+        t.calls_per_step, t.call_index = int(calls[0]), int(calls[1])
     dp = getattr(model, "_dp", None)
     if dp is not None and step_state is not None and training:
         t.dp = C.pointer(dp)                 # in-kernel SyncBN exchange over the symmetric buffer
@@ -45,7 +47,7 @@ def _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offse
 
 
 @_cabi.device_guard
-def run_forward(model, x, training, saved=None, out=None, step=None, step_state=None):
+def run_forward(model, x, training, saved=None, out=None, step=None, step_state=None, calls=None):
     """Forward with saved activations.  Returns (out, saved, ctx_struct)."""
     lib, cfg = _cabi.lib(), C.byref(model._cfg)
     fmt = model._fmt_code(model.train_format)
@@ -63,7 +65,7 @@ def run_forward(model, x, training, saved=None, out=None, step=None, step_state=
         saved = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
     if out is None:
         out = torch.empty(B, model.output_size, dtype=torch.float32, device=x.device)
-    t = _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offset, step_state)
+    t = _make_ctx(model, x, out, saved, fmt, training, step, global_batch, row_offset, step_state, calls)
     st = _cabi.stream_ptr()
     if not sync_bn or bool(t.dp):
         _cabi.check(lib.lifter_train_forward(cfg, C.byref(t), st))

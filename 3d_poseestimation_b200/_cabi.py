@@ -68,6 +68,17 @@ class PoseLossDesc(C.Structure):
                 ("w_bone", C.c_float), ("dpred", C.c_void_p), ("scratch", C.c_void_p), ("out", C.c_void_p)]
 
 
+class Phase5LossDesc(C.Structure):
+    """``lifter_phase5_loss_t``"""
+    _fields_ = [(k, C.c_void_p) for k in ("out_pred", "out_pred_flip", "out_gt", "out_gt_flip", "pred2d", "gt2d", "pred3d",
+                                          "gt3d")] + [("mode", C.c_int32)] + \
+               [(k, C.c_void_p) for k in ("mean3d", "std3d", "mean2d", "std2d", "root", "intrinsics")] + \
+               [("w_reproj", C.c_float), ("w_bone", C.c_float), ("rows", C.c_int64), ("global_rows", C.c_int64),
+                ("joints", C.c_int32)] + \
+               [(k, C.c_void_p) for k in ("d_out_pred", "d_out_pred_flip", "d_out_gt", "d_out_gt_flip", "d_pred2d",
+                                          "d_pred3d", "scratch", "out")]
+
+
 class VitDesc(C.Structure):
     """``lifter_vit_t``: shapes, fp32 parameters and 16-bit GEMM operands of the MyViT lifter."""
     _fields_ = [(k, C.c_int32) for k in ("tokens", "in_dim", "hidden", "heads", "blocks", "mlp_dim", "head_dim", "out_dim",
@@ -130,6 +141,10 @@ SIGNATURES = {
     "lifter_affine_cols": (_I32, [_P, _P, _I64, _I32, _P, _P, _I32, _P]),
     "lifter_pose_loss_scratch_bytes": (_I64, [_I64, _I32]),
     "lifter_pose_loss": (_I32, [C.POINTER(PoseLossDesc), _P]),
+    "lifter_phase5_loss_scratch_bytes": (_I64, [_I64]),
+    "lifter_phase5_loss": (_I32, [C.POINTER(Phase5LossDesc), _P]),
+    "lifter_phase5_input_grad": (_I32, [_P, _P, _P, _I64, _I32, _P, _P]),
+    "lifter_sum_buffers": (_I32, [_P, _P, _P, _P, _P, _I64, _P]),
     "lifter_l1_sum": (_I32, [_P, _P, _I64, _I32, _I32, _F, _P, _P, _P]),
     "lifter_l1_grad": (_I32, [_P, _P, _I64, _I32, _I32, _P, _F, _P, _P, _P]),
     "lifter_adam_step": (_I32, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _I32, _F, _P]),

@@ -17,6 +17,7 @@
 #include "heatmap_ops.cuh"
 #include "layout.cuh"
 #include "loss_adam.cuh"
+#include "phase5_ops.cuh"
 #include "pose_ops.cuh"
 #include "train_kernels.cuh"
 
@@ -695,6 +696,35 @@ int lifter_pose_loss(const lifter_pose_loss_t* d, void* stream) {
     a.w_mpjpe = d->w_mpjpe; a.w_reproj = d->w_reproj; a.w_bone = d->w_bone;
     a.dpred = d->dpred; a.partials = d->scratch; a.out = d->out;
     return pose_loss(a, static_cast<cudaStream_t>(stream));
+}
+
+int64_t lifter_phase5_loss_scratch_bytes(int64_t rows) {
+    if (rows < 1) return LIFTER_ERR_INVALID;
+    return static_cast<int64_t>(phase5_partial_rows(rows)) * 8 * 4;
+}
+
+int lifter_phase5_loss(const lifter_phase5_loss_t* d, void* stream) {
+    LIFTER_REQUIRE(d != nullptr, "phase5_loss: null descriptor");
+    Phase5LossArgs a;
+    a.out_pred = d->out_pred; a.out_pred_flip = d->out_pred_flip; a.out_gt = d->out_gt; a.out_gt_flip = d->out_gt_flip;
+    a.pred2d = d->pred2d; a.gt2d = d->gt2d; a.pred3d = d->pred3d; a.gt3d = d->gt3d; a.mode = d->mode;
+    a.mean3d = d->mean3d; a.std3d = d->std3d; a.mean2d = d->mean2d; a.std2d = d->std2d; a.root = d->root;
+    a.intrinsics = d->intrinsics; a.w_reproj = d->intrinsics != nullptr ? d->w_reproj : 0.0f; a.w_bone = d->w_bone;
+    a.rows = d->rows; a.global_rows = d->global_rows > 0 ? d->global_rows : d->rows; a.J = d->joints;
+    a.d_out_pred = d->d_out_pred; a.d_out_pred_flip = d->d_out_pred_flip; a.d_out_gt = d->d_out_gt;
+    a.d_out_gt_flip = d->d_out_gt_flip; a.d_pred2d = d->d_pred2d; a.d_pred3d = d->d_pred3d;
+    a.partials = d->scratch; a.out = d->out;
+    return phase5_loss(a, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_phase5_input_grad(const float* d_own, const float* dx, const float* dx_flip, int64_t rows, int joints,
+                             float* out, void* stream) {
+    return phase5_input_grad(d_own, dx, dx_flip, rows, joints, out, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_sum_buffers(float* dst, const float* a, const float* b, const float* c, const float* d, int64_t n,
+                       void* stream) {
+    return sum_buffers(dst, a, b, c, d, n, static_cast<cudaStream_t>(stream));
 }
 
 int lifter_l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, float scale, float* scratch,

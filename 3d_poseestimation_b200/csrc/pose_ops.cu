@@ -1,5 +1,7 @@
 #include "pose_ops.cuh"
 
+#include "pose_math.cuh"
+
 namespace lifter {
 
 namespace {
@@ -63,15 +65,7 @@ __global__ void coco2h36m_kernel(const float* __restrict__ in, int C, float* __r
     out[idx] = v;
 }
 
-constexpr int PL_ROWS = 64;             // rows (= threads) per block
-constexpr int PL_MAXJ = 21;
-
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-    for (int s = 16; s >= 1; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
-    return v;
-}
-__device__ __forceinline__ float sgn(float d) { return d > 0.0f ? 1.0f : (d < 0.0f ? -1.0f : 0.0f); }
+__device__ __forceinline__ float warp_sum(float v) { return pl_warp_sum(v); }
 
 // One thread per pose; the block's rows are staged through shared memory with coalesced loads / stores (rows are
 // 204 bytes: a thread-per-row global access pattern would touch 32 sectors per instruction).
@@ -99,62 +93,20 @@ __global__ void __launch_bounds__(PL_ROWS) pose_loss_kernel(PoseLossArgs a) {
     const int r = threadIdx.x;
     const bool live = r < nrows;
     float l_mp = 0.0f, l_rp = 0.0f, l_bn = 0.0f;
-    float P[PL_MAXJ][3], G[PL_MAXJ][3];
+    float G[PL_MAXJ][3];
     const float inv_rows = 1.0f / static_cast<float>(a.global_rows);
     if (live) {
-        const float g_mp = a.w_mpjpe * inv_rows / J, g_rp = a.w_reproj * inv_rows / (2 * J), g_bn = a.w_bone * inv_rows / 16.0f;
-        float rx = 0.0f, ry = 0.0f, rz = 0.0f, fx = 0.0f, fy = 0.0f, cx = 0.0f, cy = 0.0f;
-        if (a.root != nullptr) { rx = a.root[(row0 + r) * 3]; ry = a.root[(row0 + r) * 3 + 1]; rz = a.root[(row0 + r) * 3 + 2]; }
+        PoseRowArgs ra;
+        ra.J = J; ra.mean = a.mean; ra.stdv = a.stdv;
+        ra.g_mp = a.w_mpjpe * inv_rows / J; ra.g_rp = a.w_reproj * inv_rows / (2 * J); ra.g_bn = a.w_bone * inv_rows / 16.0f;
+        ra.reproj = a.intrinsics != nullptr; ra.bone = a.w_bone != 0.0f;
+        ra.rx = ra.ry = ra.rz = ra.fx = ra.fy = ra.cx = ra.cy = 0.0f;
+        if (a.root != nullptr) { ra.rx = a.root[(row0 + r) * 3]; ra.ry = a.root[(row0 + r) * 3 + 1]; ra.rz = a.root[(row0 + r) * 3 + 2]; }
         if (a.intrinsics != nullptr) {
             const float4 k = *reinterpret_cast<const float4*>(a.intrinsics + (row0 + r) * 4);
-            fx = k.x; fy = k.y; cx = k.z; cy = k.w;
+            ra.fx = k.x; ra.fy = k.y; ra.cx = k.z; ra.cy = k.w;
         }
-        float T[PL_MAXJ][3];
-#pragma unroll
-        for (int j = 0; j < PL_MAXJ; ++j) {
-            if (j >= J) break;
-#pragma unroll
-            for (int d = 0; d < 3; ++d) {
-                const float sd = a.stdv != nullptr ? a.stdv[3 * j + d] : 1.0f, mu = a.mean != nullptr ? a.mean[3 * j + d] : 0.0f;
-                P[j][d] = fmaf(s_pred[r * O + 3 * j + d], sd, mu);
-                T[j][d] = fmaf(s_tgt[r * O + 3 * j + d], sd, mu);
-            }
-            // MPJPE (losses.py:3-7 per joint; two2three.py:389-392 mean): torch.norm's gradient is 0 at 0
-            const float dx = P[j][0] - T[j][0], dy = P[j][1] - T[j][1], dz = P[j][2] - T[j][2];
-            const float e = sqrtf(dx * dx + dy * dy + dz * dz);
-            l_mp += e;
-            atomicAdd(&s_metric[j], e);
-            const float s = e > 0.0f ? g_mp / e : 0.0f;
-            G[j][0] = s * dx; G[j][1] = s * dy; G[j][2] = s * dz;
-            if (a.intrinsics != nullptr) {          // pinhole reprojection, pixel / 1000 (PARITY UNPINNED)
-                const float X = P[j][0] + rx, Y = P[j][1] + ry, Z = P[j][2] + rz;
-                const float iz = 1.0f / Z;
-                const float u = (fx * X * iz + cx) * 1e-3f, v = (fy * Y * iz + cy) * 1e-3f;
-                const float du = u - s_t2d[r * 2 * J + 2 * j], dv = v - s_t2d[r * 2 * J + 2 * j + 1];
-                l_rp += fabsf(du) + fabsf(dv);
-                const float su = sgn(du) * g_rp * 1e-3f * fx * iz, sv = sgn(dv) * g_rp * 1e-3f * fy * iz;
-                G[j][0] += su;
-                G[j][1] += sv;
-                G[j][2] -= (su * X + sv * Y) * iz;
-            }
-        }
-        if (a.w_bone != 0.0f && J == 17) {          // bone lengths over the 16 skeleton edges (PARITY UNPINNED)
-            // (compile-time joint indices keep P / T / G in registers)
-#define LIFTER_BONE(p, c)                                                                                     \
-    {                                                                                                         \
-        const float bx = P[c][0] - P[p][0], by = P[c][1] - P[p][1], bz = P[c][2] - P[p][2];                   \
-        const float tx = T[c][0] - T[p][0], ty = T[c][1] - T[p][1], tz = T[c][2] - T[p][2];                   \
-        const float lp = sqrtf(bx * bx + by * by + bz * bz), lt = sqrtf(tx * tx + ty * ty + tz * tz);         \
-        l_bn += fabsf(lp - lt);                                                                               \
-        const float s = lp > 0.0f ? sgn(lp - lt) * g_bn / lp : 0.0f;                                          \
-        G[c][0] += s * bx; G[c][1] += s * by; G[c][2] += s * bz;                                              \
-        G[p][0] -= s * bx; G[p][1] -= s * by; G[p][2] -= s * bz;                                              \
-    }
-            LIFTER_BONE(0, 1) LIFTER_BONE(1, 2) LIFTER_BONE(2, 3) LIFTER_BONE(0, 4) LIFTER_BONE(4, 5) LIFTER_BONE(5, 6)
-            LIFTER_BONE(0, 7) LIFTER_BONE(7, 8) LIFTER_BONE(8, 9) LIFTER_BONE(9, 10) LIFTER_BONE(8, 11)
-            LIFTER_BONE(11, 12) LIFTER_BONE(12, 13) LIFTER_BONE(8, 14) LIFTER_BONE(14, 15) LIFTER_BONE(15, 16)
-#undef LIFTER_BONE
-        }
+        pose_row_terms(ra, s_pred + r * O, s_tgt + r * O, s_t2d + r * 2 * J, G, l_mp, l_rp, l_bn, s_metric);
     }
     __syncthreads();                                // every thread is done reading s_pred
     if (a.dpred != nullptr) {

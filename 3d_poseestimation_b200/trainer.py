@@ -458,6 +458,146 @@ class LifterTrainer:
         self._sync_state()
 
 
+class Phase5Trainer(LifterTrainer):
+    """The loop body of the phase-5 script around the lifter as ONE replayable kernel sequence
+    (``phase5_loop/backup_june8.py:120-175``; same shape in ``train_5.py:123-205``):
+
+        lift_pred = (flip_pose(lift(flip_pose(y1_hat))) + lift(y1_hat)) / 2        four train-mode lifter forwards,
+        lift_gt   = (flip_pose(lift(flip_pose(y1))) + lift(y1)) / 2                each with its own BatchNorm batch
+        loss = TriangleLoss(y1_hat, y2_hat, lift_gt, lift_pred, y1, y2)            statistics and dropout masks
+        loss.backward(); optimizer_lift.step()
+
+    ``y1_hat`` / ``y2_hat`` are what the image models predict (out of scope here: they arrive as tensors); the step
+    leaves ``d loss / d y1_hat`` and ``d loss / d y2_hat`` in ``grad_pred2d`` / ``grad_pred3d`` for them, and updates the
+    lifter with AdamW (``backup_june8.py:83``).  ``loss="triangle"`` is ``TriangleLoss`` (the lifts of the ground-truth
+    key points run -- they move the BatchNorm running statistics -- but get no gradient), ``"triangle_sep"``
+    ``TriangleLoss_sep`` (``train_5.py:73``).  ``w_reproj`` / ``w_bone`` add the pinhole-reprojection and bone-length
+    terms on ``lift_pred`` -- PARITY UNPINNED, there is no reference implementation -- which need
+    ``stats3d=(mean, std)``, and for the reprojection ``intrinsics`` per pose, ``stats2d`` and optionally ``root``.
+    ``step(y1_hat, y2_hat, y1, y2[, intrinsics])``; ``losses`` holds ``[total, loss_2d, loss_3d, loss_lift, gap,
+    reprojection, bone, 0]`` on the device (the reference reads four of them with ``.cpu().item()`` every step).
+    """
+
+    def __init__(self, model, lr=1e-4, loss="triangle", optimizer="adamw", flip=True, w_reproj=0.0, w_bone=0.0,
+                 stats3d=None, stats2d=None, root=None, **kw):
+        if loss not in ("triangle", "triangle_sep"):
+            raise ValueError("Phase5Trainer: loss must be 'triangle' (TriangleLoss) or 'triangle_sep' (TriangleLoss_sep)")
+        if model.input_size % 2 != 0 or model.output_size // 3 * 2 != model.input_size:
+            raise ValueError("Phase5Trainer lifts (J, 2) key points to (J, 3) joints")
+        self.mode = 1 if loss == "triangle_sep" else 0
+        self.flip = bool(flip)
+        super().__init__(model, lr=lr, loss="l1", optimizer=optimizer, **kw)
+        dev = model._flat.device
+        J = self.joints
+        self.w_reproj, self.w_bone = float(w_reproj), float(w_bone)
+
+        def vec(v, n):
+            return None if v is None else torch.as_tensor(v, dtype=torch.float32, device=dev).reshape(-1).contiguous()[:n]
+        self.mean3d, self.std3d = (vec(stats3d[0], 3 * J), vec(stats3d[1], 3 * J)) if stats3d is not None else (None, None)
+        self.mean2d, self.std2d = (vec(stats2d[0], 2 * J), vec(stats2d[1], 2 * J)) if stats2d is not None else (None, None)
+        self.root = vec(root, 3)
+        if (self.w_reproj or self.w_bone) and self.mean3d is None:
+            raise ValueError("Phase5Trainer: the reprojection / bone terms work on de-standardised joints: pass stats3d")
+        self.losses = torch.zeros(8, dtype=torch.float32, device=dev)
+        self.loss_out = self.losses                                        # [0] is the total, like the base class
+        self.grad_pred2d = self.grad_pred3d = None
+
+    def _bn_calls_per_step(self):
+        return 4 if getattr(self, "flip", True) else 2
+
+    def _alloc_buffers(self, B, dev):
+        lib, cfg = _cabi.lib(), C.byref(self.model._cfg)
+        O, I, n = self.model.output_size, self.model.input_size, self._bn_calls_per_step()
+        nb = _cabi.check(lib.lifter_train_saved_bytes(cfg, B))
+        f32 = dict(dtype=torch.float32, device=dev)
+        return dict(
+            saved=[torch.empty(nb, dtype=torch.uint8, device=dev) for _ in range(n)],
+            scratch=torch.empty(_cabi.check(lib.lifter_train_scratch_bytes(cfg, B)), dtype=torch.uint8, device=dev),
+            out=[torch.empty(B, O, **f32) for _ in range(n)], dout=[torch.empty(B, O, **f32) for _ in range(n)],
+            xflip=[torch.empty(B, I, **f32) for _ in range(2)], dx=[torch.empty(B, I, **f32) for _ in range(2)],
+            d2_own=torch.empty(B, I, **f32), d2=torch.empty(B, I, **f32), d3=torch.empty(B, O, **f32),
+            grads=[torch.empty_like(self.model._flat) for _ in range(n)],
+            root=None if self.root is None else self.root.reshape(1, 3).expand(B, 3).contiguous(),
+            lscratch=torch.empty(_cabi.check(lib.lifter_phase5_loss_scratch_bytes(B)), dtype=torch.uint8, device=dev))
+
+    def _check_inputs(self, y1_hat, y2_hat, y1, y2, intrinsics=None):
+        model = self.model
+        a = model._check_input(y1_hat)
+        g2 = model._check_input(y1)
+        B = a.shape[0]
+        out = [a]
+        for t, width, what in ((y2_hat, model.output_size, "predicted 3D pose"), (g2, model.input_size, "2D key points"),
+                               (y2, model.output_size, "3D pose")):
+            t = t.reshape(t.shape[0], -1)
+            if t.shape != (B, width) or t.dtype != torch.float32 or not t.is_cuda:
+                raise RuntimeError(f"{what}: expected a float32 CUDA tensor of {B} x {width} values")
+            out.append(t.contiguous())
+        if intrinsics is not None:
+            k = intrinsics.reshape(intrinsics.shape[0], -1)
+            if k.shape != (B, 4) or k.dtype != torch.float32 or not k.is_cuda:
+                raise RuntimeError(f"intrinsics: expected a float32 CUDA tensor of {B} x 4 values (fx, fy, cx, cy)")
+            out.append(k.contiguous())
+        elif self.w_reproj:
+            raise RuntimeError("Phase5Trainer(w_reproj != 0): step() needs the camera intrinsics of every pose")
+        return tuple(out)
+
+    def _enqueue(self, inputs, b, accumulate_metric, state):
+        y1_hat, y2_hat, y1, y2 = inputs[:4]
+        intr = inputs[4] if len(inputs) > 4 else None
+        model = self.model
+        lib, cfg = _cabi.lib(), C.byref(model._cfg)
+        B, J, st = y1_hat.shape[0], self.joints, _cabi.stream_ptr()
+        n = self._bn_calls_per_step()
+        if state is not None:
+            _cabi.check(lib.lifter_step_advance(_cabi.ptr(state), self.betas[0], self.betas[1],
+                                                self.weight_decay if self.decoupled else 0.0, st))
+        xs = [y1_hat, y1]                                  # backup_june8.py:137-138, then the flipped twins :152-153
+        if self.flip:
+            for k, src in enumerate((y1_hat, y1)):
+                _cabi.check(lib.lifter_flip_pose(_cabi.ptr(src), _cabi.ptr(b["xflip"][k]), B, J, 2, 0, st))
+            xs += b["xflip"]
+        ctxs = []
+        for k, x in enumerate(xs):                         # every call: own batch statistics, masks, running-stat update
+            _, _, t = _autograd.run_forward(model, x, True, saved=b["saved"][k], out=b["out"][k], step=self.step_count,
+                                            step_state=state, calls=(n, k))
+            ctxs.append(t)
+        d = _cabi.Phase5LossDesc()
+        d.out_pred, d.out_gt = b["out"][0].data_ptr(), b["out"][1].data_ptr()
+        d.d_out_pred, d.d_out_gt = b["dout"][0].data_ptr(), b["dout"][1].data_ptr()
+        if self.flip:
+            d.out_pred_flip, d.out_gt_flip = b["out"][2].data_ptr(), b["out"][3].data_ptr()
+            d.d_out_pred_flip, d.d_out_gt_flip = b["dout"][2].data_ptr(), b["dout"][3].data_ptr()
+        d.pred2d, d.gt2d, d.pred3d, d.gt3d = y1_hat.data_ptr(), y1.data_ptr(), y2_hat.data_ptr(), y2.data_ptr()
+        d.mode = self.mode
+        for name in ("mean3d", "std3d", "mean2d", "std2d"):
+            v = getattr(self, name)
+            setattr(d, name, None if v is None else v.data_ptr())
+        d.root = None if b["root"] is None else b["root"].data_ptr()
+        d.intrinsics = None if (intr is None or not self.w_reproj) else intr.data_ptr()
+        d.w_reproj, d.w_bone = self.w_reproj, self.w_bone
+        d.rows, d.global_rows, d.joints = B, B * self.world, J
+        d.d_pred2d, d.d_pred3d = b["d2_own"].data_ptr(), b["d3"].data_ptr()
+        d.scratch, d.out = b["lscratch"].data_ptr(), self.losses.data_ptr()
+        _cabi.check(lib.lifter_phase5_loss(C.byref(d), st))
+        # backward of every forward that reached the loss: the lifts of the predicted key points also return the
+        # gradient w.r.t. their input (it flows on into the 2D model, SURVEY 3.3)
+        live = [k for k in range(n) if self.mode == 1 or k % 2 == 0]
+        for k in live:
+            _autograd.run_backward(model, ctxs[k], b["dout"][k], b["grads"][k], b["dx"][k // 2] if k % 2 == 0 else None,
+                                   scratch=b["scratch"])
+        g = [b["grads"][k] for k in live]
+        if len(g) == 1:
+            self.grad.copy_(g[0])
+        else:
+            _cabi.check(lib.lifter_sum_buffers(_cabi.ptr(self.grad), _cabi.ptr(g[0]), _cabi.ptr(g[1]),
+                                               _cabi.ptr(g[2]) if len(g) > 2 else None,
+                                               _cabi.ptr(g[3]) if len(g) > 3 else None, self.grad.numel(), st))
+        _cabi.check(lib.lifter_phase5_input_grad(_cabi.ptr(b["d2_own"]), _cabi.ptr(b["dx"][0]),
+                                                 _cabi.ptr(b["dx"][1]) if self.flip else None, B, J, _cabi.ptr(b["d2"]), st))
+        self.grad_pred2d, self.grad_pred3d = b["d2"], b["d3"]
+        self._optimise(None, None, None, state, fused_backward=False)
+
+
 @_cabi.device_guard
 def evaluate(model, batches, loss="mse", flip=None, metric_std=None, n_samples=None, zero_centre=True):
     """The validation loop of ``train_1.py:112-145`` without its per-batch host syncs.

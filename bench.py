@@ -49,6 +49,11 @@ FLOP_PER_POSE_WIDE_TRAIN = 206_409_728
 # configs[3]: four lifter forwards per pose (pred / gt keypoints, each plus its flipped twin) and the backward of the
 # two that reach the loss, with the gradient into the predicted 2D input (SURVEY §3.3, §8d "25,688,064 if input grad")
 FLOP_PER_POSE_PHASE5 = 4 * FLOP_PER_POSE_INFER + 2 * (25_688_064 - FLOP_PER_POSE_INFER)
+# my_HybrIK/utils.py:131-172: (fx, fy, cx, cy) in pixels of the four Human3.6M cameras
+H36M_INTRINSICS = [(1145.0494384765625, 1143.7811279296875, 512.54150390625, 515.4514770507812),
+                   (1149.6756591796875, 1147.5916748046875, 508.8486328125, 508.0649108886719),
+                   (1149.1407470703125, 1148.7989501953125, 519.8158569335938, 501.40264892578125),
+                   (1145.5113525390625, 1144.77392578125, 514.9682006835938, 501.88201904296875)]
 WORKLOADS = {"eval": "configs[1]", "train": "configs[2]", "phase5": "configs[3]", "wide": "configs[4]"}
 
 
@@ -125,14 +130,16 @@ def synth_wide(batch, seed):
 def synth_phase5(batch, seed):
     """configs[3]: what the phase-5 loop hands the lifter per step (backup_june8.py:128-138): the 2D model's prediction
     ``y1_hat`` and the 3D model's ``y2_hat`` (stand-ins: ground truth + noise, the image CNNs are out of scope), the
-    ground truth ``y1`` / ``y2``, and a camera id per pose for the (parity-unpinned) reprojection term."""
+    ground truth ``y1`` / ``y2``, and the intrinsics of a camera drawn per pose (my_HybrIK/utils.py:131-172) for the
+    parity-unpinned reprojection term."""
     import torch
     y1, y2 = synth_batch(batch, seed)
     g = torch.Generator().manual_seed(seed + 7919)
     y1_hat = y1 + 0.05 * torch.randn(y1.shape, generator=g)
     y2_hat = y2 + 0.10 * torch.randn(y2.shape, generator=g)
     cam = torch.randint(0, 4, (batch,), generator=g)
-    return y1_hat.contiguous(), y2_hat.contiguous(), y1, y2, cam
+    intr = torch.tensor(H36M_INTRINSICS, dtype=torch.float32)[cam].contiguous()      # (fx, fy, cx, cy) per pose
+    return y1_hat.contiguous(), y2_hat.contiguous(), y1, y2, intr
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm
@@ -201,7 +208,7 @@ def cpu_arm(workload, steps, warmup, budget_s=25.0, with_c1=True):
     elif workload == "phase5":
         from oracle import losses_oracle as L          # flip_pose: my_HybrIK/utils.py imports matplotlib (absent)
         batch = TRAIN_BATCH
-        y1_hat, y2_hat, y1, y2, _ = synth_phase5(batch, 0)
+        y1_hat, y2_hat, y1, y2, _ = synth_phase5(batch, 0)       # (the reference has no reprojection term to feed)
         model.train()
         opt = torch.optim.AdamW(model.parameters(), lr=1e-4)
         tri = rl.TriangleLoss()
@@ -327,7 +334,15 @@ def gpu_arm(args, rank, world, local_rank):
     def build_trainer(workload, model, lr=1e-4, dp=True):
         kw = dict(world_size=world, rank=rank, require_symmetric=True) if (dp and world > 1) else {}
         if workload == "phase5":
-            return trainer_mod.Phase5Trainer(model, lr=lr, optimizer="adamw", seed=2, w_reproj=0.1, w_bone=0.1, **kw)
+            import numpy as np
+            st = dict(np.load(os.path.join(ROOT, "tests", "golden", "h36m_stats.npz")))
+            m3 = torch.from_numpy(st["mean_train_3d"]).float().clone()
+            root = m3[0].clone()
+            m3[0] = 0                         # zero_centre (H36_dataset.py:288-289): the root's mean is the absolute root
+            return trainer_mod.Phase5Trainer(model, lr=lr, loss="triangle", optimizer="adamw", seed=2, w_reproj=0.1,
+                                             w_bone=0.1, stats3d=(m3, torch.from_numpy(st["std_train_3d"]).float()),
+                                             stats2d=(torch.from_numpy(st["mean_train_2d"]).float(),
+                                                      torch.from_numpy(st["std_train_2d"]).float()), root=root, **kw)
         return trainer_mod.LifterTrainer(model, lr=lr, loss="mse", optimizer="adam", seed=2, **kw)
 
     def host_batch(workload, batch, seed):

@@ -240,6 +240,45 @@ typedef struct lifter_pose_loss {
 int64_t lifter_pose_loss_scratch_bytes(int64_t rows, int joints);
 int lifter_pose_loss(const lifter_pose_loss_t* desc, void* stream);
 
+/* The loss of the phase-5 loop around the lifter (phase5_loop/backup_june8.py:137-161, train_5.py:145-181) as ONE
+ * kernel + one finalize: flip averaging lift = (flip_pose(lifter(flip_pose(x))) + lifter(x)) / 2 of both lifts, the L1
+ * terms of TriangleLoss (mode 0, losses.py:24-53: L1(pred2d, gt2d) + L1(pred3d, gt3d) + L1(lift_pred, pred3d)) or
+ * TriangleLoss_sep (mode 1, losses.py:81-110: L1(pred2d, gt2d) + L1(pred3d, gt3d) + L1(lift_gt, gt3d) +
+ * L1(lift_pred, lift_gt)), Project = False, and every gradient the loop back-propagates: w.r.t. the (up to) four lifter
+ * outputs, the predicted 2D key points (the loss's own share; the lifter's input gradient is added by
+ * lifter_phase5_input_grad) and the predicted 3D pose.  Optional terms on lift_pred with NO reference implementation
+ * (PARITY UNPINNED): pinhole reprojection L1 and bone-length L1, as in lifter_pose_loss.
+ * out[8] = total, loss_2d, loss_3d, loss_lift, domain gap (mode 1), reprojection, bone, 0 -- the reference returns
+ * (total, loss_2d, loss_3d, loss_lift, loss_proj) and reads each with .cpu().item() every step (losses.py:48-51).   */
+typedef struct lifter_phase5_loss {
+    const float* out_pred;        /* [rows][joints*3] lifter(pred 2D)                                              */
+    const float* out_pred_flip;   /* lifter(flip_pose(pred 2D)); nullable: Flip = False                            */
+    const float* out_gt;          /* lifter(gt 2D); nullable in mode 0 (TriangleLoss does not read it)             */
+    const float* out_gt_flip;
+    const float* pred2d; const float* gt2d;      /* [rows][joints*2]                                               */
+    const float* pred3d; const float* gt3d;      /* [rows][joints*3]                                               */
+    int32_t mode;
+    const float* mean3d; const float* std3d;     /* [joints*3] nullable: joints = v * std + mean (unpinned terms)  */
+    const float* mean2d; const float* std2d;     /* [joints*2] nullable: gt2d * std + mean = key points, pixel/1000 */
+    const float* root;                           /* [rows][3] nullable                                             */
+    const float* intrinsics;                     /* [rows][4] fx fy cx cy (pixels), nullable: no reprojection      */
+    float w_reproj, w_bone;
+    int64_t rows, global_rows; int32_t joints;
+    float* d_out_pred; float* d_out_pred_flip; float* d_out_gt; float* d_out_gt_flip;
+    float* d_pred2d; float* d_pred3d;
+    float* scratch;                              /* lifter_phase5_loss_scratch_bytes()                             */
+    float* out;                                  /* [8]                                                            */
+} lifter_phase5_loss_t;
+int64_t lifter_phase5_loss_scratch_bytes(int64_t rows);
+int lifter_phase5_loss(const lifter_phase5_loss_t* desc, void* stream);
+/* out = d_own + dx + flip_pose-VJP(dx_flip): gradient w.r.t. the predicted 2D key points from the loss itself, the plain
+ * lifter forward and the flipped one (dx_flip nullable).  [rows][joints*2]                                          */
+int lifter_phase5_input_grad(const float* d_own, const float* dx, const float* dx_flip, int64_t rows, int joints,
+                             float* out, void* stream);
+/* dst = a + b (+ c + d): sums the flat parameter gradients of the backward passes of one step; n %% 4 == 0.        */
+int lifter_sum_buffers(float* dst, const float* a, const float* b, const float* c, const float* d, int64_t n,
+                       void* stream);
+
 /* torch.optim.Adam / AdamW (train_1.py:39) over the flat buffer; step is 1-based; n %% 4 == 0.           */
 int lifter_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                      float eps, float weight_decay, int decoupled, int step, float grad_scale, void* stream);
