@@ -92,7 +92,7 @@ __global__ void __launch_bounds__(PL_ROWS) phase5_loss_kernel(Phase5LossArgs a) 
                 if (have_gt) og[3 * j + d] = dlg;             // d_lift_gt, split over the two outputs below
             }
         }
-        __syncwarp();
+        // (no warp-level sync here: a thread touches only its own row, and rows past the batch skip this branch)
         // ---- unpinned terms on the lifted pose (same per-pose arithmetic as the fused pose-loss kernel)
         if (a.intrinsics != nullptr || a.w_bone != 0.0f) {
             PoseRowArgs ra;
