@@ -94,6 +94,7 @@ class VitGrads(C.Structure):
 
 
 LOSS_MSE, LOSS_L1, LOSS_MPJPE = 0, 1, 2
+LOSS_STATIC_MAX_ROWS = 65536
 DP_MAX_WORLD = 8
 DP_FLAG_BYTES = 256
 
@@ -141,6 +142,7 @@ SIGNATURES = {
     "lifter_affine_cols": (_I32, [_P, _P, _I64, _I32, _P, _P, _I32, _P]),
     "lifter_pose_loss_scratch_bytes": (_I64, [_I64, _I32]),
     "lifter_pose_loss": (_I32, [C.POINTER(PoseLossDesc), _P]),
+    "lifter_loss_static": (_I32, [_P, _P, _I64, _I32, _I32, _I64, _P, _P, _P, _I32, _P]),
     "lifter_phase5_loss_scratch_bytes": (_I64, [_I64]),
     "lifter_phase5_loss": (_I32, [C.POINTER(Phase5LossDesc), _P]),
     "lifter_phase5_input_grad": (_I32, [_P, _P, _P, _I64, _I32, _P, _P]),

@@ -424,4 +424,46 @@ int step_advance(void* state, float beta1, float beta2, float weight_decay, cuda
     return LIFTER_OK;
 }
 
+// ---------------------------------------------------------------------------------- no-allocation variant of the loss
+// lifter_loss_static (include/lifter_b200.h): the fused loss with its per-block partial sums in a file-scope device array
+// instead of caller-provided scratch -- for callers that cannot allocate (CUDA-graph capture, serving loops, harnesses
+// that forbid cudaMalloc).  Every GPU that loads the library holds the array (88 KB) until the process exits.
+constexpr long LOSS_STATIC_MAX_ROWS = LIFTER_LOSS_STATIC_MAX_ROWS;                       // 65,536 rows per call
+constexpr long LOSS_STATIC_FLOATS = (LOSS_STATIC_MAX_ROWS / LOSS_ROWS_PER_BLOCK) * (1 + MAX_J);   // 1,024 blocks x 22
+static __device__ __align__(256) float g_loss_static_scratch[LOSS_STATIC_FLOATS];
+
+// In host code `g_loss_static_scratch` is a host-side stand-in, not a device address: the kernels get the address that
+// cudaGetSymbolAddress reports for the CURRENT device, looked up once per device and cached.
+static int loss_static_scratch(float** out) {
+    static float* per_device[64] = {};
+    int dev = 0;
+    LIFTER_CHECK_CUDA(cudaGetDevice(&dev));
+    LIFTER_REQUIRE(dev >= 0 && dev < 64, "loss_static: device index %d out of range", dev);
+    if (per_device[dev] == nullptr) {
+        void* ptr = nullptr;
+        LIFTER_CHECK_CUDA(cudaGetSymbolAddress(&ptr, g_loss_static_scratch));
+        LIFTER_REQUIRE(ptr != nullptr, "loss_static: cudaGetSymbolAddress returned a null address");
+        per_device[dev] = static_cast<float*>(ptr);
+    }
+    *out = per_device[dev];
+    return LIFTER_OK;
+}
+
 }  // namespace lifter
+
+extern "C" int lifter_loss_static(const float* pred, const float* target, int64_t rows, int joints, int kind,
+                                  int64_t global_rows, const float* stdv, float* dpred, float* out,
+                                  int accumulate_metric, void* stream) {
+    using namespace lifter;
+    LIFTER_REQUIRE(pred && target && out, "loss_static: null pointer");
+    LIFTER_REQUIRE(rows >= 1 && rows <= LOSS_STATIC_MAX_ROWS,
+                   "loss_static: %lld rows exceed the static scratch (at most %ld rows per call; use lifter_loss with "
+                   "caller-provided scratch for larger batches)", static_cast<long long>(rows), LOSS_STATIC_MAX_ROWS);
+    LIFTER_REQUIRE(joints >= 1 && joints <= MAX_J, "loss_static: %d joints unsupported (1..%d)", joints, MAX_J);
+    float* scratch = nullptr;
+    LIFTER_PROPAGATE(loss_static_scratch(&scratch));
+    // nothing in the scratch has to start at zero: block b of the loss kernel overwrites all 1 + joints floats of its
+    // partial row and the finalize kernel reads only the rows this call wrote, so the last call's contents are inert
+    return fused_loss(pred, target, rows, joints, kind, static_cast<double>(global_rows), stdv, dpred, scratch, out,
+                      accumulate_metric, static_cast<cudaStream_t>(stream));
+}

@@ -177,6 +177,18 @@ int lifter_train_backward(const lifter_config_t* cfg, const lifter_train_ctx_t* 
 int64_t lifter_loss_scratch_bytes(int64_t rows, int joints);
 int lifter_loss(const float* pred, const float* target, int64_t rows, int joints, int kind, int64_t global_rows,
                 const float* stdv, float* dpred, float* scratch, float* out, int accumulate_metric, void* stream);
+/* lifter_loss WITHOUT caller-provided scratch and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, arithmetic and results as lifter_loss; the per-block partial
+ * sums live in a file-scope `static __device__` array of the library (88 KB, held by every GPU that loads the library
+ * until the process exits), so rows <= LIFTER_LOSS_STATIC_MAX_ROWS and joints <= 21 -- larger calls are rejected with
+ * LIFTER_ERR_INVALID.  Calls no cudaMalloc / cudaFree / allocating routine; the first call on a device looks the
+ * array's address up once (cudaGetSymbolAddress, with that device current -- make it before a graph capture).  EVERY
+ * call on a device shares the one array: calls that overlap on the GPU (two streams, two threads) race -- serialise them
+ * on one stream.  Nothing in the array needs clearing between calls (each call overwrites what it reads).          */
+#define LIFTER_LOSS_STATIC_MAX_ROWS 65536
+int lifter_loss_static(const float* pred, const float* target, int64_t rows, int joints, int kind, int64_t global_rows,
+                       const float* stdv, float* dpred, float* out, int accumulate_metric, void* stream);
 /* L1 building blocks of TriangleLoss / TriangleLoss_sep (losses.py:10-119); centre = the reference's
  * "t[1:] -= t[0]" on both tensors.  scratch: ceil(n / 2048) floats.                                      */
 int lifter_l1_sum(const float* a, const float* b, int64_t n, int row_len, int centre, float scale, float* scratch,
