@@ -425,16 +425,21 @@ def gpu_arm(args, rank, world, local_rank):
         sustained = None
         if with_clocks:
             with ClockSampler(local_rank) as clk:
+                t_wait = time.perf_counter()                    # the first nvidia-smi query on a fresh box can take > 1 s:
+                while not clk.samples and time.perf_counter() - t_wait < 8.0:     # let it answer once before timing
+                    time.sleep(0.05)
+                barrier()
+                start = len(clk.samples)
                 ms = timed(step, steps, warmup)
-                in_region = len(clk.samples)
+                in_region = len(clk.samples) - start
                 # nvidia-smi answers every ~0.1 s, so a 20-step region sees no sample.  The same step therefore runs on
-                # for >= 1.5 s as a second, separately timed region ("sustained").  Its step count derives from the
+                # for >= 2 s as a second, separately timed region ("sustained").  Its step count derives from the
                 # max-over-ranks step time, so every rank runs the same number of (exchanging) steps.
-                n_sus = max(steps, int(1500.0 / max(ms, 1e-3)))
+                n_sus = max(steps, int(2000.0 / max(ms, 1e-3)))
                 first = len(clk.samples)
                 ms_sus = timed(step, n_sus, 0)
                 last = len(clk.samples)
-            clocks = clk.summary()
+            clocks = clk.summary(start)                         # samples taken under load only
             clocks["samples_in_timed_region"] = in_region
             sc = clk.summary(first, last)
             sc["samples_in_timed_region"] = sc.pop("samples")
