@@ -49,6 +49,16 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 int num_sms();   // cached SM count of the current device
+// cudaFuncSetAttribute is PER DEVICE: a launcher keeps one PerDeviceOnce per kernel and configures the kernel the first
+// time it runs on each device (a process-wide flag left the second GPU of a process unconfigured: "invalid argument").
+struct PerDeviceOnce {
+    bool done[64] = {};
+    bool* slot() {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+        return &done[dev];
+    }
+};
 bool pdl_enabled();   // programmatic dependent launch on every kernel (LIFTER_NO_PDL=1 turns it off)
 long long launch_count();           // kernel launches issued by this library so far (captured launches count once)
 long long dp_spin_limit_clocks();   // give-up time of the cross-GPU waits in SM clocks (0 = never); LIFTER_DP_TIMEOUT_S

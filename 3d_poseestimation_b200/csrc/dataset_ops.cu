@@ -334,7 +334,8 @@ int keypoint_stats(const float* data, int64_t frames, int J, int D, int zc, doub
     const int blocks = keypoint_stats_blocks(frames, cols);
     if (reinterpret_cast<uintptr_t>(data) % 16 == 0) {               // bulk copies need a 16-byte aligned source
         const size_t smem = static_cast<size_t>(DS_STAGES) * DS_TR * cols * sizeof(float);
-        static bool configured = false;
+        static PerDeviceOnce once;
+    bool& configured = *once.slot();
         if (!configured) {
             LIFTER_CHECK_CUDA(cudaFuncSetAttribute(keypoint_stats_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                    DS_STAGES * DS_TR * DS_MAXC * static_cast<int>(sizeof(float))));
@@ -369,7 +370,8 @@ int process_keypoints(const float* in, float* out, int64_t frames, int J, int D,
     const int ocols = cols - (root_mode == ROOT_DROP ? D : 0);
     if (reinterpret_cast<uintptr_t>(in) % 16 == 0) {                 // bulk copies need a 16-byte aligned source
         const size_t smem = static_cast<size_t>(DS_STAGES) * DS_TR * cols * sizeof(float);
-        static bool configured = false;
+        static PerDeviceOnce once;
+    bool& configured = *once.slot();
         if (!configured) {
             LIFTER_CHECK_CUDA(cudaFuncSetAttribute(process_keypoints_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                    DS_STAGES * DS_TR * DS_MAXC * static_cast<int>(sizeof(float))));

@@ -548,7 +548,8 @@ template <int BLOCK_N, bool TWO_SM, bool GELU = false>
 int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     using C = Cfg<BLOCK_N, TWO_SM>;
     constexpr int CL = TWO_SM ? 2 : 1;
-    static bool configured = false;
+    static PerDeviceOnce once;
+    bool& configured = *once.slot();
     if (!configured) {
         LIFTER_CHECK_CUDA(cudaFuncSetAttribute(lifter_gemm_kernel<BLOCK_N, TWO_SM, GELU>,
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));

@@ -253,7 +253,8 @@ int phase5_loss(const Phase5LossArgs& a, cudaStream_t st) {
     LIFTER_REQUIRE((a.mean3d == nullptr) == (a.std3d == nullptr) && (a.mean2d == nullptr) == (a.std2d == nullptr),
                    "phase5_loss: mean and std come together");
     LIFTER_REQUIRE(a.w_bone == 0.0f || a.J == 17, "phase5_loss: the bone-length term is defined on the 17-joint H36M skeleton");
-    static bool configured = false;
+    static PerDeviceOnce once;
+    bool& configured = *once.slot();
     const size_t smem = (static_cast<size_t>(PL_ROWS) * (6 * 3 * a.J + 2 * 2 * a.J) + 6 * (PL_ROWS / 32) + 4) * sizeof(float);
     LIFTER_REQUIRE(smem <= 200 * 1024, "phase5_loss: tile does not fit shared memory");
     if (!configured) {

@@ -217,7 +217,8 @@ int pose_loss(const PoseLossArgs& a, cudaStream_t st) {
     LIFTER_REQUIRE((a.mean == nullptr) == (a.stdv == nullptr), "pose_loss: mean and std come together");
     LIFTER_REQUIRE(a.intrinsics == nullptr || a.target2d != nullptr, "pose_loss: reprojection needs the 2D target");
     LIFTER_REQUIRE(a.w_bone == 0.0f || a.J == 17, "pose_loss: the bone-length term is defined on the 17-joint H36M skeleton");
-    static bool configured = false;
+    static PerDeviceOnce once;
+    bool& configured = *once.slot();
     const size_t smem = (static_cast<size_t>(PL_ROWS) * (3 * a.J + 3 * a.J + 2 * a.J) + PL_MAXJ + 3 * (PL_ROWS / 32) + 4) * sizeof(float);
     if (!configured) {
         LIFTER_CHECK_CUDA(cudaFuncSetAttribute(pose_loss_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));

@@ -482,7 +482,7 @@ def gpu_arm(args, rank, world, local_rank):
         """N data-parallel ranks == one process on the concatenated global batch (SURVEY §8c multi-GPU oracle), on the
         exact path that was just timed (graph replay, in-kernel SyncBN exchange, per-layer reduce-scatter/Adam/all-gather
         on the side stream)."""
-        batch, lr = TRAIN_BATCH, 1e-3
+        batch, lr = TRAIN_BATCH, 1e-4                                     # the learning rate of the timed run
         glob = [[torch.cat([t for t in col]) for col in zip(*[host_batch(workload, batch, 1000 * s + r) for r in range(world)])]
                 for s in range(k)]
         # data parallel
@@ -506,8 +506,12 @@ def gpu_arm(args, rank, world, local_rank):
         torch.cuda.synchronize()
         loss_err = max(abs(a - b) / abs(b) for a, b in zip(losses, ref_losses))
         pd = ((dp_flat - ref._flat).norm() / ref._flat.norm()).item()
+        # the UPDATE the k steps made, not the parameters (Adam at lr 1e-4 moves a weight by 3e-4 in three steps: any two
+        # runs agree on the parameters).  Adam's first steps are sign-like, so a gradient entry within bf16 noise of zero
+        # flips its whole step when the summation order changes (N shards vs one batch): measured 0.03-0.12; a rank's
+        # gradient missing from the exchange, or local instead of global BatchNorm statistics, gives >= 0.5
         ud = ((dp_flat - ref._flat).norm() / (ref._flat - p0).norm()).item()
-        rmd = (dp_rm - ref._rm).abs().max().item()
+        rmd = ((dp_rm - ref._rm).abs().max() / ref._rm.abs().max()).item()
         other = dp_flat.clone()
         dist.broadcast(other, src=0)
         same = torch.tensor([1.0 if torch.equal(other, dp_flat) else 0.0], device=dev)
@@ -515,11 +519,12 @@ def gpu_arm(args, rank, world, local_rank):
         vals = torch.tensor([loss_err, pd, ud, rmd], device=dev, dtype=torch.float64)
         dist.all_reduce(vals, op=dist.ReduceOp.MAX)
         loss_err, pd, ud, rmd = [float(v) for v in vals]
-        ok = loss_err < 2e-3 and pd < 2e-3 and rmd < 1e-3 and bool(same.item())
+        tol = {"loss_rel_err": 1e-3, "param_rel_diff": 1e-3, "update_rel_diff": 0.2, "running_mean_rel_diff": 5e-3}
+        ok = loss_err < tol["loss_rel_err"] and pd < tol["param_rel_diff"] and ud < tol["update_rel_diff"] and \
+            rmd < tol["running_mean_rel_diff"] and bool(same.item())
         return {"world": world, "steps": k, "batch_per_gpu": batch, "lr": lr, "loss_rel_err": loss_err, "param_rel_diff": pd,
-                "update_rel_diff": ud, "running_mean_max_diff": rmd, "replicas_identical": bool(same.item()),
-                "tolerance": {"loss_rel_err": 2e-3, "param_rel_diff": 2e-3, "running_mean_max_diff": 1e-3}, "ok": ok,
-                "losses_dp": losses, "losses_single_process": ref_losses}
+                "update_rel_diff": ud, "running_mean_rel_diff": rmd, "replicas_identical": bool(same.item()),
+                "tolerance": tol, "ok": ok, "losses_dp": losses, "losses_single_process": ref_losses}
 
     line = measure(args.workload, args.steps, args.warmup, True)
     if args.workload == "train" and world == 1 and not profiling:
