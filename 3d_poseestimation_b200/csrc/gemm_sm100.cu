@@ -28,6 +28,8 @@
 // or MN-major (wgrad contracts over the batch, so both of its operands are MN-major).
 #include "gemm_sm100.cuh"
 
+#include "bn_device.cuh"
+
 #include <stdlib.h>
 #include <string.h>
 
@@ -86,6 +88,19 @@ struct alignas(64) GemmParams {
     float* stat_sq;
     unsigned long long* timeline;      // debug hook: [gridDim.x][32] globaltimer stamps (nullptr in production)
     int stages;                        // ring depth in use (<= Cfg::STAGES; lowered only by the debug hook)
+    // whole-layer mode (FUSED instantiation only; see FusedBnArgs in gemm_sm100.cuh)
+    CUtensorMap tmOut;                 // the activation a [M][N], 64 x 32 boxes like tmD (tmR: the block residual)
+    BnFwdFinalize fbn;
+    double* fb_sums_out;
+    uint8_t* fb_bits;
+    unsigned* fb_barrier;
+    int fb_stat_rows, fb_has_resid, fb_dropout;
+    uint32_t fb_threshold;             // one-bit lanes: 0 keep all, 1 keep where the bit is set, 2 keep none
+    float fb_inv_keep;
+    PhiloxKeys fb_keys;
+    uint32_t fb_site, fb_step, fb_step_mul, fb_step_add;
+    const unsigned* fb_step_dev;
+    long long fb_row_offset;
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -153,7 +168,31 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return fmaf(-ax, p * t * e, fmaxf(x, 0.0f));                     // relu(x) - |x| Phi(-|x|)
 }
 
-template <int BLOCK_N, bool TWO_SM, bool GELU>
+// arrive-and-wait of the epilogue warps of EVERY CTA of the grid (one thread per CTA talks to the counter; the grid is at
+// most one CTA per SM, so all CTAs are resident).  `counter` starts at zero; a lost CTA traps after ~4 s instead of hanging.
+template <int EPI_THREADS>
+__device__ __forceinline__ void epilogue_grid_barrier(unsigned* counter, unsigned nblocks) {
+    __threadfence();
+    named_bar_sync(1, EPI_THREADS);
+    if (threadIdx.x == 128) {
+        unsigned seen;
+        asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(seen) : "l"(counter) : "memory");
+        long long t0 = 0;
+        unsigned spins = 0;
+        while (true) {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
+            if (seen >= nblocks) break;
+            if ((++spins & 0x3FF) == 0) {
+                const long long now = clock64();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > 8000000000LL) __trap();
+            }
+        }
+    }
+    named_bar_sync(1, EPI_THREADS);
+}
+
+template <int BLOCK_N, bool TWO_SM, bool GELU, bool FUSED = false>
 __global__ void LIFTER_GEMM_REGS
 lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
     using C = Cfg<BLOCK_N, TWO_SM>;
@@ -179,7 +218,8 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
         tma_prefetch_desc(&p.tmA);
         tma_prefetch_desc(&p.tmB);
         if (p.out_mode != OUT_32_DIRECT) tma_prefetch_desc(&p.tmD);
-        if (p.has_residual) tma_prefetch_desc(&p.tmR);
+        if (p.has_residual || (FUSED && p.fb_has_resid)) tma_prefetch_desc(&p.tmR);
+        if (FUSED) tma_prefetch_desc(&p.tmOut);
     } else if (warp == 1 && lane == 0) {
         for (int i = 0; i < p.stages; ++i) {
             mbar_init(bar_full + i * 8, 1);            // the (leader's) producer arms it; TMA bytes complete it
@@ -371,14 +411,14 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                 float (&x)[32] = v[c & 1];
                 if (c + 1 < C::NCH) {
                     tmem_ld_32x32(taddr + (c + 1) * 32, v[(c + 1) & 1]);      // in flight while chunk c is processed
-                } else {                                                    // accumulator fully read: hand TMEM back
+                } else if (!FUSED) {                                        // accumulator fully read: hand TMEM back
                     tcgen05_fence_before();
                     __syncwarp();
                     if (lane == 0) {
                         if (!TWO_SM || crank == 0) mbar_arrive(bar_tempty + as * 8);
                         else mbar_arrive_remote(bar_tempty + as * 8, 0);
                     }
-                }
+                }                                                           // (FUSED: the tile stays in TMEM for pass 2)
                 const int n0 = ncol0 + c * 32;
                 if (p.has_affine) {
 #pragma unroll
@@ -485,6 +525,177 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
             }
             if (threadIdx.x == 128 && it < 8) TL_STAMP(6 + 3 * it);
         }
+        if constexpr (FUSED) {
+            constexpr int EPI_THREADS = 32 * C::EPI_WARPS;
+            // ================= column finalize, shared out over the grid =================
+            if (lane == 0) tma_store_wait_read<0>();               // pass 1's z stores have read the staging buffers
+            if (threadIdx.x == 128) TL_STAMP(27);                  // pass 1 done in this CTA
+            epilogue_grid_barrier<EPI_THREADS>(p.fb_barrier, gridDim.x);       // every partial row of the layer is written
+            if (threadIdx.x == 128) TL_STAMP(28);
+            {
+                double (*sh)[32][8] = reinterpret_cast<double (*)[32][8]>(smem + C::OFF_STG);   // [2][32][8], 4 KB
+                const int tid = static_cast<int>(threadIdx.x) - 128;
+                const int cc = tid & 7, lane_r = tid >> 3;         // 8 columns x 32 row lanes
+                const BnFwdFinalize& f = p.fbn;
+                for (int cb = blockIdx.x; cb * 8 < p.N; cb += gridDim.x) {
+                    const int col = cb * 8 + cc;
+                    BnColumnInputs ci = {0.0f, 1.0f, 0.0f, 0.0f, 1.0f};
+                    if (lane_r == 0 && col < p.N) ci = bn_column_inputs(f, col);
+                    double sa = 0.0, sb = 0.0;
+                    if (col < p.N) {
+                        for (int r = lane_r; r < p.fb_stat_rows; r += 32) {
+                            sa += static_cast<double>(ldg_f32(p.stat_sum + static_cast<long>(r) * p.N + col));
+                            sb += static_cast<double>(ldg_f32(p.stat_sq + static_cast<long>(r) * p.N + col));
+                        }
+                    }
+                    sh[0][lane_r][cc] = sa;
+                    sh[1][lane_r][cc] = sb;
+                    named_bar_sync(1, EPI_THREADS);
+#pragma unroll
+                    for (int st = 16; st >= 1; st >>= 1) {         // fixed pairing: deterministic
+                        if (lane_r < st) {
+                            sh[0][lane_r][cc] += sh[0][lane_r + st][cc];
+                            sh[1][lane_r][cc] += sh[1][lane_r + st][cc];
+                        }
+                        named_bar_sync(1, EPI_THREADS);
+                    }
+                    double ta = sh[0][0][cc], tb = sh[1][0][cc];
+                    named_bar_sync(1, EPI_THREADS);                // sh is reused by the next column group
+                    if (f.ex.world > 1 && lane_r == 0) exchange_column_sums(f.ex, p.N, col, col < p.N, ta, tb);
+                    if (lane_r == 0 && col < p.N) {
+                        p.fb_sums_out[col] = ta;
+                        p.fb_sums_out[p.N + col] = tb;
+                        if (col == 0 && f.num_batches_tracked != nullptr) *f.num_batches_tracked += 1;
+                        bn_finalize_fwd_col(f, col, ta, tb, ci);
+                    }
+                }
+            }
+            if (threadIdx.x == 128) TL_STAMP(29);                  // this CTA's share of the column finalize done
+            epilogue_grid_barrier<EPI_THREADS>(p.fb_barrier + 1, gridDim.x);   // scale / shift of every column exist
+            if (threadIdx.x == 128) TL_STAMP(30);
+
+            // ================= pass 2: BatchNorm + ReLU + dropout (+ residual) straight from TMEM =================
+            const uint32_t dstep = (p.fb_step_dev != nullptr ? *p.fb_step_dev : p.fb_step) * p.fb_step_mul + p.fb_step_add;
+            const int bits_ld = p.N >> 3;
+            it = 0;
+            for (int tile = first_tile; tile < p.num_tiles; tile += tile_step, ++it) {
+                const int m_grp = tile / tiles_per_m;
+                const int m_blk = m_grp * CL + crank;
+                const int n_blk = tile - m_grp * tiles_per_m;      // splits == 1
+                const uint32_t as = it & 1;
+                named_bar_sync(1, EPI_THREADS);                    // everyone is done with the previous tile's coefficients
+                for (int i = ew * 32 + lane; i < BLOCK_N; i += EPI_THREADS) {
+                    const int n = n_blk * BLOCK_N + i;             // 1 / (1 - p) folded in (positive: ReLU unchanged)
+                    s_scale[i] = n < p.N ? __ldcg(p.fbn.scale + n) * p.fb_inv_keep : 0.0f;
+                    s_shift[i] = n < p.N ? __ldcg(p.fbn.shift + n) * p.fb_inv_keep : 0.0f;
+                }
+                named_bar_sync(1, EPI_THREADS);
+                const int row0 = m_blk * BLOCK_M + q * 32;
+                const bool tile_ok = m_blk < p.num_m_blocks;
+                const int rows_valid = min(max(p.M - row0, 0), 32);
+                const int ncol0 = n_blk * BLOCK_N + col_base;
+                if (p.fb_has_resid) {                              // block input tiles ahead of the arithmetic
+                    if (lane == 0) {
+                        tma_store_wait_read<0>();
+#pragma unroll
+                        for (int j = 0; j < C::NCH / 2; ++j) {
+                            const uint32_t b = (buf + j) & 1u;
+                            mbar_arrive_expect_tx(rbar + b * 8, 4096);
+                            tma_load_2d(&p.tmR, stg_addr + b * 4096, rbar + b * 8, ncol0 + j * 64, row0);
+                        }
+                    }
+                    __syncwarp();
+                }
+                // dropout stream (philox.cuh, one-bit lanes): a call covers 16 rows x 8 columns; the warp's 32 rows are two
+                // row groups, a 32-column chunk four column groups.  Lane L computes the call of (row group L / 16, column
+                // group (L / 4) % 4) and keeps word L % 4 of its 128 bits; row r's byte for column group k is byte r % 4 of
+                // word (r / 4) % 4 of call (r / 16, k), i.e. it sits on lane (L & 16) | (k << 2) | ((L >> 2) & 3).
+                const uint32_t grow = static_cast<uint32_t>(row0 + static_cast<int>(lane) + p.fb_row_offset);
+                const uint32_t taddr = tmem_base + ((q * 32u) << 16) + as * BLOCK_N + col_base;
+                float v[2][32];
+                tmem_ld_32x32(taddr, v[0]);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < C::NCH; ++c) {
+                    float (&x)[32] = v[c & 1];
+                    if (c + 1 < C::NCH) tmem_ld_32x32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+                    const int n0 = ncol0 + c * 32;
+                    uint32_t keep = 0xFFFFFFFFu;
+                    if (p.fb_dropout) {
+                        if (p.fb_threshold == 1u) {
+                            const Philox4 r4 = philox4x32_10(grow >> 4, static_cast<uint32_t>(n0 >> 3) + ((lane >> 2) & 3u),
+                                                             p.fb_site, dstep, p.fb_keys);
+                            const uint32_t sel = lane & 3u;
+                            const uint32_t mine = sel == 0 ? r4.x : (sel == 1 ? r4.y : (sel == 2 ? r4.z : r4.w));
+                            keep = 0u;
+#pragma unroll
+                            for (uint32_t k = 0; k < 4; ++k) {
+                                const uint32_t word = __shfl_sync(0xffffffffu, mine, (lane & 16u) | (k << 2) | ((lane >> 2) & 3u));
+                                keep |= ((word >> ((lane & 3u) * 8u)) & 0xFFu) << (8u * k);
+                            }
+                        } else if (p.fb_threshold != 0u) {
+                            keep = 0u;
+                        }
+                    }
+                    uint32_t active = 0u;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2) {              // z as the 16-bit value pass 1 stored (backward reads that)
+                        const float2 zr = unpack16(pack16(x[j], x[j + 1], fmt), fmt);
+                        const float y0 = fmaf(zr.x, s_scale[col_base + c * 32 + j], s_shift[col_base + c * 32 + j]);
+                        const float y1 = fmaf(zr.y, s_scale[col_base + c * 32 + j + 1], s_shift[col_base + c * 32 + j + 1]);
+                        const bool on0 = ((keep >> j) & 1u) && (y0 > 0.0f), on1 = ((keep >> (j + 1)) & 1u) && (y1 > 0.0f);
+                        active |= (on0 ? 1u : 0u) << j;
+                        active |= (on1 ? 1u : 0u) << (j + 1);
+                        x[j] = on0 ? y0 : 0.0f;
+                        x[j + 1] = on1 ? y1 : 0.0f;
+                    }
+                    if (tile_ok && static_cast<int>(lane) < rows_valid && n0 < p.N)
+                        *reinterpret_cast<uint32_t*>(p.fb_bits + static_cast<long>(row0 + lane) * bits_ld + (n0 >> 3)) = active;
+                    const uint32_t half = c & 1;
+                    const uint32_t dst = stg_addr + buf * 4096 + lane * 128;
+                    if (half == 0) {
+                        if (p.fb_has_resid) {
+                            mbar_wait(rbar + buf * 8, (rph >> buf) & 1u);
+                            rph ^= 1u << buf;
+                        } else {
+                            if (lane == 0) tma_store_wait_read<1>();
+                            __syncwarp();
+                        }
+                    }
+                    if (p.fb_has_resid) {
+#pragma unroll
+                        for (int qq = 0; qq < 4; ++qq) {
+                            const uint4 r = lds128(dst + (((half * 4 + qq) ^ (lane & 7)) * 16));
+                            const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float2 f2 = unpack16(w[e], fmt);
+                                x[qq * 8 + e * 2] += f2.x;
+                                x[qq * 8 + e * 2 + 1] += f2.y;
+                            }
+                        }
+                    }
+                    uint32_t pk[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) pk[j] = pack16(x[2 * j], x[2 * j + 1], fmt);
+#pragma unroll
+                    for (int qq = 0; qq < 4; ++qq)
+                        sts128(dst + (((half * 4 + qq) ^ (lane & 7)) * 16), pk[4 * qq], pk[4 * qq + 1], pk[4 * qq + 2],
+                               pk[4 * qq + 3]);
+                    if (half == 1) {
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0 && tile_ok) {
+                            tma_store_2d(&p.tmOut, stg_addr + buf * 4096, ncol0 + (c >> 1) * 64, row0);
+                            tma_store_commit();
+                        }
+                        buf ^= 1;
+                    }
+                    if (c + 1 < C::NCH) tmem_ld_wait();
+                }
+            }
+            if (threadIdx.x == 128) TL_STAMP(31);                  // pass 2 issued (its bulk stores may still be reading smem)
+        }
         // smem must outlive the READS of the last bulk stores; their global writes complete with the grid (what the
         // next kernel's griddepcontrol.wait / stream order waits for), so the CTA need not sit through them
         if (lane == 0) tma_store_wait_read<0>();
@@ -544,14 +755,14 @@ int encode_2d(CUtensorMap* map, CUtensorMapDataType dt, int elem_bytes, const vo
     return LIFTER_OK;
 }
 
-template <int BLOCK_N, bool TWO_SM, bool GELU = false>
+template <int BLOCK_N, bool TWO_SM, bool GELU = false, bool FUSED = false>
 int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     using C = Cfg<BLOCK_N, TWO_SM>;
     constexpr int CL = TWO_SM ? 2 : 1;
     static PerDeviceOnce once;
     bool& configured = *once.slot();
     if (!configured) {
-        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(lifter_gemm_kernel<BLOCK_N, TWO_SM, GELU>,
+        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(lifter_gemm_kernel<BLOCK_N, TWO_SM, GELU, FUSED>,
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
         configured = true;
     }
@@ -565,6 +776,11 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     if (a.out_mode == OUT_16_TMA) {
         LIFTER_PROPAGATE(encode_2d(&p.tmD, dt16, 2, a.D, a.M, a.N, a.ldd, 64, 32));
         if (a.residual != nullptr) LIFTER_PROPAGATE(encode_2d(&p.tmR, dt16, 2, a.residual, a.M, a.N, a.ldr, 64, 32));
+        if (FUSED) {
+            const FusedBnArgs& fb = *a.fused_bn;
+            LIFTER_PROPAGATE(encode_2d(&p.tmOut, dt16, 2, fb.a_out, a.M, a.N, a.N, 64, 32));
+            if (fb.resid != nullptr) LIFTER_PROPAGATE(encode_2d(&p.tmR, dt16, 2, fb.resid, a.M, a.N, fb.ldr, 64, 32));
+        }
     } else if (a.out_mode == OUT_32_TMA) {
         // rows of the last slab are clipped to M, so a single-slab output may be exactly [M][ldd]
         LIFTER_PROPAGATE(encode_2d(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, a.D,
@@ -588,7 +804,9 @@ int launch_impl(GemmParams& p, const GemmArgs& a, cudaStream_t stream) {
     const int clusters = p.num_tiles < max_clusters ? p.num_tiles : max_clusters;
     cfg.gridDim = dim3(clusters * CL);
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
-    LIFTER_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lifter_gemm_kernel<BLOCK_N, TWO_SM, GELU>, p));
+    if (FUSED)      // every tile must stay in TMEM across the grid barriers: at most two per pair, all pairs resident
+        LIFTER_REQUIRE(p.num_tiles <= 2 * clusters && a.max_ctas == 0, "gemm: %d tiles do not fit the fused layer mode", p.num_tiles);
+    LIFTER_CHECK_CUDA(cudaLaunchKernelEx(&cfg, lifter_gemm_kernel<BLOCK_N, TWO_SM, GELU, FUSED>, p));
     if (a.tag != nullptr) trace_mark(a.tag, stream); else trace_mark("gemm", stream);
     return LIFTER_OK;
 }
@@ -604,6 +822,18 @@ int gemm_effective_splits(int K, int splits) {
     return ceil_div(kb, per);
 }
 int gemm_stat_rows(int M) { return ceil_div(M, BLOCK_M) * 4; }
+
+// whole-layer mode: CTA pairs, 256-wide column blocks, at most two tiles per pair, one-bit dropout lanes on 16-row groups
+bool gemm_fused_bn_fits(int M, int N, float p, int apply_dropout, long long row_offset) {
+    if (M < 2 * BLOCK_M || N < 256 || N % 256 != 0) return false;
+    const int pairs = num_sms() / 2;
+    const long tiles = static_cast<long>(ceil_div(ceil_div(M, BLOCK_M), 2)) * (N / 256);
+    if (tiles > 2l * pairs) return false;
+    if (apply_dropout && p > 0.0f) {
+        if (dropout_lanes(p).bits != 1 || row_offset % 16 != 0) return false;
+    }
+    return true;
+}
 
 int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     LIFTER_REQUIRE(a.M > 0 && a.N > 0 && a.K > 0, "gemm: empty problem (M=%d N=%d K=%d)", a.M, a.N, a.K);
@@ -637,6 +867,26 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     p.stat_sum = a.stat_sum; p.stat_sq = a.stat_sq;
     p.timeline = a.timeline;
 
+    if (a.fused_bn != nullptr) {
+        const FusedBnArgs& fb = *a.fused_bn;
+        LIFTER_REQUIRE(a.out_mode == OUT_16_TMA && a.stat_sum != nullptr && a.splits == 1 && a.residual == nullptr &&
+                       a.scale == nullptr && a.shift == nullptr && a.relu == 0 && a.cluster != 1,
+                       "gemm: the fused layer mode takes the plain z = A W^T launch with column statistics");
+        LIFTER_REQUIRE(gemm_fused_bn_fits(a.M, a.N, fb.p, fb.apply_dropout, fb.row_offset), "gemm: shape does not fit the fused layer mode");
+        LIFTER_REQUIRE(fb.a_out && fb.bits && fb.barrier && fb.sums_out && fb.f.scale && fb.f.shift && fb.f.mean_z && fb.f.rstd,
+                       "gemm: fused layer mode: null pointer");
+        LIFTER_REQUIRE(fb.f.use_bn && fb.f.bn_mode == 0 && fb.f.H == a.N, "gemm: the fused layer mode is batch-statistics BatchNorm");
+        p.fbn = fb.f; p.fb_sums_out = fb.sums_out; p.fb_bits = fb.bits; p.fb_barrier = fb.barrier;
+        p.fb_stat_rows = gemm_stat_rows(a.M); p.fb_has_resid = fb.resid != nullptr ? 1 : 0;
+        const bool drop = fb.apply_dropout && fb.p > 0.0f;
+        p.fb_dropout = drop ? 1 : 0;
+        p.fb_threshold = drop ? dropout_lanes(fb.p).threshold : 0u;
+        p.fb_inv_keep = drop ? (fb.p < 1.0f ? 1.0f / (1.0f - fb.p) : 0.0f) : 1.0f;
+        p.fb_keys = philox_round_keys(fb.seed);
+        p.fb_site = fb.site; p.fb_step = fb.step; p.fb_step_mul = fb.step_mul; p.fb_step_add = fb.step_add;
+        p.fb_step_dev = fb.step_dev; p.fb_row_offset = fb.row_offset;
+        return launch_impl<256, true, false, true>(p, a, stream);
+    }
     // CTA pairs (cta_group::2, 256-row tiles) whenever there are two M-blocks to pair up.
     // a.cluster: 0 = auto, 1 = single-CTA tiles, 2 = pairs (when the shape allows).
     const bool pair = a.cluster != 1 && p.num_m_blocks >= 2 && a.N > 64;

@@ -1,6 +1,8 @@
 // Host-side descriptor of one tcgen05 GEMM launch (see gemm_sm100.cu).
 #pragma once
 #include "common.cuh"
+#include "philox.cuh"
+#include "train_kernels.cuh"
 
 namespace lifter {
 
@@ -9,6 +11,26 @@ enum : int {
     OUT_32_TMA = 1,     // fp32 output (split-K partial slabs) through smem staging + TMA store
     OUT_32_DIRECT = 2,  // fp32 output with row stride n_valid (<= 64 columns, rows contiguous)
 };
+
+// A whole hidden layer of the training forward in ONE launch (GemmArgs::fused_bn): z = A W^T as usual (16-bit z stored,
+// column partial sums written by the epilogue), but the fp32 accumulators STAY in TMEM while the grid meets at a barrier,
+// shares out the column finalize (fp64 sums over the partial rows, SyncBN exchange, scale / shift, running statistics),
+// meets again, and then every CTA applies BatchNorm + ReLU + Philox dropout (+ block residual) to its own tiles straight
+// from TMEM and stores the activation and the "active" bits.  Replaces GEMM + bn_reduce_finalize_fwd + bn_apply_fwd
+// (three launches, z written and read back).  Needs: CTA pairs with at most TWO 256 x 256 tiles per pair (the 512 TMEM
+// columns hold both; 8,192 x 1,024 on 74 pairs = 128 tiles fits), N % 256 == 0, one-bit dropout lanes (p = 0.5) or no
+// dropout, row_offset % 16 == 0.  gemm_fused_bn_fits() tells; the caller falls back to the three launches otherwise.
+struct FusedBnArgs {
+    BnFwdFinalize f;                  // `sums` unused (the kernel reduces the epilogue's partial rows itself); ex = SyncBN
+    double* sums_out = nullptr;       // [2][N] global column sums (kept for tests / the NCCL path)
+    void* a_out = nullptr;            // 16-bit [M][N] activation
+    const void* resid = nullptr; long ldr = 0;   // 16-bit block input added after dropout (nullable)
+    uint8_t* bits = nullptr;          // [M][N/8]: ReLU-active AND kept
+    int apply_dropout = 0; float p = 0.0f; unsigned long long seed = 0;
+    unsigned step = 0, site = 0, step_mul = 1, step_add = 0; const unsigned* step_dev = nullptr; long long row_offset = 0;
+    unsigned* barrier = nullptr;      // two words, zero when the kernel starts
+};
+bool gemm_fused_bn_fits(int M, int N, float p, int apply_dropout, long long row_offset);
 
 // D[M][N] = sum_k A(m,k) * B(n,k), 16-bit operands, fp32 accumulation in TMEM.
 //   A "K-major":  global A  is [M rows][K cols]   (row-major, K contiguous)
@@ -35,6 +57,7 @@ struct GemmArgs {
     const char* tag = nullptr;                // name in the debug trace
     int max_stages = 0;                       // debug hook: cap the operand ring depth (0 = all that fit)
     int max_ctas = 0;                         // cap the persistent grid (0 = every SM), for kernels meant to run side by side
+    const FusedBnArgs* fused_bn = nullptr;    // whole-layer mode (see FusedBnArgs); needs OUT_16_TMA + stat_sum / stat_sq
 };
 
 int gemm_slab_rows(int M);                    // rows of one split-K slab (M rounded up to 128)

@@ -244,6 +244,36 @@ int64_t lifter_train_bwd_sums_offset(const lifter_config_t* cfg, int64_t batch, 
 
 // ---------------------------------------------------------------------------------------------- forward
 // fused = single-GPU path: the column-sum reduction is merged into the finalize kernel (no all-reduce between)
+// LIFTER_FUSE_LAYER=1: the single-call forward runs every hidden layer that fits as ONE launch of the whole-layer kernel
+// (GEMM + column statistics + grid barriers + BatchNorm / ReLU / dropout / residual from TMEM; gemm_sm100.cuh).  OFF by
+// default: measured on B200 (profiles/r02_layer_timeline_*.txt) the second epilogue pass cannot overlap any MMA and costs
+// 5-10 us per layer, so the layer's period (34-40 us) only ties the three launches it replaces (37 us) and the training
+// step is 0.516 ms against 0.484 ms.  Read on every call (a getenv), so tests switch it inside one process.
+static bool fuse_layer_enabled() {
+    const char* e = getenv("LIFTER_FUSE_LAYER");
+    return e != nullptr && e[0] == '1';
+}
+// single-call forward, batch-statistics BatchNorm, shape fits: the whole layer is ONE launch
+static bool fwd_whole_layer(const lifter_config_t* cfg, const lifter_train_ctx_t* t, const Layout& lay, int l, bool fused) {
+    if (!(fused && cfg->use_bn && t->bn_mode == 0 && fuse_layer_enabled() && 2 * l + 1 < GRID_BARRIER_WORDS)) return false;
+    const int drop = t->apply_dropout && cfg->p_dropout > 0.0f;
+    return gemm_fused_bn_fits(static_cast<int>(t->batch), lay.H, cfg->p_dropout, drop, t->row_offset);
+}
+
+static void fill_finalize(const lifter_config_t* cfg, const lifter_train_ctx_t* t, const Layout& lay, const SavedWs& w, int l,
+                          BnFwdFinalize* f) {
+    const int H = lay.H;
+    f->sums = w.sums[l]; f->count = static_cast<double>(t->global_batch);
+    f->bias = t->params + lay.p_off[lay.t_bias(l)];
+    f->gamma = t->params + lay.p_off[lay.t_gamma(l)];
+    f->beta = t->params + lay.p_off[lay.t_beta(l)];
+    f->running_mean = t->running_mean ? t->running_mean + static_cast<int64_t>(l) * H : nullptr;
+    f->running_var = t->running_var ? t->running_var + static_cast<int64_t>(l) * H : nullptr;
+    f->num_batches_tracked = t->num_batches_tracked ? reinterpret_cast<long long*>(t->num_batches_tracked) + l : nullptr;
+    f->momentum = cfg->bn_momentum; f->eps = cfg->bn_eps; f->H = H; f->use_bn = cfg->use_bn; f->bn_mode = t->bn_mode;
+    f->mean_z = w.mean_z[l]; f->rstd = w.rstd[l]; f->scale = w.scale[l]; f->shift = w.shift[l];
+}
+
 static int fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_ctx_t* t, int l, void* stream, bool fused) {
     Layout lay;
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, false));
@@ -261,6 +291,26 @@ static int fwd_layer_gemm(const lifter_config_t* cfg, const lifter_train_ctx_t* 
     g.M = B; g.N = H; g.K = lay.in_pad(l); g.fmt = t->fmt; g.out_mode = OUT_16_TMA; g.D = w.z[l]; g.ldd = H;
     if (stats) { g.stat_sum = w.psum; g.stat_sq = w.psq; }
     g.tag = "gemm_fwd";
+    FusedBnArgs fb;
+    if (fwd_whole_layer(cfg, t, lay, l, fused)) {              // GEMM + statistics + BN / ReLU / dropout / residual
+        fill_finalize(cfg, t, lay, w, l, &fb.f);
+        LIFTER_PROPAGATE(fill_exchange(lay, t, l, &fb.f.ex));
+        fb.sums_out = w.sums[l]; fb.a_out = w.a[l]; fb.bits = w.bits[l];
+        fb.resid = (l >= 2 && l % 2 == 0) ? w.a[l - 2] : nullptr; fb.ldr = H;
+        fb.apply_dropout = t->apply_dropout && cfg->p_dropout > 0.0f; fb.p = cfg->p_dropout; fb.seed = t->seed;
+        fb.step = t->step; fb.site = static_cast<unsigned>(l);
+        fb.step_mul = t->calls_per_step > 0 ? static_cast<unsigned>(t->calls_per_step) : 1u;
+        fb.step_add = static_cast<unsigned>(t->call_index);
+        fb.step_dev = t->step_state != nullptr ? reinterpret_cast<const unsigned*>(t->step_state) : nullptr;
+        fb.row_offset = t->row_offset;
+        fb.barrier = w.bars + 2 * l;
+        g.fused_bn = &fb;
+        g.tag = "layer_fwd";
+    }
+    // debug: LIFTER_DEBUG_TIMELINE_PTR=<device address of uint64 [layers][SMs][32]> makes the forward GEMMs stamp their
+    // phases with %globaltimer (scripts/layer_timeline.py); never set in production
+    if (const char* e = getenv("LIFTER_DEBUG_TIMELINE_PTR"))
+        g.timeline = reinterpret_cast<unsigned long long*>(strtoull(e, nullptr, 0)) + static_cast<size_t>(l) * num_sms() * 32;
     LIFTER_PROPAGATE(gemm_launch(g, st));
     if (stats && !fused)
         LIFTER_PROPAGATE(reduce_rows_f64(w.psum, w.psq, gemm_stat_rows(B), H, H, w.sums[l], w.sums[l] + H, st));
@@ -272,6 +322,7 @@ static int fwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t
     LIFTER_PROPAGATE(check_ctx(cfg, t, &lay, false));
     LIFTER_REQUIRE(l >= 0 && l < lay.L, "forward: layer %d out of range", l);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (fwd_whole_layer(cfg, t, lay, l, fused)) return LIFTER_OK;          // done inside the layer kernel
     SavedWs w;
     carve_saved(lay, t->batch, t->saved, &w);
     const int H = lay.H;
