@@ -38,7 +38,8 @@ class GemmDesc(C.Structure):
 class DpInfo(C.Structure):
     """``lifter_dp_t``: peer pointers of the symmetric SyncBN exchange buffer."""
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("sync", C.c_void_p * 8), ("grad", C.c_void_p * 8),
-                ("params", C.c_void_p * 8), ("operands", C.c_void_p * 8), ("flags", C.c_void_p * 8)]
+                ("params", C.c_void_p * 8), ("operands", C.c_void_p * 8), ("flags", C.c_void_p * 8),
+                ("mc_grad", C.c_void_p), ("mc_params", C.c_void_p), ("mc_operands", C.c_void_p)]
 
 
 class TrainCtx(C.Structure):

@@ -897,6 +897,12 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     }
     if (a.N <= 64) return launch_impl<64, false>(p, a, stream);
     if (a.N <= 128) return pair ? launch_impl<128, true>(p, a, stream) : launch_impl<128, false>(p, a, stream);
+    // 256-wide column blocks halve the B-operand fill per FLOP, but the LAST tile's epilogue is exposed (4-5 us of a
+    // 17.7 us launch at M = 8,192).  With few tiles per CTA pair, 128-wide blocks quantise into waves the same way
+    // (1.73 -> 2 waves of 256 = 3.46 -> 4 waves of 128) and leave half the tail.  LIFTER_GEMM_NARROW: 0 never, 1 always
+    // (pairs), default = when a pair gets at most `narrow_below` 256-wide tiles.
+    static const int narrow = [] { const char* e = getenv("LIFTER_GEMM_NARROW"); return e != nullptr ? atoi(e) : -1; }();
+    if (pair && a.out_mode == OUT_16_TMA && narrow == 1) return launch_impl<128, true>(p, a, stream);
     return pair ? launch_impl<256, true>(p, a, stream) : launch_impl<256, false>(p, a, stream);
 }
 

@@ -111,6 +111,14 @@ bool fuse_bn_launches(bool forward) {
     return forward ? fwd : bwd;
 }
 
+// NVSwitch multicast in the data-parallel optimiser (multimem.ld_reduce / multimem.st) when the caller provides the
+// multicast mappings.  Default: for more than two ranks -- with ONE peer it saves no traffic and adds a switch hop
+// (measured on 2 B200: 0.563 vs 0.537 ms per step).  LIFTER_DP_MULTICAST=0 / 1 forces it off / on.
+bool dp_multicast_enabled(int world) {
+    static const int forced = [] { const char* e = getenv("LIFTER_DP_MULTICAST"); return e != nullptr ? (e[0] == '0' ? 0 : 1) : -1; }();
+    return forced >= 0 ? forced == 1 : world > 2;
+}
+
 int wgrad_splits(int M, int N, int K) {
     const int bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);
     const int tiles = ceil_div(M, 128) * ceil_div(N, bn);
@@ -653,6 +661,9 @@ static int optim_range(const Layout& lay, const lifter_train_ctx_t* t, const lif
     }
     d.epoch = reinterpret_cast<const unsigned*>(t->step_state) + 1;
     d.phase = phase; d.last = last ? 1 : 0;
+    if (g->mc_grad && g->mc_params && g->mc_operands && dp_multicast_enabled(g->world)) {
+        d.mc_g = static_cast<const float*>(g->mc_grad); d.mc_p = static_cast<float*>(g->mc_params); d.mc_op = g->mc_operands;
+    }
     return adam_step_dp(d, st);
 }
 
@@ -852,6 +863,9 @@ int lifter_dp_adam_step(const lifter_config_t* cfg, const lifter_dp_t* dp, float
         a.w_pad[l] = l < lay.L ? lay.in_pad(l) : lay.H;
     }
     d.epoch = reinterpret_cast<const unsigned*>(state) + 1;
+    if (dp->mc_grad && dp->mc_params && dp->mc_operands && dp_multicast_enabled(dp->world)) {
+        d.mc_g = static_cast<const float*>(dp->mc_grad); d.mc_p = static_cast<float*>(dp->mc_params); d.mc_op = dp->mc_operands;
+    }
     return adam_step_dp(d, static_cast<cudaStream_t>(stream));
 }
 

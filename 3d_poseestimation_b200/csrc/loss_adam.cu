@@ -238,6 +238,24 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
     return r;
 }
 
+// NVSwitch multicast (multimem.*, sm_90+): one load that returns the SUM of the addressed float4 over every rank's copy
+// (reduced inside the switch), one store that lands in every rank's copy.  Weak operations: the flag handshakes around
+// the kernel order them against the peers' kernels.
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+    return r;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ void multimem_st_b64(void* mc, uint32_t a, uint32_t b) {     // two 32-bit words of packed 16-bit data
+    asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc), "f"(__uint_as_float(a)), "f"(__uint_as_float(b))
+                 : "memory");
+}
+
 constexpr int DP_UNROLL = 2;
 __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_size, float inv_sqrt_bc2, float decay) {
     griddep_launch();
@@ -247,7 +265,8 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
     const unsigned epoch = *d.epoch * static_cast<unsigned>(ADAM_DP_PHASES) + static_cast<unsigned>(d.phase);
     unsigned* my_flags = d.flag_peer[d.rank];
     // ---- barrier 1: every rank's gradient is complete (my predecessor kernels finished: this kernel runs)
-    if (threadIdx.x < d.world) {
+    // (d.external_flags: a one-block dp_flag_kernel in front of this launch did the handshake -- no block of this grid spins)
+    if (!d.external_flags && threadIdx.x < d.world) {
         if (blockIdx.x == 0) st_release_sys_u32(d.flag_peer[threadIdx.x] + d.rank, epoch);
         wait_epoch(my_flags + threadIdx.x, epoch, d.spin_limit);
     }
@@ -262,18 +281,24 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
 #pragma unroll
         for (int u = 0; u < DP_UNROLL; ++u) {
             const long i = i0 + u * stride;
+            if (d.mc_g != nullptr) {                                          // reduced in the switch: one load
+                if (i < hi) gs[u][0] = multimem_ld_reduce_f4(d.mc_g + i * 4);
+            } else {
 #pragma unroll
-            for (int q = 0; q < ADAM_DP_MAX_WORLD; ++q)
-                if (q < d.world && i < hi) gs[u][q] = ld_peer_f4(d.g_peer[q] + i * 4);
+                for (int q = 0; q < ADAM_DP_MAX_WORLD; ++q)
+                    if (q < d.world && i < hi) gs[u][q] = ld_peer_f4(d.g_peer[q] + i * 4);
+            }
         }
 #pragma unroll
         for (int u = 0; u < DP_UNROLL; ++u) {
             const long i = i0 + u * stride;
             if (i >= hi) break;
             float4 g4 = gs[u][0];
+            if (d.mc_g == nullptr) {
 #pragma unroll
-            for (int q = 1; q < ADAM_DP_MAX_WORLD; ++q)
-                if (q < d.world) { g4.x += gs[u][q].x; g4.y += gs[u][q].y; g4.z += gs[u][q].z; g4.w += gs[u][q].w; }
+                for (int q = 1; q < ADAM_DP_MAX_WORLD; ++q)
+                    if (q < d.world) { g4.x += gs[u][q].x; g4.y += gs[u][q].y; g4.z += gs[u][q].z; g4.w += gs[u][q].w; }
+            }
             float4 p = reinterpret_cast<float4*>(a.p)[i];
             float4 m = reinterpret_cast<float4*>(a.m)[i];
             float4 v = reinterpret_cast<float4*>(a.v)[i];
@@ -290,7 +315,8 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
             }
             reinterpret_cast<float4*>(a.m)[i] = m;
             reinterpret_cast<float4*>(a.v)[i] = v;
-            for (int q = 0; q < d.world; ++q) reinterpret_cast<float4*>(d.p_peer[q])[i] = p;
+            if (d.mc_p != nullptr) multimem_st_f4(d.mc_p + i * 4, p);
+            else for (int q = 0; q < d.world; ++q) reinterpret_cast<float4*>(d.p_peer[q])[i] = p;
             if (a.operands != nullptr) {
                 const long idx = i * 4;
                 for (int t = 0; t < a.nw; ++t) {
@@ -298,8 +324,11 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
                     if (e0 < 0 || e0 >= a.w_numel[t]) continue;
                     if (a.w_in[t] == a.w_pad[t]) {
                         const uint2 w2 = make_uint2(pack16(p.x, p.y, a.op_fmt), pack16(p.z, p.w, a.op_fmt));
-                        for (int q = 0; q < d.world; ++q)
-                            *reinterpret_cast<uint2*>(static_cast<uint16_t*>(d.op_peer[q]) + a.w_off[t] + e0) = w2;
+                        if (d.mc_op != nullptr)
+                            multimem_st_b64(static_cast<uint16_t*>(d.mc_op) + a.w_off[t] + e0, w2.x, w2.y);
+                        else
+                            for (int q = 0; q < d.world; ++q)
+                                *reinterpret_cast<uint2*>(static_cast<uint16_t*>(d.op_peer[q]) + a.w_off[t] + e0) = w2;
                     } else {
 #pragma unroll
                         for (int e = 0; e < 4; ++e) {
@@ -317,7 +346,7 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
         }
     }
     // ---- barrier 2: the last block of this rank tells every peer "my stores are done" and waits for theirs
-    if (!d.last) return;                 // an earlier range of the step: the closing launch orders all of them
+    if (!d.last || d.external_flags) return;   // an earlier range of the step / the closing handshake is its own launch
     __threadfence_system();
     __syncthreads();
     __shared__ unsigned last;
@@ -330,6 +359,22 @@ __global__ void __launch_bounds__(256) adam_dp_kernel(AdamDpArgs d, float step_s
             st_release_sys_u32(d.flag_peer[threadIdx.x] + d.world + d.rank, epoch);
             wait_epoch(my_flags + d.world + threadIdx.x, epoch, d.spin_limit);
         }
+    }
+}
+
+// One-block handshake of the data-parallel optimiser: rank r raises flag[slot + r] on every peer and waits until every
+// peer has raised its flag here.  Runs as its own launch in front of (slot 0: "every rank's gradient of this range is
+// complete") and behind (slot world: "every rank's parameter stores of this step have landed") the range kernels, so
+// that the stream order carries the dependency and no compute block ever spins on a system-scope flag beside the
+// backward GEMMs (with the handshake inside the range kernel, each of its ~590 blocks polled until the peer arrived).
+__global__ void dp_flag_kernel(AdamDpArgs d, int slot) {
+    griddep_launch();
+    griddep_wait();
+    const unsigned epoch = *d.epoch * static_cast<unsigned>(ADAM_DP_PHASES) + static_cast<unsigned>(d.phase);
+    if (threadIdx.x < d.world) {
+        __threadfence_system();
+        st_release_sys_u32(d.flag_peer[threadIdx.x] + slot + d.rank, epoch);
+        wait_epoch(d.flag_peer[d.rank] + slot + threadIdx.x, epoch, d.spin_limit);
     }
 }
 
@@ -410,10 +455,15 @@ int adam_step_dp(const AdamDpArgs& d_in, cudaStream_t st) {
     LIFTER_REQUIRE(a.dyn != nullptr && d.epoch != nullptr, "adam_dp: needs the device step state");
     const long slice4 = (a.n / 4 + d.world - 1) / d.world;
     long blocks = (slice4 + 256 * DP_UNROLL - 1) / (256 * DP_UNROLL);
-    const long cap = static_cast<long>(num_sms()) * 4;                      // all blocks co-resident (flag barriers)
+    // LIFTER_DP_INKERNEL_FLAGS=1: the round-1 form (handshakes inside the range kernel, all blocks co-resident)
+    static const bool inkernel = [] { const char* e = getenv("LIFTER_DP_INKERNEL_FLAGS"); return e != nullptr && e[0] == '1'; }();
+    d.external_flags = inkernel ? 0 : 1;
+    const long cap = static_cast<long>(num_sms()) * (inkernel ? 4 : 2);
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
+    if (!inkernel) LIFTER_CHECK_CUDA(launch_pdl("dp_flag_kernel", dp_flag_kernel, dim3(1), dim3(32), 0, st, d, 0));
     LIFTER_CHECK_CUDA(launch_pdl("adam_dp_kernel", adam_dp_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), 0, st, d, 0.0f, 1.0f, 1.0f));
+    if (!inkernel && d.last) LIFTER_CHECK_CUDA(launch_pdl("dp_flag_kernel", dp_flag_kernel, dim3(1), dim3(32), 0, st, d, d.world));
     return LIFTER_OK;
 }
 

@@ -58,6 +58,8 @@ struct AdamDpArgs {
     // step * ADAM_DP_PHASES + phase; only the `last` launch runs the closing "all stores have landed" barrier
     int phase = 0, last = 1;
     long long spin_limit = 0;                    // SM clocks a peer is waited for (0 = forever); set by adam_step_dp
+    const float* mc_g = nullptr; float* mc_p = nullptr; void* mc_op = nullptr;   // NVSwitch multicast views (nullable)
+    int external_flags = 0;                      // the flag handshakes run as their own one-block launches (set by adam_step_dp)
 };
 constexpr int ADAM_DP_PHASES = 64;
 int adam_step_dp(const AdamDpArgs& a, cudaStream_t st);

@@ -128,6 +128,9 @@ __global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, co
 // current one is computed; a warp instruction still touches 32 x 16 contiguous bytes of one row.
 constexpr int AP_ROWS = 16;
 constexpr int AP_SUB = 4;
+__device__ __forceinline__ uint4 and4(const uint4& a, const uint4& m) {
+    return make_uint4(a.x & m.x, a.y & m.y, a.z & m.z, a.w & m.w);
+}
 
 template <int FMT>
 __device__ __forceinline__ void apply_rows(const BnApplyFwd& a, long base, long end, const DropoutLanes& lanes, float inv_keep,
@@ -216,6 +219,110 @@ __global__ void __launch_bounds__(EW_THREADS, 2) bn_apply_fwd_kernel(BnApplyFwd 
     apply_rows<FMT>(a, base, end, lanes, inv_keep, keys, a.scale, a.shift);
 }
 
+// ---- warp-unit variant ---------------------------------------------------------------------------------------------
+// The block-per-32-rows kernel above launches 256 blocks of 256 threads for 8,192 x 1,024 (two resident per SM at 124
+// registers): 0.86 waves, so some SMs carry two blocks and some one, and an SM never holds more than 16 warps (ncu:
+// 21 % of the warp slots, 28 % issue utilisation, 20 instructions per element).  Here the unit of work is ONE WARP:
+// 16 consecutive rows (one Philox call per 8 columns) x 32 column groups = 256 columns; blocks of two warps, so the same
+// layer is 1,024 small blocks that the hardware spreads evenly (6.9 per SM, all resident at once).  The keep mask is
+// applied to the packed 16-bit words through a 256-entry table (one LDS + four ANDs per eight elements), ReLU is a max,
+// and only the "active" bit costs a compare per element.
+constexpr int APW_THREADS = 64;
+
+// APW_SUB rows of loads in flight together (x 2 buffers) at MINB resident blocks per SM: <4, 8> = 16 warps, deep prefetch,
+// 128 registers; <2, 12> = 24 warps, shallow prefetch, 80 registers
+template <int FMT, int APW_SUB, int MINB>
+__global__ void __launch_bounds__(APW_THREADS, MINB) bn_apply_fwd_warp_kernel(BnApplyFwd a, int chunks, int cpw,
+                                                                        DropoutLanes lanes, float inv_keep,
+                                                                        const PhiloxKeys keys) {
+    griddep_launch();
+    __shared__ uint4 lut[256];
+    for (int b = threadIdx.x; b < 256; b += APW_THREADS) {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            w[i] = (((b >> (2 * i)) & 1) ? 0x0000FFFFu : 0u) | (((b >> (2 * i + 1)) & 1) ? 0xFFFF0000u : 0u);
+        lut[b] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    __syncthreads();
+    griddep_wait();
+    const int lane = threadIdx.x & 31;
+    const long wu = static_cast<long>(blockIdx.x) * (APW_THREADS / 32) + (threadIdx.x >> 5);
+    const int rpw = 32 / cpw;                                     // 16-row groups a warp walks side by side (1 when H >= 256)
+    const long rg = wu / chunks;
+    const int cg = static_cast<int>(wu - rg * chunks) * cpw + lane % cpw;
+    const long g0 = (rg * rpw + lane / cpw) * AP_ROWS;
+    if (g0 >= a.rows) return;
+    const int tpr = a.H >> 3;
+    const long H = a.H;
+    const int n = static_cast<int>(min(static_cast<long>(AP_ROWS), a.rows - g0));
+    float sc[8], sh[8];
+    load8f(a.scale + cg * 8, sc);
+    load8f(a.shift + cg * 8, sh);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { sc[e] *= inv_keep; sh[e] *= inv_keep; }
+    const uint32_t dstep = (a.step_dev != nullptr ? *a.step_dev : a.step) * a.step_mul + a.step_add;
+    const bool has_resid = a.resid != nullptr, dropout = a.apply_dropout != 0;
+    const uint32_t rmask = (1u << lanes.rows_shift) - 1u;
+    const uint16_t* zp = static_cast<const uint16_t*>(a.z) + g0 * H + cg * 8;
+    const uint16_t* rp = has_resid ? static_cast<const uint16_t*>(a.resid) + g0 * H + cg * 8 : nullptr;
+    uint16_t* ap = static_cast<uint16_t*>(a.a) + g0 * H + cg * 8;
+    uint8_t* bp = a.bits + g0 * tpr + cg;
+    const uint32_t grow0 = static_cast<uint32_t>(g0 + a.row_offset);
+    uint4 zq[2][APW_SUB], rq[2][APW_SUB];
+    auto load = [&](int s, uint4 (&zb)[APW_SUB], uint4 (&rb)[APW_SUB]) {
+#pragma unroll
+        for (int u = 0; u < APW_SUB; ++u) {
+            const int r = s * APW_SUB + u;
+            zb[u] = make_uint4(0, 0, 0, 0);
+            rb[u] = make_uint4(0, 0, 0, 0);
+            if (r < n) {
+                zb[u] = ldg_stream(zp + r * H);
+                if (has_resid) rb[u] = ldg_stream(rp + r * H);
+            }
+        }
+    };
+    Philox4 rnd = {0u, 0u, 0u, 0u};
+    load(0, zq[0], rq[0]);
+#pragma unroll
+    for (int s = 0; s < AP_ROWS / APW_SUB; ++s) {
+        if ((s + 1) * APW_SUB < n) load(s + 1, zq[(s + 1) & 1], rq[(s + 1) & 1]);
+#pragma unroll
+        for (int u = 0; u < APW_SUB; ++u) {
+            const int r = s * APW_SUB + u;
+            if (r >= n) break;
+            const uint32_t grow = grow0 + static_cast<uint32_t>(r);
+            uint32_t keep = 0xFFu;
+            if (dropout) {
+                if (r == 0 || (grow & rmask) == 0u)
+                    rnd = philox4x32_10(grow >> lanes.rows_shift, static_cast<uint32_t>(cg), a.site, dstep, keys);
+                keep = dropout_keep8(rnd, grow, lanes.bits, lanes.threshold);
+            }
+            float z[8];
+            unpack8(zq[s & 1][u], FMT, z);
+            uint32_t pos = 0;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const float y = fmaf(z[e], sc[e], sh[e]);
+                pos |= (y > 0.0f) ? (1u << e) : 0u;
+                z[e] = fmaxf(y, 0.0f);
+            }
+            const uint32_t active = pos & keep;
+            if (has_resid) {
+                // the dropped elements must be zero BEFORE the residual is added: mask in fp32 only where needed
+                float rr[8];
+                unpack8(rq[s & 1][u], FMT, rr);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) z[e] = ((keep >> e) & 1u) ? z[e] + rr[e] : rr[e];
+                *reinterpret_cast<uint4*>(ap + r * H) = pack8(z, FMT);
+            } else {
+                *reinterpret_cast<uint4*>(ap + r * H) = and4(pack8(z, FMT), lut[keep]);
+            }
+            bp[static_cast<long>(r) * tpr] = static_cast<uint8_t>(active);
+        }
+    }
+}
+
 // ---- the column sums of the GEMM epilogue -> batch statistics -> apply, in ONE launch --------------------------------
 // Blocks first share out the second stage of the column reduction (8 columns each: fp64 sums over the GEMM's partial
 // rows, SyncBN exchange, scale / shift, running statistics), meet at a grid barrier, then every block applies
@@ -292,9 +399,6 @@ __device__ __forceinline__ void fill_mask_lut(uint4* lut) {
             w[i] = (((b >> (2 * i)) & 1) ? 0x0000FFFFu : 0u) | (((b >> (2 * i + 1)) & 1) ? 0xFFFF0000u : 0u);
         lut[b] = make_uint4(w[0], w[1], w[2], w[3]);
     }
-}
-__device__ __forceinline__ uint4 and4(const uint4& a, const uint4& m) {
-    return make_uint4(a.x & m.x, a.y & m.y, a.z & m.z, a.w & m.w);
 }
 
 // pass 1: partial column sums of gm = (g masked by the active bit) and of gm * z (raw z).  The finalize turns them
@@ -794,6 +898,19 @@ int bn_apply_fwd(const BnApplyFwd& a, cudaStream_t st) {
     const DropoutLanes lanes = dropout_lanes(a.p);
     const PhiloxKeys keys = philox_round_keys(a.seed);
     const float inv_keep = (a.apply_dropout && a.p < 1.0f) ? 1.0f / (1.0f - a.p) : (a.apply_dropout ? 0.0f : 1.0f);
+    static const bool block_variant = [] { const char* e = getenv("LIFTER_APPLY_BLOCK"); return e != nullptr && e[0] == '1'; }();
+    if (!block_variant) {                         // one warp per 16 rows x 256 columns, two warps per block
+        const int tpr = a.H / 8;
+        const int cpw = tpr < 32 ? tpr : 32, chunks = tpr / cpw, rpw = 32 / cpw;
+        const int64_t units = ((a.rows + static_cast<int64_t>(rpw) * AP_ROWS - 1) / (static_cast<int64_t>(rpw) * AP_ROWS)) * chunks;
+        const unsigned blocks = static_cast<unsigned>((units + APW_THREADS / 32 - 1) / (APW_THREADS / 32));
+        static const bool shallow = [] { const char* e = getenv("LIFTER_APPLY_SHALLOW"); return e != nullptr && e[0] == '1'; }();
+        auto kern = a.fmt == FMT_BF16 ? (shallow ? bn_apply_fwd_warp_kernel<FMT_BF16, 2, 12> : bn_apply_fwd_warp_kernel<FMT_BF16, 4, 8>)
+                                      : (shallow ? bn_apply_fwd_warp_kernel<FMT_F16, 2, 12> : bn_apply_fwd_warp_kernel<FMT_F16, 4, 8>);
+        LIFTER_CHECK_CUDA(launch_pdl("bn_apply_fwd_warp_kernel", kern, dim3(blocks), dim3(APW_THREADS), 0, st, a, chunks, cpw, lanes, inv_keep, keys));
+        return LIFTER_OK;
+    }
+    // (LIFTER_APPLY_BLOCK=1: the block-per-32-rows kernel, kept for A/B timing)
     // a block owns whole 16-row groups; up to four blocks per SM's worth of them, filled evenly
     const int64_t group = static_cast<int64_t>(EW_THREADS / (a.H / 8)) * AP_ROWS;
     const int64_t groups = (a.rows + group - 1) / group;

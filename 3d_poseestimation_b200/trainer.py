@@ -72,7 +72,9 @@ class LifterTrainer:
         # data parallel: capture the NCCL gradient all-reduce into the step graph too (LIFTER_DP_GRAPH=0 turns it off)
         self.graph_collectives = os.environ.get("LIFTER_DP_GRAPH", "1") != "0"
         # per-layer optimiser ranges inside backward (LIFTER_FUSE_OPTIM=0: one Adam launch after backward)
-        self.fuse_optimizer = os.environ.get("LIFTER_FUSE_OPTIM", "1") != "0"
+        # (data parallel: measured on 2 B200, the ranges are SLOWER than one closing reduce-scatter / Adam / all-gather launch,
+        #  0.547 vs 0.535 ms per step -- profiles/r02_dp_breakdown*.jsonl -- so the default there is the closing launch)
+        self.fuse_optimizer = os.environ.get("LIFTER_FUSE_OPTIM", "1" if self.world == 1 else "0") != "0"
         self._state_stale = False
         self._sym = None
         self._dp_adam = False
@@ -139,6 +141,9 @@ class LifterTrainer:
             dp.grad[p] = base + off_grad
             dp.params[p] = base + off_par
             dp.operands[p] = base + off_ops
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)             # NVSwitch multicast view of the same buffer (0: none)
+        if mc:
+            dp.mc_grad, dp.mc_params, dp.mc_operands = mc + off_grad, mc + off_par, mc + off_ops
         self._sym, self._sym_hdl = buf, hdl
         # gradients, parameters and the training operand copy live in the symmetric buffer from now on
         self.grad = buf[off_grad:off_grad + 4 * n].view(torch.float32)

@@ -115,6 +115,11 @@ typedef struct lifter_dp {
     void* params[LIFTER_DP_MAX_WORLD];
     void* operands[LIFTER_DP_MAX_WORLD];
     void* flags[LIFTER_DP_MAX_WORLD];
+    /* Optional NVSwitch multicast mappings of the SAME three regions (one address that reaches every rank's copy, e.g.
+     * torch symmetric memory's multicast_ptr + the region offset); all three set or all NULL.  With them the optimiser
+     * kernel reduces its gradient slice in the switch (multimem.ld_reduce) and broadcasts the new parameters and dense
+     * operand copies with one store each (multimem.st) instead of `world` unicast loads / stores per element.          */
+    void* mc_grad; void* mc_params; void* mc_operands;
 } lifter_dp_t;
 #define LIFTER_DP_FLAG_BYTES 256
 int64_t lifter_dp_sync_bytes(const struct lifter_config* cfg, int world);
