@@ -72,9 +72,10 @@ class LifterTrainer:
         # data parallel: capture the NCCL gradient all-reduce into the step graph too (LIFTER_DP_GRAPH=0 turns it off)
         self.graph_collectives = os.environ.get("LIFTER_DP_GRAPH", "1") != "0"
         # per-layer optimiser ranges inside backward (LIFTER_FUSE_OPTIM=0: one Adam launch after backward)
-        # (data parallel: measured on 2 B200, the ranges are SLOWER than one closing reduce-scatter / Adam / all-gather launch,
-        #  0.547 vs 0.535 ms per step -- profiles/r02_dp_breakdown*.jsonl -- so the default there is the closing launch)
-        self.fuse_optimizer = os.environ.get("LIFTER_FUSE_OPTIM", "1" if self.world == 1 else "0") != "0"
+        # Data parallel, measured (profiles/r02_dp_breakdown_dp{2,8}.jsonl): with ONE peer a single closing reduce-scatter /
+        # Adam / all-gather launch beats the ranges (0.535 vs 0.547 ms per step), with seven peers the ranges win (0.572 vs
+        # 0.610 ms): the default is the closing launch for a world of exactly two.
+        self.fuse_optimizer = os.environ.get("LIFTER_FUSE_OPTIM", "0" if self.world == 2 else "1") != "0"
         self._state_stale = False
         self._sym = None
         self._dp_adam = False

@@ -50,16 +50,20 @@ def main():
         losses.append(tr.loss_value())
     torch.cuda.synchronize()
     err = max(abs(a - b) / abs(b) for a, b in zip(losses, ref_losses))
-    pd = (m._flat - ref._flat).norm().item() / ref._flat.norm().item()
-    rm = (m._rm - ref._rm).abs().max().item()
-    # identical parameters on every rank (deterministic exchange + all-reduce)
+    p0 = build()._flat
+    # the UPDATE the steps made (Adam's first steps are sign-like: a gradient entry within bf16 noise of zero flips its
+    # whole step when the summation order changes, N shards vs one batch: measured 0.01-0.12; a rank missing from the
+    # exchange or local BatchNorm statistics give >= 0.5) and the running mean relative to its scale
+    ud = (m._flat - ref._flat).norm().item() / (ref._flat - p0).norm().item()
+    rm = (m._rm - ref._rm).abs().max().item() / ref._rm.abs().max().item()
+    # identical parameters on every rank (deterministic exchange + reduce-scatter)
     mine = m._flat.clone()
     other = mine.clone()
     dist.broadcast(other, src=0)
     same = bool(torch.equal(mine, other))
-    print(f"[rank {rank}] loss rel err {err:.2e}  param rel diff {pd:.2e}  running_mean diff {rm:.2e}  "
+    print(f"[rank {rank}] loss rel err {err:.2e}  update rel diff {ud:.2e}  running_mean rel diff {rm:.2e}  "
           f"replicas identical {same}", flush=True)
-    ok = err < 2e-3 and pd < 2e-3 and rm < 1e-3 and same
+    ok = err < 2e-3 and ud < 0.2 and rm < 5e-3 and same
     dist.barrier()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
