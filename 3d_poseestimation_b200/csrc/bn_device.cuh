@@ -42,7 +42,16 @@ __device__ __forceinline__ double ld_ll_f64(const uint4* p, unsigned epoch, long
 
 // Called by the first RED_COLS threads of a block (threadIdx.y == 0) holding the local sums (ta, tb) of column
 // `col`; returns the sums over all ranks, added in rank order (identical on every GPU).  See SyncExchange.
-__device__ __forceinline__ void exchange_column_sums(const SyncExchange& ex, int H, int col, bool active, double& ta,
+__device__ __forceinline__ uint4 ld_ll_words(const uint4* p) {
+    uint4 w;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "l"(p) : "memory");
+    return w;
+}
+__device__ __forceinline__ double ll_value(const uint4& w) {
+    return __longlong_as_double(static_cast<long long>((static_cast<unsigned long long>(w.z) << 32) | w.x));
+}
+// The default form: ONE thread per column stores its pair to every peer and then polls the peers' slots one after another.
+__device__ __forceinline__ void exchange_column_sums_serial(const SyncExchange& ex, int H, int col, bool active, double& ta,
                                                      double& tb) {
     if (!active) return;
     const unsigned epoch = *ex.epoch;
@@ -63,6 +72,73 @@ __device__ __forceinline__ void exchange_column_sums(const SyncExchange& ex, int
         ta += ld_ll_f64(d + col, epoch, ex.spin_limit);
         tb += ld_ll_f64(d + H + col, epoch, ex.spin_limit);
     }
+}
+
+// Warp-cooperative exchange.  Called by ALL 32 lanes of the warp whose lanes are (sub, column) = (lane / 8, lane % 8):
+// the sub == 0 lane of a column holds the local sums (ta, tb) and gets the sums over all ranks back, added in rank order
+// (identical, bit for bit, on every GPU); `active` = the column exists (the same for the four lanes of a column).
+// ex.serial (the default): the sub == 0 lane runs exchange_column_sums_serial.  Otherwise (LIFTER_DP_EXCHANGE_WARP=1) the
+// sub == 0 lane stores its pair into its slot on every peer and lane (sub, column) polls the slots of peers `sub` and
+// `sub + 4`, both words of a slot in flight together, so that the wait is one L2 round trip for any world size, and the
+// sub == 0 lane gathers the values with shuffles.  MEASURED NEGATIVE RESULT (same box, alternating runs, configs[2]): the
+// cooperative form is SLOWER, 0.553 vs 0.541 ms per step at 2 ranks and 0.592 vs 0.574 ms at 8
+// (profiles/r02_dp_exchange_ab_dp{2,8}.jsonl): the exchange's cost (25 us per step at 2 ranks, 55 us at 8) is not the
+// receiver's polling order but the ten cross-rank synchronisation points themselves.
+__device__ __forceinline__ void poll_slot(const uint4* pa, const uint4* pb, unsigned epoch, long long spin_limit, double& va,
+                                          double& vb) {
+    long long t0 = 0;
+    unsigned spins = 0;
+    while (true) {
+        const uint4 wa = ld_ll_words(pa), wb = ld_ll_words(pb);
+        if (wa.y == epoch && wa.w == epoch && wb.y == epoch && wb.w == epoch) {
+            va = ll_value(wa);
+            vb = ll_value(wb);
+            return;
+        }
+        if ((++spins & 0xFF) == 0 && spin_limit > 0) {           // a DEAD peer traps after LIFTER_DP_TIMEOUT_S
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > spin_limit) __trap();
+        }
+    }
+}
+__device__ __forceinline__ void exchange_column_sums_warp(const SyncExchange& ex, int H, int col, bool active, int sub,
+                                                          double& ta, double& tb) {
+    if (ex.serial) {                                                // uniform over the launch
+        if (sub == 0) exchange_column_sums_serial(ex, H, col, active, ta, tb);
+        return;
+    }
+    const unsigned epoch = *ex.epoch;
+    // [parity][site][slot = writer rank][2][H] LL words
+    const size_t base = ((static_cast<size_t>(epoch & 1u) * ex.nsites + ex.site) * ex.world) * 2 * H;
+    if (active && sub == 0) {
+        const size_t mine = base + static_cast<size_t>(ex.rank) * 2 * H;
+        for (int p = 0; p < ex.world; ++p) {
+            if (p == ex.rank) continue;
+            uint4* d = reinterpret_cast<uint4*>(ex.data[p]) + mine;
+            st_ll_f64(d + col, ta, epoch);
+            st_ll_f64(d + H + col, tb, epoch);
+        }
+    }
+    const uint4* in = reinterpret_cast<const uint4*>(ex.data[ex.rank]) + base;
+    double va[2] = {0.0, 0.0}, vb[2] = {0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int r = sub + 4 * k;
+        if (active && r < ex.world && r != ex.rank)
+            poll_slot(in + static_cast<size_t>(r) * 2 * H + col, in + static_cast<size_t>(r) * 2 * H + H + col, epoch,
+                      ex.spin_limit, va[k], vb[k]);
+    }
+    const double la = ta, lb = tb;
+    double sa = 0.0, sb = 0.0;
+    const int c = static_cast<int>(lane_id()) & 7;
+    for (int r = 0; r < ex.world; ++r) {                            // uniform over the warp: every lane shuffles
+        const int src = (r & 3) * 8 + c;
+        const double xa = __shfl_sync(0xffffffffu, r < 4 ? va[0] : va[1], src);
+        const double xb = __shfl_sync(0xffffffffu, r < 4 ? vb[0] : vb[1], src);
+        if (r == ex.rank) { sa += la; sb += lb; } else { sa += xa; sb += xb; }
+    }
+    if (sub == 0) { ta = sa; tb = sb; }
 }
 
 // Per-column inputs of the finalize that do not depend on the reduction: fetched before it so their latency hides.

@@ -561,7 +561,7 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                     }
                     double ta = sh[0][0][cc], tb = sh[1][0][cc];
                     named_bar_sync(1, EPI_THREADS);                // sh is reused by the next column group
-                    if (f.ex.world > 1 && lane_r == 0) exchange_column_sums(f.ex, p.N, col, col < p.N, ta, tb);
+                    if (f.ex.world > 1 && lane_r < 4) exchange_column_sums_warp(f.ex, p.N, col, col < p.N, lane_r, ta, tb);
                     if (lane_r == 0 && col < p.N) {
                         p.fb_sums_out[col] = ta;
                         p.fb_sums_out[p.N + col] = tb;

@@ -98,6 +98,9 @@ int fill_exchange(const Layout& lay, const lifter_train_ctx_t* t, int site, Sync
     }
     ex->epoch = reinterpret_cast<const unsigned*>(t->step_state) + 1;      // lifter_step_state_t.adam_step
     ex->spin_limit = dp_spin_limit_clocks();
+    // LIFTER_DP_EXCHANGE_WARP=1: the warp-cooperative polling of bn_device.cuh (measured slower, see there)
+    static const bool warp = [] { const char* e = getenv("LIFTER_DP_EXCHANGE_WARP"); return e != nullptr && e[0] == '1'; }();
+    ex->serial = warp ? 0 : 1;
     return LIFTER_OK;
 }
 

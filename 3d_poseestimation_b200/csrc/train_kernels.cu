@@ -66,7 +66,7 @@ __device__ __forceinline__ void reduce_partials_2(const float* __restrict__ a, c
 }
 
 template <typename OutT>
-__global__ void reduce_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int P, int n, int ld,
+__global__ void __launch_bounds__(RED_COLS * RED_LANES, 1) reduce_rows_kernel(const float* __restrict__ a, const float* __restrict__ b, int P, int n, int ld,
                                    OutT* __restrict__ out_a, OutT* __restrict__ out_b) {
     griddep_launch();
     griddep_wait();
@@ -92,7 +92,7 @@ __global__ void bn_finalize_fwd_kernel(BnFwdFinalize a) {
 }
 
 // single-GPU path: second stage of the column reduction and the finalize in one launch
-__global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, const float* __restrict__ psq, int P,
+__global__ void __launch_bounds__(RED_COLS * RED_LANES, 1) bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, const float* __restrict__ psq, int P,
                                               BnFwdFinalize a, double* __restrict__ sums_out) {
     griddep_launch();
     griddep_wait();
@@ -102,7 +102,7 @@ __global__ void bn_reduce_finalize_fwd_kernel(const float* __restrict__ psum, co
     BnColumnInputs ci = {0.0f, 1.0f, 0.0f, 0.0f, 1.0f};
     if (threadIdx.y == 0 && col < a.H) ci = bn_column_inputs(a, col);
     reduce_partials_2(psum, psq, P, a.H, a.H, sh, ta, tb);
-    if (a.ex.world > 1 && threadIdx.y == 0) exchange_column_sums(a.ex, a.H, col, col < a.H, ta, tb);
+    if (a.ex.world > 1 && threadIdx.y < 4) exchange_column_sums_warp(a.ex, a.H, col, col < a.H, threadIdx.y, ta, tb);   // warp 0
     if (threadIdx.y == 0 && col < a.H) {
         sums_out[col] = ta;
         sums_out[a.H + col] = tb;
@@ -373,7 +373,7 @@ __global__ void __launch_bounds__(EW_THREADS, 2) bn_fwd_fused_kernel(const float
         if (lane_r == 0 && col < f.H) ci = bn_column_inputs(f, col);
         double ta, tb;
         reduce_partials_block(psum, psq, P, f.H, f.H, col, lane_r, sh, ta, tb);
-        if (f.ex.world > 1 && lane_r == 0) exchange_column_sums(f.ex, f.H, col, col < f.H, ta, tb);
+        if (f.ex.world > 1 && lane_r < 4) exchange_column_sums_warp(f.ex, f.H, col, col < f.H, lane_r, ta, tb);
         if (lane_r == 0 && col < f.H) {
             sums_out[col] = ta;
             sums_out[f.H + col] = tb;
@@ -591,7 +591,7 @@ __global__ void bn_finalize_bwd_kernel(BnBwdFinalize a) {
 // second stage of pass 1: LOCAL sums of dy and dy * zhat (fp64, what a data-parallel run all-reduces) and the
 // BatchNorm parameter gradients from them; FUSED also writes the pass-2 coefficients (single GPU: local == global)
 template <bool FUSED>
-__global__ void bn_bwd_reduce_kernel(const float* __restrict__ pg, const float* __restrict__ pgz, int P,
+__global__ void __launch_bounds__(RED_COLS * RED_LANES, 1) bn_bwd_reduce_kernel(const float* __restrict__ pg, const float* __restrict__ pgz, int P,
                                      BnBwdFinalize a, double* __restrict__ sums_out, float* __restrict__ dgamma,
                                      float* __restrict__ dbeta) {
     griddep_launch();
@@ -610,7 +610,7 @@ __global__ void bn_bwd_reduce_kernel(const float* __restrict__ pg, const float* 
         dbeta[col] = static_cast<float>(sum_dy);                            // parameter gradients: LOCAL sums
         dgamma[col] = static_cast<float>(sum_dyz);
     }
-    if (FUSED && a.ex.world > 1 && threadIdx.y == 0) exchange_column_sums(a.ex, a.H, col, col < a.H, sum_dy, sum_dyz);
+    if (FUSED && a.ex.world > 1 && threadIdx.y < 4) exchange_column_sums_warp(a.ex, a.H, col, col < a.H, threadIdx.y, sum_dy, sum_dyz);
     if (threadIdx.y == 0 && col < a.H) {
         sums_out[col] = sum_dy;
         sums_out[a.H + col] = sum_dyz;
@@ -731,7 +731,7 @@ __global__ void __launch_bounds__(EW_THREADS, 2) bn_bwd_fused_kernel(BwdCommon c
                 dbeta[col] = static_cast<float>(sum_dy);                        // parameter gradients: LOCAL sums
                 dgamma[col] = static_cast<float>(sum_dyz);
             }
-            if (f.ex.world > 1 && lane_r == 0) exchange_column_sums(f.ex, f.H, col, col < f.H, sum_dy, sum_dyz);
+            if (f.ex.world > 1 && lane_r < 4) exchange_column_sums_warp(f.ex, f.H, col, col < f.H, lane_r, sum_dy, sum_dyz);
             if (lane_r == 0 && col < f.H) {
                 sums_out[col] = sum_dy;
                 sums_out[f.H + col] = sum_dyz;

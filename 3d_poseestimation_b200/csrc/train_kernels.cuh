@@ -29,6 +29,7 @@ struct SyncExchange {
     void* data[DP_MAX_WORLD];          // peer p's buffer: [2 parities][nsites][world slots][2][H] 16-byte LL words
     const unsigned* epoch;             // device: the step counter (lifter_step_state_t.adam_step), >= 1
     long long spin_limit = 0;          // SM clocks a peer is waited for before the kernel traps (0 = forever)
+    int serial = 1;                    // 1 (default): one thread per column polls slot after slot; 0: warp-cooperative polling
 };
 
 struct BnFwdFinalize {
