@@ -19,8 +19,9 @@ normalise, denormalise = _m.normalise, _m.denormalise
 normalise_minmax, denormalise_minmax = _m.normalise_minmax, _m.denormalise_minmax
 PoseLoss, l1_loss, coco2h36m = _m.PoseLoss, _m.l1_loss, _m.coco2h36m
 keypoint_stats, process_data = _m.keypoint_stats, _m.process_data
+keypoints_to_heatmap_3D = _m.keypoints_to_heatmap_3D          # phase3_direct/my_HybrIK/H36_dataset.py:196-202
 H36M_EDGES, H36M_INTRINSICS, LEFT_JOINTS, RIGHT_JOINTS = _m.H36M_EDGES, _m.H36M_INTRINSICS, _m.LEFT_JOINTS, _m.RIGHT_JOINTS
 
 __all__ = ["loss_MPJPE", "TriangleLoss", "TriangleLoss_sep", "flip_pose", "flip_average", "epoch_mpjpe_mm",
-           "normalise", "denormalise", "normalise_minmax", "denormalise_minmax", "PoseLoss", "l1_loss", "coco2h36m", "keypoint_stats", "process_data",
+           "normalise", "denormalise", "normalise_minmax", "denormalise_minmax", "PoseLoss", "l1_loss", "coco2h36m", "keypoint_stats", "process_data", "keypoints_to_heatmap_3D",
            "H36M_EDGES", "H36M_INTRINSICS", "LEFT_JOINTS", "RIGHT_JOINTS"]
