@@ -86,6 +86,8 @@ struct alignas(64) GemmParams {
     int slab_rows;
     float* stat_sum;
     float* stat_sq;
+    const float* resid32;              // OUT_32_TMA: fp32 residual [M][ldr32] (nullptr: none)
+    long ldr32;
     unsigned long long* timeline;      // debug hook: [gridDim.x][32] globaltimer stamps (nullptr in production)
     int stages;                        // ring depth in use (<= Cfg::STAGES; lowered only by the debug hook)
     // whole-layer mode (FUSED instantiation only; see FusedBnArgs in gemm_sm100.cuh)
@@ -492,6 +494,20 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                         buf ^= 1;
                     }
                 } else if (p.out_mode == OUT_32_TMA) {
+                    if (p.resid32 != nullptr && tile_ok && static_cast<int>(lane) < rows_valid) {
+                        // fp32 residual stream (MyViT eval path): this lane's row, 32 consecutive columns = one 128-byte line
+                        const float* rr = p.resid32 + static_cast<long>(row0 + lane) * p.ldr32 + n0;
+                        if (n0 + 32 <= p.N) {
+#pragma unroll
+                            for (int qq = 0; qq < 8; ++qq) {
+                                const float4 r4 = *reinterpret_cast<const float4*>(rr + 4 * qq);
+                                x[4 * qq] += r4.x; x[4 * qq + 1] += r4.y; x[4 * qq + 2] += r4.z; x[4 * qq + 3] += r4.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) if (n0 + j < p.N) x[j] += rr[j];
+                        }
+                    }
                     if (lane == 0) tma_store_wait_read<1>();
                     __syncwarp();
                     const uint32_t dst = stg_addr + buf * 4096 + lane * 128;
@@ -846,6 +862,9 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
         LIFTER_REQUIRE(a.n_valid > 0 && a.n_valid <= 64 && a.N <= 64, "gemm: direct fp32 output holds at most 64 columns");
     LIFTER_REQUIRE(a.stat_sum == nullptr || (a.out_mode == OUT_16_TMA && a.stat_sq != nullptr),
                    "gemm: column statistics ride on the 16-bit output");
+    LIFTER_REQUIRE(a.residual32 == nullptr || (a.out_mode == OUT_32_TMA && a.splits == 1 && a.ldr32 % 4 == 0 &&
+                                               (reinterpret_cast<uintptr_t>(a.residual32) & 15) == 0),
+                   "gemm: the fp32 residual rides on the single-slab fp32 output and needs 16-byte aligned rows");
     LIFTER_REQUIRE(a.residual == nullptr || (a.out_mode == OUT_16_TMA && a.ldr % 8 == 0),
                    "gemm: the residual rides on the 16-bit output and needs a 16-byte row stride");
 
@@ -865,6 +884,7 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     p.out_direct = static_cast<float*>(a.D); p.n_valid = a.n_valid;
     p.slab_rows = gemm_slab_rows(a.M);
     p.stat_sum = a.stat_sum; p.stat_sq = a.stat_sq;
+    p.resid32 = a.residual32; p.ldr32 = a.ldr32;
     p.timeline = a.timeline;
 
     if (a.fused_bn != nullptr) {

@@ -84,6 +84,17 @@ __device__ __forceinline__ void load_row16(const void* in, long row, int lane, f
     }
 }
 
+// fp32 rows of the residual stream (eval path): lane l holds columns v * 256 + l * 8 + [0, 8) as two float4
+template <int NV>
+__device__ __forceinline__ void store_row32(float* out, long row, int lane, const float (&x)[NV][8]) {
+    float4* dst = reinterpret_cast<float4*>(out + row * (NV * 256));
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        dst[v * 64 + lane * 2] = make_float4(x[v][0], x[v][1], x[v][2], x[v][3]);
+        dst[v * 64 + lane * 2 + 1] = make_float4(x[v][4], x[v][5], x[v][6], x[v][7]);
+    }
+}
+
 #define VIT_DISPATCH_NV(nv, CALL)                     \
     switch (nv) {                                     \
         case 1: { constexpr int NV = 1; CALL; break; } \

@@ -7,6 +7,7 @@
 //   vit_attention_kernel  softmax(q k^T / sqrt(d_head)) v for the 17 x 17 token pairs of one (pose, head)   [FP32 pipe]
 #include "vit_ops.cuh"
 
+#include "elementwise.cuh"
 #include "gemm_sm100.cuh"
 #include "vit_common.cuh"
 
@@ -24,7 +25,7 @@ __global__ void __launch_bounds__(256) vit_embed_kernel(const float* __restrict_
                                                         const float* __restrict__ pos, void* __restrict__ h,
                                                         const float* __restrict__ g1, const float* __restrict__ b1,
                                                         const float* __restrict__ g2, const float* __restrict__ b2, float eps,
-                                                        void* __restrict__ u, int fmt) {
+                                                        void* __restrict__ u, int fmt, float* __restrict__ h32) {
     griddep_launch();
     griddep_wait();
     const int lane = threadIdx.x & 31;
@@ -70,7 +71,8 @@ __global__ void __launch_bounds__(256) vit_embed_kernel(const float* __restrict_
                 }
             }
         }
-        store_row16<NV>(h, t, lane, v, fmt);
+        if (h32 != nullptr) store_row32<NV>(h32, t, lane, v);      // fp32 residual stream (eval path)
+        else store_row16<NV>(h, t, lane, v, fmt);
         if (g1 != nullptr) {
             warp_layernorm<NV>(v, ln1, eps);
             warp_layernorm<NV>(v, ln2, eps);
@@ -82,7 +84,7 @@ __global__ void __launch_bounds__(256) vit_embed_kernel(const float* __restrict_
 
 // out = LN2(LN1(in)) (g2 == nullptr: one LayerNorm).  in / out 16-bit [T][Hd]; statistics and affine in fp32, no
 // 16-bit rounding between the two norms.
-template <int NV>
+template <int NV, bool IN32 = false>
 __global__ void __launch_bounds__(256) vit_layernorm_kernel(const void* __restrict__ in, long T, const float* __restrict__ g1,
                                                             const float* __restrict__ b1, const float* __restrict__ g2,
                                                             const float* __restrict__ b2, float eps, void* __restrict__ out,
@@ -96,31 +98,43 @@ __global__ void __launch_bounds__(256) vit_layernorm_kernel(const void* __restri
     load_row_params<NV>(ln1, g1, b1, lane);
     if (g2 != nullptr) load_row_params<NV>(ln2, g2, b2, lane);
     const long t1 = min(T, t0 + VIT_RPW);
-    const uint4* src = reinterpret_cast<const uint4*>(static_cast<const unsigned short*>(in));
-    uint4 cur[NV], nxt[NV];
+    // IN32: the input rows are the fp32 residual stream (eval path): two 16-byte vectors per lane and 256 columns
+    constexpr int VPR = IN32 ? 2 : 1;                                 // uint4 vectors per lane per 256 columns
+    const uint4* src = reinterpret_cast<const uint4*>(in);
+    uint4 cur[NV * VPR], nxt[NV * VPR];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) cur[k] = src[t0 * (NV * 32) + k * 32 + lane];
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+        for (int q = 0; q < VPR; ++q) cur[k * VPR + q] = src[t0 * (NV * 32 * VPR) + k * 32 * VPR + lane * VPR + q];
     for (long t = t0; t < t1; ++t) {
         if (t + 1 < t1) {                                             // next row in flight while this one is normalised
 #pragma unroll
-            for (int k = 0; k < NV; ++k) nxt[k] = src[(t + 1) * (NV * 32) + k * 32 + lane];
+            for (int k = 0; k < NV; ++k)
+#pragma unroll
+                for (int q = 0; q < VPR; ++q) nxt[k * VPR + q] = src[(t + 1) * (NV * 32 * VPR) + k * 32 * VPR + lane * VPR + q];
         }
         float v[NV][8];
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
-            const uint32_t wd[4] = {cur[k].x, cur[k].y, cur[k].z, cur[k].w};
+            if constexpr (IN32) {
+                const uint4 a = cur[k * 2], b = cur[k * 2 + 1];
+                v[k][0] = __uint_as_float(a.x); v[k][1] = __uint_as_float(a.y); v[k][2] = __uint_as_float(a.z); v[k][3] = __uint_as_float(a.w);
+                v[k][4] = __uint_as_float(b.x); v[k][5] = __uint_as_float(b.y); v[k][6] = __uint_as_float(b.z); v[k][7] = __uint_as_float(b.w);
+            } else {
+                const uint32_t wd[4] = {cur[k].x, cur[k].y, cur[k].z, cur[k].w};
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const float2 f = unpack16(wd[e], fmt);
-                v[k][2 * e] = f.x;
-                v[k][2 * e + 1] = f.y;
+                for (int e = 0; e < 4; ++e) {
+                    const float2 f = unpack16(wd[e], fmt);
+                    v[k][2 * e] = f.x;
+                    v[k][2 * e + 1] = f.y;
+                }
             }
         }
         warp_layernorm<NV>(v, ln1, eps);
         if (g2 != nullptr) warp_layernorm<NV>(v, ln2, eps);
         store_row16<NV>(out, t, lane, v, fmt);
 #pragma unroll
-        for (int k = 0; k < NV; ++k) cur[k] = nxt[k];
+        for (int k = 0; k < NV * VPR; ++k) cur[k] = nxt[k];
     }
 }
 
@@ -298,10 +312,10 @@ int vit_embed(const VitDesc& d, const float* x, long T, void* h, const float* ln
     const float* l3 = ln0 ? ln0 + 3 * H : nullptr;
     if (d.in_dim == 2) {
         VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_kernel", vit_embed_kernel<NV, 2>, dim3(row_blocks), dim3(256), 0, st, x, T,
-                                                         d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, h, ln0, l1, l2, l3, d.ln_eps, u, d.fmt)));
+                                                         d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, h, ln0, l1, l2, l3, d.ln_eps, u, d.fmt, static_cast<float*>(nullptr))));
     } else {
         VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_kernel", vit_embed_kernel<NV, 0>, dim3(row_blocks), dim3(256), 0, st, x, T,
-                                                         d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, h, ln0, l1, l2, l3, d.ln_eps, u, d.fmt)));
+                                                         d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, h, ln0, l1, l2, l3, d.ln_eps, u, d.fmt, static_cast<float*>(nullptr))));
     }
     return LIFTER_OK;
 }
@@ -311,6 +325,15 @@ int vit_layernorm(const void* in, long T, const float* g1, const float* b1, cons
     const unsigned row_blocks = static_cast<unsigned>((T + 8 * VIT_RPW - 1) / (8 * VIT_RPW));
     VIT_DISPATCH_NV(H / 256, LIFTER_CHECK_CUDA(launch_pdl("vit_layernorm_kernel", vit_layernorm_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
                                                           in, T, g1, b1, g2, b2, eps, out, fmt)));
+    return LIFTER_OK;
+}
+
+// LayerNorm(s) of the fp32 residual stream -> 16-bit GEMM operand (eval path)
+static int vit_layernorm32(const float* in, long T, const float* g1, const float* b1, const float* g2, const float* b2, float eps,
+                           void* out, int H, int fmt, cudaStream_t st) {
+    const unsigned row_blocks = static_cast<unsigned>((T + 8 * VIT_RPW - 1) / (8 * VIT_RPW));
+    VIT_DISPATCH_NV(H / 256, LIFTER_CHECK_CUDA(launch_pdl("vit_layernorm_kernel<fp32 in>", vit_layernorm_kernel<NV, true>, dim3(row_blocks), dim3(256), 0, st,
+                                                          static_cast<const void*>(in), T, g1, b1, g2, b2, eps, out, fmt)));
     return LIFTER_OK;
 }
 
@@ -328,8 +351,12 @@ int vit_attention(const void* qkv, long pose_heads, int tokens, int heads, int d
     return LIFTER_OK;
 }
 
-// 16-bit elements per token in the workspace: h0, h1, u, o (hidden each), qkv (3 hidden), m (mlp_dim), r (head_dim)
-static long vit_ws_halfs_per_token(const VitDesc& d) { return 7L * d.hidden + d.mlp_dim + d.head_dim; }
+// Workspace per token, in 16-bit units: the residual stream h0, h1 in FP32 (2 x 2 hidden), then 16-bit u, o (hidden
+// each), qkv (3 hidden), m (mlp_dim), r (head_dim).  The residual stream is fp32 in the eval path: of the fifteen 16-bit
+// rounding points of the round-1 forward, the two per block on `h` were the largest error term (0.094 of 0.143 mm rms
+// after de-normalisation, scripts/vit_rounding_ablation.py) and put ~0.5 % of the coordinates outside north_star's
+// 0.5 mm + 1e-2 band; GEMM operands (u, o, m, the head input) and weights stay 16-bit.
+static long vit_ws_halfs_per_token(const VitDesc& d) { return 9L * d.hidden + d.mlp_dim + d.head_dim; }
 
 int64_t vit_workspace_bytes(const VitDesc& d, int64_t poses) {
     if (vit_validate(d) != LIFTER_OK || poses < 0) return LIFTER_ERR_INVALID;
@@ -346,29 +373,28 @@ int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace
     const long T = poses * d.tokens;
     LIFTER_REQUIRE(T <= 0x7fffffffL, "vit_forward: %ld tokens in one call; process the batch in chunks", T);
     const int H = d.hidden, nv = H / 256, dh = H / d.heads, M = static_cast<int>(T);
-    unsigned short* ws = static_cast<unsigned short*>(workspace);
-    unsigned short* h0 = ws;
-    unsigned short* h1 = h0 + T * H;
-    unsigned short* u = h1 + T * H;
+    float* h0 = static_cast<float*>(workspace);                      // fp32 residual stream, two buffers
+    float* h1 = h0 + T * H;
+    unsigned short* u = reinterpret_cast<unsigned short*>(h1 + T * H);
     unsigned short* o = u + T * H;
     unsigned short* qkv = o + T * H;
     unsigned short* m = qkv + T * 3L * H;
     unsigned short* r = m + T * static_cast<long>(d.mlp_dim);
     const unsigned row_blocks = static_cast<unsigned>((T + 8 * VIT_RPW - 1) / (8 * VIT_RPW));   // 8 warps x VIT_RPW token rows per block
 
-    {   // embedding (+ the first block's LayerNorm pair)
+    {   // embedding -> h0 (fp32) (+ the first block's LayerNorm pair -> u)
         const float* ln0 = d.blocks > 0 ? d.ln : nullptr;
         const float* l1 = ln0 ? ln0 + H : nullptr;
         const float* l2 = ln0 ? ln0 + 2 * H : nullptr;
         const float* l3 = ln0 ? ln0 + 3 * H : nullptr;
         if (d.in_dim == 2) {
             VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_kernel", vit_embed_kernel<NV, 2>, dim3(row_blocks), dim3(256), 0, st, x, T,
-                                                             d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, static_cast<void*>(h0), ln0, l1, l2, l3,
-                                                             d.ln_eps, static_cast<void*>(u), d.fmt)));
+                                                             d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, static_cast<void*>(nullptr), ln0, l1, l2, l3,
+                                                             d.ln_eps, static_cast<void*>(u), d.fmt, h0)));
         } else {
             VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_kernel", vit_embed_kernel<NV, 0>, dim3(row_blocks), dim3(256), 0, st, x, T,
-                                                             d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, static_cast<void*>(h0), ln0, l1, l2, l3,
-                                                             d.ln_eps, static_cast<void*>(u), d.fmt)));
+                                                             d.tokens, d.in_dim, d.map_w, d.map_b, d.pos, static_cast<void*>(nullptr), ln0, l1, l2, l3,
+                                                             d.ln_eps, static_cast<void*>(u), d.fmt, h0)));
         }
     }
     const size_t smem = att_smem_bytes(d.tokens, dh);
@@ -386,9 +412,7 @@ int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace
         const char* w1 = static_cast<const char*>(d.w_mlp1) + static_cast<long>(b) * d.mlp_dim * H * esz;
         const char* w2 = static_cast<const char*>(d.w_mlp2) + static_cast<long>(b) * H * d.mlp_dim * esz;
         // u = mhsa.norm(norm1(h0))   (block 0: done by the embedding kernel)      baselineModel.py:303, 244
-        if (b > 0) VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_layernorm_kernel", vit_layernorm_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
-                                                         static_cast<const void*>(h0), T, ln, ln + H, ln + 2 * H, ln + 3 * H, d.ln_eps,
-                                                         static_cast<void*>(u), d.fmt)));
+        if (b > 0) LIFTER_PROPAGATE(vit_layernorm32(h0, T, ln, ln + H, ln + 2 * H, ln + 3 * H, d.ln_eps, u, H, d.fmt, st));
         GemmArgs g;                                                             // qkv = u Wqkv^T (no bias)   :246
         g.A = u; g.lda = H; g.B = wqkv; g.ldb = H; g.M = M; g.N = 3 * H; g.K = H; g.fmt = d.fmt;
         g.out_mode = OUT_16_TMA; g.D = qkv; g.ldd = 3 * H; g.tag = "vit_qkv";
@@ -399,26 +423,26 @@ int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace
         else
             LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<32>, dim3(static_cast<unsigned>((pose_heads + ATT_WARPS - 1) / ATT_WARPS)),
                                          dim3(ATT_WARPS * 32), smem, st, static_cast<const void*>(qkv), pose_heads, d.tokens, d.heads, scale_log2e, static_cast<void*>(o), d.fmt));
-        GemmArgs go;                                                            // h1 = h0 + o Wout^T        :254, 303
+        GemmArgs go;                                                            // h1 = h0 + o Wout^T  (fp32 in, fp32 out)   :254, 303
         go.A = o; go.lda = H; go.B = wout; go.ldb = H; go.M = M; go.N = H; go.K = H; go.fmt = d.fmt;
-        go.out_mode = OUT_16_TMA; go.D = h1; go.ldd = H; go.residual = h0; go.ldr = H; go.tag = "vit_attn_out";
+        go.out_mode = OUT_32_TMA; go.D = h1; go.ldd = H; go.residual32 = h0; go.ldr32 = H; go.tag = "vit_attn_out";
         LIFTER_PROPAGATE(gemm_launch(go, st));
-        VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_layernorm_kernel", vit_layernorm_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
-                                                         static_cast<const void*>(h1), T, ln + 4 * H, ln + 5 * H, static_cast<const float*>(nullptr),
-                                                         static_cast<const float*>(nullptr), d.ln_eps, static_cast<void*>(u), d.fmt)));
+        LIFTER_PROPAGATE(vit_layernorm32(h1, T, ln + 4 * H, ln + 5 * H, nullptr, nullptr, d.ln_eps, u, H, d.fmt, st));
         GemmArgs g1;                                                            // m = GELU(u W1^T + b1)     :296-298
         g1.A = u; g1.lda = H; g1.B = w1; g1.ldb = H; g1.M = M; g1.N = d.mlp_dim; g1.K = H; g1.fmt = d.fmt;
         g1.out_mode = OUT_16_TMA; g1.D = m; g1.ldd = d.mlp_dim; g1.shift = d.mlp_b1 + static_cast<long>(b) * d.mlp_dim; g1.relu = 2;
         g1.tag = "vit_mlp1";
         LIFTER_PROPAGATE(gemm_launch(g1, st));
-        GemmArgs g2;                                                            // h0 = h1 + m W2^T + b2     :299, 304
+        GemmArgs g2;                                                            // h0 = h1 + m W2^T + b2  (fp32)     :299, 304
         g2.A = m; g2.lda = d.mlp_dim; g2.B = w2; g2.ldb = d.mlp_dim; g2.M = M; g2.N = H; g2.K = d.mlp_dim; g2.fmt = d.fmt;
-        g2.out_mode = OUT_16_TMA; g2.D = h0; g2.ldd = H; g2.shift = d.mlp_b2 + static_cast<long>(b) * H; g2.residual = h1; g2.ldr = H;
+        g2.out_mode = OUT_32_TMA; g2.D = h0; g2.ldd = H; g2.shift = d.mlp_b2 + static_cast<long>(b) * H; g2.residual32 = h1; g2.ldr32 = H;
         g2.tag = "vit_mlp2";
         LIFTER_PROPAGATE(gemm_launch(g2, st));
     }
+    // the head's first Linear takes the final residual stream as a 16-bit operand: one conversion pass into u
+    LIFTER_PROPAGATE(prep_input(h0, T, H, H, nullptr, nullptr, u, d.fmt, st));
     GemmArgs gh;                                                                // r = ReLU(h0 Wh1^T + b)    :336-338
-    gh.A = h0; gh.lda = H; gh.B = d.w_head1; gh.ldb = H; gh.M = M; gh.N = d.head_dim; gh.K = H; gh.fmt = d.fmt;
+    gh.A = u; gh.lda = H; gh.B = d.w_head1; gh.ldb = H; gh.M = M; gh.N = d.head_dim; gh.K = H; gh.fmt = d.fmt;
     gh.out_mode = OUT_16_TMA; gh.D = r; gh.ldd = d.head_dim; gh.shift = d.head_b1; gh.relu = 1; gh.tag = "vit_head1";
     LIFTER_PROPAGATE(gemm_launch(gh, st));
     GemmArgs gf;                                                                // out = r Wh2^T + b (fp32)  :339

@@ -172,6 +172,12 @@ int lifter_train_bwd_begin(const lifter_config_t* cfg, const lifter_train_ctx_t*
 int lifter_train_bwd_layer_stats(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, int layer, void* stream);
 int lifter_train_bwd_layer_finish(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, int layer, void* stream);
 int lifter_train_backward(const lifter_config_t* cfg, const lifter_train_ctx_t* ctx, void* stream);  /* all layers, one GPU */
+/* Ownership note (an exception to "the library owns only plan handles"): lifter_train_backward and
+ * lifter_train_backward_step run the weight-gradient GEMMs (and the optimiser ranges) on side streams so that they overlap
+ * the BatchNorm-backward chain.  The library creates, on first use and per device, two non-blocking streams and a few
+ * timing-disabled events for this and keeps them until the process exits; they fork from and join back into `stream`
+ * with events, so the call is still ordered on `stream` and legal under stream capture.  LIFTER_WGRAD_STREAM=0 keeps
+ * everything on `stream` (the per-layer entry points above never use the side streams).                              */
 
 /* Fused loss + gradient + MPJPE metric (losses.py:3-7, train_1.py:37,94,100; two2three.py:387-390).
  * kind 0: MSELoss(mean), 1: L1Loss(mean), 2: mean MPJPE.  out[0] = loss over `global_rows`, out[1..joints] =

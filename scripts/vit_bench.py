@@ -101,7 +101,7 @@ with torch.no_grad():
 
 print(json.dumps({
     "metric": "lifted poses/sec (MyViT eval inference)", "value": B / ms * 1e3, "unit": "poses/s", "n_gpus": 1, "ms_per_step": ms,
-    "higher_is_better": True, "dtype": "fp16 operands and activations, fp32 accumulate / LayerNorm / softmax", "data": "synthetic",
+    "higher_is_better": True, "dtype": "fp16 GEMM operands, fp32 residual stream / accumulate / LayerNorm / softmax", "data": "synthetic",
     "config": {"workload": f"MyViT(chw=(1,17,2), n_blocks=2, hidden_d=256, n_heads=4) eval forward, {B} poses, {chunk} poses per pass",
                "chunk_sweep_ms": {str(k): round(v, 3) for k, v in sweep.items()}},
     "model_flop_per_pose": flop_pose, "model_tflops": B * flop_pose / ms / 1e9,

@@ -154,3 +154,38 @@ def test_model_on_another_device_than_the_current_one(pkg):
         outs.append((e, l, m._flat.cpu()))
         assert torch.cuda.current_device() == 0
     assert torch.equal(outs[0][0], outs[1][0]) and outs[0][1] == outs[1][1] and torch.equal(outs[0][2], outs[1][2])
+
+
+def test_graph_replay_revalidates_operands_and_survives_batch_size_changes(pkg):
+    """ADVICE round 1 (trainer.py): a replayed graph reads the 16-bit operand copy, so a parameter edit between steps
+    (load_state_dict, .apply(weight_init), an in-place write) must reach it; and a step at another batch size must not
+    free buffers whose addresses are baked into a graph that is still cached (three batch sizes stay resident, older
+    graphs are dropped together with their buffers)."""
+    trainer_mod = importlib.import_module("3d_poseestimation_b200.trainer")
+    params, buffers = lo.numpy_init(34, 51, 256, 1, seed=8, randomize_bn=False)
+    sd0 = {**params, **buffers}
+    rs = np.random.RandomState(5)
+    data = {B: (T(rs.normal(0, 1, (B, 34)).astype(np.float32)).cuda(), T(rs.normal(0, 1, (B, 51)).astype(np.float32)).cuda())
+            for B in (256, 100, 64, 32, 48)}
+
+    def fresh():
+        m = pkg.LinearModel(34, 51, linear_size=256, num_stage=1, p_dropout=0.0, BN=True)      # no dropout: the loss depends
+        m.load_state_dict(sd0)                                                                  # on the weights only
+        m = m.cuda()
+        return m, trainer_mod.LifterTrainer(m, lr=1e-2, loss="mse", optimizer="adam", seed=1)
+    m, tr = fresh()
+    first = {B: float(fresh()[1].step(*data[B]).item()) for B in data}            # first-step loss of untouched weights
+    l = [float(tr.step(*data[256]).item()) for _ in range(4)]
+    assert abs(l[0] - first[256]) < 1e-6 * first[256] and l[3] < 0.9 * l[0]       # replay trains
+    m.load_state_dict(sd0)                                                         # weights back: the replay must see them
+    assert abs(float(tr.step(*data[256]).item()) - first[256]) < 1e-5 * first[256]
+    with torch.no_grad():
+        m.w2.bias.add_(0.5)                                                        # in-place edit between replays
+    shifted = float(tr.step(*data[256]).item())
+    assert abs(shifted - first[256]) > 1e-3 * first[256]
+    # batch sizes come and go (a trailing partial batch, then more sizes than stay resident), 256 in between every time
+    for B in (100, 256, 64, 256, 32, 48, 100, 256):
+        m.load_state_dict(sd0)
+        got = float(tr.step(*data[B]).item())
+        assert abs(got - first[B]) < 1e-5 * first[B], (B, got, first[B])
+    assert len(tr._bufs) <= tr.MAX_RESIDENT_BATCH_SIZES and all(k[0] in tr._bufs for k in tr._graphs)

@@ -60,12 +60,12 @@ def test_vit_eval_matches_oracle_after_denormalisation(pkg, golden_dir, B):
     err = (out - ref).abs()
     tol = 0.5e-3 + 1e-2 * ref.abs()                      # north_star: 0.5 mm absolute + 1e-2 relative (metres)
     frac_ok = float((err <= tol).float().mean())
-    # 16-bit storage of every activation through two transformer blocks (~15 rounding points, ~1e-3 of the output
-    # scale in total; these un-trained weights give outputs of several standard deviations): the north_star band holds
-    # for all but a tail of small-valued coordinates, and everything is inside 2 mm + 1e-2 relative.  DESIGN.md section 8.
-    assert frac_ok >= 0.995, f"{100 * (1 - frac_ok):.2f} % of the outputs outside 0.5 mm + 1e-2 relative"
-    loose = 2e-3 + 1e-2 * ref.abs()
-    assert bool((err <= loose).all()), f"max err {err.max().item() * 1e3:.3f} mm; worst err/tol {(err / loose).max().item():.2f}"
+    # The residual stream is fp32 in the eval path (round 2); GEMM operands and weights are 16-bit.  Round 1 kept the stream
+    # in 16 bits too and left ~0.5 % of the coordinates outside the band (all inside 2 mm): the CPU ablation
+    # (scripts/vit_rounding_ablation.py) put the worst error at 0.64 of the tolerance with an fp32 stream.
+    worst = float((err / tol).max())
+    print(f"[B={B}] worst err/tol {worst:.2f}, max err {err.max().item() * 1e3:.3f} mm, in band {100 * frac_ok:.3f} %")
+    assert frac_ok == 1.0, f"{100 * (1 - frac_ok):.3f} % of the outputs outside 0.5 mm + 1e-2 relative (worst err/tol {worst:.2f})"
     assert rel_l2(out - m3, ref - m3) < 3e-3
 
 
