@@ -80,6 +80,11 @@ class Phase5LossDesc(C.Structure):
                                           "d_pred3d", "scratch", "out")]
 
 
+class AdamTable(C.Structure):
+    """``lifter_adam_table_t``"""
+    _fields_ = [("n", C.c_int32), ("p_off", C.c_int64 * 16), ("numel", C.c_int64 * 16), ("op_off", C.c_int64 * 16)]
+
+
 class VitDesc(C.Structure):
     """``lifter_vit_t``: shapes, fp32 parameters and 16-bit GEMM operands of the MyViT lifter."""
     _fields_ = [(k, C.c_int32) for k in ("tokens", "in_dim", "hidden", "heads", "blocks", "mlp_dim", "head_dim", "out_dim",
@@ -154,6 +159,8 @@ SIGNATURES = {
     "lifter_dp_sync_bytes": (_I64, [_CFG, _I32]),
     "lifter_step_advance": (_I32, [_P, _F, _F, _F, _P]),
     "lifter_adam_step_packed": (_I32, [_CFG, _P, _P, _P, _P, _F, _F, _F, _F, _F, _I32, _I32, _F, _P, _P, _I32, _P]),
+    "lifter_adam_step_table": (_I32, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _I32, _F, _P, _P, _I32, C.POINTER(AdamTable), _P]),
+    "lifter_vit_map_grad": (_I32, [_P, _I32, _I32, _P, _P, _P]),
     "lifter_dp_adam_step": (_I32, [_CFG, C.POINTER(DpInfo), _P, _P, _F, _F, _F, _F, _I32, _F, _P, _I32, _P]),
     "lifter_vit_workspace_bytes": (_I64, [C.POINTER(VitDesc), _I64]),
     "lifter_vit_forward": (_I32, [C.POINTER(VitDesc), _P, _I64, _P, _P, _P]),

@@ -835,6 +835,30 @@ int lifter_adam_step_packed(const lifter_config_t* cfg, float* p, const float* g
     return LIFTER_OK;
 }
 
+int lifter_adam_step_table(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                           float eps, float weight_decay, int decoupled, int step, float grad_scale,
+                           const lifter_step_state_t* state, void* operands, int fmt, const lifter_adam_table_t* table,
+                           void* stream) {
+    LIFTER_REQUIRE(p && g && m && v, "adam: null pointer");
+    LIFTER_REQUIRE(fmt == FMT_F16 || fmt == FMT_BF16, "adam: unknown operand format %d", fmt);
+    AdamArgs a;
+    a.p = p; a.g = g; a.m = m; a.v = v; a.n = n; a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
+    a.weight_decay = weight_decay; a.decoupled = decoupled; a.step = step; a.grad_scale = grad_scale;
+    a.dyn = reinterpret_cast<const float*>(state);
+    if (operands != nullptr) {
+        LIFTER_REQUIRE(table != nullptr && table->n >= 1 && table->n <= ADAM_MAX_WEIGHTS, "adam: operand table with 1..%d ranges", ADAM_MAX_WEIGHTS);
+        a.operands = operands; a.op_fmt = fmt; a.nw = table->n;
+        for (int t = 0; t < table->n; ++t) {
+            LIFTER_REQUIRE(table->p_off[t] >= 0 && table->numel[t] > 0 && table->p_off[t] + table->numel[t] <= n &&
+                           table->p_off[t] % 4 == 0 && table->numel[t] % 4 == 0 && table->op_off[t] % 4 == 0 && table->op_off[t] >= 0,
+                           "adam: operand range %d must lie inside the buffer with offsets / length multiples of 4", t);
+            a.w_p_off[t] = table->p_off[t]; a.w_numel[t] = table->numel[t]; a.w_off[t] = table->op_off[t];
+            a.w_in[t] = 1; a.w_pad[t] = 1;                              // dense: same linear offset in both buffers
+        }
+    }
+    return adam_step(a, static_cast<cudaStream_t>(stream));
+}
+
 int lifter_dp_adam_step(const lifter_config_t* cfg, const lifter_dp_t* dp, float* m, float* v, float beta1, float beta2,
                         float eps, float weight_decay, int decoupled, float grad_scale,
                         const lifter_step_state_t* state, int fmt, void* stream) {

@@ -803,6 +803,19 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
 
 lifter::VitDesc lifter_vit_to_desc(const lifter_vit_t* v);        // vit_ops.cu
 
+namespace lifter {
+namespace {
+__global__ void vit_map_grad_kernel(const float* __restrict__ gmap, int in_d, int H, float* __restrict__ dw, float* __restrict__ db) {
+    griddep_launch();
+    griddep_wait();
+    const int h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= H) return;
+    db[h] = gmap[h];
+    for (int i = 0; i < in_d; ++i) dw[h * in_d + i] = gmap[(1 + i) * H + h];
+}
+}  // namespace
+}  // namespace lifter
+
 extern "C" {
 
 int64_t lifter_vit_saved_bytes(const lifter_vit_t* vit, int64_t poses) {
@@ -827,6 +840,13 @@ int lifter_vit_backward(const lifter_vit_t* vit, const float* x, int64_t poses, 
     G.map = g->map; G.ln = g->ln; G.w_qkv = g->w_qkv; G.w_out = g->w_out; G.w_mlp1 = g->w_mlp1; G.mlp_b1 = g->mlp_b1;
     G.w_mlp2 = g->w_mlp2; G.mlp_b2 = g->mlp_b2; G.w_head1 = g->w_head1; G.head_b1 = g->head_b1; G.w_head2 = g->w_head2; G.head_b2 = g->head_b2;
     return lifter::vit_backward(lifter_vit_to_desc(vit), x, poses, saved, dout, scratch, G, dx, static_cast<cudaStream_t>(stream));
+}
+
+int lifter_vit_map_grad(const float* gmap, int in_dim, int hidden, float* d_weight, float* d_bias, void* stream) {
+    LIFTER_REQUIRE(gmap && d_weight && d_bias && in_dim >= 1 && hidden >= 1, "vit_map_grad: bad arguments");
+    LIFTER_CHECK_CUDA(lifter::launch_pdl("vit_map_grad_kernel", lifter::vit_map_grad_kernel, dim3((hidden + 255) / 256), dim3(256), 0,
+                                         static_cast<cudaStream_t>(stream), gmap, in_dim, hidden, d_weight, d_bias));
+    return LIFTER_OK;
 }
 
 }  // extern "C"

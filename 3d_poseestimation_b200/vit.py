@@ -166,7 +166,8 @@ class MyViT(torch.nn.Module):
 
     # ------------------------------------------------------------------------------------------------ packing
     def _pack_key(self):
-        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+        # _param_epoch: bumped by VitTrainer, whose optimiser kernel rewrites the (re-homed) parameters behind autograd's back
+        return (getattr(self, "_param_epoch", 0),) + tuple((p.data_ptr(), p._version) for p in self.parameters())
 
     def _pack(self, dev, fmt=None):
         """fp32 side tables and 16-bit GEMM operands in the layout of ``lifter_vit_t``; rebuilt when a parameter changed."""

@@ -314,6 +314,18 @@ int lifter_adam_step_packed(const lifter_config_t* cfg, float* p, const float* g
                             float beta1, float beta2, float eps, float weight_decay, int decoupled, int step,
                             float grad_scale, const lifter_step_state_t* state, void* operands, int fmt, void* stream);
 
+/* The same fused pass for ANY flat fp32 buffer (the MyViT trainer uses it): Adam / AdamW over p[0 .. n) and, in the same
+ * pass, the 16-bit GEMM operand copies of up to 16 DENSE ranges of it: range t covers p[p_off[t] .. p_off[t] + numel[t])
+ * and is written to operands[op_off[t] ..] (elements; every offset and length a multiple of 4).                    */
+typedef struct lifter_adam_table {
+    int32_t n;                                   /* ranges in use, <= 16                                          */
+    int64_t p_off[16]; int64_t numel[16]; int64_t op_off[16];
+} lifter_adam_table_t;
+int lifter_adam_step_table(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                           float eps, float weight_decay, int decoupled, int step, float grad_scale,
+                           const lifter_step_state_t* state, void* operands, int fmt, const lifter_adam_table_t* table,
+                           void* stream);
+
 /* Data-parallel optimiser step as ONE kernel over NVLink peer memory (replaces gradient all-reduce + Adam): rank r
  * sums slice r of every rank's gradient with P2P loads (rank order: deterministic), runs Adam/AdamW on that slice
  * (m, v: only slice r is touched on rank r) and stores the new parameters and operand copies into every rank's
@@ -386,6 +398,10 @@ int lifter_vit_train_forward(const lifter_vit_t* vit, const float* x, int64_t po
 /* dx: nullable, [poses][tokens][in_dim] fp32 = d loss / d key points (the phase-5 loop feeds the lifter from a 2D model) */
 int lifter_vit_backward(const lifter_vit_t* vit, const float* x, int64_t poses, const void* saved, const float* dout,
                         void* scratch, const lifter_vit_grads_t* grads, float* dx, void* stream);
+
+/* lifter_vit_backward leaves d linear_mapper as [1 + in_dim][hidden] (bias row, then one row per input value); this
+ * re-lays it as the module's parameters: d_weight [hidden][in_dim], d_bias [hidden] (the fused trainer's flat gradient). */
+int lifter_vit_map_grad(const float* gmap, int in_dim, int hidden, float* d_weight, float* d_bias, void* stream);
 
 /* ---- test hook: one tcgen05 GEMM  D[M][N] = sum_k A(m,k) B(n,k) ------------------------------------ */
 typedef struct lifter_gemm_desc {

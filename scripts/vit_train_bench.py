@@ -49,6 +49,13 @@ def timed(fn, reps=20, warm=5):
 
 ms = timed(step)
 ms_noopt = timed(lambda i: step(i, False))
+# the fused trainer: flat parameters, fused MSE, ONE Adam launch that also refreshes the operands, CUDA-graph replay
+VT = importlib.import_module("3d_poseestimation_b200.vit_trainer").VitTrainer
+m2 = pkg.MyViT().cuda().train()
+tr = VT(m2, lr=1e-4)
+ms_fused = timed(lambda i: tr.step(*sets[i % 4]), reps=40, warm=5)
+tr_e = VT(pkg.MyViT().cuda().train(), lr=1e-4, use_graph=False)
+ms_fused_eager = timed(lambda i: tr_e.step(*sets[i % 4]), reps=40, warm=5)
 # CPU oracle on a bounded sample
 from oracle import vit_oracle as V  # noqa: E402
 params = {k: v.detach().cpu().clone().requires_grad_(k != "pos_embed") for k, v in m.state_dict().items()}
@@ -70,12 +77,14 @@ while time.perf_counter() - t0 < 10.0:
     reps += 1
 cpu_s = (time.perf_counter() - t0) / reps
 print(json.dumps({
-    "metric": "lifted poses/sec (MyViT fwd+bwd+Adam)", "value": B / ms * 1e3, "unit": "poses/s", "n_gpus": 1, "ms_per_step": ms,
-    "ms_per_step_without_optimizer": ms_noopt, "higher_is_better": True,
+    "metric": "lifted poses/sec (MyViT fwd+bwd+Adam)", "value": B / ms_fused * 1e3, "unit": "poses/s", "n_gpus": 1,
+    "ms_per_step": ms_fused, "ms_per_step_eager_launches": ms_fused_eager, "gpu_launches": tr.graph_launches(),
+    "autograd_torch_optim": {"value": B / ms * 1e3, "ms_per_step": ms, "ms_per_step_without_optimizer": ms_noopt},
+    "higher_is_better": True,
     "dtype": "bf16 operands / activations / stored gradients, fp32 accumulate, fp32 parameters and parameter gradients",
     "data": "synthetic", "config": {"workload": f"MyViT(chw=(1,17,2), n_blocks=2, hidden_d=256, n_heads=4) training step, {B} poses, MSE, "
-                                                 "torch.optim.Adam over model.parameters()"},
-    "model_flop_per_pose": flop_pose, "model_tflops": B * flop_pose / ms / 1e9,
+                                                 "VitTrainer (flat Adam, fused MSE, CUDA-graph replay), 4 rotating batches; saved activations of a step exceed L2"},
+    "model_flop_per_pose": flop_pose, "model_tflops": B * flop_pose / ms_fused / 1e9,
     "cpu_baseline": {"value": 256 / cpu_s, "unit": "poses/s", "cores": os.cpu_count(), "kind": "port",
                      "sample": "256 poses per step, oracle/vit_oracle.py + autograd + torch.optim.Adam (PyTorch fp32 CPU)"}}))
 step(0)
