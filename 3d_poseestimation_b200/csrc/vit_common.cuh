@@ -5,6 +5,15 @@
 #include "common.cuh"
 
 namespace lifter {
+
+// Ampere-style asynchronous 16-byte copies global -> shared (no register staging): a warp that stages its whole working set
+// issues every copy before waiting once, so one (pose, head) has all its loads in flight instead of one per loop trip.
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
 namespace {
 
 constexpr int VIT_MAX_TOKENS = 32;

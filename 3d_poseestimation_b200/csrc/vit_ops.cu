@@ -185,10 +185,11 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
     const unsigned short* src = static_cast<const unsigned short*>(qkv) + pose * tokens * (3L * Hd) + head * DH;
     for (int i = lane; i < 3 * R * VPR; i += 32) {
         const int vec = i % VPR, rs = i / VPR, slice = rs / R, n = rs - slice * R;
-        uint4 val = make_uint4(0u, 0u, 0u, 0u);
-        if (n < tokens) val = *reinterpret_cast<const uint4*>(src + n * (3L * Hd) + slice * Hd + vec * 8);
-        *reinterpret_cast<uint4*>(sq + (slice * R + n) * LDS + vec * 8) = val;
+        unsigned short* dst = sq + (slice * R + n) * LDS + vec * 8;
+        if (n < tokens) cp_async16(smem_u32(dst), src + n * (3L * Hd) + slice * Hd + vec * 8);
+        else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
     }
+    cp_async_wait_all();
     __syncwarp();
     const uint32_t q_addr = smem_u32(sq), k_addr = q_addr + R * LDS * 2, v_addr = k_addr + R * LDS * 2;
     const int g = lane >> 2, t4 = lane & 3;

@@ -331,10 +331,17 @@ namespace {
 
 // Backward of softmax(q k^T / sqrt d) v for one (pose, head) per warp on mma.sync m16n8k16 (fp32 accumulate), the layout
 // of the forward kernel: q, k, v, dO slices staged with `tokens + 1` rows (every MMA-tile row past the token count aliases
-// the zero row).  Per 16-row query tile: S = q k^T and dP = dO v^T as accumulator fragments, softmax and
-// dS = P (dP - rowsum(dP P)) / sqrt d in fp32 on the fragments, dq = dS k with dS re-used in registers as the A operand;
-// P and dS also go to shared memory as 16-bit [query][key] tiles, from which dk = dS^T q and dv = P^T dO read their A
-// operands TRANSPOSED with ldmatrix.trans.  qkv, dqkv 16-bit [T][3 Hd]; dO 16-bit [T][Hd].
+// the zero row), all copies of a (pose, head) in flight at once (cp.async).  Four phases, each reading shared memory only:
+//   1. per 16-row query tile: S = q k^T and dP = dO v^T as accumulator fragments, softmax and
+//      dS = P (dP - rowsum(dP P)) / sqrt d in fp32 on the fragments; P and dS go to shared memory as 16-bit [query][key]
+//      tiles (again tokens + 1 rows: the tile rows past the token count are the zero row);
+//   2. dv = P^T dO   (A operand = the P tile TRANSPOSED by ldmatrix.trans)  -> staged over the v rows (dead after phase 1);
+//   3. dk = dS^T q   (same, from the dS tile)                               -> staged over the dO rows (dead after phase 2);
+//   4. dq = dS k     (A operand = the dS tile as stored)                    -> staged over the q rows (dead after phase 3);
+// then dq | dk | dv leave with coalesced 16-byte stores.  Round-2 rewrite: the first version issued one global load per
+// loop trip (1.2 TB/s, latency-bound), 3,260 instructions per (pose, head) -- runtime operand-format branches around every
+// MMA / pack, 96 predicated 4-byte global stores -- and held 15.5 KB of shared memory per warp (12 warps per SM).
+// qkv, dqkv 16-bit [T][3 Hd]; dO 16-bit [T][Hd].
 constexpr int ATTB_WARPS = 4;
 constexpr int ATTB_LDP = 40;                           // halfs per row of the P / dS tiles (32 keys + 8: conflict-free ldmatrix)
 
@@ -346,8 +353,9 @@ __device__ __forceinline__ void attb_ldsm_x4_trans(uint32_t (&r)[4], uint32_t ad
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
 }
-__device__ __forceinline__ void attb_mma(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1, int fmt) {
-    if (fmt == FMT_BF16)
+template <int FMT>
+__device__ __forceinline__ void attb_mma(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    if constexpr (FMT == FMT_BF16)
         asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
                      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
     else
@@ -355,13 +363,13 @@ __device__ __forceinline__ void attb_mma(float (&c)[4], const uint32_t (&a)[4], 
                      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-template <int DH>
+template <int DH, int FMT>
 __global__ void __launch_bounds__(ATTB_WARPS * 32) vit_attention_bwd_kernel(const void* __restrict__ qkv, const void* __restrict__ dO,
                                                                             long pose_heads, int tokens, int heads, float scale,
-                                                                            void* __restrict__ dqkv, int fmt) {
+                                                                            void* __restrict__ dqkv) {
     griddep_launch();
     griddep_wait();
-    constexpr int LDS = DH + 8, VPR = DH / 8;
+    constexpr int LDS = DH + 8, VPR = DH / 8, RPP = 32 / VPR;         // RPP: staged rows per warp-wide pass of 16-byte vectors
     extern __shared__ __align__(16) unsigned char attb_smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const long ph = static_cast<long>(blockIdx.x) * ATTB_WARPS + wid;
@@ -370,58 +378,61 @@ __global__ void __launch_bounds__(ATTB_WARPS * 32) vit_attention_bwd_kernel(cons
     const int head = static_cast<int>(ph - pose * heads);
     const int Hd = heads * DH, N = tokens, R = tokens + 1;
     const int MT = (N + 15) / 16, NT = (N + 7) / 8;
-    const size_t per_warp = static_cast<size_t>(4) * R * LDS * 2 + static_cast<size_t>(2) * 32 * ATTB_LDP * 2;
+    const size_t per_warp = (static_cast<size_t>(4) * R * LDS + static_cast<size_t>(2) * R * ATTB_LDP) * 2;
     unsigned short* sq = reinterpret_cast<unsigned short*>(attb_smem + wid * per_warp);
     unsigned short* sP = sq + 4 * R * LDS;
-    unsigned short* sS = sP + 32 * ATTB_LDP;
+    unsigned short* sS = sP + R * ATTB_LDP;
     const unsigned short* src = static_cast<const unsigned short*>(qkv) + pose * N * (3L * Hd) + head * DH;
     const unsigned short* srcdo = static_cast<const unsigned short*>(dO) + pose * N * static_cast<long>(Hd) + head * DH;
-    for (int i = lane; i < 4 * R * VPR; i += 32) {
-        const int vec = i % VPR, rs = i / VPR, slice = rs / R, n = rs - slice * R;
-        uint4 val = make_uint4(0u, 0u, 0u, 0u);
-        if (n < N) val = slice < 3 ? *reinterpret_cast<const uint4*>(src + n * (3L * Hd) + slice * Hd + vec * 8)
-                                   : *reinterpret_cast<const uint4*>(srcdo + n * static_cast<long>(Hd) + vec * 8);
-        *reinterpret_cast<uint4*>(sq + (slice * R + n) * LDS + vec * 8) = val;
+    const int vec = lane % VPR, rsub = lane / VPR;
+#pragma unroll
+    for (int slice = 0; slice < 4; ++slice) {
+        const unsigned short* g0 = slice < 3 ? src + slice * Hd + vec * 8 : srcdo + vec * 8;
+        const long gstride = slice < 3 ? 3L * Hd : static_cast<long>(Hd);
+        for (int n = rsub; n < R; n += RPP) {
+            unsigned short* dst = sq + (slice * R + n) * LDS + vec * 8;
+            if (n < N) cp_async16(smem_u32(dst), g0 + n * gstride);
+            else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+        }
     }
+    if (lane < 2 * (ATTB_LDP / 8)) {                                  // zero rows of the P and dS tiles
+        unsigned short* z = (lane < ATTB_LDP / 8 ? sP : sS) + N * ATTB_LDP + (lane % (ATTB_LDP / 8)) * 8;
+        *reinterpret_cast<uint4*>(z) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    cp_async_wait_all();
     __syncwarp();
     const uint32_t q_addr = smem_u32(sq), k_addr = q_addr + R * LDS * 2, v_addr = k_addr + R * LDS * 2, do_addr = v_addr + R * LDS * 2;
     const uint32_t p_addr = smem_u32(sP), s_addr = smem_u32(sS);
     const int g = lane >> 2, t4 = lane & 3;
     const float scale_log2e = scale * 1.4426950408889634f;
-    unsigned short* out_base = static_cast<unsigned short*>(dqkv) + pose * N * (3L * Hd) + head * DH;
-    auto store_frags = [&](int slice, int row0, const float (&oc)[DH / 8][4]) {      // accumulator tile -> dqkv rows row0 .. + 15
-#pragma unroll
-        for (int dn = 0; dn < DH / 8; ++dn) {
-            if (row0 + g < N)
-                *reinterpret_cast<uint32_t*>(out_base + (row0 + g) * (3L * Hd) + slice * Hd + dn * 8 + t4 * 2) = pack16(oc[dn][0], oc[dn][1], fmt);
-            if (row0 + g + 8 < N)
-                *reinterpret_cast<uint32_t*>(out_base + (row0 + g + 8) * (3L * Hd) + slice * Hd + dn * 8 + t4 * 2) = pack16(oc[dn][2], oc[dn][3], fmt);
-        }
-    };
+    // ldmatrix row selectors of this lane: "a" = A-operand / transposed-B pattern, "b" = B-operand pattern
+    const int row_a = (lane & 7) + ((lane >> 3) & 1) * 8, col_a = (lane >> 4) * 8;
+    const int row_b = (lane & 7) + (lane >> 4) * 8, col_b = ((lane >> 3) & 1) * 8;
+    // ---- phase 1 ------------------------------------------------------------------------------------------------------
     for (int mt = 0; mt < MT; ++mt) {
         float sc[4][4], dp[4][4];
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
             for (int e = 0; e < 4; ++e) sc[nt][e] = dp[nt][e] = 0.0f;
+        const int arow = min(mt * 16 + row_a, N);
 #pragma unroll
         for (int ks = 0; ks < DH / 16; ++ks) {
             uint32_t aq[4], ad[4];
-            const int arow = min(mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, N);
-            attb_ldsm_x4(aq, q_addr + (arow * LDS + ks * 16 + (lane >> 4) * 8) * 2);
-            attb_ldsm_x4(ad, do_addr + (arow * LDS + ks * 16 + (lane >> 4) * 8) * 2);
+            attb_ldsm_x4(aq, q_addr + (arow * LDS + ks * 16 + col_a) * 2);
+            attb_ldsm_x4(ad, do_addr + (arow * LDS + ks * 16 + col_a) * 2);
 #pragma unroll
             for (int np = 0; np < 2; ++np) {
                 if (np * 2 < NT) {
                     uint32_t bk[4], bv[4];
-                    const int brow = min(np * 16 + (lane & 7) + (lane >> 4) * 8, N);
-                    attb_ldsm_x4(bk, k_addr + (brow * LDS + ks * 16 + ((lane >> 3) & 1) * 8) * 2);
-                    attb_ldsm_x4(bv, v_addr + (brow * LDS + ks * 16 + ((lane >> 3) & 1) * 8) * 2);
-                    attb_mma(sc[np * 2], aq, bk[0], bk[1], fmt);
-                    attb_mma(dp[np * 2], ad, bv[0], bv[1], fmt);
+                    const int brow = min(np * 16 + row_b, N);
+                    attb_ldsm_x4(bk, k_addr + (brow * LDS + ks * 16 + col_b) * 2);
+                    attb_ldsm_x4(bv, v_addr + (brow * LDS + ks * 16 + col_b) * 2);
+                    attb_mma<FMT>(sc[np * 2], aq, bk[0], bk[1]);
+                    attb_mma<FMT>(dp[np * 2], ad, bv[0], bv[1]);
                     if (np * 2 + 1 < NT) {
-                        attb_mma(sc[np * 2 + 1], aq, bk[2], bk[3], fmt);
-                        attb_mma(dp[np * 2 + 1], ad, bv[2], bv[3], fmt);
+                        attb_mma<FMT>(sc[np * 2 + 1], aq, bk[2], bk[3]);
+                        attb_mma<FMT>(dp[np * 2 + 1], ad, bv[2], bv[3]);
                     }
                 }
             }
@@ -452,7 +463,7 @@ __global__ void __launch_bounds__(ATTB_WARPS * 32) vit_attention_bwd_kernel(cons
         for (int h = 0; h < 2; ++h) {
             den[h] += __shfl_xor_sync(0xffffffffu, den[h], 1);
             den[h] += __shfl_xor_sync(0xffffffffu, den[h], 2);
-            den[h] = (mt * 16 + g + h * 8 < N) ? 1.0f / den[h] : 0.0f;          // query rows past the token count: P = 0
+            den[h] = 1.0f / den[h];
         }
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt)
@@ -466,71 +477,126 @@ __global__ void __launch_bounds__(ATTB_WARPS * 32) vit_attention_bwd_kernel(cons
             D[h] += __shfl_xor_sync(0xffffffffu, D[h], 1);
             D[h] += __shfl_xor_sync(0xffffffffu, D[h], 2);
         }
+        const int r0 = mt * 16 + g, r1 = r0 + 8;                                  // query rows past the token count stay the zero row
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
 #pragma unroll
             for (int e = 0; e < 4; ++e) dp[nt][e] = sc[nt][e] * (dp[nt][e] - D[e >> 1]) * scale;      // dS
             const int col = nt * 8 + t4 * 2;
-            *reinterpret_cast<uint32_t*>(sP + (mt * 16 + g) * ATTB_LDP + col) = pack16(sc[nt][0], sc[nt][1], fmt);
-            *reinterpret_cast<uint32_t*>(sP + (mt * 16 + g + 8) * ATTB_LDP + col) = pack16(sc[nt][2], sc[nt][3], fmt);
-            *reinterpret_cast<uint32_t*>(sS + (mt * 16 + g) * ATTB_LDP + col) = pack16(dp[nt][0], dp[nt][1], fmt);
-            *reinterpret_cast<uint32_t*>(sS + (mt * 16 + g + 8) * ATTB_LDP + col) = pack16(dp[nt][2], dp[nt][3], fmt);
+            if (r0 < N) {
+                *reinterpret_cast<uint32_t*>(sP + r0 * ATTB_LDP + col) = pack16(sc[nt][0], sc[nt][1], FMT);
+                *reinterpret_cast<uint32_t*>(sS + r0 * ATTB_LDP + col) = pack16(dp[nt][0], dp[nt][1], FMT);
+            }
+            if (r1 < N) {
+                *reinterpret_cast<uint32_t*>(sP + r1 * ATTB_LDP + col) = pack16(sc[nt][2], sc[nt][3], FMT);
+                *reinterpret_cast<uint32_t*>(sS + r1 * ATTB_LDP + col) = pack16(dp[nt][2], dp[nt][3], FMT);
+            }
         }
-        // dq = dS k
+    }
+    __syncwarp();
+    auto stage = [&](unsigned short* region, int row0, const float (&oc)[DH / 8][4]) {     // accumulator tile -> staged rows
+        const int r0 = row0 + g, r1 = r0 + 8;
+#pragma unroll
+        for (int dn = 0; dn < DH / 8; ++dn) {
+            if (r0 < N) *reinterpret_cast<uint32_t*>(region + r0 * LDS + dn * 8 + t4 * 2) = pack16(oc[dn][0], oc[dn][1], FMT);
+            if (r1 < N) *reinterpret_cast<uint32_t*>(region + r1 * LDS + dn * 8 + t4 * 2) = pack16(oc[dn][2], oc[dn][3], FMT);
+        }
+    };
+    // ---- phases 2 and 3: dv = P^T dO over the v rows, then dk = dS^T q over the dO rows ---------------------------------------
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+        const uint32_t a_base = which == 0 ? p_addr : s_addr;
+        const uint32_t b_base = which == 0 ? do_addr : q_addr;
+        unsigned short* region = which == 0 ? sq + 2 * R * LDS : sq + 3 * R * LDS;
+        float oc[2][DH / 8][4];                                                  // both key tiles at once: one load of the B
+#pragma unroll                                                                   // fragments (q / dO columns) serves both
+        for (int jt = 0; jt < 2; ++jt)
+#pragma unroll
+            for (int dn = 0; dn < DH / 8; ++dn)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) oc[jt][dn][e] = 0.0f;
+        for (int it = 0; it < MT; ++it) {                                        // queries it * 16 .. + 15
+            const int qrow_a = min(it * 16 + (lane & 7) + ((lane >> 4) & 1) * 8, N);
+            const int qrow_b = min(it * 16 + row_a, N);
+            uint32_t b[DH / 16][4];
+#pragma unroll
+            for (int dq = 0; dq < DH / 16; ++dq) attb_ldsm_x4_trans(b[dq], b_base + (qrow_b * LDS + dq * 16 + col_a) * 2);
+#pragma unroll
+            for (int jt = 0; jt < 2; ++jt) {
+                if (jt < MT) {
+                    uint32_t a[4];                                               // A = (tile stored [query][key])^T
+                    attb_ldsm_x4_trans(a, a_base + (qrow_a * ATTB_LDP + jt * 16 + ((lane >> 3) & 1) * 8) * 2);
+#pragma unroll
+                    for (int dq = 0; dq < DH / 16; ++dq) {
+                        attb_mma<FMT>(oc[jt][dq * 2], a, b[dq][0], b[dq][1]);
+                        attb_mma<FMT>(oc[jt][dq * 2 + 1], a, b[dq][2], b[dq][3]);
+                    }
+                }
+            }
+        }
+        __syncwarp();                                                            // every lane is done reading the region's old rows
+#pragma unroll
+        for (int jt = 0; jt < 2; ++jt)
+            if (jt < MT) stage(region, jt * 16, oc[jt]);
+    }
+    // ---- phase 4: dq = dS k over the q rows ----------------------------------------------------------------------------------
+    for (int mt = 0; mt < MT; ++mt) {
         float oc[DH / 8][4];
 #pragma unroll
         for (int dn = 0; dn < DH / 8; ++dn)
 #pragma unroll
             for (int e = 0; e < 4; ++e) oc[dn][e] = 0.0f;
+        const int arow = min(mt * 16 + row_a, N);
 #pragma unroll
         for (int kt = 0; kt < 2; ++kt) {
             if (kt * 2 < NT) {
                 uint32_t pa[4];
-                pa[0] = pack16(dp[kt * 2][0], dp[kt * 2][1], fmt);
-                pa[1] = pack16(dp[kt * 2][2], dp[kt * 2][3], fmt);
-                pa[2] = pack16(dp[kt * 2 + 1][0], dp[kt * 2 + 1][1], fmt);
-                pa[3] = pack16(dp[kt * 2 + 1][2], dp[kt * 2 + 1][3], fmt);
+                attb_ldsm_x4(pa, s_addr + (arow * ATTB_LDP + kt * 16 + col_a) * 2);
+                const int krow = min(kt * 16 + row_a, N);
 #pragma unroll
                 for (int dq = 0; dq < DH / 16; ++dq) {
                     uint32_t bk[4];
-                    attb_ldsm_x4_trans(bk, k_addr + (min(kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, N) * LDS + dq * 16 + (lane >> 4) * 8) * 2);
-                    attb_mma(oc[dq * 2], pa, bk[0], bk[1], fmt);
-                    attb_mma(oc[dq * 2 + 1], pa, bk[2], bk[3], fmt);
+                    attb_ldsm_x4_trans(bk, k_addr + (krow * LDS + dq * 16 + col_a) * 2);
+                    attb_mma<FMT>(oc[dq * 2], pa, bk[0], bk[1]);
+                    attb_mma<FMT>(oc[dq * 2 + 1], pa, bk[2], bk[3]);
                 }
             }
         }
-        store_frags(0, mt * 16, oc);
+        stage(sq, mt * 16, oc);                                                  // q: last read in phase 3
     }
     __syncwarp();
-    // dk = dS^T q, dv = P^T dO: key rows jt * 16 .. + 15, contraction over the queries
-    for (int jt = 0; jt < MT; ++jt) {
+    unsigned short* out_base = static_cast<unsigned short*>(dqkv) + pose * N * (3L * Hd) + head * DH + vec * 8;
 #pragma unroll
-        for (int which = 0; which < 2; ++which) {
-            const uint32_t a_base = which == 0 ? s_addr : p_addr;
-            const uint32_t b_base = which == 0 ? q_addr : do_addr;
-            float oc[DH / 8][4];
-#pragma unroll
-            for (int dn = 0; dn < DH / 8; ++dn)
-#pragma unroll
-                for (int e = 0; e < 4; ++e) oc[dn][e] = 0.0f;
-            for (int it = 0; it < MT; ++it) {                                   // queries it * 16 .. + 15
-                uint32_t a[4];                                                   // A = (tile stored [query][key])^T
-                attb_ldsm_x4_trans(a, a_base + ((it * 16 + (lane & 7) + ((lane >> 4) & 1) * 8) * ATTB_LDP + jt * 16 + ((lane >> 3) & 1) * 8) * 2);
-#pragma unroll
-                for (int dq = 0; dq < DH / 16; ++dq) {
-                    uint32_t b[4];
-                    attb_ldsm_x4_trans(b, b_base + (min(it * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, N) * LDS + dq * 16 + (lane >> 4) * 8) * 2);
-                    attb_mma(oc[dq * 2], a, b[0], b[1], fmt);
-                    attb_mma(oc[dq * 2 + 1], a, b[2], b[3], fmt);
-                }
-            }
-            store_frags(which == 0 ? 1 : 2, jt * 16, oc);
-        }
+    for (int slice = 0; slice < 3; ++slice) {                                    // dq <- q rows, dk <- dO rows, dv <- v rows
+        const unsigned short* region = sq + (slice == 0 ? 0 : slice == 1 ? 3 : 2) * R * LDS + vec * 8;
+        for (int n = rsub; n < N; n += RPP)
+            *reinterpret_cast<uint4*>(out_base + n * (3L * Hd) + slice * Hd) = *reinterpret_cast<const uint4*>(region + n * LDS);
     }
 }
 
 size_t attb_smem_bytes(int tokens, int dh) {
-    return static_cast<size_t>(ATTB_WARPS) * (static_cast<size_t>(4) * (tokens + 1) * (dh + 8) * 2 + static_cast<size_t>(2) * 32 * ATTB_LDP * 2);
+    return static_cast<size_t>(ATTB_WARPS) * (static_cast<size_t>(4) * (tokens + 1) * (dh + 8) + static_cast<size_t>(2) * (tokens + 1) * ATTB_LDP) * 2;
+}
+
+template <int DH, int FMT>
+int attention_bwd_launch(const void* qkv, const void* dO, long pose_heads, int tokens, int heads, float scale, void* dqkv, size_t smem,
+                         cudaStream_t st) {
+    static PerDeviceOnce once;
+    bool* configured = once.slot();
+    if (!*configured) {
+        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_bwd_kernel<DH, FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        *configured = true;
+    }
+    LIFTER_CHECK_CUDA(launch_pdl("vit_attention_bwd_kernel", vit_attention_bwd_kernel<DH, FMT>, dim3(static_cast<unsigned>((pose_heads + ATTB_WARPS - 1) / ATTB_WARPS)),
+                                 dim3(ATTB_WARPS * 32), smem, st, qkv, dO, pose_heads, tokens, heads, scale, dqkv));
+    return LIFTER_OK;
+}
+int attention_bwd(const void* qkv, const void* dO, long pose_heads, int tokens, int heads, int dh, float scale, void* dqkv, int fmt,
+                  size_t smem, cudaStream_t st) {
+    if (dh == 64) return fmt == FMT_BF16 ? attention_bwd_launch<64, FMT_BF16>(qkv, dO, pose_heads, tokens, heads, scale, dqkv, smem, st)
+                                         : attention_bwd_launch<64, FMT_F16>(qkv, dO, pose_heads, tokens, heads, scale, dqkv, smem, st);
+    return fmt == FMT_BF16 ? attention_bwd_launch<32, FMT_BF16>(qkv, dO, pose_heads, tokens, heads, scale, dqkv, smem, st)
+                           : attention_bwd_launch<32, FMT_F16>(qkv, dO, pose_heads, tokens, heads, scale, dqkv, smem, st);
 }
 
 }  // namespace
@@ -572,7 +638,7 @@ long slab_floats(int M_out, int N_in, int K) {
 
 struct BwdScratch {
     unsigned short *dout16, *dr, *dhA, *dhB, *du, *dO, *dm, *dqkv;
-    float *slabs, *part;
+    float *slabs, *part, *part_side;      // part_side: column-sum partials of the weight-gradient stream
     size_t bytes;
 };
 
@@ -603,6 +669,7 @@ BwdScratch bwd_scratch(const VitDesc& d, int64_t poses, void* base) {
     const long po = static_cast<long>(ew_partial_rows(T, 64)) * 64;
     part = po > part ? po : part;
     s.part = reinterpret_cast<float*>(take(part * 4));
+    s.part_side = reinterpret_cast<float*>(take(cs * 4));
     s.bytes = static_cast<size_t>(p - static_cast<char*>(base));
     return s;
 }
@@ -648,6 +715,38 @@ int dgrad16(const unsigned short* dZ, int M_out, const void* W, int N_in, int T,
     if (residual != nullptr) { g.residual = residual; g.ldr = N_in; }
     g.tag = "vit_dgrad";
     return gemm_launch(g, st);
+}
+
+// Nothing on the data-gradient chain reads a parameter gradient, so the weight-gradient GEMMs (tensor pipe) and the bias
+// column sums run on a second stream beside the attention / LayerNorm / GELU backward kernels (FP32 pipe, HBM) of the chain.
+// One library-owned stream and a few timing-disabled events per device, created on first use and kept until the process
+// exits (the ownership exception include/lifter_b200.h documents); forks from and joins back into the caller's stream with
+// events, so the call stays ordered on `st` and is legal under stream capture.  LIFTER_VIT_WGRAD_STREAM=0: one stream.
+struct VitSide {
+    cudaStream_t st = nullptr;
+    cudaEvent_t fork = nullptr, dhA = nullptr, dm = nullptr, dhB = nullptr, dqkv = nullptr, join = nullptr;
+};
+VitSide* vit_side() {
+    static VitSide per_device[64];
+    const char* e = getenv("LIFTER_VIT_WGRAD_STREAM");
+    if (e != nullptr && e[0] == '0') return nullptr;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    VitSide* s = &per_device[dev];
+    if (s->st == nullptr) {
+        if (cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess) { s->st = nullptr; return nullptr; }
+        cudaEvent_t* ev[6] = {&s->fork, &s->dhA, &s->dm, &s->dhB, &s->dqkv, &s->join};
+        for (cudaEvent_t* x : ev)
+            if (cudaEventCreateWithFlags(x, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    }
+    return s;
+}
+// everything enqueued on `from` so far happens before whatever is enqueued on `to` next
+int order_after(cudaEvent_t ev, cudaStream_t from, cudaStream_t to) {
+    if (from == to) return LIFTER_OK;
+    LIFTER_CHECK_CUDA(cudaEventRecord(ev, from));
+    LIFTER_CHECK_CUDA(cudaStreamWaitEvent(to, ev, 0));
+    return LIFTER_OK;
 }
 
 int validate_train(const VitDesc& d) {
@@ -737,22 +836,35 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
     const int Ti = static_cast<int>(T);
     const unsigned short* S = static_cast<const unsigned short*>(saved);
     const unsigned row_blocks = static_cast<unsigned>(part_rows(T));
+    VitSide* side = vit_side();
+    cudaStream_t ws = side != nullptr ? side->st : st;                 // weight-gradient stream
+    auto fork = [&]() -> int { return side != nullptr ? order_after(side->fork, st, ws) : LIFTER_OK; };
+    auto side_done = [&](cudaEvent_t VitSide::*ev) -> int {            // the side stream is done reading a dZ buffer
+        if (side != nullptr) LIFTER_CHECK_CUDA(cudaEventRecord(side->*ev, ws));
+        return LIFTER_OK;
+    };
+    auto wait_side = [&](cudaEvent_t VitSide::*ev) -> int {            // ... before the chain overwrites it
+        if (side != nullptr) LIFTER_CHECK_CUDA(cudaStreamWaitEvent(st, side->*ev, 0));
+        return LIFTER_OK;
+    };
     // ---- head -------------------------------------------------------------------------------------------------------------
     LIFTER_PROPAGATE(prep_grad_out(dout, T, d.out_dim, 64, fmt, B.dout16, B.part, st));
     LIFTER_PROPAGATE(reduce_rows_f32(B.part, ew_partial_rows(T, 64), d.out_dim, 64, G.head_b2, st));
-    LIFTER_PROPAGATE(wgrad16(B.dout16, 64, S + L.r, Hh, Ti, d.out_dim, B.slabs, G.w_head2, fmt, st));
+    LIFTER_PROPAGATE(fork());
+    LIFTER_PROPAGATE(wgrad16(B.dout16, 64, S + L.r, Hh, Ti, d.out_dim, B.slabs, G.w_head2, fmt, ws));
     LIFTER_PROPAGATE(dgrad16(B.dout16, 64, d.w_head2, Hh, Ti, B.dr, nullptr, fmt, st));
     LIFTER_PROPAGATE(pointwise(S + L.r, B.dr, B.dr, T * Hh, 2, fmt, st));
-    LIFTER_PROPAGATE(colsum16(B.dr, T, Hh, B.part, G.head_b1, fmt, st));
-    LIFTER_PROPAGATE(wgrad16(B.dr, Hh, S + L.hlast(), H, Ti, Hh, B.slabs, G.w_head1, fmt, st));
+    LIFTER_PROPAGATE(fork());
+    LIFTER_PROPAGATE(colsum16(B.dr, T, Hh, B.part_side, G.head_b1, fmt, ws));
+    LIFTER_PROPAGATE(wgrad16(B.dr, Hh, S + L.hlast(), H, Ti, Hh, B.slabs, G.w_head1, fmt, ws));
     LIFTER_PROPAGATE(dgrad16(B.dr, Hh, d.w_head1, H, Ti, B.dhA, nullptr, fmt, st));
     // ---- blocks, last to first; dhA holds d loss / d (block output) -------------------------------------------------------------
     const size_t smem = attb_smem_bytes(d.tokens, dh);
-    if (dh == 64) LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_bwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    else          LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    LIFTER_REQUIRE(d.tokens <= 32, "vit_backward: at most 32 tokens per pose");
     const long pose_heads = poses * d.heads;
     const float att_scale = 1.0f / sqrtf(static_cast<float>(dh));
     for (int b = d.blocks - 1; b >= 0; --b) {
+        const bool first = b == d.blocks - 1;
         const float* ln = d.ln + static_cast<long>(b) * 6 * H;
         float* gln = G.ln + static_cast<long>(b) * 6 * H;
         const char* wqkv = static_cast<const char*>(d.w_qkv) + static_cast<long>(b) * 3 * H * H * 2;
@@ -760,31 +872,36 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
         const char* w1 = static_cast<const char*>(d.w_mlp1) + static_cast<long>(b) * Mm * H * 2;
         const char* w2 = static_cast<const char*>(d.w_mlp2) + static_cast<long>(b) * H * Mm * 2;
         // MLP: hout = h1 + W2 GELU(W1 LN2(h1) + b1) + b2
-        LIFTER_PROPAGATE(colsum16(B.dhA, T, H, B.part, G.mlp_b2 + static_cast<long>(b) * H, fmt, st));
-        LIFTER_PROPAGATE(wgrad16(B.dhA, H, S + L.m(b), Mm, Ti, H, B.slabs, G.w_mlp2 + static_cast<long>(b) * H * Mm, fmt, st));
+        LIFTER_PROPAGATE(fork());
+        LIFTER_PROPAGATE(colsum16(B.dhA, T, H, B.part_side, G.mlp_b2 + static_cast<long>(b) * H, fmt, ws));
+        LIFTER_PROPAGATE(wgrad16(B.dhA, H, S + L.m(b), Mm, Ti, H, B.slabs, G.w_mlp2 + static_cast<long>(b) * H * Mm, fmt, ws));
+        LIFTER_PROPAGATE(side_done(&VitSide::dhA));
+        if (!first) LIFTER_PROPAGATE(wait_side(&VitSide::dm));
         LIFTER_PROPAGATE(dgrad16(B.dhA, H, w2, Mm, Ti, B.dm, nullptr, fmt, st));
         LIFTER_PROPAGATE(pointwise(S + L.z1(b), B.dm, B.dm, T * Mm, 1, fmt, st));
-        LIFTER_PROPAGATE(colsum16(B.dm, T, Mm, B.part, G.mlp_b1 + static_cast<long>(b) * Mm, fmt, st));
-        LIFTER_PROPAGATE(wgrad16(B.dm, Mm, S + L.u2(b), H, Ti, Mm, B.slabs, G.w_mlp1 + static_cast<long>(b) * Mm * H, fmt, st));
+        LIFTER_PROPAGATE(fork());
+        LIFTER_PROPAGATE(colsum16(B.dm, T, Mm, B.part_side, G.mlp_b1 + static_cast<long>(b) * Mm, fmt, ws));
+        LIFTER_PROPAGATE(wgrad16(B.dm, Mm, S + L.u2(b), H, Ti, Mm, B.slabs, G.w_mlp1 + static_cast<long>(b) * Mm * H, fmt, ws));
+        LIFTER_PROPAGATE(side_done(&VitSide::dm));
         LIFTER_PROPAGATE(dgrad16(B.dm, Mm, w1, H, Ti, B.du, nullptr, fmt, st));
+        if (!first) LIFTER_PROPAGATE(wait_side(&VitSide::dhB));
         VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_ln_bwd_kernel", vit_ln_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
                                                          static_cast<const void*>(S + L.h1(b)), static_cast<const void*>(B.du), static_cast<const void*>(B.dhA), T,
                                                          ln + 4 * H, ln + 5 * H, static_cast<const float*>(nullptr), static_cast<const float*>(nullptr), d.ln_eps,
                                                          static_cast<void*>(B.dhB), B.part, fmt)));
         LIFTER_PROPAGATE(reduce_rows_f32(B.part, static_cast<int>(row_blocks), 2 * H, 4 * H, gln + 4 * H, st));
         // attention: h1 = hin + Wout attn(Wqkv LN(LN(hin)))
-        LIFTER_PROPAGATE(wgrad16(B.dhB, H, S + L.o(b), H, Ti, H, B.slabs, G.w_out + static_cast<long>(b) * H * H, fmt, st));
+        LIFTER_PROPAGATE(fork());
+        LIFTER_PROPAGATE(wgrad16(B.dhB, H, S + L.o(b), H, Ti, H, B.slabs, G.w_out + static_cast<long>(b) * H * H, fmt, ws));
+        LIFTER_PROPAGATE(side_done(&VitSide::dhB));
         LIFTER_PROPAGATE(dgrad16(B.dhB, H, wout, H, Ti, B.dO, nullptr, fmt, st));
-        if (dh == 64)
-            LIFTER_CHECK_CUDA(launch_pdl("vit_attention_bwd_kernel", vit_attention_bwd_kernel<64>, dim3(static_cast<unsigned>((pose_heads + ATTB_WARPS - 1) / ATTB_WARPS)),
-                                         dim3(ATTB_WARPS * 32), smem, st, static_cast<const void*>(S + L.qkv(b)), static_cast<const void*>(B.dO), pose_heads, d.tokens,
-                                         d.heads, att_scale, static_cast<void*>(B.dqkv), fmt));
-        else
-            LIFTER_CHECK_CUDA(launch_pdl("vit_attention_bwd_kernel", vit_attention_bwd_kernel<32>, dim3(static_cast<unsigned>((pose_heads + ATTB_WARPS - 1) / ATTB_WARPS)),
-                                         dim3(ATTB_WARPS * 32), smem, st, static_cast<const void*>(S + L.qkv(b)), static_cast<const void*>(B.dO), pose_heads, d.tokens,
-                                         d.heads, att_scale, static_cast<void*>(B.dqkv), fmt));
-        LIFTER_PROPAGATE(wgrad16(B.dqkv, 3 * H, S + L.u1(b), H, Ti, 3 * H, B.slabs, G.w_qkv + static_cast<long>(b) * 3 * H * H, fmt, st));
+        if (!first) LIFTER_PROPAGATE(wait_side(&VitSide::dqkv));
+        LIFTER_PROPAGATE(attention_bwd(S + L.qkv(b), B.dO, pose_heads, d.tokens, d.heads, dh, att_scale, B.dqkv, fmt, smem, st));
+        LIFTER_PROPAGATE(fork());
+        LIFTER_PROPAGATE(wgrad16(B.dqkv, 3 * H, S + L.u1(b), H, Ti, 3 * H, B.slabs, G.w_qkv + static_cast<long>(b) * 3 * H * H, fmt, ws));
+        LIFTER_PROPAGATE(side_done(&VitSide::dqkv));
         LIFTER_PROPAGATE(dgrad16(B.dqkv, 3 * H, wqkv, H, Ti, B.du, nullptr, fmt, st));
+        LIFTER_PROPAGATE(wait_side(&VitSide::dhA));                  // this block's mlp_b2 / w_mlp2 tasks have read dhA
         VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_ln_bwd_kernel", vit_ln_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
                                                          static_cast<const void*>(S + L.hin(b)), static_cast<const void*>(B.du), static_cast<const void*>(B.dhB), T,
                                                          ln, ln + H, ln + 2 * H, ln + 3 * H, d.ln_eps, static_cast<void*>(B.dhA), B.part, fmt)));
@@ -793,7 +910,8 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
     // ---- embedding: d linear_mapper (positional table has requires_grad = False, baselineModel.py:330) -------------------------------
     VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_bwd_kernel", vit_embed_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
                                                      static_cast<const void*>(B.dhA), x, T, d.in_dim, B.part, d.map_w, dx, fmt)));
-    return reduce_rows_f32(B.part, static_cast<int>(row_blocks), (1 + d.in_dim) * H, (1 + d.in_dim) * H, G.map, st);
+    LIFTER_PROPAGATE(reduce_rows_f32(B.part, static_cast<int>(row_blocks), (1 + d.in_dim) * H, (1 + d.in_dim) * H, G.map, st));
+    return side != nullptr ? order_after(side->join, ws, st) : LIFTER_OK;       // the call is complete on `st`
 }
 
 }  // namespace lifter

@@ -56,6 +56,10 @@ tr = VT(m2, lr=1e-4)
 ms_fused = timed(lambda i: tr.step(*sets[i % 4]), reps=40, warm=5)
 tr_e = VT(pkg.MyViT().cuda().train(), lr=1e-4, use_graph=False)
 ms_fused_eager = timed(lambda i: tr_e.step(*sets[i % 4]), reps=40, warm=5)
+os.environ["LIFTER_VIT_WGRAD_STREAM"] = "0"          # A/B: weight gradients on the chain's own stream (read at capture)
+tr_1 = VT(pkg.MyViT().cuda().train(), lr=1e-4)
+ms_fused_one_stream = timed(lambda i: tr_1.step(*sets[i % 4]), reps=40, warm=5)
+del os.environ["LIFTER_VIT_WGRAD_STREAM"]
 # CPU oracle on a bounded sample
 from oracle import vit_oracle as V  # noqa: E402
 params = {k: v.detach().cpu().clone().requires_grad_(k != "pos_embed") for k, v in m.state_dict().items()}
@@ -78,7 +82,7 @@ while time.perf_counter() - t0 < 10.0:
 cpu_s = (time.perf_counter() - t0) / reps
 print(json.dumps({
     "metric": "lifted poses/sec (MyViT fwd+bwd+Adam)", "value": B / ms_fused * 1e3, "unit": "poses/s", "n_gpus": 1,
-    "ms_per_step": ms_fused, "ms_per_step_eager_launches": ms_fused_eager, "gpu_launches": tr.graph_launches(),
+    "ms_per_step": ms_fused, "ms_per_step_eager_launches": ms_fused_eager, "ms_per_step_one_stream": ms_fused_one_stream, "gpu_launches": tr.graph_launches(),
     "autograd_torch_optim": {"value": B / ms * 1e3, "ms_per_step": ms, "ms_per_step_without_optimizer": ms_noopt},
     "higher_is_better": True,
     "dtype": "bf16 operands / activations / stored gradients, fp32 accumulate, fp32 parameters and parameter gradients",
@@ -89,6 +93,7 @@ print(json.dumps({
                      "sample": "256 poses per step, oracle/vit_oracle.py + autograd + torch.optim.Adam (PyTorch fp32 CPU)"}}))
 step(0)
 torch.cuda.synchronize()
+os.environ["LIFTER_VIT_WGRAD_STREAM"] = "0"        # the split serialises launches anyway: keep them on one stream
 cabi.check(cabi.lib().lifter_trace_begin(cabi.stream_ptr()))
 step(1, False)
 buf = C.create_string_buffer(1 << 17)
