@@ -154,8 +154,9 @@ __device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
 }
-__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1, int fmt) {
-    if (fmt == FMT_BF16)
+template <int FMT>
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    if constexpr (FMT == FMT_BF16)
         asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
                      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
     else
@@ -163,10 +164,11 @@ __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], 
                      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-template <int DH>
+template <int DH, int FMT>
 __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const void* __restrict__ qkv, long pose_heads,
                                                                        int tokens, int heads, float scale_log2e,
-                                                                       void* __restrict__ o, int fmt) {
+                                                                       void* __restrict__ o) {
+    constexpr int fmt = FMT;
     griddep_launch();
     griddep_wait();
     constexpr int LDS = DH + 8;                        // halfs per staged row: 16-byte aligned, conflict-free for ldmatrix
@@ -183,12 +185,15 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
                                                        // memory per warp = more resident warps for a latency-bound kernel)
     unsigned short* sq = reinterpret_cast<unsigned short*>(att_smem) + static_cast<size_t>(wid) * (3 * R * LDS);
     const unsigned short* src = static_cast<const unsigned short*>(qkv) + pose * tokens * (3L * Hd) + head * DH;
-    for (int i = lane; i < 3 * R * VPR; i += 32) {
-        const int vec = i % VPR, rs = i / VPR, slice = rs / R, n = rs - slice * R;
-        unsigned short* dst = sq + (slice * R + n) * LDS + vec * 8;
-        if (n < tokens) cp_async16(smem_u32(dst), src + n * (3L * Hd) + slice * Hd + vec * 8);
-        else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
-    }
+    constexpr int RPP = 32 / VPR;                      // staged rows per warp-wide pass of 16-byte vectors
+    const int vec = lane % VPR, rsub = lane / VPR;
+#pragma unroll
+    for (int slice = 0; slice < 3; ++slice)
+        for (int n = rsub; n < R; n += RPP) {
+            unsigned short* dst = sq + (slice * R + n) * LDS + vec * 8;
+            if (n < tokens) cp_async16(smem_u32(dst), src + n * (3L * Hd) + slice * Hd + vec * 8);
+            else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+        }
     cp_async_wait_all();
     __syncwarp();
     const uint32_t q_addr = smem_u32(sq), k_addr = q_addr + R * LDS * 2, v_addr = k_addr + R * LDS * 2;
@@ -209,8 +214,8 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
                 if (np * 2 < NT) {
                     uint32_t bk[4];                    // [0], [1]: tile 2 np (k lo, k hi); [2], [3]: tile 2 np + 1
                     ldsm_x4(bk, k_addr + (min(np * 16 + (lane & 7) + (lane >> 4) * 8, tokens) * LDS + ks * 16 + ((lane >> 3) & 1) * 8) * 2);
-                    mma16816(sc[np * 2], a, bk[0], bk[1], fmt);
-                    if (np * 2 + 1 < NT) mma16816(sc[np * 2 + 1], a, bk[2], bk[3], fmt);
+                    mma16816<FMT>(sc[np * 2], a, bk[0], bk[1]);
+                    if (np * 2 + 1 < NT) mma16816<FMT>(sc[np * 2 + 1], a, bk[2], bk[3]);
                 }
             }
         }
@@ -261,8 +266,8 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
                 for (int dp = 0; dp < DH / 16; ++dp) {                 // value column tiles 2 dp, 2 dp + 1
                     uint32_t bv[4];
                     ldsm_x4_trans(bv, v_addr + (min(kt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8, tokens) * LDS + dp * 16 + (lane >> 4) * 8) * 2);
-                    mma16816(oc[dp * 2], pa, bv[0], bv[1], fmt);
-                    mma16816(oc[dp * 2 + 1], pa, bv[2], bv[3], fmt);
+                    mma16816<FMT>(oc[dp * 2], pa, bv[0], bv[1]);
+                    mma16816<FMT>(oc[dp * 2 + 1], pa, bv[2], bv[3]);
                 }
             }
         }
@@ -278,10 +283,8 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) vit_attention_kernel(const voi
     }
     __syncwarp();
     unsigned short* dst = static_cast<unsigned short*>(o) + pose * tokens * static_cast<long>(Hd) + head * DH;
-    for (int i = lane; i < tokens * VPR; i += 32) {
-        const int vec = i % VPR, n = i / VPR;
+    for (int n = rsub; n < tokens; n += RPP)
         *reinterpret_cast<uint4*>(dst + n * static_cast<long>(Hd) + vec * 8) = *reinterpret_cast<const uint4*>(sq + n * LDS + vec * 8);
-    }
 }
 
 size_t att_smem_bytes(int tokens, int dh) {
@@ -338,18 +341,28 @@ static int vit_layernorm32(const float* in, long T, const float* g1, const float
     return LIFTER_OK;
 }
 
+template <int DH, int FMT>
+static int attention_launch(const void* qkv, long pose_heads, int tokens, int heads, float scale_log2e, void* o, size_t smem, cudaStream_t st) {
+    static PerDeviceOnce once;
+    bool* configured = once.slot();
+    if (!*configured) {
+        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<DH, FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+        *configured = true;
+    }
+    const dim3 grid(static_cast<unsigned>((pose_heads + ATT_WARPS - 1) / ATT_WARPS));
+    LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<DH, FMT>, grid, dim3(ATT_WARPS * 32), smem, st, qkv, pose_heads, tokens,
+                                 heads, scale_log2e, o));
+    return LIFTER_OK;
+}
+
 int vit_attention(const void* qkv, long pose_heads, int tokens, int heads, int dh, void* o, int fmt, cudaStream_t st) {
     const size_t smem = att_smem_bytes(tokens, dh);
+    LIFTER_REQUIRE(smem <= 64 * 1024, "vit_attention: %d tokens of width %d need %zu bytes of shared memory per block", tokens, dh, smem);
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(dh));
-    const dim3 grid(static_cast<unsigned>((pose_heads + ATT_WARPS - 1) / ATT_WARPS));
-    if (dh == 64) {
-        if (smem > 48 * 1024) LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<64>, grid, dim3(ATT_WARPS * 32), smem, st, qkv, pose_heads, tokens, heads, scale_log2e, o, fmt));
-    } else {
-        if (smem > 48 * 1024) LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<32>, grid, dim3(ATT_WARPS * 32), smem, st, qkv, pose_heads, tokens, heads, scale_log2e, o, fmt));
-    }
-    return LIFTER_OK;
+    if (dh == 64) return fmt == FMT_BF16 ? attention_launch<64, FMT_BF16>(qkv, pose_heads, tokens, heads, scale_log2e, o, smem, st)
+                                         : attention_launch<64, FMT_F16>(qkv, pose_heads, tokens, heads, scale_log2e, o, smem, st);
+    return fmt == FMT_BF16 ? attention_launch<32, FMT_BF16>(qkv, pose_heads, tokens, heads, scale_log2e, o, smem, st)
+                           : attention_launch<32, FMT_F16>(qkv, pose_heads, tokens, heads, scale_log2e, o, smem, st);
 }
 
 // Workspace per token, in 16-bit units: the residual stream h0, h1 in FP32 (2 x 2 hidden), then 16-bit u, o (hidden
@@ -398,12 +411,6 @@ int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace
                                                              d.ln_eps, static_cast<void*>(u), d.fmt, h0)));
         }
     }
-    const size_t smem = att_smem_bytes(d.tokens, dh);
-    if (smem > 48 * 1024) {                         // static would do below 48 KB; cheap enough to set every call
-        if (dh == 64) LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-        else          LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_attention_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    }
-    const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(dh));
     const long pose_heads = poses * d.heads;
     const size_t esz = 2;
     for (int b = 0; b < d.blocks; ++b) {
@@ -418,12 +425,7 @@ int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace
         g.A = u; g.lda = H; g.B = wqkv; g.ldb = H; g.M = M; g.N = 3 * H; g.K = H; g.fmt = d.fmt;
         g.out_mode = OUT_16_TMA; g.D = qkv; g.ldd = 3 * H; g.tag = "vit_qkv";
         LIFTER_PROPAGATE(gemm_launch(g, st));
-        if (dh == 64)
-            LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<64>, dim3(static_cast<unsigned>((pose_heads + ATT_WARPS - 1) / ATT_WARPS)),
-                                         dim3(ATT_WARPS * 32), smem, st, static_cast<const void*>(qkv), pose_heads, d.tokens, d.heads, scale_log2e, static_cast<void*>(o), d.fmt));
-        else
-            LIFTER_CHECK_CUDA(launch_pdl("vit_attention_kernel", vit_attention_kernel<32>, dim3(static_cast<unsigned>((pose_heads + ATT_WARPS - 1) / ATT_WARPS)),
-                                         dim3(ATT_WARPS * 32), smem, st, static_cast<const void*>(qkv), pose_heads, d.tokens, d.heads, scale_log2e, static_cast<void*>(o), d.fmt));
+        LIFTER_PROPAGATE(vit_attention(qkv, pose_heads, d.tokens, d.heads, dh, o, d.fmt, st));
         GemmArgs go;                                                            // h1 = h0 + o Wout^T  (fp32 in, fp32 out)   :254, 303
         go.A = o; go.lda = H; go.B = wout; go.ldb = H; go.M = M; go.N = H; go.K = H; go.fmt = d.fmt;
         go.out_mode = OUT_32_TMA; go.D = h1; go.ldd = H; go.residual32 = h0; go.ldr32 = H; go.tag = "vit_attn_out";

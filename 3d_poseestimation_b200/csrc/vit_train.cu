@@ -176,39 +176,52 @@ __device__ __forceinline__ void ln_bwd_row(float (&dy)[NV][8], const float (&xh)
         for (int e = 0; e < 8; ++e) dy[v][e] = rstd * (dy[v][e] - c1 - xh[v][e] * c2);
 }
 
-// dx_out = dres + d/dx [ LN2(LN1(x)) ] . dy   (g2 == nullptr: one LayerNorm; dres nullable).
+// dx_out = dres + d/dx [ LN2(LN1(x)) ] . dy   (TWO == false: one LayerNorm; dres nullable).
 // part [gridDim.x][4][Hd]: block partials of d gain1, d bias1, d gain2, d bias2.
-template <int NV>
-__global__ void __launch_bounds__(256) vit_ln_bwd_kernel(const void* __restrict__ x, const void* __restrict__ dy_in,
-                                                         const void* __restrict__ dres, long T, const float* __restrict__ g1,
-                                                         const float* __restrict__ b1, const float* __restrict__ g2,
-                                                         const float* __restrict__ b2, float eps, void* __restrict__ dx_out,
-                                                         float* __restrict__ part, int fmt) {
+// Each warp owns `rows_per_warp` consecutive token rows and keeps the raw 16-bit rows of the next LNB_DEPTH rows in flight
+// in a private shared-memory ring (cp.async; lane l copies and later reads the same 16 bytes, so the ring needs no
+// barrier).  Round 2: the first version prefetched ONE row ahead in registers -- 24 KB in flight per SM, 3.4 TB/s, 128
+// registers -- and paid the 4-array block reduction once per 64 rows; the grid is now two blocks per SM.
+template <int NV> struct LnbCfg { static constexpr int DEPTH = NV <= 2 ? 4 : 2, SMEM = 8 * DEPTH * 3 * NV * 512; };
+
+template <int DEPTH_M1>
+__device__ __forceinline__ void cp_async_wait_group() {
+    asm volatile("cp.async.wait_group %0;" :: "n"(DEPTH_M1) : "memory");
+}
+
+template <int NV, bool TWO>
+__global__ void __launch_bounds__(256, NV == 1 ? 2 : 1) vit_ln_bwd_kernel(const void* __restrict__ x, const void* __restrict__ dy_in,
+                                                            const void* __restrict__ dres, long T, long rows_per_warp,
+                                                            const float* __restrict__ g1, const float* __restrict__ b1,
+                                                            const float* __restrict__ g2, const float* __restrict__ b2, float eps,
+                                                            void* __restrict__ dx_out, float* __restrict__ part, int fmt) {
     griddep_launch();
     griddep_wait();
-    __shared__ float sh[8 * NV * 256];
-    constexpr int Hd = NV * 256;
-    const int lane = threadIdx.x & 31;
-    const long t0 = (static_cast<long>(blockIdx.x) * 8 + (threadIdx.x >> 5)) * VIT_RPW;
-    const long t1 = min(T, t0 + VIT_RPW);
-    RowParams<NV> p1, p2;
-    load_row_params<NV>(p1, g1, b1, lane);
-    if (g2 != nullptr) load_row_params<NV>(p2, g2, b2, lane);
-    float dg1[NV][8], db1[NV][8], dg2[NV][8], db2[NV][8];
+    extern __shared__ __align__(16) unsigned char lnb_smem[];
+    constexpr int Hd = NV * 256, DEPTH = LnbCfg<NV>::DEPTH, ROWB = NV * 512;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long t0 = min(T, (static_cast<long>(blockIdx.x) * 8 + wid) * rows_per_warp);
+    const long t1 = min(T, t0 + rows_per_warp);
+    unsigned char* ring = lnb_smem + wid * (DEPTH * 3 * ROWB) + lane * 16;
+    const uint32_t ring_addr = smem_u32(ring);
+    const char* srcs[3] = {static_cast<const char*>(x), static_cast<const char*>(dy_in), static_cast<const char*>(dres)};
+    auto issue = [&](long row, int slot) {                            // the three raw rows of `row` -> ring slot
+        if (row < t1) {
 #pragma unroll
-    for (int v = 0; v < NV; ++v)
+            for (int a = 0; a < 3; ++a) {
+                if (a == 2 && dres == nullptr) break;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) dg1[v][e] = db1[v][e] = dg2[v][e] = db2[v][e] = 0.0f;
-    // raw rows of the NEXT iteration are in flight while this one is processed (the kernel is latency-bound otherwise)
-    auto load_raw = [&](const void* base, long row, uint4 (&r)[NV]) {
-        const uint4* src = reinterpret_cast<const uint4*>(static_cast<const unsigned short*>(base) + row * Hd);
-#pragma unroll
-        for (int v = 0; v < NV; ++v) r[v] = src[v * 32 + lane];
+                for (int v = 0; v < NV; ++v)
+                    cp_async16(ring_addr + (slot * 3 + a) * ROWB + v * 512, srcs[a] + row * (Hd * 2L) + v * 512 + lane * 16);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");            // one group per row, empty past the end: uniform counting
     };
-    auto unpack_raw = [&](const uint4 (&r)[NV], float (&f)[NV][8]) {
+    auto read_raw = [&](int slot, int a, float (&f)[NV][8]) {
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
-            const uint32_t wd[4] = {r[v].x, r[v].y, r[v].z, r[v].w};
+            const uint4 r = *reinterpret_cast<const uint4*>(ring + (slot * 3 + a) * ROWB + v * 512);
+            const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
                 const float2 p = unpack16(wd[e], fmt);
@@ -217,28 +230,36 @@ __global__ void __launch_bounds__(256) vit_ln_bwd_kernel(const void* __restrict_
             }
         }
     };
-    uint4 cx[NV], cd[NV], cr[NV], nx[NV], nd[NV], nr[NV];
-    if (t0 < t1) {
-        load_raw(x, t0, cx);
-        load_raw(dy_in, t0, cd);
-        if (dres != nullptr) load_raw(dres, t0, cr);
-    }
+#pragma unroll
+    for (int k = 0; k < DEPTH; ++k) issue(t0 + k, k);
+    RowParams<NV> p1, p2;
+    load_row_params<NV>(p1, g1, b1, lane);
+    if constexpr (TWO) load_row_params<NV>(p2, g2, b2, lane);
+    float dg1[NV][8], db1[NV][8], dg2[TWO ? NV : 1][8], db2[TWO ? NV : 1][8];
+#pragma unroll
+    for (int v = 0; v < NV; ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dg1[v][e] = db1[v][e] = 0.0f;
+#pragma unroll
+    for (int v = 0; v < (TWO ? NV : 1); ++v)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dg2[v][e] = db2[v][e] = 0.0f;
+    int slot = 0;
     for (long t = t0; t < t1; ++t) {
-        if (t + 1 < t1) {
-            load_raw(x, t + 1, nx);
-            load_raw(dy_in, t + 1, nd);
-            if (dres != nullptr) load_raw(dres, t + 1, nr);
-        }
-        float xh1[NV][8], d[NV][8];
-        unpack_raw(cx, xh1);
-        unpack_raw(cd, d);
+        cp_async_wait_group<DEPTH - 1>();                              // the group of row t has landed
+        float xh1[NV][8], d[NV][8], r[NV][8];
+        read_raw(slot, 0, xh1);
+        read_raw(slot, 1, d);
+        if (dres != nullptr) read_raw(slot, 2, r);
+        issue(t + DEPTH, slot);                                        // the slot's values are in registers: refill it
+        slot = slot + 1 == DEPTH ? 0 : slot + 1;
         float mean, rstd1;
         ln_stats<NV>(xh1, mean, rstd1, eps);
 #pragma unroll
         for (int v = 0; v < NV; ++v)
 #pragma unroll
             for (int e = 0; e < 8; ++e) xh1[v][e] = (xh1[v][e] - mean) * rstd1;
-        if (g2 != nullptr) {
+        if constexpr (TWO) {
             float xh2[NV][8];
 #pragma unroll
             for (int v = 0; v < NV; ++v)
@@ -254,22 +275,22 @@ __global__ void __launch_bounds__(256) vit_ln_bwd_kernel(const void* __restrict_
         }
         ln_bwd_row<NV>(d, xh1, p1.g, rstd1, dg1, db1);
         if (dres != nullptr) {
-            float r[NV][8];
-            unpack_raw(cr, r);
 #pragma unroll
             for (int v = 0; v < NV; ++v)
 #pragma unroll
                 for (int e = 0; e < 8; ++e) d[v][e] += r[v][e];
         }
         store_row16<NV>(dx_out, t, lane, d, fmt);
-#pragma unroll
-        for (int v = 0; v < NV; ++v) { cx[v] = nx[v]; cd[v] = nd[v]; cr[v] = nr[v]; }
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    float* sh = reinterpret_cast<float*>(lnb_smem);                    // the ring is dead: block reduction scratch [8][Hd]
     float* dst = part + static_cast<long>(blockIdx.x) * 4 * Hd;
     block_colsum_store<NV>(dg1, sh, dst);
     block_colsum_store<NV>(db1, sh, dst + Hd);
-    block_colsum_store<NV>(dg2, sh, dst + 2 * Hd);
-    block_colsum_store<NV>(db2, sh, dst + 3 * Hd);
+    if constexpr (TWO) {
+        block_colsum_store<NV>(dg2, sh, dst + 2 * Hd);
+        block_colsum_store<NV>(db2, sh, dst + 3 * Hd);
+    }
 }
 
 // d linear_mapper: part [gridDim.x][1 + in_d][Hd]: block partials of sum_t dh[t][c] (bias) and sum_t dh[t][c] x[t][i]
@@ -749,6 +770,32 @@ int order_after(cudaEvent_t ev, cudaStream_t from, cudaStream_t to) {
     return LIFTER_OK;
 }
 
+// LayerNorm backward over T rows; returns the number of partial rows it wrote to `part` (each [4][H]) in *blocks
+template <int NV, bool TWO>
+int ln_bwd_launch(const void* x, const void* dy, const void* dres, long T, const float* g1, const float* b1, const float* g2, const float* b2,
+                  float eps, void* dx_out, float* part, int max_blocks, int fmt, int* blocks, cudaStream_t st) {
+    static PerDeviceOnce once;
+    bool* configured = once.slot();
+    if (!*configured) {
+        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_ln_bwd_kernel<NV, TWO>, cudaFuncAttributeMaxDynamicSharedMemorySize, LnbCfg<NV>::SMEM));
+        *configured = true;
+    }
+    int grid = 2 * num_sms();
+    if (grid > max_blocks) grid = max_blocks;
+    const long rows_per_warp = (T + grid * 8L - 1) / (grid * 8L);
+    grid = static_cast<int>((T + rows_per_warp * 8 - 1) / (rows_per_warp * 8));
+    *blocks = grid;
+    LIFTER_CHECK_CUDA(launch_pdl("vit_ln_bwd_kernel", vit_ln_bwd_kernel<NV, TWO>, dim3(grid), dim3(256), static_cast<size_t>(LnbCfg<NV>::SMEM), st,
+                                 x, dy, dres, T, rows_per_warp, g1, b1, g2, b2, eps, dx_out, part, fmt));
+    return LIFTER_OK;
+}
+int ln_bwd(int nv, const void* x, const void* dy, const void* dres, long T, const float* g1, const float* b1, const float* g2, const float* b2,
+           float eps, void* dx_out, float* part, int max_blocks, int fmt, int* blocks, cudaStream_t st) {
+    if (g2 != nullptr) { VIT_DISPATCH_NV(nv, return (ln_bwd_launch<NV, true>(x, dy, dres, T, g1, b1, g2, b2, eps, dx_out, part, max_blocks, fmt, blocks, st))); }
+    else               { VIT_DISPATCH_NV(nv, return (ln_bwd_launch<NV, false>(x, dy, dres, T, g1, b1, g2, b2, eps, dx_out, part, max_blocks, fmt, blocks, st))); }
+    return LIFTER_OK;
+}
+
 int validate_train(const VitDesc& d) {
     LIFTER_PROPAGATE(vit_validate(d));
     LIFTER_REQUIRE(d.mlp_dim <= 2048 && 3 * d.hidden <= 2048, "vit training: hidden width %d unsupported (256 or 512)", d.hidden);
@@ -885,11 +932,10 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
         LIFTER_PROPAGATE(side_done(&VitSide::dm));
         LIFTER_PROPAGATE(dgrad16(B.dm, Mm, w1, H, Ti, B.du, nullptr, fmt, st));
         if (!first) LIFTER_PROPAGATE(wait_side(&VitSide::dhB));
-        VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_ln_bwd_kernel", vit_ln_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
-                                                         static_cast<const void*>(S + L.h1(b)), static_cast<const void*>(B.du), static_cast<const void*>(B.dhA), T,
-                                                         ln + 4 * H, ln + 5 * H, static_cast<const float*>(nullptr), static_cast<const float*>(nullptr), d.ln_eps,
-                                                         static_cast<void*>(B.dhB), B.part, fmt)));
-        LIFTER_PROPAGATE(reduce_rows_f32(B.part, static_cast<int>(row_blocks), 2 * H, 4 * H, gln + 4 * H, st));
+        int lnb = 0;
+        LIFTER_PROPAGATE(ln_bwd(nv, S + L.h1(b), B.du, B.dhA, T, ln + 4 * H, ln + 5 * H, nullptr, nullptr, d.ln_eps, B.dhB, B.part,
+                                static_cast<int>(row_blocks), fmt, &lnb, st));
+        LIFTER_PROPAGATE(reduce_rows_f32(B.part, lnb, 2 * H, 4 * H, gln + 4 * H, st));
         // attention: h1 = hin + Wout attn(Wqkv LN(LN(hin)))
         LIFTER_PROPAGATE(fork());
         LIFTER_PROPAGATE(wgrad16(B.dhB, H, S + L.o(b), H, Ti, H, B.slabs, G.w_out + static_cast<long>(b) * H * H, fmt, ws));
@@ -902,10 +948,9 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
         LIFTER_PROPAGATE(side_done(&VitSide::dqkv));
         LIFTER_PROPAGATE(dgrad16(B.dqkv, 3 * H, wqkv, H, Ti, B.du, nullptr, fmt, st));
         LIFTER_PROPAGATE(wait_side(&VitSide::dhA));                  // this block's mlp_b2 / w_mlp2 tasks have read dhA
-        VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_ln_bwd_kernel", vit_ln_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
-                                                         static_cast<const void*>(S + L.hin(b)), static_cast<const void*>(B.du), static_cast<const void*>(B.dhB), T,
-                                                         ln, ln + H, ln + 2 * H, ln + 3 * H, d.ln_eps, static_cast<void*>(B.dhA), B.part, fmt)));
-        LIFTER_PROPAGATE(reduce_rows_f32(B.part, static_cast<int>(row_blocks), 4 * H, 4 * H, gln, st));
+        LIFTER_PROPAGATE(ln_bwd(nv, S + L.hin(b), B.du, B.dhB, T, ln, ln + H, ln + 2 * H, ln + 3 * H, d.ln_eps, B.dhA, B.part,
+                                static_cast<int>(row_blocks), fmt, &lnb, st));
+        LIFTER_PROPAGATE(reduce_rows_f32(B.part, lnb, 4 * H, 4 * H, gln, st));
     }
     // ---- embedding: d linear_mapper (positional table has requires_grad = False, baselineModel.py:330) -------------------------------
     VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_bwd_kernel", vit_embed_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,

@@ -246,6 +246,24 @@ class VitTrainer:
         self.model._param_epoch = getattr(self.model, "_param_epoch", 0) + 1
         return self.loss_out[0]
 
+    def run_epoch(self, batches):
+        """The epoch loop of ``train_1.py:73-100`` over HOST batches ``(x, y)`` (fp32 CPU tensors, pinned for the upload to
+        be asynchronous): per step an H2D copy of the batch, the step, and the loss into pinned host memory; ONE wait at the
+        end (the reference blocks on ``loss.cpu().item()`` every step, train_1.py:98).  Returns the losses (CPU tensor)."""
+        batches = list(batches)
+        if not batches:
+            return torch.empty(0)
+        out = torch.empty(len(batches), dtype=torch.float32).pin_memory()
+        with torch.cuda.device(self.device):
+            for i, (x, y) in enumerate(batches):
+                if x.is_cuda or y.is_cuda:
+                    raise RuntimeError("run_epoch takes host batches; call step() with device tensors")
+                xd = x.to(self.device, non_blocking=True)
+                yd = y.to(self.device, non_blocking=True)
+                out[i:i + 1].copy_(self.step(xd, yd).reshape(1), non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+        return out.clone()
+
     def _sync_state(self):
         self.state[1] = self.step_count
         self.state.view(torch.float32)[2] = self.lr

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the B200-native lifter hot path (contract: see the task statement / DESIGN.md §7).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload train|eval|wide|phase5] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload train|eval|wide|phase5|vit|vit_eval] [--impl ours|reference]
 
 The default workload is BASELINE.json's metric, "lifted poses/sec (fwd+bwd)": the data-parallel training step of
 configs[2] (8,192 poses per GPU); with one GPU the line also carries an ``inference`` object with the eval-mode
@@ -54,7 +54,14 @@ H36M_INTRINSICS = [(1145.0494384765625, 1143.7811279296875, 512.54150390625, 515
                    (1149.6756591796875, 1147.5916748046875, 508.8486328125, 508.0649108886719),
                    (1149.1407470703125, 1148.7989501953125, 519.8158569335938, 501.40264892578125),
                    (1145.5113525390625, 1144.77392578125, 514.9682006835938, 501.88201904296875)]
-WORKLOADS = {"eval": "configs[1]", "train": "configs[2]", "phase5": "configs[3]", "wide": "configs[4]"}
+WORKLOADS = {"eval": "configs[1]", "train": "configs[2]", "phase5": "configs[3]", "wide": "configs[4]",
+             "vit": "SURVEY 8 f1 (MyViT training)", "vit_eval": "SURVEY 8 f1 (MyViT eval)"}
+# MyViT(chw=(1, 17, 2), n_blocks=2, hidden_d=256, n_heads=4, out_d=3), baselineModel.py:307-362: multiply-adds x 2 per pose
+VIT_H, VIT_N, VIT_NB = 256, 17, 2
+FLOP_PER_POSE_VIT_INFER = 2 * VIT_N * (2 * VIT_H + VIT_NB * (VIT_H * 3 * VIT_H + VIT_H * VIT_H + 2 * VIT_H * 4 * VIT_H)
+                                       + VIT_H * (VIT_H // 2) + (VIT_H // 2) * 3) + VIT_NB * 4 * VIT_N * VIT_N * VIT_H
+FLOP_PER_POSE_VIT_TRAIN = 3 * FLOP_PER_POSE_VIT_INFER      # dgrad + wgrad ~ 2 x forward (no data gradient into the 2-wide input)
+VIT_EVAL_CHUNK = 16384                   # poses per pass of the eval kernel sequence (scripts/vit_bench.py sweep)
 
 
 def peaks():
@@ -118,6 +125,12 @@ def synth_batch(batch, seed):
     xn = ((x - m2) / s2).reshape(batch, 34).contiguous()
     yn = torch.randn(batch, 51, generator=g)                       # target in normalised units: N(0,1) by construction
     return xn, yn
+
+
+def synth_vit(batch, seed):
+    """Key points (B, 17, 2) and targets (B, 17, 3) for the MyViT lifter: the H36M-shaped rows of synth_batch, per joint."""
+    x, y = synth_batch(batch, seed)
+    return x.reshape(batch, VIT_N, 2).contiguous(), y.reshape(batch, VIT_N, 3).contiguous()
 
 
 def synth_wide(batch, seed):
@@ -193,10 +206,34 @@ def cpu_arm(workload, steps, warmup, budget_s=25.0, with_c1=True):
     rm, rl, info = ref
     i_dim, h, s = WIDE if workload == "wide" else (I_DIM, H, S)
     torch.manual_seed(1)
-    model = rm.LinearModel(i_dim=i_dim, o_dim=O_DIM, p_dropout=0.5, linear_size=h, num_stage=s, BN=True)
+    if workload in ("vit", "vit_eval"):
+        model = rm.MyViT(chw=(1, VIT_N, 2), n_blocks=VIT_NB, hidden_d=VIT_H, n_heads=4, out_d=3)
+    else:
+        model = rm.LinearModel(i_dim=i_dim, o_dim=O_DIM, p_dropout=0.5, linear_size=h, num_stage=s, BN=True)
     out = {"unit": "poses/s", "cores": cores, "threads": torch.get_num_threads(), "kind": "reference",
            "reference_files": info, "torch": torch.__version__}
-    if workload == "eval":
+    if workload in ("vit", "vit_eval"):
+        # a BOUNDED sample: the full 8,192 / 65,536-pose step of the transformer takes minutes per step on the host cores
+        batch = 1024 if workload == "vit" else 4096
+        x, y = synth_vit(batch, 0)
+        if workload == "vit_eval":
+            model.eval()
+
+            def step():
+                with torch.no_grad():
+                    model(x)
+            sample = f"{batch} of the poses per step: the imported MyViT, eval forward under no_grad"
+        else:
+            model.train()
+            opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+            loss_fn = torch.nn.MSELoss(reduction="mean")
+
+            def step():
+                opt.zero_grad()
+                loss_fn(model(x), y).backward()
+                opt.step()
+            sample = f"{batch} of the poses per step: the imported MyViT, fwd + MSELoss + backward + Adam.step (train_1.py:73-100)"
+    elif workload == "eval":
         batch = EVAL_BATCH
         x, _ = synth_batch(batch, 0)
         model.eval()
@@ -267,6 +304,26 @@ def cpu_arm_port(workload, steps, warmup, budget_s=25.0):
     from oracle import adam_oracle, lifter_oracle as lo
     from oracle.philox import dropout_keep_mask
     cores = os.cpu_count() or 1
+    if workload in ("vit", "vit_eval"):
+        from oracle import vit_oracle as V
+        torch.set_num_threads(cores)
+        batch = 1024 if workload == "vit" else 4096
+        x, y = synth_vit(batch, 0)
+        prm = {k: v.clone().requires_grad_(workload == "vit" and k != "pos_embed") for k, v in V.numpy_init(1).items()}
+        if workload == "vit":
+            opt = torch.optim.Adam([v for v in prm.values() if v.requires_grad], lr=1e-4)
+
+            def step():
+                opt.zero_grad()
+                torch.nn.functional.mse_loss(V.vit_forward(prm, x), y).backward()
+                opt.step()
+        else:
+            def step():
+                with torch.no_grad():
+                    V.vit_forward(prm, x)
+        ms, n = _time_cpu(step, steps, min(warmup, 2), budget_s)
+        return {"value": batch / (ms / 1e3), "unit": "poses/s", "cores": cores, "kind": "port", "ms_per_step": ms, "steps_timed": n,
+                "batch": batch, "sample": f"{batch} of the poses per step, oracle/vit_oracle.py (PyTorch fp32 CPU)"}
     i_dim, h, s = WIDE if workload == "wide" else (I_DIM, H, S)
     params, buffers = lo.numpy_init(i_dim, O_DIM, h, s, seed=1, randomize_bn=False)
     if workload == "eval":
@@ -327,11 +384,15 @@ def gpu_arm(args, rank, world, local_rank):
 
     def build_model(workload):
         torch.manual_seed(1)
+        if workload in ("vit", "vit_eval"):
+            return pkg.MyViT(chw=(1, VIT_N, 2), n_blocks=VIT_NB, hidden_d=VIT_H, n_heads=4, out_d=3).to(dev)
         if workload == "wide":
             return pkg.LinearModel(WIDE[0], O_DIM, linear_size=WIDE[1], num_stage=WIDE[2], p_dropout=0.5, BN=True).to(dev)
         return pkg.LinearModel(I_DIM, O_DIM, linear_size=H, num_stage=S, p_dropout=0.5, BN=True).to(dev)
 
     def build_trainer(workload, model, lr=1e-4, dp=True):
+        if workload == "vit":             # no exchange step: N GPUs run N independent replicas of the step
+            return importlib.import_module(PKG + ".vit_trainer").VitTrainer(model.train(), lr=lr, optimizer="adam")
         kw = dict(world_size=world, rank=rank, require_symmetric=True) if (dp and world > 1) else {}
         if workload == "phase5":
             import numpy as np
@@ -346,6 +407,8 @@ def gpu_arm(args, rank, world, local_rank):
         return trainer_mod.LifterTrainer(model, lr=lr, loss="mse", optimizer="adam", seed=2, **kw)
 
     def host_batch(workload, batch, seed):
+        if workload in ("vit", "vit_eval"):
+            return synth_vit(batch, seed)
         if workload == "phase5":
             return synth_phase5(batch, seed)
         return synth_wide(batch, seed) if workload == "wide" else synth_batch(batch, seed)
@@ -354,7 +417,31 @@ def gpu_arm(args, rank, world, local_rank):
         """One workload on this rank's GPU: device-resident throughput, end-to-end throughput, dominant kernel."""
         model = build_model(workload)
         tr = None
-        if workload == "eval":
+        if workload == "vit_eval":
+            batch = EVAL_BATCH
+            model.eval()
+            model.chunk_poses = VIT_EVAL_CHUNK
+            xh = synth_vit(batch, rank)[0].pin_memory()
+            xd = xh.to(dev)
+            xs = torch.empty_like(xd)
+            outh = torch.empty(batch, VIT_N, 3).pin_memory()
+
+            def step():
+                model.infer(xd)
+
+            def run_e2e(n):                                  # host key points in, host predictions out, every step
+                for _ in range(n):
+                    xs.copy_(xh, non_blocking=True)
+                    outh.copy_(model.infer(xs), non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+            h2d, d2h = xh.numel() * 4, outh.numel() * 4
+            dtype = "fp16 GEMM operands, fp32 residual stream / accumulate / LayerNorm / softmax"
+            cfg = {"workload": f"SURVEY 8 f1: MyViT(chw=(1,17,2), n_blocks=2, hidden_d=256, n_heads=4) eval forward, batch {batch} "
+                               f"synthetic H36M 2D poses per GPU, {VIT_EVAL_CHUNK} poses per pass of the kernel sequence",
+                   "batch_per_gpu": batch, "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
+                   "l2": "one pass streams > 1 GB of activations (> 126 MB L2); no flush needed"}
+            flop = FLOP_PER_POSE_VIT_INFER
+        elif workload == "eval":
             batch = EVAL_BATCH
             model.eval()
             xh, _ = synth_batch(batch, rank)
@@ -392,7 +479,9 @@ def gpu_arm(args, rank, world, local_rank):
             h2d, d2h = sum(t.numel() * t.element_size() for t in host), 4
             dtype = "bf16 operands, fp32 accumulate/master weights"
             par = f"dp{world}"
-            if world > 1:
+            if workload == "vit":
+                par = f"replicas x{world} (no exchange step built for the transformer lifter)" if world > 1 else "single GPU"
+            elif world > 1:
                 par += " (in-kernel SyncBN exchange + fused reduce-scatter/Adam/all-gather over NVLink symmetric memory)"
             what = {"train": "training step fwd + MSE + bwd + Adam, dropout 0.5, batch {b}/GPU, synced BatchNorm, 1024-wide, "
                              "2 residual blocks",
@@ -401,12 +490,17 @@ def gpu_arm(args, rank, world, local_rank):
                     "phase5": "phase-5 loop body around the lifter (backup_june8.py:120-175), {b} poses/GPU: 4 train-mode lifter "
                               "forwards (predicted / ground-truth 2D, each with its flipped twin), flip averaging, TriangleLoss "
                               "+ pinhole-reprojection and bone-length terms (parity unpinned) on synthetic H36M intrinsics, "
-                              "backward into the lifter and the predicted 2D / 3D inputs, AdamW"}[workload].format(b=batch)
+                              "backward into the lifter and the predicted 2D / 3D inputs, AdamW",
+                    "vit": "MyViT(chw=(1,17,2), n_blocks=2, hidden_d=256, n_heads=4) training step fwd + MSE + bwd + Adam, {b} "
+                           "poses/GPU, VitTrainer (flat parameters, one optimiser launch, CUDA-graph replay)"}[workload].format(b=batch)
             cfg = {"workload": f"{WORKLOADS[workload]}: {what}", "batch_per_gpu": batch, "global_batch": batch * world,
                    "parallelism": par, "cuda_graph": bool(tr.use_graph),
                    "l2": "one step touches >= 0.4 GB of saved activations and gradients per GPU (> 126 MB L2), so "
                          "consecutive steps do not find their inputs in L2; no explicit flush"}
-            flop = {"train": FLOP_PER_POSE_TRAIN, "wide": FLOP_PER_POSE_WIDE_TRAIN, "phase5": FLOP_PER_POSE_PHASE5}[workload]
+            flop = {"train": FLOP_PER_POSE_TRAIN, "wide": FLOP_PER_POSE_WIDE_TRAIN, "phase5": FLOP_PER_POSE_PHASE5,
+                    "vit": FLOP_PER_POSE_VIT_TRAIN}[workload]
+            if workload == "vit":
+                dtype = "bf16 operands / activations / stored gradients, fp32 accumulate, fp32 parameters and parameter gradients"
 
         def timed(fn, steps, warmup):
             for _ in range(warmup):
@@ -459,11 +553,20 @@ def gpu_arm(args, rank, world, local_rank):
 
         roof = None
         if rank == 0:   # dominant kernel alone: the H x H tcgen05 GEMM at this workload's per-launch shape
-            roof = gemm_roofline(cabi, dev, batch, cabi.FMT_F16 if workload == "eval" else cabi.FMT_BF16, pk,
-                                 WIDE[1] if workload == "wide" else H, profiling)
-        launches = tr.graph_launches() if tr is not None else model.infer_launches(batch)
+            if workload in ("vit", "vit_eval"):
+                roof = vit_gemm_roofline(cabi, dev, (VIT_EVAL_CHUNK if workload == "vit_eval" else batch) * VIT_N,
+                                         cabi.FMT_F16 if workload == "vit_eval" else cabi.FMT_BF16, pk)
+            else:
+                roof = gemm_roofline(cabi, dev, batch, cabi.FMT_F16 if workload == "eval" else cabi.FMT_BF16, pk,
+                                     WIDE[1] if workload == "wide" else H, profiling)
+        if workload == "vit_eval":
+            n0 = cabi.lib().lifter_launch_count()
+            model.infer(xd)
+            launches = int(cabi.lib().lifter_launch_count() - n0)
+        else:
+            launches = tr.graph_launches() if tr is not None else model.infer_launches(batch)
         value = batch * world / (ms / 1e3)
-        return {"metric": "lifted poses/sec" + (" (eval inference)" if workload == "eval" else " (fwd+bwd+Adam)"),
+        return {"metric": "lifted poses/sec" + (" (eval inference)" if workload in ("eval", "vit_eval") else " (fwd+bwd+Adam)"),
                 "value": value, "unit": "poses/s", "n_gpus": world, "steps": steps, "warmup": warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype,
                 "data": "synthetic (H36M-shaped keypoints from the repo's mean/std statistics, random-init weights)",
@@ -534,7 +637,7 @@ def gpu_arm(args, rank, world, local_rank):
                                                  "model_tflops", "gpu_launches_per_step")}
         line["inference"]["workload"] = inf["config"]["workload"]
     ok = True
-    if world > 1 and args.workload != "eval" and not profiling:
+    if world > 1 and args.workload not in ("eval", "vit", "vit_eval") and not profiling:
         line["dp_check"] = dp_check(args.workload)
         ok = line["dp_check"]["ok"]
     if rank == 0:
@@ -617,6 +720,46 @@ def gemm_roofline(cabi, dev, rows, fmt, pk, H=H, profiling=False):
     return out
 
 
+def vit_gemm_roofline(cabi, dev, T, fmt, pk):
+    """The dominant GEMM of the transformer lifter alone: the MLP-up projection with bias + GELU in the epilogue,
+    u [T][256] x W1 [1024][256]^T -> m [T][1024] (baselineModel.py:294-296), operands rotated past L2."""
+    import ctypes as C
+
+    import torch
+    Hd, sets = VIT_H, 4
+    dt = torch.float16 if fmt == cabi.FMT_F16 else torch.bfloat16
+    A = [torch.randn(T, Hd, device=dev).to(dt) for _ in range(sets)]
+    W = (torch.randn(4 * Hd, Hd, device=dev) / 16).to(dt)
+    bias = torch.randn(4 * Hd, device=dev)
+    D = [torch.empty(T, 4 * Hd, device=dev, dtype=dt) for _ in range(sets)]
+    descs = []
+    for i in range(sets):
+        d = cabi.GemmDesc()
+        d.A, d.lda, d.B, d.ldb = A[i].data_ptr(), Hd, W.data_ptr(), Hd
+        d.M, d.N, d.K, d.fmt, d.out_mode, d.D, d.ldd, d.relu, d.splits = T, 4 * Hd, Hd, fmt, cabi.OUT_16, D[i].data_ptr(), 4 * Hd, 2, 1
+        d.shift = bias.data_ptr()
+        descs.append(d)
+    lib, st = cabi.lib(), cabi.stream_ptr()
+    for i in range(6):
+        cabi.check(lib.lifter_gemm(C.byref(descs[i % sets]), st))
+    torch.cuda.synchronize()
+    reps = 20
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(reps):
+        cabi.check(lib.lifter_gemm(C.byref(descs[i % sets]), st))
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / reps * 1e3
+    tflop = 2.0 * T * 4 * Hd * Hd / 1e12
+    return {"bound": "tensor", "kernel": f"lifter_gemm_kernel<256, 2-SM, GELU> M={T} N=1024 K=256 (+bias+GELU epilogue)",
+            "achieved": tflop / (us / 1e6), "peak": pk["bf16"], "unit": "TFLOP/s", "frac": tflop / (us / 1e6) / pk["bf16"],
+            "us_per_launch": us, "traffic": None, "algorithmic_bytes": 2.0 * (T * Hd + 4 * Hd * Hd + T * 4 * Hd),
+            "peak_source": pk.get("source"),
+            "note": "K = 256: four K-blocks per tile, so the epilogue (bias + GELU + 16-bit store), not the MMA, bounds this launch; "
+                    "the step as a whole is a mix of such GEMMs and HBM-bound row kernels (profiles/README.md)"}
+
+
 def hbm_rooflines(cabi, dev, pk, batch):
     """The HBM-bound kernels of the step timed alone with CUDA events: fused Adam over the flat buffer
     (28 B/param + 2 B operand copy) and the fused loss + gradient + metric kernel (612 B/pose)."""
@@ -690,8 +833,10 @@ def main():
         r = cpu_arm(args.workload, steps=args.steps, warmup=args.warmup, budget_s=100.0)
         what = {"eval": "configs[1] eval inference, batch 65536", "train": "configs[2] training step, batch 8192",
                 "wide": "configs[4] widened-lifter training step, batch 8192",
-                "phase5": "configs[3] phase-5 loop body around the lifter, batch 8192"}[args.workload]
-        line = {"impl": "reference", "metric": "lifted poses/sec" + (" (eval inference)" if args.workload == "eval" else " (fwd+bwd+Adam)"),
+                "phase5": "configs[3] phase-5 loop body around the lifter, batch 8192",
+                "vit": "SURVEY 8 f1 MyViT training step (GPU arm: batch 8192)",
+                "vit_eval": "SURVEY 8 f1 MyViT eval inference (GPU arm: batch 65536)"}[args.workload]
+        line = {"impl": "reference", "metric": "lifted poses/sec" + (" (eval inference)" if args.workload in ("eval", "vit_eval") else " (fwd+bwd+Adam)"),
                 "value": r["value"], "unit": "poses/s", "n_gpus": args.gpus, "steps": r["steps_timed"], "warmup": args.warmup,
                 "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "fp32", "data": "synthetic (same generator as the GPU arm)",
