@@ -79,6 +79,7 @@ struct alignas(64) GemmParams {
     int M, N, K;
     int num_m_blocks, num_n_blocks, splits, k_blocks_total, k_blocks_per_split, num_tiles;   // num_tiles counts M-groups
     int a_mn_major, b_mn_major, fmt, out_mode, relu, has_affine, has_residual, affine_n;
+    int resid_mul_gelu_grad;           // GELU instantiation only: result *= GELU'(residual) instead of GELU(result) + residual
     const float* scale;
     const float* shift;
     float* out_direct;
@@ -168,6 +169,20 @@ __device__ __forceinline__ float gelu_erf(float x) {
     p = fmaf(p, t, 0.5f * 0.254829592f);
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * (-0.5f * 1.4426950408889634f)));
     return fmaf(-ax, p * t * e, fmaxf(x, 0.0f));                     // relu(x) - |x| Phi(-|x|)
+}
+
+// d GELU(x) / dx = Phi(x) + x phi(x), same polynomial
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+    const float ax = fabsf(x);
+    float t, e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(ax, 0.3275911f * 0.70710678118654752f, 1.0f)));
+    float p = fmaf(0.5f * 1.061405429f, t, 0.5f * -1.453152027f);
+    p = fmaf(p, t, 0.5f * 1.421413741f);
+    p = fmaf(p, t, 0.5f * -0.284496736f);
+    p = fmaf(p, t, 0.5f * 0.254829592f);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * (-0.5f * 1.4426950408889634f)));
+    const float tail = p * t * e;                                     // Phi(-|x|)
+    return fmaf(x, e * 0.3989422804014327f, x >= 0.0f ? 1.0f - tail : tail);
 }
 
 // arrive-and-wait of the epilogue warps of EVERY CTA of the grid (one thread per CTA talks to the counter; the grid is at
@@ -428,8 +443,10 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                         x[j] = fmaf(x[j], s_scale[col_base + c * 32 + j], s_shift[col_base + c * 32 + j]);
                 }
                 if constexpr (GELU) {          // torch.nn.GELU(); its own instantiation: the lifter's kernels carry none of it
+                    if (!p.resid_mul_gelu_grad) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) x[j] = gelu_erf(x[j]);
+                        for (int j = 0; j < 32; ++j) x[j] = gelu_erf(x[j]);
+                    }
                 } else if (p.relu) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.0f);
@@ -455,8 +472,13 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
 #pragma unroll
                             for (int e = 0; e < 4; ++e) {
                                 const float2 f = unpack16(w[e], fmt);
-                                x[qq * 8 + e * 2] += f.x;
-                                x[qq * 8 + e * 2 + 1] += f.y;
+                                if (GELU && p.resid_mul_gelu_grad) {
+                                    x[qq * 8 + e * 2] *= gelu_erf_grad(f.x);
+                                    x[qq * 8 + e * 2 + 1] *= gelu_erf_grad(f.y);
+                                } else {
+                                    x[qq * 8 + e * 2] += f.x;
+                                    x[qq * 8 + e * 2 + 1] += f.y;
+                                }
                             }
                         }
                     }
@@ -879,6 +901,9 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     p.fmt = a.fmt; p.out_mode = a.out_mode; p.relu = a.relu;
     p.has_affine = (a.scale != nullptr || a.shift != nullptr) ? 1 : 0;
     p.has_residual = a.residual != nullptr ? 1 : 0;
+    LIFTER_REQUIRE(a.residual_op == 0 || (a.residual_op == 1 && a.residual != nullptr && a.relu == 0 && a.N > 128),
+                   "gemm: residual_op 1 (multiply by GELU'(residual)) needs a residual, no activation and N > 128");
+    p.resid_mul_gelu_grad = a.residual_op == 1 ? 1 : 0;
     p.scale = a.scale; p.shift = a.shift;
     p.affine_n = (a.shift_valid > 0 && a.shift_valid < a.N) ? a.shift_valid : a.N;
     p.out_direct = static_cast<float*>(a.D); p.n_valid = a.n_valid;
@@ -911,8 +936,8 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     // a.cluster: 0 = auto, 1 = single-CTA tiles, 2 = pairs (when the shape allows).
     const bool pair = a.cluster != 1 && p.num_m_blocks >= 2 && a.N > 64;
     LIFTER_REQUIRE(a.relu >= 0 && a.relu <= 2, "gemm: activation %d (0 none, 1 ReLU, 2 GELU)", a.relu);
-    if (a.relu == 2) {                                     // GELU epilogue: the transformer lifter's MLP-up projection
-        LIFTER_REQUIRE(a.N > 128, "gemm: the GELU epilogue is built for N > 128 (got %d)", a.N);
+    if (a.relu == 2 || a.residual_op == 1) {               // GELU epilogue: the transformer lifter's MLP-up projection (forward)
+        LIFTER_REQUIRE(a.N > 128, "gemm: the GELU epilogue is built for N > 128 (got %d)", a.N);      // or its backward
         return pair ? launch_impl<256, true, true>(p, a, stream) : launch_impl<256, false, true>(p, a, stream);
     }
     if (a.N <= 64) return launch_impl<64, false>(p, a, stream);

@@ -51,6 +51,8 @@ struct GemmArgs {
     const float* shift = nullptr;             // per-column add      (nullptr = 0)
     int shift_valid = 0;                      // entries of scale/shift that exist (0 = N); columns past it use 1 / 0
     const void* residual = nullptr; long ldr = 0;   // 16-bit [M][ldr], added after the activation
+    int residual_op = 0;                            // 1: MULTIPLY the result by GELU'(residual) instead (backward of the
+                                                    // transformer lifter's GELU: d z1 = (d m) * GELU'(z1) in the dgrad epilogue)
     const float* residual32 = nullptr; long ldr32 = 0;   // OUT_32_TMA, one split: fp32 [M][ldr32] added after the activation (fp32 residual stream)
     float* stat_sum = nullptr;                // [4*ceil(M/128)][N] per-32-row-slab column sums of the stored values
     float* stat_sq = nullptr;                 // same, squares

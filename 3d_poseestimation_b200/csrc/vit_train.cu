@@ -728,12 +728,12 @@ int wgrad16(const unsigned short* dZ, int M_out, const unsigned short* X, int N_
 
 // dX [T][N_in] (16-bit) = dZ [T][M_out] W [M_out][N_in] (+ residual)
 int dgrad16(const unsigned short* dZ, int M_out, const void* W, int N_in, int T, unsigned short* dX, const unsigned short* residual,
-            int fmt, cudaStream_t st) {
+            int fmt, cudaStream_t st, int residual_op = 0) {
     GemmArgs g;
     g.A = dZ; g.lda = M_out;
     g.B = W; g.ldb = N_in; g.b_mn_major = 1;
     g.M = T; g.N = N_in; g.K = M_out; g.fmt = fmt; g.out_mode = OUT_16_TMA; g.D = dX; g.ldd = N_in;
-    if (residual != nullptr) { g.residual = residual; g.ldr = N_in; }
+    if (residual != nullptr) { g.residual = residual; g.ldr = N_in; g.residual_op = residual_op; }
     g.tag = "vit_dgrad";
     return gemm_launch(g, st);
 }
@@ -883,6 +883,11 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
     const int Ti = static_cast<int>(T);
     const unsigned short* S = static_cast<const unsigned short*>(saved);
     const unsigned row_blocks = static_cast<unsigned>(part_rows(T));
+    // LIFTER_VIT_FUSE_GELU_BWD=1: d z1 = (dhA W2) * GELU'(z1) in the epilogue of the data-gradient GEMM instead of a pointwise
+    // pass.  Measured SLOWER on B200 (3.53 vs 3.50 ms per step): that GEMM has K = 256 and is epilogue-bound already, the
+    // GELU' arithmetic costs it +190 us per launch against the 145 us pass it replaces.  Default off.
+    const char* fg = getenv("LIFTER_VIT_FUSE_GELU_BWD");
+    const bool fuse_gelu_bwd = fg != nullptr && fg[0] == '1' && Mm > 128;
     VitSide* side = vit_side();
     cudaStream_t ws = side != nullptr ? side->st : st;                 // weight-gradient stream
     auto fork = [&]() -> int { return side != nullptr ? order_after(side->fork, st, ws) : LIFTER_OK; };
@@ -924,8 +929,12 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
         LIFTER_PROPAGATE(wgrad16(B.dhA, H, S + L.m(b), Mm, Ti, H, B.slabs, G.w_mlp2 + static_cast<long>(b) * H * Mm, fmt, ws));
         LIFTER_PROPAGATE(side_done(&VitSide::dhA));
         if (!first) LIFTER_PROPAGATE(wait_side(&VitSide::dm));
-        LIFTER_PROPAGATE(dgrad16(B.dhA, H, w2, Mm, Ti, B.dm, nullptr, fmt, st));
-        LIFTER_PROPAGATE(pointwise(S + L.z1(b), B.dm, B.dm, T * Mm, 1, fmt, st));
+        if (fuse_gelu_bwd) {     // d z1 = (dhA W2) * GELU'(z1) in the epilogue of the data-gradient GEMM
+            LIFTER_PROPAGATE(dgrad16(B.dhA, H, w2, Mm, Ti, B.dm, S + L.z1(b), fmt, st, 1));
+        } else {
+            LIFTER_PROPAGATE(dgrad16(B.dhA, H, w2, Mm, Ti, B.dm, nullptr, fmt, st));
+            LIFTER_PROPAGATE(pointwise(S + L.z1(b), B.dm, B.dm, T * Mm, 1, fmt, st));
+        }
         LIFTER_PROPAGATE(fork());
         LIFTER_PROPAGATE(colsum16(B.dm, T, Mm, B.part_side, G.mlp_b1 + static_cast<long>(b) * Mm, fmt, ws));
         LIFTER_PROPAGATE(wgrad16(B.dm, Mm, S + L.u2(b), H, Ti, Mm, B.slabs, G.w_mlp1 + static_cast<long>(b) * Mm * H, fmt, ws));

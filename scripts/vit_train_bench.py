@@ -60,6 +60,10 @@ os.environ["LIFTER_VIT_WGRAD_STREAM"] = "0"          # A/B: weight gradients on 
 tr_1 = VT(pkg.MyViT().cuda().train(), lr=1e-4)
 ms_fused_one_stream = timed(lambda i: tr_1.step(*sets[i % 4]), reps=40, warm=5)
 del os.environ["LIFTER_VIT_WGRAD_STREAM"]
+os.environ["LIFTER_VIT_FUSE_GELU_BWD"] = "1"         # A/B: GELU backward in the epilogue of the data-gradient GEMM (default: own pass)
+tr_2 = VT(pkg.MyViT().cuda().train(), lr=1e-4)
+ms_fused_gelu_pass = timed(lambda i: tr_2.step(*sets[i % 4]), reps=40, warm=5)
+del os.environ["LIFTER_VIT_FUSE_GELU_BWD"]
 # CPU oracle on a bounded sample
 from oracle import vit_oracle as V  # noqa: E402
 params = {k: v.detach().cpu().clone().requires_grad_(k != "pos_embed") for k, v in m.state_dict().items()}
@@ -82,7 +86,7 @@ while time.perf_counter() - t0 < 10.0:
 cpu_s = (time.perf_counter() - t0) / reps
 print(json.dumps({
     "metric": "lifted poses/sec (MyViT fwd+bwd+Adam)", "value": B / ms_fused * 1e3, "unit": "poses/s", "n_gpus": 1,
-    "ms_per_step": ms_fused, "ms_per_step_eager_launches": ms_fused_eager, "ms_per_step_one_stream": ms_fused_one_stream, "gpu_launches": tr.graph_launches(),
+    "ms_per_step": ms_fused, "ms_per_step_eager_launches": ms_fused_eager, "ms_per_step_one_stream": ms_fused_one_stream, "ms_per_step_gelu_backward_in_dgrad_epilogue": ms_fused_gelu_pass, "gpu_launches": tr.graph_launches(),
     "autograd_torch_optim": {"value": B / ms * 1e3, "ms_per_step": ms, "ms_per_step_without_optimizer": ms_noopt},
     "higher_is_better": True,
     "dtype": "bf16 operands / activations / stored gradients, fp32 accumulate, fp32 parameters and parameter gradients",

@@ -166,12 +166,18 @@ def _check_grads(m, ref, rel_tol=3e-2):
         assert rel_l2(g, r) < rel_tol and cos > 0.999, f"{n}: rel {rel_l2(g, r):.3e} cos {cos:.6f}"
 
 
+@pytest.mark.parametrize("switches", [{}, {"LIFTER_VIT_FUSE_GELU_BWD": "1"}, {"LIFTER_VIT_WGRAD_STREAM": "0"}],
+                         ids=["default", "gelu-bwd-in-dgrad", "one-stream"])
 @pytest.mark.parametrize("fmt", ["bf16", "fp16"])
 @pytest.mark.parametrize("tag,cfg", [("default", {}), ("b3h8", dict(n_blocks=3, n_heads=8))])
-def test_vit_backward_matches_reference_golden(pkg, golden_dir, tag, cfg, fmt):
+def test_vit_backward_matches_reference_golden(pkg, golden_dir, tag, cfg, fmt, switches, monkeypatch):
     """loss.backward() (train_1.py:94-95) on the reference's golden inputs: the loss against the imported reference's,
     every parameter gradient against autograd through the oracle (itself pinned to the reference's gradients), and two
-    gradient tensors directly against the reference's.  16-bit operands and stored gradients: agreement to ~1e-2."""
+    gradient tensors directly against the reference's.  16-bit operands and stored gradients: agreement to ~1e-2.
+    ``switches``: the library's A/B paths (GELU backward in the data-gradient GEMM's epilogue; weight gradients on the
+    chain's own stream) must give the same gradients."""
+    for k, v in switches.items():
+        monkeypatch.setenv(k, v)
     g = np.load(os.path.join(golden_dir, "vit.npz"))
     params = V.numpy_init(11, **cfg)
     m = pkg.MyViT(**cfg)
@@ -300,3 +306,69 @@ def test_vit_fused_trainer_matches_the_autograd_loop(pkg, optimizer, use_graph):
     assert b.linear_mapper.weight.data_ptr() == tr.flat.data_ptr()
     with pytest.raises(ValueError):
         tr.step(xe[:, :5], xe)
+
+
+def _vt():
+    import importlib
+    return importlib.import_module("3d_poseestimation_b200.vit_trainer").VitTrainer
+
+
+def test_vit_fused_trainer_graph_replay_equals_eager_across_batch_sizes(pkg):
+    """Graph replay (device step state, one captured graph per batch size, at most three resident sizes) against the same
+    kernel sequence launched eagerly with host scalars: identical arithmetic, so the losses agree to fp32 round-off while
+    the batch size walks through five values (evicting and re-capturing graphs) and the learning rate changes."""
+    VT = _vt()
+    params = V.numpy_init(3)
+    a, b = pkg.MyViT(), pkg.MyViT()
+    a.load_state_dict(params)
+    b.load_state_dict(params)
+    ta, tb = VT(a.cuda().train(), lr=3e-4, optimizer="adamw"), VT(b.cuda().train(), lr=3e-4, optimizer="adamw", use_graph=False)
+    g = torch.Generator().manual_seed(9)
+    la, lb = [], []
+    for i, B in enumerate([32, 48, 64, 80, 96, 32, 32, 48, 48, 96, 96, 96]):
+        x, y = torch.randn(B, 17, 2, generator=g).cuda(), torch.randn(B, 17, 3, generator=g).cuda()
+        if i == 6:
+            ta.set_lr(1e-4)
+            tb.set_lr(1e-4)
+        la.append(ta.step(x, y).clone())
+        lb.append(tb.step(x, y).clone())
+    la, lb = torch.stack(la).cpu().numpy(), torch.stack(lb).cpu().numpy()
+    np.testing.assert_allclose(la, lb, rtol=2e-5)
+    assert len(ta._graphs) <= VT.MAX_RESIDENT_BATCH_SIZES and len(ta._bufs) <= VT.MAX_RESIDENT_BATCH_SIZES
+    assert rel_l2(ta.flat.cpu(), tb.flat.cpu()) < 1e-5
+    # optimiser state round trip into a fresh trainer + host-side parameter writes (load_state_dict copies into the re-homed views)
+    c = pkg.MyViT()
+    tc = VT(c.cuda().train(), lr=1e-4, optimizer="adamw")
+    c.load_state_dict(a.state_dict())
+    tc.refresh_operands()
+    tc.load_state_dict(ta.state_dict())
+    x, y = torch.randn(64, 17, 2, generator=g).cuda(), torch.randn(64, 17, 3, generator=g).cuda()
+    np.testing.assert_allclose(float(tc.step(x, y)), float(ta.step(x, y)), rtol=2e-5)
+    assert rel_l2(tc.flat.cpu(), ta.flat.cpu()) < 1e-5
+
+
+def test_vit_fused_trainer_at_the_bench_shape(pkg):
+    """The exact path ``bench.py --workload vit`` times (8,192 poses, bf16, graph replay): three steps against the autograd
+    loop over the same kernels, and run_epoch (host batches in, host losses out) against step()."""
+    VT = _vt()
+    torch.manual_seed(1)
+    a = pkg.MyViT().cuda().train()
+    b = pkg.MyViT().cuda().train()
+    b.load_state_dict(a.state_dict())
+    opt = torch.optim.Adam(a.parameters(), lr=1e-4)
+    tr = VT(b, lr=1e-4)
+    g = torch.Generator().manual_seed(2)
+    hosts = [(torch.randn(8192, 17, 2, generator=g).pin_memory(), torch.randn(8192, 17, 3, generator=g).pin_memory()) for _ in range(3)]
+    exp = []
+    for x, y in hosts:
+        opt.zero_grad()
+        loss = torch.nn.functional.mse_loss(a(x.cuda()), y.cuda())
+        loss.backward()
+        opt.step()
+        exp.append(float(loss))
+    got = tr.run_epoch(hosts).numpy()
+    np.testing.assert_allclose(got[:2], exp[:2], rtol=1e-4)
+    np.testing.assert_allclose(got, exp, rtol=3e-3)
+    assert tr.graph_launches() >= 60 and tr.step_count == 3
+    with pytest.raises(RuntimeError):
+        tr.run_epoch([(hosts[0][0].cuda(), hosts[0][1].cuda())])
