@@ -23,7 +23,11 @@ static int wgrad_splits(int M, int N, int K) {
     const int tiles = ceil_div(M, 128) * ceil_div(N, bn);
     int s = num_sms() / tiles;
     if (s < 1) s = 1;
-    if (s > 16) s = 16;
+    // K is the token count here (139,264 at 8,192 poses): a 256 x 256 gradient has two tiles, and the cap of 16 slabs the
+    // lifter's 8,192-row batches use would leave it on 32 of 148 SMs.  Up to 74 slabs while a slab keeps >= 2,048 rows.
+    const int by_rows = K / 2048 > 16 ? K / 2048 : 16;
+    const int cap = by_rows < 74 ? by_rows : 74;
+    if (s > cap) s = cap;
     return gemm_effective_splits(K, s);
 }
 
