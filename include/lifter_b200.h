@@ -177,7 +177,8 @@ int lifter_train_backward(const lifter_config_t* cfg, const lifter_train_ctx_t* 
  * the BatchNorm-backward chain.  The library creates, on first use and per device, two non-blocking streams and a few
  * timing-disabled events for this and keeps them until the process exits; they fork from and join back into `stream`
  * with events, so the call is still ordered on `stream` and legal under stream capture.  LIFTER_WGRAD_STREAM=0 keeps
- * everything on `stream` (the per-layer entry points above never use the side streams).                              */
+ * everything on `stream` (the per-layer entry points above never use the side streams).  lifter_vit_backward does the
+ * same with one more stream and six events of its own (LIFTER_VIT_WGRAD_STREAM=0: one stream).                         */
 
 /* Fused loss + gradient + MPJPE metric (losses.py:3-7, train_1.py:37,94,100; two2three.py:387-390).
  * kind 0: MSELoss(mean), 1: L1Loss(mean), 2: mean MPJPE.  out[0] = loss over `global_rows`, out[1..joints] =
