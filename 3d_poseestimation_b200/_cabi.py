@@ -226,6 +226,8 @@ def _cuda_device_of(obj, depth=0):
     if torch.is_tensor(obj):
         return obj.device if obj.is_cuda else None
     flat = getattr(obj, "_flat", None)                       # LinearModel
+    if not torch.is_tensor(flat):
+        flat = getattr(obj, "flat", None)                    # VitTrainer
     if torch.is_tensor(flat):
         return flat.device if flat.is_cuda else None
     if depth == 0:

@@ -46,7 +46,7 @@ def timed(fn, reps=5, warm=3):
 
 
 x = torch.randn(B, 17, 2, device="cuda")
-sweep = {c: timed(lambda: m.infer(x, chunk_poses=c)) for c in (2048, 4096, 8192, 16384)}
+sweep = {c: timed(lambda: m.infer(x, chunk_poses=c)) for c in (2048, 4096, 8192, 16384, 32768, 65536)}
 chunk = min(sweep, key=sweep.get)
 ms = sweep[chunk]
 xh = torch.randn(B, 17, 2).pin_memory()
