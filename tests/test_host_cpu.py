@@ -127,6 +127,20 @@ def test_cpu_forward_raises_no_fallback(pkg):
         m(torch.zeros(2, 17, 2))
 
 
+def test_fused_transformer_trainer_has_no_cpu_path(pkg):
+    """VitTrainer (the fused MyViT step) refuses a model that is not on a GPU, and argument errors come before any CUDA call."""
+    import importlib
+    VT = importlib.import_module("3d_poseestimation_b200.vit_trainer").VitTrainer
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        VT(pkg.MyViT())
+    with pytest.raises(TypeError):
+        VT(pkg.LinearModel(34, 51, linear_size=64, num_stage=1))
+    with pytest.raises(ValueError, match="out_d"):
+        VT(pkg.MyViT(chw=(1, 17, 3), out_d=2))
+    with pytest.raises(ValueError, match="optimizer"):
+        VT(pkg.MyViT(), optimizer="sgd")
+
+
 def test_product_does_not_import_oracle():
     pkgdir = os.path.join(ROOT, "3d_poseestimation_b200")
     for dirpath, _, files in os.walk(pkgdir):
