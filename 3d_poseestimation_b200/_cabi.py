@@ -161,6 +161,7 @@ SIGNATURES = {
     "lifter_adam_step_packed": (_I32, [_CFG, _P, _P, _P, _P, _F, _F, _F, _F, _F, _I32, _I32, _F, _P, _P, _I32, _P]),
     "lifter_adam_step_table": (_I32, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _F, _I32, _I32, _F, _P, _P, _I32, C.POINTER(AdamTable), _P]),
     "lifter_vit_map_grad": (_I32, [_P, _I32, _I32, _P, _P, _P]),
+    "lifter_dp_adam_step_table": (_I32, [C.POINTER(DpInfo), _I64, _P, _P, _F, _F, _F, _F, _I32, _F, _P, _I32, C.POINTER(AdamTable), _P]),
     "lifter_dp_adam_step": (_I32, [_CFG, C.POINTER(DpInfo), _P, _P, _F, _F, _F, _F, _I32, _F, _P, _I32, _P]),
     "lifter_vit_workspace_bytes": (_I64, [C.POINTER(VitDesc), _I64]),
     "lifter_vit_forward": (_I32, [C.POINTER(VitDesc), _P, _I64, _P, _P, _P]),

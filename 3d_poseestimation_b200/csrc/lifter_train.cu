@@ -896,6 +896,43 @@ int lifter_dp_adam_step(const lifter_config_t* cfg, const lifter_dp_t* dp, float
     return adam_step_dp(d, static_cast<cudaStream_t>(stream));
 }
 
+int lifter_dp_adam_step_table(const lifter_dp_t* dp, int64_t n, float* m, float* v, float beta1, float beta2, float eps,
+                              float weight_decay, int decoupled, float grad_scale, const lifter_step_state_t* state,
+                              int fmt, const lifter_adam_table_t* table, void* stream) {
+    LIFTER_REQUIRE(dp != nullptr && m && v && state && table, "dp_adam: null pointer");
+    LIFTER_REQUIRE(dp->world >= 2 && dp->world <= ADAM_DP_MAX_WORLD && dp->rank >= 0 && dp->rank < dp->world,
+                   "dp_adam: world %d / rank %d out of range", dp->world, dp->rank);
+    LIFTER_REQUIRE(fmt == FMT_F16 || fmt == FMT_BF16, "dp_adam: unknown operand format %d", fmt);
+    LIFTER_REQUIRE(n > 0 && n % 4 == 0, "dp_adam: the buffer length must be a positive multiple of 4");
+    LIFTER_REQUIRE(table->n >= 1 && table->n <= ADAM_MAX_WEIGHTS, "dp_adam: operand table with 1..%d ranges", ADAM_MAX_WEIGHTS);
+    AdamDpArgs d;
+    d.world = dp->world; d.rank = dp->rank;
+    for (int q = 0; q < dp->world; ++q) {
+        LIFTER_REQUIRE(dp->grad[q] && dp->params[q] && dp->operands[q] && dp->flags[q], "dp_adam: null peer buffer %d", q);
+        d.g_peer[q] = static_cast<const float*>(dp->grad[q]);
+        d.p_peer[q] = static_cast<float*>(dp->params[q]);
+        d.op_peer[q] = dp->operands[q];
+        d.flag_peer[q] = static_cast<unsigned*>(dp->flags[q]);
+    }
+    AdamArgs& a = d.a;
+    a.p = d.p_peer[d.rank]; a.g = d.g_peer[d.rank]; a.m = m; a.v = v; a.n = n;
+    a.lr = 0.0f; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay; a.decoupled = decoupled;
+    a.step = 1; a.grad_scale = grad_scale; a.dyn = reinterpret_cast<const float*>(state);
+    a.operands = d.op_peer[d.rank]; a.op_fmt = fmt; a.nw = table->n;
+    for (int t = 0; t < table->n; ++t) {
+        LIFTER_REQUIRE(table->p_off[t] >= 0 && table->numel[t] > 0 && table->p_off[t] + table->numel[t] <= n &&
+                       table->p_off[t] % 4 == 0 && table->numel[t] % 4 == 0 && table->op_off[t] % 4 == 0 && table->op_off[t] >= 0,
+                       "dp_adam: operand range %d must lie inside the buffer with offsets / length multiples of 4", t);
+        a.w_p_off[t] = table->p_off[t]; a.w_numel[t] = table->numel[t]; a.w_off[t] = table->op_off[t];
+        a.w_in[t] = 1; a.w_pad[t] = 1;
+    }
+    d.epoch = reinterpret_cast<const unsigned*>(state) + 1;
+    if (dp->mc_grad && dp->mc_params && dp->mc_operands && dp_multicast_enabled(dp->world)) {
+        d.mc_g = static_cast<const float*>(dp->mc_grad); d.mc_p = static_cast<float*>(dp->mc_params); d.mc_op = dp->mc_operands;
+    }
+    return adam_step_dp(d, static_cast<cudaStream_t>(stream));
+}
+
 int lifter_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                      float eps, float weight_decay, int decoupled, int step, float grad_scale, void* stream) {
     LIFTER_REQUIRE(p && g && m && v, "adam: null pointer");

@@ -33,14 +33,18 @@ class VitTrainer:
     """``VitTrainer(model, lr=1e-4, optimizer="adam")`` then ``loss = trainer.step(x, y)`` per batch.
 
     ``x``: (B, joints, in_d) key points, ``y``: (B, joints, 3) targets, both fp32 on the model's device.  ``step`` returns
-    the device scalar of the MSE loss (``float(loss)`` synchronises).  ``optimizer``: "adam" (L2 ``weight_decay``, default 0,
+    the device scalar of the MSE loss (``float(loss)`` synchronises).  ``world_size > 1`` (one process per GPU of one NVSwitch
+    box, ``torch.distributed`` initialised with NCCL for the plumbing): every rank steps on its own B rows, the loss is the
+    mean over all ``B * world_size`` rows (``step`` returns this rank's share, ``loss_value()`` the sum), and the optimiser
+    launch becomes the fused NVLink reduce-scatter / Adam / all-gather kernel of the lifter (``lifter_dp_adam_step_table``):
+    the model has no BatchNorm, so that kernel is the step's only exchange.  ``optimizer``: "adam" (L2 ``weight_decay``, default 0,
     ``torch.optim.Adam``) or "adamw" (decoupled, default 0.01, ``torch.optim.AdamW``); ``set_lr`` is what
     ``ReduceLROnPlateau`` would drive (train_1.py:41,106)."""
 
     MAX_RESIDENT_BATCH_SIZES = 3
 
     def __init__(self, model: MyViT, lr=1e-4, optimizer="adam", betas=(0.9, 0.999), eps=1e-8, weight_decay=None,
-                 use_graph=True):
+                 use_graph=True, world_size=1, rank=0, process_group=None):
         if not isinstance(model, MyViT):
             raise TypeError("VitTrainer drives the MyViT lifter")
         if model.out_d != 3:
@@ -58,6 +62,16 @@ class VitTrainer:
         self.use_graph = bool(use_graph)
         self.step_count = 0
         self.joints = model.chw[1]
+        self.world, self.rank, self.pg = int(world_size), int(rank), process_group
+        if self.world > 1:
+            import torch.distributed as dist
+            if not dist.is_initialized():
+                raise RuntimeError("VitTrainer(world_size > 1) needs torch.distributed (backend 'nccl') to be initialised")
+            if self.world > _cabi.DP_MAX_WORLD:
+                raise RuntimeError(f"VitTrainer: the NVLink exchange serves at most {_cabi.DP_MAX_WORLD} ranks (one NVSwitch box)")
+            if self.pg is None:
+                self.pg = dist.group.WORLD
+        self._dp = None
         with torch.cuda.device(dev):
             self._flatten()
             self.state = torch.zeros(8, dtype=torch.int32, device=dev)
@@ -87,9 +101,13 @@ class VitTrainer:
         self.n = o
         self.off = off
         self.w0 = off["w_qkv"][0]                                   # the weight regions are the tail [w0, n)
-        flat = torch.zeros(self.n, dtype=torch.float32, device=dev)
-        self.flat, self.grad = flat, torch.zeros_like(flat)
-        self.m_buf, self.v_buf = torch.zeros_like(flat), torch.zeros_like(flat)
+        n_op = self.n - self.w0
+        if self.world > 1:
+            flat, self.grad, sym_ops = self._symmetric_buffers(self.n, n_op)
+        else:
+            flat, self.grad, sym_ops = torch.zeros(self.n, dtype=torch.float32, device=dev), torch.zeros(self.n, dtype=torch.float32, device=dev), None
+        self.flat = flat
+        self.m_buf, self.v_buf = torch.zeros(self.n, dtype=torch.float32, device=dev), torch.zeros(self.n, dtype=torch.float32, device=dev)
         reg = lambda k, *shape: flat[off[k][0]:off[k][0] + off[k][1]].view(*shape)
 
         def rehome(p, view):
@@ -122,7 +140,16 @@ class VitTrainer:
         # 16-bit GEMM operands of the weight tail, refreshed by the optimiser pass from here on
         self.fmt = 0 if m.train_format == "fp16" else 1
         dt = torch.float16 if self.fmt == 0 else torch.bfloat16
-        self.operands = flat[self.w0:].to(dt)
+        if self.world > 1:
+            # every replica starts from rank 0's parameters (what DistributedDataParallel does at construction)
+            import torch.distributed as dist
+            dist.broadcast(flat, src=dist.get_global_rank(self.pg, 0), group=self.pg)
+            self.operands = sym_ops.view(dt)
+            self.operands.copy_(flat[self.w0:])
+            torch.cuda.synchronize(dev)
+            dist.barrier(group=self.pg)
+        else:
+            self.operands = flat[self.w0:].to(dt)
         self.gmap = torch.zeros((1 + m.input_d) * H, dtype=torch.float32, device=dev)
         d = _cabi.VitDesc()
         d.tokens, d.in_dim, d.hidden, d.heads, d.blocks = m.chw[1], m.input_d, H, m.n_heads, nb
@@ -146,6 +173,40 @@ class VitTrainer:
             t.p_off[i], t.numel[i], t.op_off[i] = off[k][0], n, off[k][0] - self.w0
         self.table = t
         m._packed.clear()
+
+    def _symmetric_buffers(self, n, n_op):
+        """Gradient, parameter and operand buffers in ONE NVLink symmetric allocation (peer-mapped on every rank), plus the
+        flag block of the fused reduce-scatter / Adam / all-gather kernel (``lifter_dp_adam_step_table``)."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        dev = self.device
+
+        def up(v):
+            return (v + 255) // 256 * 256
+        off_grad = _cabi.DP_FLAG_BYTES
+        off_par = off_grad + up(4 * n)
+        off_ops = off_par + up(4 * n)
+        total = off_ops + up(2 * n_op)
+        try:
+            buf = symm.empty(total, dtype=torch.uint8, device=dev)
+            buf.zero_()
+            hdl = symm.rendezvous(buf, self.pg)
+        except Exception as e:                                   # noqa: BLE001
+            raise RuntimeError(f"VitTrainer(world_size={self.world}): NVLink symmetric memory is unavailable ({e}); there is "
+                               "no NCCL fallback for this trainer") from e
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=self.pg)                              # every rank's buffer is zeroed before first use
+        dp = _cabi.DpInfo()
+        dp.world, dp.rank = self.world, self.rank
+        for p in range(self.world):
+            base = int(hdl.buffer_ptrs[p])
+            dp.flags[p], dp.grad[p], dp.params[p], dp.operands[p] = base, base + off_grad, base + off_par, base + off_ops
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)          # NVSwitch multicast view of the same buffer (0: none)
+        if mc:
+            dp.mc_grad, dp.mc_params, dp.mc_operands = mc + off_grad, mc + off_par, mc + off_ops
+        self._sym, self._sym_hdl, self._dp = buf, hdl, dp
+        return (buf[off_par:off_par + 4 * n].view(torch.float32), buf[off_grad:off_grad + 4 * n].view(torch.float32),
+                buf[off_ops:off_ops + 2 * n_op])
 
     def refresh_operands(self):
         """Call after writing parameters from the host side (``load_state_dict``, manual edits)."""
@@ -188,13 +249,20 @@ class VitTrainer:
         if state is not None:
             _cabi.check(lib.lifter_step_advance(_cabi.ptr(state), self.betas[0], self.betas[1], wd if self.decoupled else 0.0, st))
         _cabi.check(lib.lifter_vit_train_forward(d, _cabi.ptr(b["x"]), B, _cabi.ptr(b["saved"]), _cabi.ptr(b["out"]), st))
-        _cabi.check(lib.lifter_loss(_cabi.ptr(b["out"]), _cabi.ptr(b["y"]), B, self.joints, _cabi.LOSS_MSE, B, None,
+        _cabi.check(lib.lifter_loss(_cabi.ptr(b["out"]), _cabi.ptr(b["y"]), B, self.joints, _cabi.LOSS_MSE, B * self.world, None,
                                     _cabi.ptr(b["dpred"]), _cabi.ptr(b["lscratch"]), _cabi.ptr(self.loss_out), 0, st))
         _cabi.check(lib.lifter_vit_backward(d, _cabi.ptr(b["x"]), B, _cabi.ptr(b["saved"]), _cabi.ptr(b["dpred"]),
                                             _cabi.ptr(b["scratch"]), C.byref(self.G), None, st))
         _cabi.check(lib.lifter_vit_map_grad(_cabi.ptr(self.gmap), m.input_d, m.hidden_d,
                                             C.c_void_p(self.grad.data_ptr() + 4 * self.off["map_w"][0]),
                                             C.c_void_p(self.grad.data_ptr() + 4 * self.off["map_b"][0]), st))
+        if self._dp is not None:
+            # data parallel: rank r sums slice r of every rank's gradient over NVLink, runs Adam on it and stores the new
+            # parameters and operand copies into every rank's buffers -- one kernel, no collective call
+            _cabi.check(lib.lifter_dp_adam_step_table(C.byref(self._dp), self.n, _cabi.ptr(self.m_buf), _cabi.ptr(self.v_buf),
+                                                      self.betas[0], self.betas[1], self.eps, wd, int(self.decoupled), 1.0,
+                                                      _cabi.ptr(state), self.fmt, C.byref(self.table), st))
+            return
         _cabi.check(lib.lifter_adam_step_table(_cabi.ptr(self.flat), _cabi.ptr(self.grad), _cabi.ptr(self.m_buf),
                                                _cabi.ptr(self.v_buf), self.n, self.lr, self.betas[0], self.betas[1], self.eps, wd,
                                                int(self.decoupled), self.step_count + 1, 1.0,
@@ -225,13 +293,19 @@ class VitTrainer:
         b["x"].copy_(x, non_blocking=True)
         b["y"].copy_(y, non_blocking=True)
         if not self.use_graph or B not in self._warm:
-            # the first step at a batch size runs eagerly (plans, kernel attributes); it is a real step
+            # the first step at a batch size runs eagerly (plans, kernel attributes); it is a real step.  Data parallel: the
+            # exchange kernel takes its epoch from the device step state, so the eager step advances that state too
             lib = _cabi.lib()
             n0 = lib.lifter_launch_count()
-            self._enqueue(b, B, None)
+            if self._dp is not None:
+                if self._state_stale:
+                    self._sync_state()
+                self._enqueue(b, B, self.state)
+            else:
+                self._enqueue(b, B, None)
+                self._state_stale = True
             self._launches = int(lib.lifter_launch_count() - n0)
             self._warm.add(B)
-            self._state_stale = True
         else:
             g = self._graphs.get(B)
             if g is None:
@@ -262,6 +336,11 @@ class VitTrainer:
                 yd = y.to(self.device, non_blocking=True)
                 out[i:i + 1].copy_(self.step(xd, yd).reshape(1), non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
+            if self.world > 1:                                   # each rank holds its share of the global mean
+                import torch.distributed as dist
+                t = out.to(self.device)
+                dist.all_reduce(t, group=self.pg)
+                return t.cpu()
         return out.clone()
 
     def _sync_state(self):
@@ -274,6 +353,12 @@ class VitTrainer:
         self.state.view(torch.float32)[2] = self.lr
 
     def loss_value(self):
+        """Host read of the last step's loss (synchronises); data parallel: the sum of the ranks' shares = the global mean."""
+        if self.world > 1:
+            import torch.distributed as dist
+            t = self.loss_out[:1].clone()
+            dist.all_reduce(t, group=self.pg)
+            return float(t.item())
         return float(self.loss_out[0].item())
 
     def graph_launches(self):

@@ -391,8 +391,9 @@ def gpu_arm(args, rank, world, local_rank):
         return pkg.LinearModel(I_DIM, O_DIM, linear_size=H, num_stage=S, p_dropout=0.5, BN=True).to(dev)
 
     def build_trainer(workload, model, lr=1e-4, dp=True):
-        if workload == "vit":             # no exchange step: N GPUs run N independent replicas of the step
-            return importlib.import_module(PKG + ".vit_trainer").VitTrainer(model.train(), lr=lr, optimizer="adam")
+        if workload == "vit":             # no BatchNorm: the fused reduce-scatter / Adam / all-gather launch is the only exchange
+            kw = dict(world_size=world, rank=rank) if (dp and world > 1) else {}
+            return importlib.import_module(PKG + ".vit_trainer").VitTrainer(model.train(), lr=lr, optimizer="adam", **kw)
         kw = dict(world_size=world, rank=rank, require_symmetric=True) if (dp and world > 1) else {}
         if workload == "phase5":
             import numpy as np
@@ -480,7 +481,8 @@ def gpu_arm(args, rank, world, local_rank):
             dtype = "bf16 operands, fp32 accumulate/master weights"
             par = f"dp{world}"
             if workload == "vit":
-                par = f"replicas x{world} (no exchange step built for the transformer lifter)" if world > 1 else "single GPU"
+                par = (f"dp{world} (fused reduce-scatter/Adam/all-gather over NVLink symmetric memory; no BatchNorm, so no other "
+                       "exchange)") if world > 1 else "single GPU"
             elif world > 1:
                 par += " (in-kernel SyncBN exchange + fused reduce-scatter/Adam/all-gather over NVLink symmetric memory)"
             what = {"train": "training step fwd + MSE + bwd + Adam, dropout 0.5, batch {b}/GPU, synced BatchNorm, 1024-wide, "
@@ -629,6 +631,42 @@ def gpu_arm(args, rank, world, local_rank):
                 "update_rel_diff": ud, "running_mean_rel_diff": rmd, "replicas_identical": bool(same.item()),
                 "tolerance": tol, "ok": ok, "losses_dp": losses, "losses_single_process": ref_losses}
 
+    def dp_check_vit(k=3):
+        """The same check for the transformer lifter: N data-parallel VitTrainer ranks == one process on the concatenated batch."""
+        batch, lr = TRAIN_BATCH, 1e-4
+        glob = [[torch.cat(col) for col in zip(*[host_batch("vit", batch, 1000 * s + r) for r in range(world)])] for s in range(k)]
+        m = build_model("vit")
+        tr = build_trainer("vit", m, lr=lr)
+        p0 = tr.flat.clone()
+        losses = []
+        for s in range(k):
+            tr.step(*[t[rank * batch:(rank + 1) * batch].to(dev) for t in glob[s]])
+            losses.append(tr.loss_value())
+        torch.cuda.synchronize()
+        dp_flat = tr.flat.clone()
+        ref = build_model("vit")
+        tr_ref = build_trainer("vit", ref, lr=lr, dp=False)
+        ref_losses = []
+        for s in range(k):
+            tr_ref.step(*[t.to(dev) for t in glob[s]])
+            ref_losses.append(tr_ref.loss_value())
+        torch.cuda.synchronize()
+        loss_err = max(abs(a - b) / abs(b) for a, b in zip(losses, ref_losses))
+        pd = ((dp_flat - tr_ref.flat).norm() / tr_ref.flat.norm()).item()
+        ud = ((dp_flat - tr_ref.flat).norm() / (tr_ref.flat - p0).norm()).item()
+        other = dp_flat.clone()
+        dist.broadcast(other, src=0)
+        same = torch.tensor([1.0 if torch.equal(other, dp_flat) else 0.0], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        vals = torch.tensor([loss_err, pd, ud], device=dev, dtype=torch.float64)
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+        loss_err, pd, ud = [float(v) for v in vals]
+        tol = {"loss_rel_err": 1e-3, "param_rel_diff": 1e-3, "update_rel_diff": 0.2}
+        ok = loss_err < tol["loss_rel_err"] and pd < tol["param_rel_diff"] and ud < tol["update_rel_diff"] and bool(same.item())
+        return {"world": world, "steps": k, "batch_per_gpu": batch, "lr": lr, "loss_rel_err": loss_err, "param_rel_diff": pd,
+                "update_rel_diff": ud, "replicas_identical": bool(same.item()), "tolerance": tol, "ok": ok,
+                "losses_dp": losses, "losses_single_process": ref_losses}
+
     line = measure(args.workload, args.steps, args.warmup, True)
     if args.workload == "train" and world == 1 and not profiling:
         # the same lifter in eval mode (BASELINE.json configs[1]), reported beside the headline training number
@@ -637,7 +675,10 @@ def gpu_arm(args, rank, world, local_rank):
                                                  "model_tflops", "gpu_launches_per_step")}
         line["inference"]["workload"] = inf["config"]["workload"]
     ok = True
-    if world > 1 and args.workload not in ("eval", "vit", "vit_eval") and not profiling:
+    if world > 1 and args.workload == "vit" and not profiling:
+        line["dp_check"] = dp_check_vit()
+        ok = line["dp_check"]["ok"]
+    elif world > 1 and args.workload not in ("eval", "vit_eval") and not profiling:
         line["dp_check"] = dp_check(args.workload)
         ok = line["dp_check"]["ok"]
     if rank == 0:

@@ -335,6 +335,12 @@ int lifter_dp_adam_step(const lifter_config_t* cfg, const lifter_dp_t* dp, float
                         float eps, float weight_decay, int decoupled, float grad_scale,
                         const lifter_step_state_t* state, int fmt, void* stream);
 
+/* The same kernel for ANY flat fp32 buffer of n parameters (n % 4 == 0) with a table of dense 16-bit operand ranges (the
+ * data-parallel MyViT trainer): dp->grad / params / operands / flags must be set, dp->sync is not read.             */
+int lifter_dp_adam_step_table(const lifter_dp_t* dp, int64_t n, float* m, float* v, float beta1, float beta2, float eps,
+                              float weight_decay, int decoupled, float grad_scale, const lifter_step_state_t* state,
+                              int fmt, const lifter_adam_table_t* table, void* stream);
+
 /* Backward pass WITH the optimiser folded in (needs ctx->step_state): as soon as a layer's gradients are complete —
  * weight gradient reduced, its data-gradient GEMM done with the old weights — Adam/AdamW runs on that layer's range of
  * the flat buffer on a side stream while the layers below are still in backward.  With ctx->dp (world > 1, peer

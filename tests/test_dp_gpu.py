@@ -16,6 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CASES = [  # world, case, use_graph, fuse_optim, divergent_init
     (2, "small", "1", "1", "0"), (2, "bench", "1", "1", "0"), (2, "bench", "1", "0", "0"), (2, "small", "0", "1", "0"),
     (2, "small", "1", "1", "1"), (4, "bench", "1", "1", "0"), (8, "bench", "1", "1", "0"),
+    (2, "vit", "1", "1", "0"), (2, "vit", "0", "1", "0"), (4, "vit", "1", "1", "0"),      # the transformer lifter
 ]
 
 
