@@ -443,7 +443,7 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                         x[j] = fmaf(x[j], s_scale[col_base + c * 32 + j], s_shift[col_base + c * 32 + j]);
                 }
                 if constexpr (GELU) {          // torch.nn.GELU(); its own instantiation: the lifter's kernels carry none of it
-                    if (!p.resid_mul_gelu_grad) {
+                    if (p.relu == 2) {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) x[j] = gelu_erf(x[j]);
                     }
@@ -453,6 +453,16 @@ lifter_gemm_kernel(const __grid_constant__ GemmParams p) {
                 }
 
                 if (p.out_mode == OUT_16_TMA) {
+                    if constexpr (GELU) {      // fp32 residual stream folded into a 16-bit output (last block of the MyViT eval path)
+                        if (p.resid32 != nullptr && tile_ok && static_cast<int>(lane) < rows_valid && n0 + 32 <= p.N) {
+                            const float* rr = p.resid32 + static_cast<long>(row0 + lane) * p.ldr32 + n0;
+#pragma unroll
+                            for (int qq = 0; qq < 8; ++qq) {
+                                const float4 r4 = *reinterpret_cast<const float4*>(rr + 4 * qq);
+                                x[4 * qq] += r4.x; x[4 * qq + 1] += r4.y; x[4 * qq + 2] += r4.z; x[4 * qq + 3] += r4.w;
+                            }
+                        }
+                    }
                     const uint32_t half = c & 1;
                     const uint32_t dst = stg_addr + buf * 4096 + lane * 128;
                     if (half == 0) {
@@ -884,9 +894,11 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
         LIFTER_REQUIRE(a.n_valid > 0 && a.n_valid <= 64 && a.N <= 64, "gemm: direct fp32 output holds at most 64 columns");
     LIFTER_REQUIRE(a.stat_sum == nullptr || (a.out_mode == OUT_16_TMA && a.stat_sq != nullptr),
                    "gemm: column statistics ride on the 16-bit output");
-    LIFTER_REQUIRE(a.residual32 == nullptr || (a.out_mode == OUT_32_TMA && a.splits == 1 && a.ldr32 % 4 == 0 &&
-                                               (reinterpret_cast<uintptr_t>(a.residual32) & 15) == 0),
-                   "gemm: the fp32 residual rides on the single-slab fp32 output and needs 16-byte aligned rows");
+    LIFTER_REQUIRE(a.residual32 == nullptr || (((a.out_mode == OUT_32_TMA && a.splits == 1) ||
+                                                (a.out_mode == OUT_16_TMA && a.N > 128 && a.N % 32 == 0 && a.residual == nullptr)) &&
+                                               a.ldr32 % 4 == 0 && (reinterpret_cast<uintptr_t>(a.residual32) & 15) == 0),
+                   "gemm: the fp32 residual rides on the single-slab fp32 output, or on a 16-bit output with N > 128 and N % 32 == 0, "
+                   "and needs 16-byte aligned rows");
     LIFTER_REQUIRE(a.residual == nullptr || (a.out_mode == OUT_16_TMA && a.ldr % 8 == 0),
                    "gemm: the residual rides on the 16-bit output and needs a 16-byte row stride");
 
@@ -936,7 +948,8 @@ int gemm_launch(const GemmArgs& a, cudaStream_t stream) {
     // a.cluster: 0 = auto, 1 = single-CTA tiles, 2 = pairs (when the shape allows).
     const bool pair = a.cluster != 1 && p.num_m_blocks >= 2 && a.N > 64;
     LIFTER_REQUIRE(a.relu >= 0 && a.relu <= 2, "gemm: activation %d (0 none, 1 ReLU, 2 GELU)", a.relu);
-    if (a.relu == 2 || a.residual_op == 1) {               // GELU epilogue: the transformer lifter's MLP-up projection (forward)
+    if (a.relu == 2 || a.residual_op == 1 || (a.residual32 != nullptr && a.out_mode == OUT_16_TMA)) {
+        // the transformer lifter's instantiation: GELU epilogue of the MLP-up projection (forward), GELU' of its backward, fp32 residual on a 16-bit output
         LIFTER_REQUIRE(a.N > 128, "gemm: the GELU epilogue is built for N > 128 (got %d)", a.N);      // or its backward
         return pair ? launch_impl<256, true, true>(p, a, stream) : launch_impl<256, false, true>(p, a, stream);
     }

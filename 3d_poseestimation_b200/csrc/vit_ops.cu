@@ -440,10 +440,13 @@ int vit_forward(const VitDesc& d, const float* x, int64_t poses, void* workspace
         g2.A = m; g2.lda = d.mlp_dim; g2.B = w2; g2.ldb = d.mlp_dim; g2.M = M; g2.N = H; g2.K = d.mlp_dim; g2.fmt = d.fmt;
         g2.out_mode = OUT_32_TMA; g2.D = h0; g2.ldd = H; g2.shift = d.mlp_b2 + static_cast<long>(b) * H; g2.residual32 = h1; g2.ldr32 = H;
         g2.tag = "vit_mlp2";
+        if (b == d.blocks - 1) {       // only the head reads the final residual stream, as a 16-bit operand: store it as one (u)
+            g2.out_mode = OUT_16_TMA; g2.D = u;
+        }
         LIFTER_PROPAGATE(gemm_launch(g2, st));
     }
-    // the head's first Linear takes the final residual stream as a 16-bit operand: one conversion pass into u
-    LIFTER_PROPAGATE(prep_input(h0, T, H, H, nullptr, nullptr, u, d.fmt, st));
+    // no blocks: the head's first Linear takes the embedding (fp32) as a 16-bit operand through one conversion pass
+    if (d.blocks == 0) LIFTER_PROPAGATE(prep_input(h0, T, H, H, nullptr, nullptr, u, d.fmt, st));
     GemmArgs gh;                                                                // r = ReLU(h0 Wh1^T + b)    :336-338
     gh.A = u; gh.lda = H; gh.B = d.w_head1; gh.ldb = H; gh.M = M; gh.N = d.head_dim; gh.K = H; gh.fmt = d.fmt;
     gh.out_mode = OUT_16_TMA; gh.D = r; gh.ldd = d.head_dim; gh.shift = d.head_b1; gh.relu = 1; gh.tag = "vit_head1";

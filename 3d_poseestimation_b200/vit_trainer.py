@@ -366,9 +366,13 @@ class VitTrainer:
         return self._launches
 
     def state_dict(self):
-        return {"step": self.step_count, "lr": self.lr, "m": self.m_buf, "v": self.v_buf}
+        """Optimiser state.  Data parallel: rank r owns (and updates) slice r of ``m`` / ``v`` only -- save and load it per rank,
+        with the same world size."""
+        return {"step": self.step_count, "lr": self.lr, "m": self.m_buf, "v": self.v_buf, "world": self.world, "rank": self.rank}
 
     def load_state_dict(self, sd):
+        if int(sd.get("world", self.world)) != self.world or int(sd.get("rank", self.rank)) != self.rank:
+            raise ValueError("VitTrainer.load_state_dict: the optimiser state was saved by another rank / world size")
         self.step_count, self.lr = int(sd["step"]), float(sd["lr"])
         self.m_buf.copy_(sd["m"])
         self.v_buf.copy_(sd["v"])

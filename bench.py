@@ -61,7 +61,7 @@ VIT_H, VIT_N, VIT_NB = 256, 17, 2
 FLOP_PER_POSE_VIT_INFER = 2 * VIT_N * (2 * VIT_H + VIT_NB * (VIT_H * 3 * VIT_H + VIT_H * VIT_H + 2 * VIT_H * 4 * VIT_H)
                                        + VIT_H * (VIT_H // 2) + (VIT_H // 2) * 3) + VIT_NB * 4 * VIT_N * VIT_N * VIT_H
 FLOP_PER_POSE_VIT_TRAIN = 3 * FLOP_PER_POSE_VIT_INFER      # dgrad + wgrad ~ 2 x forward (no data gradient into the 2-wide input)
-VIT_EVAL_CHUNK = 65536                   # poses per pass of the eval kernel sequence: the whole batch (scripts/vit_bench.py sweep: 10.9 ms at 8,192, 9.9 ms at 65,536)
+VIT_EVAL_CHUNK = 32768                   # poses per pass of the eval kernel sequence (scripts/vit_bench.py sweep: 10.6 ms at 8,192, 9.6 at 32,768, 9.8 at 65,536)
 
 
 def peaks():
