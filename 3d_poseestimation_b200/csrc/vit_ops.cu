@@ -84,44 +84,54 @@ __global__ void __launch_bounds__(256) vit_embed_kernel(const float* __restrict_
 
 // out = LN2(LN1(in)) (g2 == nullptr: one LayerNorm).  in / out 16-bit [T][Hd]; statistics and affine in fp32, no
 // 16-bit rounding between the two norms.
+constexpr int LN_DEPTH = 4;                          // input rows a warp keeps in flight (cp.async ring, private to the warp)
 template <int NV, bool IN32 = false>
-__global__ void __launch_bounds__(256) vit_layernorm_kernel(const void* __restrict__ in, long T, const float* __restrict__ g1,
-                                                            const float* __restrict__ b1, const float* __restrict__ g2,
-                                                            const float* __restrict__ b2, float eps, void* __restrict__ out,
-                                                            int fmt) {
+__global__ void __launch_bounds__(256) vit_layernorm_kernel(const void* __restrict__ in, long T, long rows_per_warp,
+                                                            const float* __restrict__ g1, const float* __restrict__ b1,
+                                                            const float* __restrict__ g2, const float* __restrict__ b2, float eps,
+                                                            void* __restrict__ out, int fmt) {
     griddep_launch();
     griddep_wait();
-    const int lane = threadIdx.x & 31;
-    const long t0 = (static_cast<long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * VIT_RPW;
-    if (t0 >= T) return;
-    RowParams<NV> ln1, ln2;
-    load_row_params<NV>(ln1, g1, b1, lane);
-    if (g2 != nullptr) load_row_params<NV>(ln2, g2, b2, lane);
-    const long t1 = min(T, t0 + VIT_RPW);
+    extern __shared__ __align__(16) unsigned char ln_smem[];
     // IN32: the input rows are the fp32 residual stream (eval path): two 16-byte vectors per lane and 256 columns
     constexpr int VPR = IN32 ? 2 : 1;                                 // uint4 vectors per lane per 256 columns
-    const uint4* src = reinterpret_cast<const uint4*>(in);
-    uint4 cur[NV * VPR], nxt[NV * VPR];
-#pragma unroll
-    for (int k = 0; k < NV; ++k)
-#pragma unroll
-        for (int q = 0; q < VPR; ++q) cur[k * VPR + q] = src[t0 * (NV * 32 * VPR) + k * 32 * VPR + lane * VPR + q];
-    for (long t = t0; t < t1; ++t) {
-        if (t + 1 < t1) {                                             // next row in flight while this one is normalised
+    constexpr int ROWB = NV * 512 * VPR;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long t0 = (static_cast<long>(blockIdx.x) * 8 + wid) * rows_per_warp;
+    if (t0 >= T) return;
+    const long t1 = min(T, t0 + rows_per_warp);
+    unsigned char* ring = ln_smem + wid * (LN_DEPTH * ROWB) + lane * (16 * VPR);
+    const uint32_t ring_addr = smem_u32(ring);
+    auto issue = [&](long row, int slot) {            // lane l copies, and later reads, the same bytes: no barrier needed
+        if (row < t1) {
 #pragma unroll
             for (int k = 0; k < NV; ++k)
 #pragma unroll
-                for (int q = 0; q < VPR; ++q) nxt[k * VPR + q] = src[(t + 1) * (NV * 32 * VPR) + k * 32 * VPR + lane * VPR + q];
+                for (int q = 0; q < VPR; ++q)
+                    cp_async16(ring_addr + slot * ROWB + k * 512 * VPR + q * 16,
+                               static_cast<const char*>(in) + row * static_cast<long>(ROWB) + k * 512 * VPR + lane * (16 * VPR) + q * 16);
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+#pragma unroll
+    for (int k = 0; k < LN_DEPTH; ++k) issue(t0 + k, k);
+    RowParams<NV> ln1, ln2;
+    load_row_params<NV>(ln1, g1, b1, lane);
+    if (g2 != nullptr) load_row_params<NV>(ln2, g2, b2, lane);
+    int slot = 0;
+    for (long t = t0; t < t1; ++t) {
+        asm volatile("cp.async.wait_group %0;" :: "n"(LN_DEPTH - 1) : "memory");
         float v[NV][8];
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
+            const unsigned char* src = ring + slot * ROWB + k * 512 * VPR;
             if constexpr (IN32) {
-                const uint4 a = cur[k * 2], b = cur[k * 2 + 1];
+                const uint4 a = *reinterpret_cast<const uint4*>(src), b = *reinterpret_cast<const uint4*>(src + 16);
                 v[k][0] = __uint_as_float(a.x); v[k][1] = __uint_as_float(a.y); v[k][2] = __uint_as_float(a.z); v[k][3] = __uint_as_float(a.w);
                 v[k][4] = __uint_as_float(b.x); v[k][5] = __uint_as_float(b.y); v[k][6] = __uint_as_float(b.z); v[k][7] = __uint_as_float(b.w);
             } else {
-                const uint32_t wd[4] = {cur[k].x, cur[k].y, cur[k].z, cur[k].w};
+                const uint4 c = *reinterpret_cast<const uint4*>(src);
+                const uint32_t wd[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const float2 f = unpack16(wd[e], fmt);
@@ -130,12 +140,13 @@ __global__ void __launch_bounds__(256) vit_layernorm_kernel(const void* __restri
                 }
             }
         }
+        issue(t + LN_DEPTH, slot);
+        slot = slot + 1 == LN_DEPTH ? 0 : slot + 1;
         warp_layernorm<NV>(v, ln1, eps);
         if (g2 != nullptr) warp_layernorm<NV>(v, ln2, eps);
         store_row16<NV>(out, t, lane, v, fmt);
-#pragma unroll
-        for (int k = 0; k < NV * VPR; ++k) cur[k] = nxt[k];
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 // baselineModel.py:243-253.  qkv 16-bit [T][3 * Hd] = [q | k | v], each (head, d) major; o 16-bit [T][Hd].
@@ -324,20 +335,35 @@ int vit_embed(const VitDesc& d, const float* x, long T, void* h, const float* ln
     return LIFTER_OK;
 }
 
+template <int NV, bool IN32>
+static int layernorm_launch(const void* in, long T, const float* g1, const float* b1, const float* g2, const float* b2, float eps, void* out,
+                            int fmt, cudaStream_t st) {
+    constexpr int SMEM = 8 * LN_DEPTH * NV * 512 * (IN32 ? 2 : 1);
+    static PerDeviceOnce once;
+    bool* configured = once.slot();
+    if (!*configured) {
+        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_layernorm_kernel<NV, IN32>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        *configured = true;
+    }
+    // about four blocks per SM, at least VIT_RPW rows per warp (the ring's fill is paid once per warp)
+    long rows_per_warp = (T + 4L * num_sms() * 8 - 1) / (4L * num_sms() * 8);
+    if (rows_per_warp < VIT_RPW) rows_per_warp = VIT_RPW;
+    const unsigned blocks = static_cast<unsigned>((T + rows_per_warp * 8 - 1) / (rows_per_warp * 8));
+    LIFTER_CHECK_CUDA(launch_pdl(IN32 ? "vit_layernorm_kernel<fp32 in>" : "vit_layernorm_kernel", vit_layernorm_kernel<NV, IN32>, dim3(blocks), dim3(256),
+                                 static_cast<size_t>(SMEM), st, in, T, rows_per_warp, g1, b1, g2, b2, eps, out, fmt));
+    return LIFTER_OK;
+}
+
 int vit_layernorm(const void* in, long T, const float* g1, const float* b1, const float* g2, const float* b2, float eps, void* out,
                   int H, int fmt, cudaStream_t st) {
-    const unsigned row_blocks = static_cast<unsigned>((T + 8 * VIT_RPW - 1) / (8 * VIT_RPW));
-    VIT_DISPATCH_NV(H / 256, LIFTER_CHECK_CUDA(launch_pdl("vit_layernorm_kernel", vit_layernorm_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
-                                                          in, T, g1, b1, g2, b2, eps, out, fmt)));
+    VIT_DISPATCH_NV(H / 256, return (layernorm_launch<NV, false>(in, T, g1, b1, g2, b2, eps, out, fmt, st)));
     return LIFTER_OK;
 }
 
 // LayerNorm(s) of the fp32 residual stream -> 16-bit GEMM operand (eval path)
 static int vit_layernorm32(const float* in, long T, const float* g1, const float* b1, const float* g2, const float* b2, float eps,
                            void* out, int H, int fmt, cudaStream_t st) {
-    const unsigned row_blocks = static_cast<unsigned>((T + 8 * VIT_RPW - 1) / (8 * VIT_RPW));
-    VIT_DISPATCH_NV(H / 256, LIFTER_CHECK_CUDA(launch_pdl("vit_layernorm_kernel<fp32 in>", vit_layernorm_kernel<NV, true>, dim3(row_blocks), dim3(256), 0, st,
-                                                          static_cast<const void*>(in), T, g1, b1, g2, b2, eps, out, fmt)));
+    VIT_DISPATCH_NV(H / 256, return (layernorm_launch<NV, true>(static_cast<const void*>(in), T, g1, b1, g2, b2, eps, out, fmt, st)));
     return LIFTER_OK;
 }
 

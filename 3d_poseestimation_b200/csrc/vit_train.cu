@@ -298,17 +298,37 @@ __global__ void __launch_bounds__(256, NV == 1 ? 2 : 1) vit_ln_bwd_kernel(const 
 }
 
 // d linear_mapper: part [gridDim.x][1 + in_d][Hd]: block partials of sum_t dh[t][c] (bias) and sum_t dh[t][c] x[t][i]
+// Same row walk as vit_ln_bwd_kernel: `rows_per_warp` consecutive rows per warp, the next EMB_DEPTH gradient rows in flight in
+// a private cp.async ring, the next row's key point in registers, two blocks per SM (the first version loaded one row,
+// used it, loaded the next: 55 us for a 71 MB read).
+constexpr int EMB_DEPTH = 4;
 template <int NV>
 __global__ void __launch_bounds__(256) vit_embed_bwd_kernel(const void* __restrict__ dh, const float* __restrict__ x, long T,
-                                                            int in_d, float* __restrict__ part, const float* __restrict__ w,
-                                                            float* __restrict__ dx, int fmt) {
+                                                            long rows_per_warp, int in_d, float* __restrict__ part,
+                                                            const float* __restrict__ w, float* __restrict__ dx, int fmt) {
     griddep_launch();
     griddep_wait();
-    __shared__ float sh[8 * NV * 256];
-    constexpr int Hd = NV * 256;
-    const int lane = threadIdx.x & 31;
-    const long t0 = (static_cast<long>(blockIdx.x) * 8 + (threadIdx.x >> 5)) * VIT_RPW;
-    const long t1 = min(T, t0 + VIT_RPW);
+    extern __shared__ __align__(16) unsigned char emb_smem[];
+    constexpr int Hd = NV * 256, ROWB = NV * 512;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long t0 = min(T, (static_cast<long>(blockIdx.x) * 8 + wid) * rows_per_warp);
+    const long t1 = min(T, t0 + rows_per_warp);
+    unsigned char* ring = emb_smem + wid * (EMB_DEPTH * ROWB) + lane * 16;
+    const uint32_t ring_addr = smem_u32(ring);
+    auto issue = [&](long row, int slot) {
+        if (row < t1) {
+#pragma unroll
+            for (int v = 0; v < NV; ++v)
+                cp_async16(ring_addr + slot * ROWB + v * 512, static_cast<const char*>(dh) + row * (Hd * 2L) + v * 512 + lane * 16);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    auto load_x = [&](long row, float (&xi)[4]) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) xi[i] = (i < in_d && row < t1) ? x[row * in_d + i] : 0.0f;
+    };
+#pragma unroll
+    for (int k = 0; k < EMB_DEPTH; ++k) issue(t0 + k, k);
     float acc[5][NV][8];
 #pragma unroll
     for (int k = 0; k < 5; ++k)
@@ -316,12 +336,29 @@ __global__ void __launch_bounds__(256) vit_embed_bwd_kernel(const void* __restri
         for (int v = 0; v < NV; ++v)
 #pragma unroll
             for (int e = 0; e < 8; ++e) acc[k][v][e] = 0.0f;
+    float xn[4];
+    load_x(t0, xn);
+    int slot = 0;
     for (long t = t0; t < t1; ++t) {
-        float d[NV][8];
-        load_row16<NV>(dh, t, lane, d, fmt);
         float xi[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) xi[i] = i < in_d ? x[t * in_d + i] : 0.0f;
+        for (int i = 0; i < 4; ++i) xi[i] = xn[i];
+        load_x(t + 1, xn);
+        cp_async_wait_group<EMB_DEPTH - 1>();
+        float d[NV][8];
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            const uint4 r = *reinterpret_cast<const uint4*>(ring + slot * ROWB + v * 512);
+            const uint32_t wd[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack16(wd[e], fmt);
+                d[v][2 * e] = f.x;
+                d[v][2 * e + 1] = f.y;
+            }
+        }
+        issue(t + EMB_DEPTH, slot);
+        slot = slot + 1 == EMB_DEPTH ? 0 : slot + 1;
 #pragma unroll
         for (int v = 0; v < NV; ++v)
 #pragma unroll
@@ -342,6 +379,8 @@ __global__ void __launch_bounds__(256) vit_embed_bwd_kernel(const void* __restri
             }
         }
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    float* sh = reinterpret_cast<float*>(emb_smem);                    // the ring is dead: block reduction scratch [8][Hd]
     float* dst = part + static_cast<long>(blockIdx.x) * (1 + in_d) * Hd;
 #pragma unroll
     for (int k = 0; k < 5; ++k)
@@ -800,6 +839,26 @@ int ln_bwd(int nv, const void* x, const void* dy, const void* dres, long T, cons
     return LIFTER_OK;
 }
 
+template <int NV>
+int embed_bwd_launch(const void* dh, const float* x, long T, int in_d, float* part, int max_blocks, const float* w, float* dx, int fmt,
+                     int* blocks, cudaStream_t st) {
+    constexpr int SMEM = 8 * EMB_DEPTH * NV * 512;
+    static PerDeviceOnce once;
+    bool* configured = once.slot();
+    if (!*configured) {
+        LIFTER_CHECK_CUDA(cudaFuncSetAttribute(vit_embed_bwd_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+        *configured = true;
+    }
+    int grid = 2 * num_sms();
+    if (grid > max_blocks) grid = max_blocks;
+    const long rows_per_warp = (T + grid * 8L - 1) / (grid * 8L);
+    grid = static_cast<int>((T + rows_per_warp * 8 - 1) / (rows_per_warp * 8));
+    *blocks = grid;
+    LIFTER_CHECK_CUDA(launch_pdl("vit_embed_bwd_kernel", vit_embed_bwd_kernel<NV>, dim3(grid), dim3(256), static_cast<size_t>(SMEM), st,
+                                 dh, x, T, rows_per_warp, in_d, part, w, dx, fmt));
+    return LIFTER_OK;
+}
+
 int validate_train(const VitDesc& d) {
     LIFTER_PROPAGATE(vit_validate(d));
     LIFTER_REQUIRE(d.mlp_dim <= 2048 && 3 * d.hidden <= 2048, "vit training: hidden width %d unsupported (256 or 512)", d.hidden);
@@ -966,9 +1025,9 @@ int vit_backward(const VitDesc& d, const float* x, int64_t poses, const void* sa
         LIFTER_PROPAGATE(reduce_rows_f32(B.part, lnb, 4 * H, 4 * H, gln, st));
     }
     // ---- embedding: d linear_mapper (positional table has requires_grad = False, baselineModel.py:330) -------------------------------
-    VIT_DISPATCH_NV(nv, LIFTER_CHECK_CUDA(launch_pdl("vit_embed_bwd_kernel", vit_embed_bwd_kernel<NV>, dim3(row_blocks), dim3(256), 0, st,
-                                                     static_cast<const void*>(B.dhA), x, T, d.in_dim, B.part, d.map_w, dx, fmt)));
-    LIFTER_PROPAGATE(reduce_rows_f32(B.part, static_cast<int>(row_blocks), (1 + d.in_dim) * H, (1 + d.in_dim) * H, G.map, st));
+    int emb_blocks = 0;
+    VIT_DISPATCH_NV(nv, LIFTER_PROPAGATE((embed_bwd_launch<NV>(B.dhA, x, T, d.in_dim, B.part, static_cast<int>(row_blocks), d.map_w, dx, fmt, &emb_blocks, st))));
+    LIFTER_PROPAGATE(reduce_rows_f32(B.part, emb_blocks, (1 + d.in_dim) * H, (1 + d.in_dim) * H, G.map, st));
     return side != nullptr ? order_after(side->join, ws, st) : LIFTER_OK;       // the call is complete on `st`
 }
 
